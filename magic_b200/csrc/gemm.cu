@@ -1,0 +1,222 @@
+// Host-side planning and launch of the tcgen05 GEMM: tensor maps, split-K choice, finishing pass.
+#include "gemm.h"
+#include <cstdio>
+#include <cstring>
+
+namespace magic {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+// split-K partial sums (fp32 workspace) -> fused epilogue.  One thread per (row, 32-column chunk).
+template <int EPI>
+__global__ void gemm_finish_kernel(EpiArgs e, const float* __restrict__ ws, long long ws_ld, int M, int N) {
+  const int chunks = (N + 31) >> 5;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int row = (int)(idx / chunks);
+  const int c = (int)(idx % chunks);
+  if (row >= M) return;
+  const float4* src = reinterpret_cast<const float4*>(ws + (long long)row * ws_ld + c * 32);
+  uint32_t r[32];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    float4 v = src[q];
+    r[4 * q] = __float_as_uint(v.x);
+    r[4 * q + 1] = __float_as_uint(v.y);
+    r[4 * q + 2] = __float_as_uint(v.z);
+    r[4 * q + 3] = __float_as_uint(v.w);
+  }
+  float dummy = 0.f;
+  epilogue_chunk<EPI>(e, r, row, c * 32, M, N, dummy);
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+static cudaError_t set_smem() {
+  return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)kGemmSmemBytes);
+}
+
+std::string gemm_init() {
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t err = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (err != cudaSuccess || fn == nullptr || qres != cudaDriverEntryPointSuccess)
+      return std::string("cuTensorMapEncodeTiled not available: ") + cudaGetErrorString(err);
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  cudaError_t e = cudaSuccess;
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_STORE_F32>();
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_ACT>();
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_BCE>();
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_SIGMOID>();
+  if (e == cudaSuccess) e = set_smem<false, false, EPI_STORE_F32>();
+  if (e == cudaSuccess) e = set_smem<false, false, EPI_DACT>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32>();
+  if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
+  return "";
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements, 128B swizzle.
+static std::string make_tmap(CUtensorMap* out, const void* ptr, long long inner, long long outer, long long ld,
+                             int box_inner, int box_outer) {
+  if (!g_encode) return "gemm_init() not called";
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return "tensor map: base not 16-byte aligned";
+  if ((ld * 2) % 16 != 0) return "tensor map: row pitch not a multiple of 16 bytes";
+  if (inner <= 0 || outer <= 0) return "tensor map: empty extent";
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[160];
+    snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled failed (%d) inner=%lld outer=%lld ld=%lld box=%dx%d", (int)r,
+             inner, outer, ld, box_inner, box_outer);
+    return buf;
+  }
+  return "";
+}
+
+// Minimise waves * (k-blocks per item + fixed per-item overhead), see DESIGN.md "split-K".
+int choose_splitk(int tiles, int total_kb, int num_sms) {
+  const double overhead = 8.0;   // epilogue + pipeline fill, in k-block units
+  int best = 1;
+  double best_cost = 1e30;
+  int max_split = total_kb / 4;
+  if (max_split > 64) max_split = 64;
+  if (max_split < 1) max_split = 1;
+  for (int s = 1; s <= max_split; ++s) {
+    int per = (total_kb + s - 1) / s;
+    if ((long long)(s - 1) * per >= total_kb) continue;   // would leave an empty split
+    long long items = (long long)tiles * s;
+    long long waves = (items + num_sms - 1) / num_sms;
+    double cost = (double)waves * (per + overhead) * (s > 1 ? 1.02 : 1.0);
+    if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
+  }
+  return best;
+}
+
+std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
+  GemmPlan& pl = *out;
+  memset(&pl.args, 0, sizeof(pl.args));
+  pl.kind = p.kind;
+  pl.epi = p.epi;
+  if (p.ngroups < 1 || p.ngroups > kMaxGroups || p.nseg < 1 || p.nseg > kMaxSegs) return "bad ngroups/nseg";
+  const bool a_mn = p.kind == GEMM_WGRAD, b_mn = p.kind != GEMM_DGRAD;
+  for (int g = 0; g < p.ngroups; ++g)
+    for (int s = 0; s < p.nseg; ++s) {
+      const Mat& A = p.a[g][s];
+      const Mat& B = p.b[g][s];
+      std::string err;
+      if (!a_mn) {   // Mat[M,K]
+        if (A.cols != p.K) return "A cols != K";
+        err = make_tmap(&pl.args.ta[g][s], A.ptr, A.cols, A.rows, A.ld, kBlockK, kBlockM);
+      } else {       // Mat[K,M]
+        if (A.rows != p.K) return "A rows != K";
+        err = make_tmap(&pl.args.ta[g][s], A.ptr, A.cols, A.rows, A.ld, 64, kBlockK);
+      }
+      if (!err.empty()) return "A: " + err;
+      if (!b_mn) {   // Mat[N,K]
+        if (B.cols != p.K) return "B cols != K";
+        err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, kBlockN);
+      } else {       // Mat[K,N]
+        if (B.rows != p.K) return "B rows != K";
+        err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, 64, kBlockK);
+      }
+      if (!err.empty()) return "B: " + err;
+    }
+  GemmArgs& a = pl.args;
+  a.M = p.M;
+  a.N = p.N;
+  a.kblocks = (p.K + kBlockK - 1) / kBlockK;
+  a.nseg = p.nseg;
+  a.ngroups = p.ngroups;
+  a.tiles_m = (p.M + kBlockM - 1) / kBlockM;
+  a.tiles_n = (p.N + kBlockN - 1) / kBlockN;
+  const int tiles = a.tiles_m * a.tiles_n * a.ngroups;
+  const int total_kb = a.nseg * a.kblocks;
+  const bool linear = p.epi == EPI_STORE_F32;
+  const bool can_split = linear || (p.ws != nullptr && p.ngroups == 1 && (p.epi == EPI_ACT || p.epi == EPI_DACT));
+  int split = 1;
+  if (can_split) split = p.force_splitk > 0 ? p.force_splitk : choose_splitk(tiles, total_kb, num_sms);
+  {
+    int per = (total_kb + split - 1) / split;
+    while (split > 1 && (long long)(split - 1) * per >= total_kb) { --split; per = (total_kb + split - 1) / split; }
+  }
+  a.splitk = split;
+  pl.two_pass = false;
+  for (int g = 0; g < p.ngroups; ++g) a.epi[g] = p.e[g];
+  if (split > 1) {
+    if (linear) {
+      for (int g = 0; g < p.ngroups; ++g) a.epi[g].atomic = 1;   // caller zeroes the destination
+    } else {
+      pl.two_pass = true;
+      pl.ws = p.ws;
+      pl.ws_ld = p.ws_ld;
+      pl.finish_epi_kind = p.epi;
+      pl.finish_epi[0] = p.e[0];
+      EpiArgs st;
+      memset(&st, 0, sizeof st);
+      st.out = p.ws;
+      st.ld_out = p.ws_ld;
+      st.alpha = 1.f;
+      st.atomic = 1;
+      a.epi[0] = st;
+      pl.epi = EPI_STORE_F32;
+    }
+  }
+  const long long items = (long long)tiles * split;
+  pl.grid = (int)(items < num_sms ? items : num_sms);
+  pl.flops = 2.0 * p.M * (double)p.N * p.K * p.nseg * p.ngroups;
+  return "";
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
+  gemm_tcgen05_kernel<A_MN, B_MN, EPI><<<pl.grid, kGemmThreads, kGemmSmemBytes, s>>>(pl.args);
+}
+
+int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
+  int launches = 0;
+  if (pl.two_pass) {
+    cudaMemsetAsync(pl.ws, 0, sizeof(float) * pl.ws_ld * pl.args.M, s);
+  }
+  const int key = pl.kind * 8 + pl.epi;
+  switch (key) {
+    case GEMM_FWD * 8 + EPI_STORE_F32: launch_variant<false, true, EPI_STORE_F32>(pl, s); break;
+    case GEMM_FWD * 8 + EPI_ACT: launch_variant<false, true, EPI_ACT>(pl, s); break;
+    case GEMM_FWD * 8 + EPI_BCE: launch_variant<false, true, EPI_BCE>(pl, s); break;
+    case GEMM_FWD * 8 + EPI_SIGMOID: launch_variant<false, true, EPI_SIGMOID>(pl, s); break;
+    case GEMM_DGRAD * 8 + EPI_STORE_F32: launch_variant<false, false, EPI_STORE_F32>(pl, s); break;
+    case GEMM_DGRAD * 8 + EPI_DACT: launch_variant<false, false, EPI_DACT>(pl, s); break;
+    case GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32>(pl, s); break;
+    default:
+      if (err) *err = "gemm_launch: unsupported (kind, epilogue) combination";
+      return -1;
+  }
+  ++launches;
+  if (pl.two_pass) {
+    const int chunks = (pl.args.N + 31) / 32;
+    const long long n = (long long)pl.args.M * chunks;
+    const int bs = 256;
+    const int gs = (int)((n + bs - 1) / bs);
+    if (pl.finish_epi_kind == EPI_ACT)
+      gemm_finish_kernel<EPI_ACT><<<gs, bs, 0, s>>>(pl.finish_epi[0], pl.ws, pl.ws_ld, pl.args.M, pl.args.N);
+    else
+      gemm_finish_kernel<EPI_DACT><<<gs, bs, 0, s>>>(pl.finish_epi[0], pl.ws, pl.ws_ld, pl.args.M, pl.args.N);
+    ++launches;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    if (err) *err = std::string("gemm launch failed: ") + cudaGetErrorString(e);
+    return -1;
+  }
+  return launches;
+}
+
+}  // namespace magic

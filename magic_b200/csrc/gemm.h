@@ -1,0 +1,56 @@
+// Host-side planning and launch of the tcgen05 GEMM (gemm_sm100.cuh).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <string>
+#include "gemm_sm100.cuh"
+
+namespace magic {
+
+// A bf16 row-major matrix view in HBM: element (r, c) at ptr[r * ld + c].
+struct Mat {
+  const __nv_bfloat16* ptr = nullptr;
+  long long rows = 0, cols = 0, ld = 0;
+  Mat() {}
+  Mat(const __nv_bfloat16* p, long long r, long long c, long long l) : ptr(p), rows(r), cols(c), ld(l) {}
+};
+
+enum GemmKind : int {
+  GEMM_FWD = 0,    // D[M,N] = A[M,K] . B[K,N]        A: Mat[M,K]   B: Mat[K,N] (weights as stored)
+  GEMM_DGRAD = 1,  // D[M,N] = A[M,K] . B[N,K]^T      A: Mat[M,K]   B: Mat[N,K]
+  GEMM_WGRAD = 2,  // D[M,N] = A[K,M]^T . B[K,N]      A: Mat[K,M]   B: Mat[K,N]   (K = batch rows)
+};
+
+struct GemmPlan {
+  GemmArgs args;
+  int kind = 0, epi = 0, grid = 0;
+  // split-K with a non-linear epilogue: GEMM accumulates fp32 into ws (red.add), then finish applies epi
+  bool two_pass = false;
+  float* ws = nullptr;
+  long long ws_ld = 0;
+  EpiArgs finish_epi[kMaxGroups];
+  int finish_epi_kind = 0;
+  double flops = 0;
+};
+
+struct GemmProblem {
+  int kind = GEMM_FWD;
+  int epi = EPI_STORE_F32;
+  int ngroups = 1, nseg = 1;
+  Mat a[kMaxGroups][kMaxSegs], b[kMaxGroups][kMaxSegs];
+  EpiArgs e[kMaxGroups];
+  int M = 0, N = 0, K = 0;   // N: columns the epilogue writes (ACT: the output pitch)
+  int force_splitk = 0;      // 0 = heuristic
+  float* ws = nullptr;       // fp32 workspace [M, ws_ld] for two-pass split-K (ACT / DACT); may be null
+  long long ws_ld = 0;
+};
+
+// Returns empty string on success, else an error message.
+std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out);
+// Enqueue (workspace zeroing, GEMM, finishing pass) on the stream.  Returns the number of kernels launched.
+int gemm_launch(const GemmPlan& plan, cudaStream_t stream, std::string* err);
+std::string gemm_init();   // resolves cuTensorMapEncodeTiled, sets max dynamic smem on every variant
+int choose_splitk(int tiles, int total_kb, int num_sms);
+
+}  // namespace magic

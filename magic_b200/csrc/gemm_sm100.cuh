@@ -1,0 +1,416 @@
+// Persistent, warp-specialised tcgen05 GEMM for sm_100a.
+//
+//   D[M,N] = sum over segments s of  A_s[M,K] * B_s[K,N]     (bf16 in, fp32 accumulate in TMEM)
+//
+// One kernel serves every dense layer of the magic autoencoder step:
+//   forward   y = x.W        A K-major (activations [M,K]),  B MN-major (weights [K,N] as the reference
+//                             stores them, 8c/vae.py:93,347)
+//   dgrad     dx = dy.W^T    A K-major, B K-major
+//   wgrad     dW = x^T.dy    A MN-major, B MN-major (reduction over the batch)
+// "Segments" concatenate along K: they carry the bf16x3 split of the fp32 mode (hi*hi + hi*lo + lo*hi)
+// through one accumulator.  "Groups" batch independent problems of identical shape (the two optimisers'
+// wgrads) into one launch.  Split-K spreads long reductions with few output tiles over all SMs; partial
+// sums are combined with vector red.global.add.
+//
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
+// warps 2..5 = epilogue (TMEM -> registers -> fused epilogue -> global).  Two TMEM accumulator stages
+// (2 x 256 columns) let the epilogue of tile i overlap the MMAs of tile i+1.
+#pragma once
+#include <cuda.h>
+#include "ptx.cuh"
+
+namespace magic {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockN = 256;
+constexpr int kBlockK = 64;   // 64 bf16 = one 128-byte swizzle row
+constexpr int kStages = 4;
+constexpr int kUmmaK = 16;
+constexpr int kMaxGroups = 2;
+constexpr int kMaxSegs = 3;
+constexpr int kGemmThreads = 192;
+constexpr uint32_t kStageBytesA = kBlockM * kBlockK * 2;   // 16 KiB
+constexpr uint32_t kStageBytesB = kBlockN * kBlockK * 2;   // 32 KiB
+constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
+constexpr uint32_t kAtomBytes = 64 * kBlockK * 2;          // one 64(MN) x 64(K) MN-major TMA box
+constexpr uint32_t kTmemCols = 2 * kBlockN;                // 512: two accumulator stages
+constexpr uint32_t kGemmSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+
+enum EpiKind : int { EPI_STORE_F32 = 0, EPI_ACT = 1, EPI_DACT = 2, EPI_BCE = 3, EPI_SIGMOID = 4 };
+enum ActKind : int { ACT_NONE = 0, ACT_TANH = 1, ACT_ELU = 2 };
+
+struct EpiArgs {
+  void* out;                  // f32 (STORE_F32, SIGMOID) or bf16 (ACT, DACT, BCE)
+  void* out_lo;               // bf16 low part for the split (fp32) mode, or nullptr
+  long long ld_out;           // row pitch of out, elements
+  const __nv_bfloat16* aux;   // DACT: forward activations y;  BCE: target plane x
+  const __nv_bfloat16* aux_lo;
+  long long ld_aux;
+  int aux_split;              // DACT: aux row = r < aux_split ? r : r - aux_shift
+  int aux_shift;
+  float alpha;                // scale on the accumulator (STORE_F32/ACT/DACT), on the loss sum (BCE)
+  int n_valid;                // ACT/DACT: cols < n_valid are data; ACT writes 1.0 at col n_valid (bias column)
+  int act;                    // ActKind
+  int atomic;                 // STORE_F32: red.add instead of store (split-K)
+  int precise;                // 1: accurate tanhf/expm1f/logf;  0: MUFU approximations (bf16 mode)
+  float* scalar;              // BCE: sum of the per-element loss (scaled by alpha) is added here
+};
+
+struct GemmArgs {
+  CUtensorMap ta[kMaxGroups][kMaxSegs];
+  CUtensorMap tb[kMaxGroups][kMaxSegs];
+  EpiArgs epi[kMaxGroups];
+  int M, N;          // rows < M and cols < N are written
+  int kblocks;       // K blocks (of 64) per segment
+  int nseg, ngroups, splitk;
+  int tiles_m, tiles_n;
+};
+
+struct WorkItem {
+  int g, m0, n0, kb0, kb1;
+};
+
+__device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w) {
+  WorkItem it;
+  int nt = w % a.tiles_n;
+  int t = w / a.tiles_n;
+  int mt = t % a.tiles_m;
+  t /= a.tiles_m;
+  it.g = t % a.ngroups;
+  int ks = t / a.ngroups;
+  int total_kb = a.nseg * a.kblocks;
+  int per = (total_kb + a.splitk - 1) / a.splitk;
+  it.kb0 = ks * per;
+  it.kb1 = min(total_kb, it.kb0 + per);
+  it.m0 = mt * kBlockM;
+  it.n0 = nt * kBlockN;
+  return it;
+}
+
+// ---------------------------------------------------------------------------- epilogue math
+__device__ __forceinline__ float act_fwd(float x, int act, int precise) {
+  if (act == ACT_TANH) {
+    if (precise) return tanhf(x);
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+  }
+  if (act == ACT_ELU) {
+    if (precise) return x > 0.f ? x : expm1f(x);
+    return x > 0.f ? x : __expf(x) - 1.f;
+  }
+  return x;
+}
+// derivative written in terms of the OUTPUT y: tanh' = 1 - y^2 ; elu' = 1 (y > 0) else y + 1
+__device__ __forceinline__ float act_bwd_from_y(float y, int act) {
+  if (act == ACT_TANH) return 1.f - y * y;
+  if (act == ACT_ELU) return y > 0.f ? 1.f : y + 1.f;
+  return 1.f;
+}
+// softplus(b) and sigmoid(b) from t = exp(-|b|)
+__device__ __forceinline__ void softplus_sigmoid(float b, int precise, float& sp, float& sg) {
+  if (precise) {
+    float t = expf(-fabsf(b));
+    sp = fmaxf(b, 0.f) + log1pf(t);
+    float r = 1.f / (1.f + t);
+    sg = b >= 0.f ? r : t * r;
+  } else {
+    float t = __expf(-fabsf(b));
+    // log1p(t), t in (0,1]: t*P(t) keeps relative accuracy for tiny t (confident pixels dominate a trained model)
+    // degree-5 fit of log1p(t)/t on (0,1], max relative error 8.5e-6
+    float p = fmaf(t, -0.023868885f, 0.10122161f);
+    p = fmaf(t, p, -0.21004808f);
+    p = fmaf(t, p, 0.32520646f);
+    p = fmaf(t, p, -0.49936134f);
+    p = fmaf(t, p, 0.9999916f);
+    sp = fmaf(t, p, fmaxf(b, 0.f));
+    float r = __fdividef(1.f, 1.f + t);
+    sg = b >= 0.f ? r : t * r;
+  }
+}
+
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
+                                               int N, float& loss_acc) {
+  if (row >= M) return;
+  if constexpr (EPI == EPI_STORE_F32) {
+    float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      float v0 = __uint_as_float(r[j]) * e.alpha, v1 = __uint_as_float(r[j + 1]) * e.alpha;
+      float v2 = __uint_as_float(r[j + 2]) * e.alpha, v3 = __uint_as_float(r[j + 3]) * e.alpha;
+      if (col0 + j + 3 < N) {
+        if (e.atomic) ptx::red_add_v4(out + j, v0, v1, v2, v3);
+        else *reinterpret_cast<float4*>(out + j) = make_float4(v0, v1, v2, v3);
+      } else {
+        float v[4] = {v0, v1, v2, v3};
+        for (int q = 0; q < 4; ++q)
+          if (col0 + j + q < N) {
+            if (e.atomic) atomicAdd(out + j + q, v[q]);
+            else out[j + q] = v[q];
+          }
+      }
+    }
+  } else if constexpr (EPI == EPI_SIGMOID) {
+    float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      if (col0 + j < N) {
+        float sp, sg;
+        softplus_sigmoid(__uint_as_float(r[j]), 1, sp, sg);
+        out[j] = sg;
+      }
+    }
+  } else if constexpr (EPI == EPI_ACT) {
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      float v[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        int c = col0 + j + q;
+        float x = __uint_as_float(r[j + q]) * e.alpha;
+        v[q] = c < e.n_valid ? act_fwd(x, e.act, e.precise) : (c == e.n_valid ? 1.f : 0.f);
+      }
+      uint32_t h = ptx::pack_bf16(v[0], v[1]);
+      hi[j >> 1] = h;
+      lo[j >> 1] = ptx::pack_bf16(v[0] - ptx::bf16_lo(h), v[1] - ptx::bf16_hi(h));
+    }
+    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+    if (e.out_lo) {
+      uint4* ol =
+          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+    }
+  } else if constexpr (EPI == EPI_DACT) {
+    int ar = row < e.aux_split ? row : row - e.aux_shift;
+    const uint4* ap = reinterpret_cast<const uint4*>(e.aux + (long long)ar * e.ld_aux + col0);
+    uint32_t y[16], yl[16];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 t = ap[q];
+      y[4 * q] = t.x; y[4 * q + 1] = t.y; y[4 * q + 2] = t.z; y[4 * q + 3] = t.w;
+    }
+    if (e.aux_lo) {
+      const uint4* alp = reinterpret_cast<const uint4*>(e.aux_lo + (long long)ar * e.ld_aux + col0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 t = alp[q];
+        yl[4 * q] = t.x; yl[4 * q + 1] = t.y; yl[4 * q + 2] = t.z; yl[4 * q + 3] = t.w;
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 16; ++q) yl[q] = 0u;
+    }
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      float y0 = ptx::bf16_lo(y[j >> 1]) + ptx::bf16_lo(yl[j >> 1]);
+      float y1 = ptx::bf16_hi(y[j >> 1]) + ptx::bf16_hi(yl[j >> 1]);
+      float v0 = (col0 + j < e.n_valid) ? __uint_as_float(r[j]) * e.alpha * act_bwd_from_y(y0, e.act) : 0.f;
+      float v1 = (col0 + j + 1 < e.n_valid) ? __uint_as_float(r[j + 1]) * e.alpha * act_bwd_from_y(y1, e.act) : 0.f;
+      uint32_t h = ptx::pack_bf16(v0, v1);
+      hi[j >> 1] = h;
+      lo[j >> 1] = ptx::pack_bf16(v0 - ptx::bf16_lo(h), v1 - ptx::bf16_hi(h));
+    }
+    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+    if (e.out_lo) {
+      uint4* ol =
+          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+    }
+  } else if constexpr (EPI == EPI_BCE) {
+    // logits a -> loss += softplus(a) - x*a ; dA = sigmoid(a) - x      (x in {0,1}; 8c/vae.py:260-263)
+    const uint4* xp = reinterpret_cast<const uint4*>(e.aux + (long long)row * e.ld_aux + col0);
+    uint32_t x[16];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 t = xp[q];
+      x[4 * q] = t.x; x[4 * q + 1] = t.y; x[4 * q + 2] = t.z; x[4 * q + 3] = t.w;
+    }
+    uint32_t hi[16], lo[16];
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      float a0 = __uint_as_float(r[j]), a1 = __uint_as_float(r[j + 1]);
+      float x0 = ptx::bf16_lo(x[j >> 1]), x1 = ptx::bf16_hi(x[j >> 1]);
+      float sp0, sg0, sp1, sg1;
+      softplus_sigmoid(a0, e.precise, sp0, sg0);
+      softplus_sigmoid(a1, e.precise, sp1, sg1);
+      bool in0 = col0 + j < N, in1 = col0 + j + 1 < N;
+      float d0 = in0 ? sg0 - x0 : 0.f, d1 = in1 ? sg1 - x1 : 0.f;
+      if (in0) acc += sp0 - x0 * a0;
+      if (in1) acc += sp1 - x1 * a1;
+      uint32_t h = ptx::pack_bf16(d0, d1);
+      hi[j >> 1] = h;
+      lo[j >> 1] = ptx::pack_bf16(d0 - ptx::bf16_lo(h), d1 - ptx::bf16_hi(h));
+    }
+    loss_acc += acc;
+    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+    if (e.out_lo) {
+      uint4* ol =
+          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------- the kernel
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
+  extern __shared__ uint8_t smem_raw[];
+  // 128-byte swizzle atoms need 1024-byte aligned stage bases
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kStageBytesA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kStages;
+  uint64_t* tfull_bar = bars + 2 * kStages;
+  uint64_t* tempty_bar = bars + 2 * kStages + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_work = args.tiles_m * args.tiles_n * args.ngroups * args.splitk;
+
+  if (warp == 0 && lane == 0) {
+    for (int g = 0; g < args.ngroups; ++g)
+      for (int s = 0; s < args.nseg; ++s) {
+        ptx::tma_prefetch_desc(&args.ta[g][s]);
+        ptx::tma_prefetch_desc(&args.tb[g][s]);
+      }
+    for (int i = 0; i < kStages; ++i) {
+      ptx::mbar_init(&full_bar[i], 1);
+      ptx::mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tfull_bar[i], 1);
+      ptx::mbar_init(&tempty_bar[i], 128);
+    }
+    ptx::fence_barrier_init();
+  } else if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (one thread)
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const WorkItem it = decode_work(args, w);
+        for (int kb = it.kb0; kb < it.kb1; ++kb) {
+          const int seg = kb / args.kblocks;
+          const int k0 = (kb - seg * args.kblocks) * kBlockK;
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          ptx::mbar_expect_tx(&full_bar[stage], kStageBytes);
+          uint8_t* sa = smem_a + stage * kStageBytesA;
+          uint8_t* sb = smem_b + stage * kStageBytesB;
+          const CUtensorMap* ta = &args.ta[it.g][seg];
+          const CUtensorMap* tb = &args.tb[it.g][seg];
+          if constexpr (!A_MN) {
+            ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);              // box {64 k, 128 m}
+          } else {
+#pragma unroll
+            for (int i = 0; i < kBlockM / 64; ++i)                               // boxes {64 m, 64 k}
+              ptx::tma_load_2d(ta, &full_bar[stage], sa + i * kAtomBytes, it.m0 + 64 * i, k0);
+          }
+          if constexpr (!B_MN) {
+            ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);              // box {64 k, 256 n}
+          } else {
+#pragma unroll
+            for (int i = 0; i < kBlockN / 64; ++i)                               // boxes {64 n, 64 k}
+              ptx::tma_load_2d(tb, &full_bar[stage], sb + i * kAtomBytes, it.n0 + 64 * i, k0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(kBlockM, kBlockN, A_MN, B_MN);
+      // K-major SW128: 8-row groups 1024 B apart, K advance = 32 B inside the swizzle row.
+      // MN-major SW128: 64-element MN atoms kBlockK*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO),
+      //                 K advance = 16 rows * 128 B.
+      constexpr uint32_t a_lbo = A_MN ? kAtomBytes : 0, b_lbo = B_MN ? kAtomBytes : 0;
+      constexpr uint32_t a_kadv = A_MN ? kUmmaK * 128 : kUmmaK * 2, b_kadv = B_MN ? kUmmaK * 128 : kUmmaK * 2;
+      uint32_t stage = 0, phase = 0, iter = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
+        const WorkItem it = decode_work(args, w);
+        const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
+        ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kBlockN;
+        for (int kb = it.kb0; kb < it.kb1; ++kb) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t a_base = ptx::smem_u32(smem_a + stage * kStageBytesA);
+          const uint32_t b_base = ptx::smem_u32(smem_b + stage * kStageBytesB);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            const uint64_t da = ptx::make_smem_desc_sw128(a_base + k * a_kadv, a_lbo, 1024);
+            const uint64_t db = ptx::make_smem_desc_sw128(b_base + k * b_kadv, b_lbo, 1024);
+            ptx::umma_bf16(d_tmem, da, db, idesc, (kb > it.kb0 || k > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        ptx::umma_commit(&tfull_bar[acc]);        // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue warps (TMEM lane quarter = warp % 4)
+    const int q = warp & 3;
+    uint32_t iter = 0;
+    float loss_acc = 0.f;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
+      const WorkItem it = decode_work(args, w);
+      const EpiArgs& e = args.epi[it.g];
+      const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
+      ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+      ptx::tc_fence_after();
+      const int row = it.m0 + q * 32 + lane;
+      const int ncols = min(kBlockN, args.N - it.n0);
+      const int nchunks = (ncols + 31) >> 5;
+      for (int c = 0; c < nchunks; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kBlockN + c * 32, r);
+        ptx::tmem_ld_wait();
+        if (c == nchunks - 1) {   // all TMEM reads of this accumulator are done: hand it back to the MMA warp
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(&tempty_bar[acc]);
+        }
+        epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc);
+      }
+    }
+    if constexpr (EPI == EPI_BCE) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
+      if (lane == 0 && total_work > 0) atomicAdd(args.epi[0].scalar, loss_acc * args.epi[0].alpha);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+}  // namespace magic

@@ -1,0 +1,295 @@
+// Stand-alone self-test + micro-benchmark of the tcgen05 GEMM against a host double reference.
+// Build: see magic_b200/build.py (target selftest_gemm).  Run on a B200: ./selftest_gemm [bench]
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <vector>
+#include <string>
+#include "gemm.h"
+
+using namespace magic;
+
+#define CK(x)                                                                          \
+  do {                                                                                 \
+    cudaError_t e_ = (x);                                                              \
+    if (e_ != cudaSuccess) {                                                           \
+      printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__);  \
+      exit(2);                                                                         \
+    }                                                                                  \
+  } while (0)
+
+static uint32_t rng_state = 12345u;
+static float frand() {
+  rng_state = rng_state * 1664525u + 1013904223u;
+  return ((rng_state >> 8) & 0xFFFF) / 65536.0f - 0.5f;
+}
+static float bf16r(float x) { return __bfloat162float(__float2bfloat16(x)); }
+
+struct HostMat {
+  std::vector<float> v;   // bf16-rounded values
+  long long rows, cols, ld;
+  __nv_bfloat16* d = nullptr;
+  void init(long long r, long long c, long long l, float scale, bool binary = false) {
+    rows = r; cols = c; ld = l;
+    v.assign(r * l, 0.f);
+    std::vector<__nv_bfloat16> h(r * l);
+    for (long long i = 0; i < r; ++i)
+      for (long long j = 0; j < l; ++j) {
+        float x = j < c ? (binary ? (frand() > 0.3f ? 1.f : 0.f) : bf16r(frand() * scale)) : 7.0f;  // junk in the pad
+        v[i * l + j] = x;
+        h[i * l + j] = __float2bfloat16(x);
+      }
+    CK(cudaMalloc(&d, sizeof(__nv_bfloat16) * r * l));
+    CK(cudaMemcpy(d, h.data(), sizeof(__nv_bfloat16) * r * l, cudaMemcpyHostToDevice));
+  }
+  Mat mat() const { return Mat(d, rows, cols, ld); }
+  float at(long long r, long long c) const { return v[r * ld + c]; }
+};
+
+static int g_fail = 0;
+static void report(const char* name, double maxerr, double tol) {
+  printf("%-46s max_err %.3e  (tol %.1e)  %s\n", name, maxerr, tol, maxerr <= tol ? "OK" : "FAIL");
+  if (!(maxerr <= tol)) ++g_fail;
+}
+
+// reference D[M,N] for the three kinds, one group, nseg segments
+static void host_ref(int kind, int M, int N, int K, int nseg, const HostMat* a, const HostMat* b, std::vector<double>& D) {
+  D.assign((size_t)M * N, 0.0);
+  for (int s = 0; s < nseg; ++s)
+    for (int m = 0; m < M; ++m)
+      for (int n = 0; n < N; ++n) {
+        double acc = 0;
+        for (int k = 0; k < K; ++k) {
+          double av = kind == GEMM_WGRAD ? a[s].at(k, m) : a[s].at(m, k);
+          double bv = kind == GEMM_DGRAD ? b[s].at(n, k) : b[s].at(k, n);
+          acc += av * bv;
+        }
+        D[(size_t)m * N + n] += acc;
+      }
+}
+
+static void test_store(int kind, int M, int N, int K, int nseg, int split, int sms) {
+  HostMat a[3], b[3];
+  for (int s = 0; s < nseg; ++s) {
+    if (kind == GEMM_WGRAD) a[s].init(K, M, (M + 63) / 64 * 64, 1.f); else a[s].init(M, K, (K + 63) / 64 * 64, 1.f);
+    if (kind == GEMM_DGRAD) b[s].init(N, K, (K + 63) / 64 * 64, 1.f); else b[s].init(K, N, (N + 63) / 64 * 64, 1.f);
+  }
+  long long ldo = (N + 3) / 4 * 4;
+  float* dout;
+  CK(cudaMalloc(&dout, sizeof(float) * M * ldo));
+  CK(cudaMemset(dout, 0, sizeof(float) * M * ldo));
+  GemmProblem p;
+  p.kind = kind; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
+  for (int s = 0; s < nseg; ++s) { p.a[0][s] = a[s].mat(); p.b[0][s] = b[s].mat(); }
+  EpiArgs e = {};
+  e.out = dout; e.ld_out = ldo; e.alpha = 0.5f;
+  p.e[0] = e;
+  GemmPlan pl;
+  std::string err = gemm_plan(p, sms, &pl);
+  if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+  if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
+  CK(cudaDeviceSynchronize());
+  std::vector<float> h((size_t)M * ldo);
+  CK(cudaMemcpy(h.data(), dout, sizeof(float) * M * ldo, cudaMemcpyDeviceToHost));
+  std::vector<double> D;
+  host_ref(kind, M, N, K, nseg, a, b, D);
+  double me = 0;
+  for (int m = 0; m < M; ++m)
+    for (int n = 0; n < N; ++n) me = fmax(me, fabs(h[(size_t)m * ldo + n] - 0.5 * D[(size_t)m * N + n]));
+  char name[128];
+  snprintf(name, sizeof name, "store kind=%d M=%d N=%d K=%d nseg=%d split=%d(%d)", kind, M, N, K, nseg, split, pl.args.splitk);
+  report(name, me, 2e-3 * sqrt((double)K * nseg) * 0.1 + 1e-4);
+  for (int s = 0; s < nseg; ++s) { cudaFree(a[s].d); cudaFree(b[s].d); }
+  cudaFree(dout);
+}
+
+static void test_wgrad_groups(int M, int N, int K, int sms) {
+  HostMat a[2], b[2];
+  float* dout[2];
+  long long ldo = (N + 3) / 4 * 4;
+  GemmProblem p;
+  p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K;
+  for (int g = 0; g < 2; ++g) {
+    a[g].init(K, M, (M + 63) / 64 * 64, 1.f, true);
+    b[g].init(K, N, (N + 63) / 64 * 64, 1.f);
+    CK(cudaMalloc(&dout[g], sizeof(float) * M * ldo));
+    CK(cudaMemset(dout[g], 0, sizeof(float) * M * ldo));
+    p.a[g][0] = a[g].mat(); p.b[g][0] = b[g].mat();
+    EpiArgs e = {};
+    e.out = dout[g]; e.ld_out = ldo; e.alpha = 1.f;
+    p.e[g] = e;
+  }
+  GemmPlan pl;
+  std::string err = gemm_plan(p, sms, &pl);
+  if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+  if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
+  CK(cudaDeviceSynchronize());
+  double me = 0;
+  for (int g = 0; g < 2; ++g) {
+    std::vector<float> h((size_t)M * ldo);
+    CK(cudaMemcpy(h.data(), dout[g], sizeof(float) * M * ldo, cudaMemcpyDeviceToHost));
+    std::vector<double> D;
+    host_ref(GEMM_WGRAD, M, N, K, 1, &a[g], &b[g], D);
+    for (int m = 0; m < M; ++m)
+      for (int n = 0; n < N; ++n) me = fmax(me, fabs(h[(size_t)m * ldo + n] - D[(size_t)m * N + n]));
+  }
+  char name[128];
+  snprintf(name, sizeof name, "wgrad 2 groups M=%d N=%d K=%d split=%d", M, N, K, pl.args.splitk);
+  report(name, me, 2e-3 * sqrt((double)K) * 0.1 + 1e-4);
+}
+
+static double sigm(double x) { return 1.0 / (1.0 + exp(-x)); }
+
+// ACT (fwd, optional two-pass), DACT (dgrad), BCE (fwd)
+static void test_fused(int epi, int M, int Nv, int K, int split, int precise, int sms) {
+  const int kind = epi == EPI_DACT ? GEMM_DGRAD : GEMM_FWD;
+  const long long ldo = (Nv + 1 + 63) / 64 * 64;
+  HostMat a, b, aux;
+  a.init(M, K, (K + 63) / 64 * 64, 1.f);
+  if (kind == GEMM_DGRAD) b.init(Nv + 1, K, (K + 63) / 64 * 64, 0.5f); else b.init(K, Nv, (Nv + 63) / 64 * 64, 0.5f);
+  aux.init(M, ldo, ldo, 1.f, epi == EPI_BCE);
+  __nv_bfloat16 *dout, *dlo;
+  CK(cudaMalloc(&dout, 2 * M * ldo));
+  CK(cudaMalloc(&dlo, 2 * M * ldo));
+  CK(cudaMemset(dout, 0xFF, 2 * M * ldo));
+  float* scalar;
+  CK(cudaMalloc(&scalar, 4));
+  CK(cudaMemset(scalar, 0, 4));
+  float* ws = nullptr;
+  CK(cudaMalloc(&ws, sizeof(float) * M * ldo));
+  GemmProblem p;
+  p.kind = kind; p.epi = epi; p.M = M; p.K = K; p.force_splitk = split;
+  p.N = epi == EPI_BCE ? Nv : (int)ldo;
+  p.a[0][0] = a.mat(); p.b[0][0] = b.mat();
+  p.ws = ws; p.ws_ld = ldo;
+  EpiArgs e = {};
+  e.out = dout; e.out_lo = dlo; e.ld_out = ldo; e.alpha = epi == EPI_BCE ? 0.25f : 1.f; e.n_valid = Nv;
+  e.act = ACT_TANH; e.precise = precise; e.aux = aux.d; e.ld_aux = ldo; e.aux_split = M / 2; e.aux_shift = epi == EPI_DACT ? M / 4 : 0;
+  e.scalar = scalar;
+  if (epi != EPI_DACT) { e.aux_split = 1 << 30; }
+  p.e[0] = e;
+  GemmPlan pl;
+  std::string err = gemm_plan(p, sms, &pl);
+  if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+  if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
+  CK(cudaDeviceSynchronize());
+  std::vector<__nv_bfloat16> h(M * ldo), hl(M * ldo);
+  CK(cudaMemcpy(h.data(), dout, 2 * M * ldo, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(hl.data(), dlo, 2 * M * ldo, cudaMemcpyDeviceToHost));
+  float hs = 0;
+  CK(cudaMemcpy(&hs, scalar, 4, cudaMemcpyDeviceToHost));
+  double me = 0, me_pad = 0, loss = 0;
+  const int Ncols = epi == EPI_BCE ? Nv : (int)ldo;
+  for (int m = 0; m < M; ++m)
+    for (int n = 0; n < Ncols; ++n) {
+      double acc = 0;
+      if (n < (kind == GEMM_DGRAD ? Nv + 1 : Nv))
+        for (int k = 0; k < K; ++k) acc += (double)a.at(m, k) * (kind == GEMM_DGRAD ? b.at(n, k) : b.at(k, n));
+      double want;
+      if (epi == EPI_ACT) want = n < Nv ? tanh(acc) : (n == Nv ? 1.0 : 0.0);
+      else if (epi == EPI_DACT) {
+        int ar = m < M / 2 ? m : m - M / 4;
+        double y = aux.at(ar, n);
+        want = n < Nv ? acc * (1 - y * y) : 0.0;
+      } else {
+        double x = aux.at(m, n);
+        want = sigm(acc) - x;
+        loss += log1p(exp(-fabs(acc))) + fmax(acc, 0.0) - x * acc;
+      }
+      double got = (double)__bfloat162float(h[m * ldo + n]) + (double)__bfloat162float(hl[m * ldo + n]);
+      double err1 = fabs(got - want);
+      if (n < Nv) me = fmax(me, err1); else me_pad = fmax(me_pad, err1);
+    }
+  char name[128];
+  snprintf(name, sizeof name, "fused epi=%d M=%d Nv=%d K=%d split=%d(%d,2pass=%d) prec=%d", epi, M, Nv, K, split,
+           pl.args.splitk, (int)pl.two_pass, precise);
+  report(name, me, precise ? 3e-4 : 4e-3);
+  if (epi != EPI_BCE) report("   pad/ones columns", me_pad, 0.0);
+  if (epi == EPI_BCE) {
+    double rel = fabs(hs - 0.25 * loss) / fabs(0.25 * loss);
+    report("   bce loss sum (relative)", rel, precise ? 1e-5 : 1e-4);
+  }
+  cudaFree(a.d); cudaFree(b.d); cudaFree(aux.d); cudaFree(dout); cudaFree(dlo); cudaFree(scalar); cudaFree(ws);
+}
+
+static void bench(int kind, int M, int N, int K, int split, int sms, const char* label) {
+  __nv_bfloat16 *a, *b;
+  size_t na = (size_t)(kind == GEMM_WGRAD ? K : M) * (kind == GEMM_WGRAD ? (M + 63) / 64 * 64 : (K + 63) / 64 * 64);
+  size_t nb = (size_t)(kind == GEMM_DGRAD ? N : K) * (kind == GEMM_DGRAD ? (K + 63) / 64 * 64 : (N + 63) / 64 * 64);
+  CK(cudaMalloc(&a, na * 2)); CK(cudaMalloc(&b, nb * 2));
+  CK(cudaMemset(a, 0, na * 2)); CK(cudaMemset(b, 0, nb * 2));
+  float* out;
+  long long ldo = (N + 3) / 4 * 4;
+  CK(cudaMalloc(&out, sizeof(float) * M * ldo));
+  CK(cudaMemset(out, 0, sizeof(float) * M * ldo));
+  GemmProblem p;
+  p.kind = kind; p.epi = EPI_STORE_F32; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
+  p.a[0][0] = kind == GEMM_WGRAD ? Mat(a, K, M, (M + 63) / 64 * 64) : Mat(a, M, K, (K + 63) / 64 * 64);
+  p.b[0][0] = kind == GEMM_DGRAD ? Mat(b, N, K, (K + 63) / 64 * 64) : Mat(b, K, N, (N + 63) / 64 * 64);
+  EpiArgs e = {};
+  e.out = out; e.ld_out = ldo; e.alpha = 1.f;
+  p.e[0] = e;
+  GemmPlan pl;
+  std::string err = gemm_plan(p, sms, &pl);
+  if (!err.empty()) { printf("plan error: %s\n", err.c_str()); return; }
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  for (int i = 0; i < 3; ++i) gemm_launch(pl, 0, &err);
+  CK(cudaDeviceSynchronize());
+  const int iters = 10;
+  cudaEventRecord(e0);
+  for (int i = 0; i < iters; ++i) gemm_launch(pl, 0, &err);
+  cudaEventRecord(e1);
+  CK(cudaDeviceSynchronize());
+  float ms;
+  cudaEventElapsedTime(&ms, e0, e1);
+  ms /= iters;
+  printf("bench %-28s M=%d N=%d K=%d split=%d grid=%d: %.3f ms  %.1f TFLOP/s\n", label, M, N, K, pl.args.splitk, pl.grid,
+         ms, 2.0 * M * N * K / ms * 1e-9);
+  cudaFree(a); cudaFree(b); cudaFree(out);
+}
+
+int main(int argc, char** argv) {
+  int dev = 0;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, dev));
+  printf("device: %s, %d SMs, cc %d.%d\n", prop.name, prop.multiProcessorCount, prop.major, prop.minor);
+  const int sms = prop.multiProcessorCount;
+  std::string err = gemm_init();
+  if (!err.empty()) { printf("gemm_init: %s\n", err.c_str()); return 2; }
+  const bool do_bench = argc > 1 && std::string(argv[1]) == "bench";
+  // plain GEMMs, all three operand layouts, K tails, M/N tails, segments, split-K
+  test_store(GEMM_FWD, 128, 256, 64, 1, 1, sms);
+  test_store(GEMM_FWD, 128, 256, 256, 1, 1, sms);
+  test_store(GEMM_DGRAD, 128, 256, 64, 1, 1, sms);
+  test_store(GEMM_WGRAD, 128, 256, 64, 1, 1, sms);
+  test_store(GEMM_FWD, 300, 500, 200, 1, 1, sms);
+  test_store(GEMM_FWD, 300, 500, 1000, 2, 3, sms);
+  test_store(GEMM_DGRAD, 300, 501, 840, 1, 1, sms);
+  test_store(GEMM_DGRAD, 300, 501, 840, 3, 4, sms);
+  test_store(GEMM_WGRAD, 501, 500, 700, 1, 1, sms);
+  test_store(GEMM_WGRAD, 501, 40, 1024, 2, 0, sms);
+  test_store(GEMM_FWD, 1000, 4, 501, 1, 0, sms);
+  test_wgrad_groups(1100, 500, 512, sms);
+  // fused epilogues
+  test_fused(EPI_ACT, 300, 500, 501, 1, 1, sms);
+  test_fused(EPI_ACT, 300, 500, 501, 1, 0, sms);
+  test_fused(EPI_ACT, 300, 500, 2000, 4, 1, sms);
+  test_fused(EPI_DACT, 512, 500, 400, 1, 1, sms);
+  test_fused(EPI_DACT, 512, 500, 4000, 5, 1, sms);
+  test_fused(EPI_BCE, 300, 1000, 501, 1, 1, sms);
+  test_fused(EPI_BCE, 300, 1000, 501, 1, 0, sms);
+  printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
+  if (do_bench) {
+    bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");
+    bench(GEMM_FWD, 12288, 512, 40064, 0, sms, "enc L0 fwd (auto split)");
+    bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd");
+    bench(GEMM_DGRAD, 4096, 512, 40000, 0, sms, "dec out dgrad (auto split)");
+    bench(GEMM_WGRAD, 512, 40000, 4096, 1, sms, "dec out wgrad");
+    bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad");
+    bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd");
+    bench(GEMM_WGRAD, 512, 512, 8192, 0, sms, "hidden wgrad (auto split)");
+    bench(GEMM_FWD, 8192, 8192, 8192, 1, sms, "square 8192");
+  }
+  return g_fail ? 1 : 0;
+}
