@@ -1,0 +1,144 @@
+/* magic_b200.h -- C ABI of the B200-native training engine for the "magic" asymmetric autoencoder.
+ *
+ * The reference (ag8/magic) has no FFI/plugin layer: its boundary is the Python surface of an experiment
+ * directory (constants.py / vae.py / main.py).  This header is the C-ABI that a binding for that surface
+ * calls; every entry point names the reference interface it replaces (paths relative to the reference
+ * root).  magic_b200/tango.py is the ctypes binding that re-creates `TangoEncoder` on top of it; see
+ * INTEGRATION.md for the stub a maintainer adds to <exp>/vae.py.
+ *
+ * Conventions: every function returns 0 on success, non-zero on error (message: magic_last_error());
+ * no exception crosses the boundary.  Pointers named d_* are DEVICE pointers, h_* are HOST pointers.
+ * The caller owns every buffer it passes in; the handle owns parameters, optimiser state, activations
+ * and workspaces.  Calls enqueue on the cudaStream_t given at create time and do not synchronise unless
+ * the name ends in _host or the comment says so.  A handle is not re-entrant: one handle per GPU/rank,
+ * driven by one thread (the reference drives its session from one Python thread, 8c/main.py:38-84).
+ * The library never falls back to a CPU path: without a CUDA device magic_create fails.
+ */
+#ifndef MAGIC_B200_H
+#define MAGIC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MAGIC_MAX_ENC_LAYERS 8
+
+enum { MAGIC_ACT_TANH = 1, MAGIC_ACT_ELU = 2 };                 /* 8c/vae.py:56, 11a/vae.py:58 */
+enum { MAGIC_METRIC_COSINE = 0, MAGIC_METRIC_SQDIFF = 1 };      /* 8c/constants.py:5-7,60 */
+enum { MAGIC_PRECISION_BF16 = 0, MAGIC_PRECISION_FP32 = 1 };    /* fp32 = bf16x3 split operands, fp32 accumulate */
+enum { MAGIC_FWD_DISTANCE = 0, MAGIC_FWD_ZMEAN = 1, MAGIC_FWD_RECON = 2 };
+enum { MAGIC_SLOT_M = 0, MAGIC_SLOT_V = 1 };
+
+/* Hyper-parameters the reference hard-codes in TangoEncoder.__init__ (8c/vae.py:30-66) and FLAGS
+ * (8c/constants.py:32,52,60). */
+typedef struct magic_config {
+  int32_t D;                          /* pixels per image: IMAGE_SIZE^2 = 40000 (8c/vae.py:81); multiple of 8 */
+  int32_t n_enc;                      /* number of encoder hidden layers (8c/vae.py:30) */
+  int32_t enc[MAGIC_MAX_ENC_LAYERS];  /* their widths */
+  int32_t dec[2];                     /* decoder hidden widths (8c/vae.py:36) */
+  int32_t L;                          /* latent dimensions (8c/vae.py:49) */
+  int32_t act;                        /* MAGIC_ACT_* */
+  int32_t metric;                     /* MAGIC_METRIC_* */
+  int32_t reciprocal;                 /* distance = 1/distance (9a/vae.py:301,303) */
+  float def_weight;                   /* 10 (8c/vae.py:287) or 100 (11a/vae.py:293) */
+  float lr1, lr2;                     /* 8c/vae.py:63 */
+  float beta1, beta2, eps;            /* tf.train.AdamOptimizer defaults 0.9, 0.999, 1e-8 */
+  int32_t precision;                  /* MAGIC_PRECISION_* */
+  int32_t batch_local;                /* pairs per step on this rank (static, like 8c/vae.py:367) */
+  int32_t batch_global;               /* pairs per step over all ranks: every batch mean divides by this */
+  int32_t rank, world;                /* data-parallel position; world > 1 needs magic_comm_init */
+  uint64_t seed;                      /* seed of the internal counter-based RNG (noise, generator) */
+} magic_config;
+
+typedef struct magic_handle magic_handle;
+
+typedef struct magic_stats {
+  int64_t steps;                 /* optimiser steps taken */
+  int64_t launches_last_step;    /* kernels of this library launched by the last magic_step */
+  double gemm_flops_per_step;    /* issued tensor-core FLOPs per step (incl. padding and split terms) */
+  double model_flops_per_pair;   /* algorithmic FLOPs per pair, SURVEY 8.4: 2*(11 enc + 3 dec - 4 D H) */
+  int64_t n_params1, n_params2;  /* parameters trained by optimiser 1 / 2 (unpadded) */
+  int64_t hbm_bytes;             /* device memory owned by the handle */
+} magic_stats;
+
+const char* magic_last_error(void);
+int magic_version(void);
+
+/* TangoEncoder.__init__ (8c/vae.py:22-326): builds parameters (Xavier-uniform from cfg.seed, zero biases),
+ * both optimisers' slots, activations, TMA descriptors and GEMM plans.  `stream` is a cudaStream_t (NULL =
+ * legacy default stream). */
+int magic_create(const magic_config* cfg, void* stream, magic_handle** out);
+int magic_destroy(magic_handle* h);
+int magic_sync(magic_handle* h);
+int magic_get_stats(magic_handle* h, magic_stats* out);
+
+/* Variables in the reference's creation order (8c/vae.py:89-147) minus the two dead decoder_out_log_sigma_*
+ * tensors: weights [in,out] row-major used as y = x.W + b, biases [out].  shape[1] = 0 for a bias vector. */
+int magic_param_count(magic_handle* h, int32_t* n);
+int magic_param_info(magic_handle* h, int32_t i, const char** name, int64_t shape[2], int32_t* optimisers);
+int magic_set_param(magic_handle* h, int32_t i, const float* h_src);   /* synchronises */
+int magic_get_param(magic_handle* h, int32_t i, float* h_dst);         /* synchronises */
+/* gradient of the last step: which = 1 -> d cost (optimiser 1), 2 -> d training_loss (optimiser 2) */
+int magic_get_grad(magic_handle* h, int32_t which, int32_t i, float* h_dst);
+/* optimiser slots and step counter (checkpointing; the reference has none from 7c on) */
+int magic_get_slot(magic_handle* h, int32_t which, int32_t slot, int32_t i, float* h_dst);
+int magic_set_slot(magic_handle* h, int32_t which, int32_t slot, int32_t i, const float* h_src);
+int magic_get_step(magic_handle* h, int64_t* t);
+int magic_set_step(magic_handle* h, int64_t t);
+
+/* Input of one step.  The reference feeds X[B,120000] fp32, channel-interleaved (ch0 lock, ch1 rotated lock,
+ * ch2 key; 8c/vae.py:166-179, 8c/overlap_input.py:195).  Each loader converts into the handle's planar bf16
+ * operand buffer (pixels are {0,1}: exact). */
+int magic_load_interleaved(magic_handle* h, const float* d_x);                       /* [B, 3*D] */
+int magic_load_planar_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* d_rot, const uint8_t* d_key);
+/* Replaces overlap_input.inputs() (8c/overlap_input.py:76-124): synthesises B shape pairs + rotated lock +
+ * max-overlap labels on the device for (seed, step, rank).  Labels go to an internal buffer used when
+ * magic_step is given d_labels = NULL. */
+int magic_generate_batch(magic_handle* h, uint64_t seed, uint64_t step);
+int magic_export_batch(magic_handle* h, float* d_x /* [B,3*D] or NULL */, float* d_labels /* [B] or NULL */);
+
+/* TangoEncoder.partial_fit (8c/vae.py:379-405; 6-tuple variant 11a/vae.py:385-411) on the loaded batch:
+ * forward, both backward passes at the pre-step weights, both Adam updates (W <- W - d1 - d2).
+ *   d_labels : [B] overlap areas, or NULL to use the generated labels
+ *   d_eps3   : [3,B,L] N(0,1) noise in stream order (lock, rot, key) (8c/vae.py:367), or NULL -> internal RNG
+ *   d_losses5: [5] = cost, training_loss, rec_loss, lat_loss, def_loss (global-batch means)
+ *   d_distance: [B] local distances (11a returns them) or NULL */
+int magic_step(magic_handle* h, const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance);
+/* Same, without the Adam update (gradients stay readable through magic_get_grad): parity tests. */
+int magic_step_grads_only(magic_handle* h, const float* d_labels, const float* d_eps3, float* d_losses5,
+                          float* d_distance);
+/* Host-buffer form of partial_fit: H2D copies of X/labels/eps, the step, D2H of the results, then a stream
+ * synchronise.  h_eps3 and h_distance may be NULL. */
+int magic_partial_fit_host(magic_handle* h, const float* h_x, const float* h_labels, const float* h_eps3,
+                           float h_losses5[5], float* h_distance);
+
+/* get_predictions / transform / reconstruct (8c/vae.py:407-434) on the loaded batch:
+ *   MAGIC_FWD_DISTANCE -> d_out[B] (needs d_labels = NULL; sampled z: pass d_eps3 or NULL for RNG)
+ *   MAGIC_FWD_ZMEAN    -> d_out[B,L]      MAGIC_FWD_RECON -> d_out[B,D] */
+int magic_forward(magic_handle* h, int32_t what, const float* d_eps3, float* d_out);
+/* generate (8c/vae.py:416-428): decoder-only forward from a fed z [B,L] -> [B,D] */
+int magic_decode(magic_handle* h, const float* d_z, float* d_out);
+
+/* Data parallelism (new; the reference is single-device).  `nccl_unique_id` is the 128-byte ncclUniqueId
+ * created on rank 0 and distributed by the host framework.  Afterwards magic_step all-reduces the cosine
+ * batch statistics, the two gradients and the loss scalars over NCCL inside the step. */
+int magic_comm_unique_id(void* h_id128);
+int magic_comm_init(magic_handle* h, const void* h_nccl_unique_id128);
+
+/* Per-launch CUDA-event timing of the step's kernels (bench.py's roofline and profiles/).  The report is text,
+ * one line per kernel family: "<tag> <ms summed> <launches> <tensor flops summed>".  Reading it synchronises
+ * and resets the accumulators. */
+int magic_profile_enable(magic_handle* h, int32_t on);
+int magic_profile_report(magic_handle* h, char* h_buf, int64_t cap);
+
+/* Native self-test hook used by tests/: runs one GEMM of the given kind through the tcgen05 kernel.
+ * kind 0: D = A[M,K].B[K,N]; 1: D = A[M,K].B[N,K]^T; 2: D = A[K,M]^T.B[K,N].  bf16 in, fp32 out [M,N]. */
+int magic_test_gemm(int32_t kind, int32_t M, int32_t N, int32_t K, const void* d_a, int64_t lda, const void* d_b,
+                    int64_t ldb, float* d_out, int64_t ldo, int32_t splitk, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MAGIC_B200_H */

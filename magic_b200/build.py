@@ -58,13 +58,13 @@ def build(force: bool = False, verbose: bool = True) -> str:
         objs = dict(zip([os.path.basename(s) for s in srcs], ex.map(lambda s: _compile(s, force), srcs)))
     lib_objs = [objs[s] for s in LIB_SOURCES if s in objs]
     if len(lib_objs) == len(LIB_SOURCES) and (force or _stale(LIB, lib_objs)):
-        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + lib_objs + ["-lcudart", "-ldl"]
+        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + lib_objs + ["-cudart", "static", "-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n%s\n%s" % (r.stdout, r.stderr))
     st_objs = [objs[s] for s in SELFTEST_SOURCES if s in objs]
     if len(st_objs) == len(SELFTEST_SOURCES) and (force or _stale(SELFTEST, st_objs)):
-        cmd = [NVCC] + ARCH + ["-o", SELFTEST] + st_objs + ["-lcudart"]
+        cmd = [NVCC] + ARCH + ["-o", SELFTEST] + st_objs + ["-cudart", "static"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("selftest link failed:\n%s\n%s" % (r.stdout, r.stderr))

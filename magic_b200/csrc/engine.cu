@@ -1,0 +1,762 @@
+// The training engine: parameter layout, activations, GEMM plans and the step (see engine.h).
+#include "engine.h"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <dlfcn.h>
+
+namespace magic {
+
+#define MAGIC_CUDA(x)                                                                                    \
+  do {                                                                                                   \
+    cudaError_t e_ = (x);                                                                                \
+    if (e_ != cudaSuccess) return std::string(#x) + ": " + cudaGetErrorString(e_);                       \
+  } while (0)
+#define MAGIC_TRY(x)                 \
+  do {                               \
+    std::string s_ = (x);            \
+    if (!s_.empty()) return s_;      \
+  } while (0)
+
+static long long round_up(long long v, long long m) { return (v + m - 1) / m * m; }
+
+// ------------------------------------------------------------------ small device helpers
+__global__ void fill_kernel(float* p, long long n, float v) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+// Xavier-uniform window init (8c/utils.py:346-353): U(-b, b), b = sqrt(6 / (fan_in + fan_out)).
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__global__ void xavier_kernel(float* w, long long ld, int nrows, int col0, int ncols, float bound, uint64_t key) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)nrows * ncols) return;
+  const int r = (int)(i / ncols), c = (int)(i % ncols);
+  const uint32_t bits = (uint32_t)(mix64(key + (uint64_t)i) >> 32);
+  const float u = (bits >> 8) * (1.0f / 16777216.0f);
+  w[(long long)r * ld + col0 + c] = (2.f * u - 1.f) * bound;
+}
+
+// losses5 = [cost, training, rec, kl, def] from sums = [rec, kl, def, training]
+__global__ void finalize_losses_kernel(const float* sums, float* out) {
+  if (threadIdx.x == 0) {
+    out[0] = sums[0] + sums[1] + sums[2];
+    out[1] = sums[3];
+    out[2] = sums[0];
+    out[3] = sums[1];
+    out[4] = sums[2];
+  }
+}
+
+// user z [B,L] fp32 -> decoder input bf16 [B, ld] with the bias column (generate(), 8c/vae.py:416-428)
+__global__ void z_to_zdec_kernel(const float* z, int B, int L, bf16* hi, bf16* lo, long long ld) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * (L + 1)) return;
+  const int i = (int)(idx / (L + 1)), j = (int)(idx % (L + 1));
+  const float v = j < L ? z[(long long)i * L + j] : 1.f;
+  const bf16 h = __float2bfloat16(v);
+  hi[(long long)i * ld + j] = h;
+  if (lo) lo[(long long)i * ld + j] = __float2bfloat16(v - __bfloat162float(h));
+}
+
+// ------------------------------------------------------------------ NCCL through dlopen (optional at run time)
+typedef int (*nccl_get_uid_t)(void*);
+struct NcclUid { char b[128]; };
+typedef int (*nccl_init_rank2_t)(void**, int, NcclUid, int);
+typedef int (*nccl_allreduce_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*nccl_destroy_t)(void*);
+typedef const char* (*nccl_errstr_t)(int);
+struct NcclApi {
+  void* lib = nullptr;
+  nccl_get_uid_t get_uid = nullptr;
+  nccl_init_rank2_t init_rank = nullptr;
+  nccl_allreduce_t allreduce = nullptr;
+  nccl_destroy_t destroy = nullptr;
+  nccl_errstr_t errstr = nullptr;
+};
+static NcclApi g_nccl;
+static std::string load_nccl() {
+  if (g_nccl.lib) return "";
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    g_nccl.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (g_nccl.lib) break;
+  }
+  if (!g_nccl.lib) return "NCCL not found (dlopen libnccl.so.2 failed): data parallelism unavailable";
+  g_nccl.get_uid = (nccl_get_uid_t)dlsym(g_nccl.lib, "ncclGetUniqueId");
+  g_nccl.init_rank = (nccl_init_rank2_t)dlsym(g_nccl.lib, "ncclCommInitRank");
+  g_nccl.allreduce = (nccl_allreduce_t)dlsym(g_nccl.lib, "ncclAllReduce");
+  g_nccl.destroy = (nccl_destroy_t)dlsym(g_nccl.lib, "ncclCommDestroy");
+  g_nccl.errstr = (nccl_errstr_t)dlsym(g_nccl.lib, "ncclGetErrorString");
+  if (!g_nccl.get_uid || !g_nccl.init_rank || !g_nccl.allreduce) return "NCCL symbols missing";
+  return "";
+}
+std::string nccl_unique_id(void* out128) {
+  MAGIC_TRY(load_nccl());
+  int r = g_nccl.get_uid(out128);
+  if (r != 0) return std::string("ncclGetUniqueId: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "error");
+  return "";
+}
+
+// ------------------------------------------------------------------ Engine: allocation / layout
+Engine::~Engine() {
+  // the process-lifetime handle frees with the context; explicit frees keep repeated create/destroy clean
+  cudaStreamSynchronize(stream);
+  void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, X_.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
+                  D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
+                  statbuf_, g_row_, dist_, labels_int_, losses_dev_, stage_x_, stage_labels_, stage_eps_};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
+  for (auto& a : dH_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
+  if (comm_ && g_nccl.destroy) g_nccl.destroy(comm_);
+  if (comm_stream_) cudaStreamDestroy(comm_stream_);
+  for (auto& e : ev_bwd_) if (e) cudaEventDestroy(e);
+  if (ev_comm_) cudaEventDestroy(ev_comm_);
+}
+
+std::string Engine::alloc(void** p, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  MAGIC_CUDA(cudaMalloc(p, bytes));
+  MAGIC_CUDA(cudaMemsetAsync(*p, 0, bytes, stream));
+  stats.hbm_bytes += (int64_t)bytes;
+  return "";
+}
+
+std::string Engine::alloc_act(Act* a, long long rows, int width_plus_bias) {
+  a->rows = rows;
+  a->ld = round_up(width_plus_bias, 64);
+  MAGIC_TRY(alloc((void**)&a->hi, sizeof(bf16) * rows * a->ld));
+  if (split) MAGIC_TRY(alloc((void**)&a->lo, sizeof(bf16) * rows * a->ld));
+  return "";
+}
+
+std::string Engine::init(const magic_config& c, cudaStream_t s) {
+  cfg = c;
+  stream = s;
+  if (c.D <= 0 || c.D % 8 != 0) return "config: D must be a positive multiple of 8";
+  if (c.n_enc < 1 || c.n_enc > MAGIC_MAX_ENC_LAYERS) return "config: n_enc out of range";   // 8c/vae.py:31
+  if (c.L < 1) return "config: L must be >= 1";
+  if (c.act != MAGIC_ACT_TANH && c.act != MAGIC_ACT_ELU) return "config: unknown activation";
+  if (c.metric != MAGIC_METRIC_COSINE && c.metric != MAGIC_METRIC_SQDIFF)
+    return "Invalid distance metric: " + std::to_string(c.metric);                           // 8c/vae.py:305
+  if (c.batch_local < 1 || c.batch_global < c.batch_local) return "config: bad batch sizes";
+  if (c.world < 1 || c.rank < 0 || c.rank >= c.world) return "config: bad rank/world";
+  int dev = 0;
+  MAGIC_CUDA(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  MAGIC_CUDA(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10) return std::string("this library is built for sm_100a (B200); found ") + prop.name;
+  num_sms = prop.multiProcessorCount;
+  MAGIC_TRY(gemm_init());
+
+  E = c.n_enc; B = c.batch_local; D = c.D; L = c.L;
+  split = c.precision == MAGIC_PRECISION_FP32;
+  inv_bg = 1.0f / (float)c.batch_global;
+
+  // ---- layers and the flat parameter layout: [enc0 .. enc(E-1) | heads] [dec h1 | dec h2 | dec out]
+  lin.clear();
+  long long off = 0;
+  auto add = [&](int Kv, int Nv) {
+    Linear l;
+    l.Kv = Kv; l.Nv = Nv; l.ld = round_up(Nv, 64); l.off = off;
+    off += l.size();
+    lin.push_back(l);
+    return (int)lin.size() - 1;
+  };
+  add(D, c.enc[0]);
+  for (int i = 1; i < E; ++i) add(c.enc[i - 1], c.enc[i]);
+  iHead = add(c.enc[E - 1], 2 * L);
+  n_both = off;
+  iD1 = add(L, c.dec[0]);
+  iD2 = add(c.dec[0], c.dec[1]);
+  iOut = add(c.dec[1], D);
+  n_total = off;
+
+  // ---- reference variables as windows (creation order of 8c/vae.py:89-147, dead tensors omitted)
+  views.clear();
+  auto view = [&](const std::string& name, int layer, bool bias, int col0, int ncols, int opts) {
+    ParamView v;
+    v.name = name; v.layer = layer; v.is_bias = bias; v.col0 = col0; v.ncols = ncols; v.optimisers = opts;
+    v.row0 = bias ? lin[layer].Kv : 0;
+    v.nrows = bias ? 1 : lin[layer].Kv;
+    views.push_back(v);
+  };
+  char nm[64];
+  for (int i = 0; i < E; ++i) { snprintf(nm, sizeof nm, "encoder_h%d_weights", i); view(nm, i, false, 0, lin[i].Nv, 3); }
+  view("encoder_out_mean_weights", iHead, false, 0, L, 3);
+  view("encoder_out_log_sigma_weights", iHead, false, L, L, 3);
+  for (int i = 0; i < E; ++i) { snprintf(nm, sizeof nm, "encoder_b%d_biases", i); view(nm, i, true, 0, lin[i].Nv, 3); }
+  view("encoder_out_mean_biases", iHead, true, 0, L, 3);
+  view("encoder_out_log_sigma_biases", iHead, true, L, L, 3);
+  view("decoder_h1_weights", iD1, false, 0, lin[iD1].Nv, 1);
+  view("decoder_h2_weights", iD2, false, 0, lin[iD2].Nv, 1);
+  view("decoder_out_mean_weights", iOut, false, 0, lin[iOut].Nv, 1);
+  view("decoder_b1_biases", iD1, true, 0, lin[iD1].Nv, 1);
+  view("decoder_b2_biases", iD2, true, 0, lin[iD2].Nv, 1);
+  view("decoder_out_mean_biases", iOut, true, 0, lin[iOut].Nv, 1);
+  stats.n_params1 = stats.n_params2 = 0;
+  for (auto& v : views) {
+    const long long n = (long long)v.nrows * v.ncols;
+    stats.n_params1 += n;
+    if (v.optimisers & 2) stats.n_params2 += n;
+  }
+  {
+    // MAC = 11 enc + 3 dec - 4 D H0, enc = sum of encoder layer MACs incl. both heads
+    double enc = (double)D * c.enc[0], dec = (double)L * c.dec[0] + (double)c.dec[0] * c.dec[1] + (double)c.dec[1] * D;
+    for (int i = 1; i < E; ++i) enc += (double)c.enc[i - 1] * c.enc[i];
+    enc += 2.0 * c.enc[E - 1] * L;
+    stats.model_flops_per_pair = 2.0 * (11.0 * enc + 3.0 * dec - 4.0 * (double)D * c.enc[0]);
+  }
+
+  // ---- parameter-shaped buffers
+  MAGIC_TRY(alloc((void**)&p_, sizeof(float) * n_total));
+  MAGIC_TRY(alloc((void**)&g1_, sizeof(float) * n_total));
+  MAGIC_TRY(alloc((void**)&m1_, sizeof(float) * n_total));
+  MAGIC_TRY(alloc((void**)&v1_, sizeof(float) * n_total));
+  MAGIC_TRY(alloc((void**)&g2_, sizeof(float) * n_both));
+  MAGIC_TRY(alloc((void**)&m2_, sizeof(float) * n_both));
+  MAGIC_TRY(alloc((void**)&v2_, sizeof(float) * n_both));
+  MAGIC_TRY(alloc((void**)&w_hi_, sizeof(bf16) * n_total));
+  if (split) MAGIC_TRY(alloc((void**)&w_lo_, sizeof(bf16) * n_total));
+  for (size_t vi = 0; vi < views.size(); ++vi) {
+    const ParamView& v = views[vi];
+    if (v.is_bias) continue;   // biases start at zero (8c/vae.py:119)
+    const Linear& l = lin[v.layer];
+    const float bound = sqrtf(6.0f / (float)(l.Kv + v.ncols));
+    const long long n = (long long)v.nrows * v.ncols;
+    xavier_kernel<<<(int)((n + 255) / 256), 256, 0, stream>>>(p_ + l.off, l.ld, v.nrows, v.col0, v.ncols, bound,
+                                                               c.seed * 0x9E3779B97F4A7C15ull + vi * 0x1000000000ull);
+  }
+  shadow_dirty_ = true;
+
+  // ---- activations
+  MAGIC_TRY(alloc_act(&X_, 3LL * B, D + 1));
+  if (X_.lo) { cudaFree(X_.lo); stats.hbm_bytes -= (int64_t)(sizeof(bf16) * X_.rows * X_.ld); X_.lo = nullptr; }  // pixels are exact in bf16
+  H_.resize(E);
+  dH_.resize(E);
+  for (int i = 0; i < E; ++i) {
+    MAGIC_TRY(alloc_act(&H_[i], 3LL * B, c.enc[i] + 1));
+    MAGIC_TRY(alloc_act(&dH_[i], 4LL * B, c.enc[i] + 1));
+  }
+  ld_heads_ = round_up(2 * L, 64);
+  MAGIC_TRY(alloc((void**)&heads_, sizeof(float) * 3 * B * ld_heads_));
+  MAGIC_TRY(alloc((void**)&z_, sizeof(float) * 3 * B * L));
+  MAGIC_TRY(alloc_act(&zdec_, B, L + 1));
+  MAGIC_TRY(alloc_act(&D1_, B, c.dec[0] + 1));
+  MAGIC_TRY(alloc_act(&D2_, B, c.dec[1] + 1));
+  MAGIC_TRY(alloc_act(&dA_, B, D));
+  MAGIC_TRY(alloc_act(&dD2_, B, c.dec[1] + 1));
+  MAGIC_TRY(alloc_act(&dD1_, B, c.dec[0] + 1));
+  ld_dz_ = round_up(L, 64);
+  MAGIC_TRY(alloc((void**)&dz_dec_, sizeof(float) * B * ld_dz_));
+  MAGIC_TRY(alloc_act(&dheads_, 4LL * B, 2 * L));
+  ws_ld_ = 64;
+  for (int i = 0; i < E; ++i) ws_ld_ = std::max(ws_ld_, H_[i].ld);
+  ws_ld_ = std::max(ws_ld_, std::max(D1_.ld, D2_.ld));
+  MAGIC_TRY(alloc((void**)&ws_, sizeof(float) * 4 * B * ws_ld_));
+  MAGIC_TRY(alloc((void**)&statbuf_, sizeof(float) * (8 + 3 * L)));
+  MAGIC_TRY(alloc((void**)&g_row_, sizeof(float) * B));
+  MAGIC_TRY(alloc((void**)&dist_, sizeof(float) * B));
+  MAGIC_TRY(alloc((void**)&labels_int_, sizeof(float) * B));
+  MAGIC_TRY(alloc((void**)&losses_dev_, sizeof(float) * 8));
+  for (auto& e : ev_bwd_) MAGIC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  MAGIC_CUDA(cudaEventCreateWithFlags(&ev_comm_, cudaEventDisableTiming));
+  MAGIC_TRY(build_plans());
+  MAGIC_CUDA(cudaStreamSynchronize(stream));
+  return "";
+}
+
+// ------------------------------------------------------------------ plans
+Mat Engine::wmat(int layer, bool lo) const {
+  const Linear& l = lin[layer];
+  return Mat((lo ? w_lo_ : w_hi_) + l.off, l.rows(), l.Nv, l.ld);
+}
+Mat Engine::amat(const Act& a, bool lo, long long row0, long long rows, long long cols) {
+  return Mat((lo ? a.lo : a.hi) + row0 * a.ld, rows, cols, a.ld);
+}
+// bf16 mode: one segment.  fp32 mode: a*b ~ a_hi*b_hi + a_hi*b_lo + a_lo*b_hi (a_lo*b_lo ~ 2^-18 dropped);
+// an exact A (binary pixels) needs only the first two.
+int Engine::add_segments(GemmProblem& p, int g, Mat a_hi, Mat a_lo, Mat b_hi, Mat b_lo, bool a_exact) {
+  p.a[g][0] = a_hi; p.b[g][0] = b_hi;
+  int n = 1;
+  if (split) {
+    p.a[g][1] = a_hi; p.b[g][1] = b_lo; n = 2;
+    if (!a_exact) { p.a[g][2] = a_lo; p.b[g][2] = b_hi; n = 3; }
+  }
+  p.nseg = n;
+  return n;
+}
+
+std::string Engine::build_plans() {
+  const magic_config& c = cfg;
+  const int prec = split ? 1 : 0;
+  double flops = 0;
+  auto finish = [&](GemmProblem& p, GemmPlan* pl, const char* what) -> std::string {
+    std::string err = gemm_plan(p, num_sms, pl);
+    if (!err.empty()) return std::string(what) + ": " + err;
+    flops += pl->flops;
+    return "";
+  };
+  auto act_epi = [&](const Act& out, int n_valid) {
+    EpiArgs e;
+    memset(&e, 0, sizeof e);
+    e.out = out.hi; e.out_lo = out.lo; e.ld_out = out.ld; e.alpha = 1.f; e.n_valid = n_valid; e.act = c.act;
+    e.precise = prec; e.aux_split = 1 << 30;
+    return e;
+  };
+  auto f32_epi = [&](float* out, long long ld, float alpha) {
+    EpiArgs e;
+    memset(&e, 0, sizeof e);
+    e.out = out; e.ld_out = ld; e.alpha = alpha; e.aux_split = 1 << 30;
+    return e;
+  };
+  auto dact_epi = [&](const Act& out, const Act& y, int n_valid, int aux_split, int aux_shift) {
+    EpiArgs e = act_epi(out, n_valid);
+    e.aux = y.hi; e.aux_lo = y.lo; e.ld_aux = y.ld; e.aux_split = aux_split; e.aux_shift = aux_shift;
+    return e;
+  };
+
+  // ---------------- forward: encoder (three streams stacked, M = 3B), heads
+  fwd_enc_.assign(E + 1, GemmPlan());
+  for (int i = 0; i < E; ++i) {
+    GemmProblem p;
+    p.kind = GEMM_FWD; p.epi = EPI_ACT; p.M = 3 * B; p.K = lin[i].Kv + 1; p.N = (int)H_[i].ld;
+    const Act& in = i == 0 ? X_ : H_[i - 1];
+    add_segments(p, 0, amat(in, false, 0, 3LL * B, p.K), amat(in, true, 0, 3LL * B, p.K), wmat(i, false), wmat(i, true),
+                 i == 0);
+    p.e[0] = act_epi(H_[i], lin[i].Nv);
+    p.ws = ws_; p.ws_ld = H_[i].ld;
+    MAGIC_TRY(finish(p, &fwd_enc_[i], "fwd enc"));
+  }
+  {
+    GemmProblem p;
+    p.kind = GEMM_FWD; p.epi = EPI_STORE_F32; p.M = 3 * B; p.K = lin[iHead].Kv + 1; p.N = 2 * L;
+    const Act& in = H_[E - 1];
+    add_segments(p, 0, amat(in, false, 0, 3LL * B, p.K), amat(in, true, 0, 3LL * B, p.K), wmat(iHead, false),
+                 wmat(iHead, true), false);
+    p.e[0] = f32_epi(heads_, ld_heads_, 1.f);
+    p.force_splitk = 1;
+    MAGIC_TRY(finish(p, &fwd_enc_[E], "fwd heads"));
+  }
+  // ---------------- forward: decoder (lock stream only, 8c/vae.py:221-226)
+  auto dec_fwd = [&](GemmPlan* pl, const Act& in, int layer, const Act& out) -> std::string {
+    GemmProblem p;
+    p.kind = GEMM_FWD; p.epi = EPI_ACT; p.M = B; p.K = lin[layer].Kv + 1; p.N = (int)out.ld;
+    add_segments(p, 0, amat(in, false, 0, B, p.K), amat(in, true, 0, B, p.K), wmat(layer, false), wmat(layer, true), false);
+    p.e[0] = act_epi(out, lin[layer].Nv);
+    p.ws = ws_; p.ws_ld = out.ld;
+    return finish(p, pl, "fwd dec");
+  };
+  MAGIC_TRY(dec_fwd(&pl_d1_, zdec_, iD1, D1_));
+  MAGIC_TRY(dec_fwd(&pl_d2_, D1_, iD2, D2_));
+  for (int v = 0; v < 2; ++v) {
+    GemmProblem p;
+    p.kind = GEMM_FWD; p.epi = v == 0 ? EPI_BCE : EPI_SIGMOID; p.M = B; p.K = lin[iOut].Kv + 1; p.N = D;
+    add_segments(p, 0, amat(D2_, false, 0, B, p.K), amat(D2_, true, 0, B, p.K), wmat(iOut, false), wmat(iOut, true), false);
+    EpiArgs e;
+    memset(&e, 0, sizeof e);
+    if (v == 0) {
+      e.out = dA_.hi; e.out_lo = dA_.lo; e.ld_out = dA_.ld;
+      e.aux = X_.hi + (long long)B * X_.ld; e.ld_aux = X_.ld;   // lock plane (rows [B, 2B))
+      e.alpha = inv_bg; e.scalar = statbuf_ + 0; e.precise = prec;
+    } else {
+      e.out = nullptr; e.ld_out = D;                             // output pointer patched per call
+    }
+    e.aux_split = 1 << 30;
+    p.e[0] = e;
+    MAGIC_TRY(finish(p, v == 0 ? &pl_out_bce_ : &pl_out_sig_, "fwd dec out"));
+    if (v == 1) flops -= pl_out_sig_.flops;
+  }
+
+  // ---------------- backward of `cost` through the decoder
+  zero_.clear();
+  auto wgrad1 = [&](GemmPlan* pl, const Act& x, int xcols, const Act& dy, int layer) -> std::string {
+    GemmProblem p;
+    p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.M = xcols; p.N = lin[layer].Nv; p.K = B;
+    add_segments(p, 0, amat(x, false, 0, B, xcols), amat(x, true, 0, B, xcols), amat(dy, false, 0, B, p.N),
+                 amat(dy, true, 0, B, p.N), false);
+    p.e[0] = f32_epi(g1_ + lin[layer].off, lin[layer].ld, inv_bg);
+    MAGIC_TRY(finish(p, pl, "wgrad dec"));
+    if (pl->args.splitk > 1) zero_.push_back({g1_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
+    return "";
+  };
+  auto dgrad1 = [&](GemmPlan* pl, const Act& dy, int layer, const Act& y, const Act& out) -> std::string {
+    GemmProblem p;
+    p.kind = GEMM_DGRAD; p.epi = EPI_DACT; p.M = B; p.K = lin[layer].Nv; p.N = (int)out.ld;
+    add_segments(p, 0, amat(dy, false, 0, B, p.K), amat(dy, true, 0, B, p.K), wmat(layer, false), wmat(layer, true), false);
+    p.e[0] = dact_epi(out, y, lin[layer].Kv, 1 << 30, 0);
+    p.ws = ws_; p.ws_ld = out.ld;
+    return finish(p, pl, "dgrad dec");
+  };
+  MAGIC_TRY(wgrad1(&pl_wg_out_, D2_, c.dec[1] + 1, dA_, iOut));
+  MAGIC_TRY(dgrad1(&pl_dg_out_, dA_, iOut, D2_, dD2_));
+  MAGIC_TRY(wgrad1(&pl_wg_h2_, D1_, c.dec[0] + 1, dD2_, iD2));
+  MAGIC_TRY(dgrad1(&pl_dg_h2_, dD2_, iD2, D1_, dD1_));
+  MAGIC_TRY(wgrad1(&pl_wg_h1_, zdec_, L + 1, dD1_, iD1));
+  {
+    GemmProblem p;   // d z_lock (unscaled), fp32
+    p.kind = GEMM_DGRAD; p.epi = EPI_STORE_F32; p.M = B; p.K = lin[iD1].Nv; p.N = L;
+    add_segments(p, 0, amat(dD1_, false, 0, B, p.K), amat(dD1_, true, 0, B, p.K), wmat(iD1, false), wmat(iD1, true), false);
+    p.e[0] = f32_epi(dz_dec_, ld_dz_, 1.f);
+    p.force_splitk = 1;
+    MAGIC_TRY(finish(p, &pl_dg_h1_, "dgrad dec h1"));
+  }
+
+  // ---------------- backward through the encoder: four streams [rot|cost ; lock|cost ; lock|metric ; key|metric]
+  auto wgrad2 = [&](GemmPlan* pl, const Act& x, int xcols, bool x_exact, const Act& dy, int layer) -> std::string {
+    GemmProblem p;
+    p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.M = xcols; p.N = lin[layer].Nv; p.K = 2 * B;
+    // optimiser 1 (cost): x rows [rot; lock] = [0, 2B), dy rows [0, 2B).  optimiser 2 (metric): x rows [lock; key] =
+    // [B, 3B), dy rows [2B, 4B).
+    add_segments(p, 0, amat(x, false, 0, 2LL * B, xcols), amat(x, true, 0, 2LL * B, xcols), amat(dy, false, 0, 2LL * B, p.N),
+                 amat(dy, true, 0, 2LL * B, p.N), x_exact);
+    add_segments(p, 1, amat(x, false, B, 2LL * B, xcols), amat(x, true, B, 2LL * B, xcols),
+                 amat(dy, false, 2LL * B, 2LL * B, p.N), amat(dy, true, 2LL * B, 2LL * B, p.N), x_exact);
+    p.e[0] = f32_epi(g1_ + lin[layer].off, lin[layer].ld, 1.f);
+    p.e[1] = f32_epi(g2_ + lin[layer].off, lin[layer].ld, 1.f);
+    MAGIC_TRY(finish(p, pl, "wgrad enc"));
+    if (pl->args.splitk > 1) {
+      zero_.push_back({g1_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
+      zero_.push_back({g2_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
+    }
+    return "";
+  };
+  auto dgrad2 = [&](GemmPlan* pl, const Act& dy, int layer, const Act& y, const Act& out) -> std::string {
+    GemmProblem p;
+    p.kind = GEMM_DGRAD; p.epi = EPI_DACT; p.M = 4 * B; p.K = lin[layer].Nv; p.N = (int)out.ld;
+    add_segments(p, 0, amat(dy, false, 0, 4LL * B, p.K), amat(dy, true, 0, 4LL * B, p.K), wmat(layer, false),
+                 wmat(layer, true), false);
+    p.e[0] = dact_epi(out, y, lin[layer].Kv, 2 * B, B);   // y rows: r < 2B -> r ; else r - B
+    p.ws = ws_; p.ws_ld = out.ld;
+    return finish(p, pl, "dgrad enc");
+  };
+  MAGIC_TRY(wgrad2(&pl_wg_head_, H_[E - 1], c.enc[E - 1] + 1, false, dheads_, iHead));
+  MAGIC_TRY(dgrad2(&pl_dg_head_, dheads_, iHead, H_[E - 1], dH_[E - 1]));
+  pl_wg_enc_.assign(E, GemmPlan());
+  pl_dg_enc_.assign(E, GemmPlan());
+  for (int i = E - 1; i >= 1; --i) {
+    MAGIC_TRY(wgrad2(&pl_wg_enc_[i], H_[i - 1], c.enc[i - 1] + 1, false, dH_[i], i));
+    MAGIC_TRY(dgrad2(&pl_dg_enc_[i], dH_[i], i, H_[i - 1], dH_[i - 1]));
+  }
+  MAGIC_TRY(wgrad2(&pl_wg_enc_[0], X_, D + 1, true, dH_[0], 0));
+  stats.gemm_flops_per_step = flops;
+  return "";
+}
+
+// ------------------------------------------------------------------ inputs
+std::string Engine::load_interleaved(const float* d_x) {
+  if (!d_x) return "load_interleaved: null input";
+  prof_begin("input.deinterleave"); deinterleave_f32(d_x, B, D, X_.hi, X_.ld, stream); prof_end();
+  MAGIC_CUDA(cudaGetLastError());
+  have_labels_ = false;
+  return "";
+}
+std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uint8_t* k) {
+  if (!l || !r || !k) return "load_planar_u8: null input";
+  planar_u8(l, r, k, B, D, X_.hi, X_.ld, stream);
+  MAGIC_CUDA(cudaGetLastError());
+  have_labels_ = false;
+  return "";
+}
+std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
+  const int side = (int)llround(sqrt((double)D));
+  if (side * side != D) return "generate: D is not a square canvas";
+  // fold the rank into the seed so every rank draws different pairs
+  prof_begin("input.generate");
+  generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, X_.hi, X_.ld, labels_int_, stream);
+  prof_end();
+  MAGIC_CUDA(cudaGetLastError());
+  have_labels_ = true;
+  return "";
+}
+std::string Engine::export_batch(float* d_x, float* d_labels) {
+  if (d_x) planes_to_interleaved_f32(X_.hi, X_.ld, B, D, d_x, stream);
+  if (d_labels) MAGIC_CUDA(cudaMemcpyAsync(d_labels, labels_int_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
+  MAGIC_CUDA(cudaGetLastError());
+  return "";
+}
+
+// ------------------------------------------------------------------ step
+void Engine::refresh_shadow() {
+  if (!shadow_dirty_) return;
+  shadow_refresh(p_, w_hi_, w_lo_, n_total, stream);
+  shadow_dirty_ = false;
+}
+
+void Engine::profile_enable(bool on) { profile_ = on; }
+void Engine::prof_begin(const char* tag, double flops) {
+  if (!profile_) return;
+  ProfRec r;
+  r.tag = tag; r.flops = flops;
+  for (cudaEvent_t* e : {&r.a, &r.b}) {
+    if (!prof_pool_.empty()) { *e = prof_pool_.back(); prof_pool_.pop_back(); }
+    else cudaEventCreate(e);
+  }
+  cudaEventRecord(r.a, stream);
+  prof_pending_.push_back(r);
+}
+void Engine::prof_end() {
+  if (!profile_ || prof_pending_.empty()) return;
+  cudaEventRecord(prof_pending_.back().b, stream);
+}
+std::string Engine::profile_report() {
+  cudaStreamSynchronize(stream);
+  for (auto& r : prof_pending_) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    ProfAcc* acc = nullptr;
+    for (auto& a : prof_acc_) if (a.tag == r.tag) { acc = &a; break; }
+    if (!acc) { prof_acc_.push_back(ProfAcc()); acc = &prof_acc_.back(); acc->tag = r.tag; }
+    acc->ms += ms; acc->n += 1; acc->flops += r.flops;
+    prof_pool_.push_back(r.a); prof_pool_.push_back(r.b);
+  }
+  prof_pending_.clear();
+  std::string out;
+  char buf[256];
+  for (auto& a : prof_acc_) {
+    snprintf(buf, sizeof buf, "%s %.6f %lld %.6e\n", a.tag.c_str(), a.ms, a.n, a.flops);
+    out += buf;
+  }
+  prof_acc_.clear();
+  return out;
+}
+
+std::string Engine::launch(GemmPlan& pl, int* launches, const char* tag) {
+  std::string err;
+  prof_begin(tag, pl.flops);
+  const int n = gemm_launch(pl, stream, &err);
+  prof_end();
+  if (n < 0) return err;
+  *launches += n;
+  return "";
+}
+
+LatentArgs Engine::latent_args(const float* d_eps3, const float* d_labels) {
+  LatentArgs a;
+  memset(&a, 0, sizeof a);
+  a.B = B; a.L = L; a.inv_bg = inv_bg; a.def_weight = cfg.def_weight;
+  a.metric = cfg.metric == MAGIC_METRIC_COSINE ? METRIC_COSINE : METRIC_SQDIFF;
+  a.reciprocal = cfg.reciprocal;
+  a.heads = heads_; a.ld_heads = ld_heads_;
+  a.eps = d_eps3;
+  a.seed = cfg.seed + 0x51ED270B9F2D4C11ull * (uint64_t)(cfg.rank + 1);
+  a.step = (uint64_t)t;
+  a.z = z_;
+  a.zdec = zdec_.hi; a.zdec_lo = zdec_.lo; a.ld_zdec = zdec_.ld;
+  a.labels = d_labels;
+  a.sums = statbuf_; a.colsq = statbuf_ + 8; a.colS = statbuf_ + 8 + 2 * L;
+  a.g = g_row_; a.distance = dist_;
+  a.dz_dec = dz_dec_; a.ld_dz = ld_dz_;
+  a.dheads = dheads_.hi; a.dheads_lo = dheads_.lo; a.ld_dheads = dheads_.ld;
+  return a;
+}
+
+std::string Engine::allreduce(float* buf, size_t n, cudaStream_t s) {
+  if (cfg.world == 1) return "";
+  if (!comm_) return "world > 1 but magic_comm_init was not called";
+  const int r = g_nccl.allreduce(buf, buf, n, /*ncclFloat32*/ 7, /*ncclSum*/ 0, comm_, s);
+  if (r != 0) return std::string("ncclAllReduce: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "error");
+  return "";
+}
+
+std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) {
+  refresh_shadow();
+  MAGIC_CUDA(cudaMemsetAsync(statbuf_, 0, sizeof(float) * (8 + 3 * L), stream));
+  for (int i = 0; i <= E; ++i) MAGIC_TRY(launch(fwd_enc_[i], launches, i == 0 ? "gemm.fwd_enc0" : (i == E ? "gemm.fwd_heads" : "gemm.fwd_enc_hidden")));
+  const float* labels = have_labels_ext_ ? labels_ext_ : labels_int_;
+  LatentArgs la = latent_args(d_eps3, labels);
+  prof_begin("latent.forward"); latent_forward(la, stream); prof_end();
+  const bool cosine = cfg.metric == MAGIC_METRIC_COSINE;
+  if (cosine) MAGIC_TRY(allreduce(statbuf_ + 8, 2 * (size_t)L, stream));        // batch-axis norms over the GLOBAL batch
+  prof_begin("latent.metric"); latent_metric(la, stream); prof_end();
+  if (cosine && train) MAGIC_TRY(allreduce(statbuf_ + 8 + 2 * L, (size_t)L, stream));
+  *launches += 2;
+  MAGIC_TRY(launch(pl_d1_, launches, "gemm.fwd_dec_hidden"));
+  MAGIC_TRY(launch(pl_d2_, launches, "gemm.fwd_dec_hidden"));
+  if (train) MAGIC_TRY(launch(pl_out_bce_, launches, "gemm.fwd_dec_out_bce"));
+  MAGIC_CUDA(cudaGetLastError());
+  return "";
+}
+
+std::string Engine::run_backward(int* launches) {
+  prof_begin("memset.grad_windows");
+  for (auto& z : zero_) MAGIC_CUDA(cudaMemsetAsync(z.ptr, 0, z.bytes, stream));
+  prof_end();
+  const bool dp = cfg.world > 1;
+  MAGIC_TRY(launch(pl_wg_out_, launches, "gemm.wgrad_dec_out"));
+  MAGIC_TRY(launch(pl_dg_out_, launches, "gemm.dgrad_dec_out"));
+  MAGIC_TRY(launch(pl_wg_h2_, launches, "gemm.wgrad_small"));
+  MAGIC_TRY(launch(pl_dg_h2_, launches, "gemm.dgrad_small"));
+  MAGIC_TRY(launch(pl_wg_h1_, launches, "gemm.wgrad_small"));
+  if (dp) {   // bucket 0: all decoder gradients are final -> reduce them while the encoder backward runs
+    MAGIC_CUDA(cudaEventRecord(ev_bwd_[0], stream));
+    MAGIC_CUDA(cudaStreamWaitEvent(comm_stream_, ev_bwd_[0], 0));
+    MAGIC_TRY(allreduce(g1_ + n_both, (size_t)(n_total - n_both), comm_stream_));
+  }
+  MAGIC_TRY(launch(pl_dg_h1_, launches, "gemm.dgrad_small"));
+  LatentArgs la = latent_args(nullptr, labels_int_);
+  prof_begin("latent.backward"); latent_backward(la, stream); prof_end();
+  *launches += 1;
+  MAGIC_TRY(launch(pl_wg_head_, launches, "gemm.wgrad_small"));
+  MAGIC_TRY(launch(pl_dg_head_, launches, "gemm.dgrad_small"));
+  for (int i = E - 1; i >= 1; --i) {
+    MAGIC_TRY(launch(pl_wg_enc_[i], launches, "gemm.wgrad_small"));
+    MAGIC_TRY(launch(pl_dg_enc_[i], launches, "gemm.dgrad_small"));
+  }
+  if (dp) {   // bucket 1: hidden encoder layers + heads, both optimisers
+    MAGIC_CUDA(cudaEventRecord(ev_bwd_[1], stream));
+    MAGIC_CUDA(cudaStreamWaitEvent(comm_stream_, ev_bwd_[1], 0));
+    const long long o1 = lin[0].size();
+    MAGIC_TRY(allreduce(g1_ + o1, (size_t)(n_both - o1), comm_stream_));
+    MAGIC_TRY(allreduce(g2_ + o1, (size_t)(n_both - o1), comm_stream_));
+  }
+  MAGIC_TRY(launch(pl_wg_enc_[0], launches, "gemm.wgrad_enc0"));
+  if (dp) {   // bucket 2: the two 40000-wide first-layer gradients
+    MAGIC_CUDA(cudaEventRecord(ev_bwd_[2], stream));
+    MAGIC_CUDA(cudaStreamWaitEvent(comm_stream_, ev_bwd_[2], 0));
+    MAGIC_TRY(allreduce(g1_, (size_t)lin[0].size(), comm_stream_));
+    MAGIC_TRY(allreduce(g2_, (size_t)lin[0].size(), comm_stream_));
+    MAGIC_CUDA(cudaEventRecord(ev_comm_, comm_stream_));
+    MAGIC_CUDA(cudaStreamWaitEvent(stream, ev_comm_, 0));
+  }
+  MAGIC_CUDA(cudaGetLastError());
+  return "";
+}
+
+std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply) {
+  if (!d_labels && !have_labels_) return "step: no labels (pass d_labels or call magic_generate_batch first)";
+  if (d_labels) { labels_ext_ = d_labels; have_labels_ext_ = true; } else { have_labels_ext_ = false; }
+  int launches = 0;
+  std::string err = run_forward(d_eps3, true, &launches);
+  if (err.empty()) err = run_backward(&launches);
+  have_labels_ext_ = false;
+  if (!err.empty()) return err;
+  MAGIC_TRY(allreduce(statbuf_, 4, stream));   // loss scalars: local sums / Bg add up to the global means
+  if (d_losses5) { finalize_losses_kernel<<<1, 32, 0, stream>>>(statbuf_, d_losses5); ++launches; }
+  if (d_distance) MAGIC_CUDA(cudaMemcpyAsync(d_distance, dist_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
+  if (apply) {
+    ++t;
+    AdamArgs a;
+    memset(&a, 0, sizeof a);
+    a.p = p_; a.g1 = g1_; a.g2 = g2_; a.m1 = m1_; a.v1 = v1_; a.m2 = m2_; a.v2 = v2_;
+    a.w_hi = w_hi_; a.w_lo = w_lo_;
+    a.n_both = n_both; a.n_total = n_total;
+    const double b1 = cfg.beta1, b2 = cfg.beta2;
+    const double corr = sqrt(1.0 - pow(b2, (double)t)) / (1.0 - pow(b1, (double)t));
+    a.lr_t1 = (float)(cfg.lr1 * corr);
+    a.lr_t2 = (float)(cfg.lr2 * corr);
+    a.beta1 = cfg.beta1; a.beta2 = cfg.beta2; a.eps = cfg.eps;
+    prof_begin("adam.dual"); adam_dual(a, stream); prof_end();
+    ++launches;
+    stats.steps = t;
+  }
+  MAGIC_CUDA(cudaGetLastError());
+  stats.launches_last_step = launches;
+  return "";
+}
+
+std::string Engine::partial_fit_host(const float* h_x, const float* h_labels, const float* h_eps3, float* h_losses5,
+                                     float* h_distance) {
+  if (!h_x || !h_labels || !h_losses5) return "partial_fit_host: null argument";
+  const size_t nx = (size_t)B * 3 * D;
+  if (!stage_x_) MAGIC_TRY(alloc((void**)&stage_x_, sizeof(float) * nx));
+  if (!stage_labels_) MAGIC_TRY(alloc((void**)&stage_labels_, sizeof(float) * B));
+  if (h_eps3 && !stage_eps_) MAGIC_TRY(alloc((void**)&stage_eps_, sizeof(float) * 3 * B * L));
+  MAGIC_CUDA(cudaMemcpyAsync(stage_x_, h_x, sizeof(float) * nx, cudaMemcpyHostToDevice, stream));
+  MAGIC_CUDA(cudaMemcpyAsync(stage_labels_, h_labels, sizeof(float) * B, cudaMemcpyHostToDevice, stream));
+  if (h_eps3) MAGIC_CUDA(cudaMemcpyAsync(stage_eps_, h_eps3, sizeof(float) * 3 * B * L, cudaMemcpyHostToDevice, stream));
+  MAGIC_TRY(load_interleaved(stage_x_));
+  MAGIC_TRY(step(stage_labels_, h_eps3 ? stage_eps_ : nullptr, losses_dev_, nullptr, true));
+  MAGIC_CUDA(cudaMemcpyAsync(h_losses5, losses_dev_, sizeof(float) * 5, cudaMemcpyDeviceToHost, stream));
+  if (h_distance) MAGIC_CUDA(cudaMemcpyAsync(h_distance, dist_, sizeof(float) * B, cudaMemcpyDeviceToHost, stream));
+  MAGIC_CUDA(cudaStreamSynchronize(stream));
+  return "";
+}
+
+// ------------------------------------------------------------------ inference (8c/vae.py:407-434)
+std::string Engine::forward(int what, const float* d_eps3, float* d_out) {
+  if (!d_out) return "forward: null output";
+  int launches = 0;
+  have_labels_ext_ = false;
+  MAGIC_TRY(run_forward(d_eps3, false, &launches));
+  if (what == MAGIC_FWD_DISTANCE) {
+    MAGIC_CUDA(cudaMemcpyAsync(d_out, dist_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
+  } else if (what == MAGIC_FWD_ZMEAN) {   // z_mean of the lock stream: heads rows [B, 2B), cols [0, L)
+    MAGIC_CUDA(cudaMemcpy2DAsync(d_out, sizeof(float) * L, heads_ + (long long)B * ld_heads_, sizeof(float) * ld_heads_,
+                                 sizeof(float) * L, B, cudaMemcpyDeviceToDevice, stream));
+  } else if (what == MAGIC_FWD_RECON) {
+    pl_out_sig_.args.epi[0].out = d_out;
+    MAGIC_TRY(launch(pl_out_sig_, &launches, "gemm.fwd_dec_out_sigmoid"));
+  } else {
+    return "forward: unknown output selector";
+  }
+  return "";
+}
+
+std::string Engine::decode(const float* d_z, float* d_out) {
+  if (!d_z || !d_out) return "decode: null argument";
+  refresh_shadow();
+  const long long n = (long long)B * (L + 1);
+  z_to_zdec_kernel<<<(int)((n + 255) / 256), 256, 0, stream>>>(d_z, B, L, zdec_.hi, zdec_.lo, zdec_.ld);
+  int launches = 0;
+  MAGIC_TRY(launch(pl_d1_, &launches, "gemm.fwd_dec_hidden"));
+  MAGIC_TRY(launch(pl_d2_, &launches, "gemm.fwd_dec_hidden"));
+  pl_out_sig_.args.epi[0].out = d_out;
+  MAGIC_TRY(launch(pl_out_sig_, &launches, "gemm.fwd_dec_out_sigmoid"));
+  MAGIC_CUDA(cudaGetLastError());
+  return "";
+}
+
+// ------------------------------------------------------------------ data parallel
+std::string Engine::comm_init(const void* uid) {
+  MAGIC_TRY(load_nccl());
+  NcclUid id;
+  memcpy(&id, uid, sizeof id);
+  const int r = g_nccl.init_rank(&comm_, cfg.world, id, cfg.rank);
+  if (r != 0) return std::string("ncclCommInitRank: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "error");
+  nccl_ = &g_nccl;
+  MAGIC_CUDA(cudaStreamCreateWithFlags(&comm_stream_, cudaStreamNonBlocking));
+  return "";
+}
+
+// ------------------------------------------------------------------ parameter windows
+std::string Engine::copy_param(int i, float* h_dst, const float* h_src, const float* base) {
+  if (i < 0 || i >= (int)views.size()) return "parameter index out of range";
+  const ParamView& v = views[i];
+  const Linear& l = lin[v.layer];
+  float* win = const_cast<float*>(base) + l.off + (long long)v.row0 * l.ld + v.col0;
+  MAGIC_CUDA(cudaStreamSynchronize(stream));
+  if (h_dst)
+    MAGIC_CUDA(cudaMemcpy2D(h_dst, sizeof(float) * v.ncols, win, sizeof(float) * l.ld, sizeof(float) * v.ncols, v.nrows,
+                            cudaMemcpyDeviceToHost));
+  else
+    MAGIC_CUDA(cudaMemcpy2D(win, sizeof(float) * l.ld, h_src, sizeof(float) * v.ncols, sizeof(float) * v.ncols, v.nrows,
+                            cudaMemcpyHostToDevice));
+  return "";
+}
+std::string Engine::set_param(int i, const float* h) {
+  if (!h) return "set_param: null source";
+  shadow_dirty_ = true;
+  return copy_param(i, nullptr, h, p_);
+}
+std::string Engine::get_grad(int which, int i, float* h) {
+  if (which != 1 && which != 2) return "get_grad: which must be 1 or 2";
+  if (i < 0 || i >= (int)views.size()) return "parameter index out of range";
+  if (which == 2 && !(views[i].optimisers & 2)) return "get_grad: optimiser 2 does not train this variable";
+  return copy_param(i, h, nullptr, which == 1 ? g1_ : g2_);
+}
+std::string Engine::slot(int which, int sl, int i, float* h_dst, const float* h_src) {
+  if (which != 1 && which != 2) return "slot: which must be 1 or 2";
+  if (i < 0 || i >= (int)views.size()) return "parameter index out of range";
+  if (which == 2 && !(views[i].optimisers & 2)) return "slot: optimiser 2 does not train this variable";
+  const float* base = which == 1 ? (sl == MAGIC_SLOT_M ? m1_ : v1_) : (sl == MAGIC_SLOT_M ? m2_ : v2_);
+  return copy_param(i, h_dst, h_src, base);
+}
+
+}  // namespace magic

@@ -1,0 +1,144 @@
+// The training engine behind the C ABI: parameter layout, activations, GEMM plans, step orchestration.
+#pragma once
+#include <string>
+#include <vector>
+#include "magic_b200.h"
+#include "gemm.h"
+#include "kernels.h"
+
+namespace magic {
+
+typedef __nv_bfloat16 bf16;
+
+// One dense layer y = [x | 1] . Wp, with the bias stored as the extra row Kv of the padded weight matrix
+// (bias-as-row: biases and bias gradients ride through the GEMMs).
+struct Linear {
+  int Kv = 0, Nv = 0;          // valid fan-in / fan-out
+  long long ld = 0;            // row pitch of Wp (elements), multiple of 64
+  long long off = 0;           // offset of Wp in the flat parameter buffers
+  long long rows() const { return Kv + 1; }
+  long long size() const { return rows() * ld; }
+};
+
+// A reference variable (8c/vae.py:89-147) as a rectangular window of a Linear's padded matrix.
+struct ParamView {
+  std::string name;
+  int layer = 0;               // index into Engine::lin
+  int row0 = 0, nrows = 0;     // window rows
+  int col0 = 0, ncols = 0;     // window cols
+  bool is_bias = false;
+  int optimisers = 1;          // bitmask: 1 = cost optimiser, 2 = metric optimiser
+};
+
+struct Act {                   // bf16 activation buffer (+ low part in the fp32 mode)
+  bf16* hi = nullptr;
+  bf16* lo = nullptr;
+  long long rows = 0, ld = 0;
+};
+
+struct NcclApi;
+
+class Engine {
+ public:
+  Engine() {}
+  ~Engine();
+  std::string init(const magic_config& cfg, cudaStream_t stream);
+
+  std::string load_interleaved(const float* d_x);
+  std::string load_planar_u8(const uint8_t* l, const uint8_t* r, const uint8_t* k);
+  std::string generate(uint64_t seed, uint64_t step);
+  std::string export_batch(float* d_x, float* d_labels);
+  std::string step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply);
+  std::string partial_fit_host(const float* h_x, const float* h_labels, const float* h_eps3, float* h_losses5,
+                               float* h_distance);
+  std::string forward(int what, const float* d_eps3, float* d_out);
+  std::string decode(const float* d_z, float* d_out);
+  std::string comm_init(const void* uid);
+  // per-launch CUDA-event timing (bench / optimisation aid): tag -> accumulated ms, launches
+  void profile_enable(bool on);
+  std::string profile_report();     // synchronises; "tag ms count flops\n" lines; resets the accumulators
+
+  std::string copy_param(int i, float* h_dst, const float* h_src, const float* base);   // get (h_dst) or set (h_src)
+  std::string get_param(int i, float* h) { return copy_param(i, h, nullptr, p_); }
+  std::string set_param(int i, const float* h);
+  std::string get_grad(int which, int i, float* h);
+  std::string slot(int which, int slot, int i, float* h_dst, const float* h_src);
+
+  magic_config cfg{};
+  cudaStream_t stream = nullptr;
+  std::vector<Linear> lin;          // encoder hidden 0..E-1, heads, dec h1, dec h2, dec out
+  std::vector<ParamView> views;
+  long long n_both = 0, n_total = 0;
+  int64_t t = 0;                    // optimiser step counter
+  magic_stats stats{};
+
+ private:
+  std::string alloc(void** p, size_t bytes);
+  std::string alloc_act(Act* a, long long rows, int width_plus_bias);
+  std::string build_plans();
+  std::string run_forward(const float* d_eps3, bool train, int* launches);
+  std::string run_backward(int* launches);
+  std::string launch(GemmPlan& pl, int* launches, const char* tag);
+  void prof_begin(const char* tag, double flops = 0);
+  void prof_end();
+  struct ProfRec { std::string tag; cudaEvent_t a, b; double flops; };
+  std::vector<ProfRec> prof_pending_;
+  std::vector<cudaEvent_t> prof_pool_;
+  struct ProfAcc { std::string tag; double ms = 0; long long n = 0; double flops = 0; };
+  std::vector<ProfAcc> prof_acc_;
+  bool profile_ = false;
+  void refresh_shadow();
+  LatentArgs latent_args(const float* d_eps3, const float* d_labels);
+  Mat wmat(int layer, bool lo) const;                 // weights as stored: Mat[Kv+1, Nv]
+  static Mat amat(const Act& a, bool lo, long long row0, long long rows, long long cols);
+  int add_segments(GemmProblem& p, int g, Mat a_hi, Mat a_lo, Mat b_hi, Mat b_lo, bool a_exact);
+
+  int E = 0, iHead = 0, iD1 = 0, iD2 = 0, iOut = 0;
+  int B = 0, D = 0, L = 0;
+  bool split = false;               // fp32 mode (bf16x3)
+  int num_sms = 148;
+  float inv_bg = 1.f;
+
+  // flat parameter-shaped buffers
+  float *p_ = nullptr, *g1_ = nullptr, *g2_ = nullptr, *m1_ = nullptr, *v1_ = nullptr, *m2_ = nullptr, *v2_ = nullptr;
+  bf16 *w_hi_ = nullptr, *w_lo_ = nullptr;
+  bool shadow_dirty_ = true;
+
+  // activations
+  Act X_;                           // [3B, D+1]  rows [rot; lock; key]
+  std::vector<Act> H_;              // encoder hidden outputs [3B, enc_i + 1]
+  float* heads_ = nullptr; long long ld_heads_ = 0;      // [3B, 2L] fp32
+  float* z_ = nullptr;              // [3B, L]
+  Act zdec_, D1_, D2_;              // decoder input / hidden [B, *]
+  Act dA_;                          // [B, D]  sigma(a) - x
+  Act dD2_, dD1_;                   // decoder pre-activation grads [B, *]
+  float* dz_dec_ = nullptr; long long ld_dz_ = 0;        // [B, L] fp32
+  Act dheads_;                      // [4B, 2L]
+  std::vector<Act> dH_;             // encoder pre-activation grads [4B, enc_i]
+  float* ws_ = nullptr; long long ws_ld_ = 0;            // split-K workspace
+  float* statbuf_ = nullptr;        // [8 sums | 2L colsq | L colS]
+  float *g_row_ = nullptr, *dist_ = nullptr, *labels_int_ = nullptr, *losses_dev_ = nullptr;
+  float *stage_x_ = nullptr, *stage_labels_ = nullptr, *stage_eps_ = nullptr;   // partial_fit_host staging
+  bool have_labels_ = false;
+  const float* labels_ext_ = nullptr;
+  bool have_labels_ext_ = false;
+
+  // plans
+  std::vector<GemmPlan> fwd_enc_;   // E hidden + heads
+  GemmPlan pl_d1_, pl_d2_, pl_out_bce_, pl_out_sig_;
+  GemmPlan pl_wg_out_, pl_dg_out_, pl_wg_h2_, pl_dg_h2_, pl_wg_h1_, pl_dg_h1_;
+  GemmPlan pl_wg_head_, pl_dg_head_;
+  std::vector<GemmPlan> pl_wg_enc_, pl_dg_enc_;   // index i: wgrad of layer i; dgrad through layer i (i >= 1)
+  struct ZeroRange { float* ptr; size_t bytes; };
+  std::vector<ZeroRange> zero_;     // gradient windows written with red.add (split-K) -> cleared every step
+
+  // data parallel
+  NcclApi* nccl_ = nullptr;
+  void* comm_ = nullptr;
+  cudaStream_t comm_stream_ = nullptr;
+  cudaEvent_t ev_bwd_[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_comm_ = nullptr;
+  std::string allreduce(float* buf, size_t n, cudaStream_t s);
+};
+
+}  // namespace magic

@@ -138,6 +138,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.ngroups = p.ngroups;
   a.tiles_m = (p.M + kBlockM - 1) / kBlockM;
   a.tiles_n = (p.N + kBlockN - 1) / kBlockN;
+  a.m_fastest = p.N > p.M ? 1 : 0;   // keep the larger operand's tiles adjacent in time so it is read from HBM once
   const int tiles = a.tiles_m * a.tiles_n * a.ngroups;
   const int total_kb = a.nseg * a.kblocks;
   const bool linear = p.epi == EPI_STORE_F32;

@@ -64,6 +64,7 @@ struct GemmArgs {
   int kblocks;       // K blocks (of 64) per segment
   int nseg, ngroups, splitk;
   int tiles_m, tiles_n;
+  int m_fastest;     // tile order: consecutive work items walk M first (B is the large operand) or N first
 };
 
 struct WorkItem {
@@ -72,10 +73,14 @@ struct WorkItem {
 
 __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w) {
   WorkItem it;
-  int nt = w % a.tiles_n;
-  int t = w / a.tiles_n;
-  int mt = t % a.tiles_m;
-  t /= a.tiles_m;
+  int nt, mt, t;
+  if (a.m_fastest) {
+    mt = w % a.tiles_m; t = w / a.tiles_m;
+    nt = t % a.tiles_n; t /= a.tiles_n;
+  } else {
+    nt = w % a.tiles_n; t = w / a.tiles_n;
+    mt = t % a.tiles_m; t /= a.tiles_m;
+  }
   it.g = t % a.ngroups;
   int ks = t / a.ngroups;
   int total_kb = a.nseg * a.kblocks;

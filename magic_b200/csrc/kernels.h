@@ -1,0 +1,72 @@
+// Non-GEMM kernels of the step: latent layer (reparameterisation, KL, deformation, metric loss and the four
+// upstream latent gradients), fused dual Adam, input layout conversion, synthetic pair generator.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace magic {
+
+enum MetricKind : int { METRIC_COSINE = 0, METRIC_SQDIFF = 1 };
+
+// Row order of every [3B, *] activation buffer: [rot ; lock ; key]  (so both optimisers' wgrads read a
+// contiguous 2B-row range: cost -> rows [0,2B), metric -> rows [B,3B)).
+// Row order of every [4B, *] backward buffer: [rot|cost ; lock|cost ; lock|metric ; key|metric].
+struct LatentArgs {
+  int B;                 // local batch (pairs)
+  int L;                 // latent dims
+  float inv_bg;          // 1 / global batch
+  float def_weight;      // 10 (8c/vae.py:287) or 100 (11a/vae.py:293)
+  int metric;            // MetricKind
+  int reciprocal;        // 9a/vae.py:301
+  const float* heads;    // [3B, ld_heads]: mu at cols [0,L), log sigma^2 at cols [L,2L)
+  long long ld_heads;
+  const float* eps;      // [3, B, L] in API order (lock, rot, key), or nullptr -> internal RNG
+  uint64_t seed, step;   // internal RNG counters (seed, step, rank folded into seed by the host)
+  float* z;              // [3B, L] sampled latents (row order rot, lock, key)
+  __nv_bfloat16* zdec;   // [B, ld_zdec] decoder input: z_lock, 1.0 at col L (bias column), zero pad
+  __nv_bfloat16* zdec_lo;
+  long long ld_zdec;
+  const float* labels;   // [B]
+  float* colsq;          // [2, L]  sum_i z_lock^2, sum_i z_key^2   (cosine; all-reduced across ranks)
+  float* colS;           // [L]     sum_i g_i a^_ij b^_ij           (cosine backward; all-reduced)
+  float* g;              // [B]     d training_loss / d dist_i (pre-reciprocal chain applied)
+  float* distance;       // [B]     f(dist_i) as returned by get_predictions
+  float* sums;           // [8]: 0 rec (written by the BCE epilogue), 1 kl, 2 def, 3 training  -- already / Bg
+  const float* dz_dec;   // [B, ld_dz] decoder dgrad into z_lock, unscaled (sum over pixels of (sigma-x).W)
+  long long ld_dz;
+  __nv_bfloat16* dheads; // [4B, ld_dheads]: d mu at cols [0,L), d log sigma^2 at [L,2L)
+  __nv_bfloat16* dheads_lo;
+  long long ld_dheads;
+};
+
+void latent_forward(const LatentArgs& a, cudaStream_t s);     // z, zdec, kl, def, colsq (cosine) ; sqdiff: also metric
+void latent_metric(const LatentArgs& a, cudaStream_t s);      // distance, training loss, g, colS (needs final colsq)
+void latent_backward(const LatentArgs& a, cudaStream_t s);    // dheads for the four backward streams
+
+struct AdamArgs {
+  float* p;                       // fp32 master parameters, flat
+  const float* g1; const float* g2;
+  float* m1; float* v1; float* m2; float* v2;
+  __nv_bfloat16* w_hi; __nv_bfloat16* w_lo;   // bf16 shadow (lo may be null)
+  long long n_both;               // leading elements updated by both optimisers (encoder)
+  long long n_total;              // all elements (encoder + used decoder)
+  float lr_t1, lr_t2;             // lr * sqrt(1-beta2^t) / (1-beta1^t)
+  float beta1, beta2, eps;
+};
+void adam_dual(const AdamArgs& a, cudaStream_t s);
+void shadow_refresh(const float* p, __nv_bfloat16* hi, __nv_bfloat16* lo, long long n, cudaStream_t s);
+
+// X [B, 3*D] fp32 channel-interleaved (8c/vae.py:166, ch0 lock, ch1 rot, ch2 key) -> planes bf16 [3B, ld]
+// rows [rot; lock; key], 1.0 at col D, zeros after.
+void deinterleave_f32(const float* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s);
+void planar_u8(const uint8_t* lock, const uint8_t* rot, const uint8_t* key, int B, int D, __nv_bfloat16* planes,
+               long long ld, cudaStream_t s);
+void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B, int D, float* x, cudaStream_t s);
+
+// On-device synthetic shape pairs (replaces 8c/overlap_input.py): random filled shapes on a
+// side x side canvas, nearest-neighbour rotated copy (8c/utils.py:329-340), integer overlap label.
+void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, float* labels,
+                    cudaStream_t s);
+
+}  // namespace magic

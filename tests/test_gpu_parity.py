@@ -1,0 +1,129 @@
+"""Parity of the CUDA engine (through the C ABI) against the float64 oracle on identical weights, inputs,
+labels and noise.  Tolerances are BASELINE.json's: 1e-4 (fp32 mode) and 2e-2 (bf16 mode), applied as relative
+L2 error per tensor (tests/util.py)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import tango_oracle as orc
+from tests.util import TOL, engine_config_from_oracle, make_pair, oracle_config, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+MINI = dict(encoder_neurons=[120, 72], decoder_neurons=[88, 104], n_input=1600)
+
+CASES = [
+    # name, oracle config kwargs, batch
+    ("mini-cos", dict(latent=20, **MINI), 64),
+    ("mini-cos-recip", dict(latent=2, reciprocal=True, **MINI), 48),
+    ("mini-sqdiff-elu", dict(latent=80, act="elu", metric="sqdiff", reciprocal=True, def_weight=100.0,
+                             lr=(1e-6, 1e-8), **MINI), 24),
+    ("mini-ragged", dict(latent=7, encoder_neurons=[100], decoder_neurons=[60, 52], n_input=400), 37),
+]
+
+
+# Operand precision of the two modes relative to true fp32 (2^-24): the fp32 mode carries hi+lo bf16 pairs
+# (2^-17), the bf16 mode 2^-9.  An ill-conditioned quantity (9a: reciprocal of a near-zero cosine sum) amplifies
+# ANY rounding, also the reference's own fp32 arithmetic; its amplification is measured by running the oracle in
+# float32 ("noise floor").  Allowed error = max(north_star tolerance, AMP * floor).
+AMP = {"fp32": 2.0 * 2 ** 7, "bf16": 2.0 * 2 ** 15}
+
+
+def _compare_step(ocfg, batch, precision):
+    state, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, batch, precision)
+    tol, amp = TOL[precision], AMP[precision]
+    out, g1, g2 = state.grads(xl, xr, xk, y, eps)
+    s32 = orc.OracleState(ocfg, params=state.params, dtype=torch.float32)
+    f32 = lambda t: t.to(torch.float32)
+    out32, g1_32, g2_32 = s32.grads(f32(xl), f32(xr), f32(xk), f32(y), f32(eps))
+    eng.load_interleaved(orc.interleave(xl, xr, xk).to(torch.float32))
+    losses, dist = eng.step(labels=y.to(torch.float32), eps3=eps.to(torch.float32), apply=False, want_distance=True)
+    losses = losses.cpu().numpy()
+    report = {}
+    for i, k in enumerate(orc.LOSS_KEYS):
+        ref = float(out[k])
+        floor = abs(float(out32[k]) - ref) / max(abs(ref), 1e-30)
+        err = abs(losses[i] - ref) / max(abs(ref), 1e-30)
+        report[k] = (err, max(tol, amp * floor))
+    report["distance"] = (rel_l2(dist.cpu().numpy(), out["distance"].numpy()),
+                          max(tol, amp * rel_l2(out32["distance"].numpy(), out["distance"].numpy())))
+    for which, g, g32 in ((1, g1, g1_32), (2, g2, g2_32)):
+        for name, ref in g.items():
+            floor = rel_l2(g32[name].numpy(), ref.numpy())
+            report[(which, name)] = (rel_l2(eng.get_grad(which, name), ref.numpy()), max(tol, amp * floor))
+    bad = {k: v for k, v in report.items() if not v[0] <= v[1]}
+    assert not bad, "mismatch (rel error, allowed): %s" % bad
+    eng.close()
+    return report
+
+
+@pytest.mark.parametrize("name,kw,batch", CASES, ids=[c[0] for c in CASES])
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_losses_and_gradients(name, kw, batch, precision):
+    _compare_step(oracle_config(**kw), batch, precision)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_full_size_8c(precision):
+    """Experiment 8c as written (D=40000, 500x4, L=20), small batch so the float64 oracle finishes in seconds."""
+    _compare_step(orc.OracleConfig.experiment("8c"), 12, precision)
+
+
+def test_full_size_11a_fp32():
+    _compare_step(orc.OracleConfig.experiment("11a"), 8, "fp32")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_ten_steps_track_the_oracle(precision):
+    """Params after 10 steps of both Adam optimisers (TF1 formula, W <- W - d1 - d2)."""
+    ocfg = oracle_config(latent=20, **MINI)
+    state, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, 64, precision)
+    X = orc.interleave(xl, xr, xk).to(torch.float32)
+    p0 = {k: v.clone() for k, v in state.params.items()}
+    for it in range(10):
+        out, _, _ = state.step(xl, xr, xk, y, eps)
+        eng.load_interleaved(X)
+        losses, _ = eng.step(labels=y.to(torch.float32), eps3=eps.to(torch.float32))
+        l = losses.cpu().numpy()
+        assert abs(l[0] - float(out["cost"])) <= max(TOL[precision], 1e-3) * abs(float(out["cost"])), (it, l[0])
+    assert eng.step_count == 10
+    # compare the accumulated UPDATE (the first Adam steps move every weight by ~lr regardless of |g|, so the
+    # update vector is the sensitive quantity); sign flips of ~zero gradients bound the achievable agreement
+    for name in eng.param_names:
+        upd_ref = (state.params[name] - p0[name]).numpy()
+        upd = eng.get_param(name).astype(np.float64) - p0[name].numpy()
+        if np.linalg.norm(upd_ref) == 0:
+            assert np.linalg.norm(upd) == 0
+            continue
+        assert rel_l2(upd, upd_ref) <= (0.02 if precision == "fp32" else 0.25), name
+    eng.close()
+
+
+def test_inference_surface():
+    """get_predictions / transform / reconstruct / generate (8c/vae.py:407-434)."""
+    from magic_b200 import _lib
+    ocfg = oracle_config(latent=20, **MINI)
+    state, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, 64, "fp32")
+    eng.load_interleaved(orc.interleave(xl, xr, xk).to(torch.float32))
+    out = orc.forward(ocfg, state.params, xl, xr, xk, y, eps)
+    e32 = eps.to(torch.float32)
+    assert rel_l2(eng.forward(_lib.FWD_DISTANCE, e32).cpu().numpy(), out["distance"].numpy()) <= 1e-4
+    assert rel_l2(eng.forward(_lib.FWD_ZMEAN, e32).cpu().numpy(), out["z_mean"].numpy()) <= 1e-4
+    rec = torch.sigmoid(out["logits"]).numpy()
+    assert rel_l2(eng.forward(_lib.FWD_RECON, e32).cpu().numpy(), rec) <= 1e-4
+    z = torch.randn(64, 20, dtype=torch.float64)
+    ref = torch.sigmoid(orc.decode_logits(ocfg, state.params, z)).numpy()
+    assert rel_l2(eng.decode(z.to(torch.float32)).cpu().numpy(), ref) <= 1e-4
+    eng.close()
+
+
+def test_host_partial_fit_matches_device_path():
+    ocfg = oracle_config(latent=20, **MINI)
+    state, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, 64, "fp32")
+    X = orc.interleave(xl, xr, xk).to(torch.float32).numpy()
+    out, _, _ = state.step(xl, xr, xk, y, eps)
+    losses, dist = eng.partial_fit_host(X, y.numpy().astype(np.float32), eps.numpy().astype(np.float32), True)
+    for i, k in enumerate(orc.LOSS_KEYS):
+        assert abs(losses[i] - float(out[k])) <= 1e-4 * abs(float(out[k])), k
+    assert rel_l2(dist, out["distance"].numpy()) <= 1e-4
+    eng.close()
