@@ -466,7 +466,7 @@ std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uin
 }
 std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
   const int side = (int)llround(sqrt((double)D));
-  if (side * side != D) return "generate: D is not a square canvas";
+  if (side * side != D || side % 8 != 0) return "generate: D must be a square canvas with side % 8 == 0";
   // fold the rank into the seed so every rank draws different pairs
   prof_begin("input.generate");
   generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, X_.hi, X_.ld, labels_int_, stream);

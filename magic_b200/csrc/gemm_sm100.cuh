@@ -12,8 +12,8 @@
 // wgrads) into one launch.  Split-K spreads long reductions with few output tiles over all SMs; partial
 // sums are combined with vector red.global.add.
 //
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
-// warps 2..5 = epilogue (TMEM -> registers -> fused epilogue -> global).  Two TMEM accumulator stages
+// Roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
+// warps 2..9 = epilogue (TMEM -> registers -> fused epilogue -> global).  Two TMEM accumulator stages
 // (2 x 256 columns) let the epilogue of tile i overlap the MMAs of tile i+1.
 #pragma once
 #include <cuda.h>
@@ -28,7 +28,8 @@ constexpr int kStages = 4;
 constexpr int kUmmaK = 16;
 constexpr int kMaxGroups = 2;
 constexpr int kMaxSegs = 3;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
+constexpr int kEpiWarps = 8;
 constexpr uint32_t kStageBytesA = kBlockM * kBlockK * 2;   // 16 KiB
 constexpr uint32_t kStageBytesB = kBlockN * kBlockK * 2;   // 32 KiB
 constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
@@ -93,28 +94,33 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w) {
 }
 
 // ---------------------------------------------------------------------------- epilogue math
-__device__ __forceinline__ float act_fwd(float x, int act, int precise) {
-  if (act == ACT_TANH) {
-    if (precise) return tanhf(x);
+// ACT / PRECISE are compile-time: a run-time branch inside the per-element loops would stop ptxas from
+// interleaving the (independent) elements, and the epilogue warps have nobody else to hide latency behind.
+template <int ACT, bool PRECISE>
+__device__ __forceinline__ float act_fwd(float x) {
+  if constexpr (ACT == ACT_TANH) {
+    if constexpr (PRECISE) return tanhf(x);
     float y;
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
-  }
-  if (act == ACT_ELU) {
-    if (precise) return x > 0.f ? x : expm1f(x);
+  } else if constexpr (ACT == ACT_ELU) {
+    if constexpr (PRECISE) return x > 0.f ? x : expm1f(x);
     return x > 0.f ? x : __expf(x) - 1.f;
+  } else {
+    return x;
   }
-  return x;
 }
 // derivative written in terms of the OUTPUT y: tanh' = 1 - y^2 ; elu' = 1 (y > 0) else y + 1
-__device__ __forceinline__ float act_bwd_from_y(float y, int act) {
-  if (act == ACT_TANH) return 1.f - y * y;
-  if (act == ACT_ELU) return y > 0.f ? 1.f : y + 1.f;
-  return 1.f;
+template <int ACT>
+__device__ __forceinline__ float act_bwd_from_y(float y) {
+  if constexpr (ACT == ACT_TANH) return 1.f - y * y;
+  else if constexpr (ACT == ACT_ELU) return y > 0.f ? 1.f : y + 1.f;
+  else return 1.f;
 }
 // softplus(b) and sigmoid(b) from t = exp(-|b|)
-__device__ __forceinline__ void softplus_sigmoid(float b, int precise, float& sp, float& sg) {
-  if (precise) {
+template <bool PRECISE>
+__device__ __forceinline__ void softplus_sigmoid(float b, float& sp, float& sg) {
+  if constexpr (PRECISE) {
     float t = expf(-fabsf(b));
     sp = fmaxf(b, 0.f) + log1pf(t);
     float r = 1.f / (1.f + t);
@@ -134,27 +140,33 @@ __device__ __forceinline__ void softplus_sigmoid(float b, int precise, float& sp
   }
 }
 
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
-                                               int N, float& loss_acc) {
-  if (row >= M) return;
+template <int EPI, int ACT, bool PRECISE>
+__device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
+                                              int N, float& loss_acc) {
   if constexpr (EPI == EPI_STORE_F32) {
     float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
+    const float alpha = e.alpha;
+    if (col0 + 32 <= N) {
+      if (e.atomic) {
 #pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-      float v0 = __uint_as_float(r[j]) * e.alpha, v1 = __uint_as_float(r[j + 1]) * e.alpha;
-      float v2 = __uint_as_float(r[j + 2]) * e.alpha, v3 = __uint_as_float(r[j + 3]) * e.alpha;
-      if (col0 + j + 3 < N) {
-        if (e.atomic) ptx::red_add_v4(out + j, v0, v1, v2, v3);
-        else *reinterpret_cast<float4*>(out + j) = make_float4(v0, v1, v2, v3);
+        for (int j = 0; j < 32; j += 4)
+          ptx::red_add_v4(out + j, __uint_as_float(r[j]) * alpha, __uint_as_float(r[j + 1]) * alpha,
+                          __uint_as_float(r[j + 2]) * alpha, __uint_as_float(r[j + 3]) * alpha);
       } else {
-        float v[4] = {v0, v1, v2, v3};
-        for (int q = 0; q < 4; ++q)
-          if (col0 + j + q < N) {
-            if (e.atomic) atomicAdd(out + j + q, v[q]);
-            else out[j + q] = v[q];
-          }
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(out + j) =
+              make_float4(__uint_as_float(r[j]) * alpha, __uint_as_float(r[j + 1]) * alpha,
+                          __uint_as_float(r[j + 2]) * alpha, __uint_as_float(r[j + 3]) * alpha);
       }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < N) {
+          const float v = __uint_as_float(r[j]) * alpha;
+          if (e.atomic) atomicAdd(out + j, v);
+          else out[j] = v;
+        }
     }
   } else if constexpr (EPI == EPI_SIGMOID) {
     float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
@@ -162,7 +174,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t 
     for (int j = 0; j < 32; ++j) {
       if (col0 + j < N) {
         float sp, sg;
-        softplus_sigmoid(__uint_as_float(r[j]), 1, sp, sg);
+        softplus_sigmoid<true>(__uint_as_float(r[j]), sp, sg);
         out[j] = sg;
       }
     }
@@ -175,7 +187,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t 
       for (int q = 0; q < 2; ++q) {
         int c = col0 + j + q;
         float x = __uint_as_float(r[j + q]) * e.alpha;
-        v[q] = c < e.n_valid ? act_fwd(x, e.act, e.precise) : (c == e.n_valid ? 1.f : 0.f);
+        v[q] = c < e.n_valid ? act_fwd<ACT, PRECISE>(x) : (c == e.n_valid ? 1.f : 0.f);
       }
       uint32_t h = ptx::pack_bf16(v[0], v[1]);
       hi[j >> 1] = h;
@@ -215,8 +227,8 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t 
     for (int j = 0; j < 32; j += 2) {
       float y0 = ptx::bf16_lo(y[j >> 1]) + ptx::bf16_lo(yl[j >> 1]);
       float y1 = ptx::bf16_hi(y[j >> 1]) + ptx::bf16_hi(yl[j >> 1]);
-      float v0 = (col0 + j < e.n_valid) ? __uint_as_float(r[j]) * e.alpha * act_bwd_from_y(y0, e.act) : 0.f;
-      float v1 = (col0 + j + 1 < e.n_valid) ? __uint_as_float(r[j + 1]) * e.alpha * act_bwd_from_y(y1, e.act) : 0.f;
+      float v0 = (col0 + j < e.n_valid) ? __uint_as_float(r[j]) * e.alpha * act_bwd_from_y<ACT>(y0) : 0.f;
+      float v1 = (col0 + j + 1 < e.n_valid) ? __uint_as_float(r[j + 1]) * e.alpha * act_bwd_from_y<ACT>(y1) : 0.f;
       uint32_t h = ptx::pack_bf16(v0, v1);
       hi[j >> 1] = h;
       lo[j >> 1] = ptx::pack_bf16(v0 - ptx::bf16_lo(h), v1 - ptx::bf16_hi(h));
@@ -246,8 +258,8 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t 
       float a0 = __uint_as_float(r[j]), a1 = __uint_as_float(r[j + 1]);
       float x0 = ptx::bf16_lo(x[j >> 1]), x1 = ptx::bf16_hi(x[j >> 1]);
       float sp0, sg0, sp1, sg1;
-      softplus_sigmoid(a0, e.precise, sp0, sg0);
-      softplus_sigmoid(a1, e.precise, sp1, sg1);
+      softplus_sigmoid<PRECISE>(a0, sp0, sg0);
+      softplus_sigmoid<PRECISE>(a1, sp1, sg1);
       bool in0 = col0 + j < N, in1 = col0 + j + 1 < N;
       float d0 = in0 ? sg0 - x0 : 0.f, d1 = in1 ? sg1 - x1 : 0.f;
       if (in0) acc += sp0 - x0 * a0;
@@ -266,6 +278,27 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t 
 #pragma unroll
       for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
     }
+  }
+}
+
+// Run-time (act, precise) -> compile-time variant, decided once per 32-column chunk (warp-uniform).
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
+                                               int N, float& loss_acc) {
+  if (row >= M) return;
+  if constexpr (EPI == EPI_ACT || EPI == EPI_DACT) {
+    if (e.act == ACT_TANH) {
+      if (e.precise) epilogue_impl<EPI, ACT_TANH, true>(e, r, row, col0, M, N, loss_acc);
+      else epilogue_impl<EPI, ACT_TANH, false>(e, r, row, col0, M, N, loss_acc);
+    } else {
+      if (e.precise) epilogue_impl<EPI, ACT_ELU, true>(e, r, row, col0, M, N, loss_acc);
+      else epilogue_impl<EPI, ACT_ELU, false>(e, r, row, col0, M, N, loss_acc);
+    }
+  } else if constexpr (EPI == EPI_BCE) {
+    if (e.precise) epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc);
+    else epilogue_impl<EPI, ACT_NONE, false>(e, r, row, col0, M, N, loss_acc);
+  } else {
+    epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc);
   }
 }
 
@@ -300,7 +333,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tcgen05_kernel(const __g
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
-      ptx::mbar_init(&tempty_bar[i], 128);
+      ptx::mbar_init(&tempty_bar[i], kEpiWarps * 32);
     }
     ptx::fence_barrier_init();
   } else if (warp == 1) {
@@ -379,8 +412,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tcgen05_kernel(const __g
       }
     }
   } else {
-    // ------------------------------------------------------------ epilogue warps (TMEM lane quarter = warp % 4)
+    // ------------------------------------------------------------ epilogue warps
+    // TMEM lane quarter = warp % 4 (hardware rule); the two warps of a quarter split the 32-column chunks
+    // even/odd, so every scheduler has two epilogue warps to overlap latencies with.
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
     uint32_t iter = 0;
     float loss_acc = 0.f;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
@@ -392,15 +428,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tcgen05_kernel(const __g
       const int row = it.m0 + q * 32 + lane;
       const int ncols = min(kBlockN, args.N - it.n0);
       const int nchunks = (ncols + 31) >> 5;
-      for (int c = 0; c < nchunks; ++c) {
+      bool arrived = false;
+      for (int c = half; c < nchunks; c += 2) {
         uint32_t r[32];
         ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kBlockN + c * 32, r);
         ptx::tmem_ld_wait();
-        if (c == nchunks - 1) {   // all TMEM reads of this accumulator are done: hand it back to the MMA warp
+        if (c + 2 >= nchunks) {   // this warp's last TMEM read of the accumulator: hand it back to the MMA warp
           ptx::tc_fence_before();
           ptx::mbar_arrive(&tempty_bar[acc]);
+          arrived = true;
         }
         epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc);
+      }
+      if (!arrived) {
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(&tempty_bar[acc]);
       }
     }
     if constexpr (EPI == EPI_BCE) {

@@ -366,94 +366,120 @@ void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B,
 //        "maximum overlap area"; the reference's dataset generator is not in the repository).
 constexpr int kPrims = 3;
 constexpr int kLabelRots = 8;
+// A primitive as an affine map to its unit frame: u = ax*x + ay*y + a0 ; v = bx*x + by*y + b0 ;
+// ellipse: u^2 + v^2 <= 1 ; box: max(|u|,|v|) <= 1.
+struct Prim { float ax, ay, a0, bx, by, b0; int box; };
 struct Shape {
-  float cx[kPrims], cy[kPrims], a[kPrims], b[kPrims], cs[kPrims], sn[kPrims];
-  int box[kPrims];
+  Prim p[kPrims];
+  float xmin, xmax, ymin, ymax;   // pixel bounding box of the union
 };
-__device__ __forceinline__ void make_shape(Shape& s, uint64_t key, float side) {
-#pragma unroll
-  for (int k = 0; k < kPrims; ++k) {
-    const uint64_t r0 = splitmix64(key + 3 * k), r1 = splitmix64(key + 3 * k + 1), r2 = splitmix64(key + 3 * k + 2);
-    const float c = 0.5f * (side - 1.f);
-    s.cx[k] = c + (u01((uint32_t)r0) - 0.5f) * 0.24f * side;
-    s.cy[k] = c + (u01((uint32_t)(r0 >> 32)) - 0.5f) * 0.24f * side;
-    s.a[k] = (0.05f + 0.11f * u01((uint32_t)r1)) * side;
-    s.b[k] = (0.05f + 0.11f * u01((uint32_t)(r1 >> 32))) * side;
-    const float phi = 6.2831853f * u01((uint32_t)r2);
-    s.cs[k] = cosf(phi);
-    s.sn[k] = sinf(phi);
-    s.box[k] = (int)((r2 >> 40) & 1);
-  }
+__device__ __forceinline__ bool prim_hit(const Prim& q, float x, float y) {
+  const float u = fmaf(q.ax, x, fmaf(q.ay, y, q.a0)), v = fmaf(q.bx, x, fmaf(q.by, y, q.b0));
+  return q.box ? fmaxf(fabsf(u), fabsf(v)) <= 1.f : fmaf(u, u, v * v) <= 1.f;
 }
 __device__ __forceinline__ bool inside(const Shape& s, float x, float y) {
+  if (x < s.xmin || x > s.xmax || y < s.ymin || y > s.ymax) return false;
   bool in = false;
 #pragma unroll
-  for (int k = 0; k < kPrims; ++k) {
-    const float dx = x - s.cx[k], dy = y - s.cy[k];
-    const float u = (dx * s.cs[k] + dy * s.sn[k]) / s.a[k], v = (-dx * s.sn[k] + dy * s.cs[k]) / s.b[k];
-    in |= s.box[k] ? (fabsf(u) <= 1.f && fabsf(v) <= 1.f) : (u * u + v * v <= 1.f);
-  }
+  for (int k = 0; k < kPrims; ++k) in |= prim_hit(s.p[k], x, y);
   return in;
 }
+__device__ void make_shape(Shape& s, uint64_t key, float side) {
+  s.xmin = s.ymin = 1e9f;
+  s.xmax = s.ymax = -1e9f;
+  const float c = 0.5f * (side - 1.f);
+  for (int k = 0; k < kPrims; ++k) {
+    const uint64_t r0 = splitmix64(key + 3 * k), r1 = splitmix64(key + 3 * k + 1), r2 = splitmix64(key + 3 * k + 2);
+    const float cx = c + (u01((uint32_t)r0) - 0.5f) * 0.24f * side;
+    const float cy = c + (u01((uint32_t)(r0 >> 32)) - 0.5f) * 0.24f * side;
+    const float a = (0.05f + 0.11f * u01((uint32_t)r1)) * side;
+    const float b = (0.05f + 0.11f * u01((uint32_t)(r1 >> 32))) * side;
+    float sn, cs;
+    sincospif(2.f * u01((uint32_t)r2), &sn, &cs);
+    Prim& q = s.p[k];
+    q.box = (int)((r2 >> 40) & 1);
+    q.ax = cs / a; q.ay = sn / a; q.a0 = -(cx * cs + cy * sn) / a;
+    q.bx = -sn / b; q.by = cs / b; q.b0 = (cx * sn - cy * cs) / b;
+    const float rad = q.box ? sqrtf(a * a + b * b) : fmaxf(a, b);
+    s.xmin = fminf(s.xmin, cx - rad); s.xmax = fmaxf(s.xmax, cx + rad);
+    s.ymin = fminf(s.ymin, cy - rad); s.ymax = fmaxf(s.ymax, cy + rad);
+  }
+}
 
-__global__ void __launch_bounds__(256) generate_pairs_kernel(uint64_t seed, uint64_t step, int B, int side,
-                                                             __nv_bfloat16* planes, long long ld, float* labels) {
+__global__ void __launch_bounds__(256, 3) generate_pairs_kernel(uint64_t seed, uint64_t step, int B, int side,
+                                                                __nv_bfloat16* planes, long long ld, float* labels) {
   const int i = blockIdx.x;
   const int D = side * side;
   __shared__ Shape lock_s, key_s;
+  __shared__ Prim key_rot[kLabelRots][kPrims];   // key primitives composed with the label rotations
   __shared__ float rot_cs, rot_sn;
   __shared__ int counts[kLabelRots];
+  const float c = 0.5f * (side - 1.f);
   if (threadIdx.x == 0) {
     make_shape(lock_s, rng_key(seed, step, 11, (uint64_t)i * 64), (float)side);
-    make_shape(key_s, rng_key(seed, step, 12, (uint64_t)i * 64), (float)side);
-    const float th = 6.2831853f * u01((uint32_t)rng_key(seed, step, 13, i));   // angle ~ U[0, 2 pi)
-    rot_cs = cosf(th);
-    rot_sn = sinf(th);
+    float sn, cs;
+    sincospif(2.f * u01((uint32_t)rng_key(seed, step, 13, i)), &sn, &cs);   // angle ~ U[0, 2 pi)
+    rot_cs = cs;
+    rot_sn = sn;
   }
+  if (threadIdx.x == 32) make_shape(key_s, rng_key(seed, step, 12, (uint64_t)i * 64), (float)side);
   if (threadIdx.x < kLabelRots) counts[threadIdx.x] = 0;
   __syncthreads();
-  const float c = 0.5f * (side - 1.f);
+  if (threadIdx.x < kLabelRots * kPrims) {
+    // test point = R_r (x - c) + c ; fold R_r and the translation into the primitive's affine map
+    const int r = threadIdx.x / kPrims, k = threadIdx.x % kPrims;
+    float rs, rc;
+    sincospif(2.f * r / kLabelRots, &rs, &rc);
+    const Prim q = key_s.p[k];
+    Prim o;
+    o.box = q.box;
+    const float tx = c - rc * c + rs * c, ty = c - rs * c - rc * c;   // kx = rc x - rs y + tx ; ky = rs x + rc y + ty
+    o.ax = q.ax * rc + q.ay * rs; o.ay = -q.ax * rs + q.ay * rc; o.a0 = q.ax * tx + q.ay * ty + q.a0;
+    o.bx = q.bx * rc + q.by * rs; o.by = -q.bx * rs + q.by * rc; o.b0 = q.bx * tx + q.by * ty + q.b0;
+    key_rot[r][k] = o;
+  }
+  __syncthreads();
   int cnt[kLabelRots];
 #pragma unroll
   for (int r = 0; r < kLabelRots; ++r) cnt[r] = 0;
+  const float rcs = rot_cs, rsn = rot_sn;
+  const float smax = side - 1.f;
   const int chunks = (int)(ld / 8);
+  const int chunks_per_row = side / 8;     // host guarantees side % 8 == 0
   for (int ch = threadIdx.x; ch < chunks; ch += blockDim.x) {
-    uint32_t wl[4], wr[4], wk[4];
+    uint32_t wl[4] = {0, 0, 0, 0}, wr[4] = {0, 0, 0, 0}, wk[4] = {0, 0, 0, 0};
+    const int p0 = ch * 8;
+    if (p0 < D) {
+      const int yi = ch / chunks_per_row, x0 = (ch - yi * chunks_per_row) * 8;
+      const float y = (float)yi;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      float vl[2], vr[2], vk[2];
+      for (int e = 0; e < 8; ++e) {
+        const float x = (float)(x0 + e);
+        const bool l = inside(lock_s, x, y);
+        const bool k = inside(key_s, x, y);
+        // inverse map of the rotation, nearest source pixel, zero outside the canvas
+        const float sx = rintf(fmaf(rcs, x - c, fmaf(-rsn, y - c, c))), sy = rintf(fmaf(rsn, x - c, fmaf(rcs, y - c, c)));
+        const bool rr = sx >= 0.f && sy >= 0.f && sx <= smax && sy <= smax && inside(lock_s, sx, sy);
+        const uint32_t one = (e & 1) ? 0x3F800000u : 0x00003F80u;   // bf16 1.0 in the high / low half
+        if (l) wl[e >> 1] |= one;
+        if (rr) wr[e >> 1] |= one;
+        if (k) wk[e >> 1] |= one;
+        if (l) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int p = ch * 8 + 2 * q + h;
-        if (p < D) {
-          const int yi = p / side, xi = p - yi * side;
-          const float x = (float)xi, y = (float)yi;
-          const bool l = inside(lock_s, x, y);
-          const bool k = inside(key_s, x, y);
-          // inverse map of the rotation, nearest source pixel, zero outside the canvas
-          const float sx = rintf(rot_cs * (x - c) - rot_sn * (y - c) + c), sy = rintf(rot_sn * (x - c) + rot_cs * (y - c) + c);
-          const bool rr = sx >= 0.f && sy >= 0.f && sx <= side - 1.f && sy <= side - 1.f && inside(lock_s, sx, sy);
-          vl[h] = l ? 1.f : 0.f; vr[h] = rr ? 1.f : 0.f; vk[h] = k ? 1.f : 0.f;
-          if (l) {
+          for (int r = 0; r < kLabelRots; ++r) {
+            bool in = false;
 #pragma unroll
-            for (int r = 0; r < kLabelRots; ++r) {
-              float rs, rc;
-              sincospif(2.f * r / kLabelRots, &rs, &rc);
-              const float kx = rc * (x - c) - rs * (y - c) + c, ky = rs * (x - c) + rc * (y - c) + c;
-              cnt[r] += inside(key_s, kx, ky) ? 1 : 0;
-            }
+            for (int q = 0; q < kPrims; ++q) in |= prim_hit(key_rot[r][q], x, y);
+            cnt[r] += in ? 1 : 0;
           }
-        } else {
-          vl[h] = vr[h] = vk[h] = (p == D) ? 1.f : 0.f;   // bias column then zero pad
         }
       }
-      wl[q] = ptx::pack_bf16(vl[0], vl[1]);
-      wr[q] = ptx::pack_bf16(vr[0], vr[1]);
-      wk[q] = ptx::pack_bf16(vk[0], vk[1]);
+    } else if (p0 == D) {
+      wl[0] = wr[0] = wk[0] = 0x00003F80u;   // bias column (1.0) then zero pad
     }
-    *reinterpret_cast<uint4*>(planes + (long long)i * ld + ch * 8) = make_uint4(wr[0], wr[1], wr[2], wr[3]);
-    *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + ch * 8) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
-    *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + ch * 8) = make_uint4(wk[0], wk[1], wk[2], wk[3]);
+    *reinterpret_cast<uint4*>(planes + (long long)i * ld + p0) = make_uint4(wr[0], wr[1], wr[2], wr[3]);
+    *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + p0) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
+    *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + p0) = make_uint4(wk[0], wk[1], wk[2], wk[3]);
   }
 #pragma unroll
   for (int r = 0; r < kLabelRots; ++r) {
