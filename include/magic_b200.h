@@ -98,6 +98,9 @@ int magic_load_planar_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* 
  * magic_step is given d_labels = NULL. */
 int magic_generate_batch(magic_handle* h, uint64_t seed, uint64_t step);
 int magic_export_batch(magic_handle* h, float* d_x /* [B,3*D] or NULL */, float* d_labels /* [B] or NULL */);
+/* Q14 fixed-point (cos, sin) of the rotation the generator applied to each lock, [B,2] int32: with them the rotated
+ * plane and the label are reproducible bit for bit from the exported lock/key planes (tests/test_generator.py). */
+int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn);
 
 /* TangoEncoder.partial_fit (8c/vae.py:379-405; 6-tuple variant 11a/vae.py:385-411) on the loaded batch:
  * forward, both backward passes at the pre-step weights, both Adam updates (W <- W - d1 - d2).

@@ -139,6 +139,10 @@ int magic_generate_batch(magic_handle* h, uint64_t seed, uint64_t step) {
   CHECK_HANDLE(h);
   return done(h->eng.generate(seed, step));
 }
+int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn) {
+  CHECK_HANDLE(h);
+  return done(h->eng.export_rotation(d_cs_sn));
+}
 int magic_export_batch(magic_handle* h, float* d_x, float* d_labels) {
   CHECK_HANDLE(h);
   return done(h->eng.export_batch(d_x, d_labels));

@@ -109,7 +109,7 @@ Engine::~Engine() {
   cudaStreamSynchronize(stream);
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, X_.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
-                  statbuf_, g_row_, dist_, labels_int_, losses_dev_, stage_x_, stage_labels_, stage_eps_};
+                  statbuf_, g_row_, dist_, labels_int_, losses_dev_, stage_x_, stage_labels_, stage_eps_, xbits_, rot_cs_sn_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
@@ -237,6 +237,9 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
 
   // ---- activations
   MAGIC_TRY(alloc_act(&X_, 3LL * B, D + 1));
+  xb_ld_ = (int)round_up((D + 31) / 32, 8);
+  MAGIC_TRY(alloc((void**)&xbits_, sizeof(uint32_t) * (size_t)B * xb_ld_));
+  MAGIC_TRY(alloc((void**)&rot_cs_sn_, sizeof(int) * 2 * (size_t)B));
   if (X_.lo) { cudaFree(X_.lo); stats.hbm_bytes -= (int64_t)(sizeof(bf16) * X_.rows * X_.ld); X_.lo = nullptr; }  // pixels are exact in bf16
   H_.resize(E);
   dH_.resize(E);
@@ -363,7 +366,7 @@ std::string Engine::build_plans() {
     memset(&e, 0, sizeof e);
     if (v == 0) {
       e.out = dA_.hi; e.out_lo = dA_.lo; e.ld_out = dA_.ld;
-      e.aux = X_.hi + (long long)B * X_.ld; e.ld_aux = X_.ld;   // lock plane (rows [B, 2B))
+      e.xbits = xbits_; e.xb_ld = xb_ld_;                       // packed lock plane (the reconstruction target)
       e.alpha = inv_bg; e.scalar = statbuf_ + 0; e.precise = prec;
     } else {
       e.out = nullptr; e.ld_out = D;                             // output pointer patched per call
@@ -452,7 +455,10 @@ std::string Engine::build_plans() {
 // ------------------------------------------------------------------ inputs
 std::string Engine::load_interleaved(const float* d_x) {
   if (!d_x) return "load_interleaved: null input";
-  prof_begin("input.deinterleave"); deinterleave_f32(d_x, B, D, X_.hi, X_.ld, stream); prof_end();
+  prof_begin("input.deinterleave");
+  deinterleave_f32(d_x, B, D, X_.hi, X_.ld, stream);
+  pack_lock_bits(X_.hi, X_.ld, B, D, xbits_, xb_ld_, stream);
+  prof_end();
   MAGIC_CUDA(cudaGetLastError());
   have_labels_ = false;
   return "";
@@ -460,19 +466,28 @@ std::string Engine::load_interleaved(const float* d_x) {
 std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uint8_t* k) {
   if (!l || !r || !k) return "load_planar_u8: null input";
   planar_u8(l, r, k, B, D, X_.hi, X_.ld, stream);
+  pack_lock_bits(X_.hi, X_.ld, B, D, xbits_, xb_ld_, stream);
   MAGIC_CUDA(cudaGetLastError());
   have_labels_ = false;
   return "";
 }
 std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
   const int side = (int)llround(sqrt((double)D));
-  if (side * side != D || side % 8 != 0) return "generate: D must be a square canvas with side % 8 == 0";
+  if (side * side != D || side % 8 != 0 || side > 256)
+    return "generate: D must be a square canvas with side % 8 == 0 and side <= 256";
   // fold the rank into the seed so every rank draws different pairs
   prof_begin("input.generate");
-  generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, X_.hi, X_.ld, labels_int_, stream);
+  generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, X_.hi, X_.ld, xbits_, xb_ld_,
+                 labels_int_, rot_cs_sn_, stream);
   prof_end();
   MAGIC_CUDA(cudaGetLastError());
   have_labels_ = true;
+  return "";
+}
+std::string Engine::export_rotation(int32_t* d_cs_sn) {
+  if (!d_cs_sn) return "export_rotation: null output";
+  if (!have_labels_) return "export_rotation: no generated batch is loaded";
+  MAGIC_CUDA(cudaMemcpyAsync(d_cs_sn, rot_cs_sn_, sizeof(int) * 2 * (size_t)B, cudaMemcpyDeviceToDevice, stream));
   return "";
 }
 std::string Engine::export_batch(float* d_x, float* d_labels) {

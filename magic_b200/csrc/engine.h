@@ -48,6 +48,7 @@ class Engine {
   std::string load_planar_u8(const uint8_t* l, const uint8_t* r, const uint8_t* k);
   std::string generate(uint64_t seed, uint64_t step);
   std::string export_batch(float* d_x, float* d_labels);
+  std::string export_rotation(int32_t* d_cs_sn);
   std::string step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply);
   std::string partial_fit_host(const float* h_x, const float* h_labels, const float* h_eps3, float* h_losses5,
                                float* h_distance);
@@ -106,6 +107,8 @@ class Engine {
 
   // activations
   Act X_;                           // [3B, D+1]  rows [rot; lock; key]
+  uint32_t* xbits_ = nullptr; int xb_ld_ = 0;   // [B, xb_ld] packed lock plane: the BCE epilogue's target
+  int* rot_cs_sn_ = nullptr;        // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
   std::vector<Act> H_;              // encoder hidden outputs [3B, enc_i + 1]
   float* heads_ = nullptr; long long ld_heads_ = 0;      // [3B, 2L] fp32
   float* z_ = nullptr;              // [3B, L]

@@ -179,7 +179,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
 
 template <bool A_MN, bool B_MN, int EPI>
 static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
-  gemm_tcgen05_kernel<A_MN, B_MN, EPI><<<pl.grid, kGemmThreads, kGemmSmemBytes, s>>>(pl.args);
+  gemm_tcgen05_kernel<A_MN, B_MN, EPI><<<pl.grid, gemm_threads(EPI), kGemmSmemBytes, s>>>(pl.args);
 }
 
 int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {

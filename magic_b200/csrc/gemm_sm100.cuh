@@ -28,8 +28,11 @@ constexpr int kStages = 4;
 constexpr int kUmmaK = 16;
 constexpr int kMaxGroups = 2;
 constexpr int kMaxSegs = 3;
-constexpr int kGemmThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
-constexpr int kEpiWarps = 8;
+// warp 0 TMA, warp 1 MMA, then the epilogue warps: 8 (two per TMEM lane quarter / scheduler) for the cheap
+// epilogues, 16 for the sigmoid-BCE epilogue whose ~20 instructions per element need four warps per scheduler to
+// hide MUFU and TMEM latencies.
+__host__ __device__ constexpr int epi_warps(int epi) { return epi == 3 /*EPI_BCE*/ ? 16 : 8; }
+__host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 constexpr uint32_t kStageBytesA = kBlockM * kBlockK * 2;   // 16 KiB
 constexpr uint32_t kStageBytesB = kBlockN * kBlockK * 2;   // 32 KiB
 constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
@@ -44,7 +47,9 @@ struct EpiArgs {
   void* out;                  // f32 (STORE_F32, SIGMOID) or bf16 (ACT, DACT, BCE)
   void* out_lo;               // bf16 low part for the split (fp32) mode, or nullptr
   long long ld_out;           // row pitch of out, elements
-  const __nv_bfloat16* aux;   // DACT: forward activations y;  BCE: target plane x
+  const __nv_bfloat16* aux;   // DACT: forward activations y
+  const uint32_t* xbits;      // BCE: packed target plane x (bit p & 31 of word p >> 5 of row r), row pitch xb_ld words
+  int xb_ld;
   const __nv_bfloat16* aux_lo;
   long long ld_aux;
   int aux_split;              // DACT: aux row = r < aux_split ? r : r - aux_shift
@@ -142,7 +147,7 @@ __device__ __forceinline__ void softplus_sigmoid(float b, float& sp, float& sg) 
 
 template <int EPI, int ACT, bool PRECISE>
 __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
-                                              int N, float& loss_acc) {
+                                              int N, float& loss_acc, uint32_t xw) {
   if constexpr (EPI == EPI_STORE_F32) {
     float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
     const float alpha = e.alpha;
@@ -244,39 +249,56 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
     }
   } else if constexpr (EPI == EPI_BCE) {
     // logits a -> loss += softplus(a) - x*a ; dA = sigmoid(a) - x      (x in {0,1}; 8c/vae.py:260-263)
-    const uint4* xp = reinterpret_cast<const uint4*>(e.aux + (long long)row * e.ld_aux + col0);
-    uint32_t x[16];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      uint4 t = xp[q];
-      x[4 * q] = t.x; x[4 * q + 1] = t.y; x[4 * q + 2] = t.z; x[4 * q + 3] = t.w;
-    }
-    uint32_t hi[16], lo[16];
+    // With s = a for x = 0 and s = -a for x = 1:  loss = softplus(s),  dA = sigmoid(s) with the sign of (1 - 2x).
+    // `xw` holds this row's 32 target bits for the chunk (bit j <-> column col0 + j).
+        uint32_t hi[16], lo[16];
     float acc = 0.f;
+    const bool full = col0 + 32 <= N;
 #pragma unroll
     for (int j = 0; j < 32; j += 2) {
-      float a0 = __uint_as_float(r[j]), a1 = __uint_as_float(r[j + 1]);
-      float x0 = ptx::bf16_lo(x[j >> 1]), x1 = ptx::bf16_hi(x[j >> 1]);
-      float sp0, sg0, sp1, sg1;
-      softplus_sigmoid<PRECISE>(a0, sp0, sg0);
-      softplus_sigmoid<PRECISE>(a1, sp1, sg1);
-      bool in0 = col0 + j < N, in1 = col0 + j + 1 < N;
-      float d0 = in0 ? sg0 - x0 : 0.f, d1 = in1 ? sg1 - x1 : 0.f;
-      if (in0) acc += sp0 - x0 * a0;
-      if (in1) acc += sp1 - x1 * a1;
-      uint32_t h = ptx::pack_bf16(d0, d1);
-      hi[j >> 1] = h;
-      lo[j >> 1] = ptx::pack_bf16(d0 - ptx::bf16_lo(h), d1 - ptx::bf16_hi(h));
+      float d[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const uint32_t sign = (xw << (31 - (j + q))) & 0x80000000u;
+        const float sv = __uint_as_float(r[j + q] ^ sign);
+        float sp, sg;
+        if constexpr (PRECISE) {
+          softplus_sigmoid<true>(sv, sp, sg);
+        } else {
+          float t;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fabsf(sv) * -1.4426950408889634f));
+          float rr;
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rr) : "f"(1.f + t));
+          // sigmoid(s) = 0.5 + sgn(s) * (0.5 - t/(1+t))
+          const float h = fmaf(-t, rr, 0.5f);
+          sg = 0.5f + __uint_as_float(__float_as_uint(h) ^ (__float_as_uint(sv) & 0x80000000u));
+          // log1p(t) = t * P(t), degree-5 fit of log1p(t)/t on (0,1], max relative error 8.5e-6
+          float p = fmaf(t, -0.023868885f, 0.10122161f);
+          p = fmaf(t, p, -0.21004808f);
+          p = fmaf(t, p, 0.32520646f);
+          p = fmaf(t, p, -0.49936134f);
+          p = fmaf(t, p, 0.9999916f);
+          sp = fmaf(t, p, fmaxf(sv, 0.f));
+        }
+        const bool in = full || (col0 + j + q < N);
+        d[q] = in ? __uint_as_float(__float_as_uint(sg) ^ sign) : 0.f;
+        acc += in ? sp : 0.f;
+      }
+      const uint32_t h2 = ptx::pack_bf16(d[0], d[1]);
+      hi[j >> 1] = h2;
+      if constexpr (PRECISE) lo[j >> 1] = ptx::pack_bf16(d[0] - ptx::bf16_lo(h2), d[1] - ptx::bf16_hi(h2));
     }
     loss_acc += acc;
     uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
 #pragma unroll
     for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
-    if (e.out_lo) {
-      uint4* ol =
-          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
+    if constexpr (PRECISE) {
+      if (e.out_lo) {
+        uint4* ol =
+            reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+        for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+      }
     }
   }
 }
@@ -284,27 +306,27 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
 // Run-time (act, precise) -> compile-time variant, decided once per 32-column chunk (warp-uniform).
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
-                                               int N, float& loss_acc) {
+                                               int N, float& loss_acc, uint32_t xw = 0u) {
   if (row >= M) return;
   if constexpr (EPI == EPI_ACT || EPI == EPI_DACT) {
     if (e.act == ACT_TANH) {
-      if (e.precise) epilogue_impl<EPI, ACT_TANH, true>(e, r, row, col0, M, N, loss_acc);
-      else epilogue_impl<EPI, ACT_TANH, false>(e, r, row, col0, M, N, loss_acc);
+      if (e.precise) epilogue_impl<EPI, ACT_TANH, true>(e, r, row, col0, M, N, loss_acc, xw);
+      else epilogue_impl<EPI, ACT_TANH, false>(e, r, row, col0, M, N, loss_acc, xw);
     } else {
-      if (e.precise) epilogue_impl<EPI, ACT_ELU, true>(e, r, row, col0, M, N, loss_acc);
-      else epilogue_impl<EPI, ACT_ELU, false>(e, r, row, col0, M, N, loss_acc);
+      if (e.precise) epilogue_impl<EPI, ACT_ELU, true>(e, r, row, col0, M, N, loss_acc, xw);
+      else epilogue_impl<EPI, ACT_ELU, false>(e, r, row, col0, M, N, loss_acc, xw);
     }
   } else if constexpr (EPI == EPI_BCE) {
-    if (e.precise) epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc);
-    else epilogue_impl<EPI, ACT_NONE, false>(e, r, row, col0, M, N, loss_acc);
+    if (e.precise) epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc, xw);
+    else epilogue_impl<EPI, ACT_NONE, false>(e, r, row, col0, M, N, loss_acc, xw);
   } else {
-    epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc);
+    epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc, xw);
   }
 }
 
 // ---------------------------------------------------------------------------- the kernel
 template <bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(kGemmThreads, 1) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
+__global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
   extern __shared__ uint8_t smem_raw[];
   // 128-byte swizzle atoms need 1024-byte aligned stage bases
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -333,7 +355,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tcgen05_kernel(const __g
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
-      ptx::mbar_init(&tempty_bar[i], kEpiWarps * 32);
+      ptx::mbar_init(&tempty_bar[i], epi_warps(EPI) * 32);
     }
     ptx::fence_barrier_init();
   } else if (warp == 1) {
@@ -416,29 +438,45 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tcgen05_kernel(const __g
     // TMEM lane quarter = warp % 4 (hardware rule); the two warps of a quarter split the 32-column chunks
     // even/odd, so every scheduler has two epilogue warps to overlap latencies with.
     const int q = warp & 3;
-    const int half = (warp - 2) >> 2;
+    constexpr int kGroups = epi_warps(EPI) / 4;          // warps per lane quarter; chunk c belongs to group c % kGroups
+    constexpr int kMaxOwn = (kBlockN / 32 + kGroups - 1) / kGroups;
+    const int grp = (warp - 2) >> 2;
     uint32_t iter = 0;
     float loss_acc = 0.f;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
       const WorkItem it = decode_work(args, w);
       const EpiArgs& e = args.epi[it.g];
       const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
-      ptx::mbar_wait(&tfull_bar[acc], acc_phase);
-      ptx::tc_fence_after();
       const int row = it.m0 + q * 32 + lane;
       const int ncols = min(kBlockN, args.N - it.n0);
       const int nchunks = (ncols + 31) >> 5;
+      // BCE: this row's packed target bits for the chunks this warp owns, fetched before the accumulator wait
+      uint32_t xw[kMaxOwn];
+      if constexpr (EPI == EPI_BCE) {
+#pragma unroll
+        for (int k = 0; k < kMaxOwn; ++k) {
+          const int c = grp + k * kGroups;
+          xw[k] = (row < args.M && c < nchunks) ? __ldg(e.xbits + (long long)row * e.xb_ld + ((it.n0 >> 5) + c)) : 0u;
+        }
+      }
+      ptx::mbar_wait(&tfull_bar[acc], acc_phase);
+      ptx::tc_fence_after();
       bool arrived = false;
-      for (int c = half; c < nchunks; c += 2) {
+#pragma unroll
+      for (int k = 0; k < kMaxOwn; ++k) {
+        const int c = grp + k * kGroups;
+        if (c >= nchunks) break;
         uint32_t r[32];
         ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kBlockN + c * 32, r);
         ptx::tmem_ld_wait();
-        if (c + 2 >= nchunks) {   // this warp's last TMEM read of the accumulator: hand it back to the MMA warp
+        if (c + kGroups >= nchunks) {   // this warp's last TMEM read of the accumulator: hand it back to the MMA warp
           ptx::tc_fence_before();
           ptx::mbar_arrive(&tempty_bar[acc]);
           arrived = true;
         }
-        epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc);
+        uint32_t xwk = 0u;
+        if constexpr (EPI == EPI_BCE) xwk = xw[k];
+        epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
       }
       if (!arrived) {
         ptx::tc_fence_before();

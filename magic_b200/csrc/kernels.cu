@@ -358,135 +358,204 @@ void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B,
 }
 
 // ------------------------------------------------------------------ synthetic pair generator
-// A shape is the union of 3 analytic primitives (ellipse or rotated box) near the canvas centre; mean filled
-// area ~8.5 % of the canvas like the reference's data (overlap_micro.zip: 710..7213 px of 40000).
-// rot  = nearest-neighbour rotation of lock about ((W-1)/2,(H-1)/2), zero fill  (tf.contrib.image.rotate,
-//        8c/utils.py:337-338; third-party arithmetic, parity unpinned)
-// label = max over 8 rotations of the key about the centre of |lock AND rot(key)|  (README.md:19-27: the
-//        "maximum overlap area"; the reference's dataset generator is not in the repository).
+// One CTA per pair, four phases, all on 1-bit-per-pixel bitmaps in shared memory (pixel p = y*side + x is bit
+// p & 31 of word p >> 5):
+//   1. scanline rasterisation of lock and key: a shape is the union of 3 convex primitives (ellipse or rotated
+//      box) near the canvas centre, so every (primitive, row) is one x-interval found in closed form; mean
+//      filled area ~8.5 % of the canvas like the reference's data (overlap_micro.zip: 710..7213 px of 40000);
+//   2. rot = nearest-neighbour rotation of lock about ((W-1)/2,(H-1)/2) by a random angle, zero fill (the
+//      arithmetic of tf.contrib.image.rotate, 8c/utils.py:337-338; third-party, parity unpinned).  The inverse
+//      map is evaluated in Q14 fixed point on doubled coordinates so that the CPU check in tests/ reproduces it
+//      bit for bit:  sx = (CS*(2x-W+1) - SN*(2y-W+1) + (W<<14)) >> 15,  sy = (SN*(2x-W+1) + CS*(2y-W+1) + (W<<14)) >> 15;
+//   3. label = max over the 8 rotations r*45 deg of the key (same inverse map, fixed Q14 constants) of
+//      popcount(lock AND rot_r(key))  (README.md:19-27: the "maximum overlap area"; the reference's dataset
+//      generator is not in the repository);
+//   4. expansion of the three bitmaps to the bf16 operand planes (rows [rot; lock; key], 1.0 in the bias column
+//      D, zero pad) with 16-byte coalesced stores, plus the packed lock bitmap the BCE epilogue reads.
 constexpr int kPrims = 3;
 constexpr int kLabelRots = 8;
-// A primitive as an affine map to its unit frame: u = ax*x + ay*y + a0 ; v = bx*x + by*y + b0 ;
-// ellipse: u^2 + v^2 <= 1 ; box: max(|u|,|v|) <= 1.
-struct Prim { float ax, ay, a0, bx, by, b0; int box; };
-struct Shape {
-  Prim p[kPrims];
-  float xmin, xmax, ymin, ymax;   // pixel bounding box of the union
-};
-__device__ __forceinline__ bool prim_hit(const Prim& q, float x, float y) {
-  const float u = fmaf(q.ax, x, fmaf(q.ay, y, q.a0)), v = fmaf(q.bx, x, fmaf(q.by, y, q.b0));
-  return q.box ? fmaxf(fabsf(u), fabsf(v)) <= 1.f : fmaf(u, u, v * v) <= 1.f;
-}
-__device__ __forceinline__ bool inside(const Shape& s, float x, float y) {
-  if (x < s.xmin || x > s.xmax || y < s.ymin || y > s.ymax) return false;
-  bool in = false;
-#pragma unroll
-  for (int k = 0; k < kPrims; ++k) in |= prim_hit(s.p[k], x, y);
-  return in;
-}
-__device__ void make_shape(Shape& s, uint64_t key, float side) {
-  s.xmin = s.ymin = 1e9f;
-  s.xmax = s.ymax = -1e9f;
+constexpr int kGenThreads = 256;
+constexpr int kMaxBitWords = 2048;                       // canvas up to 256 x 256
+// Q14 (cos, sin) of r * 45 degrees, r = 0..3; rotation r + 4 is DEFINED as the point reflection of rotation r's
+// source pixel through the canvas centre (sx, sy) -> (W-1-sx, W-1-sy), which shares the coordinate arithmetic.
+__host__ __device__ constexpr int rot_cs(int r) { return r == 0 ? 16384 : r == 1 ? 11585 : r == 2 ? 0 : -11585; }
+__host__ __device__ constexpr int rot_sn(int r) { return r == 0 ? 0 : r == 1 ? 11585 : r == 2 ? 16384 : 11585; }
+
+struct Prim { float cx, cy, a, b, cs, sn; int box; };
+
+__device__ void make_prims(Prim* out, uint64_t key, float side) {
   const float c = 0.5f * (side - 1.f);
   for (int k = 0; k < kPrims; ++k) {
     const uint64_t r0 = splitmix64(key + 3 * k), r1 = splitmix64(key + 3 * k + 1), r2 = splitmix64(key + 3 * k + 2);
-    const float cx = c + (u01((uint32_t)r0) - 0.5f) * 0.24f * side;
-    const float cy = c + (u01((uint32_t)(r0 >> 32)) - 0.5f) * 0.24f * side;
-    const float a = (0.05f + 0.11f * u01((uint32_t)r1)) * side;
-    const float b = (0.05f + 0.11f * u01((uint32_t)(r1 >> 32))) * side;
-    float sn, cs;
-    sincospif(2.f * u01((uint32_t)r2), &sn, &cs);
-    Prim& q = s.p[k];
+    Prim& q = out[k];
+    q.cx = c + (u01((uint32_t)r0) - 0.5f) * 0.24f * side;
+    q.cy = c + (u01((uint32_t)(r0 >> 32)) - 0.5f) * 0.24f * side;
+    q.a = (0.05f + 0.11f * u01((uint32_t)r1)) * side;
+    q.b = (0.05f + 0.11f * u01((uint32_t)(r1 >> 32))) * side;
+    sincospif(2.f * u01((uint32_t)r2), &q.sn, &q.cs);
     q.box = (int)((r2 >> 40) & 1);
-    q.ax = cs / a; q.ay = sn / a; q.a0 = -(cx * cs + cy * sn) / a;
-    q.bx = -sn / b; q.by = cs / b; q.b0 = (cx * sn - cy * cs) / b;
-    const float rad = q.box ? sqrtf(a * a + b * b) : fmaxf(a, b);
-    s.xmin = fminf(s.xmin, cx - rad); s.xmax = fmaxf(s.xmax, cx + rad);
-    s.ymin = fminf(s.ymin, cy - rad); s.ymax = fmaxf(s.ymax, cy + rad);
   }
 }
 
-__global__ void __launch_bounds__(256, 3) generate_pairs_kernel(uint64_t seed, uint64_t step, int B, int side,
-                                                                __nv_bfloat16* planes, long long ld, float* labels) {
+// x-interval [lo, hi] (relative to cx) of primitive q on the row at vertical offset dy; false if empty
+__device__ __forceinline__ bool prim_row_interval(const Prim& q, float dy, float& lo, float& hi) {
+  if (!q.box) {
+    const float ia = 1.f / (q.a * q.a), ib = 1.f / (q.b * q.b);
+    const float A = q.cs * q.cs * ia + q.sn * q.sn * ib;
+    const float Bh = dy * q.cs * q.sn * (ia - ib);
+    const float C = dy * dy * (q.sn * q.sn * ia + q.cs * q.cs * ib) - 1.f;
+    const float disc = Bh * Bh - A * C;
+    if (disc < 0.f) return false;
+    const float sq = sqrtf(disc), inv = 1.f / A;
+    lo = (-Bh - sq) * inv;
+    hi = (-Bh + sq) * inv;
+    return true;
+  }
+  lo = -1e9f; hi = 1e9f;
+  // |cs dx + sn dy| <= a   and   |-sn dx + cs dy| <= b
+  const float al[2] = {q.cs, -q.sn}, be[2] = {q.sn * dy, q.cs * dy}, ga[2] = {q.a, q.b};
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    if (fabsf(al[c]) < 1e-6f) {
+      if (fabsf(be[c]) > ga[c]) return false;
+    } else {
+      const float i = 1.f / al[c];
+      const float x0 = (-ga[c] - be[c]) * i, x1 = (ga[c] - be[c]) * i;
+      lo = fmaxf(lo, fminf(x0, x1));
+      hi = fminf(hi, fmaxf(x0, x1));
+    }
+  }
+  return lo <= hi;
+}
+
+// OR the bit range [p0, p1] (inclusive, linear pixel indices) into a shared-memory bitmap
+__device__ __forceinline__ void or_bit_range(uint32_t* bm, int p0, int p1) {
+  const int w0 = p0 >> 5, w1 = p1 >> 5;
+  const uint32_t m0 = 0xFFFFFFFFu << (p0 & 31), m1 = 0xFFFFFFFFu >> (31 - (p1 & 31));
+  if (w0 == w1) { atomicOr(&bm[w0], m0 & m1); return; }
+  atomicOr(&bm[w0], m0);
+  for (int w = w0 + 1; w < w1; ++w) atomicOr(&bm[w], 0xFFFFFFFFu);
+  atomicOr(&bm[w1], m1);
+}
+
+// linear index of the source pixel of (x, y) under the Q14 inverse rotation (cs, sn) about the canvas centre;
+// -1 outside the canvas
+__device__ __forceinline__ int rotated_index(int x, int y, int side, int cs, int sn) {
+  const int X2 = 2 * x - side + 1, Y2 = 2 * y - side + 1;
+  const int sx = (cs * X2 - sn * Y2 + (side << 14)) >> 15;
+  const int sy = (sn * X2 + cs * Y2 + (side << 14)) >> 15;
+  if ((unsigned)sx >= (unsigned)side || (unsigned)sy >= (unsigned)side) return -1;
+  return sy * side + sx;
+}
+__device__ __forceinline__ uint32_t bit_at(const uint32_t* bm, int sp) {
+  return sp < 0 ? 0u : (bm[sp >> 5] >> (sp & 31)) & 1u;
+}
+
+// nibble -> four bf16 values (two packed words): bit k of the nibble -> 1.0 (0x3F80) in element k
+__device__ __forceinline__ uint2 expand_nibble(uint32_t n) {
+  uint2 r;
+  r.x = ((n & 1u) ? 0x00003F80u : 0u) | ((n & 2u) ? 0x3F800000u : 0u);
+  r.y = ((n & 4u) ? 0x00003F80u : 0u) | ((n & 8u) ? 0x3F800000u : 0u);
+  return r;
+}
+__device__ __forceinline__ uint4 expand_byte(uint32_t b) {
+  const uint2 lo = expand_nibble(b & 15u), hi = expand_nibble((b >> 4) & 15u);
+  return make_uint4(lo.x, lo.y, hi.x, hi.y);
+}
+
+__global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t seed, uint64_t step, int B, int side,
+                                                                     uint32_t inv_side /* ceil(2^32 / side) */,
+                                                                     __nv_bfloat16* planes, long long ld,
+                                                                     uint32_t* xbits, int xb_ld, float* labels,
+                                                                     int* rot_cs_sn) {
   const int i = blockIdx.x;
   const int D = side * side;
-  __shared__ Shape lock_s, key_s;
-  __shared__ Prim key_rot[kLabelRots][kPrims];   // key primitives composed with the label rotations
-  __shared__ float rot_cs, rot_sn;
+  const int nwords = (D + 31) >> 5;
+  __shared__ uint32_t bm[3][kMaxBitWords];     // 0 lock, 1 key, 2 rot
+  __shared__ uint4 lut[256];                   // byte of 8 pixels -> 8 bf16
+  __shared__ Prim prims[2][kPrims];
+  __shared__ int rot_q14[2];
+  __shared__ int rot_radius;                   // every lock pixel lies within this distance of the centre
   __shared__ int counts[kLabelRots];
-  const float c = 0.5f * (side - 1.f);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int w = threadIdx.x; w < nwords + 8; w += kGenThreads) bm[0][w] = bm[1][w] = bm[2][w] = 0u;
+  lut[threadIdx.x] = expand_byte(threadIdx.x);           // kGenThreads == 256
   if (threadIdx.x == 0) {
-    make_shape(lock_s, rng_key(seed, step, 11, (uint64_t)i * 64), (float)side);
+    make_prims(prims[0], rng_key(seed, step, 11, (uint64_t)i * 64), (float)side);
     float sn, cs;
     sincospif(2.f * u01((uint32_t)rng_key(seed, step, 13, i)), &sn, &cs);   // angle ~ U[0, 2 pi)
-    rot_cs = cs;
-    rot_sn = sn;
+    rot_q14[0] = __float2int_rn(cs * 16384.f);
+    rot_q14[1] = __float2int_rn(sn * 16384.f);
+    if (rot_cs_sn) { rot_cs_sn[2 * i] = rot_q14[0]; rot_cs_sn[2 * i + 1] = rot_q14[1]; }
+    const float c = 0.5f * (side - 1.f);
+    float rad = 0.f;
+    for (int k = 0; k < kPrims; ++k) {
+      const Prim& q = prims[0][k];
+      const float ext = q.box ? sqrtf(q.a * q.a + q.b * q.b) : fmaxf(q.a, q.b);
+      rad = fmaxf(rad, sqrtf((q.cx - c) * (q.cx - c) + (q.cy - c) * (q.cy - c)) + ext);
+    }
+    rot_radius = (int)ceilf(rad) + 2;
   }
-  if (threadIdx.x == 32) make_shape(key_s, rng_key(seed, step, 12, (uint64_t)i * 64), (float)side);
+  if (threadIdx.x == 32) make_prims(prims[1], rng_key(seed, step, 12, (uint64_t)i * 64), (float)side);
   if (threadIdx.x < kLabelRots) counts[threadIdx.x] = 0;
   __syncthreads();
-  if (threadIdx.x < kLabelRots * kPrims) {
-    // test point = R_r (x - c) + c ; fold R_r and the translation into the primitive's affine map
-    const int r = threadIdx.x / kPrims, k = threadIdx.x % kPrims;
-    float rs, rc;
-    sincospif(2.f * r / kLabelRots, &rs, &rc);
-    const Prim q = key_s.p[k];
-    Prim o;
-    o.box = q.box;
-    const float tx = c - rc * c + rs * c, ty = c - rs * c - rc * c;   // kx = rc x - rs y + tx ; ky = rs x + rc y + ty
-    o.ax = q.ax * rc + q.ay * rs; o.ay = -q.ax * rs + q.ay * rc; o.a0 = q.ax * tx + q.ay * ty + q.a0;
-    o.bx = q.bx * rc + q.by * rs; o.by = -q.bx * rs + q.by * rc; o.b0 = q.bx * tx + q.by * ty + q.b0;
-    key_rot[r][k] = o;
+
+  // ---- 1. scanline rasterisation: one work item per (shape, row)
+  for (int it = threadIdx.x; it < 2 * side; it += kGenThreads) {
+    const int s = it >= side ? 1 : 0, y = it - s * side;
+#pragma unroll
+    for (int k = 0; k < kPrims; ++k) {
+      const Prim& q = prims[s][k];
+      float lo, hi;
+      if (!prim_row_interval(q, (float)y - q.cy, lo, hi)) continue;
+      const int x0 = max(0, (int)ceilf(q.cx + lo)), x1 = min(side - 1, (int)floorf(q.cx + hi));
+      if (x0 <= x1) or_bit_range(bm[s], y * side + x0, y * side + x1);
+    }
   }
   __syncthreads();
+
+  // ---- 2. rotated lock: one warp per 32-pixel word, ballot assembles the word.  Only rows inside the disc that
+  //         contains the lock can receive pixels.
+  {
+    const int cs = rot_q14[0], sn = rot_q14[1];
+    const int ylo = max(0, (side - 1) / 2 - rot_radius), yhi = min(side - 1, side / 2 + rot_radius);
+    const int xlo = ylo, xhi = yhi;
+    const int w_begin = (ylo * side) >> 5, w_end = min(nwords, ((yhi * side + side - 1) >> 5) + 1);
+    for (int w = w_begin + warp; w < w_end; w += kGenThreads / 32) {
+      const int p0 = w * 32;
+      const int y0 = (int)__umulhi((uint32_t)p0, inv_side), x0 = p0 - y0 * side;
+      if (x0 + 31 < side && (x0 > xhi || x0 + 31 < xlo)) continue;     // whole word on one row, outside the disc's box
+      int x = x0 + lane, y = y0;
+      if (x >= side) { x -= side; ++y; }
+      const uint32_t bit = (p0 + lane < D) ? bit_at(bm[0], rotated_index(x, y, side, cs, sn)) : 0u;
+      const uint32_t word = __ballot_sync(0xffffffffu, bit != 0u);
+      if (lane == 0) bm[2][w] = word;
+    }
+  }
+  // ---- 3. label: only words where the lock has pixels; every lane sees the same ballot, so the counts stay
+  //         in registers without a reduction
   int cnt[kLabelRots];
 #pragma unroll
   for (int r = 0; r < kLabelRots; ++r) cnt[r] = 0;
-  const float rcs = rot_cs, rsn = rot_sn;
-  const float smax = side - 1.f;
-  const int chunks = (int)(ld / 8);
-  const int chunks_per_row = side / 8;     // host guarantees side % 8 == 0
-  for (int ch = threadIdx.x; ch < chunks; ch += blockDim.x) {
-    uint32_t wl[4] = {0, 0, 0, 0}, wr[4] = {0, 0, 0, 0}, wk[4] = {0, 0, 0, 0};
-    const int p0 = ch * 8;
-    if (p0 < D) {
-      const int yi = ch / chunks_per_row, x0 = (ch - yi * chunks_per_row) * 8;
-      const float y = (float)yi;
+  for (int w = warp; w < nwords; w += kGenThreads / 32) {
+    const uint32_t lw = bm[0][w];
+    if (lw == 0u) continue;
+    const int p0 = w * 32;
+    const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
+    int x = p0 - y0 * side + lane, y = y0;
+    if (x >= side) { x -= side; ++y; }
+    const bool valid = p0 + lane < D;
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float x = (float)(x0 + e);
-        const bool l = inside(lock_s, x, y);
-        const bool k = inside(key_s, x, y);
-        // inverse map of the rotation, nearest source pixel, zero outside the canvas
-        const float sx = rintf(fmaf(rcs, x - c, fmaf(-rsn, y - c, c))), sy = rintf(fmaf(rsn, x - c, fmaf(rcs, y - c, c)));
-        const bool rr = sx >= 0.f && sy >= 0.f && sx <= smax && sy <= smax && inside(lock_s, sx, sy);
-        const uint32_t one = (e & 1) ? 0x3F800000u : 0x00003F80u;   // bf16 1.0 in the high / low half
-        if (l) wl[e >> 1] |= one;
-        if (rr) wr[e >> 1] |= one;
-        if (k) wk[e >> 1] |= one;
-        if (l) {
-#pragma unroll
-          for (int r = 0; r < kLabelRots; ++r) {
-            bool in = false;
-#pragma unroll
-            for (int q = 0; q < kPrims; ++q) in |= prim_hit(key_rot[r][q], x, y);
-            cnt[r] += in ? 1 : 0;
-          }
-        }
-      }
-    } else if (p0 == D) {
-      wl[0] = wr[0] = wk[0] = 0x00003F80u;   // bias column (1.0) then zero pad
+    for (int r = 0; r < kLabelRots / 2; ++r) {
+      const int sp = valid ? rotated_index(x, y, side, rot_cs(r), rot_sn(r)) : -1;
+      cnt[r] += __popc(__ballot_sync(0xffffffffu, bit_at(bm[1], sp) != 0u) & lw);
+      cnt[r + 4] += __popc(__ballot_sync(0xffffffffu, bit_at(bm[1], sp < 0 ? -1 : D - 1 - sp) != 0u) & lw);
     }
-    *reinterpret_cast<uint4*>(planes + (long long)i * ld + p0) = make_uint4(wr[0], wr[1], wr[2], wr[3]);
-    *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + p0) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
-    *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + p0) = make_uint4(wk[0], wk[1], wk[2], wk[3]);
   }
+  if (lane == 0) {
 #pragma unroll
-  for (int r = 0; r < kLabelRots; ++r) {
-    int v = cnt[r];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&counts[r], v);
+    for (int r = 0; r < kLabelRots; ++r)
+      if (cnt[r]) atomicAdd(&counts[r], cnt[r]);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -494,11 +563,52 @@ __global__ void __launch_bounds__(256, 3) generate_pairs_kernel(uint64_t seed, u
     for (int r = 0; r < kLabelRots; ++r) best = max(best, counts[r]);
     labels[i] = (float)best;
   }
+
+  // ---- 4. expand to the bf16 operand planes: 8 pixels (one bitmap byte) -> one 16-byte store per plane
+  const int chunks = (int)(ld / 8);
+  const uint8_t* bl = reinterpret_cast<const uint8_t*>(bm[0]);
+  const uint8_t* bk = reinterpret_cast<const uint8_t*>(bm[1]);
+  const uint8_t* br = reinterpret_cast<const uint8_t*>(bm[2]);
+  uint4* prot = reinterpret_cast<uint4*>(planes + (long long)i * ld);
+  uint4* plock = reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld);
+  uint4* pkey = reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld);
+  const int data_chunks = D / 8;               // D % 8 == 0 (host checks)
+  for (int ch = threadIdx.x; ch < chunks; ch += kGenThreads) {
+    uint4 vl, vr, vk;
+    if (ch < data_chunks) {
+      vl = lut[bl[ch]]; vr = lut[br[ch]]; vk = lut[bk[ch]];
+    } else {
+      vl = vr = vk = make_uint4(ch == data_chunks ? 0x00003F80u : 0u, 0u, 0u, 0u);   // bias column (1.0), then zero pad
+    }
+    prot[ch] = vr; plock[ch] = vl; pkey[ch] = vk;
+  }
+  if (xbits)
+    for (int w = threadIdx.x; w < xb_ld; w += kGenThreads) xbits[(long long)i * xb_ld + w] = w < nwords ? bm[0][w] : 0u;
 }
 
-void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, float* labels,
-                    cudaStream_t s) {
-  generate_pairs_kernel<<<B, 256, 0, s>>>(seed, step, B, side, planes, ld, labels);
+void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, uint32_t* xbits,
+                    int xb_ld, float* labels, int* rot_cs_sn, cudaStream_t s) {
+  const uint32_t inv_side = (uint32_t)((0x100000000ull + (uint64_t)side - 1) / (uint64_t)side);
+  generate_pairs_kernel<<<B, kGenThreads, 0, s>>>(seed, step, B, side, inv_side, planes, ld, xbits, xb_ld, labels,
+                                                  rot_cs_sn);
+}
+
+// lock plane (bf16 {0,1}, rows [B, 2B) of planes) -> packed bitmap xbits[B, xb_ld] for the loaders that do not
+// come through the generator.  One warp per 32-pixel word.
+__global__ void __launch_bounds__(256) pack_lock_bits_kernel(const __nv_bfloat16* __restrict__ planes, long long ld, int B,
+                                                             int D, uint32_t* xbits, int xb_ld) {
+  const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (gw >= (long long)B * xb_ld) return;
+  const int i = (int)(gw / xb_ld), w = (int)(gw % xb_ld);
+  const int p = w * 32 + lane;
+  const bool bit = p < D && __bfloat162float(planes[(long long)(B + i) * ld + p]) != 0.f;
+  const uint32_t word = __ballot_sync(0xffffffffu, bit);
+  if (lane == 0) xbits[gw] = word;
+}
+void pack_lock_bits(const __nv_bfloat16* planes, long long ld, int B, int D, uint32_t* xbits, int xb_ld, cudaStream_t s) {
+  const long long threads = (long long)B * xb_ld * 32;
+  pack_lock_bits_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(planes, ld, B, D, xbits, xb_ld);
 }
 
 

@@ -152,6 +152,18 @@ static void test_fused(int epi, int M, int Nv, int K, int split, int precise, in
   CK(cudaMalloc(&dout, 2 * M * ldo));
   CK(cudaMalloc(&dlo, 2 * M * ldo));
   CK(cudaMemset(dout, 0xFF, 2 * M * ldo));
+  CK(cudaMemset(dlo, 0, 2 * M * ldo));
+  // BCE target as packed bits (bit n & 31 of word n >> 5 of row m)
+  const int xb_ld = (int)((ldo + 31) / 32 + 7) / 8 * 8;
+  uint32_t* dbits = nullptr;
+  if (epi == EPI_BCE) {
+    std::vector<uint32_t> hb((size_t)M * xb_ld, 0u);
+    for (int m = 0; m < M; ++m)
+      for (int n = 0; n < Nv; ++n)
+        if (aux.at(m, n) != 0.f) hb[(size_t)m * xb_ld + (n >> 5)] |= 1u << (n & 31);
+    CK(cudaMalloc(&dbits, sizeof(uint32_t) * hb.size()));
+    CK(cudaMemcpy(dbits, hb.data(), sizeof(uint32_t) * hb.size(), cudaMemcpyHostToDevice));
+  }
   float* scalar;
   CK(cudaMalloc(&scalar, 4));
   CK(cudaMemset(scalar, 0, 4));
@@ -163,7 +175,9 @@ static void test_fused(int epi, int M, int Nv, int K, int split, int precise, in
   p.a[0][0] = a.mat(); p.b[0][0] = b.mat();
   p.ws = ws; p.ws_ld = ldo;
   EpiArgs e = {};
-  e.out = dout; e.out_lo = dlo; e.ld_out = ldo; e.alpha = epi == EPI_BCE ? 0.25f : 1.f; e.n_valid = Nv;
+  e.out = dout; e.out_lo = (epi == EPI_BCE && !precise) ? nullptr : dlo; e.ld_out = ldo;
+  e.alpha = epi == EPI_BCE ? 0.25f : 1.f; e.n_valid = Nv;
+  e.xbits = dbits; e.xb_ld = xb_ld;
   e.act = ACT_TANH; e.precise = precise; e.aux = aux.d; e.ld_aux = ldo; e.aux_split = M / 2; e.aux_shift = epi == EPI_DACT ? M / 4 : 0;
   e.scalar = scalar;
   if (epi != EPI_DACT) { e.aux_split = 1 << 30; }
@@ -210,6 +224,7 @@ static void test_fused(int epi, int M, int Nv, int K, int split, int precise, in
     report("   bce loss sum (relative)", rel, precise ? 1e-5 : 1e-4);
   }
   cudaFree(a.d); cudaFree(b.d); cudaFree(aux.d); cudaFree(dout); cudaFree(dlo); cudaFree(scalar); cudaFree(ws);
+  if (dbits) cudaFree(dbits);
 }
 
 static void bench(int kind, int M, int N, int K, int split, int sms, const char* label) {

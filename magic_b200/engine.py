@@ -233,6 +233,12 @@ class Engine:
         check(self.lib.magic_export_batch(self._h, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr())))
         return x, y
 
+    def export_rotation(self) -> torch.Tensor:
+        """[B,2] int32: Q14 (cos, sin) of the rotation the generator applied to each lock."""
+        r = torch.empty(self.B, 2, dtype=torch.int32, device=self.device)
+        check(self.lib.magic_export_rotation(self._h, C.c_void_p(r.data_ptr())))
+        return r
+
     # ------------------------------------------------------------------ step / inference
     def step(self, labels=None, eps3=None, apply: bool = True, want_distance: bool = False):
         """One optimiser step on the loaded batch; returns (losses[5] device tensor, distance or None).

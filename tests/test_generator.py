@@ -1,0 +1,100 @@
+"""On-device shape-pair generator (replaces 8c/overlap_input.py): a numpy restatement of its integer
+rotation and label arithmetic must reproduce the rotated plane and the label bit for bit from the exported lock/key
+planes; the shape statistics must look like the reference's data (tests/golden/overlap_micro_16.npz)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROT_CS = [16384, 11585, 0, -11585]      # Q14 cos/sin of r * 45 degrees, r = 0..3 (kernels.cu: rot_cs / rot_sn);
+ROT_SN = [0, 11585, 16384, 11585]       # rotation r + 4 = rotation r with the source point-reflected through the centre
+
+
+def nn_rotate(img: np.ndarray, cs: int, sn: int, reflect: bool = False) -> np.ndarray:
+    """Nearest-neighbour inverse-map rotation about the canvas centre in Q14 fixed point on doubled coordinates
+    (the arithmetic of tf.contrib.image.rotate, 8c/utils.py:337-338, restated with integers), zero fill."""
+    side = img.shape[0]
+    y, x = np.meshgrid(np.arange(side, dtype=np.int64), np.arange(side, dtype=np.int64), indexing="ij")
+    X2, Y2 = 2 * x - side + 1, 2 * y - side + 1
+    sx = (cs * X2 - sn * Y2 + (side << 14)) >> 15
+    sy = (sn * X2 + cs * Y2 + (side << 14)) >> 15
+    ok = (sx >= 0) & (sx < side) & (sy >= 0) & (sy < side)
+    if reflect:
+        sx, sy = side - 1 - sx, side - 1 - sy
+    out = np.zeros_like(img)
+    out[ok] = img[sy[ok], sx[ok]]
+    return out
+
+
+def _generate(side: int, B: int, seed: int, step: int):
+    from magic_b200.engine import Engine, EngineConfig
+    eng = Engine(EngineConfig(D=side * side, encoder_neurons=(64,), decoder_neurons=(64, 64), latent=8, batch=B))
+    eng.generate_batch(seed, step)
+    X, y = eng.export_batch()
+    rot = eng.export_rotation().cpu().numpy()
+    X = X.cpu().numpy().reshape(B, side, side, 3)
+    y = y.cpu().numpy()
+    return eng, X[..., 0], X[..., 1], X[..., 2], y, rot
+
+
+@pytest.mark.parametrize("side,B", [(200, 48), (40, 37), (256, 5)])
+def test_rotation_and_label_are_bit_exact(side, B):
+    eng, lock, rotp, key, y, rot = _generate(side, B, seed=3, step=7)
+    assert set(np.unique(lock)) <= {0.0, 1.0} and set(np.unique(key)) <= {0.0, 1.0} and set(np.unique(rotp)) <= {0.0, 1.0}
+    for i in range(B):
+        cs, sn = int(rot[i, 0]), int(rot[i, 1])
+        assert abs(cs * cs + sn * sn - 16384 * 16384) < 4 * 16384          # a unit vector in Q14
+        np.testing.assert_array_equal(rotp[i], nn_rotate(lock[i], cs, sn), err_msg="rot plane, pair %d" % i)
+        best = max(int((lock[i] * nn_rotate(key[i], ROT_CS[r % 4], ROT_SN[r % 4], r >= 4)).sum()) for r in range(8))
+        assert int(y[i]) == best, (i, y[i], best)
+    eng.close()
+
+
+def test_batches_depend_on_seed_step_and_are_reproducible():
+    eng, lock_a, _, _, y_a, _ = _generate(200, 8, seed=1, step=0)
+    eng.generate_batch(1, 1)
+    lock_b = eng.export_batch()[0].cpu().numpy().reshape(8, 200, 200, 3)[..., 0]
+    eng.generate_batch(1, 0)
+    lock_c = eng.export_batch()[0].cpu().numpy().reshape(8, 200, 200, 3)[..., 0]
+    assert not np.array_equal(lock_a, lock_b)
+    np.testing.assert_array_equal(lock_a, lock_c)
+    eng.close()
+
+
+def test_statistics_resemble_the_reference_data():
+    import os
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "overlap_micro_16.npz"))
+    real = np.concatenate([gold["area_lock"], gold["area_key"]]).astype(np.float64)
+    eng, lock, rotp, key, y, rot = _generate(200, 256, seed=0, step=0)
+    areas = np.concatenate([lock.reshape(256, -1).sum(1), key.reshape(256, -1).sum(1)])
+    assert 0.6 * real.mean() < areas.mean() < 1.4 * real.mean(), (areas.mean(), real.mean())
+    assert areas.min() > 200 and areas.max() < 16000
+    # rotation keeps the area up to resampling/clipping; labels are overlap areas
+    ar, al = rotp.reshape(256, -1).sum(1), lock.reshape(256, -1).sum(1)
+    assert np.all(np.abs(ar - al) <= 0.05 * al + 8)
+    assert np.all(y <= np.minimum(al, key.reshape(256, -1).sum(1)))
+    assert np.all(y >= 0) and y.mean() > 0.2 * al.mean()
+    ang = np.arctan2(rot[:, 1], rot[:, 0])
+    assert ang.min() < -2.0 and ang.max() > 2.0                          # angles cover the circle (U[0, 2 pi))
+    eng.close()
+
+
+def test_generated_batch_trains():
+    """The packed lock bitmap the BCE epilogue reads and the bf16 planes describe the same image: a step on a
+    generated batch equals a step on the same batch re-loaded through the interleaved fp32 path."""
+    from magic_b200.engine import Engine, EngineConfig
+    cfg = EngineConfig(D=1600, encoder_neurons=(120, 72), decoder_neurons=(88, 104), latent=20, batch=64, precision="fp32")
+    eng = Engine(cfg)
+    eng.generate_batch(5, 2)
+    X, y = eng.export_batch()
+    eps = torch.randn(3, 64, 20, generator=torch.Generator().manual_seed(0))
+    l1, _ = eng.step(labels=y, eps3=eps, apply=False)
+    l1 = l1.cpu().numpy().copy()
+    g1 = eng.get_grad(1, "decoder_out_mean_weights").copy()
+    eng.load_interleaved(X)
+    l2, _ = eng.step(labels=y, eps3=eps, apply=False)
+    np.testing.assert_allclose(l1, l2.cpu().numpy(), rtol=1e-6)
+    g2 = eng.get_grad(1, "decoder_out_mean_weights")      # split-K red.add order differs run to run: fp32 round-off
+    assert np.linalg.norm(g1 - g2) <= 1e-5 * np.linalg.norm(g2)
+    eng.close()
