@@ -25,7 +25,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CFLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-DMAGIC_WAIT_TRAP", "-I", INCLUDE, "-I", CSRC]
 
 LIB_SOURCES = ["gemm.cu", "kernels.cu", "engine.cu", "capi.cu"]
-SELFTEST_SOURCES = ["selftest_gemm.cu", "gemm.cu"]
+SELFTEST_SOURCES = ["selftest_gemm.cu", "gemm.cu", "kernels.cu"]
 
 
 def _deps():

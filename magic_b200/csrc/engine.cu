@@ -106,16 +106,21 @@ std::string nccl_unique_id(void* out128) {
 // ------------------------------------------------------------------ Engine: allocation / layout
 Engine::~Engine() {
   // the process-lifetime handle frees with the context; explicit frees keep repeated create/destroy clean
+  if (gen_stream_) cudaStreamSynchronize(gen_stream_);
   cudaStreamSynchronize(stream);
-  void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, X_.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
+  void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
-                  statbuf_, g_row_, dist_, labels_int_, losses_dev_, stage_x_, stage_labels_, stage_eps_, xbits_, rot_cs_sn_};
+                  statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
+                  in_[0].xbits, in_[1].xbits, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
   for (auto& a : dH_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
   if (comm_ && g_nccl.destroy) g_nccl.destroy(comm_);
   if (comm_stream_) cudaStreamDestroy(comm_stream_);
+  if (gen_stream_) cudaStreamDestroy(gen_stream_);
+  if (ev_gate_) cudaEventDestroy(ev_gate_);
+  for (auto& b : in_) { if (b.ready) cudaEventDestroy(b.ready); if (b.consumed) cudaEventDestroy(b.consumed); }
   for (auto& e : ev_bwd_) if (e) cudaEventDestroy(e);
   if (ev_comm_) cudaEventDestroy(ev_comm_);
 }
@@ -154,6 +159,8 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   if (prop.major != 10) return std::string("this library is built for sm_100a (B200); found ") + prop.name;
   num_sms = prop.multiProcessorCount;
   MAGIC_TRY(gemm_init());
+  cudaFuncSetAttribute(finalize_losses_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  cudaFuncSetAttribute(z_to_zdec_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 
   E = c.n_enc; B = c.batch_local; D = c.D; L = c.L;
   split = c.precision == MAGIC_PRECISION_FP32;
@@ -236,11 +243,20 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   shadow_dirty_ = true;
 
   // ---- activations
-  MAGIC_TRY(alloc_act(&X_, 3LL * B, D + 1));
+  // two input buffers: the generator fills one on its own stream while the step consumes the other
   xb_ld_ = (int)round_up((D + 31) / 32, 8);
-  MAGIC_TRY(alloc((void**)&xbits_, sizeof(uint32_t) * (size_t)B * xb_ld_));
-  MAGIC_TRY(alloc((void**)&rot_cs_sn_, sizeof(int) * 2 * (size_t)B));
-  if (X_.lo) { cudaFree(X_.lo); stats.hbm_bytes -= (int64_t)(sizeof(bf16) * X_.rows * X_.ld); X_.lo = nullptr; }  // pixels are exact in bf16
+  for (auto& b : in_) {
+    MAGIC_TRY(alloc_act(&b.X, 3LL * B, D + 1));
+    if (b.X.lo) { cudaFree(b.X.lo); stats.hbm_bytes -= (int64_t)(sizeof(bf16) * b.X.rows * b.X.ld); b.X.lo = nullptr; }  // pixels are exact in bf16
+    MAGIC_TRY(alloc((void**)&b.xbits, sizeof(uint32_t) * (size_t)B * xb_ld_));
+    MAGIC_TRY(alloc((void**)&b.rot, sizeof(int) * 2 * (size_t)B));
+    MAGIC_TRY(alloc((void**)&b.labels, sizeof(float) * B));
+    MAGIC_CUDA(cudaEventCreateWithFlags(&b.ready, cudaEventDisableTiming));
+    MAGIC_CUDA(cudaEventCreateWithFlags(&b.consumed, cudaEventDisableTiming));
+  }
+  MAGIC_CUDA(cudaStreamCreateWithFlags(&gen_stream_, cudaStreamNonBlocking));
+  MAGIC_CUDA(cudaEventCreateWithFlags(&ev_gate_, cudaEventDisableTiming));
+  if (const char* g = getenv("MAGIC_GEN_GATE")) gen_gate_ = atoi(g) != 0;   // tuning knob, default on
   H_.resize(E);
   dH_.resize(E);
   for (int i = 0; i < E; ++i) {
@@ -266,7 +282,6 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   MAGIC_TRY(alloc((void**)&statbuf_, sizeof(float) * (8 + 3 * L)));
   MAGIC_TRY(alloc((void**)&g_row_, sizeof(float) * B));
   MAGIC_TRY(alloc((void**)&dist_, sizeof(float) * B));
-  MAGIC_TRY(alloc((void**)&labels_int_, sizeof(float) * B));
   MAGIC_TRY(alloc((void**)&losses_dev_, sizeof(float) * 8));
   for (auto& e : ev_bwd_) MAGIC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_comm_, cudaEventDisableTiming));
@@ -328,14 +343,17 @@ std::string Engine::build_plans() {
   // ---------------- forward: encoder (three streams stacked, M = 3B), heads
   fwd_enc_.assign(E + 1, GemmPlan());
   for (int i = 0; i < E; ++i) {
-    GemmProblem p;
-    p.kind = GEMM_FWD; p.epi = EPI_ACT; p.M = 3 * B; p.K = lin[i].Kv + 1; p.N = (int)H_[i].ld;
-    const Act& in = i == 0 ? X_ : H_[i - 1];
-    add_segments(p, 0, amat(in, false, 0, 3LL * B, p.K), amat(in, true, 0, 3LL * B, p.K), wmat(i, false), wmat(i, true),
-                 i == 0);
-    p.e[0] = act_epi(H_[i], lin[i].Nv);
-    p.ws = ws_; p.ws_ld = H_[i].ld;
-    MAGIC_TRY(finish(p, &fwd_enc_[i], "fwd enc"));
+    for (int alt = 0; alt < (i == 0 ? 2 : 1); ++alt) {
+      GemmProblem p;
+      p.kind = GEMM_FWD; p.epi = EPI_ACT; p.M = 3 * B; p.K = lin[i].Kv + 1; p.N = (int)H_[i].ld;
+      const Act& in = i == 0 ? in_[alt].X : H_[i - 1];
+      add_segments(p, 0, amat(in, false, 0, 3LL * B, p.K), amat(in, true, 0, 3LL * B, p.K), wmat(i, false), wmat(i, true),
+                   i == 0);
+      p.e[0] = act_epi(H_[i], lin[i].Nv);
+      p.ws = ws_; p.ws_ld = H_[i].ld;
+      MAGIC_TRY(finish(p, alt == 0 ? &fwd_enc_[i] : &fwd_enc0_alt_, "fwd enc"));
+      if (alt == 1) flops -= fwd_enc0_alt_.flops;
+    }
   }
   {
     GemmProblem p;
@@ -358,23 +376,24 @@ std::string Engine::build_plans() {
   };
   MAGIC_TRY(dec_fwd(&pl_d1_, zdec_, iD1, D1_));
   MAGIC_TRY(dec_fwd(&pl_d2_, D1_, iD2, D2_));
-  for (int v = 0; v < 2; ++v) {
+  for (int v = 0; v < 3; ++v) {   // 0: BCE against input buffer 0; 1: sigmoid (inference); 2: BCE against input buffer 1
     GemmProblem p;
-    p.kind = GEMM_FWD; p.epi = v == 0 ? EPI_BCE : EPI_SIGMOID; p.M = B; p.K = lin[iOut].Kv + 1; p.N = D;
+    p.kind = GEMM_FWD; p.epi = v != 1 ? EPI_BCE : EPI_SIGMOID; p.M = B; p.K = lin[iOut].Kv + 1; p.N = D;
     add_segments(p, 0, amat(D2_, false, 0, B, p.K), amat(D2_, true, 0, B, p.K), wmat(iOut, false), wmat(iOut, true), false);
     EpiArgs e;
     memset(&e, 0, sizeof e);
-    if (v == 0) {
+    if (v != 1) {
       e.out = dA_.hi; e.out_lo = dA_.lo; e.ld_out = dA_.ld;
-      e.xbits = xbits_; e.xb_ld = xb_ld_;                       // packed lock plane (the reconstruction target)
+      e.xbits = in_[v / 2].xbits; e.xb_ld = xb_ld_;             // packed lock plane (the reconstruction target)
       e.alpha = inv_bg; e.scalar = statbuf_ + 0; e.precise = prec;
     } else {
       e.out = nullptr; e.ld_out = D;                             // output pointer patched per call
     }
     e.aux_split = 1 << 30;
     p.e[0] = e;
-    MAGIC_TRY(finish(p, v == 0 ? &pl_out_bce_ : &pl_out_sig_, "fwd dec out"));
-    if (v == 1) flops -= pl_out_sig_.flops;
+    GemmPlan* dst = v == 0 ? &pl_out_bce_ : (v == 1 ? &pl_out_sig_ : &pl_out_bce_alt_);
+    MAGIC_TRY(finish(p, dst, "fwd dec out"));
+    if (v != 0) flops -= dst->flops;
   }
 
   // ---------------- backward of `cost` through the decoder
@@ -447,53 +466,90 @@ std::string Engine::build_plans() {
     MAGIC_TRY(wgrad2(&pl_wg_enc_[i], H_[i - 1], c.enc[i - 1] + 1, false, dH_[i], i));
     MAGIC_TRY(dgrad2(&pl_dg_enc_[i], dH_[i], i, H_[i - 1], dH_[i - 1]));
   }
-  MAGIC_TRY(wgrad2(&pl_wg_enc_[0], X_, D + 1, true, dH_[0], 0));
+  MAGIC_TRY(wgrad2(&pl_wg_enc_[0], in_[0].X, D + 1, true, dH_[0], 0));
+  {
+    const size_t nz = zero_.size();
+    MAGIC_TRY(wgrad2(&pl_wg_enc0_alt_, in_[1].X, D + 1, true, dH_[0], 0));
+    zero_.resize(nz);                        // same gradient windows as the first variant
+    flops -= pl_wg_enc0_alt_.flops;
+  }
   stats.gemm_flops_per_step = flops;
   return "";
 }
 
 // ------------------------------------------------------------------ inputs
+// Every writer targets the buffer that is NOT loaded and then makes it the loaded one; `ready` orders the generator's
+// stream before the step's stream, `consumed` orders the step's last read before the generator's next write.
+void Engine::wait_ready(InBuf& b) {
+  if (b.ready_pending) { cudaStreamWaitEvent(stream, b.ready, 0); b.ready_pending = false; }
+}
+void Engine::mark_consumed(InBuf& b) {
+  cudaEventRecord(b.consumed, stream);
+  b.consumed_pending = true;
+}
 std::string Engine::load_interleaved(const float* d_x) {
   if (!d_x) return "load_interleaved: null input";
+  InBuf& b = in_[cur_ ^ 1];
+  wait_ready(b);
   prof_begin("input.deinterleave");
-  deinterleave_f32(d_x, B, D, X_.hi, X_.ld, stream);
-  pack_lock_bits(X_.hi, X_.ld, B, D, xbits_, xb_ld_, stream);
+  deinterleave_f32(d_x, B, D, b.X.hi, b.X.ld, stream);
+  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
   prof_end();
   MAGIC_CUDA(cudaGetLastError());
-  have_labels_ = false;
+  mark_consumed(b);
+  b.has_labels = false;
+  cur_ ^= 1;
   return "";
 }
 std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uint8_t* k) {
   if (!l || !r || !k) return "load_planar_u8: null input";
-  planar_u8(l, r, k, B, D, X_.hi, X_.ld, stream);
-  pack_lock_bits(X_.hi, X_.ld, B, D, xbits_, xb_ld_, stream);
+  InBuf& b = in_[cur_ ^ 1];
+  wait_ready(b);
+  planar_u8(l, r, k, B, D, b.X.hi, b.X.ld, stream);
+  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
   MAGIC_CUDA(cudaGetLastError());
-  have_labels_ = false;
+  mark_consumed(b);
+  b.has_labels = false;
+  cur_ ^= 1;
   return "";
 }
 std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
   const int side = (int)llround(sqrt((double)D));
   if (side * side != D || side % 8 != 0 || side > 256)
     return "generate: D must be a square canvas with side % 8 == 0 and side <= 256";
+  InBuf& b = in_[cur_ ^ 1];
+  // the generator runs on its own stream so that it overlaps the (tensor-bound) step still in flight on `stream`
+  if (b.consumed_pending) { MAGIC_CUDA(cudaStreamWaitEvent(gen_stream_, b.consumed, 0)); b.consumed_pending = false; }
+  if (gate_pending_ && gen_gate_) { MAGIC_CUDA(cudaStreamWaitEvent(gen_stream_, ev_gate_, 0)); }
+  gate_pending_ = false;
   // fold the rank into the seed so every rank draws different pairs
-  prof_begin("input.generate");
-  generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, X_.hi, X_.ld, xbits_, xb_ld_,
-                 labels_int_, rot_cs_sn_, stream);
-  prof_end();
+  prof_begin("input.generate", 0, gen_stream_);
+  generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, b.X.hi, b.X.ld, b.xbits, xb_ld_,
+                 b.labels, b.rot, num_sms, gen_stream_);
+  prof_end(gen_stream_);
   MAGIC_CUDA(cudaGetLastError());
-  have_labels_ = true;
+  MAGIC_CUDA(cudaEventRecord(b.ready, gen_stream_));
+  b.ready_pending = true;
+  b.has_labels = true;
+  cur_ ^= 1;
   return "";
 }
 std::string Engine::export_rotation(int32_t* d_cs_sn) {
   if (!d_cs_sn) return "export_rotation: null output";
-  if (!have_labels_) return "export_rotation: no generated batch is loaded";
-  MAGIC_CUDA(cudaMemcpyAsync(d_cs_sn, rot_cs_sn_, sizeof(int) * 2 * (size_t)B, cudaMemcpyDeviceToDevice, stream));
+  InBuf& b = in_[cur_];
+  if (!b.has_labels) return "export_rotation: no generated batch is loaded";
+  wait_ready(b);
+  MAGIC_CUDA(cudaMemcpyAsync(d_cs_sn, b.rot, sizeof(int) * 2 * (size_t)B, cudaMemcpyDeviceToDevice, stream));
+  mark_consumed(b);
   return "";
 }
 std::string Engine::export_batch(float* d_x, float* d_labels) {
-  if (d_x) planes_to_interleaved_f32(X_.hi, X_.ld, B, D, d_x, stream);
-  if (d_labels) MAGIC_CUDA(cudaMemcpyAsync(d_labels, labels_int_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
+  InBuf& b = in_[cur_];
+  wait_ready(b);
+  if (d_x) planes_to_interleaved_f32(b.X.hi, b.X.ld, B, D, d_x, stream);
+  if (d_labels) MAGIC_CUDA(cudaMemcpyAsync(d_labels, b.labels, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
   MAGIC_CUDA(cudaGetLastError());
+  mark_consumed(b);
   return "";
 }
 
@@ -505,22 +561,24 @@ void Engine::refresh_shadow() {
 }
 
 void Engine::profile_enable(bool on) { profile_ = on; }
-void Engine::prof_begin(const char* tag, double flops) {
+void Engine::prof_begin(const char* tag, double flops, cudaStream_t on) {
   if (!profile_) return;
+  if (!on) on = stream;
   ProfRec r;
   r.tag = tag; r.flops = flops;
   for (cudaEvent_t* e : {&r.a, &r.b}) {
     if (!prof_pool_.empty()) { *e = prof_pool_.back(); prof_pool_.pop_back(); }
     else cudaEventCreate(e);
   }
-  cudaEventRecord(r.a, stream);
+  cudaEventRecord(r.a, on);
   prof_pending_.push_back(r);
 }
-void Engine::prof_end() {
+void Engine::prof_end(cudaStream_t on) {
   if (!profile_ || prof_pending_.empty()) return;
-  cudaEventRecord(prof_pending_.back().b, stream);
+  cudaEventRecord(prof_pending_.back().b, on ? on : stream);
 }
 std::string Engine::profile_report() {
+  cudaStreamSynchronize(gen_stream_);
   cudaStreamSynchronize(stream);
   for (auto& r : prof_pending_) {
     float ms = 0.f;
@@ -582,9 +640,13 @@ std::string Engine::allreduce(float* buf, size_t n, cudaStream_t s) {
 
 std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) {
   refresh_shadow();
-  MAGIC_CUDA(cudaMemsetAsync(statbuf_, 0, sizeof(float) * (8 + 3 * L), stream));
-  for (int i = 0; i <= E; ++i) MAGIC_TRY(launch(fwd_enc_[i], launches, i == 0 ? "gemm.fwd_enc0" : (i == E ? "gemm.fwd_heads" : "gemm.fwd_enc_hidden")));
-  const float* labels = have_labels_ext_ ? labels_ext_ : labels_int_;
+  zero_fill(statbuf_, sizeof(float) * (8 + 3 * L), stream);
+  InBuf& ib = in_[cur_];
+  wait_ready(ib);
+  for (int i = 0; i <= E; ++i)
+    MAGIC_TRY(launch(i == 0 && cur_ == 1 ? fwd_enc0_alt_ : fwd_enc_[i], launches,
+                     i == 0 ? "gemm.fwd_enc0" : (i == E ? "gemm.fwd_heads" : "gemm.fwd_enc_hidden")));
+  const float* labels = have_labels_ext_ ? labels_ext_ : ib.labels;
   LatentArgs la = latent_args(d_eps3, labels);
   prof_begin("latent.forward"); latent_forward(la, stream); prof_end();
   const bool cosine = cfg.metric == MAGIC_METRIC_COSINE;
@@ -594,14 +656,22 @@ std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) 
   *launches += 2;
   MAGIC_TRY(launch(pl_d1_, launches, "gemm.fwd_dec_hidden"));
   MAGIC_TRY(launch(pl_d2_, launches, "gemm.fwd_dec_hidden"));
-  if (train) MAGIC_TRY(launch(pl_out_bce_, launches, "gemm.fwd_dec_out_bce"));
+  if (train) {
+    MAGIC_TRY(launch(cur_ == 1 ? pl_out_bce_alt_ : pl_out_bce_, launches, "gemm.fwd_dec_out_bce"));
+    // gate for the next batch's generator: let it share the GPU with the backward GEMMs (tensor-bound, HBM half
+    // idle) rather than with the HBM-bound Adam pass of the previous step
+    MAGIC_CUDA(cudaEventRecord(ev_gate_, stream));
+    gate_pending_ = true;
+  } else {
+    mark_consumed(ib);
+  }
   MAGIC_CUDA(cudaGetLastError());
   return "";
 }
 
 std::string Engine::run_backward(int* launches) {
   prof_begin("memset.grad_windows");
-  for (auto& z : zero_) MAGIC_CUDA(cudaMemsetAsync(z.ptr, 0, z.bytes, stream));
+  for (auto& z : zero_) zero_fill(z.ptr, z.bytes, stream);
   prof_end();
   const bool dp = cfg.world > 1;
   MAGIC_TRY(launch(pl_wg_out_, launches, "gemm.wgrad_dec_out"));
@@ -615,7 +685,7 @@ std::string Engine::run_backward(int* launches) {
     MAGIC_TRY(allreduce(g1_ + n_both, (size_t)(n_total - n_both), comm_stream_));
   }
   MAGIC_TRY(launch(pl_dg_h1_, launches, "gemm.dgrad_small"));
-  LatentArgs la = latent_args(nullptr, labels_int_);
+  LatentArgs la = latent_args(nullptr, in_[cur_].labels);
   prof_begin("latent.backward"); latent_backward(la, stream); prof_end();
   *launches += 1;
   MAGIC_TRY(launch(pl_wg_head_, launches, "gemm.wgrad_small"));
@@ -631,7 +701,8 @@ std::string Engine::run_backward(int* launches) {
     MAGIC_TRY(allreduce(g1_ + o1, (size_t)(n_both - o1), comm_stream_));
     MAGIC_TRY(allreduce(g2_ + o1, (size_t)(n_both - o1), comm_stream_));
   }
-  MAGIC_TRY(launch(pl_wg_enc_[0], launches, "gemm.wgrad_enc0"));
+  MAGIC_TRY(launch(cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0], launches, "gemm.wgrad_enc0"));
+  mark_consumed(in_[cur_]);                 // last read of the input buffer in the step
   if (dp) {   // bucket 2: the two 40000-wide first-layer gradients
     MAGIC_CUDA(cudaEventRecord(ev_bwd_[2], stream));
     MAGIC_CUDA(cudaStreamWaitEvent(comm_stream_, ev_bwd_[2], 0));
@@ -645,7 +716,7 @@ std::string Engine::run_backward(int* launches) {
 }
 
 std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply) {
-  if (!d_labels && !have_labels_) return "step: no labels (pass d_labels or call magic_generate_batch first)";
+  if (!d_labels && !in_[cur_].has_labels) return "step: no labels (pass d_labels or call magic_generate_batch first)";
   if (d_labels) { labels_ext_ = d_labels; have_labels_ext_ = true; } else { have_labels_ext_ = false; }
   int launches = 0;
   std::string err = run_forward(d_eps3, true, &launches);

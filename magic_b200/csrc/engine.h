@@ -80,8 +80,8 @@ class Engine {
   std::string run_forward(const float* d_eps3, bool train, int* launches);
   std::string run_backward(int* launches);
   std::string launch(GemmPlan& pl, int* launches, const char* tag);
-  void prof_begin(const char* tag, double flops = 0);
-  void prof_end();
+  void prof_begin(const char* tag, double flops = 0, cudaStream_t on = nullptr);
+  void prof_end(cudaStream_t on = nullptr);
   struct ProfRec { std::string tag; cudaEvent_t a, b; double flops; };
   std::vector<ProfRec> prof_pending_;
   std::vector<cudaEvent_t> prof_pool_;
@@ -106,9 +106,22 @@ class Engine {
   bool shadow_dirty_ = true;
 
   // activations
-  Act X_;                           // [3B, D+1]  rows [rot; lock; key]
-  uint32_t* xbits_ = nullptr; int xb_ld_ = 0;   // [B, xb_ld] packed lock plane: the BCE epilogue's target
-  int* rot_cs_sn_ = nullptr;        // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
+  struct InBuf {                    // one input batch
+    Act X;                          // [3B, D+1] bf16 planes, rows [rot; lock; key]
+    uint32_t* xbits = nullptr;      // [B, xb_ld] packed lock plane: the BCE epilogue's target
+    float* labels = nullptr;        // [B] generated overlap labels
+    int* rot = nullptr;             // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
+    cudaEvent_t ready = nullptr, consumed = nullptr;
+    bool ready_pending = false, consumed_pending = false, has_labels = false;
+  };
+  InBuf in_[2];                     // the generator fills in_[cur_ ^ 1] on gen_stream_ while the step reads in_[cur_]
+  int cur_ = 0;
+  int xb_ld_ = 0;
+  cudaStream_t gen_stream_ = nullptr;
+  cudaEvent_t ev_gate_ = nullptr;   // recorded after the forward pass: earliest start of the next batch's generator
+  bool gate_pending_ = false, gen_gate_ = true;
+  void wait_ready(InBuf& b);
+  void mark_consumed(InBuf& b);
   std::vector<Act> H_;              // encoder hidden outputs [3B, enc_i + 1]
   float* heads_ = nullptr; long long ld_heads_ = 0;      // [3B, 2L] fp32
   float* z_ = nullptr;              // [3B, L]
@@ -120,15 +133,15 @@ class Engine {
   std::vector<Act> dH_;             // encoder pre-activation grads [4B, enc_i]
   float* ws_ = nullptr; long long ws_ld_ = 0;            // split-K workspace
   float* statbuf_ = nullptr;        // [8 sums | 2L colsq | L colS]
-  float *g_row_ = nullptr, *dist_ = nullptr, *labels_int_ = nullptr, *losses_dev_ = nullptr;
+  float *g_row_ = nullptr, *dist_ = nullptr, *losses_dev_ = nullptr;
   float *stage_x_ = nullptr, *stage_labels_ = nullptr, *stage_eps_ = nullptr;   // partial_fit_host staging
-  bool have_labels_ = false;
   const float* labels_ext_ = nullptr;
   bool have_labels_ext_ = false;
 
   // plans
   std::vector<GemmPlan> fwd_enc_;   // E hidden + heads
   GemmPlan pl_d1_, pl_d2_, pl_out_bce_, pl_out_sig_;
+  GemmPlan fwd_enc0_alt_, pl_out_bce_alt_, pl_wg_enc0_alt_;   // the plans that read the input batch, on in_[1]
   GemmPlan pl_wg_out_, pl_dg_out_, pl_wg_h2_, pl_dg_h2_, pl_wg_h1_, pl_dg_h1_;
   GemmPlan pl_wg_head_, pl_dg_head_;
   std::vector<GemmPlan> pl_wg_enc_, pl_dg_enc_;   // index i: wgrad of layer i; dgrad through layer i (i >= 1)

@@ -1,5 +1,6 @@
 // Host-side planning and launch of the tcgen05 GEMM: tensor maps, split-K choice, finishing pass.
 #include "gemm.h"
+#include "kernels.h"
 #include <cstdio>
 #include <cstring>
 
@@ -56,6 +57,9 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<false, false, EPI_DACT>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32>();
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
+  cudaFuncSetAttribute(gemm_finish_kernel<EPI_ACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  cudaFuncSetAttribute(gemm_finish_kernel<EPI_DACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  kernels_init();
   return "";
 }
 
@@ -185,7 +189,7 @@ static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
 int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
   int launches = 0;
   if (pl.two_pass) {
-    cudaMemsetAsync(pl.ws, 0, sizeof(float) * pl.ws_ld * pl.args.M, s);
+    zero_fill(pl.ws, sizeof(float) * pl.ws_ld * pl.args.M, s);
   }
   const int key = pl.kind * 8 + pl.epi;
   switch (key) {

@@ -34,28 +34,40 @@ __device__ __forceinline__ void store_split(__nv_bfloat16* hi, __nv_bfloat16* lo
   if (lo) lo[idx] = __float2bfloat16(v - __bfloat162float(h));
 }
 
+// ------------------------------------------------------------------ zero fill
+// A kernel instead of cudaMemsetAsync so that every launch of the step shares one shared-memory carveout (below).
+__global__ void __launch_bounds__(256) zero_kernel(uint4* p, long long n16, uint32_t* tail, int ntail) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n16) p[i] = make_uint4(0u, 0u, 0u, 0u);
+  if (i < ntail) tail[i] = 0u;
+}
+void zero_fill(void* ptr, size_t bytes, cudaStream_t s) {   // ptr 16-byte aligned, bytes a multiple of 4
+  const long long n16 = (long long)(bytes / 16);
+  const int ntail = (int)((bytes % 16) / 4);
+  const long long n = n16 > ntail ? n16 : ntail;
+  if (n == 0) return;
+  zero_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(reinterpret_cast<uint4*>(ptr), n16,
+                                                     reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(ptr) + n16 * 16), ntail);
+}
+
 // ------------------------------------------------------------------ latent forward
-// One warp per pair; lanes stride over latent columns.  (8c/vae.py:358-371, 275-288)
+// (8c/vae.py:358-371, 275-288)  Thread <-> latent column, CTA <-> slab of kLatSlab pairs: loads are coalesced along
+// the latent axis and the batch-axis sums of squares the cosine metric needs stay in registers until the end.
 constexpr int kLatWarps = 8;
 constexpr int kLatRowsPerWarp = 4;
+constexpr int kLatSlab = 16;
 
-__global__ void __launch_bounds__(kLatWarps * 32) latent_forward_kernel(LatentArgs a) {
-  extern __shared__ float sm[];   // [2, L] column sums of squares
+__global__ void __launch_bounds__(256) latent_forward_kernel(LatentArgs a) {
   const int L = a.L, B = a.B;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  const int i0 = blockIdx.y * kLatSlab, i1 = min(B, i0 + kLatSlab);
   const bool cosine = a.metric == METRIC_COSINE;
-  if (cosine) {
-    for (int j = threadIdx.x; j < 2 * L; j += blockDim.x) sm[j] = 0.f;
-    __syncthreads();
-  }
-  float kl = 0.f, def = 0.f;
-  for (int rr = 0; rr < kLatRowsPerWarp; ++rr) {
-    const int i = (blockIdx.x * kLatWarps + warp) * kLatRowsPerWarp + rr;
-    if (i >= B) break;
-    const float* h_rot = a.heads + (long long)i * a.ld_heads;
-    const float* h_lock = a.heads + (long long)(B + i) * a.ld_heads;
-    const float* h_key = a.heads + (long long)(2 * B + i) * a.ld_heads;
-    for (int j = lane; j < L; j += 32) {
+  float kl = 0.f, def = 0.f, sq_l = 0.f, sq_k = 0.f;
+  if (j < L) {
+    for (int i = i0; i < i1; ++i) {
+      const float* h_rot = a.heads + (long long)i * a.ld_heads;
+      const float* h_lock = a.heads + (long long)(B + i) * a.ld_heads;
+      const float* h_key = a.heads + (long long)(2 * B + i) * a.ld_heads;
       float e_lock, e_rot, e_key;
       if (a.eps) {
         e_lock = a.eps[((long long)0 * B + i) * L + j];
@@ -76,25 +88,23 @@ __global__ void __launch_bounds__(kLatWarps * 32) latent_forward_kernel(LatentAr
       a.z[(long long)(B + i) * L + j] = zl;
       a.z[(long long)(2 * B + i) * L + j] = zk;
       store_split(a.zdec, a.zdec_lo, (long long)i * a.ld_zdec + j, zl);
+      if (j == 0) store_split(a.zdec, a.zdec_lo, (long long)i * a.ld_zdec + L, 1.0f);   // bias column
       kl += -0.5f * (1.f + lv - mu * mu - ex);
       const float d = zl - zr;
       def += d * d;
-      if (cosine) {
-        atomicAdd(&sm[j], zl * zl);
-        atomicAdd(&sm[L + j], zk * zk);
-      }
+      sq_l += zl * zl;
+      sq_k += zk * zk;
     }
-    if (lane == 0) store_split(a.zdec, a.zdec_lo, (long long)i * a.ld_zdec + L, 1.0f);   // bias column
+    if (cosine) {
+      atomicAdd(&a.colsq[j], sq_l);
+      atomicAdd(&a.colsq[L + j], sq_k);
+    }
   }
   kl = warp_sum(kl);
   def = warp_sum(def);
-  if (lane == 0) {
+  if ((threadIdx.x & 31) == 0 && (kl != 0.f || def != 0.f)) {
     atomicAdd(&a.sums[1], kl * a.inv_bg);
     atomicAdd(&a.sums[2], def * a.def_weight * a.inv_bg);
-  }
-  if (cosine) {
-    __syncthreads();
-    for (int j = threadIdx.x; j < 2 * L; j += blockDim.x) atomicAdd(&a.colsq[j], sm[j]);
   }
 }
 
@@ -199,7 +209,7 @@ __global__ void __launch_bounds__(256) latent_backward_kernel(LatentArgs a) {
 static int lat_blocks(int B) { return (B + kLatWarps * kLatRowsPerWarp - 1) / (kLatWarps * kLatRowsPerWarp); }
 
 void latent_forward(const LatentArgs& a, cudaStream_t s) {
-  latent_forward_kernel<<<lat_blocks(a.B), kLatWarps * 32, sizeof(float) * 2 * a.L, s>>>(a);
+  latent_forward_kernel<<<dim3((a.L + 255) / 256, (a.B + kLatSlab - 1) / kLatSlab), 256, 0, s>>>(a);
 }
 void latent_metric(const LatentArgs& a, cudaStream_t s) {
   latent_metric_kernel<<<lat_blocks(a.B), kLatWarps * 32, sizeof(float) * a.L, s>>>(a);
@@ -374,7 +384,7 @@ void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B,
 //      D, zero pad) with 16-byte coalesced stores, plus the packed lock bitmap the BCE epilogue reads.
 constexpr int kPrims = 3;
 constexpr int kLabelRots = 8;
-constexpr int kGenThreads = 256;
+constexpr int kGenThreads = 384;
 constexpr int kMaxBitWords = 2048;                       // canvas up to 256 x 256
 // Q14 (cos, sin) of r * 45 degrees, r = 0..3; rotation r + 4 is DEFINED as the point reflection of rotation r's
 // source pixel through the canvas centre (sx, sy) -> (W-1-sx, W-1-sy), which shares the coordinate arithmetic.
@@ -468,18 +478,25 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
                                                                      __nv_bfloat16* planes, long long ld,
                                                                      uint32_t* xbits, int xb_ld, float* labels,
                                                                      int* rot_cs_sn) {
-  const int i = blockIdx.x;
   const int D = side * side;
   const int nwords = (D + 31) >> 5;
-  __shared__ uint32_t bm[3][kMaxBitWords];     // 0 lock, 1 key, 2 rot
-  __shared__ uint4 lut[256];                   // byte of 8 pixels -> 8 bf16
+  // dynamic shared memory, sized by the canvas so that a generator CTA fits on an SM next to a resident GEMM CTA:
+  // [lut: 256 x uint4 | lock | key | rot bitmaps, (nwords + 8) words each]
+  extern __shared__ uint4 gen_smem[];
+  uint4* lut = gen_smem;                       // byte of 8 pixels -> 8 bf16
+  const int bm_pitch = (nwords + 8 + 3) & ~3;
+  uint32_t* const bm_base = reinterpret_cast<uint32_t*>(gen_smem + 256);
+  uint32_t* const bm[3] = {bm_base, bm_base + bm_pitch, bm_base + 2 * bm_pitch};   // 0 lock, 1 key, 2 rot
   __shared__ Prim prims[2][kPrims];
   __shared__ int rot_q14[2];
   __shared__ int rot_radius;                   // every lock pixel lies within this distance of the centre
   __shared__ int counts[kLabelRots];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < 256) lut[threadIdx.x] = expand_byte(threadIdx.x);
+  // persistent: the grid is at most one CTA per SM, so the generator shares every SM with the step's GEMM CTA
+  // instead of displacing it
+  for (int i = blockIdx.x; i < B; i += gridDim.x) {
   for (int w = threadIdx.x; w < nwords + 8; w += kGenThreads) bm[0][w] = bm[1][w] = bm[2][w] = 0u;
-  lut[threadIdx.x] = expand_byte(threadIdx.x);           // kGenThreads == 256
   if (threadIdx.x == 0) {
     make_prims(prims[0], rng_key(seed, step, 11, (uint64_t)i * 64), (float)side);
     float sn, cs;
@@ -509,7 +526,7 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
       float lo, hi;
       if (!prim_row_interval(q, (float)y - q.cy, lo, hi)) continue;
       const int x0 = max(0, (int)ceilf(q.cx + lo)), x1 = min(side - 1, (int)floorf(q.cx + hi));
-      if (x0 <= x1) or_bit_range(bm[s], y * side + x0, y * side + x1);
+      if (x0 <= x1) or_bit_range(bm_base + s * bm_pitch, y * side + x0, y * side + x1);
     }
   }
   __syncthreads();
@@ -584,13 +601,19 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
   }
   if (xbits)
     for (int w = threadIdx.x; w < xb_ld; w += kGenThreads) xbits[(long long)i * xb_ld + w] = w < nwords ? bm[0][w] : 0u;
+  __syncthreads();                             // the bitmaps are reused by the next pair
+  }
 }
 
 void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, uint32_t* xbits,
-                    int xb_ld, float* labels, int* rot_cs_sn, cudaStream_t s) {
+                    int xb_ld, float* labels, int* rot_cs_sn, int max_ctas, cudaStream_t s) {
   const uint32_t inv_side = (uint32_t)((0x100000000ull + (uint64_t)side - 1) / (uint64_t)side);
-  generate_pairs_kernel<<<B, kGenThreads, 0, s>>>(seed, step, B, side, inv_side, planes, ld, xbits, xb_ld, labels,
-                                                  rot_cs_sn);
+  // same (maximum) shared-memory carveout as the GEMM kernels: an SM only changes its carveout when it is idle, so a
+  // different preference here would make every overlapped GEMM CTA wait for the generator to drain
+  const int nwords = (side * side + 31) / 32;
+  const size_t smem = 256 * sizeof(uint4) + 3 * (size_t)((nwords + 8 + 3) & ~3) * sizeof(uint32_t);
+  generate_pairs_kernel<<<B < max_ctas ? B : max_ctas, kGenThreads, smem, s>>>(seed, step, B, side, inv_side, planes, ld, xbits, xb_ld, labels,
+                                                     rot_cs_sn);
 }
 
 // lock plane (bf16 {0,1}, rows [B, 2B) of planes) -> packed bitmap xbits[B, xb_ld] for the loaders that do not
@@ -611,5 +634,25 @@ void pack_lock_bits(const __nv_bfloat16* planes, long long ld, int B, int D, uin
   pack_lock_bits_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(planes, ld, B, D, xbits, xb_ld);
 }
 
+
+// An SM changes its shared-memory carveout only when it is idle.  The GEMM kernels need the maximum carveout and the
+// generator shares SMs with them from its own stream, so every kernel of the library asks for the same carveout:
+// no launch ever waits for co-resident CTAs of the other stream to drain.
+#define MAGIC_MAX_CARVEOUT(k) \
+  cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)
+void kernels_init() {
+  MAGIC_MAX_CARVEOUT(zero_kernel);
+  MAGIC_MAX_CARVEOUT(latent_forward_kernel);
+  MAGIC_MAX_CARVEOUT(latent_metric_kernel);
+  MAGIC_MAX_CARVEOUT(latent_backward_kernel);
+  MAGIC_MAX_CARVEOUT(adam_dual_kernel);
+  MAGIC_MAX_CARVEOUT(shadow_refresh_kernel);
+  MAGIC_MAX_CARVEOUT(deinterleave_kernel);
+  MAGIC_MAX_CARVEOUT(planar_u8_kernel);
+  MAGIC_MAX_CARVEOUT(planes_to_interleaved_kernel);
+  MAGIC_MAX_CARVEOUT(generate_pairs_kernel);
+  MAGIC_MAX_CARVEOUT(pack_lock_bits_kernel);
+  cudaGetLastError();
+}
 
 }  // namespace magic

@@ -67,9 +67,12 @@ void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B,
 // On-device synthetic shape pairs (replaces 8c/overlap_input.py): random filled shapes on a
 // side x side canvas, nearest-neighbour rotated copy (8c/utils.py:329-340), integer overlap label.
 void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, uint32_t* xbits,
-                    int xb_ld, float* labels, int* rot_cs_sn, cudaStream_t s);
+                    int xb_ld, float* labels, int* rot_cs_sn, int max_ctas, cudaStream_t s);
 // packed 1-bit copy of the lock plane (pixel p = bit p & 31 of word p >> 5, row pitch xb_ld words): the target the
 // sigmoid-BCE epilogue reads (8c/vae.py:260-263)
 void pack_lock_bits(const __nv_bfloat16* planes, long long ld, int B, int D, uint32_t* xbits, int xb_ld, cudaStream_t s);
+
+void zero_fill(void* ptr, size_t bytes, cudaStream_t s);   // kernel-based memset(0): ptr 16-byte aligned, bytes % 4 == 0
+void kernels_init();                                        // one-time function attributes (shared-memory carveout)
 
 }  // namespace magic
