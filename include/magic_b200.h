@@ -129,6 +129,17 @@ int magic_decode(magic_handle* h, const float* d_z, float* d_out);
  * batch statistics, the two gradients and the loss scalars over NCCL inside the step. */
 int magic_comm_unique_id(void* h_id128);
 int magic_comm_init(magic_handle* h, const void* h_nccl_unique_id128);
+/* Fused gradient exchange over NVLink peer memory (after magic_comm_init, all ranks on one node): every rank exports a
+ * 256-byte blob of CUDA IPC handles (its gradient staging buffer and shadow weights), the host framework all-gathers
+ * the blobs in rank order, every rank imports.  From then on the wgrad GEMM epilogues store their tiles straight into
+ * the owning rank's staging buffer (reduce-scatter fused into the GEMM), each rank runs both Adams on its 1/world
+ * slice only and stores the new bf16 weights into every rank's shadow buffer (all-gather fused into Adam); NCCL is
+ * left with the tiny cosine-statistic / loss-scalar all-reduces that double as barriers.  Without this call (or with
+ * MAGIC_DP_MODE=allreduce) gradients are all-reduced by NCCL in three buckets behind the backward pass.
+ * After it, magic_get/set_param, magic_get/set_slot and magic_get_grad are collective (every rank calls them). */
+#define MAGIC_PEER_BLOB_BYTES 256
+int magic_comm_export_peer(magic_handle* h, void* h_blob256);
+int magic_comm_import_peers(magic_handle* h, const void* h_blobs /* world x 256 bytes, rank order */);
 
 /* Per-launch CUDA-event timing of the step's kernels (bench.py's roofline and profiles/).  The report is text,
  * one line per kernel family: "<tag> <ms summed> <launches> <tensor flops summed>".  Reading it synchronises

@@ -67,6 +67,8 @@ SIGNATURES = {
     "magic_decode": (C.c_int, [_VP, _VP, _VP]),
     "magic_comm_unique_id": (C.c_int, [_VP]),
     "magic_comm_init": (C.c_int, [_VP, _VP]),
+    "magic_comm_export_peer": (C.c_int, [_VP, _VP]),
+    "magic_comm_import_peers": (C.c_int, [_VP, _VP]),
     "magic_profile_enable": (C.c_int, [_VP, _I32]),
     "magic_profile_report": (C.c_int, [_VP, C.c_char_p, _I64]),
     "magic_test_gemm": (C.c_int, [_I32, _I32, _I32, _I32, _VP, _I64, _VP, _I64, _VP, _I64, _I32, _VP]),

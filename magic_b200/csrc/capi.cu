@@ -181,6 +181,16 @@ int magic_comm_init(magic_handle* h, const void* h_nccl_unique_id128) {
   return done(h->eng.comm_init(h_nccl_unique_id128));
 }
 
+int magic_comm_export_peer(magic_handle* h, void* h_blob256) {
+  CHECK_HANDLE(h);
+  if (!h_blob256) return fail("null output");
+  return done(h->eng.comm_export_peer(h_blob256));
+}
+int magic_comm_import_peers(magic_handle* h, const void* h_blobs) {
+  CHECK_HANDLE(h);
+  if (!h_blobs) return fail("null input");
+  return done(h->eng.comm_import_peers(h_blobs));
+}
 int magic_profile_enable(magic_handle* h, int32_t on) {
   CHECK_HANDLE(h);
   h->eng.profile_enable(on != 0);

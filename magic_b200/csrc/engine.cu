@@ -69,6 +69,7 @@ typedef int (*nccl_get_uid_t)(void*);
 struct NcclUid { char b[128]; };
 typedef int (*nccl_init_rank2_t)(void**, int, NcclUid, int);
 typedef int (*nccl_allreduce_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*nccl_allgather_t)(const void*, void*, size_t, int, void*, cudaStream_t);
 typedef int (*nccl_destroy_t)(void*);
 typedef const char* (*nccl_errstr_t)(int);
 struct NcclApi {
@@ -76,6 +77,7 @@ struct NcclApi {
   nccl_get_uid_t get_uid = nullptr;
   nccl_init_rank2_t init_rank = nullptr;
   nccl_allreduce_t allreduce = nullptr;
+  nccl_allgather_t allgather = nullptr;
   nccl_destroy_t destroy = nullptr;
   nccl_errstr_t errstr = nullptr;
 };
@@ -91,6 +93,7 @@ static std::string load_nccl() {
   g_nccl.get_uid = (nccl_get_uid_t)dlsym(g_nccl.lib, "ncclGetUniqueId");
   g_nccl.init_rank = (nccl_init_rank2_t)dlsym(g_nccl.lib, "ncclCommInitRank");
   g_nccl.allreduce = (nccl_allreduce_t)dlsym(g_nccl.lib, "ncclAllReduce");
+  g_nccl.allgather = (nccl_allgather_t)dlsym(g_nccl.lib, "ncclAllGather");
   g_nccl.destroy = (nccl_destroy_t)dlsym(g_nccl.lib, "ncclCommDestroy");
   g_nccl.errstr = (nccl_errstr_t)dlsym(g_nccl.lib, "ncclGetErrorString");
   if (!g_nccl.get_uid || !g_nccl.init_rank || !g_nccl.allreduce) return "NCCL symbols missing";
@@ -111,11 +114,17 @@ Engine::~Engine() {
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
                   statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
-                  in_[0].xbits, in_[1].xbits, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot};
+                  in_[0].xbits, in_[1].xbits, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
   for (auto& a : dH_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
+  for (int r = 0; r < kMaxRanks; ++r) {
+    if (r == cfg.rank) continue;
+    if (peer_stage_[r]) cudaIpcCloseMemHandle(peer_stage_[r]);
+    if (peer_whi_[r]) cudaIpcCloseMemHandle(peer_whi_[r]);
+    if (peer_wlo_[r]) cudaIpcCloseMemHandle(peer_wlo_[r]);
+  }
   if (comm_ && g_nccl.destroy) g_nccl.destroy(comm_);
   if (comm_stream_) cudaStreamDestroy(comm_stream_);
   if (gen_stream_) cudaStreamDestroy(gen_stream_);
@@ -151,7 +160,7 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   if (c.metric != MAGIC_METRIC_COSINE && c.metric != MAGIC_METRIC_SQDIFF)
     return "Invalid distance metric: " + std::to_string(c.metric);                           // 8c/vae.py:305
   if (c.batch_local < 1 || c.batch_global < c.batch_local) return "config: bad batch sizes";
-  if (c.world < 1 || c.rank < 0 || c.rank >= c.world) return "config: bad rank/world";
+  if (c.world < 1 || c.world > kMaxRanks || c.rank < 0 || c.rank >= c.world) return "config: bad rank/world (world <= 8)";
   int dev = 0;
   MAGIC_CUDA(cudaGetDevice(&dev));
   cudaDeviceProp prop;
@@ -222,15 +231,24 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   }
 
   // ---- parameter-shaped buffers
-  MAGIC_TRY(alloc((void**)&p_, sizeof(float) * n_total));
-  MAGIC_TRY(alloc((void**)&g1_, sizeof(float) * n_total));
-  MAGIC_TRY(alloc((void**)&m1_, sizeof(float) * n_total));
-  MAGIC_TRY(alloc((void**)&v1_, sizeof(float) * n_total));
-  MAGIC_TRY(alloc((void**)&g2_, sizeof(float) * n_both));
-  MAGIC_TRY(alloc((void**)&m2_, sizeof(float) * n_both));
-  MAGIC_TRY(alloc((void**)&v2_, sizeof(float) * n_both));
-  MAGIC_TRY(alloc((void**)&w_hi_, sizeof(bf16) * n_total));
-  if (split) MAGIC_TRY(alloc((void**)&w_lo_, sizeof(bf16) * n_total));
+  // data parallel: the flat space is cut into `world` equal slices (owner r = idx / slice_len); buffers are sized
+  // world * slice_len so that slices can be all-gathered in place
+  slice_len_ = (int)(round_up(n_total, (long long)kDpGranule * c.world) / c.world);
+  alloc_len_ = c.world > 1 ? (long long)c.world * slice_len_ : n_total;
+  const long long alloc2 = c.world > 1 ? alloc_len_ : n_both;
+  MAGIC_TRY(alloc((void**)&p_, sizeof(float) * alloc_len_));
+  MAGIC_TRY(alloc((void**)&g1_, sizeof(float) * alloc_len_));
+  MAGIC_TRY(alloc((void**)&m1_, sizeof(float) * alloc_len_));
+  MAGIC_TRY(alloc((void**)&v1_, sizeof(float) * alloc_len_));
+  MAGIC_TRY(alloc((void**)&g2_, sizeof(float) * alloc2));
+  MAGIC_TRY(alloc((void**)&m2_, sizeof(float) * alloc2));
+  MAGIC_TRY(alloc((void**)&v2_, sizeof(float) * alloc2));
+  MAGIC_TRY(alloc((void**)&w_hi_, sizeof(bf16) * alloc_len_));
+  if (split) MAGIC_TRY(alloc((void**)&w_lo_, sizeof(bf16) * alloc_len_));
+  if (c.world > 1) {
+    MAGIC_TRY(alloc((void**)&stage_, sizeof(float) * 2 * alloc_len_));
+    MAGIC_TRY(alloc((void**)&barrier_buf_, sizeof(float) * 8));
+  }
   for (size_t vi = 0; vi < views.size(); ++vi) {
     const ParamView& v = views[vi];
     if (v.is_bias) continue;   // biases start at zero (8c/vae.py:119)
@@ -673,8 +691,8 @@ std::string Engine::run_backward(int* launches) {
   prof_begin("memset.grad_windows");
   for (auto& z : zero_) zero_fill(z.ptr, z.bytes, stream);
   prof_end();
-  const bool dp = cfg.world > 1;
-  MAGIC_TRY(launch(pl_wg_out_, launches, "gemm.wgrad_dec_out"));
+  const bool dp = cfg.world > 1 && !dp_fused_;     // NCCL all-reduce buckets (baseline path)
+  MAGIC_TRY(launch(dp_fused_ ? pl_wg_out_sc_ : pl_wg_out_, launches, "gemm.wgrad_dec_out"));
   MAGIC_TRY(launch(pl_dg_out_, launches, "gemm.dgrad_dec_out"));
   MAGIC_TRY(launch(pl_wg_h2_, launches, "gemm.wgrad_small"));
   MAGIC_TRY(launch(pl_dg_h2_, launches, "gemm.dgrad_small"));
@@ -701,7 +719,23 @@ std::string Engine::run_backward(int* launches) {
     MAGIC_TRY(allreduce(g1_ + o1, (size_t)(n_both - o1), comm_stream_));
     MAGIC_TRY(allreduce(g2_ + o1, (size_t)(n_both - o1), comm_stream_));
   }
-  MAGIC_TRY(launch(cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0], launches, "gemm.wgrad_enc0"));
+  if (dp_fused_) {
+    // the small layers accumulated locally (split-K red.add): hand their partial sums to the owners' staging slots.
+    // Ranges: g1 over [end of layer 0, start of decoder out), g2 over [end of layer 0, n_both).
+    PushArgs pa;
+    memset(&pa, 0, sizeof pa);
+    pa.slice_len = slice_len_; pa.rank = cfg.rank; pa.world = cfg.world; pa.gran_shift = kDpGranShift;
+    prof_begin("dp.push_small");
+    pa.src = g1_; pa.begin = lin[0].size(); pa.end = lin[iOut].off;
+    for (int r = 0; r < cfg.world; ++r) pa.peer[r] = peer_stage_[r];
+    push_range(pa, stream);
+    pa.src = g2_; pa.begin = lin[0].size(); pa.end = n_both;
+    for (int r = 0; r < cfg.world; ++r) pa.peer[r] = peer_stage_[r] + alloc_len_;
+    push_range(pa, stream);
+    prof_end();
+    *launches += 2;
+  }
+  MAGIC_TRY(launch(dp_fused_ ? pl_wg_enc0_sc_[cur_] : (cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0]), launches, "gemm.wgrad_enc0"));
   mark_consumed(in_[cur_]);                 // last read of the input buffer in the step
   if (dp) {   // bucket 2: the two 40000-wide first-layer gradients
     MAGIC_CUDA(cudaEventRecord(ev_bwd_[2], stream));
@@ -726,15 +760,35 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   MAGIC_TRY(allreduce(statbuf_, 4, stream));   // loss scalars: local sums / Bg add up to the global means
   if (d_losses5) { finalize_losses_kernel<<<1, 32, 0, stream>>>(statbuf_, d_losses5); ++launches; }
   if (d_distance) MAGIC_CUDA(cudaMemcpyAsync(d_distance, dist_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
-  if (apply) {
+  const double b1 = cfg.beta1, b2 = cfg.beta2;
+  const double corr = sqrt(1.0 - pow(b2, (double)(t + 1))) / (1.0 - pow(b1, (double)(t + 1)));
+  if (dp_fused_) {
+    // The loss all-reduce above is also the barrier that says: every rank's partial gradients have landed in the
+    // owners' staging buffers (kernel completion makes peer stores visible; NCCL orders the ranks).
+    AdamShardArgs a;
+    memset(&a, 0, sizeof a);
+    a.n_total = n_total; a.gran_shift = kDpGranShift;
+    a.n_both = n_both; a.world = cfg.world; a.rank = cfg.rank; a.slice_len = slice_len_;
+    a.stage1 = stage_; a.stage2 = stage_ + alloc_len_;
+    a.p = p_; a.m1 = m1_; a.v1 = v1_; a.m2 = m2_; a.v2 = v2_; a.g1 = g1_; a.g2 = g2_;
+    for (int r = 0; r < cfg.world; ++r) { a.w_hi[r] = peer_whi_[r]; a.w_lo[r] = peer_wlo_[r]; }
+    a.lr_t1 = (float)(cfg.lr1 * corr); a.lr_t2 = (float)(cfg.lr2 * corr);
+    a.beta1 = cfg.beta1; a.beta2 = cfg.beta2; a.eps = cfg.eps;
+    a.apply = apply ? 1 : 0;
+    prof_begin("adam.dual_sharded"); adam_dual_sharded(a, stream); prof_end();
+    ++launches;
+    // second barrier: all owners have pushed the new shadow weights (and are done reading their staging) before
+    // any rank starts the next forward pass / the next step's gradient scatter
+    MAGIC_TRY(allreduce(barrier_buf_, 1, stream));
+    if (apply) { ++t; stats.steps = t; master_stale_ = true; }
+    grads_sharded_ = true;
+  } else if (apply) {
     ++t;
     AdamArgs a;
     memset(&a, 0, sizeof a);
     a.p = p_; a.g1 = g1_; a.g2 = g2_; a.m1 = m1_; a.v1 = v1_; a.m2 = m2_; a.v2 = v2_;
     a.w_hi = w_hi_; a.w_lo = w_lo_;
     a.n_both = n_both; a.n_total = n_total;
-    const double b1 = cfg.beta1, b2 = cfg.beta2;
-    const double corr = sqrt(1.0 - pow(b2, (double)t)) / (1.0 - pow(b1, (double)t));
     a.lr_t1 = (float)(cfg.lr1 * corr);
     a.lr_t2 = (float)(cfg.lr2 * corr);
     a.beta1 = cfg.beta1; a.beta2 = cfg.beta2; a.eps = cfg.eps;
@@ -811,6 +865,109 @@ std::string Engine::comm_init(const void* uid) {
   return "";
 }
 
+// ------------------------------------------------------------------ fused data parallelism over peer memory
+struct PeerBlob {                       // what one rank tells the others (kPeerBlobBytes)
+  cudaIpcMemHandle_t stage, whi, wlo;
+  int has_lo, device;
+};
+static_assert(sizeof(PeerBlob) <= Engine::kPeerBlobBytes, "peer blob too large");
+
+std::string Engine::comm_export_peer(void* h_blob) {
+  if (cfg.world < 2) return "comm_export_peer: world == 1";
+  PeerBlob b;
+  memset(&b, 0, sizeof b);
+  MAGIC_CUDA(cudaIpcGetMemHandle(&b.stage, stage_));
+  MAGIC_CUDA(cudaIpcGetMemHandle(&b.whi, w_hi_));
+  if (w_lo_) { MAGIC_CUDA(cudaIpcGetMemHandle(&b.wlo, w_lo_)); b.has_lo = 1; }
+  MAGIC_CUDA(cudaGetDevice(&b.device));
+  memset(h_blob, 0, kPeerBlobBytes);
+  memcpy(h_blob, &b, sizeof b);
+  return "";
+}
+
+std::string Engine::comm_import_peers(const void* h_blobs) {
+  if (cfg.world < 2) return "comm_import_peers: world == 1";
+  if (!comm_) return "comm_import_peers: call magic_comm_init first";
+  const char* mode = getenv("MAGIC_DP_MODE");
+  if (mode && std::string(mode) == "allreduce") return "";       // keep the NCCL all-reduce baseline path
+  for (int r = 0; r < cfg.world; ++r) {
+    if (r == cfg.rank) {
+      peer_stage_[r] = stage_; peer_whi_[r] = w_hi_; peer_wlo_[r] = w_lo_;
+      continue;
+    }
+    PeerBlob b;
+    memcpy(&b, static_cast<const char*>(h_blobs) + (size_t)r * kPeerBlobBytes, sizeof b);
+    void* ptr = nullptr;
+    MAGIC_CUDA(cudaIpcOpenMemHandle(&ptr, b.stage, cudaIpcMemLazyEnablePeerAccess));
+    peer_stage_[r] = static_cast<float*>(ptr);
+    MAGIC_CUDA(cudaIpcOpenMemHandle(&ptr, b.whi, cudaIpcMemLazyEnablePeerAccess));
+    peer_whi_[r] = static_cast<bf16*>(ptr);
+    if (b.has_lo) {
+      MAGIC_CUDA(cudaIpcOpenMemHandle(&ptr, b.wlo, cudaIpcMemLazyEnablePeerAccess));
+      peer_wlo_[r] = static_cast<bf16*>(ptr);
+    }
+  }
+  MAGIC_TRY(build_dp_plans());
+  dp_fused_ = true;
+  return "";
+}
+
+// Scatter variants of the two 40000-wide weight gradients (97 % of the gradient bytes): same GEMMs, epilogue
+// EPI_SCATTER_F32 -> the owner's staging slot of this rank.  Never split along K (plain stores, not red.add).
+std::string Engine::build_dp_plans() {
+  auto scatter_epi = [&](int which, int layer, float alpha) {
+    EpiArgs e;
+    memset(&e, 0, sizeof e);
+    e.ld_out = lin[layer].ld; e.alpha = alpha; e.aux_split = 1 << 30;
+    e.flat_base = lin[layer].off; e.slice_len = slice_len_; e.src_rank = cfg.rank;
+    e.world = cfg.world; e.gran_shift = kDpGranShift;
+    for (int r = 0; r < cfg.world; ++r) e.peer[r] = peer_stage_[r] + (which == 2 ? alloc_len_ : 0);
+    return e;
+  };
+  {
+    GemmProblem p;
+    p.kind = GEMM_WGRAD; p.epi = EPI_SCATTER_F32; p.M = cfg.dec[1] + 1; p.N = lin[iOut].Nv; p.K = B;
+    add_segments(p, 0, amat(D2_, false, 0, B, p.M), amat(D2_, true, 0, B, p.M), amat(dA_, false, 0, B, p.N),
+                 amat(dA_, true, 0, B, p.N), false);
+    p.e[0] = scatter_epi(1, iOut, inv_bg);
+    p.force_splitk = 1;
+    std::string err = gemm_plan(p, num_sms, &pl_wg_out_sc_);
+    if (!err.empty()) return "dp wgrad dec out: " + err;
+  }
+  for (int alt = 0; alt < 2; ++alt) {
+    const Act& x = in_[alt].X;
+    const Act& dy = dH_[0];
+    GemmProblem p;
+    p.kind = GEMM_WGRAD; p.epi = EPI_SCATTER_F32; p.ngroups = 2; p.M = D + 1; p.N = lin[0].Nv; p.K = 2 * B;
+    add_segments(p, 0, amat(x, false, 0, 2LL * B, p.M), amat(x, true, 0, 2LL * B, p.M), amat(dy, false, 0, 2LL * B, p.N),
+                 amat(dy, true, 0, 2LL * B, p.N), true);
+    add_segments(p, 1, amat(x, false, B, 2LL * B, p.M), amat(x, true, B, 2LL * B, p.M),
+                 amat(dy, false, 2LL * B, 2LL * B, p.N), amat(dy, true, 2LL * B, 2LL * B, p.N), true);
+    p.e[0] = scatter_epi(1, 0, 1.f);
+    p.e[1] = scatter_epi(2, 0, 1.f);
+    p.force_splitk = 1;
+    std::string err = gemm_plan(p, num_sms, &pl_wg_enc0_sc_[alt]);
+    if (!err.empty()) return "dp wgrad enc0: " + err;
+  }
+  return "";
+}
+
+// Sharded state (fp32 master weights, optimiser slots, reduced gradients) lives only on the owner of each granule
+// between steps; host accessors assemble it first: zero what this rank does not own, all-reduce(sum).  Collective:
+// every rank must make the same call -- true for checkpointing and for the parity tests.
+std::string Engine::assemble(float* buf, long long n) {
+  mask_unowned(buf, n, cfg.world, cfg.rank, kDpGranShift, stream);
+  return allreduce(buf, (size_t)n, stream);
+}
+std::string Engine::gather_master() {
+  if (!dp_fused_ || !master_stale_) return "";
+  for (float* b : {p_, m1_, v1_}) MAGIC_TRY(assemble(b, n_total));
+  for (float* b : {m2_, v2_}) MAGIC_TRY(assemble(b, n_both));
+  MAGIC_CUDA(cudaStreamSynchronize(stream));
+  master_stale_ = false;
+  return "";
+}
+
 // ------------------------------------------------------------------ parameter windows
 std::string Engine::copy_param(int i, float* h_dst, const float* h_src, const float* base) {
   if (i < 0 || i >= (int)views.size()) return "parameter index out of range";
@@ -826,8 +983,13 @@ std::string Engine::copy_param(int i, float* h_dst, const float* h_src, const fl
                             cudaMemcpyHostToDevice));
   return "";
 }
+std::string Engine::get_param(int i, float* h) {
+  MAGIC_TRY(gather_master());
+  return copy_param(i, h, nullptr, p_);
+}
 std::string Engine::set_param(int i, const float* h) {
   if (!h) return "set_param: null source";
+  MAGIC_TRY(gather_master());
   shadow_dirty_ = true;
   return copy_param(i, nullptr, h, p_);
 }
@@ -835,12 +997,18 @@ std::string Engine::get_grad(int which, int i, float* h) {
   if (which != 1 && which != 2) return "get_grad: which must be 1 or 2";
   if (i < 0 || i >= (int)views.size()) return "parameter index out of range";
   if (which == 2 && !(views[i].optimisers & 2)) return "get_grad: optimiser 2 does not train this variable";
+  if (dp_fused_ && grads_sharded_) {        // reduced gradients exist on their owners only: gather (collective)
+    MAGIC_TRY(assemble(g1_, n_total));
+    MAGIC_TRY(assemble(g2_, n_both));
+    grads_sharded_ = false;
+  }
   return copy_param(i, h, nullptr, which == 1 ? g1_ : g2_);
 }
 std::string Engine::slot(int which, int sl, int i, float* h_dst, const float* h_src) {
   if (which != 1 && which != 2) return "slot: which must be 1 or 2";
   if (i < 0 || i >= (int)views.size()) return "parameter index out of range";
   if (which == 2 && !(views[i].optimisers & 2)) return "slot: optimiser 2 does not train this variable";
+  MAGIC_TRY(gather_master());
   const float* base = which == 1 ? (sl == MAGIC_SLOT_M ? m1_ : v1_) : (sl == MAGIC_SLOT_M ? m2_ : v2_);
   return copy_param(i, h_dst, h_src, base);
 }

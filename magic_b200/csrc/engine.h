@@ -55,12 +55,17 @@ class Engine {
   std::string forward(int what, const float* d_eps3, float* d_out);
   std::string decode(const float* d_z, float* d_out);
   std::string comm_init(const void* uid);
+  // Fused data parallelism over peer memory: every rank exports CUDA IPC handles of its gradient
+  // staging buffer and shadow weights (kPeerBlobBytes each), the host framework all-gathers them, every rank imports.
+  static constexpr int kPeerBlobBytes = 256;
+  std::string comm_export_peer(void* h_blob);
+  std::string comm_import_peers(const void* h_blobs /* world x kPeerBlobBytes, rank order */);
   // per-launch CUDA-event timing (bench / optimisation aid): tag -> accumulated ms, launches
   void profile_enable(bool on);
   std::string profile_report();     // synchronises; "tag ms count flops\n" lines; resets the accumulators
 
   std::string copy_param(int i, float* h_dst, const float* h_src, const float* base);   // get (h_dst) or set (h_src)
-  std::string get_param(int i, float* h) { return copy_param(i, h, nullptr, p_); }
+  std::string get_param(int i, float* h);
   std::string set_param(int i, const float* h);
   std::string get_grad(int which, int i, float* h);
   std::string slot(int which, int slot, int i, float* h_dst, const float* h_src);
@@ -155,6 +160,22 @@ class Engine {
   cudaEvent_t ev_bwd_[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_comm_ = nullptr;
   std::string allreduce(float* buf, size_t n, cudaStream_t s);
+  std::string assemble(float* buf, long long n);   // sharded buffer -> complete on every rank (collective)
+  static constexpr int kDpGranShift = 13, kDpGranule = 1 << kDpGranShift;   // ownership granule: 8192 elements
+  // fused DP state
+  bool dp_fused_ = false;           // wgrad epilogues scatter to the owners' staging, sharded Adam, shadow push
+  bool grads_sharded_ = false;      // reduced g1/g2 exist on their owners only (gathered by get_grad)
+  bool master_stale_ = false;       // fp32 p/m/v outside the owned slice are out of date (refreshed on demand)
+  int slice_len_ = 0;               // elements of the flat parameter space owned per rank (multiple of 1024)
+  long long alloc_len_ = 0;         // world * slice_len (>= n_total): size of the parameter-shaped buffers
+  float* stage_ = nullptr;          // [2][world][slice_len]: partial g1 / g2 of the owned slice from every rank
+  float* peer_stage_[kMaxRanks] = {};
+  bf16* peer_whi_[kMaxRanks] = {};
+  bf16* peer_wlo_[kMaxRanks] = {};
+  float* barrier_buf_ = nullptr;
+  GemmPlan pl_wg_out_sc_, pl_wg_enc0_sc_[2];   // scatter variants of the two 40000-wide wgrads
+  std::string build_dp_plans();
+  std::string gather_master();
 };
 
 }  // namespace magic

@@ -36,7 +36,7 @@ __global__ void gemm_finish_kernel(EpiArgs e, const float* __restrict__ ws, long
 template <bool A_MN, bool B_MN, int EPI>
 static cudaError_t set_smem() {
   return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)kGemmSmemBytes);
+                              (int)gemm_smem_bytes(EPI));
 }
 
 std::string gemm_init() {
@@ -56,6 +56,7 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<false, false, EPI_STORE_F32>();
   if (e == cudaSuccess) e = set_smem<false, false, EPI_DACT>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_SCATTER_F32>();
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_ACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_DACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -145,7 +146,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.m_fastest = p.N > p.M ? 1 : 0;   // keep the larger operand's tiles adjacent in time so it is read from HBM once
   const int tiles = a.tiles_m * a.tiles_n * a.ngroups;
   const int total_kb = a.nseg * a.kblocks;
-  const bool linear = p.epi == EPI_STORE_F32;
+  const bool linear = p.epi == EPI_STORE_F32;   // SCATTER_F32 stores plain values to peer memory: never split
   const bool can_split = linear || (p.ws != nullptr && p.ngroups == 1 && (p.epi == EPI_ACT || p.epi == EPI_DACT));
   int split = 1;
   if (can_split) split = p.force_splitk > 0 ? p.force_splitk : choose_splitk(tiles, total_kb, num_sms);
@@ -183,7 +184,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
 
 template <bool A_MN, bool B_MN, int EPI>
 static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
-  gemm_tcgen05_kernel<A_MN, B_MN, EPI><<<pl.grid, gemm_threads(EPI), kGemmSmemBytes, s>>>(pl.args);
+  gemm_tcgen05_kernel<A_MN, B_MN, EPI><<<pl.grid, gemm_threads(EPI), gemm_smem_bytes(EPI), s>>>(pl.args);
 }
 
 int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
@@ -200,6 +201,7 @@ int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
     case GEMM_DGRAD * 8 + EPI_STORE_F32: launch_variant<false, false, EPI_STORE_F32>(pl, s); break;
     case GEMM_DGRAD * 8 + EPI_DACT: launch_variant<false, false, EPI_DACT>(pl, s); break;
     case GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32>(pl, s); break;
+    case GEMM_WGRAD * 8 + EPI_SCATTER_F32: launch_variant<true, true, EPI_SCATTER_F32>(pl, s); break;
     default:
       if (err) *err = "gemm_launch: unsupported (kind, epilogue) combination";
       return -1;

@@ -39,8 +39,15 @@ constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
 constexpr uint32_t kAtomBytes = 64 * kBlockK * 2;          // one 64(MN) x 64(K) MN-major TMA box
 constexpr uint32_t kTmemCols = 2 * kBlockN;                // 512: two accumulator stages
 constexpr uint32_t kGemmSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+// EPI_SCATTER_F32 stages 8 rows x 128 B per epilogue warp so that every row segment leaves the SM as ONE 128-byte
+// bulk copy (full NVLink packets) instead of eight 16-byte partial-sector stores from a strided warp
+constexpr uint32_t kScatterStageBytes = 8 * 128;
+__host__ __device__ constexpr uint32_t gemm_smem_bytes(int epi) {
+  return kGemmSmemBytes + (epi == 5 /*EPI_SCATTER_F32*/ ? 8 * kScatterStageBytes : 0);
+}
 
-enum EpiKind : int { EPI_STORE_F32 = 0, EPI_ACT = 1, EPI_DACT = 2, EPI_BCE = 3, EPI_SIGMOID = 4 };
+enum EpiKind : int { EPI_STORE_F32 = 0, EPI_ACT = 1, EPI_DACT = 2, EPI_BCE = 3, EPI_SIGMOID = 4, EPI_SCATTER_F32 = 5 };
+constexpr int kMaxPeers = 8;
 enum ActKind : int { ACT_NONE = 0, ACT_TANH = 1, ACT_ELU = 2 };
 
 struct EpiArgs {
@@ -60,6 +67,17 @@ struct EpiArgs {
   int atomic;                 // STORE_F32: red.add instead of store (split-K)
   int precise;                // 1: accurate tanhf/expm1f/logf;  0: MUFU approximations (bf16 mode)
   float* scalar;              // BCE: sum of the per-element loss (scaled by alpha) is added here
+  // SCATTER_F32 (data-parallel wgrad fused with its reduce-scatter): the tile goes to the rank that owns its slice of
+  // the flat parameter space, into that rank's staging buffer (peer memory over NVLink), slot `src_rank`:
+  //   idx = flat_base + row * ld_out + col ;  granule q = idx >> gran_shift ;  owner o = q % world ;
+  //   peer[o][src_rank * slice_len + ((q / world) << gran_shift) + (idx & (granule - 1))]
+  // (granules are dealt round-robin so that every rank receives and updates the same share of every layer)
+  float* peer[kMaxPeers];
+  long long flat_base;
+  int slice_len;
+  int src_rank;
+  int world;
+  int gran_shift;
 };
 
 struct GemmArgs {
@@ -173,6 +191,8 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
           else out[j] = v;
         }
     }
+  } else if constexpr (EPI == EPI_SCATTER_F32) {
+    // handled by scatter_chunk() in the kernel (needs the warp's shared-memory staging area)
   } else if constexpr (EPI == EPI_SIGMOID) {
     float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
 #pragma unroll
@@ -300,6 +320,40 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
         for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
       }
     }
+  }
+}
+
+// EPI_SCATTER_F32: this thread's 32 consecutive fp32 of row `row` go to the owning rank's staging slot (see EpiArgs).
+// Four passes of 8 lanes: registers -> 128-byte shared-memory slot -> one cp.async.bulk of the row segment.
+__device__ __forceinline__ void scatter_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M, int N,
+                                              uint8_t* stage /* this warp's kScatterStageBytes */, int lane) {
+  const int valid = min(32, N - col0);                      // floats of this chunk inside the matrix
+  const bool active = row < M && valid > 0;
+  const long long idx = e.flat_base + (long long)row * e.ld_out + col0;
+  const int q = active ? (int)(idx >> e.gran_shift) : 0;
+  const int o = q % e.world;
+  float* dst = e.peer[o] + ((long long)e.src_rank * e.slice_len + ((long long)(q / e.world) << e.gran_shift) +
+                            (idx & ((1LL << e.gran_shift) - 1)));
+  const float alpha = e.alpha;
+  if ((valid & 3) != 0) {                                    // ragged tail that is not 16-byte granular: plain stores
+    if (active)
+      for (int j = 0; j < valid; ++j) dst[j] = __uint_as_float(r[j]) * alpha;
+    return;
+  }
+#pragma unroll
+  for (int pass = 0; pass < 4; ++pass) {
+    if ((lane >> 3) == pass) {
+      float4* slot = reinterpret_cast<float4*>(stage + (lane & 7) * 128);
+#pragma unroll
+      for (int j = 0; j < 32; j += 4)
+        slot[j >> 2] = make_float4(__uint_as_float(r[j]) * alpha, __uint_as_float(r[j + 1]) * alpha,
+                                   __uint_as_float(r[j + 2]) * alpha, __uint_as_float(r[j + 3]) * alpha);
+      ptx::fence_proxy_async_smem();
+      if (active) ptx::bulk_store(dst, slot, (uint32_t)valid * 4u);
+      ptx::bulk_commit();
+      ptx::bulk_wait_read();                                  // the slot may be overwritten by the next pass / chunk
+    }
+    __syncwarp();
   }
 }
 
@@ -476,13 +530,18 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
         }
         uint32_t xwk = 0u;
         if constexpr (EPI == EPI_BCE) xwk = xw[k];
-        epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
+        if constexpr (EPI == EPI_SCATTER_F32)
+          scatter_chunk(e, r, row, it.n0 + c * 32, args.M, args.N,
+                        smem + kStages * kStageBytes + 256 + (warp - 2) * kScatterStageBytes, lane);
+        else
+          epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
       }
       if (!arrived) {
         ptx::tc_fence_before();
         ptx::mbar_arrive(&tempty_bar[acc]);
       }
     }
+    if constexpr (EPI == EPI_SCATTER_F32) ptx::bulk_wait_all();   // all row segments have left before the CTA exits
     if constexpr (EPI == EPI_BCE) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);

@@ -269,6 +269,99 @@ void adam_dual(const AdamArgs& a, cudaStream_t s) {
   adam_dual_kernel<<<(int)((n4 + 255) / 256), 256, 0, s>>>(a);
 }
 
+// ------------------------------------------------------------------ data parallel: sharded reduce + dual Adam
+// Each rank owns one contiguous slice of the flat parameter space.  The wgrad GEMMs of all ranks have stored their
+// partial gradients into this rank's staging buffer stage[src][slice] (EPI_SCATTER_F32 / push_range below).  This
+// kernel finishes the reduce-scatter (sum over src), applies both TF1 Adams on the owned slice only (optimiser
+// state traffic / world) and all-gathers the result by storing the new bf16 shadow weights into every rank's
+// shadow buffer over NVLink.
+__global__ void __launch_bounds__(256) adam_dual_sharded_kernel(AdamShardArgs a) {
+  const long long loc = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;     // position in the owned slice
+  if (loc >= a.slice_len) return;
+  // owned granules are dealt round-robin over the ranks: local granule loc >> gs is flat granule (that * world + rank)
+  const long long i4 = ((((loc >> a.gran_shift) * a.world) + a.rank) << a.gran_shift) + (loc & ((1LL << a.gran_shift) - 1));
+  if (i4 >= a.n_total) return;
+  float4 g1 = make_float4(0.f, 0.f, 0.f, 0.f), g2 = g1;
+  const bool both = i4 < a.n_both;
+  for (int s = 0; s < a.world; ++s) {
+    const float4 t = *reinterpret_cast<const float4*>(a.stage1 + (long long)s * a.slice_len + loc);
+    g1.x += t.x; g1.y += t.y; g1.z += t.z; g1.w += t.w;
+  }
+  if (both)
+    for (int s = 0; s < a.world; ++s) {
+      const float4 t = *reinterpret_cast<const float4*>(a.stage2 + (long long)s * a.slice_len + loc);
+      g2.x += t.x; g2.y += t.y; g2.z += t.z; g2.w += t.w;
+    }
+  *reinterpret_cast<float4*>(a.g1 + i4) = g1;
+  if (both) *reinterpret_cast<float4*>(a.g2 + i4) = g2;
+  if (!a.apply) return;
+  float4 p = *reinterpret_cast<const float4*>(a.p + i4);
+  float pv[4] = {p.x, p.y, p.z, p.w};
+  {
+    float4 m = *reinterpret_cast<const float4*>(a.m1 + i4), v = *reinterpret_cast<const float4*>(a.v1 + i4);
+    pv[0] -= adam_one(g1.x, m.x, v.x, a.lr_t1, a.beta1, a.beta2, a.eps);
+    pv[1] -= adam_one(g1.y, m.y, v.y, a.lr_t1, a.beta1, a.beta2, a.eps);
+    pv[2] -= adam_one(g1.z, m.z, v.z, a.lr_t1, a.beta1, a.beta2, a.eps);
+    pv[3] -= adam_one(g1.w, m.w, v.w, a.lr_t1, a.beta1, a.beta2, a.eps);
+    *reinterpret_cast<float4*>(a.m1 + i4) = m;
+    *reinterpret_cast<float4*>(a.v1 + i4) = v;
+  }
+  if (both) {
+    float4 m = *reinterpret_cast<const float4*>(a.m2 + i4), v = *reinterpret_cast<const float4*>(a.v2 + i4);
+    pv[0] -= adam_one(g2.x, m.x, v.x, a.lr_t2, a.beta1, a.beta2, a.eps);
+    pv[1] -= adam_one(g2.y, m.y, v.y, a.lr_t2, a.beta1, a.beta2, a.eps);
+    pv[2] -= adam_one(g2.z, m.z, v.z, a.lr_t2, a.beta1, a.beta2, a.eps);
+    pv[3] -= adam_one(g2.w, m.w, v.w, a.lr_t2, a.beta1, a.beta2, a.eps);
+    *reinterpret_cast<float4*>(a.m2 + i4) = m;
+    *reinterpret_cast<float4*>(a.v2 + i4) = v;
+  }
+  *reinterpret_cast<float4*>(a.p + i4) = make_float4(pv[0], pv[1], pv[2], pv[3]);
+  const uint32_t h0 = ptx::pack_bf16(pv[0], pv[1]), h1 = ptx::pack_bf16(pv[2], pv[3]);
+  const uint2 hv = make_uint2(h0, h1);
+  uint2 lv = make_uint2(0u, 0u);
+  const bool split = a.w_lo[0] != nullptr;
+  if (split) {
+    lv.x = ptx::pack_bf16(pv[0] - ptx::bf16_lo(h0), pv[1] - ptx::bf16_hi(h0));
+    lv.y = ptx::pack_bf16(pv[2] - ptx::bf16_lo(h1), pv[3] - ptx::bf16_hi(h1));
+  }
+  for (int r = 0; r < a.world; ++r) {           // r == rank is the local copy; the others are peer stores
+    *reinterpret_cast<uint2*>(a.w_hi[r] + i4) = hv;
+    if (split) *reinterpret_cast<uint2*>(a.w_lo[r] + i4) = lv;
+  }
+}
+void adam_dual_sharded(const AdamShardArgs& a, cudaStream_t s) {
+  const long long n4 = ((long long)a.slice_len + 3) / 4;
+  if (n4 <= 0) return;
+  adam_dual_sharded_kernel<<<(int)((n4 + 255) / 256), 256, 0, s>>>(a);
+}
+
+// local partial gradients of the small layers (accumulated with split-K red.add) -> the owners' staging slots
+__global__ void __launch_bounds__(256) push_range_kernel(PushArgs a) {
+  const long long i4 = a.begin + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= a.end) return;
+  const long long q = i4 >> a.gran_shift;
+  const int o = (int)(q % a.world);
+  float* dst = a.peer[o] + ((long long)a.rank * a.slice_len + ((q / a.world) << a.gran_shift) + (i4 & ((1LL << a.gran_shift) - 1)));
+  *reinterpret_cast<float4*>(dst) = *reinterpret_cast<const float4*>(a.src + i4);
+}
+
+// zero every granule this rank does not own: a following all-reduce(sum) then assembles the full buffer on every rank
+// (host accessors of sharded state: magic_get_param / get_slot / get_grad)
+__global__ void __launch_bounds__(256) mask_unowned_kernel(float* buf, long long n, int world, int rank, int gran_shift) {
+  const long long i4 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= n) return;
+  if ((int)((i4 >> gran_shift) % world) != rank) *reinterpret_cast<float4*>(buf + i4) = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+void mask_unowned(float* buf, long long n, int world, int rank, int gran_shift, cudaStream_t s) {
+  const long long n4 = (n + 3) / 4;
+  mask_unowned_kernel<<<(int)((n4 + 255) / 256), 256, 0, s>>>(buf, n, world, rank, gran_shift);
+}
+void push_range(const PushArgs& a, cudaStream_t s) {
+  const long long n4 = (a.end - a.begin + 3) / 4;
+  if (n4 <= 0) return;
+  push_range_kernel<<<(int)((n4 + 255) / 256), 256, 0, s>>>(a);
+}
+
 __global__ void __launch_bounds__(256) shadow_refresh_kernel(const float* __restrict__ p, __nv_bfloat16* hi,
                                                              __nv_bfloat16* lo, long long n) {
   const long long i4 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -646,6 +739,9 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(latent_metric_kernel);
   MAGIC_MAX_CARVEOUT(latent_backward_kernel);
   MAGIC_MAX_CARVEOUT(adam_dual_kernel);
+  MAGIC_MAX_CARVEOUT(adam_dual_sharded_kernel);
+  MAGIC_MAX_CARVEOUT(push_range_kernel);
+  MAGIC_MAX_CARVEOUT(mask_unowned_kernel);
   MAGIC_MAX_CARVEOUT(shadow_refresh_kernel);
   MAGIC_MAX_CARVEOUT(deinterleave_kernel);
   MAGIC_MAX_CARVEOUT(planar_u8_kernel);

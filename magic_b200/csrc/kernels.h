@@ -55,6 +55,30 @@ struct AdamArgs {
   float beta1, beta2, eps;
 };
 void adam_dual(const AdamArgs& a, cudaStream_t s);
+// Data parallel: sharded reduce + dual Adam + shadow all-gather over peer memory.
+constexpr int kMaxRanks = 8;
+struct AdamShardArgs {
+  long long n_total;              // flat parameter space [0, n_total)
+  long long n_both;               // elements [0, n_both) are trained by both optimisers
+  int world, rank, slice_len;     // slice_len = owned elements per rank (granules dealt round-robin, see EpiArgs)
+  int gran_shift;
+  const float* stage1; const float* stage2;   // local staging [world][slice_len]: every rank's partial g1 / g2 of this slice
+  float *p, *m1, *v1, *m2, *v2;   // flat buffers (only the owned range is touched)
+  float *g1, *g2;                 // reduced gradients, written at the owned indices (diagnostics / parity)
+  __nv_bfloat16* w_hi[kMaxRanks]; // shadow weights of every rank (peer pointers; [rank] is local)
+  __nv_bfloat16* w_lo[kMaxRanks]; // null in the bf16 mode
+  float lr_t1, lr_t2, beta1, beta2, eps;
+  int apply;                      // 0: reduce only (magic_step_grads_only)
+};
+void adam_dual_sharded(const AdamShardArgs& a, cudaStream_t s);
+struct PushArgs {
+  const float* src;               // local flat gradient buffer
+  float* peer[kMaxRanks];         // staging base of every rank
+  long long begin, end;           // flat range, multiples of 4
+  int slice_len, rank, world, gran_shift;
+};
+void push_range(const PushArgs& a, cudaStream_t s);
+void mask_unowned(float* buf, long long n, int world, int rank, int gran_shift, cudaStream_t s);
 void shadow_refresh(const float* p, __nv_bfloat16* hi, __nv_bfloat16* lo, long long n, cudaStream_t s);
 
 // X [B, 3*D] fp32 channel-interleaved (8c/vae.py:166, ch0 lock, ch1 rot, ch2 key) -> planes bf16 [3B, ld]

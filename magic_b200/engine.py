@@ -310,3 +310,13 @@ class Engine:
         dist.broadcast(ident, src=0)
         raw = bytes(ident.cpu().numpy().tobytes())
         check(self.lib.magic_comm_init(self._h, C.c_char_p(raw)))
+        # peer-memory handles for the fused reduce-scatter / all-gather (include/magic_b200.h: magic_comm_export_peer)
+        blob = (C.c_char * 256)()
+        check(self.lib.magic_comm_export_peer(self._h, blob))
+        mine = torch.frombuffer(bytearray(blob.raw), dtype=torch.uint8).clone()
+        if dist.get_backend() == "nccl":
+            mine = mine.to(self.device)
+        allb = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+        dist.all_gather(allb, mine)
+        joined = b"".join(bytes(t.cpu().numpy().tobytes()) for t in allb)
+        check(self.lib.magic_comm_import_peers(self._h, C.c_char_p(joined)))

@@ -51,7 +51,13 @@ def _worker(rank, world, port, kw, precision, q):
         for _ in range(3):
             eng.load_interleaved(X)
             eng.step(labels=y[sl].to(torch.float32), eps3=eps[:, sl].to(torch.float32))
+        # a 4th evaluation on the updated weights: checks the bf16 shadows every rank received from the owners
+        eng.load_interleaved(X)
+        l4, _ = eng.step(labels=y[sl].to(torch.float32), eps3=eps[:, sl].to(torch.float32), apply=False)
+        res["losses4"] = l4.cpu().numpy().copy()
         res["p"] = eng.get_param("encoder_h1_weights")
+        res["p_out"] = eng.get_param("decoder_out_mean_weights")
+        res["fused"] = os.environ.get("MAGIC_DP_MODE", "fused")
         eng.sync()
         q.put((rank, res))
         eng.close()
@@ -95,3 +101,16 @@ def test_two_gpu_step_matches_full_batch_oracle(name, kw):
         for k, v in r["g2"].items():
             assert rel_l2(v, g2[k].numpy()) <= (2e-2 if ocfg.reciprocal else tol), (rank, 2, k)
     np.testing.assert_array_equal(results[0]["p"], results[1]["p"])       # replicas stay bit-identical
+    # three optimiser steps, then the losses of a 4th forward, against the oracle stepping on the full batch
+    p0 = {k: v.clone() for k, v in state.params.items()}
+    for _ in range(3):
+        state.step(xl, xr, xk, y, eps)
+    out4 = orc.forward(ocfg, state.params, xl, xr, xk, y, eps)
+    for rank in range(world):
+        for i, k in enumerate(orc.LOSS_KEYS):
+            t = 2e-2 if (ocfg.reciprocal and k == "training_loss") else 2e-3
+            assert abs(results[rank]["losses4"][i] - float(out4[k])) <= t * abs(float(out4[k])), (rank, k)
+    for name, key in (("encoder_h1_weights", "p"), ("decoder_out_mean_weights", "p_out")):
+        upd_ref = (state.params[name] - p0[name]).numpy()
+        upd = results[0][key].astype(np.float64) - p0[name].numpy()
+        assert rel_l2(upd, upd_ref) <= 0.05, name
