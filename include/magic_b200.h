@@ -92,6 +92,10 @@ int magic_set_step(magic_handle* h, int64_t t);
  * ch2 key; 8c/vae.py:166-179, 8c/overlap_input.py:195).  Each loader converts into the handle's planar bf16
  * operand buffer (pixels are {0,1}: exact). */
 int magic_load_interleaved(magic_handle* h, const float* d_x);                       /* [B, 3*D] */
+/* Same layout as uint8: any non-zero byte is a set pixel.  The reference's feed_dict converts whatever array it is
+ * given to the placeholder dtype, so a uint8/bool X is a legal argument of the same partial_fit (8c/vae.py:395); it
+ * moves a quarter of the bytes over PCIe. */
+int magic_load_interleaved_u8(magic_handle* h, const uint8_t* d_x);                  /* [B, 3*D] */
 int magic_load_planar_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* d_rot, const uint8_t* d_key);
 /* Replaces overlap_input.inputs() (8c/overlap_input.py:76-124): synthesises B shape pairs + rotated lock +
  * max-overlap labels on the device for (seed, step, rank).  Labels go to an internal buffer used when
@@ -116,6 +120,9 @@ int magic_step_grads_only(magic_handle* h, const float* d_labels, const float* d
  * synchronise.  h_eps3 and h_distance may be NULL. */
 int magic_partial_fit_host(magic_handle* h, const float* h_x, const float* h_labels, const float* h_eps3,
                            float h_losses5[5], float* h_distance);
+
+int magic_partial_fit_host_u8(magic_handle* h, const uint8_t* h_x, const float* h_labels, const float* h_eps3,
+                              float h_losses5[5], float* h_distance);
 
 /* get_predictions / transform / reconstruct (8c/vae.py:407-434) on the loaded batch:
  *   MAGIC_FWD_DISTANCE -> d_out[B] (needs d_labels = NULL; sampled z: pass d_eps3 or NULL for RNG)

@@ -56,6 +56,8 @@ SIGNATURES = {
     "magic_get_step": (C.c_int, [_VP, C.POINTER(_I64)]),
     "magic_set_step": (C.c_int, [_VP, _I64]),
     "magic_load_interleaved": (C.c_int, [_VP, _VP]),
+    "magic_load_interleaved_u8": (C.c_int, [_VP, _VP]),
+    "magic_partial_fit_host_u8": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     "magic_load_planar_u8": (C.c_int, [_VP, _VP, _VP, _VP]),
     "magic_generate_batch": (C.c_int, [_VP, _U64, _U64]),
     "magic_export_batch": (C.c_int, [_VP, _VP, _VP]),

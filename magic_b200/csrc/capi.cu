@@ -127,6 +127,15 @@ int magic_set_step(magic_handle* h, int64_t t) {
   return 0;
 }
 
+int magic_load_interleaved_u8(magic_handle* h, const uint8_t* d_x) {
+  CHECK_HANDLE(h);
+  return done(h->eng.load_interleaved_u8(d_x));
+}
+int magic_partial_fit_host_u8(magic_handle* h, const uint8_t* h_x, const float* h_labels, const float* h_eps3,
+                              float h_losses5[5], float* h_distance) {
+  CHECK_HANDLE(h);
+  return done(h->eng.partial_fit_host(h_x, true, h_labels, h_eps3, h_losses5, h_distance));
+}
 int magic_load_interleaved(magic_handle* h, const float* d_x) {
   CHECK_HANDLE(h);
   return done(h->eng.load_interleaved(d_x));
@@ -160,7 +169,7 @@ int magic_step_grads_only(magic_handle* h, const float* d_labels, const float* d
 int magic_partial_fit_host(magic_handle* h, const float* h_x, const float* h_labels, const float* h_eps3,
                            float h_losses5[5], float* h_distance) {
   CHECK_HANDLE(h);
-  return done(h->eng.partial_fit_host(h_x, h_labels, h_eps3, h_losses5, h_distance));
+  return done(h->eng.partial_fit_host(h_x, false, h_labels, h_eps3, h_losses5, h_distance));
 }
 int magic_forward(magic_handle* h, int32_t what, const float* d_eps3, float* d_out) {
   CHECK_HANDLE(h);

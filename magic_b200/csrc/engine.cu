@@ -519,6 +519,20 @@ std::string Engine::load_interleaved(const float* d_x) {
   cur_ ^= 1;
   return "";
 }
+std::string Engine::load_interleaved_u8(const uint8_t* d_x) {
+  if (!d_x) return "load_interleaved_u8: null input";
+  InBuf& b = in_[cur_ ^ 1];
+  wait_ready(b);
+  prof_begin("input.deinterleave");
+  deinterleave_u8(d_x, B, D, b.X.hi, b.X.ld, stream);
+  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
+  prof_end();
+  MAGIC_CUDA(cudaGetLastError());
+  mark_consumed(b);
+  b.has_labels = false;
+  cur_ ^= 1;
+  return "";
+}
 std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uint8_t* k) {
   if (!l || !r || !k) return "load_planar_u8: null input";
   InBuf& b = in_[cur_ ^ 1];
@@ -801,17 +815,23 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   return "";
 }
 
-std::string Engine::partial_fit_host(const float* h_x, const float* h_labels, const float* h_eps3, float* h_losses5,
-                                     float* h_distance) {
+std::string Engine::partial_fit_host(const void* h_x, bool x_is_u8, const float* h_labels, const float* h_eps3,
+                                     float* h_losses5, float* h_distance) {
   if (!h_x || !h_labels || !h_losses5) return "partial_fit_host: null argument";
   const size_t nx = (size_t)B * 3 * D;
-  if (!stage_x_) MAGIC_TRY(alloc((void**)&stage_x_, sizeof(float) * nx));
+  const size_t xbytes = x_is_u8 ? nx : nx * sizeof(float);
+  if (stage_x_bytes_ < xbytes) {
+    if (stage_x_) { MAGIC_CUDA(cudaStreamSynchronize(stream)); cudaFree(stage_x_); stage_x_ = nullptr; }
+    MAGIC_TRY(alloc((void**)&stage_x_, xbytes));
+    stage_x_bytes_ = xbytes;
+  }
   if (!stage_labels_) MAGIC_TRY(alloc((void**)&stage_labels_, sizeof(float) * B));
   if (h_eps3 && !stage_eps_) MAGIC_TRY(alloc((void**)&stage_eps_, sizeof(float) * 3 * B * L));
-  MAGIC_CUDA(cudaMemcpyAsync(stage_x_, h_x, sizeof(float) * nx, cudaMemcpyHostToDevice, stream));
+  MAGIC_CUDA(cudaMemcpyAsync(stage_x_, h_x, xbytes, cudaMemcpyHostToDevice, stream));
   MAGIC_CUDA(cudaMemcpyAsync(stage_labels_, h_labels, sizeof(float) * B, cudaMemcpyHostToDevice, stream));
   if (h_eps3) MAGIC_CUDA(cudaMemcpyAsync(stage_eps_, h_eps3, sizeof(float) * 3 * B * L, cudaMemcpyHostToDevice, stream));
-  MAGIC_TRY(load_interleaved(stage_x_));
+  if (x_is_u8) MAGIC_TRY(load_interleaved_u8(static_cast<const uint8_t*>(stage_x_)));
+  else MAGIC_TRY(load_interleaved(static_cast<const float*>(stage_x_)));
   MAGIC_TRY(step(stage_labels_, h_eps3 ? stage_eps_ : nullptr, losses_dev_, nullptr, true));
   MAGIC_CUDA(cudaMemcpyAsync(h_losses5, losses_dev_, sizeof(float) * 5, cudaMemcpyDeviceToHost, stream));
   if (h_distance) MAGIC_CUDA(cudaMemcpyAsync(h_distance, dist_, sizeof(float) * B, cudaMemcpyDeviceToHost, stream));

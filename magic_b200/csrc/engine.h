@@ -50,8 +50,9 @@ class Engine {
   std::string export_batch(float* d_x, float* d_labels);
   std::string export_rotation(int32_t* d_cs_sn);
   std::string step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply);
-  std::string partial_fit_host(const float* h_x, const float* h_labels, const float* h_eps3, float* h_losses5,
-                               float* h_distance);
+  std::string load_interleaved_u8(const uint8_t* d_x);
+  std::string partial_fit_host(const void* h_x, bool x_is_u8, const float* h_labels, const float* h_eps3,
+                               float* h_losses5, float* h_distance);
   std::string forward(int what, const float* d_eps3, float* d_out);
   std::string decode(const float* d_z, float* d_out);
   std::string comm_init(const void* uid);
@@ -139,7 +140,8 @@ class Engine {
   float* ws_ = nullptr; long long ws_ld_ = 0;            // split-K workspace
   float* statbuf_ = nullptr;        // [8 sums | 2L colsq | L colS]
   float *g_row_ = nullptr, *dist_ = nullptr, *losses_dev_ = nullptr;
-  float *stage_x_ = nullptr, *stage_labels_ = nullptr, *stage_eps_ = nullptr;   // partial_fit_host staging
+  void* stage_x_ = nullptr; size_t stage_x_bytes_ = 0;                            // partial_fit_host staging
+  float *stage_labels_ = nullptr, *stage_eps_ = nullptr;
   const float* labels_ext_ = nullptr;
   bool have_labels_ext_ = false;
 

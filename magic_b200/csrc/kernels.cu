@@ -427,6 +427,43 @@ void deinterleave_f32(const float* x, int B, int D, __nv_bfloat16* planes, long 
   deinterleave_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(x, B, D, planes, ld);
 }
 
+// X [B, 3*D] uint8 channel-interleaved ({0,1} or {0,255}: any non-zero byte is a set pixel) -> bf16 planes
+// (the compact host feed: 1/4 of the fp32 bytes over PCIe).  Each thread converts 8 pixels (24 bytes).
+__global__ void __launch_bounds__(256) deinterleave_u8_kernel(const uint8_t* __restrict__ x, int B, int D,
+                                                              __nv_bfloat16* planes, long long ld) {
+  const int per_row = (int)(ld / 8);
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * per_row) return;
+  const int i = (int)(idx / per_row);
+  const int p0 = (int)(idx % per_row) * 8;
+  uint32_t lock[4] = {0, 0, 0, 0}, rot[4] = {0, 0, 0, 0}, key[4] = {0, 0, 0, 0};
+  if (p0 + 8 <= D) {
+    const uint2* src = reinterpret_cast<const uint2*>(x + ((long long)i * D + p0) * 3);   // 24-byte groups: 8-byte aligned
+    uint8_t b[24];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      const uint2 v = src[q];
+      *reinterpret_cast<uint2*>(b + 8 * q) = v;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const uint32_t one = (e & 1) ? 0x3F800000u : 0x00003F80u;
+      if (b[3 * e]) lock[e >> 1] |= one;
+      if (b[3 * e + 1]) rot[e >> 1] |= one;
+      if (b[3 * e + 2]) key[e >> 1] |= one;
+    }
+  } else if (p0 == D) {
+    lock[0] = rot[0] = key[0] = 0x00003F80u;   // bias column (1.0), then zero pad
+  }
+  *reinterpret_cast<uint4*>(planes + (long long)i * ld + p0) = make_uint4(rot[0], rot[1], rot[2], rot[3]);
+  *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + p0) = make_uint4(lock[0], lock[1], lock[2], lock[3]);
+  *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + p0) = make_uint4(key[0], key[1], key[2], key[3]);
+}
+void deinterleave_u8(const uint8_t* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s) {
+  const long long n = (long long)B * (ld / 8);
+  deinterleave_u8_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(x, B, D, planes, ld);
+}
+
 __global__ void __launch_bounds__(256) planar_u8_kernel(const uint8_t* __restrict__ lock, const uint8_t* __restrict__ rot,
                                                         const uint8_t* __restrict__ key, int B, int D,
                                                         __nv_bfloat16* planes, long long ld) {
@@ -744,6 +781,7 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(mask_unowned_kernel);
   MAGIC_MAX_CARVEOUT(shadow_refresh_kernel);
   MAGIC_MAX_CARVEOUT(deinterleave_kernel);
+  MAGIC_MAX_CARVEOUT(deinterleave_u8_kernel);
   MAGIC_MAX_CARVEOUT(planar_u8_kernel);
   MAGIC_MAX_CARVEOUT(planes_to_interleaved_kernel);
   MAGIC_MAX_CARVEOUT(generate_pairs_kernel);

@@ -84,6 +84,7 @@ void shadow_refresh(const float* p, __nv_bfloat16* hi, __nv_bfloat16* lo, long l
 // X [B, 3*D] fp32 channel-interleaved (8c/vae.py:166, ch0 lock, ch1 rot, ch2 key) -> planes bf16 [3B, ld]
 // rows [rot; lock; key], 1.0 at col D, zeros after.
 void deinterleave_f32(const float* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s);
+void deinterleave_u8(const uint8_t* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s);
 void planar_u8(const uint8_t* lock, const uint8_t* rot, const uint8_t* key, int B, int D, __nv_bfloat16* planes,
                long long ld, cudaStream_t s);
 void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B, int D, float* x, cudaStream_t s);

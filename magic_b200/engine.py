@@ -211,9 +211,17 @@ class Engine:
         return t
 
     def load_interleaved(self, X) -> None:
-        """X: [B, 3*D] fp32, channel-interleaved as main.py feeds it (8c/vae.py:166)."""
-        t = self._dev_f32(X, (self.B, 3 * self.D))
-        check(self.lib.magic_load_interleaved(self._h, C.c_void_p(t.data_ptr())))
+        """X: [B, 3*D], channel-interleaved as main.py feeds it (8c/vae.py:166); float (any width) or uint8/bool."""
+        probe = X if isinstance(X, torch.Tensor) else np.asarray(X)
+        if probe.dtype in (torch.uint8, torch.bool, np.uint8, np.bool_):
+            t = probe if isinstance(probe, torch.Tensor) else torch.as_tensor(probe)
+            t = t.to(device=self.device, non_blocking=True).contiguous().view(torch.uint8)
+            if tuple(t.shape) != (self.B, 3 * self.D):
+                raise ValueError("expected shape %s, got %s" % ((self.B, 3 * self.D), tuple(t.shape)))
+            check(self.lib.magic_load_interleaved_u8(self._h, C.c_void_p(t.data_ptr())))
+        else:
+            t = self._dev_f32(X, (self.B, 3 * self.D))
+            check(self.lib.magic_load_interleaved(self._h, C.c_void_p(t.data_ptr())))
         self._keep = t
 
     def load_planar_u8(self, lock: torch.Tensor, rot: torch.Tensor, key: torch.Tensor) -> None:
@@ -254,14 +262,16 @@ class Engine:
     def partial_fit_host(self, X: np.ndarray, labels: np.ndarray, eps3: Optional[np.ndarray] = None,
                          want_distance: bool = False):
         """Host-buffer partial_fit through magic_partial_fit_host (copies + step + sync)."""
-        X = np.ascontiguousarray(X, dtype=np.float32)
+        u8 = X.dtype in (np.uint8, np.bool_)
+        X = np.ascontiguousarray(X) if u8 else np.ascontiguousarray(X, dtype=np.float32)
         labels = np.ascontiguousarray(labels, dtype=np.float32)
         if X.shape != (self.B, 3 * self.D) or labels.shape != (self.B,):
             raise ValueError("partial_fit expects X[%d,%d] and overlap_areas[%d]" % (self.B, 3 * self.D, self.B))
         losses = np.empty(5, dtype=np.float32)
         dist = np.empty(self.B, dtype=np.float32) if want_distance else None
         e = None if eps3 is None else np.ascontiguousarray(eps3, dtype=np.float32)
-        check(self.lib.magic_partial_fit_host(
+        fn = self.lib.magic_partial_fit_host_u8 if u8 else self.lib.magic_partial_fit_host
+        check(fn(
             self._h, X.ctypes.data_as(C.c_void_p), labels.ctypes.data_as(C.c_void_p),
             None if e is None else e.ctypes.data_as(C.c_void_p), losses.ctypes.data_as(C.c_void_p),
             None if dist is None else dist.ctypes.data_as(C.c_void_p)))

@@ -127,3 +127,23 @@ def test_host_partial_fit_matches_device_path():
         assert abs(losses[i] - float(out[k])) <= 1e-4 * abs(float(out[k])), k
     assert rel_l2(dist, out["distance"].numpy()) <= 1e-4
     eng.close()
+
+
+def test_uint8_feed_equals_float_feed():
+    """A uint8 / bool X is a legal argument of the same partial_fit (feed_dict casts to the placeholder dtype,
+    8c/vae.py:395): same step, a quarter of the PCIe bytes."""
+    ocfg = oracle_config(latent=20, **MINI)
+    _, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, 64, "fp32", seed=0)
+    _, eng2, _ = make_pair(ocfg, 64, "fp32", seed=0)
+    X = orc.interleave(xl, xr, xk).to(torch.float32).numpy()
+    yn, en = y.numpy().astype(np.float32), eps.numpy().astype(np.float32)
+    la, da = eng.partial_fit_host(X, yn, en, True)
+    lb, db = eng2.partial_fit_host((X * 255).astype(np.uint8), yn, en, True)
+    np.testing.assert_allclose(la, lb, rtol=1e-5)
+    np.testing.assert_allclose(da, db, rtol=1e-4, atol=1e-7)
+    eng2.load_interleaved(torch.as_tensor(X > 0))                 # bool tensor through the device loader
+    eng.load_interleaved(X)
+    l3, _ = eng2.step(labels=yn, eps3=en, apply=False)
+    l4, _ = eng.step(labels=yn, eps3=en, apply=False)
+    np.testing.assert_allclose(l3.cpu().numpy(), l4.cpu().numpy(), rtol=1e-5)
+    eng.close(); eng2.close()
