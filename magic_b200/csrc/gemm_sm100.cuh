@@ -89,13 +89,16 @@ struct GemmArgs {
   int nseg, ngroups, splitk;
   int tiles_m, tiles_n;
   int m_fastest;     // tile order: consecutive work items walk M first (B is the large operand) or N first
+  int cluster_m;     // CTAs per cluster along M (1, 2 or 4): they share the N tile and receive B by TMA multicast
 };
 
 struct WorkItem {
   int g, m0, n0, kb0, kb1;
 };
 
-__device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w) {
+// Work items are per CLUSTER: `tiles_m` counts cluster rows (cluster_m M-tiles each); CTA `crank` takes M-tile
+// mt * cluster_m + crank of the item.  With cluster_m == 1 this is the plain per-CTA decode.
+__device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int crank = 0) {
   WorkItem it;
   int nt, mt, t;
   if (a.m_fastest) {
@@ -105,6 +108,7 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w) {
     nt = w % a.tiles_n; t = w / a.tiles_n;
     mt = t % a.tiles_m; t /= a.tiles_m;
   }
+  mt = mt * a.cluster_m + crank;
   it.g = t % a.ngroups;
   int ks = t / a.ngroups;
   int total_kb = a.nseg * a.kblocks;
@@ -160,6 +164,70 @@ __device__ __forceinline__ void softplus_sigmoid(float b, float& sp, float& sg) 
     sp = fmaf(t, p, fmaxf(b, 0.f));
     float r = __fdividef(1.f, 1.f + t);
     sg = b >= 0.f ? r : t * r;
+  }
+}
+
+// EPI_BCE for one 32-column chunk of one row.
+// logits a -> loss += softplus(a) - x*a ; dA = sigmoid(a) - x      (x in {0,1}; 8c/vae.py:260-263)
+// With s = a for x = 0 and s = -a for x = 1:  loss = softplus(s),  dA = sigmoid(s) carrying the sign of (1 - 2x).
+// `xw` holds this row's 32 target bits (bit j <-> column col0 + j).  FULL: the whole chunk is inside the matrix, so
+// no per-element column test is compiled in (it cost ~8 of 32 instructions per element, ncu r01f).
+template <bool PRECISE, bool FULL>
+__device__ __forceinline__ void bce_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int N,
+                                          float& loss_acc, uint32_t xw) {
+  uint32_t hi[16], lo[16];
+  float acc = 0.f;
+  const int valid = FULL ? 32 : N - col0;
+#pragma unroll
+  for (int j = 0; j < 32; j += 2) {
+    float d[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const uint32_t sign = (xw << (31 - (j + q))) & 0x80000000u;
+      const float sv = __uint_as_float(r[j + q] ^ sign);
+      float sp, sg;
+      if constexpr (PRECISE) {
+        softplus_sigmoid<true>(sv, sp, sg);
+      } else {
+        float t;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fabsf(sv) * -1.4426950408889634f));
+        float rr;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rr) : "f"(1.f + t));
+        // sigmoid(s) = 0.5 + sgn(s) * (0.5 - t/(1+t))
+        const float h = fmaf(-t, rr, 0.5f);
+        sg = 0.5f + __uint_as_float(__float_as_uint(h) ^ (__float_as_uint(sv) & 0x80000000u));
+        // log1p(t) = t * P(t): degree-3 minimax fit of log1p(t)/t on (0,1], max relative error 4.8e-4 (the loss is a
+        // reported scalar; the gradient path uses sg only)
+        float p = fmaf(t, -0.0762659232f, 0.256918443f);
+        p = fmaf(t, p, -0.487505179f);
+        p = fmaf(t, p, 0.999668402f);
+        sp = fmaf(t, p, fmaxf(sv, 0.f));
+      }
+      const float dv = __uint_as_float(__float_as_uint(sg) ^ sign);
+      if constexpr (FULL) {
+        d[q] = dv;
+        acc += sp;
+      } else {
+        const bool in = j + q < valid;
+        d[q] = in ? dv : 0.f;
+        acc += in ? sp : 0.f;
+      }
+    }
+    const uint32_t h2 = ptx::pack_bf16(d[0], d[1]);
+    hi[j >> 1] = h2;
+    if constexpr (PRECISE) lo[j >> 1] = ptx::pack_bf16(d[0] - ptx::bf16_lo(h2), d[1] - ptx::bf16_hi(h2));
+  }
+  loss_acc += acc;
+  uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+  if constexpr (PRECISE) {
+    if (e.out_lo) {
+      uint4* ol =
+          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+    }
   }
 }
 
@@ -268,58 +336,8 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
       for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
     }
   } else if constexpr (EPI == EPI_BCE) {
-    // logits a -> loss += softplus(a) - x*a ; dA = sigmoid(a) - x      (x in {0,1}; 8c/vae.py:260-263)
-    // With s = a for x = 0 and s = -a for x = 1:  loss = softplus(s),  dA = sigmoid(s) with the sign of (1 - 2x).
-    // `xw` holds this row's 32 target bits for the chunk (bit j <-> column col0 + j).
-        uint32_t hi[16], lo[16];
-    float acc = 0.f;
-    const bool full = col0 + 32 <= N;
-#pragma unroll
-    for (int j = 0; j < 32; j += 2) {
-      float d[2];
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const uint32_t sign = (xw << (31 - (j + q))) & 0x80000000u;
-        const float sv = __uint_as_float(r[j + q] ^ sign);
-        float sp, sg;
-        if constexpr (PRECISE) {
-          softplus_sigmoid<true>(sv, sp, sg);
-        } else {
-          float t;
-          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fabsf(sv) * -1.4426950408889634f));
-          float rr;
-          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rr) : "f"(1.f + t));
-          // sigmoid(s) = 0.5 + sgn(s) * (0.5 - t/(1+t))
-          const float h = fmaf(-t, rr, 0.5f);
-          sg = 0.5f + __uint_as_float(__float_as_uint(h) ^ (__float_as_uint(sv) & 0x80000000u));
-          // log1p(t) = t * P(t), degree-5 fit of log1p(t)/t on (0,1], max relative error 8.5e-6
-          float p = fmaf(t, -0.023868885f, 0.10122161f);
-          p = fmaf(t, p, -0.21004808f);
-          p = fmaf(t, p, 0.32520646f);
-          p = fmaf(t, p, -0.49936134f);
-          p = fmaf(t, p, 0.9999916f);
-          sp = fmaf(t, p, fmaxf(sv, 0.f));
-        }
-        const bool in = full || (col0 + j + q < N);
-        d[q] = in ? __uint_as_float(__float_as_uint(sg) ^ sign) : 0.f;
-        acc += in ? sp : 0.f;
-      }
-      const uint32_t h2 = ptx::pack_bf16(d[0], d[1]);
-      hi[j >> 1] = h2;
-      if constexpr (PRECISE) lo[j >> 1] = ptx::pack_bf16(d[0] - ptx::bf16_lo(h2), d[1] - ptx::bf16_hi(h2));
-    }
-    loss_acc += acc;
-    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
-    if constexpr (PRECISE) {
-      if (e.out_lo) {
-        uint4* ol =
-            reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
-      }
-    }
+    if (col0 + 32 <= N) bce_chunk<PRECISE, true>(e, r, row, col0, N, loss_acc, xw);
+    else bce_chunk<PRECISE, false>(e, r, row, col0, N, loss_acc, xw);
   }
 }
 
@@ -396,6 +414,10 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_work = args.tiles_m * args.tiles_n * args.ngroups * args.splitk;
+  const int CM = args.cluster_m;
+  const int crank = CM > 1 ? (int)ptx::cluster_ctarank() : 0;
+  const int work0 = (int)blockIdx.x / CM, work_stride = (int)gridDim.x / CM;   // this cluster's first item / number of clusters
+  const uint16_t cmask = (uint16_t)((1u << CM) - 1u);
 
   if (warp == 0 && lane == 0) {
     for (int g = 0; g < args.ngroups; ++g)
@@ -405,7 +427,7 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
       }
     for (int i = 0; i < kStages; ++i) {
       ptx::mbar_init(&full_bar[i], 1);
-      ptx::mbar_init(&empty_bar[i], 1);
+      ptx::mbar_init(&empty_bar[i], CM);   // one arrival per CTA of the cluster (multicast commit)
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
@@ -417,7 +439,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (CM > 1) ptx::cluster_sync();       // barriers of every CTA are initialised before anybody multicasts into them
+  else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -425,8 +448,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
     // ------------------------------------------------------------ TMA producer (one thread)
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-        const WorkItem it = decode_work(args, w);
+      for (int w = work0; w < total_work; w += work_stride) {
+        const WorkItem it = decode_work(args, w, crank);
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           const int seg = kb / args.kblocks;
           const int k0 = (kb - seg * args.kblocks) * kBlockK;
@@ -445,10 +468,16 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
           }
           if constexpr (!B_MN) {
             ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);              // box {64 k, 256 n}
-          } else {
+          } else if (CM == 1) {
 #pragma unroll
             for (int i = 0; i < kBlockN / 64; ++i)                               // boxes {64 n, 64 k}
               ptx::tma_load_2d(tb, &full_bar[stage], sb + i * kAtomBytes, it.n0 + 64 * i, k0);
+          } else {
+            // the cluster shares this B tile: each CTA fetches 1/CM of the boxes and multicasts them to all
+#pragma unroll
+            for (int i = 0; i < kBlockN / 64; ++i)
+              if ((i % CM) == crank)
+                ptx::tma_load_2d_multicast(tb, &full_bar[stage], sb + i * kAtomBytes, it.n0 + 64 * i, k0, cmask);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -464,8 +493,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
       constexpr uint32_t a_lbo = A_MN ? kAtomBytes : 0, b_lbo = B_MN ? kAtomBytes : 0;
       constexpr uint32_t a_kadv = A_MN ? kUmmaK * 128 : kUmmaK * 2, b_kadv = B_MN ? kUmmaK * 128 : kUmmaK * 2;
       uint32_t stage = 0, phase = 0, iter = 0;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
-        const WorkItem it = decode_work(args, w);
+      for (int w = work0; w < total_work; w += work_stride, ++iter) {
+        const WorkItem it = decode_work(args, w, crank);
         const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
         ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
@@ -481,7 +510,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
             const uint64_t db = ptx::make_smem_desc_sw128(b_base + k * b_kadv, b_lbo, 1024);
             ptx::umma_bf16(d_tmem, da, db, idesc, (kb > it.kb0 || k > 0) ? 1u : 0u);
           }
-          ptx::umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
+          if (CM > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
+          else ptx::umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
         ptx::umma_commit(&tfull_bar[acc]);        // accumulator complete -> epilogue
@@ -497,8 +527,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
     const int grp = (warp - 2) >> 2;
     uint32_t iter = 0;
     float loss_acc = 0.f;
-    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
-      const WorkItem it = decode_work(args, w);
+    for (int w = work0; w < total_work; w += work_stride, ++iter) {
+      const WorkItem it = decode_work(args, w, crank);
       const EpiArgs& e = args.epi[it.g];
       const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
       const int row = it.m0 + q * 32 + lane;
@@ -550,7 +580,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if (CM > 1) ptx::cluster_sync();       // no CTA leaves while a peer may still multicast into it or arrive on its barriers
+  else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, kTmemCols);

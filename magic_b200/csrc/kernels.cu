@@ -679,30 +679,36 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
       if (lane == 0) bm[2][w] = word;
     }
   }
-  // ---- 3. label: only words where the lock has pixels; every lane sees the same ballot, so the counts stay
-  //         in registers without a reduction
+  // ---- 3. label: only words where the lock has pixels.  Each lane counts its own pixel (masked by its lock bit);
+  //         out-of-canvas sources read a bit of the zero padding behind the bitmap, so the loop is branch-free.
+  //         One warp reduction per rotation at the end.
   int cnt[kLabelRots];
 #pragma unroll
   for (int r = 0; r < kLabelRots; ++r) cnt[r] = 0;
+  const int zbit = nwords << 5;
   for (int w = warp; w < nwords; w += kGenThreads / 32) {
     const uint32_t lw = bm[0][w];
     if (lw == 0u) continue;
+    const uint32_t lb = (lw >> lane) & 1u;
     const int p0 = w * 32;
     const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
     int x = p0 - y0 * side + lane, y = y0;
     if (x >= side) { x -= side; ++y; }
-    const bool valid = p0 + lane < D;
 #pragma unroll
     for (int r = 0; r < kLabelRots / 2; ++r) {
-      const int sp = valid ? rotated_index(x, y, side, rot_cs(r), rot_sn(r)) : -1;
-      cnt[r] += __popc(__ballot_sync(0xffffffffu, bit_at(bm[1], sp) != 0u) & lw);
-      cnt[r + 4] += __popc(__ballot_sync(0xffffffffu, bit_at(bm[1], sp < 0 ? -1 : D - 1 - sp) != 0u) & lw);
+      const int sp = rotated_index(x, y, side, rot_cs(r), rot_sn(r));
+      const int spa = sp < 0 ? zbit : sp;
+      const int spb = sp < 0 ? zbit : D - 1 - sp;
+      cnt[r] += (int)((bm[1][spa >> 5] >> (spa & 31)) & lb);
+      cnt[r + 4] += (int)((bm[1][spb >> 5] >> (spb & 31)) & lb);
     }
   }
-  if (lane == 0) {
 #pragma unroll
-    for (int r = 0; r < kLabelRots; ++r)
-      if (cnt[r]) atomicAdd(&counts[r], cnt[r]);
+  for (int r = 0; r < kLabelRots; ++r) {
+    int v = cnt[r];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0 && v) atomicAdd(&counts[r], v);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
