@@ -105,6 +105,10 @@ int magic_export_batch(magic_handle* h, float* d_x /* [B,3*D] or NULL */, float*
 /* Q14 fixed-point (cos, sin) of the rotation the generator applied to each lock, [B,2] int32: with them the rotated
  * plane and the label are reproducible bit for bit from the exported lock/key planes (tests/test_generator.py). */
 int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn);
+/* The engine keeps two input batches in HBM (the loaded one and the one before it).  magic_swap_batch makes the
+ * previous one the loaded batch again without touching its data -- a held batch re-fed to partial_fit /
+ * get_predictions, as 8c/main.py:66-80 does with its test batch; bench.py alternates two resident batches with it. */
+int magic_swap_batch(magic_handle* h);
 
 /* TangoEncoder.partial_fit (8c/vae.py:379-405; 6-tuple variant 11a/vae.py:385-411) on the loaded batch:
  * forward, both backward passes at the pre-step weights, both Adam updates (W <- W - d1 - d2).

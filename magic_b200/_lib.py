@@ -62,6 +62,7 @@ SIGNATURES = {
     "magic_generate_batch": (C.c_int, [_VP, _U64, _U64]),
     "magic_export_batch": (C.c_int, [_VP, _VP, _VP]),
     "magic_export_rotation": (C.c_int, [_VP, _VP]),
+    "magic_swap_batch": (C.c_int, [_VP]),
     "magic_step": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "magic_step_grads_only": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "magic_partial_fit_host": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),

@@ -148,6 +148,10 @@ int magic_generate_batch(magic_handle* h, uint64_t seed, uint64_t step) {
   CHECK_HANDLE(h);
   return done(h->eng.generate(seed, step));
 }
+int magic_swap_batch(magic_handle* h) {
+  CHECK_HANDLE(h);
+  return done(h->eng.swap_batch());
+}
 int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn) {
   CHECK_HANDLE(h);
   return done(h->eng.export_rotation(d_cs_sn));

@@ -1,5 +1,7 @@
 // The training engine: parameter layout, activations, GEMM plans and the step (see engine.h).
 #include "engine.h"
+#include "launch.cuh"
+#include "ptx.cuh"
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -44,6 +46,7 @@ __global__ void xavier_kernel(float* w, long long ld, int nrows, int col0, int n
 
 // losses5 = [cost, training, rec, kl, def] from sums = [rec, kl, def, training]
 __global__ void finalize_losses_kernel(const float* sums, float* out) {
+  ptx::grid_dep_wait();
   if (threadIdx.x == 0) {
     out[0] = sums[0] + sums[1] + sums[2];
     out[1] = sums[3];
@@ -404,11 +407,19 @@ std::string Engine::build_plans() {
       e.out = dA_.hi; e.out_lo = dA_.lo; e.ld_out = dA_.ld;
       e.xbits = in_[v / 2].xbits; e.xb_ld = xb_ld_;             // packed lock plane (the reconstruction target)
       e.alpha = inv_bg; e.scalar = statbuf_ + 0; e.precise = prec;
+      if (const char* d = getenv("MAGIC_EPI_DBG")) e.dbg = atoi(d);   // timing experiments only: results are wrong
     } else {
       e.out = nullptr; e.ld_out = D;                             // output pointer patched per call
     }
     e.aux_split = 1 << 30;
     p.e[0] = e;
+    // MAGIC_CLUSTER_OUT=2|4: CTAs along M form a cluster and receive the weight tile by one multicast load.  Measured
+    // on B200 (profiles/r01g): no gain at cluster sizes <= 4 (L2 already merges the concurrent unicast requests) and
+    // only 33 clusters of 4 are co-resident (132 of 148 SMs), so the default stays 1.
+    {
+      const char* cm = getenv("MAGIC_CLUSTER_OUT");
+      p.cluster_m = cm ? atoi(cm) : 1;
+    }
     GemmPlan* dst = v == 0 ? &pl_out_bce_ : (v == 1 ? &pl_out_sig_ : &pl_out_bce_alt_);
     MAGIC_TRY(finish(p, dst, "fwd dec out"));
     if (v != 0) flops -= dst->flops;
@@ -516,6 +527,7 @@ std::string Engine::load_interleaved(const float* d_x) {
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
+  b.filled = true;
   cur_ ^= 1;
   return "";
 }
@@ -530,6 +542,7 @@ std::string Engine::load_interleaved_u8(const uint8_t* d_x) {
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
+  b.filled = true;
   cur_ ^= 1;
   return "";
 }
@@ -542,6 +555,7 @@ std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uin
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
+  b.filled = true;
   cur_ ^= 1;
   return "";
 }
@@ -563,6 +577,15 @@ std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
   MAGIC_CUDA(cudaEventRecord(b.ready, gen_stream_));
   b.ready_pending = true;
   b.has_labels = true;
+  b.filled = true;
+  cur_ ^= 1;
+  return "";
+}
+// Make the OTHER resident input buffer the loaded one again (it keeps the batch of the load/generate call before the
+// last one).  Lets a caller alternate between two batches that stay in HBM -- the reference re-feeds a held batch the
+// same way (8c/main.py:66-80 evaluates on a batch it dequeued earlier).
+std::string Engine::swap_batch() {
+  if (!in_[cur_ ^ 1].filled) return "swap_batch: the other input buffer has never been loaded";
   cur_ ^= 1;
   return "";
 }
@@ -772,7 +795,7 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   have_labels_ext_ = false;
   if (!err.empty()) return err;
   MAGIC_TRY(allreduce(statbuf_, 4, stream));   // loss scalars: local sums / Bg add up to the global means
-  if (d_losses5) { finalize_losses_kernel<<<1, 32, 0, stream>>>(statbuf_, d_losses5); ++launches; }
+  if (d_losses5) { launch_chain(finalize_losses_kernel, dim3(1), dim3(32), 0, stream, (const float*)statbuf_, d_losses5); ++launches; }
   if (d_distance) MAGIC_CUDA(cudaMemcpyAsync(d_distance, dist_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
   const double b1 = cfg.beta1, b2 = cfg.beta2;
   const double corr = sqrt(1.0 - pow(b2, (double)(t + 1))) / (1.0 - pow(b1, (double)(t + 1)));

@@ -1,6 +1,7 @@
 // Host-side planning and launch of the tcgen05 GEMM: tensor maps, split-K choice, finishing pass.
 #include "gemm.h"
 #include "kernels.h"
+#include "launch.cuh"
 #include <cstdio>
 #include <cstring>
 
@@ -14,6 +15,7 @@ static EncodeTiledFn g_encode = nullptr;
 // split-K partial sums (fp32 workspace) -> fused epilogue.  One thread per (row, 32-column chunk).
 template <int EPI>
 __global__ void gemm_finish_kernel(EpiArgs e, const float* __restrict__ ws, long long ws_ld, int M, int N) {
+  ptx::grid_dep_wait();
   const int chunks = (N + 31) >> 5;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int row = (int)(idx / chunks);
@@ -64,9 +66,10 @@ std::string gemm_init() {
   return "";
 }
 
-// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements, 128B swizzle.
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements, 128B swizzle
+// (operands) or 64B swizzle (the 32-column output tiles of the BCE epilogue).
 static std::string make_tmap(CUtensorMap* out, const void* ptr, long long inner, long long outer, long long ld,
-                             int box_inner, int box_outer) {
+                             int box_inner, int box_outer, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   if (!g_encode) return "gemm_init() not called";
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return "tensor map: base not 16-byte aligned";
   if ((ld * 2) % 16 != 0) return "tensor map: row pitch not a multiple of 16 bytes";
@@ -76,7 +79,7 @@ static std::string make_tmap(CUtensorMap* out, const void* ptr, long long inner,
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[160];
@@ -143,6 +146,10 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.ngroups = p.ngroups;
   a.tiles_m = (p.M + kBlockM - 1) / kBlockM;
   a.tiles_n = (p.N + kBlockN - 1) / kBlockN;
+  int cm = (b_mn && (p.cluster_m == 2 || p.cluster_m == 4)) ? p.cluster_m : 1;
+  while (cm > 1 && a.tiles_m % cm != 0) cm >>= 1;   // every CTA of a cluster gets a real M tile
+  a.cluster_m = cm;
+  a.tiles_m /= cm;                                   // cluster rows from here on
   a.m_fastest = p.N > p.M ? 1 : 0;   // keep the larger operand's tiles adjacent in time so it is read from HBM once
   const int tiles = a.tiles_m * a.tiles_n * a.ngroups;
   const int total_kb = a.nseg * a.kblocks;
@@ -176,15 +183,56 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       pl.epi = EPI_STORE_F32;
     }
   }
+  a.use_tout = 0;
+  if (p.epi == EPI_BCE && !p.e[0].precise && !getenv("MAGIC_NO_TILE_STORE")) {
+    std::string err = make_tmap(&a.tout, p.e[0].out, p.N, p.M, p.e[0].ld_out, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B);
+    if (!err.empty()) return "out: " + err;
+    a.use_tout = 1;
+  }
   const long long items = (long long)tiles * split;
-  pl.grid = (int)(items < num_sms ? items : num_sms);
+  pl.items = items;
+  const long long slots = num_sms / cm;              // refined at launch by the occupancy query when cm > 1
+  pl.grid = (int)(items < slots ? items : slots) * cm;
   pl.flops = 2.0 * p.M * (double)p.N * p.K * p.nseg * p.ngroups;
   return "";
 }
 
 template <bool A_MN, bool B_MN, int EPI>
 static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
-  gemm_tcgen05_kernel<A_MN, B_MN, EPI><<<pl.grid, gemm_threads(EPI), gemm_smem_bytes(EPI), s>>>(pl.args);
+  const int cm = pl.args.cluster_m;
+  if (cm <= 1) {
+    launch_chain(gemm_tcgen05_kernel<A_MN, B_MN, EPI>, dim3(pl.grid), dim3(gemm_threads(EPI)), gemm_smem_bytes(EPI), s,
+                 pl.args);
+    return;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof cfg);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cm;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(gemm_threads(EPI));
+  cfg.dynamicSmemBytes = gemm_smem_bytes(EPI);
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  // A cluster lives inside one GPC, so fewer than num_sms / cm clusters may be co-resident; the persistent loop
+  // strides by the number of clusters, which must therefore all be resident at once.
+  static int max_clusters[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (max_clusters[cm] == 0) {
+    cfg.gridDim = dim3(pl.grid);
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_tcgen05_kernel<A_MN, B_MN, EPI>, &cfg) != cudaSuccess || n <= 0) {
+      (void)cudaGetLastError();
+      n = pl.grid / cm;
+    }
+    max_clusters[cm] = n;
+    if (getenv("MAGIC_VERBOSE")) fprintf(stderr, "[magic] cluster_m=%d: %d co-resident clusters\n", cm, n);
+  }
+  long long ncl = pl.items < max_clusters[cm] ? pl.items : max_clusters[cm];
+  cfg.gridDim = dim3((unsigned)(ncl * cm));
+  cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<A_MN, B_MN, EPI>, pl.args);
 }
 
 int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
@@ -213,9 +261,11 @@ int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
     const int bs = 256;
     const int gs = (int)((n + bs - 1) / bs);
     if (pl.finish_epi_kind == EPI_ACT)
-      gemm_finish_kernel<EPI_ACT><<<gs, bs, 0, s>>>(pl.finish_epi[0], pl.ws, pl.ws_ld, pl.args.M, pl.args.N);
+      launch_chain(gemm_finish_kernel<EPI_ACT>, dim3(gs), dim3(bs), 0, s, pl.finish_epi[0], (const float*)pl.ws, pl.ws_ld,
+                   pl.args.M, pl.args.N);
     else
-      gemm_finish_kernel<EPI_DACT><<<gs, bs, 0, s>>>(pl.finish_epi[0], pl.ws, pl.ws_ld, pl.args.M, pl.args.N);
+      launch_chain(gemm_finish_kernel<EPI_DACT>, dim3(gs), dim3(bs), 0, s, pl.finish_epi[0], (const float*)pl.ws, pl.ws_ld,
+                   pl.args.M, pl.args.N);
     ++launches;
   }
   cudaError_t e = cudaGetLastError();

@@ -25,6 +25,7 @@ enum GemmKind : int {
 struct GemmPlan {
   GemmArgs args;
   int kind = 0, epi = 0, grid = 0;
+  long long items = 0;   // work items (per cluster when args.cluster_m > 1)
   // split-K with a non-linear epilogue: GEMM accumulates fp32 into ws (red.add), then finish applies epi
   bool two_pass = false;
   float* ws = nullptr;
@@ -42,6 +43,7 @@ struct GemmProblem {
   EpiArgs e[kMaxGroups];
   int M = 0, N = 0, K = 0;   // N: columns the epilogue writes (ACT: the output pitch)
   int force_splitk = 0;      // 0 = heuristic
+  int cluster_m = 1;         // CTAs per cluster along M sharing the B tile by TMA multicast (FWD / WGRAD kinds; 1, 2 or 4)
   float* ws = nullptr;       // fp32 workspace [M, ws_ld] for two-pass split-K (ACT / DACT); may be null
   long long ws_ld = 0;
 };

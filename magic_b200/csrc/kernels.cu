@@ -1,7 +1,9 @@
 // Non-GEMM kernels of the step (see kernels.h).  All are HBM/latency-bound elementwise or reduction kernels.
 #include "kernels.h"
 #include "ptx.cuh"
+#include "launch.cuh"
 #include <math.h>
+#include <cstring>
 
 namespace magic {
 
@@ -37,6 +39,7 @@ __device__ __forceinline__ void store_split(__nv_bfloat16* hi, __nv_bfloat16* lo
 // ------------------------------------------------------------------ zero fill
 // A kernel instead of cudaMemsetAsync so that every launch of the step shares one shared-memory carveout (below).
 __global__ void __launch_bounds__(256) zero_kernel(uint4* p, long long n16, uint32_t* tail, int ntail) {
+  ptx::grid_dep_wait();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n16) p[i] = make_uint4(0u, 0u, 0u, 0u);
   if (i < ntail) tail[i] = 0u;
@@ -46,7 +49,7 @@ void zero_fill(void* ptr, size_t bytes, cudaStream_t s) {   // ptr 16-byte align
   const int ntail = (int)((bytes % 16) / 4);
   const long long n = n16 > ntail ? n16 : ntail;
   if (n == 0) return;
-  zero_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(reinterpret_cast<uint4*>(ptr), n16,
+  launch_chain(zero_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, reinterpret_cast<uint4*>(ptr), n16,
                                                      reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(ptr) + n16 * 16), ntail);
 }
 
@@ -58,6 +61,7 @@ constexpr int kLatRowsPerWarp = 4;
 constexpr int kLatSlab = 16;
 
 __global__ void __launch_bounds__(256) latent_forward_kernel(LatentArgs a) {
+  ptx::grid_dep_wait();
   const int L = a.L, B = a.B;
   const int j = blockIdx.x * 256 + threadIdx.x;
   const int i0 = blockIdx.y * kLatSlab, i1 = min(B, i0 + kLatSlab);
@@ -110,6 +114,7 @@ __global__ void __launch_bounds__(256) latent_forward_kernel(LatentArgs a) {
 
 // ------------------------------------------------------------------ metric loss (8c/vae.py:300-307, 438-452)
 __global__ void __launch_bounds__(kLatWarps * 32) latent_metric_kernel(LatentArgs a) {
+  ptx::grid_dep_wait();
   extern __shared__ float sm[];   // [L] column sums S_j (cosine)
   const int L = a.L, B = a.B;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -162,6 +167,7 @@ __global__ void __launch_bounds__(kLatWarps * 32) latent_metric_kernel(LatentArg
 // dheads rows: [rot|cost ; lock|cost ; lock|metric ; key|metric], cols [d mu | d log sigma^2].
 // d z / d mu = 1 ;  d z / d lv = 0.5 * sqrt(exp(lv)) * eps = 0.5 * (z - mu).
 __global__ void __launch_bounds__(256) latent_backward_kernel(LatentArgs a) {
+  ptx::grid_dep_wait();
   const int L = a.L, B = a.B;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * L) return;
@@ -209,14 +215,14 @@ __global__ void __launch_bounds__(256) latent_backward_kernel(LatentArgs a) {
 static int lat_blocks(int B) { return (B + kLatWarps * kLatRowsPerWarp - 1) / (kLatWarps * kLatRowsPerWarp); }
 
 void latent_forward(const LatentArgs& a, cudaStream_t s) {
-  latent_forward_kernel<<<dim3((a.L + 255) / 256, (a.B + kLatSlab - 1) / kLatSlab), 256, 0, s>>>(a);
+  launch_chain(latent_forward_kernel, dim3((a.L + 255) / 256, (a.B + kLatSlab - 1) / kLatSlab), dim3(256), 0, s, a);
 }
 void latent_metric(const LatentArgs& a, cudaStream_t s) {
-  latent_metric_kernel<<<lat_blocks(a.B), kLatWarps * 32, sizeof(float) * a.L, s>>>(a);
+  launch_chain(latent_metric_kernel, dim3(lat_blocks(a.B)), dim3(kLatWarps * 32), sizeof(float) * a.L, s, a);
 }
 void latent_backward(const LatentArgs& a, cudaStream_t s) {
   const long long n = (long long)a.B * a.L;
-  latent_backward_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(a);
+  launch_chain(latent_backward_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, a);
 }
 
 // ------------------------------------------------------------------ fused dual Adam (8c/vae.py:314-321)
@@ -230,6 +236,7 @@ __device__ __forceinline__ float adam_one(float g, float& m, float& v, float lr_
 }
 
 __global__ void __launch_bounds__(256) adam_dual_kernel(AdamArgs a) {
+  ptx::grid_dep_wait();
   const long long i4 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i4 >= a.n_total) return;
   float4 p = *reinterpret_cast<const float4*>(a.p + i4);
@@ -266,7 +273,7 @@ __global__ void __launch_bounds__(256) adam_dual_kernel(AdamArgs a) {
 
 void adam_dual(const AdamArgs& a, cudaStream_t s) {
   const long long n4 = (a.n_total + 3) / 4;
-  adam_dual_kernel<<<(int)((n4 + 255) / 256), 256, 0, s>>>(a);
+  launch_chain(adam_dual_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, s, a);
 }
 
 // ------------------------------------------------------------------ data parallel: sharded reduce + dual Adam
@@ -276,6 +283,7 @@ void adam_dual(const AdamArgs& a, cudaStream_t s) {
 // state traffic / world) and all-gathers the result by storing the new bf16 shadow weights into every rank's
 // shadow buffer over NVLink.
 __global__ void __launch_bounds__(256) adam_dual_sharded_kernel(AdamShardArgs a) {
+  ptx::grid_dep_wait();
   const long long loc = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;     // position in the owned slice
   if (loc >= a.slice_len) return;
   // owned granules are dealt round-robin over the ranks: local granule loc >> gs is flat granule (that * world + rank)
@@ -332,11 +340,12 @@ __global__ void __launch_bounds__(256) adam_dual_sharded_kernel(AdamShardArgs a)
 void adam_dual_sharded(const AdamShardArgs& a, cudaStream_t s) {
   const long long n4 = ((long long)a.slice_len + 3) / 4;
   if (n4 <= 0) return;
-  adam_dual_sharded_kernel<<<(int)((n4 + 255) / 256), 256, 0, s>>>(a);
+  launch_chain(adam_dual_sharded_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, s, a);
 }
 
 // local partial gradients of the small layers (accumulated with split-K red.add) -> the owners' staging slots
 __global__ void __launch_bounds__(256) push_range_kernel(PushArgs a) {
+  ptx::grid_dep_wait();
   const long long i4 = a.begin + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i4 >= a.end) return;
   const long long q = i4 >> a.gran_shift;
@@ -359,7 +368,7 @@ void mask_unowned(float* buf, long long n, int world, int rank, int gran_shift, 
 void push_range(const PushArgs& a, cudaStream_t s) {
   const long long n4 = (a.end - a.begin + 3) / 4;
   if (n4 <= 0) return;
-  push_range_kernel<<<(int)((n4 + 255) / 256), 256, 0, s>>>(a);
+  launch_chain(push_range_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, s, a);
 }
 
 __global__ void __launch_bounds__(256) shadow_refresh_kernel(const float* __restrict__ p, __nv_bfloat16* hi,

@@ -68,6 +68,8 @@ static void host_ref(int kind, int M, int N, int K, int nseg, const HostMat* a, 
       }
 }
 
+static int g_cluster = 1;   // cluster_m applied to the problems built below
+
 static void test_store(int kind, int M, int N, int K, int nseg, int split, int sms) {
   HostMat a[3], b[3];
   for (int s = 0; s < nseg; ++s) {
@@ -80,6 +82,7 @@ static void test_store(int kind, int M, int N, int K, int nseg, int split, int s
   CK(cudaMemset(dout, 0, sizeof(float) * M * ldo));
   GemmProblem p;
   p.kind = kind; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
+  p.cluster_m = g_cluster;
   for (int s = 0; s < nseg; ++s) { p.a[0][s] = a[s].mat(); p.b[0][s] = b[s].mat(); }
   EpiArgs e = {};
   e.out = dout; e.ld_out = ldo; e.alpha = 0.5f;
@@ -171,6 +174,7 @@ static void test_fused(int epi, int M, int Nv, int K, int split, int precise, in
   CK(cudaMalloc(&ws, sizeof(float) * M * ldo));
   GemmProblem p;
   p.kind = kind; p.epi = epi; p.M = M; p.K = K; p.force_splitk = split;
+  p.cluster_m = g_cluster;
   p.N = epi == EPI_BCE ? Nv : (int)ldo;
   p.a[0][0] = a.mat(); p.b[0][0] = b.mat();
   p.ws = ws; p.ws_ld = ldo;
@@ -239,10 +243,12 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   CK(cudaMemset(out, 0, sizeof(float) * M * ldo));
   GemmProblem p;
   p.kind = kind; p.epi = EPI_STORE_F32; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
+  p.cluster_m = g_cluster;
   p.a[0][0] = kind == GEMM_WGRAD ? Mat(a, K, M, (M + 63) / 64 * 64) : Mat(a, M, K, (K + 63) / 64 * 64);
   p.b[0][0] = kind == GEMM_DGRAD ? Mat(b, N, K, (K + 63) / 64 * 64) : Mat(b, K, N, (N + 63) / 64 * 64);
   EpiArgs e = {};
   e.out = out; e.ld_out = ldo; e.alpha = 1.f;
+  if (const char* d = getenv("MAGIC_EPI_DBG")) e.dbg = atoi(d);
   p.e[0] = e;
   GemmPlan pl;
   std::string err = gemm_plan(p, sms, &pl);
@@ -294,17 +300,39 @@ int main(int argc, char** argv) {
   test_fused(EPI_DACT, 512, 500, 4000, 5, 1, sms);
   test_fused(EPI_BCE, 300, 1000, 501, 1, 1, sms);
   test_fused(EPI_BCE, 300, 1000, 501, 1, 0, sms);
+  // thread-block clusters along M with the B tile multicast (FWD / WGRAD kinds)
+  for (int cm = 2; cm <= 4; cm *= 2) {
+    g_cluster = cm;
+    test_store(GEMM_FWD, 1024, 1000, 520, 1, 1, sms);
+    test_store(GEMM_FWD, 1000, 300, 2000, 2, 3, sms);
+    test_store(GEMM_WGRAD, 1500, 500, 700, 1, 1, sms);
+    test_fused(EPI_BCE, 1024, 3000, 501, 1, 1, sms);
+    test_fused(EPI_BCE, 2000, 1000, 501, 1, 0, sms);
+    test_fused(EPI_ACT, 2048, 500, 501, 1, 1, sms);
+  }
+  g_cluster = 1;
   printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
   if (do_bench) {
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");
     bench(GEMM_FWD, 12288, 512, 40064, 0, sms, "enc L0 fwd (auto split)");
     bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd");
+    g_cluster = 2; bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd, cluster 2");
+    g_cluster = 4; bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd, cluster 4");
+    g_cluster = 4; bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad, cluster 4");
+    g_cluster = 4; bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd, cluster 4");
+    g_cluster = 1;
     bench(GEMM_DGRAD, 4096, 512, 40000, 0, sms, "dec out dgrad (auto split)");
     bench(GEMM_WGRAD, 512, 40000, 4096, 1, sms, "dec out wgrad");
     bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad");
     bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd");
     bench(GEMM_WGRAD, 512, 512, 8192, 0, sms, "hidden wgrad (auto split)");
     bench(GEMM_FWD, 8192, 8192, 8192, 1, sms, "square 8192");
+    bench(GEMM_FWD, 4096, 40000, 256, 1, sms, "dec-out shape, K=256");
+    bench(GEMM_FWD, 4096, 40000, 1024, 1, sms, "dec-out shape, K=1024");
+    bench(GEMM_FWD, 4096, 40000, 2048, 1, sms, "dec-out shape, K=2048");
+    bench(GEMM_FWD, 4096, 40000, 4096, 1, sms, "dec-out shape, K=4096");
+    bench(GEMM_DGRAD, 4096, 40000, 512, 1, sms, "dec-out shape, K=512, B K-major");
+    bench(GEMM_WGRAD, 4096, 40000, 512, 1, sms, "dec-out shape, K=512, A,B MN-major");
   }
   return g_fail ? 1 : 0;
 }

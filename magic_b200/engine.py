@@ -241,6 +241,10 @@ class Engine:
         check(self.lib.magic_export_batch(self._h, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr())))
         return x, y
 
+    def swap_batch(self) -> None:
+        """Make the previously loaded batch (still resident in HBM) the loaded one again."""
+        check(self.lib.magic_swap_batch(self._h))
+
     def export_rotation(self) -> torch.Tensor:
         """[B,2] int32: Q14 (cos, sin) of the rotation the generator applied to each lock."""
         r = torch.empty(self.B, 2, dtype=torch.int32, device=self.device)

@@ -1,8 +1,10 @@
-import sys, time, torch
+import os, sys, time, torch
 sys.path.insert(0, '/root/repo')
 from magic_b200.engine import Engine, EngineConfig
 exp = sys.argv[1] if len(sys.argv) > 1 else "8d"
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
+if B <= 0:
+    B = {"8c": 100, "8d": 4096, "8e": 2048, "9a": 8192, "11a": 4096}.get(exp, 4096)
 prec = sys.argv[3] if len(sys.argv) > 3 else "bf16"
 eng = Engine(EngineConfig.experiment(exp, batch=B, precision=prec))
 st = eng.stats()
@@ -11,7 +13,7 @@ for i in range(3):
     eng.generate_batch(0, i); l, _ = eng.step()
 print("losses", l.cpu().numpy(), "launches", eng.stats().launches_last_step)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-K = 10
+K = int(os.environ.get("PROBE_STEPS", "30"))
 torch.cuda.synchronize(); e0.record()
 for i in range(K):
     eng.generate_batch(0, 3 + i); l, _ = eng.step()
