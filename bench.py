@@ -10,8 +10,8 @@ passes (cost, training_loss), both Adam updates (8c/vae.py:379-405).  Default wo
 configs[1]: experiment 8d (encoder 500x4, latent 200, cosine metric) at batch 4096 per GPU; with N GPUs the
 per-GPU batch stays fixed (weak scaling) and gradients are all-reduced over NCCL inside the step.
 
-Printed line (rank 0): value = pairs/s with the batch produced on the device by the engine's generator
-(inputs resident in HBM; the generator kernel is inside the timed region so every step sees a new batch);
+Printed line (rank 0): value = pairs/s of the step with its inputs resident in HBM (two generated batches kept in
+the engine's input buffers and alternated; `with_generator` = the loop that also generates a new batch every step);
 e2e = pairs/s through the host-buffer C-ABI call magic_partial_fit_host (pinned host X[B,120000] fp32 exactly
 as main.py feeds partial_fit, H2D + step + D2H of the losses inside the timed region).
 """
@@ -256,42 +256,68 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- leg 1: device-resident throughput (generator + step), per-kernel events live in the timed region
+    # ---- leg 1 (headline `value`): the hot path with its inputs resident in HBM.  Two generated batches (983 MB of
+    # planes each at 8d/4096: together 15x the L2) stay in the engine's two input buffers and are alternated with
+    # magic_swap_batch, so every step reads a batch that the previous step evicted from L2.  No events inside.
+    eng.generate_batch(0, 0)
+    eng.generate_batch(0, 1)
     for i in range(W):
-        eng.generate_batch(0, i)
+        eng.swap_batch()
         eng.step()
-    eng.profile(True)
-    eng.generate_batch(0, W)
-    eng.step()
-    eng.profile_report()          # warm the event pool, drop the warm-up record
     sampler = ClockSampler(local)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     sampler.start()
     e0.record()
     for i in range(K):
-        eng.generate_batch(0, W + 1 + i)
+        eng.swap_batch()
         losses, _ = eng.step()
     e1.record()
     barrier()
     clocks = sampler.stop()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
-    rep = eng.profile_report()
-    eng.profile(False)
-    launches_per_step = int(eng.stats().launches_last_step) + 1     # + the generator kernel
+    launches_per_step = int(eng.stats().launches_last_step)
     final_losses = losses.cpu().numpy().tolist()
     ms_step = ms_total / K
     value = B * world * K / (ms_total * 1e-3)
 
-    # ---- leg 1b: the same loop without per-launch events and without the generator (explains `value`)
+    # ---- leg 1b: the same loop with a CUDA-event pair around every launch (engine profile mode): per-kernel device
+    # times for the roofline and the shares.  Kept out of the headline loop because an event between two kernels
+    # disables their programmatic dependent launch overlap.
+    Kp = max(3, min(K, 40))
+    eng.profile(True)
+    eng.swap_batch()
+    eng.step()
+    eng.profile_report()          # warm the event pool, drop the warm-up record
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e2.record()
-    for i in range(K):
+    for i in range(Kp):
+        eng.swap_batch()
         eng.step()
     e3.record()
     barrier()
-    ms_step_only = max_over_ranks(e2.elapsed_time(e3)) / K
+    ms_step_events = max_over_ranks(e2.elapsed_time(e3)) / Kp
+    rep = eng.profile_report()
+    eng.profile(False)
+
+    # ---- leg 1c: the generator inside the loop (row N1): a NEW batch every step, produced on the device by the
+    # engine's generator on its own stream under the previous step's backward pass
+    Kg = max(3, min(K, 100))
+    for i in range(3):
+        eng.generate_batch(0, 10 + i)
+        eng.step()
+    e8, e9 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e8.record()
+    for i in range(Kg):
+        eng.generate_batch(0, 100 + i)
+        eng.step()
+    e9.record()
+    barrier()
+    ms_gen = max_over_ranks(e8.elapsed_time(e9)) / Kg
+    with_generator = {"value": B * world / (ms_gen * 1e-3), "unit": UNIT, "ms_per_step": ms_gen, "steps": Kg,
+                      "note": "new generated batch every step inside the timed region (generator kernel + step)"}
 
     # ---- roofline of the dominant kernel family (by summed device time in the timed region)
     pk = peaks()
@@ -313,7 +339,8 @@ def run_b200(args):
                 ach, peak, unit = amount / avg_s * 1e-9, pk["hbm"], "GB/s"
             roof = {"kernel": tag, "bound": kind, "achieved": round(ach, 2), "peak": peak, "unit": unit,
                     "frac": round(ach / peak, 4), "traffic": None, "avg_launch_ms": round(ms / n, 5),
-                    "launches_timed": n, "peak_source": pk["source"] + (" (sustained)" if kind == "tensor" else ""),
+                    "launches_timed": n, "measured_over": "%d steps with an event pair around every launch, run right "
+                    "after the timed region on the same inputs" % Kp, "peak_source": pk["source"] + (" (sustained)" if kind == "tensor" else ""),
                     "algorithmic_per_launch": amount, "share_of_step": shares[tag]}
             break
     model_tflops = value / world * st.model_flops_per_pair * 1e-12
@@ -386,10 +413,12 @@ def run_b200(args):
                        "parallelism": "dp%d" % world,
                        "l2": "operands per step (bf16 planes %.0f MB, weights+Adam state %.0f MB) exceed the 126 MB L2; "
                              "no flush needed" % (3 * B * cfg.D * 2 / 1e6, st.hbm_bytes / 1e6),
-                       "inputs": "on-device generator, new batch every step, inside the timed region"},
+                       "inputs": "two generated batches resident in HBM, alternated every step (magic_swap_batch); "
+                                 "`with_generator` times the loop that generates a new batch every step"},
             "model_tflops_per_gpu": round(model_tflops, 1),
             "frac_of_bf16_sustained_peak": round(model_tflops / pk["tf_sustained"], 4),
-            "ms_per_step_without_generator_and_events": ms_step_only,
+            "with_generator": with_generator,
+            "ms_per_step_with_per_launch_events": ms_step_events,
             "roofline": roof, "kernel_time_shares": shares,
             "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
             "gpu_launches": launches_per_step * K, "gpu_launches_per_step": launches_per_step,

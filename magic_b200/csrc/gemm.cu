@@ -90,6 +90,31 @@ static std::string make_tmap(CUtensorMap* out, const void* ptr, long long inner,
   return "";
 }
 
+// MN-major bf16 operand [rows = K, cols = MN, pitch ld] as a 3-D tensor {64 contiguous, K rows, MN/64 slabs}: one box
+// {64, 64, slabs} fetches all the swizzle atoms of a pipeline stage with a single TMA instruction.  The last slab may
+// reach past `cols` into the row padding (ld is a multiple of 64), which the consumers mask.
+static std::string make_tmap_mn(CUtensorMap* out, const void* ptr, long long cols, long long rows, long long ld,
+                                int box_k, int slabs) {
+  if (!g_encode) return "gemm_init() not called";
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return "tensor map: base not 16-byte aligned";
+  if (ld % 64 != 0) return "tensor map: MN-major operand needs a row pitch that is a multiple of 64 elements";
+  if (cols <= 0 || rows <= 0 || cols > ld) return "tensor map: bad extent";
+  cuuint64_t dims[3] = {64, (cuuint64_t)rows, (cuuint64_t)((cols + 63) / 64)};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, 128};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_k, (cuuint32_t)slabs};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[160];
+    snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled(3d) failed (%d) cols=%lld rows=%lld ld=%lld slabs=%d", (int)r, cols,
+             rows, ld, slabs);
+    return buf;
+  }
+  return "";
+}
+
 // Minimise waves * (k-blocks per item + fixed per-item overhead), see DESIGN.md "split-K".
 int choose_splitk(int tiles, int total_kb, int num_sms) {
   const double overhead = 8.0;   // epilogue + pipeline fill, in k-block units
@@ -116,6 +141,8 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   pl.epi = p.epi;
   if (p.ngroups < 1 || p.ngroups > kMaxGroups || p.nseg < 1 || p.nseg > kMaxSegs) return "bad ngroups/nseg";
   const bool a_mn = p.kind == GEMM_WGRAD, b_mn = p.kind != GEMM_DGRAD;
+  int cm_b = (b_mn && (p.cluster_m == 2 || p.cluster_m == 4)) ? p.cluster_m : 1;
+  while (cm_b > 1 && ((p.M + kBlockM - 1) / kBlockM) % cm_b != 0) cm_b >>= 1;   // every CTA of a cluster gets a real M tile
   for (int g = 0; g < p.ngroups; ++g)
     for (int s = 0; s < p.nseg; ++s) {
       const Mat& A = p.a[g][s];
@@ -126,7 +153,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
         err = make_tmap(&pl.args.ta[g][s], A.ptr, A.cols, A.rows, A.ld, kBlockK, kBlockM);
       } else {       // Mat[K,M]
         if (A.rows != p.K) return "A rows != K";
-        err = make_tmap(&pl.args.ta[g][s], A.ptr, A.cols, A.rows, A.ld, 64, kBlockK);
+        err = make_tmap_mn(&pl.args.ta[g][s], A.ptr, A.cols, A.rows, A.ld, kBlockK, kBlockM / 64);
       }
       if (!err.empty()) return "A: " + err;
       if (!b_mn) {   // Mat[N,K]
@@ -134,7 +161,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
         err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, kBlockN);
       } else {       // Mat[K,N]
         if (B.rows != p.K) return "B rows != K";
-        err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, 64, kBlockK);
+        err = make_tmap_mn(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, (kBlockN / 64) / cm_b);
       }
       if (!err.empty()) return "B: " + err;
     }
@@ -146,8 +173,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.ngroups = p.ngroups;
   a.tiles_m = (p.M + kBlockM - 1) / kBlockM;
   a.tiles_n = (p.N + kBlockN - 1) / kBlockN;
-  int cm = (b_mn && (p.cluster_m == 2 || p.cluster_m == 4)) ? p.cluster_m : 1;
-  while (cm > 1 && a.tiles_m % cm != 0) cm >>= 1;   // every CTA of a cluster gets a real M tile
+  const int cm = cm_b;
   a.cluster_m = cm;
   a.tiles_m /= cm;                                   // cluster rows from here on
   a.m_fastest = p.N > p.M ? 1 : 0;   // keep the larger operand's tiles adjacent in time so it is read from HBM once

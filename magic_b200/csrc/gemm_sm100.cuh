@@ -512,22 +512,17 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
           if constexpr (!A_MN) {
             ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);              // box {64 k, 128 m}
           } else {
-#pragma unroll
-            for (int i = 0; i < kBlockM / 64; ++i)                               // boxes {64 m, 64 k}
-              ptx::tma_load_2d(ta, &full_bar[stage], sa + i * kAtomBytes, it.m0 + 64 * i, k0);
+            ptx::tma_load_3d(ta, &full_bar[stage], sa, 0, k0, it.m0 >> 6);      // box {64 m, 64 k, 2 slabs}
           }
           if constexpr (!B_MN) {
             ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);              // box {64 k, 256 n}
           } else if (CM == 1) {
-#pragma unroll
-            for (int i = 0; i < kBlockN / 64; ++i)                               // boxes {64 n, 64 k}
-              ptx::tma_load_2d(tb, &full_bar[stage], sb + i * kAtomBytes, it.n0 + 64 * i, k0);
+            ptx::tma_load_3d(tb, &full_bar[stage], sb, 0, k0, it.n0 >> 6);      // box {64 n, 64 k, 4 slabs}
           } else {
-            // the cluster shares this B tile: each CTA fetches 1/CM of the boxes and multicasts them to all
-#pragma unroll
-            for (int i = 0; i < kBlockN / 64; ++i)
-              if ((i % CM) == crank)
-                ptx::tma_load_2d_multicast(tb, &full_bar[stage], sb + i * kAtomBytes, it.n0 + 64 * i, k0, cmask);
+            // the cluster shares this B tile: each CTA fetches 4/CM slabs and multicasts them to all
+            const int per = (kBlockN / 64) / CM;
+            ptx::tma_load_3d_multicast(tb, &full_bar[stage], sb + crank * per * kAtomBytes, 0, k0,
+                                       (it.n0 >> 6) + crank * per, cmask);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }

@@ -80,6 +80,27 @@ __device__ __forceinline__ void tma_load_2d(const void* desc, uint64_t* bar, voi
       : "memory");
 }
 
+// 3-D box: used for MN-major operands viewed as {64 contiguous elements, K rows, MN/64 slabs}, so that ONE instruction
+// brings all the 64 x 64 swizzle atoms of a stage (they land back to back, slab-major) instead of one per atom.
+__device__ __forceinline__ void tma_load_3d(const void* desc, uint64_t* bar, void* smem_dst, int32_t c0, int32_t c1,
+                                            int32_t c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];"
+      :
+      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_multicast(const void* desc, uint64_t* bar, void* smem_dst, int32_t c0,
+                                                      int32_t c1, int32_t c2, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;"
+      :
+      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(desc)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
+        "h"(mask)
+      : "memory");
+}
 // Same load, multicast to the CTAs of the cluster named in `mask`: the tile lands at the same shared-memory offset in
 // every destination CTA and completes `bytes` on the mbarrier at the same offset in each of them.
 __device__ __forceinline__ void tma_load_2d_multicast(const void* desc, uint64_t* bar, void* smem_dst, int32_t c0,

@@ -1,6 +1,8 @@
-# usage: bash tools/gpu_exp.sh  -- selftest + GPU tests + probe with and without programmatic dependent launch
+# usage: bash tools/gpu_exp.sh  -- 3-D TMA boxes for MN-major operands: selftest + mainloop-only micro-benchmarks + tests + probe
 mkdir -p gpurun_out
-timeout 300 magic_b200/csrc/build/selftest_gemm > gpurun_out/selftest.log 2>&1; echo "selftest rc=$?"; grep -i -E "fail|error|PASSED" gpurun_out/selftest.log | head -20
+for d in 4 0; do
+MAGIC_EPI_DBG=$d timeout 300 magic_b200/csrc/build/selftest_gemm bench > gpurun_out/selftest_dbg$d.log 2>&1; echo "dbg=$d selftest rc=$?"; grep -i -E "fail|error|PASSED|bench" gpurun_out/selftest_dbg$d.log | grep -v "cluster" | head -40
+done
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
-for pdl in 1 0 1 0; do echo "== MAGIC_PDL=$pdl"; MAGIC_PDL=$pdl timeout 300 python tests/perf_probe.py 8d 4096 bf16 2>&1 | grep -E "8d B=|sum of"; done
-for e in 8c 9a 11a; do echo "== $e"; for pdl in 1 0; do MAGIC_PDL=$pdl timeout 300 python tests/perf_probe.py $e 0 bf16 2>&1 | grep -E "B=.*ms/step"; done; done
+timeout 300 python tests/perf_probe.py 8d 4096 bf16 2>&1 | tee gpurun_out/probe_8d_bf16.txt | grep -E "8d B=|ms/step"
+timeout 600 python bench.py --steps 100 --warmup 5 --no-cpu-baseline --e2e-steps 3 > gpurun_out/bench_try.json 2> gpurun_out/bench_try.err; tail -c 3000 gpurun_out/bench_try.json; tail -3 gpurun_out/bench_try.err
