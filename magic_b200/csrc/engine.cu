@@ -874,7 +874,7 @@ std::string Engine::forward(int what, const float* d_eps3, float* d_out) {
     MAGIC_CUDA(cudaMemcpy2DAsync(d_out, sizeof(float) * L, heads_ + (long long)B * ld_heads_, sizeof(float) * ld_heads_,
                                  sizeof(float) * L, B, cudaMemcpyDeviceToDevice, stream));
   } else if (what == MAGIC_FWD_RECON) {
-    pl_out_sig_.args.epi[0].out = d_out;
+    MAGIC_TRY(gemm_set_output(&pl_out_sig_, 0, d_out, nullptr));   // d_out must be 16-byte aligned
     MAGIC_TRY(launch(pl_out_sig_, &launches, "gemm.fwd_dec_out_sigmoid"));
   } else {
     return "forward: unknown output selector";
@@ -890,7 +890,7 @@ std::string Engine::decode(const float* d_z, float* d_out) {
   int launches = 0;
   MAGIC_TRY(launch(pl_d1_, &launches, "gemm.fwd_dec_hidden"));
   MAGIC_TRY(launch(pl_d2_, &launches, "gemm.fwd_dec_hidden"));
-  pl_out_sig_.args.epi[0].out = d_out;
+  MAGIC_TRY(gemm_set_output(&pl_out_sig_, 0, d_out, nullptr));     // d_out must be 16-byte aligned
   MAGIC_TRY(launch(pl_out_sig_, &launches, "gemm.fwd_dec_out_sigmoid"));
   MAGIC_CUDA(cudaGetLastError());
   return "";

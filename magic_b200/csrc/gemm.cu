@@ -32,7 +32,7 @@ __global__ void gemm_finish_kernel(EpiArgs e, const float* __restrict__ ws, long
     r[4 * q + 3] = __float_as_uint(v.w);
   }
   float dummy = 0.f;
-  epilogue_chunk<EPI>(e, r, row, c * 32, M, N, dummy);
+  epilogue_chunk<EPI, false>(e, TileOut{}, r, row, c * 32, M, N, dummy);
 }
 
 template <bool A_MN, bool B_MN, int EPI>
@@ -88,6 +88,55 @@ static std::string make_tmap(CUtensorMap* out, const void* ptr, long long inner,
     return buf;
   }
   return "";
+}
+
+// Output tile map over a row-major [rows, cols] matrix with pitch ld: box of 32 rows x 64 bytes (16 fp32 or 32 bf16
+// columns), 64B swizzle -- the staging layout of TileOut in gemm_sm100.cuh.
+static std::string make_tmap_out(CUtensorMap* out, void* ptr, bool f32, long long cols, long long rows, long long ld) {
+  if (!g_encode) return "gemm_init() not called";
+  const int eb = f32 ? 4 : 2;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return "output map: base not 16-byte aligned";
+  if ((ld * eb) % 16 != 0) return "output map: row pitch not a multiple of 16 bytes";
+  if (cols <= 0 || rows <= 0) return "output map: empty extent";
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * eb};
+  cuuint32_t box[2] = {f32 ? 16u : 32u, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, dims,
+                        strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[160];
+    snprintf(buf, sizeof buf, "cuTensorMapEncodeTiled(out) failed (%d) cols=%lld rows=%lld ld=%lld f32=%d", (int)r, cols,
+             rows, ld, (int)f32);
+    return buf;
+  }
+  return "";
+}
+
+// (Re)build the output maps of group g from args.epi[g].out / out_lo (null pointers are skipped: the caller patches
+// them per call and comes back through gemm_set_output).
+static std::string build_out_maps(GemmPlan& pl, int g) {
+  if (pl.epi == EPI_SCATTER_F32) return "";
+  GemmArgs& a = pl.args;
+  const EpiArgs& e = a.epi[g];
+  const bool f32 = pl.epi == EPI_STORE_F32 || pl.epi == EPI_SIGMOID;
+  if (e.out) {
+    std::string err = make_tmap_out(&a.tout[g][0], e.out, f32, a.N, a.M, e.ld_out);
+    if (!err.empty()) return err;
+  }
+  if (!f32 && e.out_lo) {
+    std::string err = make_tmap_out(&a.tout[g][1], e.out_lo, false, a.N, a.M, e.ld_out);
+    if (!err.empty()) return err;
+  }
+  return "";
+}
+
+std::string gemm_set_output(GemmPlan* pl, int g, void* out, void* out_lo) {
+  pl->args.epi[g].out = out;
+  pl->args.epi[g].out_lo = out_lo;
+  return build_out_maps(*pl, g);
 }
 
 // MN-major bf16 operand [rows = K, cols = MN, pitch ld] as a 3-D tensor {64 contiguous, K rows, MN/64 slabs}: one box
@@ -209,11 +258,9 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       pl.epi = EPI_STORE_F32;
     }
   }
-  a.use_tout = 0;
-  if (p.epi == EPI_BCE && !p.e[0].precise && !getenv("MAGIC_NO_TILE_STORE")) {
-    std::string err = make_tmap(&a.tout, p.e[0].out, p.N, p.M, p.e[0].ld_out, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B);
+  for (int g = 0; g < p.ngroups; ++g) {
+    std::string err = build_out_maps(pl, g);
     if (!err.empty()) return "out: " + err;
-    a.use_tout = 1;
   }
   const long long items = (long long)tiles * split;
   pl.items = items;

@@ -42,15 +42,14 @@ constexpr uint32_t kGemmSmemBytes = kStages * kStageBytes + 1024 /*align slack*/
 // EPI_SCATTER_F32 stages 8 rows x 128 B per epilogue warp so that every row segment leaves the SM as ONE 128-byte
 // bulk copy (full NVLink packets) instead of eight 16-byte partial-sector stores from a strided warp
 constexpr uint32_t kScatterStageBytes = 8 * 128;
-// EPI_BCE (fast mode) stages each warp's 32 x 32 bf16 chunk (64-byte rows, 64B swizzle) and hands it to a TMA tile
-// store: one warp-wide 16-byte store per lane touches 32 different rows, i.e. 32 half-written sectors per
-// instruction (2 request cycles each on the L1->crossbar port, ~58% busy in profiles/r01f); the tile store writes
-// whole 64-byte row segments and keeps the LSU out of it.
-constexpr uint32_t kTileStageBytes = 32 * 64;
+// Every epilogue except EPI_SCATTER_F32 stages its 32-row chunks for TMA tile stores (see TileOut), 2 KiB per
+// epilogue warp: 32 rows x 64 B, i.e. 32 bf16 columns or 16 fp32 columns per store.  16 KiB (32 KiB with the BCE
+// epilogue's 16 warps) on top of the pipeline keeps the CTA at 210 KiB, so that a CTA of the batch generator
+// (15 KiB, kernels.cu) still fits on the same SM and runs under the backward pass.
+__host__ __device__ constexpr uint32_t tile_stage_bytes(int epi) { return 2048u * (uint32_t)epi_warps(epi); }
 constexpr uint32_t kTileStageOffset = kStages * kStageBytes + 1024;   // after the barriers, 1024-byte aligned
 __host__ __device__ constexpr uint32_t gemm_smem_bytes(int epi) {
-  return kGemmSmemBytes + (epi == 5 /*EPI_SCATTER_F32*/ ? 8 * kScatterStageBytes : 0) +
-         (epi == 3 /*EPI_BCE*/ ? 1024 + 16 * kTileStageBytes : 0);
+  return kGemmSmemBytes + (epi == 5 /*EPI_SCATTER_F32*/ ? 8 * kScatterStageBytes : 1024 + tile_stage_bytes(epi));
 }
 
 enum EpiKind : int { EPI_STORE_F32 = 0, EPI_ACT = 1, EPI_DACT = 2, EPI_BCE = 3, EPI_SIGMOID = 4, EPI_SCATTER_F32 = 5 };
@@ -98,8 +97,7 @@ struct GemmArgs {
   int tiles_m, tiles_n;
   int m_fastest;     // tile order: consecutive work items walk M first (B is the large operand) or N first
   int cluster_m;     // CTAs per cluster along M (1, 2 or 4): they share the N tile and receive B by TMA multicast
-  int use_tout;      // EPI_BCE fast mode: the bf16 gradient leaves through `tout` (box 32 cols x 32 rows, 64B swizzle)
-  CUtensorMap tout;
+  CUtensorMap tout[kMaxGroups][2];   // output tiles (box 32 cols x 32 rows): [g][0] fp32 or bf16 hi plane, [g][1] lo plane
 };
 
 struct WorkItem {
@@ -231,48 +229,77 @@ __device__ __forceinline__ float bce_values(const EpiArgs& e, const uint32_t (&r
   return acc;
 }
 
-template <bool PRECISE, bool FULL>
-__device__ __forceinline__ void bce_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int N,
-                                          float& loss_acc, uint32_t xw) {
-  uint32_t hi[16], lo[16];
-  const float acc = bce_values<PRECISE, FULL>(e, r, col0, N, xw, hi, lo);
-  loss_acc += acc;
-  if (e.dbg & 1) {              // diagnostic: no global stores (keeps the values alive through a never-taken store)
-    if (acc != 1.2345e-33f) return;
+// ------------------------------------------------------------------ how a chunk leaves the SM
+// In the GEMM kernel lane = accumulator row, so a direct warp-wide 16-byte store touches 32 different rows: 32
+// half-written sectors per instruction, two request cycles each on the L1 -> crossbar port (58% busy in
+// profiles/r01f) and a 2-3x slower epilogue on short-K shapes (profiles/r01g).  Instead every warp stages its
+// 32-row chunk in shared memory in the TMA swizzle pattern (conflict-free for lane = row) and one lane issues a tile
+// store -- or a tile reduce-add for split-K partial sums -- through a tensor map, which also clips at the matrix edge.
+struct TileOut {
+  const CUtensorMap* hi;   // fp32 map (box 16 x 32) for the fp32 epilogues, bf16 "hi" plane (box 32 x 32) otherwise
+  const CUtensorMap* lo;   // bf16 "lo" plane (used when EpiArgs.out_lo is set)
+  uint8_t* slot;           // this warp's 2 KiB staging area: 32 rows x 64 B, 64B swizzle
+  int lane, row0;
+  int reduce;              // fp32: add into the destination
+};
+
+// lane = row: its 64 bytes go to the slot (16-byte piece j of row l sits at piece j ^ ((l >> 1) & 3), the 64B swizzle,
+// conflict-free), then one lane hands the 32 x 64 B tile to the TMA.
+template <int OFF>
+__device__ __forceinline__ void tile_emit_64(const TileOut& t, const CUtensorMap* map, const uint32_t* v, int col0,
+                                             bool reduce) {
+  if (t.lane == 0) ptx::bulk_wait_read();   // earlier tile stores of this warp have finished reading the slot
+  __syncwarp();
+  uint8_t* rowp = t.slot + t.lane * 64;
+  const int x = (t.lane >> 1) & 3;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    ptx::st_shared_v4(rowp + ((j ^ x) << 4), v[OFF + 4 * j], v[OFF + 4 * j + 1], v[OFF + 4 * j + 2], v[OFF + 4 * j + 3]);
+  ptx::fence_proxy_async_smem();
+  __syncwarp();
+  if (t.lane == 0) {
+    if (reduce) ptx::tma_reduce_add_2d(map, t.slot, col0, t.row0);
+    else ptx::tma_store_2d(map, t.slot, col0, t.row0);
+    ptx::bulk_commit();
   }
+}
+__device__ __forceinline__ void tile_emit_f32(const TileOut& t, const uint32_t (&v)[32], int col0) {
+  tile_emit_64<0>(t, t.hi, v, col0, t.reduce != 0);
+  tile_emit_64<16>(t, t.hi, v, col0 + 16, t.reduce != 0);
+}
+__device__ __forceinline__ void tile_emit_bf16(const TileOut& t, const uint32_t (&hi)[16], const uint32_t (&lo)[16],
+                                               bool with_lo, int col0) {
+  tile_emit_64<0>(t, t.hi, hi, col0, false);
+  if (with_lo) tile_emit_64<0>(t, t.lo, lo, col0, false);
+}
+// direct stores: the split-K finishing kernel (one thread per row chunk, consecutive threads on consecutive chunks)
+__device__ __forceinline__ void direct_emit_bf16(const EpiArgs& e, const uint32_t (&hi)[16], const uint32_t (&lo)[16],
+                                                 bool with_lo, int row, int col0) {
   uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
 #pragma unroll
   for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
-  if constexpr (PRECISE) {
-    if (e.out_lo) {
-      uint4* ol =
-          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
+  if (with_lo) {
+    uint4* ol = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
-    }
+    for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
   }
 }
 
-template <int EPI, int ACT, bool PRECISE>
-__device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
-                                              int N, float& loss_acc, uint32_t xw) {
+// One 32-column chunk of one accumulator row.  TILE: called by all 32 lanes of an epilogue warp of the GEMM kernel
+// (rows >= M and columns >= N are clipped by the tensor map; `row_ok` guards reads and the loss).  !TILE: one thread,
+// direct stores, row < M guaranteed by the caller.
+template <int EPI, int ACT, bool PRECISE, bool TILE>
+__device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const TileOut& t, const uint32_t (&r)[32], int row,
+                                              bool row_ok, int col0, int N, float& loss_acc, uint32_t xw) {
   if constexpr (EPI == EPI_STORE_F32) {
-    float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
     const float alpha = e.alpha;
-    if (col0 + 32 <= N) {
-      if (e.atomic) {
+    if constexpr (TILE) {
+      uint32_t v[32];
 #pragma unroll
-        for (int j = 0; j < 32; j += 4)
-          ptx::red_add_v4(out + j, __uint_as_float(r[j]) * alpha, __uint_as_float(r[j + 1]) * alpha,
-                          __uint_as_float(r[j + 2]) * alpha, __uint_as_float(r[j + 3]) * alpha);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; j += 4)
-          *reinterpret_cast<float4*>(out + j) =
-              make_float4(__uint_as_float(r[j]) * alpha, __uint_as_float(r[j + 1]) * alpha,
-                          __uint_as_float(r[j + 2]) * alpha, __uint_as_float(r[j + 3]) * alpha);
-      }
+      for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(r[j]) * alpha);
+      tile_emit_f32(t, v, col0);
     } else {
+      float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (col0 + j < N) {
@@ -282,16 +309,22 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
         }
     }
   } else if constexpr (EPI == EPI_SCATTER_F32) {
-    // handled by scatter_chunk() in the kernel (needs the warp's shared-memory staging area)
+    // handled by scatter_chunk() in the kernel (its own staging area and peer pointers)
   } else if constexpr (EPI == EPI_SIGMOID) {
-    float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
+    uint32_t v[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
-      if (col0 + j < N) {
-        float sp, sg;
-        softplus_sigmoid<true>(__uint_as_float(r[j]), sp, sg);
-        out[j] = sg;
-      }
+      float sp, sg;
+      softplus_sigmoid<true>(__uint_as_float(r[j]), sp, sg);
+      v[j] = __float_as_uint(sg);
+    }
+    if constexpr (TILE) {
+      tile_emit_f32(t, v, col0);
+    } else {
+      float* out = reinterpret_cast<float*>(e.out) + (long long)row * e.ld_out + col0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < N) out[j] = __uint_as_float(v[j]);
     }
   } else if constexpr (EPI == EPI_ACT) {
     uint32_t hi[16], lo[16];
@@ -308,34 +341,28 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
       hi[j >> 1] = h;
       lo[j >> 1] = ptx::pack_bf16(v[0] - ptx::bf16_lo(h), v[1] - ptx::bf16_hi(h));
     }
-    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
-    if (e.out_lo) {
-      uint4* ol =
-          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
-    }
+    if constexpr (TILE) tile_emit_bf16(t, hi, lo, e.out_lo != nullptr, col0);
+    else direct_emit_bf16(e, hi, lo, e.out_lo != nullptr, row, col0);
   } else if constexpr (EPI == EPI_DACT) {
-    int ar = row < e.aux_split ? row : row - e.aux_shift;
-    const uint4* ap = reinterpret_cast<const uint4*>(e.aux + (long long)ar * e.ld_aux + col0);
     uint32_t y[16], yl[16];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      uint4 t = ap[q];
-      y[4 * q] = t.x; y[4 * q + 1] = t.y; y[4 * q + 2] = t.z; y[4 * q + 3] = t.w;
-    }
-    if (e.aux_lo) {
-      const uint4* alp = reinterpret_cast<const uint4*>(e.aux_lo + (long long)ar * e.ld_aux + col0);
+    for (int q = 0; q < 16; ++q) { y[q] = 0u; yl[q] = 0u; }
+    if (row_ok) {
+      int ar = row < e.aux_split ? row : row - e.aux_shift;
+      const uint4* ap = reinterpret_cast<const uint4*>(e.aux + (long long)ar * e.ld_aux + col0);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        uint4 t = alp[q];
-        yl[4 * q] = t.x; yl[4 * q + 1] = t.y; yl[4 * q + 2] = t.z; yl[4 * q + 3] = t.w;
+        uint4 tt = ap[q];
+        y[4 * q] = tt.x; y[4 * q + 1] = tt.y; y[4 * q + 2] = tt.z; y[4 * q + 3] = tt.w;
       }
-    } else {
+      if (e.aux_lo) {
+        const uint4* alp = reinterpret_cast<const uint4*>(e.aux_lo + (long long)ar * e.ld_aux + col0);
 #pragma unroll
-      for (int q = 0; q < 16; ++q) yl[q] = 0u;
+        for (int q = 0; q < 4; ++q) {
+          uint4 tt = alp[q];
+          yl[4 * q] = tt.x; yl[4 * q + 1] = tt.y; yl[4 * q + 2] = tt.z; yl[4 * q + 3] = tt.w;
+        }
+      }
     }
     uint32_t hi[16], lo[16];
 #pragma unroll
@@ -348,45 +375,17 @@ __device__ __forceinline__ void epilogue_impl(const EpiArgs& e, const uint32_t (
       hi[j >> 1] = h;
       lo[j >> 1] = ptx::pack_bf16(v0 - ptx::bf16_lo(h), v1 - ptx::bf16_hi(h));
     }
-    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)row * e.ld_out + col0);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) o[q] = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
-    if (e.out_lo) {
-      uint4* ol =
-          reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out_lo) + (long long)row * e.ld_out + col0);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) ol[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
-    }
+    if constexpr (TILE) tile_emit_bf16(t, hi, lo, e.out_lo != nullptr, col0);
+    else direct_emit_bf16(e, hi, lo, e.out_lo != nullptr, row, col0);
   } else if constexpr (EPI == EPI_BCE) {
-    if (col0 + 32 <= N) bce_chunk<PRECISE, true>(e, r, row, col0, N, loss_acc, xw);
-    else bce_chunk<PRECISE, false>(e, r, row, col0, N, loss_acc, xw);
-  }
-}
-
-// Fast-mode BCE chunk leaving through the tile store: lane = row writes its 64 bytes into the warp's staging slot
-// (16-byte piece j of row l sits at l*64 + ((j ^ ((l >> 1) & 3)) << 4), the 64B-swizzle pattern, conflict-free), one
-// lane issues the TMA store.  Rows >= M and columns >= N are clipped by the tensor map.
-__device__ __forceinline__ void bce_chunk_tile(const EpiArgs& e, const CUtensorMap* tout, const uint32_t (&r)[32],
-                                               bool row_ok, int row0, int col0, int N, float& loss_acc, uint32_t xw,
-                                               uint8_t* slot, int lane) {
-  uint32_t hi[16], lo[16];
-  float acc;
-  if (col0 + 32 <= N) acc = bce_values<false, true>(e, r, col0, N, xw, hi, lo);
-  else acc = bce_values<false, false>(e, r, col0, N, xw, hi, lo);
-  if (row_ok) loss_acc += acc;
-  if (e.dbg & 1) return;
-  if (lane == 0) ptx::bulk_wait_read();   // the previous tile store has finished reading this slot
-  __syncwarp();
-  uint8_t* rowp = slot + lane * 64;
-  const int x = (lane >> 1) & 3;
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-    ptx::st_shared_v4(rowp + ((j ^ x) << 4), hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-  ptx::fence_proxy_async_smem();
-  __syncwarp();
-  if (lane == 0) {
-    ptx::tma_store_2d(tout, slot, col0, row0);
-    ptx::bulk_commit();
+    uint32_t hi[16], lo[16];
+    float acc;
+    if (col0 + 32 <= N) acc = bce_values<PRECISE, true>(e, r, col0, N, xw, hi, lo);
+    else acc = bce_values<PRECISE, false>(e, r, col0, N, xw, hi, lo);
+    if (row_ok) loss_acc += acc;
+    if (e.dbg & 1) return;     // diagnostic: no stores
+    if constexpr (TILE) tile_emit_bf16(t, hi, lo, PRECISE && e.out_lo != nullptr, col0);
+    else direct_emit_bf16(e, hi, lo, PRECISE && e.out_lo != nullptr, row, col0);
   }
 }
 
@@ -425,25 +424,30 @@ __device__ __forceinline__ void scatter_chunk(const EpiArgs& e, const uint32_t (
 }
 
 // Run-time (act, precise) -> compile-time variant, decided once per 32-column chunk (warp-uniform).
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const uint32_t (&r)[32], int row, int col0, int M,
-                                               int N, float& loss_acc, uint32_t xw = 0u) {
-  if (row >= M) return;
+template <int EPI, bool TILE>
+__device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const TileOut& t, const uint32_t (&r)[32], int row,
+                                               int col0, int M, int N, float& loss_acc, uint32_t xw = 0u) {
+  const bool row_ok = row < M;
+  if constexpr (!TILE) {
+    if (!row_ok) return;
+  }
   if constexpr (EPI == EPI_ACT || EPI == EPI_DACT) {
     if (e.act == ACT_TANH) {
-      if (e.precise) epilogue_impl<EPI, ACT_TANH, true>(e, r, row, col0, M, N, loss_acc, xw);
-      else epilogue_impl<EPI, ACT_TANH, false>(e, r, row, col0, M, N, loss_acc, xw);
+      if (e.precise) epilogue_impl<EPI, ACT_TANH, true, TILE>(e, t, r, row, row_ok, col0, N, loss_acc, xw);
+      else epilogue_impl<EPI, ACT_TANH, false, TILE>(e, t, r, row, row_ok, col0, N, loss_acc, xw);
     } else {
-      if (e.precise) epilogue_impl<EPI, ACT_ELU, true>(e, r, row, col0, M, N, loss_acc, xw);
-      else epilogue_impl<EPI, ACT_ELU, false>(e, r, row, col0, M, N, loss_acc, xw);
+      if (e.precise) epilogue_impl<EPI, ACT_ELU, true, TILE>(e, t, r, row, row_ok, col0, N, loss_acc, xw);
+      else epilogue_impl<EPI, ACT_ELU, false, TILE>(e, t, r, row, row_ok, col0, N, loss_acc, xw);
     }
   } else if constexpr (EPI == EPI_BCE) {
-    if (e.precise) epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc, xw);
-    else epilogue_impl<EPI, ACT_NONE, false>(e, r, row, col0, M, N, loss_acc, xw);
+    if (e.precise) epilogue_impl<EPI, ACT_NONE, true, TILE>(e, t, r, row, row_ok, col0, N, loss_acc, xw);
+    else epilogue_impl<EPI, ACT_NONE, false, TILE>(e, t, r, row, row_ok, col0, N, loss_acc, xw);
   } else {
-    epilogue_impl<EPI, ACT_NONE, true>(e, r, row, col0, M, N, loss_acc, xw);
+    epilogue_impl<EPI, ACT_NONE, true, TILE>(e, t, r, row, row_ok, col0, N, loss_acc, xw);
   }
 }
+
+static_assert(sizeof(GemmArgs) <= 4096, "kernel parameter space");
 
 // ---------------------------------------------------------------------------- the kernel
 template <bool A_MN, bool B_MN, int EPI>
@@ -612,14 +616,15 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
         if constexpr (EPI == EPI_SCATTER_F32) {
           scatter_chunk(e, r, row, it.n0 + c * 32, args.M, args.N,
                         smem + kStages * kStageBytes + 256 + (warp - 2) * kScatterStageBytes, lane);
-        } else if constexpr (EPI == EPI_BCE) {
-          if (args.use_tout)
-            bce_chunk_tile(e, &args.tout, r, row < args.M, it.m0 + q * 32, it.n0 + c * 32, args.N, loss_acc, xwk,
-                           smem + kTileStageOffset + (warp - 2) * kTileStageBytes, lane);
-          else
-            epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
         } else {
-          epilogue_chunk<EPI>(e, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
+          TileOut t;
+          t.hi = &args.tout[it.g][0];
+          t.lo = &args.tout[it.g][1];
+          t.slot = smem + kTileStageOffset + (warp - 2) * 2048;
+          t.lane = lane;
+          t.row0 = it.m0 + q * 32;
+          t.reduce = e.atomic;
+          epilogue_chunk<EPI, true>(e, t, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
         }
       }
       if (!arrived) {
@@ -627,9 +632,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
         ptx::mbar_arrive(&tempty_bar[acc]);
       }
     }
-    if constexpr (EPI == EPI_SCATTER_F32) ptx::bulk_wait_all();   // all row segments have left before the CTA exits
+    ptx::bulk_wait_all();   // every tile store / row segment this thread issued has left before the CTA exits
     if constexpr (EPI == EPI_BCE) {
-      if (args.use_tout && lane == 0) ptx::bulk_wait_all();
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
       if (lane == 0 && total_work > 0) atomicAdd(args.epi[0].scalar, loss_acc * args.epi[0].alpha);

@@ -612,6 +612,9 @@ __device__ __forceinline__ uint4 expand_byte(uint32_t b) {
   return make_uint4(lo.x, lo.y, hi.x, hi.y);
 }
 
+__device__ uint4 g_expand_lut[256];           // byte of 8 pixels -> 8 bf16 (0.0 / 1.0), filled by kernels_init()
+__global__ void fill_expand_lut_kernel() { g_expand_lut[threadIdx.x] = expand_byte(threadIdx.x); }
+
 __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t seed, uint64_t step, int B, int side,
                                                                      uint32_t inv_side /* ceil(2^32 / side) */,
                                                                      __nv_bfloat16* planes, long long ld,
@@ -620,18 +623,18 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
   const int D = side * side;
   const int nwords = (D + 31) >> 5;
   // dynamic shared memory, sized by the canvas so that a generator CTA fits on an SM next to a resident GEMM CTA:
-  // [lut: 256 x uint4 | lock | key | rot bitmaps, (nwords + 8) words each]
+  // [lock | key | rot bitmaps, (nwords + 8) words each] = 15 KiB at 200 x 200; the byte -> 8 bf16 table (4 KiB) is
+  // read through L1 from global memory (g_expand_lut) to stay under what a 210 KiB GEMM CTA leaves free
   extern __shared__ uint4 gen_smem[];
-  uint4* lut = gen_smem;                       // byte of 8 pixels -> 8 bf16
+  const uint4* __restrict__ lut = g_expand_lut;
   const int bm_pitch = (nwords + 8 + 3) & ~3;
-  uint32_t* const bm_base = reinterpret_cast<uint32_t*>(gen_smem + 256);
+  uint32_t* const bm_base = reinterpret_cast<uint32_t*>(gen_smem);
   uint32_t* const bm[3] = {bm_base, bm_base + bm_pitch, bm_base + 2 * bm_pitch};   // 0 lock, 1 key, 2 rot
   __shared__ Prim prims[2][kPrims];
   __shared__ int rot_q14[2];
   __shared__ int rot_radius;                   // every lock pixel lies within this distance of the centre
   __shared__ int counts[kLabelRots];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x < 256) lut[threadIdx.x] = expand_byte(threadIdx.x);
   // persistent: the grid is at most one CTA per SM, so the generator shares every SM with the step's GEMM CTA
   // instead of displacing it
   for (int i = blockIdx.x; i < B; i += gridDim.x) {
@@ -738,7 +741,7 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
   for (int ch = threadIdx.x; ch < chunks; ch += kGenThreads) {
     uint4 vl, vr, vk;
     if (ch < data_chunks) {
-      vl = lut[bl[ch]]; vr = lut[br[ch]]; vk = lut[bk[ch]];
+      vl = __ldg(lut + bl[ch]); vr = __ldg(lut + br[ch]); vk = __ldg(lut + bk[ch]);
     } else {
       vl = vr = vk = make_uint4(ch == data_chunks ? 0x00003F80u : 0u, 0u, 0u, 0u);   // bias column (1.0), then zero pad
     }
@@ -756,7 +759,7 @@ void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16
   // same (maximum) shared-memory carveout as the GEMM kernels: an SM only changes its carveout when it is idle, so a
   // different preference here would make every overlapped GEMM CTA wait for the generator to drain
   const int nwords = (side * side + 31) / 32;
-  const size_t smem = 256 * sizeof(uint4) + 3 * (size_t)((nwords + 8 + 3) & ~3) * sizeof(uint32_t);
+  const size_t smem = 3 * (size_t)((nwords + 8 + 3) & ~3) * sizeof(uint32_t);
   generate_pairs_kernel<<<B < max_ctas ? B : max_ctas, kGenThreads, smem, s>>>(seed, step, B, side, inv_side, planes, ld, xbits, xb_ld, labels,
                                                      rot_cs_sn);
 }
@@ -801,6 +804,8 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(planes_to_interleaved_kernel);
   MAGIC_MAX_CARVEOUT(generate_pairs_kernel);
   MAGIC_MAX_CARVEOUT(pack_lock_bits_kernel);
+  fill_expand_lut_kernel<<<1, 256>>>();
+  cudaDeviceSynchronize();      // init time only: the generator reads the table from its own stream
   cudaGetLastError();
 }
 
