@@ -131,6 +131,9 @@ Engine::~Engine() {
   if (comm_ && g_nccl.destroy) g_nccl.destroy(comm_);
   if (comm_stream_) cudaStreamDestroy(comm_stream_);
   if (gen_stream_) cudaStreamDestroy(gen_stream_);
+  if (aux_stream_) { cudaStreamSynchronize(aux_stream_); cudaStreamDestroy(aux_stream_); }
+  if (ev_aux_fork_) cudaEventDestroy(ev_aux_fork_);
+  if (ev_aux_join_) cudaEventDestroy(ev_aux_join_);
   if (ev_gate_) cudaEventDestroy(ev_gate_);
   for (auto& b : in_) { if (b.ready) cudaEventDestroy(b.ready); if (b.consumed) cudaEventDestroy(b.consumed); }
   for (auto& e : ev_bwd_) if (e) cudaEventDestroy(e);
@@ -276,6 +279,10 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
     MAGIC_CUDA(cudaEventCreateWithFlags(&b.consumed, cudaEventDisableTiming));
   }
   MAGIC_CUDA(cudaStreamCreateWithFlags(&gen_stream_, cudaStreamNonBlocking));
+  MAGIC_CUDA(cudaStreamCreateWithFlags(&aux_stream_, cudaStreamNonBlocking));
+  MAGIC_CUDA(cudaEventCreateWithFlags(&ev_aux_fork_, cudaEventDisableTiming));
+  MAGIC_CUDA(cudaEventCreateWithFlags(&ev_aux_join_, cudaEventDisableTiming));
+  if (const char* ea = getenv("MAGIC_EARLY_ADAM")) early_adam_ok_ = atoi(ea) != 0;
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_gate_, cudaEventDisableTiming));
   if (const char* g = getenv("MAGIC_GEN_GATE")) gen_gate_ = atoi(g) != 0;   // tuning knob, default on
   H_.resize(E);
@@ -740,6 +747,18 @@ std::string Engine::run_backward(int* launches) {
     MAGIC_TRY(allreduce(g1_ + n_both, (size_t)(n_total - n_both), comm_stream_));
   }
   MAGIC_TRY(launch(pl_dg_h1_, launches, "gemm.dgrad_small"));
+  if (early_adam_) {
+    // The decoder's gradients are final and nothing in this step reads its weights any more: update them now, on
+    // the side stream, while the (tensor-bound) encoder backward keeps the main stream busy.
+    MAGIC_CUDA(cudaEventRecord(ev_aux_fork_, stream));
+    MAGIC_CUDA(cudaStreamWaitEvent(aux_stream_, ev_aux_fork_, 0));
+    AdamArgs a = adam_;
+    a.begin = n_both;
+    a.thin = 2 * num_sms;
+    prof_begin("adam.decoder", 0, aux_stream_); adam_dual(a, aux_stream_); prof_end(aux_stream_);
+    MAGIC_CUDA(cudaEventRecord(ev_aux_join_, aux_stream_));
+    *launches += 1;
+  }
   LatentArgs la = latent_args(nullptr, in_[cur_].labels);
   prof_begin("latent.backward"); latent_backward(la, stream); prof_end();
   *launches += 1;
@@ -790,6 +809,16 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   if (!d_labels && !in_[cur_].has_labels) return "step: no labels (pass d_labels or call magic_generate_batch first)";
   if (d_labels) { labels_ext_ = d_labels; have_labels_ext_ = true; } else { have_labels_ext_ = false; }
   int launches = 0;
+  const double b1 = cfg.beta1, b2 = cfg.beta2;
+  const double corr = sqrt(1.0 - pow(b2, (double)(t + 1))) / (1.0 - pow(b1, (double)(t + 1)));
+  memset(&adam_, 0, sizeof adam_);
+  adam_.p = p_; adam_.g1 = g1_; adam_.g2 = g2_; adam_.m1 = m1_; adam_.v1 = v1_; adam_.m2 = m2_; adam_.v2 = v2_;
+  adam_.w_hi = w_hi_; adam_.w_lo = w_lo_;
+  adam_.n_both = n_both; adam_.n_total = n_total;
+  adam_.lr_t1 = (float)(cfg.lr1 * corr);
+  adam_.lr_t2 = (float)(cfg.lr2 * corr);
+  adam_.beta1 = cfg.beta1; adam_.beta2 = cfg.beta2; adam_.eps = cfg.eps;
+  early_adam_ = apply && cfg.world == 1 && early_adam_ok_;
   std::string err = run_forward(d_eps3, true, &launches);
   if (err.empty()) err = run_backward(&launches);
   have_labels_ext_ = false;
@@ -797,8 +826,6 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   MAGIC_TRY(allreduce(statbuf_, 4, stream));   // loss scalars: local sums / Bg add up to the global means
   if (d_losses5) { launch_chain(finalize_losses_kernel, dim3(1), dim3(32), 0, stream, (const float*)statbuf_, d_losses5); ++launches; }
   if (d_distance) MAGIC_CUDA(cudaMemcpyAsync(d_distance, dist_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
-  const double b1 = cfg.beta1, b2 = cfg.beta2;
-  const double corr = sqrt(1.0 - pow(b2, (double)(t + 1))) / (1.0 - pow(b1, (double)(t + 1)));
   if (dp_fused_) {
     // The loss all-reduce above is also the barrier that says: every rank's partial gradients have landed in the
     // owners' staging buffers (kernel completion makes peer stores visible; NCCL orders the ranks).
@@ -821,16 +848,11 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
     grads_sharded_ = true;
   } else if (apply) {
     ++t;
-    AdamArgs a;
-    memset(&a, 0, sizeof a);
-    a.p = p_; a.g1 = g1_; a.g2 = g2_; a.m1 = m1_; a.v1 = v1_; a.m2 = m2_; a.v2 = v2_;
-    a.w_hi = w_hi_; a.w_lo = w_lo_;
-    a.n_both = n_both; a.n_total = n_total;
-    a.lr_t1 = (float)(cfg.lr1 * corr);
-    a.lr_t2 = (float)(cfg.lr2 * corr);
-    a.beta1 = cfg.beta1; a.beta2 = cfg.beta2; a.eps = cfg.eps;
+    AdamArgs a = adam_;
+    if (early_adam_) a.n_total = n_both;     // the decoder range is already in flight on aux_stream_
     prof_begin("adam.dual"); adam_dual(a, stream); prof_end();
     ++launches;
+    if (early_adam_) MAGIC_CUDA(cudaStreamWaitEvent(stream, ev_aux_join_, 0));
     stats.steps = t;
   }
   MAGIC_CUDA(cudaGetLastError());

@@ -160,6 +160,12 @@ class Engine {
   NcclApi* nccl_ = nullptr;
   void* comm_ = nullptr;
   cudaStream_t comm_stream_ = nullptr;
+  // single GPU: the decoder's Adam update runs on aux_stream_ under the encoder's backward pass (HBM-bound next to
+  // tensor-bound work); adam_ holds the step's arguments, early_adam_ says the decoder range has been launched
+  cudaStream_t aux_stream_ = nullptr;
+  cudaEvent_t ev_aux_fork_ = nullptr, ev_aux_join_ = nullptr;
+  AdamArgs adam_;
+  bool early_adam_ = false, early_adam_ok_ = true;
   cudaEvent_t ev_bwd_[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_comm_ = nullptr;
   std::string allreduce(float* buf, size_t n, cudaStream_t s);

@@ -97,6 +97,7 @@ struct GemmArgs {
   int tiles_m, tiles_n;
   int m_fastest;     // tile order: consecutive work items walk M first (B is the large operand) or N first
   int cluster_m;     // CTAs per cluster along M (1, 2 or 4): they share the N tile and receive B by TMA multicast
+  long long* trace;  // diagnostics: [grid][16] clock64 stamps of the phases of each CTA (selftest "trace"), or nullptr
   CUtensorMap tout[kMaxGroups][2];   // output tiles (box 32 cols x 32 rows): [g][0] fp32 or bf16 hi plane, [g][1] lo plane
 };
 
@@ -452,6 +453,18 @@ static_assert(sizeof(GemmArgs) <= 4096, "kernel parameter space");
 // ---------------------------------------------------------------------------- the kernel
 template <bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
+#define MAGIC_TR(slot)                                                                  \
+  do {                                                                                  \
+    if (args.trace) args.trace[(size_t)blockIdx.x * 16 + (slot)] = clock64();           \
+  } while (0)
+  if (threadIdx.x == 0) {
+    MAGIC_TR(0);
+    if (args.trace) {
+      unsigned long long gt;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+      args.trace[(size_t)blockIdx.x * 16 + 11] = (long long)gt;
+    }
+  }
   extern __shared__ uint8_t smem_raw[];
   // 128-byte swizzle atoms need 1024-byte aligned stage bases
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -496,7 +509,9 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
   else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  if (threadIdx.x == 0) MAGIC_TR(1);
   ptx::grid_dep_wait();     // everything above overlapped the previous kernel's tail; its outputs are visible from here
+  if (threadIdx.x == 0) MAGIC_TR(2);
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (one thread)
@@ -528,6 +543,7 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
             ptx::tma_load_3d_multicast(tb, &full_bar[stage], sb + crank * per * kAtomBytes, 0, k0,
                                        (it.n0 >> 6) + crank * per, cmask);
           }
+          if (w == work0 && kb == it.kb0) MAGIC_TR(3);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -551,6 +567,7 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
+          if (w == work0 && kb == it.kb0) MAGIC_TR(4);
           const uint32_t a_base = ptx::smem_u32(smem_a + stage * kStageBytesA);
           const uint32_t b_base = ptx::smem_u32(smem_b + stage * kStageBytesB);
 #pragma unroll
@@ -564,7 +581,10 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
         ptx::umma_commit(&tfull_bar[acc]);        // accumulator complete -> epilogue
+        if (w == work0) MAGIC_TR(5);
       }
+      MAGIC_TR(6);
+      if (args.trace) args.trace[(size_t)blockIdx.x * 16 + 12] = iter;
       // All of this CTA's MMAs are issued: from here only its last epilogue remains, so the next kernel of the step
       // may become resident on SMs as they free and run its prologue (launch.cuh).  Triggering earlier parks the
       // following kernels' CTAs on the SMs for the whole duration and starves the generator's side stream.
@@ -598,6 +618,7 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
       }
       ptx::mbar_wait(&tfull_bar[acc], acc_phase);
       ptx::tc_fence_after();
+      if (warp == 2 && lane == 0 && w == work0) MAGIC_TR(7);
       bool arrived = false;
 #pragma unroll
       for (int k = 0; k < kMaxOwn; ++k) {
@@ -632,7 +653,9 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
         ptx::mbar_arrive(&tempty_bar[acc]);
       }
     }
+    if (warp == 2 && lane == 0) MAGIC_TR(8);
     ptx::bulk_wait_all();   // every tile store / row segment this thread issued has left before the CTA exits
+    if (warp == 2 && lane == 0) MAGIC_TR(9);
     if constexpr (EPI == EPI_BCE) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
@@ -647,6 +670,8 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
+  if (threadIdx.x == 0) MAGIC_TR(10);
+#undef MAGIC_TR
 }
 
 }  // namespace magic

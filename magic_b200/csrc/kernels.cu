@@ -57,8 +57,8 @@ void zero_fill(void* ptr, size_t bytes, cudaStream_t s) {   // ptr 16-byte align
 // (8c/vae.py:358-371, 275-288)  Thread <-> latent column, CTA <-> slab of kLatSlab pairs: loads are coalesced along
 // the latent axis and the batch-axis sums of squares the cosine metric needs stay in registers until the end.
 constexpr int kLatWarps = 8;
-constexpr int kLatRowsPerWarp = 4;
-constexpr int kLatSlab = 16;
+constexpr int kLatRowsPerWarp = 2;
+constexpr int kLatSlab = 4;    // 1024 CTAs at B = 4096: enough warps to hide the load latencies (40 -> 15 us, r01h)
 
 __global__ void __launch_bounds__(256) latent_forward_kernel(LatentArgs a) {
   ptx::grid_dep_wait();
@@ -115,12 +115,18 @@ __global__ void __launch_bounds__(256) latent_forward_kernel(LatentArgs a) {
 // ------------------------------------------------------------------ metric loss (8c/vae.py:300-307, 438-452)
 __global__ void __launch_bounds__(kLatWarps * 32) latent_metric_kernel(LatentArgs a) {
   ptx::grid_dep_wait();
-  extern __shared__ float sm[];   // [L] column sums S_j (cosine)
+  extern __shared__ float sm[];   // cosine: [L] column sums S_j | [L] 1/||a_j|| | [L] 1/||b_j||
   const int L = a.L, B = a.B;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool cosine = a.metric == METRIC_COSINE;
+  float* const s_ra = sm + L;
+  float* const s_rb = sm + 2 * L;
   if (cosine) {
-    for (int j = threadIdx.x; j < L; j += blockDim.x) sm[j] = 0.f;
+    for (int j = threadIdx.x; j < L; j += blockDim.x) {
+      sm[j] = 0.f;
+      s_ra[j] = rsqrtf(fmaxf(a.colsq[j], 1e-12f));
+      s_rb[j] = rsqrtf(fmaxf(a.colsq[L + j], 1e-12f));
+    }
     __syncthreads();
   }
   float tl = 0.f;
@@ -132,8 +138,7 @@ __global__ void __launch_bounds__(kLatWarps * 32) latent_metric_kernel(LatentArg
     float dist = 0.f;
     for (int j = lane; j < L; j += 32) {
       if (cosine) {
-        const float ra = rsqrtf(fmaxf(a.colsq[j], 1e-12f)), rb = rsqrtf(fmaxf(a.colsq[L + j], 1e-12f));
-        dist += (zl[j] * ra) * (zk[j] * rb);
+        dist += (zl[j] * s_ra[j]) * (zk[j] * s_rb[j]);
       } else {
         const float d = zl[j] - zk[j];
         dist += d * d;
@@ -150,10 +155,7 @@ __global__ void __launch_bounds__(kLatWarps * 32) latent_metric_kernel(LatentArg
       tl += err * err;
     }
     if (cosine) {
-      for (int j = lane; j < L; j += 32) {
-        const float ra = rsqrtf(fmaxf(a.colsq[j], 1e-12f)), rb = rsqrtf(fmaxf(a.colsq[L + j], 1e-12f));
-        atomicAdd(&sm[j], gi * (zl[j] * ra) * (zk[j] * rb));
-      }
+      for (int j = lane; j < L; j += 32) atomicAdd(&sm[j], gi * (zl[j] * s_ra[j]) * (zk[j] * s_rb[j]));
     }
   }
   if (lane == 0 && tl != 0.f) atomicAdd(&a.sums[3], tl * a.inv_bg);
@@ -218,7 +220,7 @@ void latent_forward(const LatentArgs& a, cudaStream_t s) {
   launch_chain(latent_forward_kernel, dim3((a.L + 255) / 256, (a.B + kLatSlab - 1) / kLatSlab), dim3(256), 0, s, a);
 }
 void latent_metric(const LatentArgs& a, cudaStream_t s) {
-  launch_chain(latent_metric_kernel, dim3(lat_blocks(a.B)), dim3(kLatWarps * 32), sizeof(float) * a.L, s, a);
+  launch_chain(latent_metric_kernel, dim3(lat_blocks(a.B)), dim3(kLatWarps * 32), sizeof(float) * 3 * a.L, s, a);
 }
 void latent_backward(const LatentArgs& a, cudaStream_t s) {
   const long long n = (long long)a.B * a.L;
@@ -237,43 +239,49 @@ __device__ __forceinline__ float adam_one(float g, float& m, float& v, float lr_
 
 __global__ void __launch_bounds__(256) adam_dual_kernel(AdamArgs a) {
   ptx::grid_dep_wait();
-  const long long i4 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (i4 >= a.n_total) return;
-  float4 p = *reinterpret_cast<const float4*>(a.p + i4);
-  float pv[4] = {p.x, p.y, p.z, p.w};
-  {
-    const float4 g = *reinterpret_cast<const float4*>(a.g1 + i4);
-    float4 m = *reinterpret_cast<const float4*>(a.m1 + i4), v = *reinterpret_cast<const float4*>(a.v1 + i4);
-    pv[0] -= adam_one(g.x, m.x, v.x, a.lr_t1, a.beta1, a.beta2, a.eps);
-    pv[1] -= adam_one(g.y, m.y, v.y, a.lr_t1, a.beta1, a.beta2, a.eps);
-    pv[2] -= adam_one(g.z, m.z, v.z, a.lr_t1, a.beta1, a.beta2, a.eps);
-    pv[3] -= adam_one(g.w, m.w, v.w, a.lr_t1, a.beta1, a.beta2, a.eps);
-    *reinterpret_cast<float4*>(a.m1 + i4) = m;
-    *reinterpret_cast<float4*>(a.v1 + i4) = v;
-  }
-  if (i4 < a.n_both) {
-    const float4 g = *reinterpret_cast<const float4*>(a.g2 + i4);
-    float4 m = *reinterpret_cast<const float4*>(a.m2 + i4), v = *reinterpret_cast<const float4*>(a.v2 + i4);
-    pv[0] -= adam_one(g.x, m.x, v.x, a.lr_t2, a.beta1, a.beta2, a.eps);
-    pv[1] -= adam_one(g.y, m.y, v.y, a.lr_t2, a.beta1, a.beta2, a.eps);
-    pv[2] -= adam_one(g.z, m.z, v.z, a.lr_t2, a.beta1, a.beta2, a.eps);
-    pv[3] -= adam_one(g.w, m.w, v.w, a.lr_t2, a.beta1, a.beta2, a.eps);
-    *reinterpret_cast<float4*>(a.m2 + i4) = m;
-    *reinterpret_cast<float4*>(a.v2 + i4) = v;
-  }
-  *reinterpret_cast<float4*>(a.p + i4) = make_float4(pv[0], pv[1], pv[2], pv[3]);
-  const uint32_t h0 = ptx::pack_bf16(pv[0], pv[1]), h1 = ptx::pack_bf16(pv[2], pv[3]);
-  *reinterpret_cast<uint2*>(a.w_hi + i4) = make_uint2(h0, h1);
-  if (a.w_lo) {
-    const uint32_t l0 = ptx::pack_bf16(pv[0] - ptx::bf16_lo(h0), pv[1] - ptx::bf16_hi(h0));
-    const uint32_t l1 = ptx::pack_bf16(pv[2] - ptx::bf16_lo(h1), pv[3] - ptx::bf16_hi(h1));
-    *reinterpret_cast<uint2*>(a.w_lo + i4) = make_uint2(l0, l1);
+  // grid-stride: the full-width launch covers the range in one pass; the side-stream launch (a.thin) uses two CTAs
+  // per SM so that it leaves room for the GEMM CTAs it runs beside
+  const long long stride = (long long)gridDim.x * blockDim.x * 4;
+  for (long long i4 = a.begin + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i4 < a.n_total; i4 += stride) {
+    float4 p = *reinterpret_cast<const float4*>(a.p + i4);
+    float pv[4] = {p.x, p.y, p.z, p.w};
+    {
+      const float4 g = *reinterpret_cast<const float4*>(a.g1 + i4);
+      float4 m = *reinterpret_cast<const float4*>(a.m1 + i4), v = *reinterpret_cast<const float4*>(a.v1 + i4);
+      pv[0] -= adam_one(g.x, m.x, v.x, a.lr_t1, a.beta1, a.beta2, a.eps);
+      pv[1] -= adam_one(g.y, m.y, v.y, a.lr_t1, a.beta1, a.beta2, a.eps);
+      pv[2] -= adam_one(g.z, m.z, v.z, a.lr_t1, a.beta1, a.beta2, a.eps);
+      pv[3] -= adam_one(g.w, m.w, v.w, a.lr_t1, a.beta1, a.beta2, a.eps);
+      *reinterpret_cast<float4*>(a.m1 + i4) = m;
+      *reinterpret_cast<float4*>(a.v1 + i4) = v;
+    }
+    if (i4 < a.n_both) {
+      const float4 g = *reinterpret_cast<const float4*>(a.g2 + i4);
+      float4 m = *reinterpret_cast<const float4*>(a.m2 + i4), v = *reinterpret_cast<const float4*>(a.v2 + i4);
+      pv[0] -= adam_one(g.x, m.x, v.x, a.lr_t2, a.beta1, a.beta2, a.eps);
+      pv[1] -= adam_one(g.y, m.y, v.y, a.lr_t2, a.beta1, a.beta2, a.eps);
+      pv[2] -= adam_one(g.z, m.z, v.z, a.lr_t2, a.beta1, a.beta2, a.eps);
+      pv[3] -= adam_one(g.w, m.w, v.w, a.lr_t2, a.beta1, a.beta2, a.eps);
+      *reinterpret_cast<float4*>(a.m2 + i4) = m;
+      *reinterpret_cast<float4*>(a.v2 + i4) = v;
+    }
+    *reinterpret_cast<float4*>(a.p + i4) = make_float4(pv[0], pv[1], pv[2], pv[3]);
+    const uint32_t h0 = ptx::pack_bf16(pv[0], pv[1]), h1 = ptx::pack_bf16(pv[2], pv[3]);
+    *reinterpret_cast<uint2*>(a.w_hi + i4) = make_uint2(h0, h1);
+    if (a.w_lo) {
+      const uint32_t l0 = ptx::pack_bf16(pv[0] - ptx::bf16_lo(h0), pv[1] - ptx::bf16_hi(h0));
+      const uint32_t l1 = ptx::pack_bf16(pv[2] - ptx::bf16_lo(h1), pv[3] - ptx::bf16_hi(h1));
+      *reinterpret_cast<uint2*>(a.w_lo + i4) = make_uint2(l0, l1);
+    }
   }
 }
 
 void adam_dual(const AdamArgs& a, cudaStream_t s) {
-  const long long n4 = (a.n_total + 3) / 4;
-  launch_chain(adam_dual_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, s, a);
+  const long long n4 = (a.n_total - a.begin + 3) / 4;
+  if (n4 <= 0) return;
+  long long blocks = (n4 + 255) / 256;
+  if (a.thin > 0 && blocks > a.thin) blocks = a.thin;
+  launch_chain(adam_dual_kernel, dim3((unsigned)blocks), dim3(256), 0, s, a);
 }
 
 // ------------------------------------------------------------------ data parallel: sharded reduce + dual Adam

@@ -49,10 +49,12 @@ struct AdamArgs {
   const float* g1; const float* g2;
   float* m1; float* v1; float* m2; float* v2;
   __nv_bfloat16* w_hi; __nv_bfloat16* w_lo;   // bf16 shadow (lo may be null)
+  long long begin;                // first element of the range to update (multiple of 4); the range ends at n_total
   long long n_both;               // leading elements updated by both optimisers (encoder)
   long long n_total;              // all elements (encoder + used decoder)
   float lr_t1, lr_t2;             // lr * sqrt(1-beta2^t) / (1-beta1^t)
   float beta1, beta2, eps;
+  int thin;                       // > 0: cap the grid at this many CTAs (grid-stride), for a launch that runs beside GEMMs
 };
 void adam_dual(const AdamArgs& a, cudaStream_t s);
 // Data parallel: sharded reduce + dual Adam + shadow all-gather over peer memory.

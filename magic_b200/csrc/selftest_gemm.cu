@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <cmath>
 #include <vector>
+#include <algorithm>
 #include <string>
 #include "gemm.h"
 
@@ -253,6 +254,35 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   GemmPlan pl;
   std::string err = gemm_plan(p, sms, &pl);
   if (!err.empty()) { printf("plan error: %s\n", err.c_str()); return; }
+  if (getenv("MAGIC_TRACE")) {   // per-CTA phase stamps of one warm launch
+    long long* tr;
+    CK(cudaMalloc(&tr, sizeof(long long) * 16 * pl.grid));
+    for (int i = 0; i < 3; ++i) gemm_launch(pl, 0, &err);
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemset(tr, 0, sizeof(long long) * 16 * pl.grid));
+    pl.args.trace = tr;
+    gemm_launch(pl, 0, &err);
+    CK(cudaDeviceSynchronize());
+    pl.args.trace = nullptr;
+    std::vector<long long> h((size_t)16 * pl.grid);
+    CK(cudaMemcpy(h.data(), tr, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost));
+    const char* names[11] = {"entry", "prologue done", "dep wait done", "first TMA issued", "first stage landed",
+                             "tile 0 MMAs issued", "all MMAs issued", "epi: tile 0 acc ready", "epi: loop done",
+                             "epi: stores drained", "exit"};
+    long long gmin = h[11], gmax = h[11];
+    for (int c = 0; c < pl.grid; ++c) { gmin = std::min(gmin, h[(size_t)c * 16 + 11]); gmax = std::max(gmax, h[(size_t)c * 16 + 11]); }
+    printf("trace %-28s grid=%d, CTA start spread %.2f us; mean / max cycles since CTA entry:\n", label, pl.grid, (gmax - gmin) * 1e-3);
+    for (int sidx = 1; sidx <= 10; ++sidx) {
+      double sum = 0; long long mx = 0; int n = 0;
+      for (int c = 0; c < pl.grid; ++c) {
+        long long v = h[(size_t)c * 16 + sidx], b = h[(size_t)c * 16];
+        if (v == 0) continue;
+        sum += (double)(v - b); mx = std::max(mx, v - b); ++n;
+      }
+      if (n) printf("   %-24s %9.0f %9lld   (%.2f / %.2f us at 1.9 GHz)\n", names[sidx], sum / n, mx, sum / n / 1900.0, mx / 1900.0);
+    }
+    CK(cudaFree(tr));
+  }
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   for (int i = 0; i < 3; ++i) gemm_launch(pl, 0, &err);
