@@ -339,8 +339,16 @@ def run_b200(args):
                 ach, peak, unit = amount / avg_s * 1e-12, pk["tf_sustained"], "TFLOP/s"
             else:
                 ach, peak, unit = amount / avg_s * 1e-9, pk["hbm"], "GB/s"
+            traffic, traffic_src = None, None
+            try:
+                tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+                ent = tj.get("%s/%d/%s" % (args.exp, B, args.precision), {}).get(tag) if world == 1 else None
+                if ent:
+                    traffic, traffic_src = ent["bytes"], ent["source"]
+            except Exception:
+                traffic = None
             roof = {"kernel": tag, "bound": kind, "achieved": round(ach, 2), "peak": peak, "unit": unit,
-                    "frac": round(ach / peak, 4), "traffic": None, "avg_launch_ms": round(ms / n, 5),
+                    "frac": round(ach / peak, 4), "traffic": traffic, "traffic_unit": "dram bytes per launch (ncu)", "traffic_source": traffic_src, "avg_launch_ms": round(ms / n, 5),
                     "launches_timed": n, "measured_over": "%d steps with an event pair around every launch, run right "
                     "after the timed region on the same inputs" % Kp, "peak_source": pk["source"] + (" (sustained)" if kind == "tensor" else ""),
                     "algorithmic_per_launch": amount, "share_of_step": shares[tag]}
