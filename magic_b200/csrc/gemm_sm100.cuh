@@ -84,7 +84,7 @@ struct EpiArgs {
   int src_rank;
   int world;
   int gran_shift;
-  int dbg;           // diagnostics (MAGIC_EPI_DBG): 1 = BCE epilogue without stores, 2 = without the transcendental math
+  int dbg;           // diagnostics (MAGIC_EPI_DBG): 1 = BCE epilogue without stores, 4 = no epilogue work at all (main loop only)
 };
 
 struct GemmArgs {
@@ -97,7 +97,7 @@ struct GemmArgs {
   int tiles_m, tiles_n;
   int m_fastest;     // tile order: consecutive work items walk M first (B is the large operand) or N first
   int cluster_m;     // CTAs per cluster along M (1, 2 or 4): they share the N tile and receive B by TMA multicast
-  long long* trace;  // diagnostics: [grid][16] clock64 stamps of the phases of each CTA (selftest "trace"), or nullptr
+  long long* trace;  // diagnostics: [grid][64] clock64 stamps of the phases of each CTA (selftest "trace"), or nullptr
   CUtensorMap tout[kMaxGroups][2];   // output tiles (box 32 cols x 32 rows): [g][0] fp32 or bf16 hi plane, [g][1] lo plane
 };
 
@@ -184,50 +184,88 @@ __device__ __forceinline__ void softplus_sigmoid(float b, float& sp, float& sg) 
 template <bool PRECISE, bool FULL>
 __device__ __forceinline__ float bce_values(const EpiArgs& e, const uint32_t (&r)[32], int col0, int N, uint32_t xw,
                                             uint32_t (&hi)[16], uint32_t (&lo)[16]) {
-  float acc = 0.f;
   const int valid = FULL ? 32 : N - col0;
+  if constexpr (PRECISE) {
+    float acc = 0.f;
 #pragma unroll
-  for (int j = 0; j < 32; j += 2) {
-    float d[2];
+    for (int j = 0; j < 32; j += 2) {
+      float d[2];
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const uint32_t sign = (xw << (31 - (j + q))) & 0x80000000u;
-      const float sv = __uint_as_float(r[j + q] ^ sign);
-      float sp, sg;
-      if constexpr (PRECISE) {
+      for (int q = 0; q < 2; ++q) {
+        const uint32_t sign = (xw << (31 - (j + q))) & 0x80000000u;
+        const float sv = __uint_as_float(r[j + q] ^ sign);
+        float sp, sg;
         softplus_sigmoid<true>(sv, sp, sg);
-      } else if (e.dbg & 2) {   // diagnostic: no transcendental math
-        sg = sv; sp = sv;
-      } else {
-        float t;
-        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fabsf(sv) * -1.4426950408889634f));
-        float rr;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rr) : "f"(1.f + t));
-        // sigmoid(s) = 0.5 + sgn(s) * (0.5 - t/(1+t))
-        const float h = fmaf(-t, rr, 0.5f);
-        sg = 0.5f + __uint_as_float(__float_as_uint(h) ^ (__float_as_uint(sv) & 0x80000000u));
-        // log1p(t) = t * P(t): degree-3 minimax fit of log1p(t)/t on (0,1], max relative error 4.8e-4 (the loss is a
-        // reported scalar; the gradient path uses sg only)
-        float p = fmaf(t, -0.0762659232f, 0.256918443f);
-        p = fmaf(t, p, -0.487505179f);
-        p = fmaf(t, p, 0.999668402f);
-        sp = fmaf(t, p, fmaxf(sv, 0.f));
-      }
-      const float dv = __uint_as_float(__float_as_uint(sg) ^ sign);
-      if constexpr (FULL) {
-        d[q] = dv;
-        acc += sp;
-      } else {
-        const bool in = j + q < valid;
+        const float dv = __uint_as_float(__float_as_uint(sg) ^ sign);
+        const bool in = FULL || j + q < valid;
         d[q] = in ? dv : 0.f;
         acc += in ? sp : 0.f;
       }
+      const uint32_t h2 = ptx::pack_bf16(d[0], d[1]);
+      hi[j >> 1] = h2;
+      lo[j >> 1] = ptx::pack_bf16(d[0] - ptx::bf16_lo(h2), d[1] - ptx::bf16_hi(h2));
     }
-    const uint32_t h2 = ptx::pack_bf16(d[0], d[1]);
-    hi[j >> 1] = h2;
-    if constexpr (PRECISE) lo[j >> 1] = ptx::pack_bf16(d[0] - ptx::bf16_lo(h2), d[1] - ptx::bf16_hi(h2));
+    return acc;
+  } else {
+    // Fast path, two columns per instruction (FFMA2/FADD2/FMUL2).  Per element:
+    //   t = 2^(-|a| log2 e) ; rr = 1/(1+t) ; u = t rr = sigmoid(-|s|) ;  sigmoid(s) = 0.5 + sgn(s) (0.5 - u)
+    //   softplus(s) = max(s, 0) + t P(t),  P = degree-3 minimax fit of log1p(t)/t on (0,1], max relative error 4.8e-4
+    //   (the loss is a reported scalar; the gradient uses sigmoid only)
+    const uint64_t k_nl2e = ptx::pk2(-1.4426950408889634f, -1.4426950408889634f), k_one = ptx::pk2(1.f, 1.f);
+    const uint64_t k_mhalf = ptx::pk2(-0.5f, -0.5f), k_half = ptx::pk2(0.5f, 0.5f);
+    const uint64_t c3 = ptx::pk2(-0.0762659232f, -0.0762659232f), c2 = ptx::pk2(0.256918443f, 0.256918443f);
+    const uint64_t c1 = ptx::pk2(-0.487505179f, -0.487505179f), c0 = ptx::pk2(0.999668402f, 0.999668402f);
+    uint64_t acc2 = ptx::pk2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      const uint32_t sg0 = (xw << (31 - j)) & 0x80000000u, sg1 = (xw << (30 - j)) & 0x80000000u;
+      const uint32_t s0 = r[j] ^ sg0, s1 = r[j + 1] ^ sg1;                     // s = a or -a
+      float d0, d1;
+      {
+        const uint64_t aa = ptx::pk2(__uint_as_float(r[j] & 0x7FFFFFFFu), __uint_as_float(r[j + 1] & 0x7FFFFFFFu));
+        float e0, e1;
+        ptx::unpk2(ptx::mul2(aa, k_nl2e), e0, e1);
+        float t0, t1;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(e0));
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(e1));
+        const uint64_t t = ptx::pk2(t0, t1);
+        float w0, w1;
+        ptx::unpk2(ptx::add2(t, k_one), w0, w1);
+        float r0, r1;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(w0));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(w1));
+        float h0, h1;                                                            // u - 0.5  (<= 0)
+        ptx::unpk2(ptx::fma2(t, ptx::pk2(r0, r1), k_mhalf), h0, h1);
+        // (0.5 - u) carrying the sign of s:  flip the sign of (u - 0.5) where s >= 0
+        const float g0 = __uint_as_float(__float_as_uint(h0) ^ (~s0 & 0x80000000u));
+        const float g1 = __uint_as_float(__float_as_uint(h1) ^ (~s1 & 0x80000000u));
+        float q0, q1;                                                            // sigmoid(s)
+        ptx::unpk2(ptx::add2(ptx::pk2(g0, g1), k_half), q0, q1);
+        d0 = __uint_as_float(__float_as_uint(q0) ^ sg0);                         // sigmoid(a) - x
+        d1 = __uint_as_float(__float_as_uint(q1) ^ sg1);
+        uint64_t pp = ptx::fma2(t, c3, c2);
+        pp = ptx::fma2(t, pp, c1);
+        pp = ptx::fma2(t, pp, c0);
+        const uint64_t relu = ptx::pk2(fmaxf(__uint_as_float(s0), 0.f), fmaxf(__uint_as_float(s1), 0.f));
+        const uint64_t sp = ptx::fma2(t, pp, relu);
+        if constexpr (FULL) {
+          acc2 = ptx::add2(acc2, sp);
+        } else {
+          float p0, p1;
+          ptx::unpk2(sp, p0, p1);
+          acc2 = ptx::add2(acc2, ptx::pk2(j < valid ? p0 : 0.f, j + 1 < valid ? p1 : 0.f));
+        }
+      }
+      if constexpr (!FULL) {
+        d0 = j < valid ? d0 : 0.f;
+        d1 = j + 1 < valid ? d1 : 0.f;
+      }
+      hi[j >> 1] = ptx::pack_bf16(d0, d1);
+    }
+    float a0, a1;
+    ptx::unpk2(acc2, a0, a1);
+    return a0 + a1;
   }
-  return acc;
 }
 
 // ------------------------------------------------------------------ how a chunk leaves the SM
@@ -452,17 +490,20 @@ static_assert(sizeof(GemmArgs) <= 4096, "kernel parameter space");
 
 // ---------------------------------------------------------------------------- the kernel
 template <bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
+// 112 registers: three of this kernel's warps (3 x 32 x 112) and three warps of the batch generator (3 x 32 x 56) fit
+// the 16K registers of one SM sub-partition, so the generator's CTA stays co-resident with every GEMM variant; it is
+// the 576-thread BCE variant has five warps on a sub-partition, hence 96.
+__global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
 #define MAGIC_TR(slot)                                                                  \
   do {                                                                                  \
-    if (args.trace) args.trace[(size_t)blockIdx.x * 16 + (slot)] = clock64();           \
+    if (args.trace) args.trace[(size_t)blockIdx.x * 64 + (slot)] = clock64();           \
   } while (0)
   if (threadIdx.x == 0) {
     MAGIC_TR(0);
     if (args.trace) {
       unsigned long long gt;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-      args.trace[(size_t)blockIdx.x * 16 + 11] = (long long)gt;
+      args.trace[(size_t)blockIdx.x * 64 + 11] = (long long)gt;
     }
   }
   extern __shared__ uint8_t smem_raw[];
@@ -563,6 +604,7 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
         const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
         ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
+        if (iter < 8) MAGIC_TR(16 + iter * 5 + 0);
         const uint32_t d_tmem = tmem_base + acc * kBlockN;
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
@@ -582,9 +624,10 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
         }
         ptx::umma_commit(&tfull_bar[acc]);        // accumulator complete -> epilogue
         if (w == work0) MAGIC_TR(5);
+        if (iter < 8) MAGIC_TR(16 + iter * 5 + 1);
       }
       MAGIC_TR(6);
-      if (args.trace) args.trace[(size_t)blockIdx.x * 16 + 12] = iter;
+      if (args.trace) args.trace[(size_t)blockIdx.x * 64 + 12] = iter;
       // All of this CTA's MMAs are issued: from here only its last epilogue remains, so the next kernel of the step
       // may become resident on SMs as they free and run its prologue (launch.cuh).  Triggering earlier parks the
       // following kernels' CTAs on the SMs for the whole duration and starves the generator's side stream.
@@ -600,6 +643,23 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
     const int grp = (warp - 2) >> 2;
     uint32_t iter = 0;
     float loss_acc = 0.f;
+    // BCE: a row's packed target bits for the chunks this warp owns.  They are fetched ONE TILE AHEAD: loaded right
+    // before the accumulator wait, their ~1.3 us of DRAM latency sat on the critical path of every tile (r01i trace).
+    uint32_t xw[kMaxOwn], xw_next[kMaxOwn];
+    auto load_xw = [&](int w_item, uint32_t (&dst)[kMaxOwn]) {
+      const WorkItem nit = decode_work(args, w_item, crank);
+      const EpiArgs& ne = args.epi[nit.g];
+      const int nrow = nit.m0 + q * 32 + lane;
+      const int nn = (min(kBlockN, args.N - nit.n0) + 31) >> 5;
+#pragma unroll
+      for (int k = 0; k < kMaxOwn; ++k) {
+        const int c = grp + k * kGroups;
+        dst[k] = (nrow < args.M && c < nn) ? __ldg(ne.xbits + (long long)nrow * ne.xb_ld + ((nit.n0 >> 5) + c)) : 0u;
+      }
+    };
+    if constexpr (EPI == EPI_BCE) {
+      if (work0 < total_work) load_xw(work0, xw_next);
+    }
     for (int w = work0; w < total_work; w += work_stride, ++iter) {
       const WorkItem it = decode_work(args, w, crank);
       const EpiArgs& e = args.epi[it.g];
@@ -607,31 +667,22 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
       const int row = it.m0 + q * 32 + lane;
       const int ncols = min(kBlockN, args.N - it.n0);
       const int nchunks = (ncols + 31) >> 5;
-      // BCE: this row's packed target bits for the chunks this warp owns, fetched before the accumulator wait
-      uint32_t xw[kMaxOwn];
       if constexpr (EPI == EPI_BCE) {
 #pragma unroll
-        for (int k = 0; k < kMaxOwn; ++k) {
-          const int c = grp + k * kGroups;
-          xw[k] = (row < args.M && c < nchunks) ? __ldg(e.xbits + (long long)row * e.xb_ld + ((it.n0 >> 5) + c)) : 0u;
-        }
+        for (int k = 0; k < kMaxOwn; ++k) xw[k] = xw_next[k];
+        if (w + work_stride < total_work) load_xw(w + work_stride, xw_next);
       }
       ptx::mbar_wait(&tfull_bar[acc], acc_phase);
       ptx::tc_fence_after();
       if (warp == 2 && lane == 0 && w == work0) MAGIC_TR(7);
+      if (warp == 2 && lane == 0 && iter < 8) MAGIC_TR(16 + iter * 5 + 2);
       bool arrived = false;
-#pragma unroll
-      for (int k = 0; k < kMaxOwn; ++k) {
+      // Two chunks are read per TMEM wait: a tcgen05.ld queues behind the MMAs already issued for the next tile, so
+      // every separate load-wait round trip costs ~1-2 us during which the accumulator stays locked (r01i: the BCE
+      // kernel ran 0.043 ms slower than its main loop with an epilogue that only read TMEM).  With 16 epilogue
+      // warps the two chunks are all a warp owns, so the accumulator is handed back before any math starts.
+      auto process = [&](const uint32_t (&r)[32], int k) {
         const int c = grp + k * kGroups;
-        if (c >= nchunks || (e.dbg & 4)) break;   // dbg 4: mainloop-only timing, the accumulator is never read
-        uint32_t r[32];
-        ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kBlockN + c * 32, r);
-        ptx::tmem_ld_wait();
-        if (c + kGroups >= nchunks) {   // this warp's last TMEM read of the accumulator: hand it back to the MMA warp
-          ptx::tc_fence_before();
-          ptx::mbar_arrive(&tempty_bar[acc]);
-          arrived = true;
-        }
         uint32_t xwk = 0u;
         if constexpr (EPI == EPI_BCE) xwk = xw[k];
         if constexpr (EPI == EPI_SCATTER_F32) {
@@ -647,11 +698,32 @@ __global__ void __launch_bounds__(gemm_threads(EPI), 1) gemm_tcgen05_kernel(cons
           t.reduce = e.atomic;
           epilogue_chunk<EPI, true>(e, t, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
         }
+      };
+      constexpr int kBatch = epi_warps(EPI) == 16 ? 2 : 1;   // 8-warp epilogues own 4 chunks: one at a time (registers)
+#pragma unroll
+      for (int k = 0; k < kMaxOwn; k += kBatch) {
+        const int c0 = grp + k * kGroups, c1 = grp + (k + 1) * kGroups;
+        if (c0 >= nchunks || (e.dbg & 4)) break;   // dbg 4: mainloop-only timing, the accumulator is never read
+        const bool two = kBatch == 2 && (k + 1 < kMaxOwn) && c1 < nchunks;
+        uint32_t ra[32], rb[32];
+        const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kBlockN;
+        ptx::tmem_ld_32x32(tbase + c0 * 32, ra);
+        if (two) ptx::tmem_ld_32x32(tbase + c1 * 32, rb);
+        ptx::tmem_ld_wait();
+        if (grp + (k + kBatch) * kGroups >= nchunks || k + kBatch >= kMaxOwn) {   // this warp's last TMEM read of the accumulator
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(&tempty_bar[acc]);
+          arrived = true;
+          if (warp == 2 && lane == 0 && iter < 8) MAGIC_TR(16 + iter * 5 + 3);
+        }
+        process(ra, k);
+        if (two) process(rb, k + 1);
       }
       if (!arrived) {
         ptx::tc_fence_before();
         ptx::mbar_arrive(&tempty_bar[acc]);
       }
+      if (warp == 2 && lane == 0 && iter < 8) MAGIC_TR(16 + iter * 5 + 4);
     }
     if (warp == 2 && lane == 0) MAGIC_TR(8);
     ptx::bulk_wait_all();   // every tile store / row segment this thread issued has left before the CTA exits

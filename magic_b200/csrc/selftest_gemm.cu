@@ -232,7 +232,7 @@ static void test_fused(int epi, int M, int Nv, int K, int split, int precise, in
   if (dbits) cudaFree(dbits);
 }
 
-static void bench(int kind, int M, int N, int K, int split, int sms, const char* label) {
+static void bench(int kind, int M, int N, int K, int split, int sms, const char* label, int epi = EPI_STORE_F32) {
   __nv_bfloat16 *a, *b;
   size_t na = (size_t)(kind == GEMM_WGRAD ? K : M) * (kind == GEMM_WGRAD ? (M + 63) / 64 * 64 : (K + 63) / 64 * 64);
   size_t nb = (size_t)(kind == GEMM_DGRAD ? N : K) * (kind == GEMM_DGRAD ? (K + 63) / 64 * 64 : (N + 63) / 64 * 64);
@@ -243,12 +243,23 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   CK(cudaMalloc(&out, sizeof(float) * M * ldo));
   CK(cudaMemset(out, 0, sizeof(float) * M * ldo));
   GemmProblem p;
-  p.kind = kind; p.epi = EPI_STORE_F32; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
+  p.kind = kind; p.epi = epi; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
   p.cluster_m = g_cluster;
   p.a[0][0] = kind == GEMM_WGRAD ? Mat(a, K, M, (M + 63) / 64 * 64) : Mat(a, M, K, (K + 63) / 64 * 64);
   p.b[0][0] = kind == GEMM_DGRAD ? Mat(b, N, K, (K + 63) / 64 * 64) : Mat(b, K, N, (N + 63) / 64 * 64);
   EpiArgs e = {};
   e.out = out; e.ld_out = ldo; e.alpha = 1.f;
+  if (epi == EPI_BCE) {   // bf16 gradient into the same buffer, all-zero packed targets, loss scalar
+    uint32_t* bits;
+    float* scalar;
+    const int xb_ld = (N + 31) / 32;
+    CK(cudaMalloc(&bits, sizeof(uint32_t) * (size_t)M * xb_ld));
+    CK(cudaMemset(bits, 0, sizeof(uint32_t) * (size_t)M * xb_ld));
+    CK(cudaMalloc(&scalar, 4));
+    CK(cudaMemset(scalar, 0, 4));
+    e.xbits = bits; e.xb_ld = xb_ld; e.scalar = scalar; e.n_valid = N; e.aux_split = 1 << 30;
+    e.ld_out = (N + 7) / 8 * 8;
+  }
   if (const char* d = getenv("MAGIC_EPI_DBG")) e.dbg = atoi(d);
   p.e[0] = e;
   GemmPlan pl;
@@ -256,30 +267,37 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   if (!err.empty()) { printf("plan error: %s\n", err.c_str()); return; }
   if (getenv("MAGIC_TRACE")) {   // per-CTA phase stamps of one warm launch
     long long* tr;
-    CK(cudaMalloc(&tr, sizeof(long long) * 16 * pl.grid));
+    CK(cudaMalloc(&tr, sizeof(long long) * 64 * pl.grid));
     for (int i = 0; i < 3; ++i) gemm_launch(pl, 0, &err);
     CK(cudaDeviceSynchronize());
-    CK(cudaMemset(tr, 0, sizeof(long long) * 16 * pl.grid));
+    CK(cudaMemset(tr, 0, sizeof(long long) * 64 * pl.grid));
     pl.args.trace = tr;
     gemm_launch(pl, 0, &err);
     CK(cudaDeviceSynchronize());
     pl.args.trace = nullptr;
-    std::vector<long long> h((size_t)16 * pl.grid);
+    std::vector<long long> h((size_t)64 * pl.grid);
     CK(cudaMemcpy(h.data(), tr, sizeof(long long) * h.size(), cudaMemcpyDeviceToHost));
     const char* names[11] = {"entry", "prologue done", "dep wait done", "first TMA issued", "first stage landed",
                              "tile 0 MMAs issued", "all MMAs issued", "epi: tile 0 acc ready", "epi: loop done",
                              "epi: stores drained", "exit"};
     long long gmin = h[11], gmax = h[11];
-    for (int c = 0; c < pl.grid; ++c) { gmin = std::min(gmin, h[(size_t)c * 16 + 11]); gmax = std::max(gmax, h[(size_t)c * 16 + 11]); }
+    for (int c = 0; c < pl.grid; ++c) { gmin = std::min(gmin, h[(size_t)c * 64 + 11]); gmax = std::max(gmax, h[(size_t)c * 64 + 11]); }
     printf("trace %-28s grid=%d, CTA start spread %.2f us; mean / max cycles since CTA entry:\n", label, pl.grid, (gmax - gmin) * 1e-3);
     for (int sidx = 1; sidx <= 10; ++sidx) {
       double sum = 0; long long mx = 0; int n = 0;
       for (int c = 0; c < pl.grid; ++c) {
-        long long v = h[(size_t)c * 16 + sidx], b = h[(size_t)c * 16];
+        long long v = h[(size_t)c * 64 + sidx], b = h[(size_t)c * 64];
         if (v == 0) continue;
         sum += (double)(v - b); mx = std::max(mx, v - b); ++n;
       }
       if (n) printf("   %-24s %9.0f %9lld   (%.2f / %.2f us at 1.9 GHz)\n", names[sidx], sum / n, mx, sum / n / 1900.0, mx / 1900.0);
+    }
+    // pipeline of the first tiles of CTA 0 (cycles since its entry)
+    printf("   CTA 0 tiles: [MMA start, MMA all issued | epi: acc ready, acc released, tile done]\n");
+    for (int it = 0; it < 8; ++it) {
+      const long long* t = &h[16 + it * 5];
+      if (t[0] == 0) break;
+      printf("     tile %d: %8lld %8lld | %8lld %8lld %8lld\n", it, t[0] - h[0], t[1] - h[0], t[2] - h[0], t[3] - h[0], t[4] - h[0]);
     }
     CK(cudaFree(tr));
   }
@@ -346,6 +364,7 @@ int main(int argc, char** argv) {
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");
     bench(GEMM_FWD, 12288, 512, 40064, 0, sms, "enc L0 fwd (auto split)");
     bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd");
+    bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd, BCE epilogue", EPI_BCE);
     g_cluster = 2; bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd, cluster 2");
     g_cluster = 4; bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd, cluster 4");
     g_cluster = 4; bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad, cluster 4");
