@@ -165,8 +165,11 @@ static std::string make_tmap_mn(CUtensorMap* out, const void* ptr, long long col
 }
 
 // Minimise waves * (k-blocks per item + fixed per-item overhead), see DESIGN.md "split-K".
-int choose_splitk(int tiles, int total_kb, int num_sms) {
+int choose_splitk(int tiles, int total_kb, int num_sms, bool two_pass) {
   const double overhead = 8.0;   // epilogue + pipeline fill, in k-block units
+  // a split with a non-linear epilogue costs two more launches (workspace zeroing + finishing pass), ~12 us ~ 27
+  // k-block times (r01a launch list): never worth it for the 8-k-block decoder layers
+  const double extra = two_pass ? 27.0 : 0.0;
   int best = 1;
   double best_cost = 1e30;
   int max_split = total_kb / 4;
@@ -177,7 +180,7 @@ int choose_splitk(int tiles, int total_kb, int num_sms) {
     if ((long long)(s - 1) * per >= total_kb) continue;   // would leave an empty split
     long long items = (long long)tiles * s;
     long long waves = (items + num_sms - 1) / num_sms;
-    double cost = (double)waves * (per + overhead) * (s > 1 ? 1.02 : 1.0);
+    double cost = (double)waves * (per + overhead) * (s > 1 ? 1.02 : 1.0) + (s > 1 ? extra : 0.0);
     if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
   }
   return best;
@@ -231,7 +234,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   const bool linear = p.epi == EPI_STORE_F32;   // SCATTER_F32 stores plain values to peer memory: never split
   const bool can_split = linear || (p.ws != nullptr && p.ngroups == 1 && (p.epi == EPI_ACT || p.epi == EPI_DACT));
   int split = 1;
-  if (can_split) split = p.force_splitk > 0 ? p.force_splitk : choose_splitk(tiles, total_kb, num_sms);
+  if (can_split) split = p.force_splitk > 0 ? p.force_splitk : choose_splitk(tiles, total_kb, num_sms, !linear);
   {
     int per = (total_kb + split - 1) / split;
     while (split > 1 && (long long)(split - 1) * per >= total_kb) { --split; per = (total_kb + split - 1) / split; }

@@ -55,6 +55,6 @@ int gemm_launch(const GemmPlan& plan, cudaStream_t stream, std::string* err);
 // Point group g's epilogue at another output matrix of the same shape and pitch (re-encodes its output tile maps).
 std::string gemm_set_output(GemmPlan* plan, int g, void* out, void* out_lo);
 std::string gemm_init();   // resolves cuTensorMapEncodeTiled, sets max dynamic smem on every variant
-int choose_splitk(int tiles, int total_kb, int num_sms);
+int choose_splitk(int tiles, int total_kb, int num_sms, bool two_pass = false);
 
 }  // namespace magic
