@@ -33,16 +33,22 @@ def _line(epoch, epochs, i, total, cost, training_loss, rec_loss, lat_loss, def_
 
 
 def train(model_cls, FLAGS, sess=None, batch_size=None, training_epochs=50, display_step=5, steps_per_epoch=None,
-          log=sys.stdout, seed=0, **model_kw):
+          log=sys.stdout, seed=0, dataset=None, **model_kw):
+    """`dataset`: a magic_b200.overlap_input.OverlapDataset (the PNG pairs + OVERLAP_AREAS of FLAGS.DATA_DIR, row N2);
+    None trains on pairs produced by the on-device generator (row N1)."""
     batch_size = int(batch_size or FLAGS.BATCH_SIZE)
     vae = model_cls(sess=sess, batch_size=batch_size, **model_kw)
-    n_samples = FLAGS.NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN
+    n_samples = len(dataset) if dataset is not None else FLAGS.NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN
     total_batch = int(steps_per_epoch or max(1, n_samples // batch_size))
+    data_iter = None
+    if dataset is not None:
+        from magic_b200.overlap_input import device_batches
+        data_iter = device_batches(vae, dataset, epochs=training_epochs * 2 + 2, shuffle=True, seed=seed)
     t0, pairs = time.time(), 0
     try:
         for epoch in range(training_epochs):
             for i in range(total_batch):
-                batch = vae.next_device_batch(seed)
+                batch = next(data_iter) if data_iter is not None else vae.next_device_batch(seed)
                 out = vae.partial_fit(batch, overlap_areas=batch.labels)
                 cost, training_loss, rec_loss, lat_loss, def_loss = out[:5]
                 pairs += batch_size
@@ -52,8 +58,8 @@ def train(model_cls, FLAGS, sess=None, batch_size=None, training_epochs=50, disp
                     print(_line(epoch, training_epochs, i, total_batch, cost, training_loss, rec_loss, lat_loss, def_loss),
                           file=log)
                 if i % 24 == 0:
-                    test = vae.next_device_batch(seed + 1)
-                    areas = test.labels.eval()
+                    test = next(data_iter) if data_iter is not None else vae.next_device_batch(seed + 1)
+                    areas = test.labels if data_iter is not None else test.labels.eval()
                     predictions = vae.get_predictions(test, overlap_areas=test.labels)
                     if vae.reciprocal_distance:
                         predictions = 1.0 / predictions             # 11a/main.py:100

@@ -97,6 +97,11 @@ int magic_load_interleaved(magic_handle* h, const float* d_x);                  
  * moves a quarter of the bytes over PCIe. */
 int magic_load_interleaved_u8(magic_handle* h, const uint8_t* d_x);                  /* [B, 3*D] */
 int magic_load_planar_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* d_rot, const uint8_t* d_key);
+/* Row N2, the dataset path: lock and key planes [B, D] uint8 as decoded from the {N}_L.png / {N}_K.png files
+ * (8c/overlap_input.py:21-73,155-170); the rotated-lock plane of 8c/overlap_input.py:181-182 (random_rotation,
+ * 8c/utils.py:329-340: angle ~ U[0, 2 pi), nearest neighbour, zero fill) is produced on the device with the
+ * generator's Q14 integer rotation for (seed, step, rank); magic_export_rotation returns the (cos, sin) used. */
+int magic_load_pairs_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* d_key, uint64_t seed, uint64_t step);
 /* Replaces overlap_input.inputs() (8c/overlap_input.py:76-124): synthesises B shape pairs + rotated lock +
  * max-overlap labels on the device for (seed, step, rank).  Labels go to an internal buffer used when
  * magic_step is given d_labels = NULL. */

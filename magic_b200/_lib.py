@@ -59,6 +59,7 @@ SIGNATURES = {
     "magic_load_interleaved_u8": (C.c_int, [_VP, _VP]),
     "magic_partial_fit_host_u8": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     "magic_load_planar_u8": (C.c_int, [_VP, _VP, _VP, _VP]),
+    "magic_load_pairs_u8": (C.c_int, [_VP, _VP, _VP, C.c_uint64, C.c_uint64]),
     "magic_generate_batch": (C.c_int, [_VP, _U64, _U64]),
     "magic_export_batch": (C.c_int, [_VP, _VP, _VP]),
     "magic_export_rotation": (C.c_int, [_VP, _VP]),

@@ -144,6 +144,10 @@ int magic_load_planar_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* 
   CHECK_HANDLE(h);
   return done(h->eng.load_planar_u8(d_lock, d_rot, d_key));
 }
+int magic_load_pairs_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* d_key, uint64_t seed, uint64_t step) {
+  CHECK_HANDLE(h);
+  return done(h->eng.load_pairs_u8(d_lock, d_key, seed, step));
+}
 int magic_generate_batch(magic_handle* h, uint64_t seed, uint64_t step) {
   CHECK_HANDLE(h);
   return done(h->eng.generate(seed, step));

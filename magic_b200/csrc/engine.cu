@@ -534,6 +534,7 @@ std::string Engine::load_interleaved(const float* d_x) {
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
+  b.has_rot = false;
   b.filled = true;
   cur_ ^= 1;
   return "";
@@ -549,6 +550,7 @@ std::string Engine::load_interleaved_u8(const uint8_t* d_x) {
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
+  b.has_rot = false;
   b.filled = true;
   cur_ ^= 1;
   return "";
@@ -562,6 +564,23 @@ std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uin
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
+  b.has_rot = false;
+  b.filled = true;
+  cur_ ^= 1;
+  return "";
+}
+std::string Engine::load_pairs_u8(const uint8_t* d_lock, const uint8_t* d_key, uint64_t seed, uint64_t step_idx) {
+  if (!d_lock || !d_key) return "load_pairs_u8: null input";
+  const int side = (int)llround(sqrt((double)D));
+  if (side * side != D) return "load_pairs_u8: D must be a square canvas";
+  InBuf& b = in_[cur_ ^ 1];
+  wait_ready(b);
+  pairs_u8(d_lock, d_key, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, b.X.hi, b.X.ld, b.rot, stream);
+  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
+  MAGIC_CUDA(cudaGetLastError());
+  mark_consumed(b);
+  b.has_labels = false;
+  b.has_rot = true;
   b.filled = true;
   cur_ ^= 1;
   return "";
@@ -599,7 +618,7 @@ std::string Engine::swap_batch() {
 std::string Engine::export_rotation(int32_t* d_cs_sn) {
   if (!d_cs_sn) return "export_rotation: null output";
   InBuf& b = in_[cur_];
-  if (!b.has_labels) return "export_rotation: no generated batch is loaded";
+  if (!b.has_labels && !b.has_rot) return "export_rotation: the loaded batch was not rotated on the device";
   wait_ready(b);
   MAGIC_CUDA(cudaMemcpyAsync(d_cs_sn, b.rot, sizeof(int) * 2 * (size_t)B, cudaMemcpyDeviceToDevice, stream));
   mark_consumed(b);

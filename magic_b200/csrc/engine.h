@@ -50,6 +50,7 @@ class Engine {
   std::string export_batch(float* d_x, float* d_labels);
   std::string export_rotation(int32_t* d_cs_sn);
   std::string swap_batch();
+  std::string load_pairs_u8(const uint8_t* d_lock, const uint8_t* d_key, uint64_t seed, uint64_t step_idx);
   std::string step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply);
   std::string load_interleaved_u8(const uint8_t* d_x);
   std::string partial_fit_host(const void* h_x, bool x_is_u8, const float* h_labels, const float* h_eps3,
@@ -119,7 +120,7 @@ class Engine {
     float* labels = nullptr;        // [B] generated overlap labels
     int* rot = nullptr;             // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
     cudaEvent_t ready = nullptr, consumed = nullptr;
-    bool ready_pending = false, consumed_pending = false, has_labels = false, filled = false;
+    bool ready_pending = false, consumed_pending = false, has_labels = false, filled = false, has_rot = false;
   };
   InBuf in_[2];                     // the generator fills in_[cur_ ^ 1] on gen_stream_ while the step reads in_[cur_]
   int cur_ = 0;

@@ -774,6 +774,50 @@ void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16
 
 // lock plane (bf16 {0,1}, rows [B, 2B) of planes) -> packed bitmap xbits[B, xb_ld] for the loaders that do not
 // come through the generator.  One warp per 32-pixel word.
+// ------------------------------------------------------------------ N2: dataset pairs -> operand planes
+// (8c/overlap_input.py:181-195: lock, random_rotation(lock), key concatenated; 8c/utils.py:329-340: the angle is
+// uniform in [0, 2 pi), nearest-neighbour, zero fill.)  lock / key are uint8 [B, D] (any non-zero byte is a set
+// pixel); the rotated plane is sampled on the fly with the generator's Q14 integer rotation, so it is reproducible
+// bit for bit from the exported (cos, sin).  One CTA per (pair, 1024-column chunk).
+__global__ void __launch_bounds__(256) pairs_u8_kernel(const uint8_t* __restrict__ lock, const uint8_t* __restrict__ key,
+                                                       int B, int side, uint64_t seed, uint64_t step,
+                                                       __nv_bfloat16* planes, long long ld, int* rot_cs_sn) {
+  __shared__ int q14[2];
+  const int i = blockIdx.y, D = side * side;
+  if (threadIdx.x == 0) {
+    float sn, cs;
+    sincospif(2.f * u01((uint32_t)rng_key(seed, step, 13, i)), &sn, &cs);   // same draw as generate_pairs_kernel
+    q14[0] = __float2int_rn(cs * 16384.f);
+    q14[1] = __float2int_rn(sn * 16384.f);
+    if (rot_cs_sn && blockIdx.x == 0) { rot_cs_sn[2 * i] = q14[0]; rot_cs_sn[2 * i + 1] = q14[1]; }
+  }
+  __syncthreads();
+  const int cs = q14[0], sn = q14[1];
+  const uint8_t* L = lock + (long long)i * D;
+  const uint8_t* K = key + (long long)i * D;
+  __nv_bfloat16* prot = planes + (long long)i * ld;
+  __nv_bfloat16* plock = planes + (long long)(B + i) * ld;
+  __nv_bfloat16* pkey = planes + (long long)(2 * B + i) * ld;
+  const __nv_bfloat16 one = __float2bfloat16(1.f), zero = __float2bfloat16(0.f);
+  for (int c = blockIdx.x * 1024 + threadIdx.x; c < min((long long)(blockIdx.x + 1) * 1024, ld); c += 256) {
+    __nv_bfloat16 vl = zero, vk = zero, vr = zero;
+    if (c < D) {
+      vl = L[c] ? one : zero;
+      vk = K[c] ? one : zero;
+      const int y = c / side, x = c - y * side;
+      const int sp = rotated_index(x, y, side, cs, sn);
+      vr = (sp >= 0 && L[sp]) ? one : zero;
+    } else if (c == D) {
+      vl = vk = vr = one;                                  // bias column
+    }
+    prot[c] = vr; plock[c] = vl; pkey[c] = vk;
+  }
+}
+void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t seed, uint64_t step,
+              __nv_bfloat16* planes, long long ld, int* rot_cs_sn, cudaStream_t s) {
+  pairs_u8_kernel<<<dim3((unsigned)((ld + 1023) / 1024), B), 256, 0, s>>>(lock, key, B, side, seed, step, planes, ld, rot_cs_sn);
+}
+
 __global__ void __launch_bounds__(256) pack_lock_bits_kernel(const __nv_bfloat16* __restrict__ planes, long long ld, int B,
                                                              int D, uint32_t* xbits, int xb_ld) {
   const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -809,6 +853,7 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(deinterleave_kernel);
   MAGIC_MAX_CARVEOUT(deinterleave_u8_kernel);
   MAGIC_MAX_CARVEOUT(planar_u8_kernel);
+  MAGIC_MAX_CARVEOUT(pairs_u8_kernel);
   MAGIC_MAX_CARVEOUT(planes_to_interleaved_kernel);
   MAGIC_MAX_CARVEOUT(generate_pairs_kernel);
   MAGIC_MAX_CARVEOUT(pack_lock_bits_kernel);

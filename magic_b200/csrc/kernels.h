@@ -97,6 +97,8 @@ void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16
                     int xb_ld, float* labels, int* rot_cs_sn, int max_ctas, cudaStream_t s);
 // packed 1-bit copy of the lock plane (pixel p = bit p & 31 of word p >> 5, row pitch xb_ld words): the target the
 // sigmoid-BCE epilogue reads (8c/vae.py:260-263)
+void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t seed, uint64_t step,
+              __nv_bfloat16* planes, long long ld, int* rot_cs_sn, cudaStream_t s);
 void pack_lock_bits(const __nv_bfloat16* planes, long long ld, int B, int D, uint32_t* xbits, int xb_ld, cudaStream_t s);
 
 void zero_fill(void* ptr, size_t bytes, cudaStream_t s);   // kernel-based memset(0): ptr 16-byte aligned, bytes % 4 == 0

@@ -232,6 +232,16 @@ class Engine:
         check(self.lib.magic_load_planar_u8(self._h, *[C.c_void_p(x.data_ptr()) for x in ts]))
         self._keep = ts
 
+    def load_pairs_u8(self, lock: torch.Tensor, key: torch.Tensor, seed: int, step: int) -> None:
+        """Dataset pairs (uint8 [B, D]) -> operand planes; the rotated lock is produced on the device."""
+        ts = [x.to(device=self.device, dtype=torch.uint8).contiguous() for x in (lock, key)]
+        for x in ts:
+            if tuple(x.shape) != (self.B, self.D):
+                raise ValueError("planes must be [B, D] uint8")
+        check(self.lib.magic_load_pairs_u8(self._h, C.c_void_p(ts[0].data_ptr()), C.c_void_p(ts[1].data_ptr()),
+                                           C.c_uint64(seed), C.c_uint64(step)))
+        self._keep = ts
+
     def generate_batch(self, seed: int, step: int) -> None:
         check(self.lib.magic_generate_batch(self._h, C.c_uint64(seed), C.c_uint64(step)))
 

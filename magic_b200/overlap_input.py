@@ -1,0 +1,187 @@
+"""Row N2: the overlap dataset path -- `{N}_L.png` / `{N}_K.png` pairs + OVERLAP_AREAS -> device batches.
+
+Host-side mirror of the reference's input pipeline for 8c-11a (8c/overlap_input.py):
+
+  * `read_png`      <- `decode_mshapes` (8c/overlap_input.py:41-73): whole file -> uint8 image.  The reference calls
+                       tf.image.decode_png; here a small pure-Python decoder (zlib inflate + numpy un-filtering) for
+                       the non-interlaced 8-bit grey / grey+alpha / RGB / RGBA / palette files the dataset contains.
+  * `OverlapDataset`<- `_inputs_with_rotation` (8c/overlap_input.py:127-211): file lists `%d_L.png` / `%d_K.png`
+                       (lines 158-165), labels from the OVERLAP_AREAS pickle (lines 146-149), pixels normalised to
+                       {0,1} (`normalize=True`, line 110-112; the files hold {0,255}).
+  * `batches`       <- `tf.train.shuffle_batch` (8c/overlap_input.py:316-322) + the JOINT dequeue of images and
+                       labels that 10a/main.py:64 introduced (8c-9b dequeue them separately and pair a batch of
+                       images with another batch's labels).  Shuffling is a fresh permutation per
+                       epoch; the last ragged batch of an epoch is dropped (the graph has a static batch size,
+                       8c/vae.py:367).
+  * the random rotation of the lock (8c/overlap_input.py:181-182, 8c/utils.py:329-340) happens on the device:
+                       `magic_load_pairs_u8` (include/magic_b200.h).
+
+Nothing here touches TensorFlow queues, threads or summaries (out of scope)."""
+from __future__ import annotations
+
+import io
+import os
+import pickle
+import struct
+import zipfile
+import zlib
+from typing import Iterator, Optional, Sequence, Tuple, Union
+
+import numpy as np
+
+_PNG_MAGIC = b"\x89PNG\r\n\x1a\n"
+_CHANNELS = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}      # colour type -> samples per pixel
+
+
+class PngError(ValueError):
+    pass
+
+
+def _unfilter(raw: np.ndarray, height: int, stride: int, bpp: int) -> np.ndarray:
+    """PNG filter types 0-4 (None, Sub, Up, Average, Paeth), one filter byte per scanline."""
+    out = np.zeros((height, stride), dtype=np.uint8)
+    prev = np.zeros(stride, dtype=np.int32)
+    pos = 0
+    for y in range(height):
+        ft = int(raw[pos])
+        line = raw[pos + 1:pos + 1 + stride].astype(np.int32)
+        pos += 1 + stride
+        if ft == 0:
+            cur = line
+        elif ft == 2:
+            cur = (line + prev) & 255
+        elif ft in (1, 3, 4):
+            cur = np.zeros(stride, dtype=np.int32)
+            for x in range(stride):               # sequential along the line by definition of these filters
+                a = cur[x - bpp] if x >= bpp else 0
+                b = prev[x]
+                if ft == 1:
+                    pred = a
+                elif ft == 3:
+                    pred = (a + b) >> 1
+                else:
+                    c = prev[x - bpp] if x >= bpp else 0
+                    p = a + b - c
+                    pa, pb, pc = abs(p - a), abs(p - b), abs(p - c)
+                    pred = a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+                cur[x] = (line[x] + pred) & 255
+        else:
+            raise PngError("bad PNG filter type %d" % ft)
+        out[y] = cur
+        prev = cur
+    return out
+
+
+def read_png(src: Union[str, bytes, os.PathLike]) -> np.ndarray:
+    """Decode a non-interlaced 8-bit PNG into uint8 [H, W] (grey / palette index expanded to luminance-free first
+    channel semantics the dataset needs: for colour images the FIRST channel is returned, as the reference reshapes
+    the decoded tensor to [IMAGE_SIZE, IMAGE_SIZE, 1], 8c/overlap_input.py:68)."""
+    data = src if isinstance(src, (bytes, bytearray)) else open(src, "rb").read()
+    if data[:8] != _PNG_MAGIC:
+        raise PngError("not a PNG file")
+    pos, idat, palette = 8, [], None
+    width = height = depth = ctype = interlace = None
+    while pos + 8 <= len(data):
+        length, tag = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + length]
+        if len(body) != length:
+            raise PngError("truncated PNG chunk")
+        crc = struct.unpack(">I", data[pos + 8 + length:pos + 12 + length])[0]
+        if zlib.crc32(tag + body) & 0xFFFFFFFF != crc:
+            raise PngError("PNG chunk CRC mismatch in %r" % tag)
+        pos += 12 + length
+        if tag == b"IHDR":
+            width, height, depth, ctype, _comp, _filt, interlace = struct.unpack(">IIBBBBB", body)
+        elif tag == b"PLTE":
+            palette = np.frombuffer(body, dtype=np.uint8).reshape(-1, 3)
+        elif tag == b"IDAT":
+            idat.append(body)
+        elif tag == b"IEND":
+            break
+    if width is None or not idat:
+        raise PngError("PNG without IHDR/IDAT")
+    if depth != 8 or interlace != 0 or ctype not in _CHANNELS:
+        raise PngError("unsupported PNG (depth %s, colour type %s, interlace %s)" % (depth, ctype, interlace))
+    ch = _CHANNELS[ctype]
+    stride = width * ch
+    raw = np.frombuffer(zlib.decompress(b"".join(idat)), dtype=np.uint8)
+    if raw.size != height * (stride + 1):
+        raise PngError("PNG data size mismatch")
+    img = _unfilter(raw, height, stride, ch).reshape(height, width, ch)
+    if ctype == 3:
+        if palette is None:
+            raise PngError("palette PNG without PLTE")
+        return palette[img[:, :, 0], 0].copy()
+    return img[:, :, 0].copy()
+
+
+def load_overlap_areas(path: Union[str, os.PathLike]) -> np.ndarray:
+    """OVERLAP_AREAS: a Python-2 pickle of max-overlap pixel counts (8c/overlap_input.py:146-149), or a .npy copy."""
+    if str(path).endswith(".npy"):
+        return np.load(path).astype(np.float32)
+    with open(path, "rb") as f:
+        return np.asarray(pickle.load(f, encoding="latin1"), dtype=np.float32)
+
+
+class OverlapDataset:
+    """Lock/key planes of the first `num_examples` pairs, uint8 {0,1}, [N, D] each, and their labels [N]."""
+
+    def __init__(self, data: Union[str, os.PathLike], overlap_areas: Union[str, os.PathLike, Sequence[float]],
+                 num_examples: Optional[int] = None, image_size: int = 200):
+        areas = load_overlap_areas(overlap_areas) if isinstance(overlap_areas, (str, os.PathLike)) \
+            else np.asarray(overlap_areas, dtype=np.float32)
+        zf = zipfile.ZipFile(data) if str(data).endswith(".zip") else None
+        names = {os.path.basename(n): n for n in zf.namelist()} if zf else None
+
+        def blob(name):
+            if zf:
+                if name not in names:
+                    raise FileNotFoundError(name)
+                return zf.read(names[name])
+            return open(os.path.join(str(data), name), "rb").read()
+
+        n = int(num_examples if num_examples is not None else len(areas))
+        if n > len(areas):
+            raise ValueError("more examples requested than labels in OVERLAP_AREAS")
+        D = image_size * image_size
+        self.lock = np.empty((n, D), dtype=np.uint8)
+        self.key = np.empty((n, D), dtype=np.uint8)
+        for i in range(n):                                   # '%d_L.png' / '%d_K.png', 8c/overlap_input.py:162-163
+            for kind, dst in (("L", self.lock), ("K", self.key)):
+                img = read_png(blob("%d_%s.png" % (i, kind)))
+                if img.shape != (image_size, image_size):
+                    raise ValueError("%d_%s.png is %s, expected %dx%d" % (i, kind, img.shape, image_size, image_size))
+                dst[i] = (img.reshape(-1) > 0)
+        self.labels = areas[:n].copy()
+        self.image_size = image_size
+
+    def __len__(self) -> int:
+        return len(self.labels)
+
+    def batches(self, batch_size: int, epochs: int = 1, shuffle: bool = True,
+                seed: int = 0) -> Iterator[Tuple[np.ndarray, np.ndarray, np.ndarray]]:
+        """Yields (lock[B, D] uint8, key[B, D] uint8, labels[B] float32), images and labels drawn JOINTLY."""
+        rng = np.random.default_rng(seed)
+        n = len(self)
+        if batch_size > n:
+            raise ValueError("batch_size %d exceeds the %d loaded examples" % (batch_size, n))
+        for _ in range(epochs):
+            order = rng.permutation(n) if shuffle else np.arange(n)
+            for s in range(0, n - batch_size + 1, batch_size):
+                idx = order[s:s + batch_size]
+                yield self.lock[idx], self.key[idx], self.labels[idx]
+
+
+def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool = True, seed: int = 0):
+    """`overlap_input.inputs(normalize=True, reshape=True, rotation=True)` for the B200 backend: yields handles
+    (magic_b200/tango.py: ResidentBatch) whose planes are already in HBM; `batch.labels` are the matching overlap
+    areas, so `vae.partial_fit(batch, overlap_areas=batch.labels)` trains on a consistent (images, labels) pair."""
+    import torch
+    from .tango import ResidentBatch
+    eng = vae.engine
+    step = 0
+    for lock, key, labels in dataset.batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed):
+        eng.load_pairs_u8(torch.from_numpy(np.ascontiguousarray(lock)), torch.from_numpy(np.ascontiguousarray(key)),
+                          seed, step)
+        step += 1
+        yield ResidentBatch(vae, np.ascontiguousarray(labels, dtype=np.float32))

@@ -46,6 +46,20 @@ class DeviceBatch:
         return self.model.engine.export_batch()[0].cpu().numpy()
 
 
+class ResidentBatch(DeviceBatch):
+    """A dataset batch that a loader call has already placed in the engine's input buffer
+    (magic_b200/overlap_input.py: `device_batches`).  `labels` is the matching numpy array of overlap areas."""
+
+    def __init__(self, model: "TangoEncoder", labels: np.ndarray):
+        self.model, self.labels = model, labels
+        self._token = object()
+        model._loaded_key = self._token
+
+    def _ensure_loaded(self) -> None:
+        if self.model._loaded_key is not self._token:
+            raise RuntimeError("this dataset batch is no longer resident: a later batch has replaced it")
+
+
 class DeviceLabels:
     def __init__(self, batch: DeviceBatch):
         self.batch = batch

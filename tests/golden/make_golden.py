@@ -6,6 +6,8 @@
 overlap_areas.npy      2a/OVERLAP_AREAS (pickle of 2000 int64 max-overlap labels) re-saved as a plain .npy
 overlap_micro_16.npz   the first 16 lock/key PNG pairs of overlap_micro.zip, 200x200, bit-packed ({0,255} -> 1 bit/px),
                        plus the pixel areas of all 100 locks and keys (generator statistics)
+png/{0..3}_{L,K}.png   the first four lock/key files of overlap_micro.zip, byte for byte (dataset samples, ~0.8 kB each):
+                       fixtures of the PNG loader path (row N2, tests/test_overlap_input.py)
 oracle_step_mini.npz   inputs and float64 outputs of one oracle step on a reduced geometry (losses, distance, a few
                        gradient tensors): pins the oracle against accidental edits of oracle/tango_oracle.py
 """
@@ -50,6 +52,17 @@ def micro():
                         area_lock=np.asarray(area_l), area_key=np.asarray(area_k))
 
 
+def png_fixtures():
+    z = zipfile.ZipFile(os.path.join(REF, "overlap_micro.zip"))
+    os.makedirs(os.path.join(HERE, "png"), exist_ok=True)
+    for i in range(4):
+        for kind in ("L", "K"):
+            cand = [n for n in z.namelist() if os.path.basename(n) == "%d_%s.png" % (i, kind)]
+            assert len(cand) == 1
+            with open(os.path.join(HERE, "png", "%d_%s.png" % (i, kind)), "wb") as f:
+                f.write(z.read(cand[0]))
+
+
 def oracle_step():
     import torch
     from oracle import tango_oracle as orc
@@ -70,5 +83,6 @@ def oracle_step():
 if __name__ == "__main__":
     labels()
     micro()
+    png_fixtures()
     oracle_step()
     print("golden fixtures written to", HERE)
