@@ -69,6 +69,13 @@ def test_full_size_8c(precision):
     _compare_step(orc.OracleConfig.experiment("8c"), 12, precision)
 
 
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+def test_benchmark_config_8d_at_full_batch(precision):
+    """bench.py's own workload: experiment 8d (L=200) at 4096 pairs -- the tile counts, split-K choices and
+    persistent-loop trip counts of the measured run, checked against the float64 oracle (about 10 s of CPU each)."""
+    _compare_step(orc.OracleConfig.experiment("8d"), 4096, precision)
+
+
 def test_full_size_11a_fp32():
     _compare_step(orc.OracleConfig.experiment("11a"), 8, "fp32")
 
