@@ -35,9 +35,9 @@ __global__ void gemm_finish_kernel(EpiArgs e, const float* __restrict__ ws, long
   epilogue_chunk<EPI, false>(e, TileOut{}, r, row, c * 32, M, N, dummy);
 }
 
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, int BN = 256>
 static cudaError_t set_smem() {
-  return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)gemm_smem_bytes(EPI));
 }
 
@@ -59,6 +59,12 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<false, false, EPI_DACT>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_SCATTER_F32>();
+  // 128-wide tiles: the short-K layers (hidden fwd / dgrad, heads, the small split-K wgrads)
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_STORE_F32, 128>();
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_ACT, 128>();
+  if (e == cudaSuccess) e = set_smem<false, false, EPI_STORE_F32, 128>();
+  if (e == cudaSuccess) e = set_smem<false, false, EPI_DACT, 128>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 128>();
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_ACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_DACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -193,6 +199,23 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   pl.epi = p.epi;
   if (p.ngroups < 1 || p.ngroups > kMaxGroups || p.nseg < 1 || p.nseg > kMaxSegs) return "bad ngroups/nseg";
   const bool a_mn = p.kind == GEMM_WGRAD, b_mn = p.kind != GEMM_DGRAD;
+  // Tile width.  128 for short-K problems whose 256-wide tiles would leave SMs without any tile (the decoder's hidden
+  // layers at M = 4096: 64 tiles; every layer at the reference's batch of 100): twice the CTAs, half the exposed
+  // epilogue (TileCfg in gemm_sm100.cuh; 10 -> 8 us per launch, profiles/r01m).  With one or two 256-wide tiles per SM
+  // the narrower tile only re-reads A twice as often -- those layers are bound by the L2 -> SM operand traffic
+  // (~690 cycles per k-block at either width, r01m trace) -- so they stay at 256.  Only the (kind, epilogue) pairs
+  // instantiated at 128 qualify; clusters stay at 256.
+  int bn = kBlockN;
+  {
+    const bool has128 = (p.epi == EPI_STORE_F32) || (p.kind == GEMM_FWD && p.epi == EPI_ACT) ||
+                        (p.kind == GEMM_DGRAD && p.epi == EPI_DACT);
+    const long long tiles256 = (long long)((p.M + kBlockM - 1) / kBlockM) * ((p.N + kBlockN - 1) / kBlockN) * p.ngroups;
+    const int kb = (p.K + kBlockK - 1) / kBlockK * p.nseg;
+    bool want = has128 && p.cluster_m <= 1 && p.N > 128 && tiles256 < (long long)num_sms && kb <= 32;
+    if (p.block_n == 128) want = has128 && p.cluster_m <= 1;
+    if (p.block_n == 256) want = false;
+    if (want) bn = 128;
+  }
   int cm_b = (b_mn && (p.cluster_m == 2 || p.cluster_m == 4)) ? p.cluster_m : 1;
   while (cm_b > 1 && ((p.M + kBlockM - 1) / kBlockM) % cm_b != 0) cm_b >>= 1;   // every CTA of a cluster gets a real M tile
   for (int g = 0; g < p.ngroups; ++g)
@@ -210,10 +233,10 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       if (!err.empty()) return "A: " + err;
       if (!b_mn) {   // Mat[N,K]
         if (B.cols != p.K) return "B cols != K";
-        err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, kBlockN);
+        err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, bn);
       } else {       // Mat[K,N]
         if (B.rows != p.K) return "B rows != K";
-        err = make_tmap_mn(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, (kBlockN / 64) / cm_b);
+        err = make_tmap_mn(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, (bn / 64) / cm_b);
       }
       if (!err.empty()) return "B: " + err;
     }
@@ -224,7 +247,8 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.nseg = p.nseg;
   a.ngroups = p.ngroups;
   a.tiles_m = (p.M + kBlockM - 1) / kBlockM;
-  a.tiles_n = (p.N + kBlockN - 1) / kBlockN;
+  a.tiles_n = (p.N + bn - 1) / bn;
+  a.bn = bn;
   const int cm = cm_b;
   a.cluster_m = cm;
   a.tiles_m /= cm;                                   // cluster rows from here on
@@ -273,11 +297,11 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   return "";
 }
 
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, int BN = 256>
 static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
   const int cm = pl.args.cluster_m;
   if (cm <= 1) {
-    launch_chain(gemm_tcgen05_kernel<A_MN, B_MN, EPI>, dim3(pl.grid), dim3(gemm_threads(EPI)), gemm_smem_bytes(EPI), s,
+    launch_chain(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, dim3(pl.grid), dim3(gemm_threads(EPI)), gemm_smem_bytes(EPI), s,
                  pl.args);
     return;
   }
@@ -299,7 +323,7 @@ static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
   if (max_clusters[cm] == 0) {
     cfg.gridDim = dim3(pl.grid);
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, gemm_tcgen05_kernel<A_MN, B_MN, EPI>, &cfg) != cudaSuccess || n <= 0) {
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, &cfg) != cudaSuccess || n <= 0) {
       (void)cudaGetLastError();
       n = pl.grid / cm;
     }
@@ -308,7 +332,7 @@ static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
   }
   long long ncl = pl.items < max_clusters[cm] ? pl.items : max_clusters[cm];
   cfg.gridDim = dim3((unsigned)(ncl * cm));
-  cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<A_MN, B_MN, EPI>, pl.args);
+  cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, pl.args);
 }
 
 int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
@@ -316,8 +340,13 @@ int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
   if (pl.two_pass) {
     zero_fill(pl.ws, sizeof(float) * pl.ws_ld * pl.args.M, s);
   }
-  const int key = pl.kind * 8 + pl.epi;
+  const int key = pl.kind * 8 + pl.epi + (pl.args.bn == 128 ? 64 : 0);
   switch (key) {
+    case 64 + GEMM_FWD * 8 + EPI_STORE_F32: launch_variant<false, true, EPI_STORE_F32, 128>(pl, s); break;
+    case 64 + GEMM_FWD * 8 + EPI_ACT: launch_variant<false, true, EPI_ACT, 128>(pl, s); break;
+    case 64 + GEMM_DGRAD * 8 + EPI_STORE_F32: launch_variant<false, false, EPI_STORE_F32, 128>(pl, s); break;
+    case 64 + GEMM_DGRAD * 8 + EPI_DACT: launch_variant<false, false, EPI_DACT, 128>(pl, s); break;
+    case 64 + GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32, 128>(pl, s); break;
     case GEMM_FWD * 8 + EPI_STORE_F32: launch_variant<false, true, EPI_STORE_F32>(pl, s); break;
     case GEMM_FWD * 8 + EPI_ACT: launch_variant<false, true, EPI_ACT>(pl, s); break;
     case GEMM_FWD * 8 + EPI_BCE: launch_variant<false, true, EPI_BCE>(pl, s); break;

@@ -43,6 +43,7 @@ struct GemmProblem {
   EpiArgs e[kMaxGroups];
   int M = 0, N = 0, K = 0;   // N: columns the epilogue writes (ACT: the output pitch)
   int force_splitk = 0;      // 0 = heuristic
+  int block_n = 0;           // tile width: 0 = heuristic, 128 or 256 forces it (self-test)
   int cluster_m = 1;         // CTAs per cluster along M sharing the B tile by TMA multicast (FWD / WGRAD kinds; 1, 2 or 4)
   float* ws = nullptr;       // fp32 workspace [M, ws_ld] for two-pass split-K (ACT / DACT); may be null
   long long ws_ld = 0;

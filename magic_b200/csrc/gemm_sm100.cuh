@@ -22,7 +22,7 @@
 namespace magic {
 
 constexpr int kBlockM = 128;
-constexpr int kBlockN = 256;
+constexpr int kBlockN = 256;   // default tile width; the kernel is also instantiated with BN = 128 (see TileCfg)
 constexpr int kBlockK = 64;   // 64 bf16 = one 128-byte swizzle row
 constexpr int kStages = 4;
 constexpr int kUmmaK = 16;
@@ -36,6 +36,19 @@ __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_w
 constexpr uint32_t kStageBytesA = kBlockM * kBlockK * 2;   // 16 KiB
 constexpr uint32_t kStageBytesB = kBlockN * kBlockK * 2;   // 32 KiB
 constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
+// Tile width BN = 256: 4 stages x 48 KiB, two 256-column accumulators.  BN = 128 (the short-K layers, where the
+// epilogue of a tile outlasts its 8 k-blocks of MMA and the last one is exposed): 6 stages x 32 KiB -- the same
+// 192 KiB -- and four 128-column accumulators, so a CTA's exposed final epilogue is half as long, the issuer may run
+// three tiles ahead of the epilogue warps, and twice as many tiles fill the 148 SMs more evenly.
+template <int BN>
+struct TileCfg {
+  static_assert(BN == 128 || BN == 256, "tile width");
+  static constexpr int kStagesN = BN == 256 ? 4 : 6;
+  static constexpr uint32_t kBytesB = BN * kBlockK * 2;
+  static constexpr uint32_t kBytes = kStageBytesA + kBytesB;
+  static constexpr int kAcc = 512 / BN;                    // accumulator stages in the 512 TMEM columns
+  static_assert(kStagesN * kBytes == kStages * kStageBytes, "both tile widths use the same pipeline footprint");
+};
 constexpr uint32_t kAtomBytes = 64 * kBlockK * 2;          // one 64(MN) x 64(K) MN-major TMA box
 constexpr uint32_t kTmemCols = 2 * kBlockN;                // 512: two accumulator stages
 constexpr uint32_t kGemmSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
@@ -96,6 +109,7 @@ struct GemmArgs {
   int nseg, ngroups, splitk;
   int tiles_m, tiles_n;
   int m_fastest;     // tile order: consecutive work items walk M first (B is the large operand) or N first
+  int bn;            // tile width the plan was built for (128 or 256) = the kernel's BN
   int cluster_m;     // CTAs per cluster along M (1, 2 or 4): they share the N tile and receive B by TMA multicast
   long long* trace;  // diagnostics: [grid][64] clock64 stamps of the phases of each CTA (selftest "trace"), or nullptr
   CUtensorMap tout[kMaxGroups][2];   // output tiles (box 32 cols x 32 rows): [g][0] fp32 or bf16 hi plane, [g][1] lo plane
@@ -125,7 +139,7 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int cr
   it.kb0 = ks * per;
   it.kb1 = min(total_kb, it.kb0 + per);
   it.m0 = mt * kBlockM;
-  it.n0 = nt * kBlockN;
+  it.n0 = nt * a.bn;
   return it;
 }
 
@@ -489,7 +503,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const TileOut& 
 static_assert(sizeof(GemmArgs) <= 4096, "kernel parameter space");
 
 // ---------------------------------------------------------------------------- the kernel
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, int BN>
 // 112 registers: three of this kernel's warps (3 x 32 x 112) and three warps of the batch generator (3 x 32 x 56) fit
 // the 16K registers of one SM sub-partition, so the generator's CTA stays co-resident with every GEMM variant; it is
 // the 576-thread BCE variant has five warps on a sub-partition, hence 96.
@@ -506,17 +520,20 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       args.trace[(size_t)blockIdx.x * 64 + 11] = (long long)gt;
     }
   }
+  using Cfg = TileCfg<BN>;
+  constexpr int kNS = Cfg::kStagesN;       // pipeline stages
+  constexpr int kAcc = Cfg::kAcc;          // accumulator stages
   extern __shared__ uint8_t smem_raw[];
   // 128-byte swizzle atoms need 1024-byte aligned stage bases
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + kStages * kStageBytesA;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  uint8_t* smem_b = smem + kNS * kStageBytesA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);   // = kNS * Cfg::kBytes
   uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + kStages;
-  uint64_t* tfull_bar = bars + 2 * kStages;
-  uint64_t* tempty_bar = bars + 2 * kStages + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  uint64_t* empty_bar = bars + kNS;
+  uint64_t* tfull_bar = bars + 2 * kNS;
+  uint64_t* tempty_bar = bars + 2 * kNS + kAcc;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kNS + 2 * kAcc);   // (2*6 + 2*4) * 8 + 4 <= 256 bytes
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -532,11 +549,11 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         ptx::tma_prefetch_desc(&args.ta[g][s]);
         ptx::tma_prefetch_desc(&args.tb[g][s]);
       }
-    for (int i = 0; i < kStages; ++i) {
+    for (int i = 0; i < kNS; ++i) {
       ptx::mbar_init(&full_bar[i], 1);
       ptx::mbar_init(&empty_bar[i], CM);   // one arrival per CTA of the cluster (multicast commit)
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kAcc; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
       ptx::mbar_init(&tempty_bar[i], epi_warps(EPI) * 32);
     }
@@ -564,9 +581,9 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
           const int seg = kb / args.kblocks;
           const int k0 = (kb - seg * args.kblocks) * kBlockK;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          ptx::mbar_expect_tx(&full_bar[stage], kStageBytes);
+          ptx::mbar_expect_tx(&full_bar[stage], Cfg::kBytes);
           uint8_t* sa = smem_a + stage * kStageBytesA;
-          uint8_t* sb = smem_b + stage * kStageBytesB;
+          uint8_t* sb = smem_b + stage * Cfg::kBytesB;
           const CUtensorMap* ta = &args.ta[it.g][seg];
           const CUtensorMap* tb = &args.tb[it.g][seg];
           if constexpr (!A_MN) {
@@ -575,24 +592,24 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
             ptx::tma_load_3d(ta, &full_bar[stage], sa, 0, k0, it.m0 >> 6);      // box {64 m, 64 k, 2 slabs}
           }
           if constexpr (!B_MN) {
-            ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);              // box {64 k, 256 n}
+            ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);              // box {64 k, BN n}
           } else if (CM == 1) {
-            ptx::tma_load_3d(tb, &full_bar[stage], sb, 0, k0, it.n0 >> 6);      // box {64 n, 64 k, 4 slabs}
+            ptx::tma_load_3d(tb, &full_bar[stage], sb, 0, k0, it.n0 >> 6);      // box {64 n, 64 k, BN/64 slabs}
           } else {
             // the cluster shares this B tile: each CTA fetches 4/CM slabs and multicasts them to all
-            const int per = (kBlockN / 64) / CM;
+            const int per = (BN / 64) / CM;
             ptx::tma_load_3d_multicast(tb, &full_bar[stage], sb + crank * per * kAtomBytes, 0, k0,
                                        (it.n0 >> 6) + crank * per, cmask);
           }
           if (w == work0 && kb == it.kb0) MAGIC_TR(3);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == kNS) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(kBlockM, kBlockN, A_MN, B_MN);
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(kBlockM, BN, A_MN, B_MN);
       // K-major SW128: 8-row groups 1024 B apart, K advance = 32 B inside the swizzle row.
       // MN-major SW128: 64-element MN atoms kBlockK*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO),
       //                 K advance = 16 rows * 128 B.
@@ -601,17 +618,17 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       uint32_t stage = 0, phase = 0, iter = 0;
       for (int w = work0; w < total_work; w += work_stride, ++iter) {
         const WorkItem it = decode_work(args, w, crank);
-        const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
+        const uint32_t acc = iter % kAcc, acc_phase = (iter / kAcc) & 1;
         ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
         if (iter < 8) MAGIC_TR(16 + iter * 5 + 0);
-        const uint32_t d_tmem = tmem_base + acc * kBlockN;
+        const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
           if (w == work0 && kb == it.kb0) MAGIC_TR(4);
           const uint32_t a_base = ptx::smem_u32(smem_a + stage * kStageBytesA);
-          const uint32_t b_base = ptx::smem_u32(smem_b + stage * kStageBytesB);
+          const uint32_t b_base = ptx::smem_u32(smem_b + stage * Cfg::kBytesB);
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             const uint64_t da = ptx::make_smem_desc_sw128(a_base + k * a_kadv, a_lbo, 1024);
@@ -620,7 +637,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
           }
           if (CM > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
           else ptx::umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == kNS) { stage = 0; phase ^= 1; }
         }
         ptx::umma_commit(&tfull_bar[acc]);        // accumulator complete -> epilogue
         if (w == work0) MAGIC_TR(5);
@@ -639,7 +656,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     // even/odd, so every scheduler has two epilogue warps to overlap latencies with.
     const int q = warp & 3;
     constexpr int kGroups = epi_warps(EPI) / 4;          // warps per lane quarter; chunk c belongs to group c % kGroups
-    constexpr int kMaxOwn = (kBlockN / 32 + kGroups - 1) / kGroups;
+    constexpr int kMaxOwn = (BN / 32 + kGroups - 1) / kGroups;
     const int grp = (warp - 2) >> 2;
     uint32_t iter = 0;
     float loss_acc = 0.f;
@@ -650,7 +667,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       const WorkItem nit = decode_work(args, w_item, crank);
       const EpiArgs& ne = args.epi[nit.g];
       const int nrow = nit.m0 + q * 32 + lane;
-      const int nn = (min(kBlockN, args.N - nit.n0) + 31) >> 5;
+      const int nn = (min(BN, args.N - nit.n0) + 31) >> 5;
 #pragma unroll
       for (int k = 0; k < kMaxOwn; ++k) {
         const int c = grp + k * kGroups;
@@ -663,9 +680,9 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     for (int w = work0; w < total_work; w += work_stride, ++iter) {
       const WorkItem it = decode_work(args, w, crank);
       const EpiArgs& e = args.epi[it.g];
-      const uint32_t acc = iter & 1, acc_phase = (iter >> 1) & 1;
+      const uint32_t acc = iter % kAcc, acc_phase = (iter / kAcc) & 1;
       const int row = it.m0 + q * 32 + lane;
-      const int ncols = min(kBlockN, args.N - it.n0);
+      const int ncols = min(BN, args.N - it.n0);
       const int nchunks = (ncols + 31) >> 5;
       if constexpr (EPI == EPI_BCE) {
 #pragma unroll
@@ -706,7 +723,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         if (c0 >= nchunks || (e.dbg & 4)) break;   // dbg 4: mainloop-only timing, the accumulator is never read
         const bool two = kBatch == 2 && (k + 1 < kMaxOwn) && c1 < nchunks;
         uint32_t ra[32], rb[32];
-        const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * kBlockN;
+        const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
         ptx::tmem_ld_32x32(tbase + c0 * 32, ra);
         if (two) ptx::tmem_ld_32x32(tbase + c1 * 32, rb);
         ptx::tmem_ld_wait();

@@ -70,6 +70,7 @@ static void host_ref(int kind, int M, int N, int K, int nseg, const HostMat* a, 
 }
 
 static int g_cluster = 1;   // cluster_m applied to the problems built below
+static int g_bn = 0;        // block_n applied to the problems built below (0 = the planner's choice)
 
 static void test_store(int kind, int M, int N, int K, int nseg, int split, int sms) {
   HostMat a[3], b[3];
@@ -84,6 +85,7 @@ static void test_store(int kind, int M, int N, int K, int nseg, int split, int s
   GemmProblem p;
   p.kind = kind; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
   p.cluster_m = g_cluster;
+  p.block_n = g_bn;
   for (int s = 0; s < nseg; ++s) { p.a[0][s] = a[s].mat(); p.b[0][s] = b[s].mat(); }
   EpiArgs e = {};
   e.out = dout; e.ld_out = ldo; e.alpha = 0.5f;
@@ -176,6 +178,7 @@ static void test_fused(int epi, int M, int Nv, int K, int split, int precise, in
   GemmProblem p;
   p.kind = kind; p.epi = epi; p.M = M; p.K = K; p.force_splitk = split;
   p.cluster_m = g_cluster;
+  p.block_n = g_bn;
   p.N = epi == EPI_BCE ? Nv : (int)ldo;
   p.a[0][0] = a.mat(); p.b[0][0] = b.mat();
   p.ws = ws; p.ws_ld = ldo;
@@ -245,6 +248,7 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   GemmProblem p;
   p.kind = kind; p.epi = epi; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
   p.cluster_m = g_cluster;
+  p.block_n = g_bn;
   p.a[0][0] = kind == GEMM_WGRAD ? Mat(a, K, M, (M + 63) / 64 * 64) : Mat(a, M, K, (K + 63) / 64 * 64);
   p.b[0][0] = kind == GEMM_DGRAD ? Mat(b, N, K, (K + 63) / 64 * 64) : Mat(b, K, N, (N + 63) / 64 * 64);
   EpiArgs e = {};
@@ -259,6 +263,11 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
     CK(cudaMemset(scalar, 0, 4));
     e.xbits = bits; e.xb_ld = xb_ld; e.scalar = scalar; e.n_valid = N; e.aux_split = 1 << 30;
     e.ld_out = (N + 7) / 8 * 8;
+  }
+  if (epi == EPI_ACT || epi == EPI_DACT) {   // bf16 activation out (hi plane only), tanh; DACT reads `b` as the stored y
+    e.act = ACT_TANH; e.n_valid = N - 1; e.ld_out = (N + 63) / 64 * 64; e.aux_split = 1 << 30;
+    e.aux = reinterpret_cast<const __nv_bfloat16*>(out); e.ld_aux = e.ld_out;
+    p.N = (int)e.ld_out;
   }
   if (const char* d = getenv("MAGIC_EPI_DBG")) e.dbg = atoi(d);
   p.e[0] = e;
@@ -359,6 +368,23 @@ int main(int argc, char** argv) {
     test_fused(EPI_ACT, 2048, 500, 501, 1, 1, sms);
   }
   g_cluster = 1;
+  // 128-wide tiles (6 pipeline stages, 4 accumulator stages), every kind / epilogue instantiated at that width
+  g_bn = 128;
+  test_store(GEMM_FWD, 128, 128, 64, 1, 1, sms);
+  test_store(GEMM_FWD, 300, 500, 200, 1, 1, sms);
+  test_store(GEMM_FWD, 2000, 500, 1000, 2, 3, sms);
+  test_store(GEMM_DGRAD, 300, 501, 840, 1, 1, sms);
+  test_store(GEMM_DGRAD, 1300, 501, 840, 3, 4, sms);
+  test_store(GEMM_WGRAD, 501, 500, 700, 1, 1, sms);
+  test_store(GEMM_WGRAD, 501, 140, 2048, 2, 0, sms);
+  test_wgrad_groups(1100, 500, 512, sms);
+  test_fused(EPI_ACT, 300, 500, 501, 1, 1, sms);
+  test_fused(EPI_ACT, 3000, 500, 501, 1, 0, sms);
+  test_fused(EPI_ACT, 300, 500, 2000, 4, 1, sms);
+  test_fused(EPI_DACT, 512, 500, 400, 1, 1, sms);
+  test_fused(EPI_DACT, 5120, 500, 512, 1, 1, sms);
+  test_fused(EPI_DACT, 512, 500, 4000, 5, 1, sms);
+  g_bn = 0;
   printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
   if (do_bench) {
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");
@@ -374,6 +400,15 @@ int main(int argc, char** argv) {
     bench(GEMM_WGRAD, 512, 40000, 4096, 1, sms, "dec out wgrad");
     bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad");
     bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd");
+    bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd, tanh epilogue", EPI_ACT);
+    bench(GEMM_DGRAD, 16384, 512, 512, 1, sms, "hidden dgrad, tanh' epilogue", EPI_DACT);
+    g_bn = 256;
+    bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd, tanh, BN=256", EPI_ACT);
+    bench(GEMM_DGRAD, 16384, 512, 512, 1, sms, "hidden dgrad, tanh', BN=256", EPI_DACT);
+    bench(GEMM_FWD, 4096, 512, 512, 1, sms, "dec hidden fwd, tanh, BN=256", EPI_ACT);
+    g_bn = 128;
+    bench(GEMM_FWD, 4096, 512, 512, 1, sms, "dec hidden fwd, tanh, BN=128", EPI_ACT);
+    g_bn = 0;
     bench(GEMM_WGRAD, 512, 512, 8192, 0, sms, "hidden wgrad (auto split)");
     bench(GEMM_FWD, 8192, 8192, 8192, 1, sms, "square 8192");
     bench(GEMM_FWD, 4096, 40000, 256, 1, sms, "dec-out shape, K=256");
