@@ -748,7 +748,9 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     if constexpr (EPI == EPI_BCE) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) loss_acc += __shfl_xor_sync(0xffffffffu, loss_acc, o);
-      if (lane == 0 && total_work > 0) atomicAdd(args.epi[0].scalar, loss_acc * args.epi[0].alpha);
+      // one atomic per CTA (not per warp: 2368 same-address atomics serialise in L2 at the kernel's tail): the warp
+      // sums meet in the staging slots, which are idle after bulk_wait_all()
+      if (lane == 0) *reinterpret_cast<float*>(smem + kTileStageOffset + (warp - 2) * 2048) = loss_acc;
     }
   }
 
@@ -758,6 +760,14 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
+  }
+  if constexpr (EPI == EPI_BCE) {
+    if (threadIdx.x == 64 && work0 < total_work) {
+      float sum = 0.f;
+#pragma unroll
+      for (int w = 0; w < epi_warps(EPI); ++w) sum += *reinterpret_cast<const float*>(smem + kTileStageOffset + w * 2048);
+      atomicAdd(args.epi[0].scalar, sum * args.epi[0].alpha);
+    }
   }
   if (threadIdx.x == 0) MAGIC_TR(10);
 #undef MAGIC_TR

@@ -58,7 +58,7 @@ void zero_fill(void* ptr, size_t bytes, cudaStream_t s) {   // ptr 16-byte align
 // the latent axis and the batch-axis sums of squares the cosine metric needs stay in registers until the end.
 constexpr int kLatWarps = 8;
 constexpr int kLatRowsPerWarp = 2;
-constexpr int kLatSlab = 4;    // 1024 CTAs at B = 4096: enough warps to hide the load latencies (40 -> 15 us, r01h)
+constexpr int kLatSlab = 8;    // 512 CTAs at B = 4096
 
 __global__ void __launch_bounds__(256) latent_forward_kernel(LatentArgs a) {
   ptx::grid_dep_wait();
@@ -104,11 +104,20 @@ __global__ void __launch_bounds__(256) latent_forward_kernel(LatentArgs a) {
       atomicAdd(&a.colsq[L + j], sq_k);
     }
   }
+  // one atomic pair per CTA: with one per warp, 8192 same-address atomics serialised in L2 (~30 us of a 40 us kernel)
+  __shared__ float red[2][8];
   kl = warp_sum(kl);
   def = warp_sum(def);
-  if ((threadIdx.x & 31) == 0 && (kl != 0.f || def != 0.f)) {
-    atomicAdd(&a.sums[1], kl * a.inv_bg);
-    atomicAdd(&a.sums[2], def * a.def_weight * a.inv_bg);
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = kl; red[1][threadIdx.x >> 5] = def; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float k2 = 0.f, d2 = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { k2 += red[0][w]; d2 += red[1][w]; }
+    if (k2 != 0.f || d2 != 0.f) {
+      atomicAdd(&a.sums[1], k2 * a.inv_bg);
+      atomicAdd(&a.sums[2], d2 * a.def_weight * a.inv_bg);
+    }
   }
 }
 
@@ -158,9 +167,16 @@ __global__ void __launch_bounds__(kLatWarps * 32) latent_metric_kernel(LatentArg
       for (int j = lane; j < L; j += 32) atomicAdd(&sm[j], gi * (zl[j] * s_ra[j]) * (zk[j] * s_rb[j]));
     }
   }
-  if (lane == 0 && tl != 0.f) atomicAdd(&a.sums[3], tl * a.inv_bg);
+  __shared__ float red_tl[kLatWarps];
+  if (lane == 0) red_tl[warp] = tl;
+  __syncthreads();                     // (also orders the sm[] atomics before the column pass below)
+  if (threadIdx.x == 0) {
+    float t2 = 0.f;
+#pragma unroll
+    for (int w = 0; w < kLatWarps; ++w) t2 += red_tl[w];
+    if (t2 != 0.f) atomicAdd(&a.sums[3], t2 * a.inv_bg);
+  }
   if (cosine) {
-    __syncthreads();
     for (int j = threadIdx.x; j < L; j += blockDim.x) atomicAdd(&a.colS[j], sm[j]);
   }
 }
