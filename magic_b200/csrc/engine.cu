@@ -434,6 +434,8 @@ std::string Engine::build_plans() {
 
   // ---------------- backward of `cost` through the decoder
   zero_.clear();
+  std::vector<GemmProblem> small_wg;   // the weight-gradient problems of every layer but the two 40000-wide ones
+  GemmProblem enc0_wg[2];
   auto wgrad1 = [&](GemmPlan* pl, const Act& x, int xcols, const Act& dy, int layer) -> std::string {
     GemmProblem p;
     p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.M = xcols; p.N = lin[layer].Nv; p.K = B;
@@ -441,6 +443,7 @@ std::string Engine::build_plans() {
                  amat(dy, true, 0, B, p.N), false);
     p.e[0] = f32_epi(g1_ + lin[layer].off, lin[layer].ld, inv_bg);
     MAGIC_TRY(finish(p, pl, "wgrad dec"));
+    if (layer != iOut) small_wg.push_back(p);
     if (pl->args.splitk > 1) zero_.push_back({g1_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
     return "";
   };
@@ -479,6 +482,8 @@ std::string Engine::build_plans() {
     p.e[0] = f32_epi(g1_ + lin[layer].off, lin[layer].ld, 1.f);
     p.e[1] = f32_epi(g2_ + lin[layer].off, lin[layer].ld, 1.f);
     MAGIC_TRY(finish(p, pl, "wgrad enc"));
+    if (layer != 0) small_wg.push_back(p);
+    else enc0_wg[pl == &pl_wg_enc0_alt_ ? 1 : 0] = p;
     if (pl->args.splitk > 1) {
       zero_.push_back({g1_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
       zero_.push_back({g2_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
@@ -508,6 +513,30 @@ std::string Engine::build_plans() {
     MAGIC_TRY(wgrad2(&pl_wg_enc0_alt_, in_[1].X, D + 1, true, dH_[0], 0));
     zero_.resize(nz);                        // same gradient windows as the first variant
     flops -= pl_wg_enc0_alt_.flops;
+  }
+  // Single GPU: the small layers' weight gradients (76 whole-K tiles at the 8d shape) ride in the last, partly empty
+  // wave of the first-layer launch instead of six launches of their own; no split-K, so no gradient windows to clear.
+  fuse_wg_ = false;
+  {
+    const char* fw = getenv("MAGIC_FUSE_WGRAD");
+    bool want = c.world == 1 && !(fw && atoi(fw) == 0);
+    size_t nx = 0;
+    for (auto& sp : small_wg) { nx += sp.ngroups; want = want && sp.nseg == enc0_wg[0].nseg; }
+    if (want && nx <= (size_t)kMaxExtra) {
+      for (int v = 0; v < 2; ++v) {
+        GemmProblem p = enc0_wg[v];
+        for (auto& sp : small_wg)
+          for (int g = 0; g < sp.ngroups; ++g) {
+            GemmExtra x;
+            for (int sg = 0; sg < sp.nseg; ++sg) { x.a[sg] = sp.a[g][sg]; x.b[sg] = sp.b[g][sg]; }
+            x.e = sp.e[g]; x.M = sp.M; x.N = sp.N; x.K = sp.K;
+            p.extra.push_back(x);
+          }
+        MAGIC_TRY(finish(p, &pl_wg_enc0_fused_[v], "wgrad enc0 + small layers"));
+        flops -= pl_wg_enc0_fused_[v].flops;
+      }
+      fuse_wg_ = true;
+    }
   }
   stats.gemm_flops_per_step = flops;
   return "";
@@ -751,15 +780,18 @@ std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) 
 }
 
 std::string Engine::run_backward(int* launches) {
-  prof_begin("memset.grad_windows");
-  for (auto& z : zero_) zero_fill(z.ptr, z.bytes, stream);
-  prof_end();
+  const bool fw = fuse_wg_;                        // small-layer wgrads folded into the first-layer launch
+  if (!fw) {
+    prof_begin("memset.grad_windows");
+    for (auto& z : zero_) zero_fill(z.ptr, z.bytes, stream);
+    prof_end();
+  }
   const bool dp = cfg.world > 1 && !dp_fused_;     // NCCL all-reduce buckets (baseline path)
   MAGIC_TRY(launch(dp_fused_ ? pl_wg_out_sc_ : pl_wg_out_, launches, "gemm.wgrad_dec_out"));
   MAGIC_TRY(launch(pl_dg_out_, launches, "gemm.dgrad_dec_out"));
-  MAGIC_TRY(launch(pl_wg_h2_, launches, "gemm.wgrad_small"));
+  if (!fw) MAGIC_TRY(launch(pl_wg_h2_, launches, "gemm.wgrad_small"));
   MAGIC_TRY(launch(pl_dg_h2_, launches, "gemm.dgrad_small"));
-  MAGIC_TRY(launch(pl_wg_h1_, launches, "gemm.wgrad_small"));
+  if (!fw) MAGIC_TRY(launch(pl_wg_h1_, launches, "gemm.wgrad_small"));
   if (dp) {   // bucket 0: all decoder gradients are final -> reduce them while the encoder backward runs
     MAGIC_CUDA(cudaEventRecord(ev_bwd_[0], stream));
     MAGIC_CUDA(cudaStreamWaitEvent(comm_stream_, ev_bwd_[0], 0));
@@ -772,7 +804,7 @@ std::string Engine::run_backward(int* launches) {
     MAGIC_CUDA(cudaEventRecord(ev_aux_fork_, stream));
     MAGIC_CUDA(cudaStreamWaitEvent(aux_stream_, ev_aux_fork_, 0));
     AdamArgs a = adam_;
-    a.begin = n_both;
+    a.begin = early_begin_;
     a.thin = 2 * num_sms;
     prof_begin("adam.decoder", 0, aux_stream_); adam_dual(a, aux_stream_); prof_end(aux_stream_);
     MAGIC_CUDA(cudaEventRecord(ev_aux_join_, aux_stream_));
@@ -781,10 +813,10 @@ std::string Engine::run_backward(int* launches) {
   LatentArgs la = latent_args(nullptr, in_[cur_].labels);
   prof_begin("latent.backward"); latent_backward(la, stream); prof_end();
   *launches += 1;
-  MAGIC_TRY(launch(pl_wg_head_, launches, "gemm.wgrad_small"));
+  if (!fw) MAGIC_TRY(launch(pl_wg_head_, launches, "gemm.wgrad_small"));
   MAGIC_TRY(launch(pl_dg_head_, launches, "gemm.dgrad_small"));
   for (int i = E - 1; i >= 1; --i) {
-    MAGIC_TRY(launch(pl_wg_enc_[i], launches, "gemm.wgrad_small"));
+    if (!fw) MAGIC_TRY(launch(pl_wg_enc_[i], launches, "gemm.wgrad_small"));
     MAGIC_TRY(launch(pl_dg_enc_[i], launches, "gemm.dgrad_small"));
   }
   if (dp) {   // bucket 1: hidden encoder layers + heads, both optimisers
@@ -810,7 +842,8 @@ std::string Engine::run_backward(int* launches) {
     prof_end();
     *launches += 2;
   }
-  MAGIC_TRY(launch(dp_fused_ ? pl_wg_enc0_sc_[cur_] : (cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0]), launches, "gemm.wgrad_enc0"));
+  MAGIC_TRY(launch(dp_fused_ ? pl_wg_enc0_sc_[cur_] : fw ? pl_wg_enc0_fused_[cur_] : (cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0]),
+                   launches, "gemm.wgrad_enc0"));
   mark_consumed(in_[cur_]);                 // last read of the input buffer in the step
   if (dp) {   // bucket 2: the two 40000-wide first-layer gradients
     MAGIC_CUDA(cudaEventRecord(ev_bwd_[2], stream));
@@ -838,6 +871,9 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   adam_.lr_t2 = (float)(cfg.lr2 * corr);
   adam_.beta1 = cfg.beta1; adam_.beta2 = cfg.beta2; adam_.eps = cfg.eps;
   early_adam_ = apply && cfg.world == 1 && early_adam_ok_;
+  // with the small wgrads folded into the last launch only the decoder's output layer (98% of the decoder) is final early
+  early_begin_ = fuse_wg_ ? lin[iOut].off : n_both;
+  if (early_begin_ % 4) early_adam_ = false;
   std::string err = run_forward(d_eps3, true, &launches);
   if (err.empty()) err = run_backward(&launches);
   have_labels_ext_ = false;
@@ -868,7 +904,7 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   } else if (apply) {
     ++t;
     AdamArgs a = adam_;
-    if (early_adam_) a.n_total = n_both;     // the decoder range is already in flight on aux_stream_
+    if (early_adam_) a.n_total = early_begin_;   // the rest of the decoder range is already in flight on aux_stream_
     prof_begin("adam.dual"); adam_dual(a, stream); prof_end();
     ++launches;
     if (early_adam_) MAGIC_CUDA(cudaStreamWaitEvent(stream, ev_aux_join_, 0));

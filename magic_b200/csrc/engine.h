@@ -150,6 +150,8 @@ class Engine {
   // plans
   std::vector<GemmPlan> fwd_enc_;   // E hidden + heads
   GemmPlan pl_d1_, pl_d2_, pl_out_bce_, pl_out_sig_;
+  GemmPlan pl_wg_enc0_fused_[2];            // first-layer wgrad + every small layer's wgrad as extra problems (world == 1)
+  bool fuse_wg_ = false;
   GemmPlan fwd_enc0_alt_, pl_out_bce_alt_, pl_wg_enc0_alt_;   // the plans that read the input batch, on in_[1]
   GemmPlan pl_wg_out_, pl_dg_out_, pl_wg_h2_, pl_dg_h2_, pl_wg_h1_, pl_dg_h1_;
   GemmPlan pl_wg_head_, pl_dg_head_;
@@ -167,6 +169,7 @@ class Engine {
   cudaEvent_t ev_aux_fork_ = nullptr, ev_aux_join_ = nullptr;
   AdamArgs adam_;
   bool early_adam_ = false, early_adam_ok_ = true;
+  long long early_begin_ = 0;               // first parameter of the early (side-stream) Adam range
   cudaEvent_t ev_bwd_[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_comm_ = nullptr;
   std::string allreduce(float* buf, size_t n, cudaStream_t s);

@@ -289,11 +289,66 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
     std::string err = build_out_maps(pl, g);
     if (!err.empty()) return "out: " + err;
   }
-  const long long items = (long long)tiles * split;
+  long long items = (long long)tiles * split;
+  pl.flops = 2.0 * p.M * (double)p.N * p.K * p.nseg * p.ngroups;
+  // ---- appended problems: descriptors into one device buffer, work items after the main problem's
+  a.nextra = 0;
+  a.xdev = nullptr;
+  pl.xbuf.reset();
+  if (!p.extra.empty()) {
+    if (p.epi != EPI_STORE_F32 || pl.epi != EPI_STORE_F32 || cm != 1) return "extra problems need EPI_STORE_F32 and no cluster";
+    if ((int)p.extra.size() > kMaxExtra) return "too many extra problems";
+    std::vector<GemmExtraDev> host(p.extra.size());
+    memset(host.data(), 0, sizeof(GemmExtraDev) * host.size());
+    int item0 = 0;
+    for (size_t i = 0; i < p.extra.size(); ++i) {
+      const GemmExtra& x = p.extra[i];
+      GemmExtraDev& d = host[i];
+      for (int sgm = 0; sgm < p.nseg; ++sgm) {
+        const Mat& A = x.a[sgm];
+        const Mat& Bm = x.b[sgm];
+        std::string err;
+        if (!a_mn) {
+          if (A.cols != x.K) return "extra A cols != K";
+          err = make_tmap(&d.ta[sgm], A.ptr, A.cols, A.rows, A.ld, kBlockK, kBlockM);
+        } else {
+          if (A.rows != x.K) return "extra A rows != K";
+          err = make_tmap_mn(&d.ta[sgm], A.ptr, A.cols, A.rows, A.ld, kBlockK, kBlockM / 64);
+        }
+        if (!err.empty()) return "extra A: " + err;
+        if (!b_mn) {
+          if (Bm.cols != x.K) return "extra B cols != K";
+          err = make_tmap(&d.tb[sgm], Bm.ptr, Bm.cols, Bm.rows, Bm.ld, kBlockK, bn);
+        } else {
+          if (Bm.rows != x.K) return "extra B rows != K";
+          err = make_tmap_mn(&d.tb[sgm], Bm.ptr, Bm.cols, Bm.rows, Bm.ld, kBlockK, bn / 64);
+        }
+        if (!err.empty()) return "extra B: " + err;
+      }
+      d.epi = x.e;
+      d.epi.atomic = 0;
+      if ((reinterpret_cast<uintptr_t>(x.e.out) & 15) != 0 || (x.e.ld_out * 4) % 16 != 0) return "extra output not 16-byte aligned";
+      std::string err = make_tmap_out(&d.tout[0], x.e.out, true, x.N, x.M, x.e.ld_out);
+      if (!err.empty()) return "extra out: " + err;
+      const int tm = (x.M + kBlockM - 1) / kBlockM, tn = (x.N + bn - 1) / bn;
+      a.x_item0[i] = item0;
+      a.x_m[i] = x.M; a.x_n[i] = x.N; a.x_kb[i] = (x.K + kBlockK - 1) / kBlockK; a.x_tn[i] = tn;
+      item0 += tm * tn;
+      pl.flops += 2.0 * x.M * (double)x.N * x.K * p.nseg;
+    }
+    a.x_item0[p.extra.size()] = item0;
+    a.nextra = (int)p.extra.size();
+    void* dptr = nullptr;
+    if (cudaMalloc(&dptr, sizeof(GemmExtraDev) * host.size()) != cudaSuccess) return "cudaMalloc(extra descriptors) failed";
+    pl.xbuf = std::shared_ptr<void>(dptr, [](void* q) { cudaFree(q); });
+    if (cudaMemcpy(dptr, host.data(), sizeof(GemmExtraDev) * host.size(), cudaMemcpyHostToDevice) != cudaSuccess)
+      return "cudaMemcpy(extra descriptors) failed";
+    a.xdev = static_cast<const GemmExtraDev*>(dptr);
+    items += item0;
+  }
   pl.items = items;
   const long long slots = num_sms / cm;              // refined at launch by the occupancy query when cm > 1
   pl.grid = (int)(items < slots ? items : slots) * cm;
-  pl.flops = 2.0 * p.M * (double)p.N * p.K * p.nseg * p.ngroups;
   return "";
 }
 

@@ -3,7 +3,9 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <memory>
 #include <string>
+#include <vector>
 #include "gemm_sm100.cuh"
 
 namespace magic {
@@ -33,6 +35,15 @@ struct GemmPlan {
   EpiArgs finish_epi[kMaxGroups];
   int finish_epi_kind = 0;
   double flops = 0;
+  std::shared_ptr<void> xbuf;   // device copy of the extras' descriptors (GemmExtraDev[nextra])
+};
+
+// A problem appended to another problem's launch (GemmExtraDev in gemm_sm100.cuh): same kind / epilogue / segment
+// count, own shape, operands and output; never split along K.
+struct GemmExtra {
+  Mat a[kMaxSegs], b[kMaxSegs];
+  EpiArgs e;
+  int M = 0, N = 0, K = 0;
 };
 
 struct GemmProblem {
@@ -43,6 +54,7 @@ struct GemmProblem {
   EpiArgs e[kMaxGroups];
   int M = 0, N = 0, K = 0;   // N: columns the epilogue writes (ACT: the output pitch)
   int force_splitk = 0;      // 0 = heuristic
+  std::vector<GemmExtra> extra;   // appended problems (EPI_STORE_F32 only)
   int block_n = 0;           // tile width: 0 = heuristic, 128 or 256 forces it (self-test)
   int cluster_m = 1;         // CTAs per cluster along M sharing the B tile by TMA multicast (FWD / WGRAD kinds; 1, 2 or 4)
   float* ws = nullptr;       // fp32 workspace [M, ws_ld] for two-pass split-K (ACT / DACT); may be null

@@ -100,6 +100,18 @@ struct EpiArgs {
   int dbg;           // diagnostics (MAGIC_EPI_DBG): 1 = BCE epilogue without stores, 4 = no epilogue work at all (main loop only)
 };
 
+// "Extra" problems ride at the end of a launch's work list: same operand layouts, precision segments and epilogue kind
+// as the main problem, but their own shapes, operands and outputs (the engine folds the small layers' weight
+// gradients into the tail of the first layer's wgrad launch, whose last wave would otherwise leave half the SMs
+// idle).  Their descriptors live in global memory so that ordinary launches do not carry them as parameters.
+constexpr int kMaxExtra = 20;
+struct alignas(128) GemmExtraDev {
+  CUtensorMap ta[kMaxSegs];
+  CUtensorMap tb[kMaxSegs];
+  CUtensorMap tout[2];
+  EpiArgs epi;
+};
+
 struct GemmArgs {
   CUtensorMap ta[kMaxGroups][kMaxSegs];
   CUtensorMap tb[kMaxGroups][kMaxSegs];
@@ -111,18 +123,39 @@ struct GemmArgs {
   int m_fastest;     // tile order: consecutive work items walk M first (B is the large operand) or N first
   int bn;            // tile width the plan was built for (128 or 256) = the kernel's BN
   int cluster_m;     // CTAs per cluster along M (1, 2 or 4): they share the N tile and receive B by TMA multicast
+  const GemmExtraDev* xdev;   // [nextra] in global memory
+  int nextra;
+  int x_item0[kMaxExtra + 1]; // work-item offsets of the extras, relative to the end of the main problem's items
+  int x_m[kMaxExtra], x_n[kMaxExtra], x_kb[kMaxExtra], x_tn[kMaxExtra];   // rows, cols, k-blocks per segment, N tiles
   long long* trace;  // diagnostics: [grid][64] clock64 stamps of the phases of each CTA (selftest "trace"), or nullptr
   CUtensorMap tout[kMaxGroups][2];   // output tiles (box 32 cols x 32 rows): [g][0] fp32 or bf16 hi plane, [g][1] lo plane
 };
 
 struct WorkItem {
-  int g, m0, n0, kb0, kb1;
+  int g;             // group of the main problem, or -1 - e for extra problem e
+  int m0, n0, kb0, kb1;
+  int M, N, kblocks; // of the problem this item belongs to
 };
 
 // Work items are per CLUSTER: `tiles_m` counts cluster rows (cluster_m M-tiles each); CTA `crank` takes M-tile
 // mt * cluster_m + crank of the item.  With cluster_m == 1 this is the plain per-CTA decode.
 __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int crank = 0) {
   WorkItem it;
+  const int main_work = a.tiles_m * a.tiles_n * a.ngroups * a.splitk;
+  if (w >= main_work) {                 // an extra problem: whole-K items, N tiles fastest
+    const int x = w - main_work;
+    int e = 0;
+    while (e + 1 < a.nextra && x >= a.x_item0[e + 1]) ++e;
+    const int l = x - a.x_item0[e];
+    it.g = -1 - e;
+    it.m0 = (l / a.x_tn[e]) * kBlockM;
+    it.n0 = (l % a.x_tn[e]) * a.bn;
+    it.kb0 = 0;
+    it.kb1 = a.nseg * a.x_kb[e];
+    it.M = a.x_m[e]; it.N = a.x_n[e]; it.kblocks = a.x_kb[e];
+    return it;
+  }
+  it.M = a.M; it.N = a.N; it.kblocks = a.kblocks;
   int nt, mt, t;
   if (a.m_fastest) {
     mt = w % a.tiles_m; t = w / a.tiles_m;
@@ -500,7 +533,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const TileOut& 
   }
 }
 
-static_assert(sizeof(GemmArgs) <= 4096, "kernel parameter space");
+static_assert(sizeof(GemmArgs) <= 4096, "kernel parameter space (kept under the classic 4 KiB)");
 
 // ---------------------------------------------------------------------------- the kernel
 template <bool A_MN, bool B_MN, int EPI, int BN>
@@ -537,7 +570,8 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_work = args.tiles_m * args.tiles_n * args.ngroups * args.splitk;
+  const int total_work = args.tiles_m * args.tiles_n * args.ngroups * args.splitk +
+                         (args.nextra > 0 ? args.x_item0[args.nextra] : 0);
   const int CM = args.cluster_m;
   const int crank = CM > 1 ? (int)ptx::cluster_ctarank() : 0;
   const int work0 = (int)blockIdx.x / CM, work_stride = (int)gridDim.x / CM;   // this cluster's first item / number of clusters
@@ -578,14 +612,14 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       for (int w = work0; w < total_work; w += work_stride) {
         const WorkItem it = decode_work(args, w, crank);
         for (int kb = it.kb0; kb < it.kb1; ++kb) {
-          const int seg = kb / args.kblocks;
-          const int k0 = (kb - seg * args.kblocks) * kBlockK;
+          const int seg = kb / it.kblocks;
+          const int k0 = (kb - seg * it.kblocks) * kBlockK;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           ptx::mbar_expect_tx(&full_bar[stage], Cfg::kBytes);
           uint8_t* sa = smem_a + stage * kStageBytesA;
           uint8_t* sb = smem_b + stage * Cfg::kBytesB;
-          const CUtensorMap* ta = &args.ta[it.g][seg];
-          const CUtensorMap* tb = &args.tb[it.g][seg];
+          const CUtensorMap* ta = it.g >= 0 ? &args.ta[it.g][seg] : &args.xdev[-1 - it.g].ta[seg];
+          const CUtensorMap* tb = it.g >= 0 ? &args.tb[it.g][seg] : &args.xdev[-1 - it.g].tb[seg];
           if constexpr (!A_MN) {
             ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);              // box {64 k, 128 m}
           } else {
@@ -679,10 +713,10 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     }
     for (int w = work0; w < total_work; w += work_stride, ++iter) {
       const WorkItem it = decode_work(args, w, crank);
-      const EpiArgs& e = args.epi[it.g];
+      const EpiArgs& e = it.g >= 0 ? args.epi[it.g] : args.xdev[-1 - it.g].epi;
       const uint32_t acc = iter % kAcc, acc_phase = (iter / kAcc) & 1;
       const int row = it.m0 + q * 32 + lane;
-      const int ncols = min(BN, args.N - it.n0);
+      const int ncols = min(BN, it.N - it.n0);
       const int nchunks = (ncols + 31) >> 5;
       if constexpr (EPI == EPI_BCE) {
 #pragma unroll
@@ -703,17 +737,17 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         uint32_t xwk = 0u;
         if constexpr (EPI == EPI_BCE) xwk = xw[k];
         if constexpr (EPI == EPI_SCATTER_F32) {
-          scatter_chunk(e, r, row, it.n0 + c * 32, args.M, args.N,
+          scatter_chunk(e, r, row, it.n0 + c * 32, it.M, it.N,
                         smem + kStages * kStageBytes + 256 + (warp - 2) * kScatterStageBytes, lane);
         } else {
           TileOut t;
-          t.hi = &args.tout[it.g][0];
-          t.lo = &args.tout[it.g][1];
+          t.hi = it.g >= 0 ? &args.tout[it.g][0] : &args.xdev[-1 - it.g].tout[0];
+          t.lo = it.g >= 0 ? &args.tout[it.g][1] : &args.xdev[-1 - it.g].tout[1];
           t.slot = smem + kTileStageOffset + (warp - 2) * 2048;
           t.lane = lane;
           t.row0 = it.m0 + q * 32;
           t.reduce = e.atomic;
-          epilogue_chunk<EPI, true>(e, t, r, row, it.n0 + c * 32, args.M, args.N, loss_acc, xwk);
+          epilogue_chunk<EPI, true>(e, t, r, row, it.n0 + c * 32, it.M, it.N, loss_acc, xwk);
         }
       };
       constexpr int kBatch = epi_warps(EPI) == 16 ? 2 : 1;   // 8-warp epilogues own 4 chunks: one at a time (registers)

@@ -144,6 +144,67 @@ static void test_wgrad_groups(int M, int N, int K, int sms) {
   report(name, me, 2e-3 * sqrt((double)K) * 0.1 + 1e-4);
 }
 
+// A two-group wgrad with problems of other shapes appended to the same launch (GemmProblem::extra)
+static void test_wgrad_extras(int sms) {
+  const int M = 700, N = 500, K = 512;
+  const int xs[4][3] = {{501, 500, 256}, {201, 400, 128}, {130, 70, 512}, {64, 256, 64}};   // {M, N, K}
+  HostMat a[2], b[2], xa[4], xb[4];
+  float* dout[2];
+  float* xout[4];
+  const long long ldo = 512;
+  GemmProblem p;
+  p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K; p.block_n = g_bn;
+  for (int g = 0; g < 2; ++g) {
+    a[g].init(K, M, (M + 63) / 64 * 64, 1.f, true);
+    b[g].init(K, N, (N + 63) / 64 * 64, 1.f);
+    CK(cudaMalloc(&dout[g], sizeof(float) * M * ldo));
+    CK(cudaMemset(dout[g], 0xFF, sizeof(float) * M * ldo));
+    p.a[g][0] = a[g].mat(); p.b[g][0] = b[g].mat();
+    EpiArgs e = {};
+    e.out = dout[g]; e.ld_out = ldo; e.alpha = 1.f;
+    p.e[g] = e;
+  }
+  for (int i = 0; i < 4; ++i) {
+    const int m = xs[i][0], n = xs[i][1], k = xs[i][2];
+    xa[i].init(k, m, (m + 63) / 64 * 64, 1.f, i % 2 == 0);
+    xb[i].init(k, n, (n + 63) / 64 * 64, 1.f);
+    CK(cudaMalloc(&xout[i], sizeof(float) * m * ldo));
+    CK(cudaMemset(xout[i], 0xFF, sizeof(float) * m * ldo));
+    GemmExtra x;
+    x.a[0] = xa[i].mat(); x.b[0] = xb[i].mat(); x.M = m; x.N = n; x.K = k;
+    EpiArgs e = {};
+    e.out = xout[i]; e.ld_out = ldo; e.alpha = 0.5f + i;
+    x.e = e;
+    p.extra.push_back(x);
+  }
+  GemmPlan pl;
+  std::string err = gemm_plan(p, sms, &pl);
+  if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+  if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
+  CK(cudaDeviceSynchronize());
+  double me = 0;
+  for (int g = 0; g < 2; ++g) {
+    std::vector<float> h((size_t)M * ldo);
+    CK(cudaMemcpy(h.data(), dout[g], sizeof(float) * M * ldo, cudaMemcpyDeviceToHost));
+    std::vector<double> D;
+    host_ref(GEMM_WGRAD, M, N, K, 1, &a[g], &b[g], D);
+    for (int m = 0; m < M; ++m)
+      for (int n = 0; n < N; ++n) me = fmax(me, fabs(h[(size_t)m * ldo + n] - D[(size_t)m * N + n]));
+  }
+  for (int i = 0; i < 4; ++i) {
+    const int m = xs[i][0], n = xs[i][1], k = xs[i][2];
+    std::vector<float> h((size_t)m * ldo);
+    CK(cudaMemcpy(h.data(), xout[i], sizeof(float) * m * ldo, cudaMemcpyDeviceToHost));
+    std::vector<double> D;
+    host_ref(GEMM_WGRAD, m, n, k, 1, &xa[i], &xb[i], D);
+    for (int r = 0; r < m; ++r)
+      for (int c = 0; c < n; ++c) me = fmax(me, fabs(h[(size_t)r * ldo + c] - (0.5 + i) * D[(size_t)r * n + c]));
+  }
+  char name[128];
+  snprintf(name, sizeof name, "wgrad 2 groups + 4 appended problems, bn=%d items=%lld", pl.args.bn, pl.items);
+  report(name, me, 2e-3 * sqrt((double)K) * 0.1 * 4 + 1e-4);
+}
+
 static double sigm(double x) { return 1.0 / (1.0 + exp(-x)); }
 
 // ACT (fwd, optional two-pass), DACT (dgrad), BCE (fwd)
@@ -349,6 +410,8 @@ int main(int argc, char** argv) {
   test_store(GEMM_WGRAD, 501, 40, 1024, 2, 0, sms);
   test_store(GEMM_FWD, 1000, 4, 501, 1, 0, sms);
   test_wgrad_groups(1100, 500, 512, sms);
+  g_bn = 256; test_wgrad_extras(sms); g_bn = 0;      // the engine's case: 256-wide tiles (first-layer wgrad fills the grid)
+  test_wgrad_extras(sms);
   // fused epilogues
   test_fused(EPI_ACT, 300, 500, 501, 1, 1, sms);
   test_fused(EPI_ACT, 300, 500, 501, 1, 0, sms);
@@ -378,6 +441,7 @@ int main(int argc, char** argv) {
   test_store(GEMM_WGRAD, 501, 500, 700, 1, 1, sms);
   test_store(GEMM_WGRAD, 501, 140, 2048, 2, 0, sms);
   test_wgrad_groups(1100, 500, 512, sms);
+  test_wgrad_extras(sms);
   test_fused(EPI_ACT, 300, 500, 501, 1, 1, sms);
   test_fused(EPI_ACT, 3000, 500, 501, 1, 0, sms);
   test_fused(EPI_ACT, 300, 500, 2000, 4, 1, sms);
