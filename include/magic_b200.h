@@ -102,6 +102,21 @@ int magic_load_planar_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* 
  * 8c/utils.py:329-340: angle ~ U[0, 2 pi), nearest neighbour, zero fill) is produced on the device with the
  * generator's Q14 integer rotation for (seed, step, rank); magic_export_rotation returns the (cos, sin) used. */
 int magic_load_pairs_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* d_key, uint64_t seed, uint64_t step);
+/* The same pairs bit-packed: [B, words_per_row] 32-bit words per plane, pixel p = bit (p & 31) of word p >> 5
+ * (numpy.packbits(..., bitorder='little') viewed as little-endian uint32): 10 KB per pair instead of the 480 KB of
+ * the float32 array the queue hands to feed_dict (8c/main.py:44, 8c/vae.py:395).  Pixels are {0,1} after
+ * normalisation (8c/overlap_input.py:185-195), so nothing is lost. */
+int magic_load_pairs_bits(magic_handle* h, const uint32_t* d_lock_bits, const uint32_t* d_key_bits, int32_t words_per_row,
+                          uint64_t seed, uint64_t step);
+/* Host-buffer form for the training loop (the QueueRunner's role, 8c/overlap_input.py:76-124, 8c/main.py:40-45):
+ * copies the packed planes and the labels [B] (or NULL) from HOST memory and unpacks them on the engine's input
+ * stream, asynchronously -- the batch of step n+1 crosses PCIe while step n runs.  activate != 0 makes the batch the
+ * loaded one (like every other loader); activate == 0 leaves it staged in the second input buffer until
+ * magic_swap_batch.  The host buffers must stay untouched until the next call that synchronises (magic_sync, a
+ * *_host call) or until a step that consumed the batch has been waited for; pinned memory keeps the copy
+ * asynchronous.  With labels given, magic_step(d_labels = NULL) uses them. */
+int magic_feed_pairs_bits_host(magic_handle* h, const uint32_t* h_lock_bits, const uint32_t* h_key_bits, const float* h_labels,
+                               int32_t words_per_row, uint64_t seed, uint64_t step, int32_t activate);
 /* Replaces overlap_input.inputs() (8c/overlap_input.py:76-124): synthesises B shape pairs + rotated lock +
  * max-overlap labels on the device for (seed, step, rank).  Labels go to an internal buffer used when
  * magic_step is given d_labels = NULL. */

@@ -148,6 +148,16 @@ int magic_load_pairs_u8(magic_handle* h, const uint8_t* d_lock, const uint8_t* d
   CHECK_HANDLE(h);
   return done(h->eng.load_pairs_u8(d_lock, d_key, seed, step));
 }
+int magic_load_pairs_bits(magic_handle* h, const uint32_t* d_lock_bits, const uint32_t* d_key_bits, int32_t words_per_row,
+                          uint64_t seed, uint64_t step) {
+  CHECK_HANDLE(h);
+  return done(h->eng.load_pairs_bits(d_lock_bits, d_key_bits, words_per_row, seed, step));
+}
+int magic_feed_pairs_bits_host(magic_handle* h, const uint32_t* h_lock_bits, const uint32_t* h_key_bits, const float* h_labels,
+                               int32_t words_per_row, uint64_t seed, uint64_t step, int32_t activate) {
+  CHECK_HANDLE(h);
+  return done(h->eng.feed_pairs_bits_host(h_lock_bits, h_key_bits, h_labels, words_per_row, seed, step, activate != 0));
+}
 int magic_generate_batch(magic_handle* h, uint64_t seed, uint64_t step) {
   CHECK_HANDLE(h);
   return done(h->eng.generate(seed, step));

@@ -117,7 +117,7 @@ Engine::~Engine() {
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
                   statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
-                  in_[0].xbits, in_[1].xbits, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_};
+                  in_[0].xbits, in_[1].xbits, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
@@ -612,6 +612,61 @@ std::string Engine::load_pairs_u8(const uint8_t* d_lock, const uint8_t* d_key, u
   b.has_rot = true;
   b.filled = true;
   cur_ ^= 1;
+  return "";
+}
+std::string Engine::load_pairs_bits(const uint32_t* d_lock, const uint32_t* d_key, int wpr, uint64_t seed, uint64_t step_idx) {
+  if (!d_lock || !d_key) return "load_pairs_bits: null input";
+  const int side = (int)llround(sqrt((double)D));
+  if (side * side != D || side > 256) return "load_pairs_bits: D must be a square canvas with side <= 256";
+  if (wpr < (D + 31) / 32) return "load_pairs_bits: words_per_row is smaller than ceil(D / 32)";
+  InBuf& b = in_[cur_ ^ 1];
+  wait_ready(b);
+  pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, b.X.hi, b.X.ld, b.xbits,
+             xb_ld_, b.rot, stream);
+  MAGIC_CUDA(cudaGetLastError());
+  mark_consumed(b);
+  b.has_labels = false;
+  b.has_rot = true;
+  b.filled = true;
+  cur_ ^= 1;
+  return "";
+}
+// Host-buffer variant for a training loop: copies and expands on the input stream (the generator's), so the batch
+// of step n+1 crosses PCIe and is unpacked while step n runs; with activate = 0 the batch stays staged in the
+// not-loaded buffer until swap_batch makes it the loaded one.
+std::string Engine::feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t* h_key, const float* h_labels, int wpr,
+                                         uint64_t seed, uint64_t step_idx, bool activate) {
+  if (!h_lock || !h_key) return "feed_pairs_bits_host: null input";
+  const int side = (int)llround(sqrt((double)D));
+  if (side * side != D || side > 256) return "feed_pairs_bits_host: D must be a square canvas with side <= 256";
+  if (wpr < (D + 31) / 32) return "feed_pairs_bits_host: words_per_row is smaller than ceil(D / 32)";
+  const size_t plane = sizeof(uint32_t) * (size_t)B * wpr;
+  if (bits_stage_bytes_ < 2 * plane) {
+    MAGIC_CUDA(cudaStreamSynchronize(gen_stream_));
+    if (bits_stage_) cudaFree(bits_stage_);
+    bits_stage_ = nullptr; bits_stage_bytes_ = 0;
+    MAGIC_CUDA(cudaMalloc((void**)&bits_stage_, 2 * plane));
+    bits_stage_bytes_ = 2 * plane;
+  }
+  InBuf& b = in_[cur_ ^ 1];
+  if (b.ready_pending) { MAGIC_CUDA(cudaStreamWaitEvent(gen_stream_, b.ready, 0)); b.ready_pending = false; }
+  if (b.consumed_pending) { MAGIC_CUDA(cudaStreamWaitEvent(gen_stream_, b.consumed, 0)); b.consumed_pending = false; }
+  uint32_t* d_lock = bits_stage_;
+  uint32_t* d_key = bits_stage_ + (size_t)B * wpr;
+  MAGIC_CUDA(cudaMemcpyAsync(d_lock, h_lock, plane, cudaMemcpyHostToDevice, gen_stream_));
+  MAGIC_CUDA(cudaMemcpyAsync(d_key, h_key, plane, cudaMemcpyHostToDevice, gen_stream_));
+  if (h_labels) MAGIC_CUDA(cudaMemcpyAsync(b.labels, h_labels, sizeof(float) * B, cudaMemcpyHostToDevice, gen_stream_));
+  prof_begin("input.pairs_bits", 0, gen_stream_);
+  pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, b.X.hi, b.X.ld, b.xbits,
+             xb_ld_, b.rot, gen_stream_);
+  prof_end(gen_stream_);
+  MAGIC_CUDA(cudaGetLastError());
+  MAGIC_CUDA(cudaEventRecord(b.ready, gen_stream_));
+  b.ready_pending = true;
+  b.has_labels = h_labels != nullptr;
+  b.has_rot = true;
+  b.filled = true;
+  if (activate) cur_ ^= 1;
   return "";
 }
 std::string Engine::generate(uint64_t seed, uint64_t step_idx) {

@@ -51,6 +51,9 @@ class Engine {
   std::string export_rotation(int32_t* d_cs_sn);
   std::string swap_batch();
   std::string load_pairs_u8(const uint8_t* d_lock, const uint8_t* d_key, uint64_t seed, uint64_t step_idx);
+  std::string load_pairs_bits(const uint32_t* d_lock, const uint32_t* d_key, int wpr, uint64_t seed, uint64_t step_idx);
+  std::string feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t* h_key, const float* h_labels, int wpr, uint64_t seed,
+                                   uint64_t step_idx, bool activate);
   std::string step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply);
   std::string load_interleaved_u8(const uint8_t* d_x);
   std::string partial_fit_host(const void* h_x, bool x_is_u8, const float* h_labels, const float* h_eps3,
@@ -144,6 +147,7 @@ class Engine {
   float *g_row_ = nullptr, *dist_ = nullptr, *losses_dev_ = nullptr;
   void* stage_x_ = nullptr; size_t stage_x_bytes_ = 0;                            // partial_fit_host staging
   float *stage_labels_ = nullptr, *stage_eps_ = nullptr;
+  uint32_t* bits_stage_ = nullptr; size_t bits_stage_bytes_ = 0;                     // feed_pairs_bits_host staging
   const float* labels_ext_ = nullptr;
   bool have_labels_ext_ = false;
 

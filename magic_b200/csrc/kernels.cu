@@ -834,6 +834,64 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
   pairs_u8_kernel<<<dim3((unsigned)((ld + 1023) / 1024), B), 256, 0, s>>>(lock, key, B, side, seed, step, planes, ld, rot_cs_sn);
 }
 
+// The same pipeline fed with bit-packed planes: lock / key are [B, wpr] 32-bit words, pixel p = bit (p & 31) of word
+// p >> 5 (the layout of xbits, numpy packbits(bitorder='little')): 10 KB per pair instead of 80 KB as uint8 or
+// 480 KB as the float32 array the reference feeds.  One CTA per (pair, 1024-column chunk), eight columns per thread
+// (one 16-byte store per plane); the lock's bitmap sits in shared memory for the rotated samples.  The first chunk's
+// CTA also copies the lock words into xbits (the BCE epilogue's packed targets).
+constexpr int kPairsBitsMaxWords = 2048;      // side <= 256
+__global__ void __launch_bounds__(128) pairs_bits_kernel(const uint32_t* __restrict__ lock, const uint32_t* __restrict__ key,
+                                                         int wpr, int B, int side, uint64_t seed, uint64_t step,
+                                                         __nv_bfloat16* planes, long long ld, uint32_t* xbits, int xb_ld,
+                                                         int* rot_cs_sn) {
+  __shared__ uint32_t bm[kPairsBitsMaxWords];
+  __shared__ int q14[2];
+  const int i = blockIdx.y, D = side * side;
+  const uint32_t* L = lock + (long long)i * wpr;
+  const uint32_t* K = key + (long long)i * wpr;
+  if (threadIdx.x == 0) {
+    float sn, cs;
+    sincospif(2.f * u01((uint32_t)rng_key(seed, step, 13, i)), &sn, &cs);   // same draw as generate_pairs_kernel
+    q14[0] = __float2int_rn(cs * 16384.f);
+    q14[1] = __float2int_rn(sn * 16384.f);
+    if (rot_cs_sn && blockIdx.x == 0) { rot_cs_sn[2 * i] = q14[0]; rot_cs_sn[2 * i + 1] = q14[1]; }
+  }
+  const int nwords = (D + 31) >> 5;
+  const uint32_t tail = (D & 31) ? ((1u << (D & 31)) - 1u) : 0xffffffffu;     // bits past D in the last word are ignored
+  for (int w = threadIdx.x; w < nwords; w += blockDim.x) {
+    const uint32_t v = __ldg(L + w) & (w == nwords - 1 ? tail : 0xffffffffu);
+    bm[w] = v;
+    if (blockIdx.x == 0) xbits[(long long)i * xb_ld + w] = v;
+  }
+  if (blockIdx.x == 0)
+    for (int w = nwords + threadIdx.x; w < xb_ld; w += blockDim.x) xbits[(long long)i * xb_ld + w] = 0u;
+  __syncthreads();
+  const int cs = q14[0], sn = q14[1];
+  const int c0 = blockIdx.x * 1024 + threadIdx.x * 8;
+  if (c0 >= ld) return;
+  uint32_t bl = 0u, bk = 0u, br = 0u;
+  if (c0 < D) {
+    const int w = c0 >> 5, sh = c0 & 31;
+    bl = (bm[w] >> sh) & 255u;
+    bk = ((__ldg(K + w) & (w == nwords - 1 ? tail : 0xffffffffu)) >> sh) & 255u;
+    int y = c0 / side, x = c0 - y * side;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (c0 + j < D) br |= bit_at(bm, rotated_index(x, y, side, cs, sn)) << j;
+      if (++x == side) { x = 0; ++y; }
+    }
+  }
+  if (D >= c0 && D < c0 + 8) { const uint32_t one = 1u << (D - c0); bl |= one; bk |= one; br |= one; }   // bias column
+  *reinterpret_cast<uint4*>(planes + (long long)i * ld + c0) = expand_byte(br);
+  *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + c0) = expand_byte(bl);
+  *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + c0) = expand_byte(bk);
+}
+void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
+                __nv_bfloat16* planes, long long ld, uint32_t* xbits, int xb_ld, int* rot_cs_sn, cudaStream_t s) {
+  pairs_bits_kernel<<<dim3((unsigned)((ld + 1023) / 1024), B), 128, 0, s>>>(lock, key, wpr, B, side, seed, step, planes, ld, xbits,
+                                                                             xb_ld, rot_cs_sn);
+}
+
 __global__ void __launch_bounds__(256) pack_lock_bits_kernel(const __nv_bfloat16* __restrict__ planes, long long ld, int B,
                                                              int D, uint32_t* xbits, int xb_ld) {
   const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -870,6 +928,7 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(deinterleave_u8_kernel);
   MAGIC_MAX_CARVEOUT(planar_u8_kernel);
   MAGIC_MAX_CARVEOUT(pairs_u8_kernel);
+  MAGIC_MAX_CARVEOUT(pairs_bits_kernel);
   MAGIC_MAX_CARVEOUT(planes_to_interleaved_kernel);
   MAGIC_MAX_CARVEOUT(generate_pairs_kernel);
   MAGIC_MAX_CARVEOUT(pack_lock_bits_kernel);

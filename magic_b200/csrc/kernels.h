@@ -99,6 +99,9 @@ void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16
 // sigmoid-BCE epilogue reads (8c/vae.py:260-263)
 void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t seed, uint64_t step,
               __nv_bfloat16* planes, long long ld, int* rot_cs_sn, cudaStream_t s);
+// bit-packed pairs: pixel p = bit (p & 31) of word p >> 5 of the pair's row (wpr words per row); also fills xbits
+void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
+                __nv_bfloat16* planes, long long ld, uint32_t* xbits, int xb_ld, int* rot_cs_sn, cudaStream_t s);
 void pack_lock_bits(const __nv_bfloat16* planes, long long ld, int B, int D, uint32_t* xbits, int xb_ld, cudaStream_t s);
 
 void zero_fill(void* ptr, size_t bytes, cudaStream_t s);   // kernel-based memset(0): ptr 16-byte aligned, bytes % 4 == 0

@@ -242,6 +242,43 @@ class Engine:
                                            C.c_uint64(seed), C.c_uint64(step)))
         self._keep = ts
 
+    @property
+    def words_per_row(self) -> int:
+        """32-bit words of one bit-packed plane row (pixel p = bit p & 31 of word p >> 5)."""
+        return (self.D + 31) // 32
+
+    def load_pairs_bits(self, lock_bits: torch.Tensor, key_bits: torch.Tensor, seed: int, step: int) -> None:
+        """Bit-packed dataset pairs already on the device (int32/uint32 [B, words_per_row]) -> operand planes."""
+        ts = [x.to(device=self.device).contiguous() for x in (lock_bits, key_bits)]
+        for x in ts:
+            if x.dim() != 2 or x.shape[0] != self.B or x.shape[1] < self.words_per_row or x.element_size() != 4:
+                raise ValueError("packed planes must be [B, >= %d] 32-bit words" % self.words_per_row)
+        check(self.lib.magic_load_pairs_bits(self._h, C.c_void_p(ts[0].data_ptr()), C.c_void_p(ts[1].data_ptr()),
+                                             C.c_int32(ts[0].shape[1]), C.c_uint64(seed), C.c_uint64(step)))
+        self._keep = ts
+
+    def feed_pairs_bits(self, lock_bits, key_bits, labels, seed: int, step: int, activate: bool = True) -> None:
+        """Bit-packed pairs in HOST memory (numpy or CPU torch, 32-bit words [B, words_per_row]; pinned keeps the
+        copy asynchronous) -> operand planes, on the engine's input stream.  activate=False leaves the batch staged
+        until swap_batch().  The arrays must not change until the step that consumes them has been waited for."""
+        arrs = []
+        for x in (lock_bits, key_bits):
+            x = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x))
+            if x.is_cuda or x.dim() != 2 or x.shape[0] != self.B or x.shape[1] < self.words_per_row \
+                    or x.element_size() != 4 or not x.is_contiguous():
+                raise ValueError("packed planes must be contiguous host arrays [B, >= %d] of 32-bit words" % self.words_per_row)
+            arrs.append(x)
+        lab = None
+        if labels is not None:
+            lab = labels if isinstance(labels, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(labels, dtype=np.float32))
+            if lab.is_cuda or lab.dtype != torch.float32 or tuple(lab.shape) != (self.B,) or not lab.is_contiguous():
+                raise ValueError("labels must be a contiguous host float32 [B]")
+        check(self.lib.magic_feed_pairs_bits_host(
+            self._h, C.c_void_p(arrs[0].data_ptr()), C.c_void_p(arrs[1].data_ptr()),
+            C.c_void_p(lab.data_ptr()) if lab is not None else None, C.c_int32(arrs[0].shape[1]),
+            C.c_uint64(seed), C.c_uint64(step), C.c_int32(1 if activate else 0)))
+        self._keep_feed = (getattr(self, "_keep_feed", ()) + ((arrs, lab),))[-2:]     # the two batches in flight
+
     def generate_batch(self, seed: int, step: int) -> None:
         check(self.lib.magic_generate_batch(self._h, C.c_uint64(seed), C.c_uint64(step)))
 

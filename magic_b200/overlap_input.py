@@ -14,7 +14,10 @@ Host-side mirror of the reference's input pipeline for 8c-11a (8c/overlap_input.
                        epoch; the last ragged batch of an epoch is dropped (the graph has a static batch size,
                        8c/vae.py:367).
   * the random rotation of the lock (8c/overlap_input.py:181-182, 8c/utils.py:329-340) happens on the device:
-                       `magic_load_pairs_u8` (include/magic_b200.h).
+                       `magic_load_pairs_u8` / `magic_load_pairs_bits` (include/magic_b200.h).
+  * `device_batches`<- the QueueRunner threads + the two `.eval()` dequeues of the training loop (8c/main.py:40-45):
+                       the dataset is kept bit-packed (10 KB per pair), batch n+1 is gathered into pinned memory and
+                       sent with `magic_feed_pairs_bits_host` while step n runs.
 
 Nothing here touches TensorFlow queues, threads or summaries (out of scope)."""
 from __future__ import annotations
@@ -123,6 +126,23 @@ def load_overlap_areas(path: Union[str, os.PathLike]) -> np.ndarray:
         return np.asarray(pickle.load(f, encoding="latin1"), dtype=np.float32)
 
 
+def pack_planes(planes: np.ndarray) -> np.ndarray:
+    """uint8/bool [N, D] (non-zero = set) -> uint32 [N, ceil(D/32)], pixel p = bit (p & 31) of word p >> 5."""
+    planes = np.asarray(planes)
+    n, d = planes.shape
+    by = np.packbits(planes != 0, axis=1, bitorder="little")
+    wpr = (d + 31) // 32
+    if by.shape[1] != 4 * wpr:
+        by = np.concatenate([by, np.zeros((n, 4 * wpr - by.shape[1]), dtype=np.uint8)], axis=1)
+    return np.ascontiguousarray(by).view("<u4")
+
+
+def unpack_planes(words: np.ndarray, d: int) -> np.ndarray:
+    """Inverse of pack_planes: uint32 [N, W] -> uint8 {0,1} [N, d]."""
+    by = np.ascontiguousarray(np.asarray(words).astype("<u4")).view(np.uint8)
+    return np.unpackbits(by, axis=1, bitorder="little")[:, :d]
+
+
 class OverlapDataset:
     """Lock/key planes of the first `num_examples` pairs, uint8 {0,1}, [N, D] each, and their labels [N]."""
 
@@ -154,13 +174,14 @@ class OverlapDataset:
                 dst[i] = (img.reshape(-1) > 0)
         self.labels = areas[:n].copy()
         self.image_size = image_size
+        self.lock_bits = pack_planes(self.lock)
+        self.key_bits = pack_planes(self.key)
 
     def __len__(self) -> int:
         return len(self.labels)
 
-    def batches(self, batch_size: int, epochs: int = 1, shuffle: bool = True,
-                seed: int = 0) -> Iterator[Tuple[np.ndarray, np.ndarray, np.ndarray]]:
-        """Yields (lock[B, D] uint8, key[B, D] uint8, labels[B] float32), images and labels drawn JOINTLY."""
+    def index_batches(self, batch_size: int, epochs: int = 1, shuffle: bool = True, seed: int = 0) -> Iterator[np.ndarray]:
+        """The example indices of every batch: a fresh permutation per epoch, the ragged tail dropped."""
         rng = np.random.default_rng(seed)
         n = len(self)
         if batch_size > n:
@@ -168,20 +189,65 @@ class OverlapDataset:
         for _ in range(epochs):
             order = rng.permutation(n) if shuffle else np.arange(n)
             for s in range(0, n - batch_size + 1, batch_size):
-                idx = order[s:s + batch_size]
-                yield self.lock[idx], self.key[idx], self.labels[idx]
+                yield order[s:s + batch_size]
+
+    def batches(self, batch_size: int, epochs: int = 1, shuffle: bool = True,
+                seed: int = 0) -> Iterator[Tuple[np.ndarray, np.ndarray, np.ndarray]]:
+        """Yields (lock[B, D] uint8, key[B, D] uint8, labels[B] float32), images and labels drawn JOINTLY."""
+        for idx in self.index_batches(batch_size, epochs, shuffle, seed):
+            yield self.lock[idx], self.key[idx], self.labels[idx]
 
 
-def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool = True, seed: int = 0):
+def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool = True, seed: int = 0,
+                   packed: bool = True):
     """`overlap_input.inputs(normalize=True, reshape=True, rotation=True)` for the B200 backend: yields handles
     (magic_b200/tango.py: ResidentBatch) whose planes are already in HBM; `batch.labels` are the matching overlap
-    areas, so `vae.partial_fit(batch, overlap_areas=batch.labels)` trains on a consistent (images, labels) pair."""
+    areas, so `vae.partial_fit(batch, overlap_areas=batch.labels)` trains on a consistent (images, labels) pair.
+
+    packed=True (default): batches travel bit-packed and one step ahead -- while the caller trains on batch n,
+    batch n+1 is already crossing PCIe / being unpacked on the engine's input stream (`magic_feed_pairs_bits_host`
+    with activate=0, then `magic_swap_batch`).  packed=False sends uint8 planes with `magic_load_pairs_u8`."""
     import torch
     from .tango import ResidentBatch
     eng = vae.engine
-    step = 0
-    for lock, key, labels in dataset.batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed):
-        eng.load_pairs_u8(torch.from_numpy(np.ascontiguousarray(lock)), torch.from_numpy(np.ascontiguousarray(key)),
-                          seed, step)
-        step += 1
-        yield ResidentBatch(vae, np.ascontiguousarray(labels, dtype=np.float32))
+    if not packed:
+        step = 0
+        for lock, key, labels in dataset.batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed):
+            eng.load_pairs_u8(torch.from_numpy(np.ascontiguousarray(lock)), torch.from_numpy(np.ascontiguousarray(key)),
+                              seed, step)
+            step += 1
+            yield ResidentBatch(vae, np.ascontiguousarray(labels, dtype=np.float32))
+        return
+
+    wpr = dataset.lock_bits.shape[1]
+    src = [torch.from_numpy(dataset.lock_bits.view(np.int32)), torch.from_numpy(dataset.key_bits.view(np.int32)),
+           torch.from_numpy(dataset.labels)]
+    pin = torch.cuda.is_available()
+    ring = [(torch.empty((eng.B, wpr), dtype=torch.int32, pin_memory=pin), torch.empty((eng.B, wpr), dtype=torch.int32, pin_memory=pin),
+             torch.empty((eng.B,), dtype=torch.float32, pin_memory=pin)) for _ in range(2)]
+
+    def send(n, idx, activate):
+        slot = ring[n % 2]                                    # its previous batch (n - 2) has been consumed by a step
+        it = torch.from_numpy(np.ascontiguousarray(idx, dtype=np.int64))
+        for dst, s_ in zip(slot, src):
+            torch.index_select(s_, 0, it, out=dst)
+        eng.feed_pairs_bits(slot[0], slot[1], slot[2], seed, n, activate=activate)
+        return slot[2].numpy().copy()
+
+    order = dataset.index_batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed)
+    idx = next(order, None)
+    if idx is None:
+        return
+    labels = send(0, idx, True)
+    n = 0
+    while True:
+        idx = next(order, None)
+        staged = send(n + 1, idx, False) if idx is not None else None
+        batch = ResidentBatch(vae, labels)
+        yield batch
+        if staged is None:
+            return
+        if vae._loaded_key is not batch._token:
+            raise RuntimeError("another load replaced the engine's input buffers while iterating the dataset")
+        eng.swap_batch()
+        labels, n = staged, n + 1

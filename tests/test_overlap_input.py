@@ -119,6 +119,22 @@ def test_dataset_and_joint_batches():
         oi.OverlapDataset(PNG_DIR, areas, num_examples=5)
 
 
+def test_bit_packing_layout_and_round_trip():
+    rng = np.random.default_rng(11)
+    for d in (40000, 45, 64, 1):
+        x = (rng.random((3, d)) < 0.4).astype(np.uint8)
+        w = oi.pack_planes(x * 255)                                  # any non-zero byte is a set pixel
+        assert w.dtype == np.dtype("<u4") and w.shape == (3, (d + 31) // 32)
+        assert np.array_equal(oi.unpack_planes(w, d), x)
+        for p in rng.integers(0, d, size=8):
+            assert ((int(w[1, p >> 5]) >> (int(p) & 31)) & 1) == x[1, p]      # pixel p = bit p & 31 of word p >> 5
+    areas = np.load(os.path.join(HERE, "golden", "overlap_areas.npy"))
+    ds = oi.OverlapDataset(PNG_DIR, areas, num_examples=4)
+    assert ds.lock_bits.shape == (4, 1250) and np.array_equal(oi.unpack_planes(ds.key_bits, 40000), ds.key)
+    got = [idx.copy() for idx in ds.index_batches(2, epochs=2, shuffle=True, seed=3)]
+    assert len(got) == 4 and sorted(np.concatenate(got[:2])) == [0, 1, 2, 3] == sorted(np.concatenate(got[2:]))
+
+
 # --------------------------------------------------------------------------- GPU tests
 @pytest.mark.gpu
 def test_dataset_pairs_on_device_and_training_step():
@@ -158,4 +174,71 @@ def test_dataset_pairs_on_device_and_training_step():
         vae.partial_fit(batch, overlap_areas=batch.labels)                            # replaced by the later load
     out2 = vae.partial_fit(nxt, overlap_areas=nxt.labels)
     assert np.isfinite(out2[0])
+    torch.cuda.synchronize()
+
+
+@pytest.mark.gpu
+def test_packed_feed_equals_the_uint8_loader_and_pipelines_one_batch_ahead():
+    import torch
+    from magic_b200.tango import TangoEncoder
+
+    class FLAGS:
+        IMAGE_SIZE, NUM_LAYERS, BATCH_SIZE = 200, 3, 2
+        NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN = 4
+        BACKEND, PRECISION = "b200", "bf16"
+
+    class Model(TangoEncoder):
+        encoder_neurons, decoder_neurons, latent_dimensions = (64, 64), (64, 64), 8
+
+    areas = np.load(os.path.join(HERE, "golden", "overlap_areas.npy"))
+    ds = oi.OverlapDataset(PNG_DIR, areas, num_examples=4)
+    vae = Model(flags=FLAGS, verbose=False)
+    eng = vae.engine
+
+    def loaded():
+        X, y = eng.export_batch()
+        return X.cpu().numpy(), eng.export_rotation().cpu().numpy(), y.cpu().numpy()
+
+    # 1. the three loaders agree bit for bit: uint8 planes, packed words on the device, packed words from the host
+    idx = np.array([2, 0])
+    eng.load_pairs_u8(torch.from_numpy(ds.lock[idx]), torch.from_numpy(ds.key[idx]), 5, 9)
+    X8, R8, _ = loaded()
+    eng.load_pairs_bits(torch.from_numpy(ds.lock_bits[idx].view(np.int32)), torch.from_numpy(ds.key_bits[idx].view(np.int32)), 5, 9)
+    Xd, Rd, _ = loaded()
+    eng.feed_pairs_bits(ds.lock_bits[idx], ds.key_bits[idx], ds.labels[idx], 5, 9)
+    Xh, Rh, yh = loaded()
+    assert np.array_equal(X8, Xd) and np.array_equal(X8, Xh) and np.array_equal(R8, Rd) and np.array_equal(R8, Rh)
+    assert np.array_equal(yh, ds.labels[idx]) and X8.sum() > 0
+    out_a = vae.engine.step(labels=ds.labels[idx])[0].cpu().numpy()                # explicit labels
+    eng.feed_pairs_bits(ds.lock_bits[idx], ds.key_bits[idx], ds.labels[idx], 5, 9)
+    # 2. a staged batch does not disturb the loaded one until swap_batch
+    other = np.array([1, 3])
+    eng.feed_pairs_bits(ds.lock_bits[other], ds.key_bits[other], ds.labels[other], 5, 10, activate=False)
+    assert np.array_equal(loaded()[0], X8)
+    eng.swap_batch()
+    Xo, _, yo = loaded()
+    assert np.array_equal(yo, ds.labels[other]) and not np.array_equal(Xo, X8)
+    assert np.array_equal(Xo.reshape(2, 40000, 3)[:, :, 0].astype(np.uint8), ds.lock[other])
+    assert np.isfinite(out_a).all()
+    # 3. the iterator: 2 epochs x 2 batches, each batch pairs images with their own labels, one batch staged ahead
+    seen = []
+    for batch in oi.device_batches(vae, ds, epochs=2, shuffle=True, seed=4):
+        X, _, y = loaded()
+        assert np.array_equal(y, batch.labels)
+        lock = X.reshape(2, 40000, 3)[:, :, 0].astype(np.uint8)
+        for r in range(2):
+            i = int(np.flatnonzero((ds.lock == lock[r]).all(1))[0])
+            assert ds.labels[i] == batch.labels[r]
+            assert np.array_equal(X.reshape(2, 40000, 3)[r, :, 2].astype(np.uint8), ds.key[i])
+            seen.append(i)
+        out = vae.partial_fit(batch, overlap_areas=batch.labels)
+        assert np.isfinite(out[0])
+    assert sorted(seen[:4]) == [0, 1, 2, 3] == sorted(seen[4:])
+    # a foreign load between two batches is reported, not silently trained on
+    it = oi.device_batches(vae, ds, epochs=2, shuffle=False)
+    next(it)
+    eng.load_pairs_u8(torch.from_numpy(ds.lock[idx]), torch.from_numpy(ds.key[idx]), 5, 9)
+    vae._loaded_key = object()
+    with pytest.raises(RuntimeError):
+        next(it)
     torch.cuda.synchronize()
