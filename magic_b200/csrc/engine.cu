@@ -117,7 +117,7 @@ Engine::~Engine() {
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
                   statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
-                  in_[0].xbits, in_[1].xbits, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_};
+                  in_[0].xb3, in_[1].xb3, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
@@ -268,11 +268,15 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
 
   // ---- activations
   // two input buffers: the generator fills one on its own stream while the step consumes the other
-  xb_ld_ = (int)round_up((D + 31) / 32, 8);
+  // packed rows: wide enough for the 64-column k-blocks of the forward GEMM and the 128-row tiles of the weight
+  // gradient (both reach past column D, the bias column, into zero padding)
+  xb_ld_ = (int)round_up(4 * ((D + 1 + 127) / 128), 8);
+  if (const char* ba = getenv("MAGIC_BITS_A")) bits_a_ = atoi(ba) != 0;
   for (auto& b : in_) {
     MAGIC_TRY(alloc_act(&b.X, 3LL * B, D + 1));
     if (b.X.lo) { cudaFree(b.X.lo); stats.hbm_bytes -= (int64_t)(sizeof(bf16) * b.X.rows * b.X.ld); b.X.lo = nullptr; }  // pixels are exact in bf16
-    MAGIC_TRY(alloc((void**)&b.xbits, sizeof(uint32_t) * (size_t)B * xb_ld_));
+    MAGIC_TRY(alloc((void**)&b.xb3, sizeof(uint32_t) * 3 * (size_t)B * xb_ld_));
+    b.xbits = b.xb3 + (size_t)B * xb_ld_;
     MAGIC_TRY(alloc((void**)&b.rot, sizeof(int) * 2 * (size_t)B));
     MAGIC_TRY(alloc((void**)&b.labels, sizeof(float) * B));
     MAGIC_CUDA(cudaEventCreateWithFlags(&b.ready, cudaEventDisableTiming));
@@ -379,6 +383,10 @@ std::string Engine::build_plans() {
                    i == 0);
       p.e[0] = act_epi(H_[i], lin[i].Nv);
       p.ws = ws_; p.ws_ld = H_[i].ld;
+      if (i == 0 && bits_a_) {   // the images stay packed in HBM: 1 KiB instead of 16 KiB per 128 x 64 stage
+        p.a_bits = true;
+        p.abits[0].base = in_[alt].xb3; p.abits[0].pitch = xb_ld_; p.abits[0].rows = 3 * B;
+      }
       MAGIC_TRY(finish(p, alt == 0 ? &fwd_enc_[i] : &fwd_enc0_alt_, "fwd enc"));
       if (alt == 1) flops -= fwd_enc0_alt_.flops;
     }
@@ -470,9 +478,15 @@ std::string Engine::build_plans() {
   }
 
   // ---------------- backward through the encoder: four streams [rot|cost ; lock|cost ; lock|metric ; key|metric]
-  auto wgrad2 = [&](GemmPlan* pl, const Act& x, int xcols, bool x_exact, const Act& dy, int layer) -> std::string {
+  auto wgrad2 = [&](GemmPlan* pl, const Act& x, int xcols, bool x_exact, const Act& dy, int layer,
+                    const uint32_t* xb = nullptr) -> std::string {
     GemmProblem p;
     p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.M = xcols; p.N = lin[layer].Nv; p.K = 2 * B;
+    if (xb) {   // packed rows [rot; lock; key]: optimiser 1 reads rows [0, 2B), optimiser 2 rows [B, 3B)
+      p.a_bits = true;
+      p.abits[0].base = xb; p.abits[0].pitch = xb_ld_; p.abits[0].rows = 2 * B;
+      p.abits[1].base = xb + (size_t)B * xb_ld_; p.abits[1].pitch = xb_ld_; p.abits[1].rows = 2 * B;
+    }
     // optimiser 1 (cost): x rows [rot; lock] = [0, 2B), dy rows [0, 2B).  optimiser 2 (metric): x rows [lock; key] =
     // [B, 3B), dy rows [2B, 4B).
     add_segments(p, 0, amat(x, false, 0, 2LL * B, xcols), amat(x, true, 0, 2LL * B, xcols), amat(dy, false, 0, 2LL * B, p.N),
@@ -507,10 +521,10 @@ std::string Engine::build_plans() {
     MAGIC_TRY(wgrad2(&pl_wg_enc_[i], H_[i - 1], c.enc[i - 1] + 1, false, dH_[i], i));
     MAGIC_TRY(dgrad2(&pl_dg_enc_[i], dH_[i], i, H_[i - 1], dH_[i - 1]));
   }
-  MAGIC_TRY(wgrad2(&pl_wg_enc_[0], in_[0].X, D + 1, true, dH_[0], 0));
+  MAGIC_TRY(wgrad2(&pl_wg_enc_[0], in_[0].X, D + 1, true, dH_[0], 0, bits_a_ ? in_[0].xb3 : nullptr));
   {
     const size_t nz = zero_.size();
-    MAGIC_TRY(wgrad2(&pl_wg_enc0_alt_, in_[1].X, D + 1, true, dH_[0], 0));
+    MAGIC_TRY(wgrad2(&pl_wg_enc0_alt_, in_[1].X, D + 1, true, dH_[0], 0, bits_a_ ? in_[1].xb3 : nullptr));
     zero_.resize(nz);                        // same gradient windows as the first variant
     flops -= pl_wg_enc0_alt_.flops;
   }
@@ -558,7 +572,8 @@ std::string Engine::load_interleaved(const float* d_x) {
   wait_ready(b);
   prof_begin("input.deinterleave");
   deinterleave_f32(d_x, B, D, b.X.hi, b.X.ld, stream);
-  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
+  pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  b.planes_valid = true;
   prof_end();
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
@@ -574,7 +589,8 @@ std::string Engine::load_interleaved_u8(const uint8_t* d_x) {
   wait_ready(b);
   prof_begin("input.deinterleave");
   deinterleave_u8(d_x, B, D, b.X.hi, b.X.ld, stream);
-  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
+  pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  b.planes_valid = true;
   prof_end();
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
@@ -589,7 +605,8 @@ std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uin
   InBuf& b = in_[cur_ ^ 1];
   wait_ready(b);
   planar_u8(l, r, k, B, D, b.X.hi, b.X.ld, stream);
-  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
+  pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  b.planes_valid = true;
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
@@ -605,7 +622,8 @@ std::string Engine::load_pairs_u8(const uint8_t* d_lock, const uint8_t* d_key, u
   InBuf& b = in_[cur_ ^ 1];
   wait_ready(b);
   pairs_u8(d_lock, d_key, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, b.X.hi, b.X.ld, b.rot, stream);
-  pack_lock_bits(b.X.hi, b.X.ld, B, D, b.xbits, xb_ld_, stream);
+  pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  b.planes_valid = true;
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
@@ -621,8 +639,9 @@ std::string Engine::load_pairs_bits(const uint32_t* d_lock, const uint32_t* d_ke
   if (wpr < (D + 31) / 32) return "load_pairs_bits: words_per_row is smaller than ceil(D / 32)";
   InBuf& b = in_[cur_ ^ 1];
   wait_ready(b);
-  pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, b.X.hi, b.X.ld, b.xbits,
-             xb_ld_, b.rot, stream);
+  pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx,
+             bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, stream);
+  b.planes_valid = !bits_a_;
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
@@ -657,8 +676,9 @@ std::string Engine::feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t*
   MAGIC_CUDA(cudaMemcpyAsync(d_key, h_key, plane, cudaMemcpyHostToDevice, gen_stream_));
   if (h_labels) MAGIC_CUDA(cudaMemcpyAsync(b.labels, h_labels, sizeof(float) * B, cudaMemcpyHostToDevice, gen_stream_));
   prof_begin("input.pairs_bits", 0, gen_stream_);
-  pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, b.X.hi, b.X.ld, b.xbits,
-             xb_ld_, b.rot, gen_stream_);
+  pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx,
+             bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, gen_stream_);
+  b.planes_valid = !bits_a_;
   prof_end(gen_stream_);
   MAGIC_CUDA(cudaGetLastError());
   MAGIC_CUDA(cudaEventRecord(b.ready, gen_stream_));
@@ -680,8 +700,9 @@ std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
   gate_pending_ = false;
   // fold the rank into the seed so every rank draws different pairs
   prof_begin("input.generate", 0, gen_stream_);
-  generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, b.X.hi, b.X.ld, b.xbits, xb_ld_,
-                 b.labels, b.rot, num_sms, gen_stream_);
+  generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, bits_a_ ? nullptr : b.X.hi, b.X.ld,
+                 b.xb3, xb_ld_, b.labels, b.rot, num_sms, gen_stream_);
+  b.planes_valid = !bits_a_;
   prof_end(gen_stream_);
   MAGIC_CUDA(cudaGetLastError());
   MAGIC_CUDA(cudaEventRecord(b.ready, gen_stream_));
@@ -711,7 +732,13 @@ std::string Engine::export_rotation(int32_t* d_cs_sn) {
 std::string Engine::export_batch(float* d_x, float* d_labels) {
   InBuf& b = in_[cur_];
   wait_ready(b);
-  if (d_x) planes_to_interleaved_f32(b.X.hi, b.X.ld, B, D, d_x, stream);
+  if (d_x) {
+    if (!b.planes_valid) {     // the batch only exists as packed rows: expand it once
+      unpack_bits_planes(b.xb3, xb_ld_, 3 * B, b.X.hi, b.X.ld, stream);
+      b.planes_valid = true;
+    }
+    planes_to_interleaved_f32(b.X.hi, b.X.ld, B, D, d_x, stream);
+  }
   if (d_labels) MAGIC_CUDA(cudaMemcpyAsync(d_labels, b.labels, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
@@ -1121,6 +1148,11 @@ std::string Engine::build_dp_plans() {
     p.e[0] = scatter_epi(1, 0, 1.f);
     p.e[1] = scatter_epi(2, 0, 1.f);
     p.force_splitk = 1;
+    if (bits_a_) {
+      p.a_bits = true;
+      p.abits[0].base = in_[alt].xb3; p.abits[0].pitch = xb_ld_; p.abits[0].rows = 2 * B;
+      p.abits[1].base = in_[alt].xb3 + (size_t)B * xb_ld_; p.abits[1].pitch = xb_ld_; p.abits[1].rows = 2 * B;
+    }
     std::string err = gemm_plan(p, num_sms, &pl_wg_enc0_sc_[alt]);
     if (!err.empty()) return "dp wgrad enc0: " + err;
   }

@@ -118,8 +118,10 @@ class Engine {
 
   // activations
   struct InBuf {                    // one input batch
-    Act X;                          // [3B, D+1] bf16 planes, rows [rot; lock; key]
-    uint32_t* xbits = nullptr;      // [B, xb_ld] packed lock plane: the BCE epilogue's target
+    Act X;                          // [3B, D+1] bf16 planes, rows [rot; lock; key] (array feeds; MAGIC_BITS_A=0: every path)
+    uint32_t* xb3 = nullptr;        // [3B, xb_ld] the same rows packed 1 bit per pixel, bias column set: the first layer's A operand
+    uint32_t* xbits = nullptr;      // = xb3 + B * xb_ld: the packed lock plane, the BCE epilogue's target
+    bool planes_valid = false;      // X holds this batch too (false when a loader only wrote the packed rows)
     float* labels = nullptr;        // [B] generated overlap labels
     int* rot = nullptr;             // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
     cudaEvent_t ready = nullptr, consumed = nullptr;
@@ -128,6 +130,7 @@ class Engine {
   InBuf in_[2];                     // the generator fills in_[cur_ ^ 1] on gen_stream_ while the step reads in_[cur_]
   int cur_ = 0;
   int xb_ld_ = 0;
+  bool bits_a_ = true;              // first-layer GEMMs read the packed rows (BitsA); MAGIC_BITS_A=0: the bf16 planes
   cudaStream_t gen_stream_ = nullptr;
   cudaEvent_t ev_gate_ = nullptr;   // recorded after the forward pass: earliest start of the next batch's generator
   bool gate_pending_ = false, gen_gate_ = true;

@@ -35,9 +35,9 @@ __global__ void gemm_finish_kernel(EpiArgs e, const float* __restrict__ ws, long
   epilogue_chunk<EPI, false>(e, TileOut{}, r, row, c * 32, M, N, dummy);
 }
 
-template <bool A_MN, bool B_MN, int EPI, int BN = 256>
+template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false>
 static cudaError_t set_smem() {
-  return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN, A_BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)gemm_smem_bytes(EPI));
 }
 
@@ -65,6 +65,12 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<false, false, EPI_STORE_F32, 128>();
   if (e == cudaSuccess) e = set_smem<false, false, EPI_DACT, 128>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 128>();
+  // A as packed bits (the first encoder layer): forward (split-K partial sums or the fused activation), weight
+  // gradient (plain or scattered to the owners' staging)
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_STORE_F32, 256, true>();
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_ACT, 256, true>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, true>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_SCATTER_F32, 256, true>();
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_ACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_DACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -199,6 +205,21 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   pl.epi = p.epi;
   if (p.ngroups < 1 || p.ngroups > kMaxGroups || p.nseg < 1 || p.nseg > kMaxSegs) return "bad ngroups/nseg";
   const bool a_mn = p.kind == GEMM_WGRAD, b_mn = p.kind != GEMM_DGRAD;
+  pl.a_bits = p.a_bits;
+  if (p.a_bits) {
+    if (p.kind == GEMM_DGRAD) return "a_bits: forward and wgrad kinds only";
+    if (!(p.epi == EPI_STORE_F32 || (p.kind == GEMM_FWD && p.epi == EPI_ACT) || (p.kind == GEMM_WGRAD && p.epi == EPI_SCATTER_F32)))
+      return "a_bits: no kernel variant for this epilogue";
+    if (p.cluster_m > 1 || p.block_n == 128) return "a_bits: 256-wide tiles without clusters only";
+    const long long tm = (p.M + kBlockM - 1) / kBlockM, kbl = (p.K + kBlockK - 1) / kBlockK;
+    const long long need = a_mn ? 4 * tm : 2 * kbl;     // words a tile row / k-block row may touch
+    for (int g = 0; g < p.ngroups; ++g) {
+      const BitsA& ba = p.abits[g];
+      if (!ba.base || (reinterpret_cast<uintptr_t>(ba.base) & 7) != 0) return "a_bits: base must be 8-byte aligned";
+      if (ba.pitch % 2 != 0 || ba.pitch < need) return "a_bits: row pitch must be even and cover the padded extent";
+      if (ba.rows < 0 || ba.rows > (a_mn ? p.K : p.M)) return "a_bits: more rows than the problem has";
+    }
+  }
   // Tile width.  128 for short-K problems whose 256-wide tiles would leave SMs without any tile (the decoder's hidden
   // layers at M = 4096: 64 tiles; every layer at the reference's batch of 100): twice the CTAs, half the exposed
   // epilogue (TileCfg in gemm_sm100.cuh; 10 -> 8 us per launch, profiles/r01m).  With one or two 256-wide tiles per SM
@@ -213,7 +234,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
     const int kb = (p.K + kBlockK - 1) / kBlockK * p.nseg;
     bool want = has128 && p.cluster_m <= 1 && p.N > 128 && tiles256 < (long long)num_sms && kb <= 32;
     if (p.block_n == 128) want = has128 && p.cluster_m <= 1;
-    if (p.block_n == 256) want = false;
+    if (p.block_n == 256 || p.a_bits) want = false;
     if (want) bn = 128;
   }
   int cm_b = (b_mn && (p.cluster_m == 2 || p.cluster_m == 4)) ? p.cluster_m : 1;
@@ -223,7 +244,8 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       const Mat& A = p.a[g][s];
       const Mat& B = p.b[g][s];
       std::string err;
-      if (!a_mn) {   // Mat[M,K]
+      if (p.a_bits) {   // no tensor map: the expander warps read args.abits[g]
+      } else if (!a_mn) {   // Mat[M,K]
         if (A.cols != p.K) return "A cols != K";
         err = make_tmap(&pl.args.ta[g][s], A.ptr, A.cols, A.rows, A.ld, kBlockK, kBlockM);
       } else {       // Mat[K,M]
@@ -241,6 +263,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       if (!err.empty()) return "B: " + err;
     }
   GemmArgs& a = pl.args;
+  for (int g = 0; g < p.ngroups; ++g) a.abits[g] = p.abits[g];
   a.M = p.M;
   a.N = p.N;
   a.kblocks = (p.K + kBlockK - 1) / kBlockK;
@@ -352,12 +375,12 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   return "";
 }
 
-template <bool A_MN, bool B_MN, int EPI, int BN = 256>
+template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false>
 static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
   const int cm = pl.args.cluster_m;
-  if (cm <= 1) {
-    launch_chain(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, dim3(pl.grid), dim3(gemm_threads(EPI)), gemm_smem_bytes(EPI), s,
-                 pl.args);
+  if (cm <= 1 || A_BITS) {
+    launch_chain(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN, A_BITS>, dim3(pl.grid), dim3(gemm_threads(EPI, A_BITS)),
+                 gemm_smem_bytes(EPI), s, pl.args);
     return;
   }
   cudaLaunchConfig_t cfg;
@@ -395,8 +418,12 @@ int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
   if (pl.two_pass) {
     zero_fill(pl.ws, sizeof(float) * pl.ws_ld * pl.args.M, s);
   }
-  const int key = pl.kind * 8 + pl.epi + (pl.args.bn == 128 ? 64 : 0);
+  const int key = pl.kind * 8 + pl.epi + (pl.args.bn == 128 ? 64 : 0) + (pl.a_bits ? 128 : 0);
   switch (key) {
+    case 128 + GEMM_FWD * 8 + EPI_STORE_F32: launch_variant<false, true, EPI_STORE_F32, 256, true>(pl, s); break;
+    case 128 + GEMM_FWD * 8 + EPI_ACT: launch_variant<false, true, EPI_ACT, 256, true>(pl, s); break;
+    case 128 + GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32, 256, true>(pl, s); break;
+    case 128 + GEMM_WGRAD * 8 + EPI_SCATTER_F32: launch_variant<true, true, EPI_SCATTER_F32, 256, true>(pl, s); break;
     case 64 + GEMM_FWD * 8 + EPI_STORE_F32: launch_variant<false, true, EPI_STORE_F32, 128>(pl, s); break;
     case 64 + GEMM_FWD * 8 + EPI_ACT: launch_variant<false, true, EPI_ACT, 128>(pl, s); break;
     case 64 + GEMM_DGRAD * 8 + EPI_STORE_F32: launch_variant<false, false, EPI_STORE_F32, 128>(pl, s); break;

@@ -27,6 +27,7 @@ enum GemmKind : int {
 struct GemmPlan {
   GemmArgs args;
   int kind = 0, epi = 0, grid = 0;
+  bool a_bits = false;   // the A_BITS kernel variant: the main problem's A operand is read as packed bits (args.abits)
   long long items = 0;   // work items (per cluster when args.cluster_m > 1)
   // split-K with a non-linear epilogue: GEMM accumulates fp32 into ws (red.add), then finish applies epi
   bool two_pass = false;
@@ -59,6 +60,11 @@ struct GemmProblem {
   int cluster_m = 1;         // CTAs per cluster along M sharing the B tile by TMA multicast (FWD / WGRAD kinds; 1, 2 or 4)
   float* ws = nullptr;       // fp32 workspace [M, ws_ld] for two-pass split-K (ACT / DACT); may be null
   long long ws_ld = 0;
+  // A as packed bits instead of a[g][*] (FWD: bits of A[M,K]; WGRAD: bits of A[K,M]; see BitsA in gemm_sm100.cuh).
+  // Every precision segment reads the same bits (a binary operand is exact in bf16: its low part is zero), so with
+  // nseg = 2 the segments are (A, B_hi), (A, B_lo).  Only b[g][*] is read from the problem; 256-wide tiles.
+  bool a_bits = false;
+  BitsA abits[kMaxGroups] = {};
 };
 
 // Returns empty string on success, else an error message.

@@ -33,6 +33,10 @@ constexpr int kMaxSegs = 3;
 // hide MUFU and TMEM latencies.
 __host__ __device__ constexpr int epi_warps(int epi) { return epi == 3 /*EPI_BCE*/ ? 16 : 8; }
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
+// A_BITS variants (the first encoder layer: its A operand is a binary image, kept in HBM as 1 bit per pixel): four more
+// warps expand the packed bits of a pipeline stage into the bf16 swizzle layout the MMA reads -- see BitsA.
+constexpr int kExpandWarps = 4;     // one per pipeline stage of the 256-wide tile configuration
+__host__ __device__ constexpr int gemm_threads(int epi, bool a_bits) { return gemm_threads(epi) + (a_bits ? 32 * kExpandWarps : 0); }
 constexpr uint32_t kStageBytesA = kBlockM * kBlockK * 2;   // 16 KiB
 constexpr uint32_t kStageBytesB = kBlockN * kBlockK * 2;   // 32 KiB
 constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
@@ -112,6 +116,16 @@ struct alignas(128) GemmExtraDev {
   EpiArgs epi;
 };
 
+// The A operand as packed bits (A_BITS kernels): element (r, c) of a row-major {0,1} matrix is bit c & 31 of word
+// base[r * pitch + (c >> 5)]; rows >= `rows` read as zero.  For the K-major kinds the matrix is A[M, K], for the wgrad
+// kind it is A[K, M] (the stored orientation of the activations, as with the bf16 operands).  A 128 x 64 stage is
+// 1 KiB of bits instead of 16 KiB of bf16 through L2; the expansion to bf16 happens on the way into shared memory.
+struct BitsA {
+  const uint32_t* base;
+  long long pitch;     // words per row, even (rows are read as 8-byte pieces)
+  int rows;
+};
+
 struct GemmArgs {
   CUtensorMap ta[kMaxGroups][kMaxSegs];
   CUtensorMap tb[kMaxGroups][kMaxSegs];
@@ -129,6 +143,7 @@ struct GemmArgs {
   int x_m[kMaxExtra], x_n[kMaxExtra], x_kb[kMaxExtra], x_tn[kMaxExtra];   // rows, cols, k-blocks per segment, N tiles
   long long* trace;  // diagnostics: [grid][64] clock64 stamps of the phases of each CTA (selftest "trace"), or nullptr
   CUtensorMap tout[kMaxGroups][2];   // output tiles (box 32 cols x 32 rows): [g][0] fp32 or bf16 hi plane, [g][1] lo plane
+  BitsA abits[kMaxGroups];           // A_BITS kernels: the main problem's A operand (extras keep bf16 A through TMA)
 };
 
 struct WorkItem {
@@ -535,8 +550,16 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const TileOut& 
 
 static_assert(sizeof(GemmArgs) <= 4096, "kernel parameter space (kept under the classic 4 KiB)");
 
+// 16 packed pixels -> 16 bf16 (0.0 / 1.0) in 8 words.  u carries bit i at position i and again at position i + 15, so
+// (u >> 2j) & 0x00010001 holds elements 2j and 2j + 1 in bit 0 of the two halves; times 0x3F80 makes each a bf16 1.0.
+__device__ __forceinline__ void expand16(uint32_t v16, uint32_t (&w)[8]) {
+  const uint32_t u = v16 | (v16 << 15);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) w[j] = ((u >> (2 * j)) & 0x00010001u) * 0x3F80u;
+}
+
 // ---------------------------------------------------------------------------- the kernel
-template <bool A_MN, bool B_MN, int EPI, int BN>
+template <bool A_MN, bool B_MN, int EPI, int BN, bool A_BITS = false>
 // 112 registers: three of this kernel's warps (3 x 32 x 112) and three warps of the batch generator (3 x 32 x 56) fit
 // the 16K registers of one SM sub-partition, so the generator's CTA stays co-resident with every GEMM variant; it is
 // the 576-thread BCE variant has five warps on a sub-partition, hence 96.
@@ -584,7 +607,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         ptx::tma_prefetch_desc(&args.tb[g][s]);
       }
     for (int i = 0; i < kNS; ++i) {
-      ptx::mbar_init(&full_bar[i], 1);
+      ptx::mbar_init(&full_bar[i], A_BITS ? 2 : 1);   // the producer's expect_tx arrival + the stage's expander warp
       ptx::mbar_init(&empty_bar[i], CM);   // one arrival per CTA of the cluster (multicast commit)
     }
     for (int i = 0; i < kAcc; ++i) {
@@ -615,15 +638,18 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
           const int seg = kb / it.kblocks;
           const int k0 = (kb - seg * it.kblocks) * kBlockK;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          ptx::mbar_expect_tx(&full_bar[stage], Cfg::kBytes);
+          const bool a_by_tma = !A_BITS || it.g < 0;   // A_BITS: the main problem's A stage is written by the expander warps
+          ptx::mbar_expect_tx(&full_bar[stage], a_by_tma ? Cfg::kBytes : Cfg::kBytesB);
           uint8_t* sa = smem_a + stage * kStageBytesA;
           uint8_t* sb = smem_b + stage * Cfg::kBytesB;
           const CUtensorMap* ta = it.g >= 0 ? &args.ta[it.g][seg] : &args.xdev[-1 - it.g].ta[seg];
           const CUtensorMap* tb = it.g >= 0 ? &args.tb[it.g][seg] : &args.xdev[-1 - it.g].tb[seg];
-          if constexpr (!A_MN) {
-            ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);              // box {64 k, 128 m}
-          } else {
-            ptx::tma_load_3d(ta, &full_bar[stage], sa, 0, k0, it.m0 >> 6);      // box {64 m, 64 k, 2 slabs}
+          if (a_by_tma) {
+            if constexpr (!A_MN) {
+              ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);              // box {64 k, 128 m}
+            } else {
+              ptx::tma_load_3d(ta, &full_bar[stage], sa, 0, k0, it.m0 >> 6);      // box {64 m, 64 k, 2 slabs}
+            }
           }
           if constexpr (!B_MN) {
             ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);              // box {64 k, BN n}
@@ -684,7 +710,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       // following kernels' CTAs on the SMs for the whole duration and starves the generator's side stream.
       ptx::grid_dep_launch();
     }
-  } else {
+  } else if (warp < 2 + epi_warps(EPI)) {
     // ------------------------------------------------------------ epilogue warps
     // TMEM lane quarter = warp % 4 (hardware rule); the two warps of a quarter split the 32-column chunks
     // even/odd, so every scheduler has two epilogue warps to overlap latencies with.
@@ -785,6 +811,94 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       // one atomic per CTA (not per warp: 2368 same-address atomics serialise in L2 at the kernel's tail): the warp
       // sums meet in the staging slots, which are idle after bulk_wait_all()
       if (lane == 0) *reinterpret_cast<float*>(smem + kTileStageOffset + (warp - 2) * 2048) = loss_acc;
+    }
+  } else if constexpr (A_BITS) {
+    // ------------------------------------------------------------ bit expanders (A_BITS kernels only)
+    // The A stage is 128 swizzle rows of 128 bytes: accumulator row r of the tile for the K-major kinds (64
+    // consecutive k), k-row r & 63 of slab r >> 6 for the MN-major kind (64 consecutive m).  Either way row r is 64
+    // consecutive bits of one row of the packed matrix and lands at byte r * 128 of the stage, 16-byte piece c at
+    // position c ^ (r & 7) -- exactly what the TMA's 128-byte swizzle would have written from a bf16 matrix.
+    // Warp e owns pipeline stage e (k-blocks e, e + 4, ... of this CTA's sequence; lane l writes rows l, l + 32,
+    // l + 64, l + 96), so four stages are being expanded at once, each with its own wait -> store -> fence -> arrive
+    // round trip (one group walking the stages in turn was bound by that latency: 920 cycles per k-block).  The bits of
+    // a warp's next k-block are fetched while it expands the current one -- four k-block times ahead of their use.
+    // (448 threads: two more warps per stage -- 576 threads -- do not fit the 16 K registers of an SM sub-partition at
+    // this kernel's 112 registers, and one warp per stage already keeps up with the MMAs: profiles/r01p)
+    static_assert(kNS == kExpandWarps, "expander warp e serves pipeline stage e");
+    const int ew = warp - (2 + epi_warps(EPI));
+    struct Cursor { int w, kb, kb1, kblocks, m0, g; bool valid; };
+    auto open = [&](Cursor& c) {
+      c.valid = false;
+      while (c.w < total_work) {
+        const WorkItem it = decode_work(args, c.w, 0);
+        if (it.kb0 < it.kb1) {
+          c.kb = it.kb0; c.kb1 = it.kb1; c.kblocks = it.kblocks; c.m0 = it.m0; c.g = it.g; c.valid = true;
+          return;
+        }
+        c.w += work_stride;
+      }
+    };
+    auto advance = [&](Cursor& c, int n) {       // n k-blocks further along the CTA's sequence of (work item, k-block)
+      while (c.valid && n > 0) {
+        const int left = c.kb1 - c.kb;
+        if (n < left) { c.kb += n; return; }
+        n -= left;
+        c.w += work_stride;
+        open(c);
+      }
+    };
+    auto fetch = [&](const Cursor& c, uint2 (&v)[4]) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) v[q] = make_uint2(0u, 0u);
+      if (c.valid && c.g >= 0) {
+        const BitsA& ba = args.abits[c.g];
+        int kk = c.kb;
+        while (kk >= c.kblocks) kk -= c.kblocks;          // k-block inside its precision segment: every segment reads the same A
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int r = lane + 32 * q;
+          int row, word;
+          if constexpr (!A_MN) { row = c.m0 + r; word = kk * (kBlockK / 32); }
+          else { row = kk * kBlockK + (r & 63); word = (c.m0 >> 5) + 2 * (r >> 6); }
+          if (row < ba.rows) v[q] = __ldg(reinterpret_cast<const uint2*>(ba.base + (long long)row * ba.pitch + word));
+        }
+      }
+    };
+    Cursor cur, pre;
+    cur.w = work0; open(cur);
+    advance(cur, ew);
+    pre = cur;
+    advance(pre, 4);
+    uint2 now[4], nxt[4];
+    fetch(cur, now);
+    uint8_t* const stage_base = smem_a + ew * kStageBytesA + lane * 128;
+    const int x = lane & 7;
+    uint32_t phase = 0;
+    while (cur.valid) {
+      fetch(pre, nxt);
+      ptx::mbar_wait(&empty_bar[ew], phase ^ 1);          // the MMAs that read this stage have retired
+      if (cur.g >= 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint8_t* dst = stage_base + q * (32 * 128);
+          const uint32_t half[4] = {now[q].x & 0xFFFFu, now[q].x >> 16, now[q].y & 0xFFFFu, now[q].y >> 16};
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            uint32_t w[8];
+            expand16(half[h], w);
+            ptx::st_shared_v4(dst + (((2 * h) ^ x) << 4), w[0], w[1], w[2], w[3]);
+            ptx::st_shared_v4(dst + (((2 * h + 1) ^ x) << 4), w[4], w[5], w[6], w[7]);
+          }
+        }
+        ptx::fence_proxy_async_smem();                    // generic-proxy writes -> visible to the MMA's async-proxy reads
+      }
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&full_bar[ew]);
+      phase ^= 1;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) now[q] = nxt[q];
+      cur = pre;
+      advance(pre, 4);
     }
   }
 

@@ -543,8 +543,10 @@ void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B,
 //   3. label = max over the 8 rotations r*45 deg of the key (same inverse map, fixed Q14 constants) of
 //      popcount(lock AND rot_r(key))  (README.md:19-27: the "maximum overlap area"; the reference's dataset
 //      generator is not in the repository);
-//   4. expansion of the three bitmaps to the bf16 operand planes (rows [rot; lock; key], 1.0 in the bias column
-//      D, zero pad) with 16-byte coalesced stores, plus the packed lock bitmap the BCE epilogue reads.
+//   4. the three bitmaps go out as they are: packed rows [rot; lock; key] of xb3 with the bias column D set -- the
+//      first layer's GEMMs read them as their A operand (BitsA, gemm_sm100.cuh) and the BCE epilogue reads the lock
+//      rows as its target.  With `planes` != nullptr (MAGIC_BITS_A=0) they are also expanded to bf16 operand planes
+//      (1.0 in the bias column, zero pad) with 16-byte coalesced stores.
 constexpr int kPrims = 3;
 constexpr int kLabelRots = 8;
 constexpr int kGenThreads = 384;
@@ -642,7 +644,7 @@ __global__ void fill_expand_lut_kernel() { g_expand_lut[threadIdx.x] = expand_by
 __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t seed, uint64_t step, int B, int side,
                                                                      uint32_t inv_side /* ceil(2^32 / side) */,
                                                                      __nv_bfloat16* planes, long long ld,
-                                                                     uint32_t* xbits, int xb_ld, float* labels,
+                                                                     uint32_t* xb3, int xb_ld, float* labels,
                                                                      int* rot_cs_sn) {
   const int D = side * side;
   const int nwords = (D + 31) >> 5;
@@ -753,7 +755,16 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
     labels[i] = (float)best;
   }
 
-  // ---- 4. expand to the bf16 operand planes: 8 pixels (one bitmap byte) -> one 16-byte store per plane
+  // ---- 4. packed rows [rot; lock; key] with the bias bit (D % 32 == 0: the bitmaps end on a word boundary)
+  for (int w = threadIdx.x; w < xb_ld; w += kGenThreads) {
+    const uint32_t bias = w == (D >> 5) ? 1u << (D & 31) : 0u;
+    const bool in = w < nwords;
+    xb3[(long long)i * xb_ld + w] = (in ? bm[2][w] : 0u) | bias;
+    xb3[(long long)(B + i) * xb_ld + w] = (in ? bm[0][w] : 0u) | bias;
+    xb3[(long long)(2 * B + i) * xb_ld + w] = (in ? bm[1][w] : 0u) | bias;
+  }
+  // ---- 4b. (optional) bf16 operand planes: 8 pixels (one bitmap byte) -> one 16-byte store per plane
+  if (planes) {
   const int chunks = (int)(ld / 8);
   const uint8_t* bl = reinterpret_cast<const uint8_t*>(bm[0]);
   const uint8_t* bk = reinterpret_cast<const uint8_t*>(bm[1]);
@@ -771,25 +782,22 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
     }
     prot[ch] = vr; plock[ch] = vl; pkey[ch] = vk;
   }
-  if (xbits)
-    for (int w = threadIdx.x; w < xb_ld; w += kGenThreads) xbits[(long long)i * xb_ld + w] = w < nwords ? bm[0][w] : 0u;
+  }
   __syncthreads();                             // the bitmaps are reused by the next pair
   }
 }
 
-void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, uint32_t* xbits,
+void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, uint32_t* xb3,
                     int xb_ld, float* labels, int* rot_cs_sn, int max_ctas, cudaStream_t s) {
   const uint32_t inv_side = (uint32_t)((0x100000000ull + (uint64_t)side - 1) / (uint64_t)side);
   // same (maximum) shared-memory carveout as the GEMM kernels: an SM only changes its carveout when it is idle, so a
   // different preference here would make every overlapped GEMM CTA wait for the generator to drain
   const int nwords = (side * side + 31) / 32;
   const size_t smem = 3 * (size_t)((nwords + 8 + 3) & ~3) * sizeof(uint32_t);
-  generate_pairs_kernel<<<B < max_ctas ? B : max_ctas, kGenThreads, smem, s>>>(seed, step, B, side, inv_side, planes, ld, xbits, xb_ld, labels,
+  generate_pairs_kernel<<<B < max_ctas ? B : max_ctas, kGenThreads, smem, s>>>(seed, step, B, side, inv_side, planes, ld, xb3, xb_ld, labels,
                                                      rot_cs_sn);
 }
 
-// lock plane (bf16 {0,1}, rows [B, 2B) of planes) -> packed bitmap xbits[B, xb_ld] for the loaders that do not
-// come through the generator.  One warp per 32-pixel word.
 // ------------------------------------------------------------------ N2: dataset pairs -> operand planes
 // (8c/overlap_input.py:181-195: lock, random_rotation(lock), key concatenated; 8c/utils.py:329-340: the angle is
 // uniform in [0, 2 pi), nearest-neighbour, zero fill.)  lock / key are uint8 [B, D] (any non-zero byte is a set
@@ -837,12 +845,13 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
 // The same pipeline fed with bit-packed planes: lock / key are [B, wpr] 32-bit words, pixel p = bit (p & 31) of word
 // p >> 5 (the layout of xbits, numpy packbits(bitorder='little')): 10 KB per pair instead of 80 KB as uint8 or
 // 480 KB as the float32 array the reference feeds.  One CTA per (pair, 1024-column chunk), eight columns per thread
-// (one 16-byte store per plane); the lock's bitmap sits in shared memory for the rotated samples.  The first chunk's
-// CTA also copies the lock words into xbits (the BCE epilogue's packed targets).
+// the lock's bitmap sits in shared memory for the rotated samples.  Output: one byte per plane into the packed rows
+// [rot; lock; key] of xb3 (bias column set; the GEMMs' A operand and the BCE target), and -- only when `planes` is given --
+// one 16-byte store per plane of expanded bf16.
 constexpr int kPairsBitsMaxWords = 2048;      // side <= 256
 __global__ void __launch_bounds__(128) pairs_bits_kernel(const uint32_t* __restrict__ lock, const uint32_t* __restrict__ key,
                                                          int wpr, int B, int side, uint64_t seed, uint64_t step,
-                                                         __nv_bfloat16* planes, long long ld, uint32_t* xbits, int xb_ld,
+                                                         __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld,
                                                          int* rot_cs_sn) {
   __shared__ uint32_t bm[kPairsBitsMaxWords];
   __shared__ int q14[2];
@@ -861,10 +870,10 @@ __global__ void __launch_bounds__(128) pairs_bits_kernel(const uint32_t* __restr
   for (int w = threadIdx.x; w < nwords; w += blockDim.x) {
     const uint32_t v = __ldg(L + w) & (w == nwords - 1 ? tail : 0xffffffffu);
     bm[w] = v;
-    if (blockIdx.x == 0) xbits[(long long)i * xb_ld + w] = v;
   }
-  if (blockIdx.x == 0)
-    for (int w = nwords + threadIdx.x; w < xb_ld; w += blockDim.x) xbits[(long long)i * xb_ld + w] = 0u;
+  if (blockIdx.x == 0)        // words past the operand pitch (ld / 32 is a whole number of words: ld % 64 == 0)
+    for (int w = (int)(ld >> 5) + threadIdx.x; w < xb_ld; w += blockDim.x)
+      xb3[(long long)i * xb_ld + w] = xb3[(long long)(B + i) * xb_ld + w] = xb3[(long long)(2 * B + i) * xb_ld + w] = 0u;
   __syncthreads();
   const int cs = q14[0], sn = q14[1];
   const int c0 = blockIdx.x * 1024 + threadIdx.x * 8;
@@ -882,30 +891,51 @@ __global__ void __launch_bounds__(128) pairs_bits_kernel(const uint32_t* __restr
     }
   }
   if (D >= c0 && D < c0 + 8) { const uint32_t one = 1u << (D - c0); bl |= one; bk |= one; br |= one; }   // bias column
-  *reinterpret_cast<uint4*>(planes + (long long)i * ld + c0) = expand_byte(br);
-  *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + c0) = expand_byte(bl);
-  *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + c0) = expand_byte(bk);
+  reinterpret_cast<uint8_t*>(xb3 + (long long)i * xb_ld)[c0 >> 3] = (uint8_t)br;
+  reinterpret_cast<uint8_t*>(xb3 + (long long)(B + i) * xb_ld)[c0 >> 3] = (uint8_t)bl;
+  reinterpret_cast<uint8_t*>(xb3 + (long long)(2 * B + i) * xb_ld)[c0 >> 3] = (uint8_t)bk;
+  if (planes) {
+    *reinterpret_cast<uint4*>(planes + (long long)i * ld + c0) = expand_byte(br);
+    *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + c0) = expand_byte(bl);
+    *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + c0) = expand_byte(bk);
+  }
 }
 void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
-                __nv_bfloat16* planes, long long ld, uint32_t* xbits, int xb_ld, int* rot_cs_sn, cudaStream_t s) {
-  pairs_bits_kernel<<<dim3((unsigned)((ld + 1023) / 1024), B), 128, 0, s>>>(lock, key, wpr, B, side, seed, step, planes, ld, xbits,
+                __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, cudaStream_t s) {
+  pairs_bits_kernel<<<dim3((unsigned)((ld + 1023) / 1024), B), 128, 0, s>>>(lock, key, wpr, B, side, seed, step, planes, ld, xb3,
                                                                              xb_ld, rot_cs_sn);
 }
 
-__global__ void __launch_bounds__(256) pack_lock_bits_kernel(const __nv_bfloat16* __restrict__ planes, long long ld, int B,
-                                                             int D, uint32_t* xbits, int xb_ld) {
+// bf16 {0,1} operand planes [rows, ld] -> packed rows xb[rows, xb_ld] with the bias column D set, for the loaders
+// that produce planes (array feeds).  One warp per 32-pixel word.
+__global__ void __launch_bounds__(256) pack_planes_bits_kernel(const __nv_bfloat16* __restrict__ planes, long long ld, int rows,
+                                                               int D, uint32_t* xb, int xb_ld) {
   const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (gw >= (long long)B * xb_ld) return;
+  if (gw >= (long long)rows * xb_ld) return;
   const int i = (int)(gw / xb_ld), w = (int)(gw % xb_ld);
   const int p = w * 32 + lane;
-  const bool bit = p < D && __bfloat162float(planes[(long long)(B + i) * ld + p]) != 0.f;
+  const bool bit = p < D ? __bfloat162float(planes[(long long)i * ld + p]) != 0.f : p == D;
   const uint32_t word = __ballot_sync(0xffffffffu, bit);
-  if (lane == 0) xbits[gw] = word;
+  if (lane == 0) xb[gw] = word;
 }
-void pack_lock_bits(const __nv_bfloat16* planes, long long ld, int B, int D, uint32_t* xbits, int xb_ld, cudaStream_t s) {
-  const long long threads = (long long)B * xb_ld * 32;
-  pack_lock_bits_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(planes, ld, B, D, xbits, xb_ld);
+void pack_planes_bits(const __nv_bfloat16* planes, long long ld, int rows, int D, uint32_t* xb, int xb_ld, cudaStream_t s) {
+  const long long threads = (long long)rows * xb_ld * 32;
+  pack_planes_bits_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(planes, ld, rows, D, xb, xb_ld);
+}
+// packed rows -> bf16 operand planes (export of a batch that was only ever held as bits): 8 pixels per thread
+__global__ void __launch_bounds__(256) unpack_bits_planes_kernel(const uint32_t* __restrict__ xb, int xb_ld, int rows,
+                                                                 __nv_bfloat16* planes, long long ld) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int chunks = (int)(ld >> 3);
+  if (idx >= (long long)rows * chunks) return;
+  const int i = (int)(idx / chunks), ch = (int)(idx % chunks);
+  const uint32_t b = reinterpret_cast<const uint8_t*>(xb + (long long)i * xb_ld)[ch];
+  reinterpret_cast<uint4*>(planes + (long long)i * ld)[ch] = expand_byte(b);
+}
+void unpack_bits_planes(const uint32_t* xb, int xb_ld, int rows, __nv_bfloat16* planes, long long ld, cudaStream_t s) {
+  const long long n = (long long)rows * (ld >> 3);
+  unpack_bits_planes_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(xb, xb_ld, rows, planes, ld);
 }
 
 
@@ -931,7 +961,8 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(pairs_bits_kernel);
   MAGIC_MAX_CARVEOUT(planes_to_interleaved_kernel);
   MAGIC_MAX_CARVEOUT(generate_pairs_kernel);
-  MAGIC_MAX_CARVEOUT(pack_lock_bits_kernel);
+  MAGIC_MAX_CARVEOUT(pack_planes_bits_kernel);
+  MAGIC_MAX_CARVEOUT(unpack_bits_planes_kernel);
   fill_expand_lut_kernel<<<1, 256>>>();
   cudaDeviceSynchronize();      // init time only: the generator reads the table from its own stream
   cudaGetLastError();

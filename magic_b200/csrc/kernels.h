@@ -93,16 +93,19 @@ void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B,
 
 // On-device synthetic shape pairs (replaces 8c/overlap_input.py): random filled shapes on a
 // side x side canvas, nearest-neighbour rotated copy (8c/utils.py:329-340), integer overlap label.
-void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, uint32_t* xbits,
+// Output: packed rows xb3[3B, xb_ld] in the order [rot; lock; key] (pixel p = bit p & 31 of word p >> 5, bias column D
+// set): the A operand of the first layer's GEMMs and, rows [B, 2B), the target the sigmoid-BCE epilogue reads
+// (8c/vae.py:260-263).  `planes` may be null; otherwise the same rows are also written as bf16 [3B, ld].
+void generate_pairs(uint64_t seed, uint64_t step, int B, int side, __nv_bfloat16* planes, long long ld, uint32_t* xb3,
                     int xb_ld, float* labels, int* rot_cs_sn, int max_ctas, cudaStream_t s);
-// packed 1-bit copy of the lock plane (pixel p = bit p & 31 of word p >> 5, row pitch xb_ld words): the target the
-// sigmoid-BCE epilogue reads (8c/vae.py:260-263)
 void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t seed, uint64_t step,
               __nv_bfloat16* planes, long long ld, int* rot_cs_sn, cudaStream_t s);
-// bit-packed pairs: pixel p = bit (p & 31) of word p >> 5 of the pair's row (wpr words per row); also fills xbits
+// bit-packed pairs: pixel p = bit (p & 31) of word p >> 5 of the pair's row (wpr words per row); fills xb3 like the
+// generator, and `planes` when it is not null
 void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
-                __nv_bfloat16* planes, long long ld, uint32_t* xbits, int xb_ld, int* rot_cs_sn, cudaStream_t s);
-void pack_lock_bits(const __nv_bfloat16* planes, long long ld, int B, int D, uint32_t* xbits, int xb_ld, cudaStream_t s);
+                __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, cudaStream_t s);
+void pack_planes_bits(const __nv_bfloat16* planes, long long ld, int rows, int D, uint32_t* xb, int xb_ld, cudaStream_t s);
+void unpack_bits_planes(const uint32_t* xb, int xb_ld, int rows, __nv_bfloat16* planes, long long ld, cudaStream_t s);
 
 void zero_fill(void* ptr, size_t bytes, cudaStream_t s);   // kernel-based memset(0): ptr 16-byte aligned, bytes % 4 == 0
 void kernels_init();                                        // one-time function attributes (shared-memory carveout)

@@ -71,6 +71,7 @@ static void host_ref(int kind, int M, int N, int K, int nseg, const HostMat* a, 
 
 static int g_cluster = 1;   // cluster_m applied to the problems built below
 static int g_bn = 0;        // block_n applied to the problems built below (0 = the planner's choice)
+static int g_bits = 0;      // bench(): A operand as packed bits (all zero)
 
 static void test_store(int kind, int M, int N, int K, int nseg, int split, int sms) {
   HostMat a[3], b[3];
@@ -205,6 +206,207 @@ static void test_wgrad_extras(int sms) {
   report(name, me, 2e-3 * sqrt((double)K) * 0.1 * 4 + 1e-4);
 }
 
+// ---------------------------------------------------------------- A operand as packed bits (A_BITS kernel variants)
+// Packs a binary HostMat (rows x cols) into bits on the device: element (r, c) -> bit c & 31 of word r * pitch + (c >> 5).
+static uint32_t* pack_bits(const HostMat& m, long long pitch) {
+  std::vector<uint32_t> h((size_t)m.rows * pitch, 0u);
+  for (long long r = 0; r < m.rows; ++r)
+    for (long long c = 0; c < m.cols; ++c)
+      if (m.at(r, c) != 0.f) h[(size_t)r * pitch + (c >> 5)] |= 1u << (c & 31);
+  uint32_t* d;
+  CK(cudaMalloc(&d, sizeof(uint32_t) * h.size()));
+  CK(cudaMemcpy(d, h.data(), sizeof(uint32_t) * h.size(), cudaMemcpyHostToDevice));
+  return d;
+}
+static long long bits_pitch(int kind, int M, int K) {
+  const long long need = kind == GEMM_WGRAD ? 4LL * ((M + 127) / 128) : 2LL * ((K + 63) / 64);
+  return (need + 7) / 8 * 8;
+}
+
+// The bits variant must reproduce the bf16-operand kernel bit for bit (same MMAs on the same shared-memory image) and
+// both must match the host reference.  FWD with nseg segments and split-K, fp32 store.
+static void test_bits_fwd_store(int M, int N, int K, int nseg, int split, int sms) {
+  HostMat a, b[3];
+  a.init(M, K, (K + 63) / 64 * 64, 1.f, true);
+  for (int s = 0; s < nseg; ++s) b[s].init(K, N, (N + 63) / 64 * 64, 1.f);
+  const long long pitch = bits_pitch(GEMM_FWD, M, K);
+  uint32_t* dbits = pack_bits(a, pitch);
+  const long long ldo = (N + 3) / 4 * 4;
+  std::vector<float> h[2];
+  int used_split = 0;
+  for (int v = 0; v < 2; ++v) {
+    float* dout;
+    CK(cudaMalloc(&dout, sizeof(float) * M * ldo));
+    CK(cudaMemset(dout, 0, sizeof(float) * M * ldo));
+    GemmProblem p;
+    p.kind = GEMM_FWD; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split; p.block_n = 256;
+    for (int s = 0; s < nseg; ++s) { p.a[0][s] = a.mat(); p.b[0][s] = b[s].mat(); }
+    if (v == 1) { p.a_bits = true; p.abits[0].base = dbits; p.abits[0].pitch = pitch; p.abits[0].rows = M; }
+    EpiArgs e = {};
+    e.out = dout; e.ld_out = ldo; e.alpha = 0.5f;
+    p.e[0] = e;
+    GemmPlan pl;
+    std::string err = gemm_plan(p, sms, &pl);
+    if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+    if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
+    CK(cudaDeviceSynchronize());
+    used_split = pl.args.splitk;
+    h[v].resize((size_t)M * ldo);
+    CK(cudaMemcpy(h[v].data(), dout, sizeof(float) * M * ldo, cudaMemcpyDeviceToHost));
+    cudaFree(dout);
+  }
+  HostMat as[3] = {a, a, a};
+  std::vector<double> D;
+  host_ref(GEMM_FWD, M, N, K, nseg, as, b, D);
+  double me = 0, diff = 0;
+  for (int m = 0; m < M; ++m)
+    for (int n = 0; n < N; ++n) {
+      me = fmax(me, fabs(h[1][(size_t)m * ldo + n] - 0.5 * D[(size_t)m * N + n]));
+      diff = fmax(diff, fabs((double)h[1][(size_t)m * ldo + n] - (double)h[0][(size_t)m * ldo + n]));
+    }
+  char name[128];
+  snprintf(name, sizeof name, "bits fwd store M=%d N=%d K=%d nseg=%d split=%d", M, N, K, nseg, used_split);
+  report(name, me, 2e-3 * sqrt((double)K * nseg) * 0.1 + 1e-4);
+  // split-K sums partial tiles with red.add in arrival order: exact equality only without a split
+  report("   bits vs bf16 operand", diff, used_split > 1 ? 1e-3 : 0.0);
+  cudaFree(a.d); cudaFree(dbits);
+  for (int s = 0; s < nseg; ++s) cudaFree(b[s].d);
+}
+
+// FWD with the fused tanh epilogue (the unsplit first layer at small batch)
+static void test_bits_fwd_act(int M, int Nv, int K, int sms) {
+  const long long ldo = (Nv + 1 + 63) / 64 * 64;
+  HostMat a, b;
+  a.init(M, K, (K + 63) / 64 * 64, 1.f, true);
+  b.init(K, Nv, (Nv + 63) / 64 * 64, 0.05f);
+  const long long pitch = bits_pitch(GEMM_FWD, M, K);
+  uint32_t* dbits = pack_bits(a, pitch);
+  std::vector<__nv_bfloat16> h[2];
+  for (int v = 0; v < 2; ++v) {
+    __nv_bfloat16* dout;
+    CK(cudaMalloc(&dout, 2 * M * ldo));
+    CK(cudaMemset(dout, 0xFF, 2 * M * ldo));
+    GemmProblem p;
+    p.kind = GEMM_FWD; p.epi = EPI_ACT; p.M = M; p.K = K; p.N = (int)ldo; p.force_splitk = 1; p.block_n = 256;
+    p.a[0][0] = a.mat(); p.b[0][0] = b.mat();
+    if (v == 1) { p.a_bits = true; p.abits[0].base = dbits; p.abits[0].pitch = pitch; p.abits[0].rows = M; }
+    EpiArgs e = {};
+    e.out = dout; e.ld_out = ldo; e.alpha = 1.f; e.n_valid = Nv; e.act = ACT_TANH; e.precise = 1; e.aux_split = 1 << 30;
+    p.e[0] = e;
+    GemmPlan pl;
+    std::string err = gemm_plan(p, sms, &pl);
+    if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+    if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
+    CK(cudaDeviceSynchronize());
+    h[v].resize((size_t)M * ldo);
+    CK(cudaMemcpy(h[v].data(), dout, 2 * M * ldo, cudaMemcpyDeviceToHost));
+    cudaFree(dout);
+  }
+  double me = 0, diff = 0;
+  for (int m = 0; m < M; ++m)
+    for (int n = 0; n < (int)ldo; ++n) {
+      double acc = 0;
+      if (n < Nv) for (int k = 0; k < K; ++k) acc += (double)a.at(m, k) * b.at(k, n);
+      const double want = n < Nv ? tanh(acc) : (n == Nv ? 1.0 : 0.0);
+      me = fmax(me, fabs((double)__bfloat162float(h[1][(size_t)m * ldo + n]) - want));
+      diff = fmax(diff, fabs((double)__bfloat162float(h[1][(size_t)m * ldo + n]) - (double)__bfloat162float(h[0][(size_t)m * ldo + n])));
+    }
+  char name[128];
+  snprintf(name, sizeof name, "bits fwd tanh M=%d Nv=%d K=%d", M, Nv, K);
+  report(name, me, 4e-3);
+  report("   bits vs bf16 operand", diff, 0.0);
+  cudaFree(a.d); cudaFree(b.d); cudaFree(dbits);
+}
+
+// WGRAD, two groups reading overlapping row ranges of one packed matrix (the engine's [rot; lock; key] stack), with and
+// without appended problems that keep their bf16 A operand
+static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms) {
+  // X [3 Bp, M] binary; group 0 = rows [0, 2 Bp), group 1 = rows [Bp, 3 Bp); dY [4 Bp, N]: group 0 rows [0, 2 Bp), group 1 rows [2 Bp, 4 Bp)
+  const int K = 2 * Bp;
+  HostMat x, dy, xa[2], xb[2];
+  x.init(3LL * Bp, M, (M + 63) / 64 * 64, 1.f, true);
+  dy.init(4LL * Bp, N, (N + 63) / 64 * 64, 1.f);
+  const long long pitch = bits_pitch(GEMM_WGRAD, M, K);
+  uint32_t* dbits = pack_bits(x, pitch);
+  const long long ldo = 512;
+  const int xs[2][3] = {{501, 500, 256}, {130, 70, 192}};
+  if (extras)
+    for (int i = 0; i < 2; ++i) {
+      xa[i].init(xs[i][2], xs[i][0], (xs[i][0] + 63) / 64 * 64, 1.f);
+      xb[i].init(xs[i][2], xs[i][1], (xs[i][1] + 63) / 64 * 64, 1.f);
+    }
+  std::vector<float> h[2][2], hx[2][2];
+  for (int v = 0; v < 2; ++v) {
+    float* dout[2];
+    float* xout[2] = {nullptr, nullptr};
+    GemmProblem p;
+    p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K; p.block_n = 256;
+    p.force_splitk = 1;
+    for (int g = 0; g < 2; ++g) {
+      CK(cudaMalloc(&dout[g], sizeof(float) * M * ldo));
+      CK(cudaMemset(dout[g], 0xFF, sizeof(float) * M * ldo));
+      p.a[g][0] = Mat(x.d + (long long)g * Bp * x.ld, K, M, x.ld);
+      p.b[g][0] = Mat(dy.d + (long long)g * 2 * Bp * dy.ld, K, N, dy.ld);
+      if (v == 1) { p.a_bits = true; p.abits[g].base = dbits + (long long)g * Bp * pitch; p.abits[g].pitch = pitch; p.abits[g].rows = K; }
+      EpiArgs e = {};
+      e.out = dout[g]; e.ld_out = ldo; e.alpha = 1.f;
+      p.e[g] = e;
+    }
+    if (extras)
+      for (int i = 0; i < 2; ++i) {
+        CK(cudaMalloc(&xout[i], sizeof(float) * xs[i][0] * ldo));
+        CK(cudaMemset(xout[i], 0xFF, sizeof(float) * xs[i][0] * ldo));
+        GemmExtra e2;
+        e2.a[0] = xa[i].mat(); e2.b[0] = xb[i].mat(); e2.M = xs[i][0]; e2.N = xs[i][1]; e2.K = xs[i][2];
+        EpiArgs e = {};
+        e.out = xout[i]; e.ld_out = ldo; e.alpha = 2.f;
+        e2.e = e;
+        p.extra.push_back(e2);
+      }
+    GemmPlan pl;
+    std::string err = gemm_plan(p, sms, &pl);
+    if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+    if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
+    CK(cudaDeviceSynchronize());
+    for (int g = 0; g < 2; ++g) {
+      h[v][g].resize((size_t)M * ldo);
+      CK(cudaMemcpy(h[v][g].data(), dout[g], sizeof(float) * M * ldo, cudaMemcpyDeviceToHost));
+      cudaFree(dout[g]);
+    }
+    if (extras)
+      for (int i = 0; i < 2; ++i) {
+        hx[v][i].resize((size_t)xs[i][0] * ldo);
+        CK(cudaMemcpy(hx[v][i].data(), xout[i], sizeof(float) * xs[i][0] * ldo, cudaMemcpyDeviceToHost));
+        cudaFree(xout[i]);
+      }
+  }
+  double me = 0, diff = 0;
+  for (int g = 0; g < 2; ++g)
+    for (int m = 0; m < M; ++m)
+      for (int n = 0; n < N; ++n) {
+        double acc = 0;
+        for (int k = 0; k < K; ++k) acc += (double)x.at((long long)g * Bp + k, m) * dy.at((long long)g * 2 * Bp + k, n);
+        me = fmax(me, fabs(h[1][g][(size_t)m * ldo + n] - acc));
+        diff = fmax(diff, fabs((double)h[1][g][(size_t)m * ldo + n] - (double)h[0][g][(size_t)m * ldo + n]));
+      }
+  if (extras)
+    for (int i = 0; i < 2; ++i) {
+      std::vector<double> D;
+      host_ref(GEMM_WGRAD, xs[i][0], xs[i][1], xs[i][2], 1, &xa[i], &xb[i], D);
+      for (int r = 0; r < xs[i][0]; ++r)
+        for (int c = 0; c < xs[i][1]; ++c) {
+          me = fmax(me, fabs(hx[1][i][(size_t)r * ldo + c] - 2.0 * D[(size_t)r * xs[i][1] + c]));
+          diff = fmax(diff, fabs((double)hx[1][i][(size_t)r * ldo + c] - (double)hx[0][i][(size_t)r * ldo + c]));
+        }
+    }
+  char name[128];
+  snprintf(name, sizeof name, "bits wgrad 2 groups M=%d N=%d K=%d%s", M, N, K, extras ? " + 2 appended" : "");
+  report(name, me, 2e-3 * sqrt((double)K) * 0.1 * 2 + 1e-4);
+  report("   bits vs bf16 operand", diff, 0.0);
+  cudaFree(x.d); cudaFree(dy.d); cudaFree(dbits);
+  if (extras) for (int i = 0; i < 2; ++i) { cudaFree(xa[i].d); cudaFree(xb[i].d); }
+}
+
 static double sigm(double x) { return 1.0 / (1.0 + exp(-x)); }
 
 // ACT (fwd, optional two-pass), DACT (dgrad), BCE (fwd)
@@ -332,6 +534,13 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   }
   if (const char* d = getenv("MAGIC_EPI_DBG")) e.dbg = atoi(d);
   p.e[0] = e;
+  uint32_t* abits = nullptr;
+  if (g_bits) {
+    const long long pitch = bits_pitch(kind, M, K), rows = kind == GEMM_WGRAD ? K : M;
+    CK(cudaMalloc(&abits, sizeof(uint32_t) * rows * pitch));
+    CK(cudaMemset(abits, 0x5A, sizeof(uint32_t) * rows * pitch));
+    p.a_bits = true; p.abits[0].base = abits; p.abits[0].pitch = pitch; p.abits[0].rows = (int)rows; p.block_n = 256;
+  }
   GemmPlan pl;
   std::string err = gemm_plan(p, sms, &pl);
   if (!err.empty()) { printf("plan error: %s\n", err.c_str()); return; }
@@ -386,6 +595,7 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   printf("bench %-28s M=%d N=%d K=%d split=%d grid=%d: %.3f ms  %.1f TFLOP/s\n", label, M, N, K, pl.args.splitk, pl.grid,
          ms, 2.0 * M * N * K / ms * 1e-9);
   cudaFree(a); cudaFree(b); cudaFree(out);
+  if (abits) cudaFree(abits);
 }
 
 int main(int argc, char** argv) {
@@ -449,6 +659,15 @@ int main(int argc, char** argv) {
   test_fused(EPI_DACT, 5120, 500, 512, 1, 1, sms);
   test_fused(EPI_DACT, 512, 500, 4000, 5, 1, sms);
   g_bn = 0;
+  // A operand as packed bits: every A_BITS instantiation except the peer scatter (engine-level DP test)
+  test_bits_fwd_store(128, 256, 64, 1, 1, sms);
+  test_bits_fwd_store(300, 500, 1000, 1, 1, sms);
+  test_bits_fwd_store(300, 500, 1601, 2, 1, sms);
+  test_bits_fwd_store(1000, 500, 3000, 2, 3, sms);
+  test_bits_fwd_act(300, 500, 1601, sms);
+  test_bits_wgrad(700, 500, 96, false, sms);
+  test_bits_wgrad(1601, 120, 100, false, sms);
+  test_bits_wgrad(1601, 500, 256, true, sms);
   printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
   if (do_bench) {
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");
@@ -463,6 +682,11 @@ int main(int argc, char** argv) {
     bench(GEMM_DGRAD, 4096, 512, 40000, 0, sms, "dec out dgrad (auto split)");
     bench(GEMM_WGRAD, 512, 40000, 4096, 1, sms, "dec out wgrad");
     bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad");
+    g_bits = 1;
+    bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd, A as bits");
+    bench(GEMM_FWD, 12288, 512, 40064, 0, sms, "enc L0 fwd, A as bits (auto split)");
+    bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad, A as bits");
+    g_bits = 0;
     bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd");
     bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd, tanh epilogue", EPI_ACT);
     bench(GEMM_DGRAD, 16384, 512, 512, 1, sms, "hidden dgrad, tanh' epilogue", EPI_DACT);

@@ -154,3 +154,30 @@ def test_uint8_feed_equals_float_feed():
     l4, _ = eng.step(labels=yn, eps3=en, apply=False)
     np.testing.assert_allclose(l3.cpu().numpy(), l4.cpu().numpy(), rtol=1e-5)
     eng.close(); eng2.close()
+
+
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+def test_packed_first_layer_operand_matches_bf16_planes(precision, monkeypatch):
+    """The first layer's A operand is read as 1 bit per pixel and expanded inside the GEMM (default); with
+    MAGIC_BITS_A=0 the same GEMMs read bf16 planes through TMA.  Same products, same accumulators: losses, the batch
+    the generator exports and every gradient must agree to fp32 summation order (tile widths / split-K differ)."""
+    from magic_b200.engine import Engine
+    from tests.util import engine_config_from_oracle
+    ocfg = oracle_config(latent=20, encoder_neurons=[120, 72], decoder_neurons=[88, 104], n_input=1600)
+    runs = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("MAGIC_BITS_A", flag)
+        eng = Engine(engine_config_from_oracle(ocfg, 96, precision, seed=5))
+        eng.generate_batch(3, 7)
+        losses, dist = eng.step(apply=False, want_distance=True)
+        X, y = eng.export_batch()
+        grads = {(w, n): eng.get_grad(w, n) for w in (1, 2) for n in eng.param_names if eng.param_opts[n] & w}
+        runs.append((losses.cpu().numpy(), dist.cpu().numpy(), X.cpu().numpy(), y.cpu().numpy(), grads))
+        eng.close()
+    a, b = runs
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])          # the same generated batch
+    assert set(np.unique(a[2])) <= {0.0, 1.0} and a[2].sum() > 0
+    np.testing.assert_allclose(a[0], b[0], rtol=2e-5)
+    assert rel_l2(a[1], b[1]) < 2e-5
+    for k in a[4]:
+        assert rel_l2(a[4][k], b[4][k]) < 2e-5, k
