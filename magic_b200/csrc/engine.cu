@@ -640,7 +640,7 @@ std::string Engine::load_pairs_bits(const uint32_t* d_lock, const uint32_t* d_ke
   InBuf& b = in_[cur_ ^ 1];
   wait_ready(b);
   pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx,
-             bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, stream);
+             bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, num_sms, stream);
   b.planes_valid = !bits_a_;
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
@@ -677,7 +677,7 @@ std::string Engine::feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t*
   if (h_labels) MAGIC_CUDA(cudaMemcpyAsync(b.labels, h_labels, sizeof(float) * B, cudaMemcpyHostToDevice, gen_stream_));
   prof_begin("input.pairs_bits", 0, gen_stream_);
   pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx,
-             bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, gen_stream_);
+             bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, num_sms, gen_stream_);
   b.planes_valid = !bits_a_;
   prof_end(gen_stream_);
   MAGIC_CUDA(cudaGetLastError());

@@ -843,67 +843,100 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
 }
 
 // The same pipeline fed with bit-packed planes: lock / key are [B, wpr] 32-bit words, pixel p = bit (p & 31) of word
-// p >> 5 (the layout of xbits, numpy packbits(bitorder='little')): 10 KB per pair instead of 80 KB as uint8 or
-// 480 KB as the float32 array the reference feeds.  One CTA per (pair, 1024-column chunk), eight columns per thread
-// the lock's bitmap sits in shared memory for the rotated samples.  Output: one byte per plane into the packed rows
-// [rot; lock; key] of xb3 (bias column set; the GEMMs' A operand and the BCE target), and -- only when `planes` is given --
-// one 16-byte store per plane of expanded bf16.
+// p >> 5 (numpy packbits(bitorder='little')): 10 KB per pair instead of 80 KB as uint8 or 480 KB as the float32
+// array the reference feeds.  Persistent CTAs, one pair at a time: the lock's bitmap goes to shared memory, lock and
+// key words pass straight through to their packed rows of xb3 (tail bits masked, bias column set), and each warp
+// assembles 32 rotated pixels into one word with a ballot -- the generator's phase 2; the disc that bounds the lock
+// (outside of which the rotated plane is empty) is measured from the bitmap while it is loaded: the farthest set
+// pixel from the centre, in doubled coordinates.  Output is the packed rows only (the GEMMs' A operand and the BCE
+// target).
 constexpr int kPairsBitsMaxWords = 2048;      // side <= 256
-__global__ void __launch_bounds__(128) pairs_bits_kernel(const uint32_t* __restrict__ lock, const uint32_t* __restrict__ key,
-                                                         int wpr, int B, int side, uint64_t seed, uint64_t step,
-                                                         __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld,
-                                                         int* rot_cs_sn) {
-  __shared__ uint32_t bm[kPairsBitsMaxWords];
+// Same footprint as the generator (384 threads, at most 56 registers, one CTA per SM): three of its warps fit beside
+// the GEMM's warps in a sub-partition's 16 K registers, so it runs UNDER the step instead of making GEMM CTAs wait for
+// a persistent grid to drain (256 threads x 2 CTAs per SM did exactly that: 0.82 ms per batch, e2e 2.41 -> 2.58 ms).
+constexpr int kPairsBitsThreads = kGenThreads;
+__global__ void __maxnreg__(56) pairs_bits_kernel(const uint32_t* __restrict__ lock,
+                                                                       const uint32_t* __restrict__ key, int wpr, int B,
+                                                                       int side, uint32_t inv_side, uint64_t seed,
+                                                                       uint64_t step, uint32_t* xb3, int xb_ld,
+                                                                       int* rot_cs_sn) {
+  extern __shared__ uint32_t bm[];              // the lock's bitmap: nwords words (5 KB at 200 x 200)
   __shared__ int q14[2];
-  const int i = blockIdx.y, D = side * side;
-  const uint32_t* L = lock + (long long)i * wpr;
-  const uint32_t* K = key + (long long)i * wpr;
-  if (threadIdx.x == 0) {
-    float sn, cs;
-    sincospif(2.f * u01((uint32_t)rng_key(seed, step, 13, i)), &sn, &cs);   // same draw as generate_pairs_kernel
-    q14[0] = __float2int_rn(cs * 16384.f);
-    q14[1] = __float2int_rn(sn * 16384.f);
-    if (rot_cs_sn && blockIdx.x == 0) { rot_cs_sn[2 * i] = q14[0]; rot_cs_sn[2 * i + 1] = q14[1]; }
-  }
+  __shared__ int r2max;                         // max over the lock's pixels of (2x - W + 1)^2 + (2y - W + 1)^2
+  const int D = side * side;
   const int nwords = (D + 31) >> 5;
   const uint32_t tail = (D & 31) ? ((1u << (D & 31)) - 1u) : 0xffffffffu;     // bits past D in the last word are ignored
-  for (int w = threadIdx.x; w < nwords; w += blockDim.x) {
-    const uint32_t v = __ldg(L + w) & (w == nwords - 1 ? tail : 0xffffffffu);
-    bm[w] = v;
-  }
-  if (blockIdx.x == 0)        // words past the operand pitch (ld / 32 is a whole number of words: ld % 64 == 0)
-    for (int w = (int)(ld >> 5) + threadIdx.x; w < xb_ld; w += blockDim.x)
-      xb3[(long long)i * xb_ld + w] = xb3[(long long)(B + i) * xb_ld + w] = xb3[(long long)(2 * B + i) * xb_ld + w] = 0u;
-  __syncthreads();
-  const int cs = q14[0], sn = q14[1];
-  const int c0 = blockIdx.x * 1024 + threadIdx.x * 8;
-  if (c0 >= ld) return;
-  uint32_t bl = 0u, bk = 0u, br = 0u;
-  if (c0 < D) {
-    const int w = c0 >> 5, sh = c0 & 31;
-    bl = (bm[w] >> sh) & 255u;
-    bk = ((__ldg(K + w) & (w == nwords - 1 ? tail : 0xffffffffu)) >> sh) & 255u;
-    int y = c0 / side, x = c0 - y * side;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      if (c0 + j < D) br |= bit_at(bm, rotated_index(x, y, side, cs, sn)) << j;
-      if (++x == side) { x = 0; ++y; }
+  const int bias_w = D >> 5;
+  const uint32_t bias_b = 1u << (D & 31);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = blockIdx.x; i < B; i += gridDim.x) {
+    const uint32_t* L = lock + (long long)i * wpr;
+    const uint32_t* K = key + (long long)i * wpr;
+    uint32_t* orot = xb3 + (long long)i * xb_ld;
+    uint32_t* olock = xb3 + (long long)(B + i) * xb_ld;
+    uint32_t* okey = xb3 + (long long)(2 * B + i) * xb_ld;
+    if (threadIdx.x == 0) {
+      float sn, cs;
+      sincospif(2.f * u01((uint32_t)rng_key(seed, step, 13, i)), &sn, &cs);   // same draw as generate_pairs_kernel
+      q14[0] = __float2int_rn(cs * 16384.f);
+      q14[1] = __float2int_rn(sn * 16384.f);
+      if (rot_cs_sn) { rot_cs_sn[2 * i] = q14[0]; rot_cs_sn[2 * i + 1] = q14[1]; }
+      r2max = 0;
     }
-  }
-  if (D >= c0 && D < c0 + 8) { const uint32_t one = 1u << (D - c0); bl |= one; bk |= one; br |= one; }   // bias column
-  reinterpret_cast<uint8_t*>(xb3 + (long long)i * xb_ld)[c0 >> 3] = (uint8_t)br;
-  reinterpret_cast<uint8_t*>(xb3 + (long long)(B + i) * xb_ld)[c0 >> 3] = (uint8_t)bl;
-  reinterpret_cast<uint8_t*>(xb3 + (long long)(2 * B + i) * xb_ld)[c0 >> 3] = (uint8_t)bk;
-  if (planes) {
-    *reinterpret_cast<uint4*>(planes + (long long)i * ld + c0) = expand_byte(br);
-    *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + c0) = expand_byte(bl);
-    *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + c0) = expand_byte(bk);
+    __syncthreads();
+    int r2 = 0;
+    auto far = [&](int p) {
+      const int y = (int)__umulhi((uint32_t)p, inv_side), x = p - y * side;
+      const int X2 = 2 * x - side + 1, Y2 = 2 * y - side + 1;
+      r2 = max(r2, X2 * X2 + Y2 * Y2);
+    };
+    for (int w = threadIdx.x; w < xb_ld; w += kPairsBitsThreads) {
+      const uint32_t m = w == nwords - 1 ? tail : 0xffffffffu;
+      const uint32_t bias = w == bias_w ? bias_b : 0u;
+      const uint32_t vl = w < nwords ? __ldg(L + w) & m : 0u;
+      const uint32_t vk = w < nwords ? __ldg(K + w) & m : 0u;
+      if (w < nwords) bm[w] = vl;
+      olock[w] = vl | bias;
+      okey[w] = vk | bias;
+      orot[w] = bias;                           // the words inside the lock's disc are overwritten below
+      if (vl) {
+        const int p0 = w * 32;
+        const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
+        if (p0 - y0 * side + 31 < side) {       // one canvas row: the farthest set pixel is the first or the last one
+          far(p0 + __ffs(vl) - 1);
+          far(p0 + 31 - __clz(vl));
+        } else {                                // the word wraps onto the next row(s): look at every set pixel
+          for (uint32_t v = vl; v; v &= v - 1) far(p0 + __ffs(v) - 1);
+        }
+      }
+    }
+    if (r2) atomicMax(&r2max, r2);
+    __syncthreads();
+    const int cs = q14[0], sn = q14[1];
+    // rotation keeps the distance from the centre; nearest-neighbour rounding moves a sample by less than one pixel
+    const int rd = (int)ceilf(sqrtf((float)r2max)) + 4;               // doubled coordinates: + 2 pixels
+    const int lo = max(0, (side - 1 - rd) >> 1), hi = min(side - 1, (side + rd) >> 1);
+    const int w_begin = (lo * side) >> 5, w_end = min(nwords, ((hi * side + side - 1) >> 5) + 1);
+    for (int w = w_begin + warp; w < w_end; w += kPairsBitsThreads / 32) {
+      const int p0 = w * 32;
+      const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
+      const int x0 = p0 - y0 * side;
+      if (x0 + 31 < side && (x0 > hi || x0 + 31 < lo)) continue;      // whole word on one row, outside the disc's box
+      int x = x0 + lane, y = y0;
+      while (x >= side) { x -= side; ++y; }
+      const uint32_t bit = (p0 + lane < D) ? bit_at(bm, rotated_index(x, y, side, cs, sn)) : 0u;
+      const uint32_t word = __ballot_sync(0xffffffffu, bit != 0u);
+      if (lane == 0) orot[w] = word | (w == bias_w ? bias_b : 0u);
+    }
+    __syncthreads();                            // the bitmap is reused by the next pair
   }
 }
 void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
-                __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, cudaStream_t s) {
-  pairs_bits_kernel<<<dim3((unsigned)((ld + 1023) / 1024), B), 128, 0, s>>>(lock, key, wpr, B, side, seed, step, planes, ld, xb3,
-                                                                             xb_ld, rot_cs_sn);
+                __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, int max_ctas, cudaStream_t s) {
+  const uint32_t inv_side = (uint32_t)((0x100000000ull + (uint64_t)side - 1) / (uint64_t)side);
+  pairs_bits_kernel<<<B < max_ctas ? B : max_ctas, kPairsBitsThreads, sizeof(uint32_t) * (size_t)((side * side + 31) / 32), s>>>(lock, key, wpr, B, side, inv_side, seed, step, xb3,
+                                                                              xb_ld, rot_cs_sn);
+  if (planes) unpack_bits_planes(xb3, xb_ld, 3 * B, planes, ld, s);     // MAGIC_BITS_A=0: the bf16 planes as well
 }
 
 // bf16 {0,1} operand planes [rows, ld] -> packed rows xb[rows, xb_ld] with the bias column D set, for the loaders

@@ -103,7 +103,7 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
 // bit-packed pairs: pixel p = bit (p & 31) of word p >> 5 of the pair's row (wpr words per row); fills xb3 like the
 // generator, and `planes` when it is not null
 void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
-                __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, cudaStream_t s);
+                __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, int max_ctas, cudaStream_t s);
 void pack_planes_bits(const __nv_bfloat16* planes, long long ld, int rows, int D, uint32_t* xb, int xb_ld, cudaStream_t s);
 void unpack_bits_planes(const uint32_t* xb, int xb_ld, int rows, __nv_bfloat16* planes, long long ld, cudaStream_t s);
 
