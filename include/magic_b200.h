@@ -130,6 +130,16 @@ int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn);
  * get_predictions, as 8c/main.py:66-80 does with its test batch; bench.py alternates two resident batches with it. */
 int magic_swap_batch(magic_handle* h);
 
+/* The images are binary and mostly empty (8.5 % of the pixels set, shapes near the canvas centre: README.md:19-27,
+ * overlap_micro.zip), and the first encoder layer -- 8c/vae.py:347, 3 of the 4 largest matrix products of the step with
+ * its weight gradient -- multiplies them.  The engine keeps them packed (1 bit per pixel) and skips every 128 x 64
+ * operand stage without a set pixel: such a stage adds exact zeros, so results are bit-identical to processing it.
+ *   magic_set_option(h, "skip_zero_stages", 0)  processes every stage (dense-input timing; default 1)
+ *   magic_input_density                          fraction of stages with a set pixel in the loaded batch:
+ *                                                out2[0] forward GEMM, out2[1] weight-gradient GEMM (synchronises) */
+int magic_set_option(magic_handle* h, const char* name, int32_t value);
+int magic_input_density(magic_handle* h, double* out2);
+
 /* TangoEncoder.partial_fit (8c/vae.py:379-405; 6-tuple variant 11a/vae.py:385-411) on the loaded batch:
  * forward, both backward passes at the pre-step weights, both Adam updates (W <- W - d1 - d2).
  *   d_labels : [B] overlap areas, or NULL to use the generated labels

@@ -66,6 +66,8 @@ SIGNATURES = {
     "magic_export_batch": (C.c_int, [_VP, _VP, _VP]),
     "magic_export_rotation": (C.c_int, [_VP, _VP]),
     "magic_swap_batch": (C.c_int, [_VP]),
+    "magic_set_option": (C.c_int, [_VP, C.c_char_p, C.c_int32]),
+    "magic_input_density": (C.c_int, [_VP, C.POINTER(C.c_double)]),
     "magic_step": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "magic_step_grads_only": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "magic_partial_fit_host": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),

@@ -166,6 +166,14 @@ int magic_swap_batch(magic_handle* h) {
   CHECK_HANDLE(h);
   return done(h->eng.swap_batch());
 }
+int magic_set_option(magic_handle* h, const char* name, int32_t value) {
+  CHECK_HANDLE(h);
+  return done(h->eng.set_option(name, value));
+}
+int magic_input_density(magic_handle* h, double* out2) {
+  CHECK_HANDLE(h);
+  return done(h->eng.input_density(out2));
+}
 int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn) {
   CHECK_HANDLE(h);
   return done(h->eng.export_rotation(d_cs_sn));

@@ -117,7 +117,7 @@ Engine::~Engine() {
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
                   statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
-                  in_[0].xb3, in_[1].xb3, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_};
+                  in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
@@ -272,11 +272,21 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   // gradient (both reach past column D, the bias column, into zero padding)
   xb_ld_ = (int)round_up(4 * ((D + 1 + 127) / 128), 8);
   if (const char* ba = getenv("MAGIC_BITS_A")) bits_a_ = atoi(ba) != 0;
+  if (const char* sz = getenv("MAGIC_SKIP_ZERO")) skip_zero_ = atoi(sz) != 0;
+  km_fwd_tiles_ = (3 * B + 127) / 128;
+  km_fwd_kb_ = (D + 1 + 63) / 64;
+  km_fwd_words_ = (km_fwd_kb_ + 31) / 32;
+  km_wg_tiles_ = (D + 1 + 127) / 128;
+  km_wg_words_ = ((2 * B + 63) / 64 + 31) / 32;
+  km_wg_off_[0] = (size_t)round_up((long long)km_fwd_tiles_ * km_fwd_words_, 4);
+  km_wg_off_[1] = km_wg_off_[0] + (size_t)round_up((long long)km_wg_tiles_ * km_wg_words_, 4);
+  km_total_ = km_wg_off_[1] + (size_t)round_up((long long)km_wg_tiles_ * km_wg_words_, 4);
   for (auto& b : in_) {
     MAGIC_TRY(alloc_act(&b.X, 3LL * B, D + 1));
     if (b.X.lo) { cudaFree(b.X.lo); stats.hbm_bytes -= (int64_t)(sizeof(bf16) * b.X.rows * b.X.ld); b.X.lo = nullptr; }  // pixels are exact in bf16
     MAGIC_TRY(alloc((void**)&b.xb3, sizeof(uint32_t) * 3 * (size_t)B * xb_ld_));
     b.xbits = b.xb3 + (size_t)B * xb_ld_;
+    MAGIC_TRY(alloc((void**)&b.kmask, sizeof(uint32_t) * km_total_));
     MAGIC_TRY(alloc((void**)&b.rot, sizeof(int) * 2 * (size_t)B));
     MAGIC_TRY(alloc((void**)&b.labels, sizeof(float) * B));
     MAGIC_CUDA(cudaEventCreateWithFlags(&b.ready, cudaEventDisableTiming));
@@ -386,6 +396,7 @@ std::string Engine::build_plans() {
       if (i == 0 && bits_a_) {   // the images stay packed in HBM: 1 KiB instead of 16 KiB per 128 x 64 stage
         p.a_bits = true;
         p.abits[0].base = in_[alt].xb3; p.abits[0].pitch = xb_ld_; p.abits[0].rows = 3 * B;
+        p.kmask[0] = in_[alt].kmask; p.kmask_words = km_fwd_words_;
       }
       MAGIC_TRY(finish(p, alt == 0 ? &fwd_enc_[i] : &fwd_enc0_alt_, "fwd enc"));
       if (alt == 1) flops -= fwd_enc0_alt_.flops;
@@ -486,6 +497,8 @@ std::string Engine::build_plans() {
       p.a_bits = true;
       p.abits[0].base = xb; p.abits[0].pitch = xb_ld_; p.abits[0].rows = 2 * B;
       p.abits[1].base = xb + (size_t)B * xb_ld_; p.abits[1].pitch = xb_ld_; p.abits[1].rows = 2 * B;
+      const uint32_t* km = xb == in_[0].xb3 ? in_[0].kmask : in_[1].kmask;
+      p.kmask[0] = km + km_wg_off_[0]; p.kmask[1] = km + km_wg_off_[1]; p.kmask_words = km_wg_words_;
     }
     // optimiser 1 (cost): x rows [rot; lock] = [0, 2B), dy rows [0, 2B).  optimiser 2 (metric): x rows [lock; key] =
     // [B, 3B), dy rows [2B, 4B).
@@ -573,6 +586,7 @@ std::string Engine::load_interleaved(const float* d_x) {
   prof_begin("input.deinterleave");
   deinterleave_f32(d_x, B, D, b.X.hi, b.X.ld, stream);
   pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  build_kmasks(b, stream);
   b.planes_valid = true;
   prof_end();
   MAGIC_CUDA(cudaGetLastError());
@@ -590,6 +604,7 @@ std::string Engine::load_interleaved_u8(const uint8_t* d_x) {
   prof_begin("input.deinterleave");
   deinterleave_u8(d_x, B, D, b.X.hi, b.X.ld, stream);
   pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  build_kmasks(b, stream);
   b.planes_valid = true;
   prof_end();
   MAGIC_CUDA(cudaGetLastError());
@@ -606,6 +621,7 @@ std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uin
   wait_ready(b);
   planar_u8(l, r, k, B, D, b.X.hi, b.X.ld, stream);
   pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  build_kmasks(b, stream);
   b.planes_valid = true;
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
@@ -623,6 +639,7 @@ std::string Engine::load_pairs_u8(const uint8_t* d_lock, const uint8_t* d_key, u
   wait_ready(b);
   pairs_u8(d_lock, d_key, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, b.X.hi, b.X.ld, b.rot, stream);
   pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
+  build_kmasks(b, stream);
   b.planes_valid = true;
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
@@ -641,6 +658,7 @@ std::string Engine::load_pairs_bits(const uint32_t* d_lock, const uint32_t* d_ke
   wait_ready(b);
   pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx,
              bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, num_sms, stream);
+  build_kmasks(b, stream);
   b.planes_valid = !bits_a_;
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
@@ -678,6 +696,7 @@ std::string Engine::feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t*
   prof_begin("input.pairs_bits", 0, gen_stream_);
   pairs_bits(d_lock, d_key, wpr, B, side, seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx,
              bits_a_ ? nullptr : b.X.hi, b.X.ld, b.xb3, xb_ld_, b.rot, num_sms, gen_stream_);
+  build_kmasks(b, gen_stream_);
   b.planes_valid = !bits_a_;
   prof_end(gen_stream_);
   MAGIC_CUDA(cudaGetLastError());
@@ -702,6 +721,7 @@ std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
   prof_begin("input.generate", 0, gen_stream_);
   generate_pairs(seed + 0x9E3779B97F4A7C15ull * (uint64_t)cfg.rank, step_idx, B, side, bits_a_ ? nullptr : b.X.hi, b.X.ld,
                  b.xb3, xb_ld_, b.labels, b.rot, num_sms, gen_stream_);
+  build_kmasks(b, gen_stream_);
   b.planes_valid = !bits_a_;
   prof_end(gen_stream_);
   MAGIC_CUDA(cudaGetLastError());
@@ -743,6 +763,48 @@ std::string Engine::export_batch(float* d_x, float* d_labels) {
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   return "";
+}
+
+// Which 128 x 64 stages of the packed rows hold a set pixel, for the forward GEMM and for the two weight-gradient
+// groups (rows [0, 2B) and [B, 3B)).  Runs behind whatever wrote the packed rows, on the same stream.
+void Engine::build_kmasks(InBuf& b, cudaStream_t s) {
+  if (!bits_a_) return;
+  prof_begin("input.kmask", 0, s);
+  build_kmask_fwd(b.xb3, xb_ld_, 3 * B, km_fwd_kb_, b.kmask, km_fwd_words_, s);
+  for (int g = 0; g < 2; ++g)
+    build_kmask_wgrad(b.xb3 + (size_t)g * B * xb_ld_, xb_ld_, 2 * B, km_wg_tiles_, b.kmask + km_wg_off_[g], km_wg_words_, s);
+  prof_end(s);
+}
+std::string Engine::set_option(const char* name, int value) {
+  if (!name) return "set_option: null name";
+  if (std::string(name) == "skip_zero_stages") { skip_zero_ = value != 0; return ""; }
+  return std::string("set_option: unknown option ") + name;
+}
+std::string Engine::input_density(double* out2) {
+  if (!out2) return "input_density: null output";
+  out2[0] = out2[1] = 1.0;
+  if (!bits_a_) return "";
+  InBuf& b = in_[cur_];
+  if (!b.filled) return "input_density: no batch loaded";
+  wait_ready(b);
+  std::vector<uint32_t> h(km_total_);
+  MAGIC_CUDA(cudaMemcpyAsync(h.data(), b.kmask, sizeof(uint32_t) * km_total_, cudaMemcpyDeviceToHost, stream));
+  MAGIC_CUDA(cudaStreamSynchronize(stream));
+  long long set = 0;
+  for (size_t i = 0; i < (size_t)km_fwd_tiles_ * km_fwd_words_; ++i) set += __builtin_popcount(h[i]);
+  out2[0] = (double)set / ((double)km_fwd_tiles_ * km_fwd_kb_);
+  set = 0;
+  for (int g = 0; g < 2; ++g)
+    for (size_t i = 0; i < (size_t)km_wg_tiles_ * km_wg_words_; ++i) set += __builtin_popcount(h[km_wg_off_[g] + i]);
+  out2[1] = (double)set / (2.0 * km_wg_tiles_ * ((2 * B + 63) / 64));
+  return "";
+}
+// The first layer's plans carry their zero-stage maps; with the option off they run without (every stage processed).
+std::string Engine::launch_maybe_dense(GemmPlan& pl, int* launches, const char* tag) {
+  if (skip_zero_ || pl.args.kmask[0] == nullptr) return launch(pl, launches, tag);
+  GemmPlan dense = pl;
+  for (auto& k : dense.args.kmask) k = nullptr;
+  return launch(dense, launches, tag);
 }
 
 // ------------------------------------------------------------------ step
@@ -836,8 +898,8 @@ std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) 
   InBuf& ib = in_[cur_];
   wait_ready(ib);
   for (int i = 0; i <= E; ++i)
-    MAGIC_TRY(launch(i == 0 && cur_ == 1 ? fwd_enc0_alt_ : fwd_enc_[i], launches,
-                     i == 0 ? "gemm.fwd_enc0" : (i == E ? "gemm.fwd_heads" : "gemm.fwd_enc_hidden")));
+    MAGIC_TRY(launch_maybe_dense(i == 0 && cur_ == 1 ? fwd_enc0_alt_ : fwd_enc_[i], launches,
+                                 i == 0 ? "gemm.fwd_enc0" : (i == E ? "gemm.fwd_heads" : "gemm.fwd_enc_hidden")));
   const float* labels = have_labels_ext_ ? labels_ext_ : ib.labels;
   LatentArgs la = latent_args(d_eps3, labels);
   prof_begin("latent.forward"); latent_forward(la, stream); prof_end();
@@ -924,8 +986,8 @@ std::string Engine::run_backward(int* launches) {
     prof_end();
     *launches += 2;
   }
-  MAGIC_TRY(launch(dp_fused_ ? pl_wg_enc0_sc_[cur_] : fw ? pl_wg_enc0_fused_[cur_] : (cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0]),
-                   launches, "gemm.wgrad_enc0"));
+  MAGIC_TRY(launch_maybe_dense(dp_fused_ ? pl_wg_enc0_sc_[cur_] : fw ? pl_wg_enc0_fused_[cur_] : (cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0]),
+                               launches, "gemm.wgrad_enc0"));
   mark_consumed(in_[cur_]);                 // last read of the input buffer in the step
   if (dp) {   // bucket 2: the two 40000-wide first-layer gradients
     MAGIC_CUDA(cudaEventRecord(ev_bwd_[2], stream));
@@ -1152,6 +1214,7 @@ std::string Engine::build_dp_plans() {
       p.a_bits = true;
       p.abits[0].base = in_[alt].xb3; p.abits[0].pitch = xb_ld_; p.abits[0].rows = 2 * B;
       p.abits[1].base = in_[alt].xb3 + (size_t)B * xb_ld_; p.abits[1].pitch = xb_ld_; p.abits[1].rows = 2 * B;
+      p.kmask[0] = in_[alt].kmask + km_wg_off_[0]; p.kmask[1] = in_[alt].kmask + km_wg_off_[1]; p.kmask_words = km_wg_words_;
     }
     std::string err = gemm_plan(p, num_sms, &pl_wg_enc0_sc_[alt]);
     if (!err.empty()) return "dp wgrad enc0: " + err;

@@ -60,6 +60,8 @@ class Engine {
                                float* h_losses5, float* h_distance);
   std::string forward(int what, const float* d_eps3, float* d_out);
   std::string decode(const float* d_z, float* d_out);
+  std::string set_option(const char* name, int value);
+  std::string input_density(double* out2);    // fraction of operand stages with a set pixel: [forward, weight gradient]
   std::string comm_init(const void* uid);
   // Fused data parallelism over peer memory: every rank exports CUDA IPC handles of its gradient
   // staging buffer and shadow weights (kPeerBlobBytes each), the host framework all-gathers them, every rank imports.
@@ -122,6 +124,7 @@ class Engine {
     uint32_t* xb3 = nullptr;        // [3B, xb_ld] the same rows packed 1 bit per pixel, bias column set: the first layer's A operand
     uint32_t* xbits = nullptr;      // = xb3 + B * xb_ld: the packed lock plane, the BCE epilogue's target
     bool planes_valid = false;      // X holds this batch too (false when a loader only wrote the packed rows)
+    uint32_t* kmask = nullptr;      // zero-stage maps of xb3: [fwd | wgrad group 0 | wgrad group 1] (GemmArgs.kmask)
     float* labels = nullptr;        // [B] generated overlap labels
     int* rot = nullptr;             // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
     cudaEvent_t ready = nullptr, consumed = nullptr;
@@ -131,6 +134,12 @@ class Engine {
   int cur_ = 0;
   int xb_ld_ = 0;
   bool bits_a_ = true;              // first-layer GEMMs read the packed rows (BitsA); MAGIC_BITS_A=0: the bf16 planes
+  bool skip_zero_ = true;           // ... and skip operand stages without a set pixel (MAGIC_SKIP_ZERO=0 / set_option: all stages)
+  int km_fwd_tiles_ = 0, km_fwd_words_ = 0, km_fwd_kb_ = 0;     // map geometry: forward (rows of 128 packed rows x k-blocks of 64 pixels)
+  int km_wg_tiles_ = 0, km_wg_words_ = 0;                       // weight gradient (tiles of 128 pixels x k-blocks of 64 batch rows)
+  size_t km_wg_off_[2] = {0, 0}, km_total_ = 0;                 // word offsets of the two groups' maps; total words
+  void build_kmasks(InBuf& b, cudaStream_t s);
+  std::string launch_maybe_dense(GemmPlan& pl, int* launches, const char* tag);
   cudaStream_t gen_stream_ = nullptr;
   cudaEvent_t ev_gate_ = nullptr;   // recorded after the forward pass: earliest start of the next batch's generator
   bool gate_pending_ = false, gen_gate_ = true;

@@ -264,6 +264,14 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
     }
   GemmArgs& a = pl.args;
   for (int g = 0; g < p.ngroups; ++g) a.abits[g] = p.abits[g];
+  if (p.a_bits && p.kmask[0] != nullptr) {
+    if (p.kmask_words * 32 < (p.K + kBlockK - 1) / kBlockK) return "kmask: rows shorter than the number of k-blocks";
+    for (int g = 0; g < p.ngroups; ++g) {
+      if (!p.kmask[g]) return "kmask: every group needs its map";
+      a.kmask[g] = p.kmask[g];
+    }
+    a.kmask_words = p.kmask_words;
+  }
   a.M = p.M;
   a.N = p.N;
   a.kblocks = (p.K + kBlockK - 1) / kBlockK;

@@ -65,6 +65,9 @@ struct GemmProblem {
   // nseg = 2 the segments are (A, B_hi), (A, B_lo).  Only b[g][*] is read from the problem; 256-wide tiles.
   bool a_bits = false;
   BitsA abits[kMaxGroups] = {};
+  // optional zero-stage map of that operand (GemmArgs.kmask): kmask[g][tile_m * kmask_words + (kk >> 5)] bit kk & 31
+  const uint32_t* kmask[kMaxGroups] = {};
+  int kmask_words = 0;
 };
 
 // Returns empty string on success, else an error message.

@@ -144,11 +144,19 @@ struct GemmArgs {
   long long* trace;  // diagnostics: [grid][64] clock64 stamps of the phases of each CTA (selftest "trace"), or nullptr
   CUtensorMap tout[kMaxGroups][2];   // output tiles (box 32 cols x 32 rows): [g][0] fp32 or bf16 hi plane, [g][1] lo plane
   BitsA abits[kMaxGroups];           // A_BITS kernels: the main problem's A operand (extras keep bf16 A through TMA)
+  // Zero-stage map of the main problem's A operand (A_BITS kernels; null = none): bit kk of row (m0 / 128) of group g's
+  // map says "k-block kk of this M tile holds at least one set pixel".  A stage whose 128 x 64 pixels are all zero adds
+  // exact zeros to the accumulator, so it is neither fetched (B) nor expanded (A) nor multiplied.  With a map the
+  // split-K slices interleave (slice s takes k-blocks s, s + splitk, ...), so that every slice sees the same mix of the
+  // images' empty margins and busy centres.
+  const uint32_t* kmask[kMaxGroups];
+  int kmask_words;                   // words per map row
 };
 
 struct WorkItem {
   int g;             // group of the main problem, or -1 - e for extra problem e
   int m0, n0, kb0, kb1;
+  int kstep;         // k-blocks kb0, kb0 + kstep, ... < kb1 (1 unless the split-K slices interleave)
   int M, N, kblocks; // of the problem this item belongs to
 };
 
@@ -167,6 +175,7 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int cr
     it.n0 = (l % a.x_tn[e]) * a.bn;
     it.kb0 = 0;
     it.kb1 = a.nseg * a.x_kb[e];
+    it.kstep = 1;
     it.M = a.x_m[e]; it.N = a.x_n[e]; it.kblocks = a.x_kb[e];
     return it;
   }
@@ -184,12 +193,51 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int cr
   int ks = t / a.ngroups;
   int total_kb = a.nseg * a.kblocks;
   int per = (total_kb + a.splitk - 1) / a.splitk;
-  it.kb0 = ks * per;
-  it.kb1 = min(total_kb, it.kb0 + per);
+  if (a.kmask[0] != nullptr && a.splitk > 1) {       // interleaved slices (see GemmArgs.kmask)
+    it.kb0 = ks; it.kb1 = total_kb; it.kstep = a.splitk;
+  } else {
+    it.kb0 = ks * per;
+    it.kb1 = min(total_kb, it.kb0 + per);
+    it.kstep = 1;
+  }
   it.m0 = mt * kBlockM;
   it.n0 = nt * a.bn;
   return it;
 }
+
+// The k-blocks one work item processes, in order: every kstep-th block of [kb0, kb1) whose bit is set in the item's
+// zero-stage map row (all of them without a map).  Producer, expanders and MMA issuer each walk the same sequence, so
+// a skipped block consumes no pipeline stage.  An item without any set block still runs its first block (an all-zero
+// A stage): the accumulator must be written before the epilogue reads it.
+struct KbWalk {
+  const uint32_t* mrow;
+  int kb, kb1, kstep, kblocks;
+  int cw;            // index of the map word held in cv (-1: none): one load per 32 candidate blocks, not one per test
+  uint32_t cv;
+  bool forced;
+  __device__ __forceinline__ bool set(int k) {
+    while (k >= kblocks) k -= kblocks;                  // the map is per k-block inside a precision segment
+    const int w = k >> 5;
+    if (w != cw) { cv = __ldg(mrow + w); cw = w; }
+    return (cv >> (k & 31)) & 1u;
+  }
+  __device__ __forceinline__ void begin(const GemmArgs& a, const WorkItem& it) {
+    mrow = (it.g >= 0 && a.kmask[it.g] != nullptr) ? a.kmask[it.g] + (long long)(it.m0 / kBlockM) * a.kmask_words : nullptr;
+    kb = it.kb0; kb1 = it.kb1; kstep = it.kstep; kblocks = it.kblocks;
+    cw = -1; cv = 0u;
+    forced = false;
+    if (mrow) {
+      while (kb < kb1 && !set(kb)) kb += kstep;
+      if (kb >= kb1) { kb = it.kb0; forced = true; }
+    }
+  }
+  __device__ __forceinline__ bool done() const { return kb >= kb1; }
+  __device__ __forceinline__ void step() {
+    if (forced) { kb = kb1; return; }
+    kb += kstep;
+    if (mrow) while (kb < kb1 && !set(kb)) kb += kstep;
+  }
+};
 
 // ---------------------------------------------------------------------------- epilogue math
 // ACT / PRECISE are compile-time: a run-time branch inside the per-element loops would stop ptxas from
@@ -589,7 +637,11 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
   uint64_t* empty_bar = bars + kNS;
   uint64_t* tfull_bar = bars + 2 * kNS;
   uint64_t* tempty_bar = bars + 2 * kNS + kAcc;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kNS + 2 * kAcc);   // (2*6 + 2*4) * 8 + 4 <= 256 bytes
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kNS + 2 * kAcc);   // (2*6 + 2*4) * 8 + 4 <= 192 bytes
+  // per pipeline stage: 1 = "last k-block of its work item", written by the producer before it arms the stage's
+  // barrier and read by the MMA issuer after that barrier completes -- the issuer needs nothing else to know about the
+  // work list (no item decoding, no zero-stage map walk on the thread whose issue rate paces the tensor pipe)
+  volatile uint32_t* stage_last = reinterpret_cast<volatile uint32_t*>(bars + 24);   // byte 192 .. 216 of the 256
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -634,10 +686,16 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       uint32_t stage = 0, phase = 0;
       for (int w = work0; w < total_work; w += work_stride) {
         const WorkItem it = decode_work(args, w, crank);
-        for (int kb = it.kb0; kb < it.kb1; ++kb) {
+        KbWalk walk;
+        bool first_kb = true;
+        walk.begin(args, it);
+        while (!walk.done()) {
+          const int kb = walk.kb;
+          walk.step();                                  // one ahead: is this the item's last block?
           const int seg = kb / it.kblocks;
           const int k0 = (kb - seg * it.kblocks) * kBlockK;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          stage_last[stage] = walk.done() ? 1u : 0u;
           const bool a_by_tma = !A_BITS || it.g < 0;   // A_BITS: the main problem's A stage is written by the expander warps
           ptx::mbar_expect_tx(&full_bar[stage], a_by_tma ? Cfg::kBytes : Cfg::kBytesB);
           uint8_t* sa = smem_a + stage * kStageBytesA;
@@ -661,7 +719,8 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
             ptx::tma_load_3d_multicast(tb, &full_bar[stage], sb + crank * per * kAtomBytes, 0, k0,
                                        (it.n0 >> 6) + crank * per, cmask);
           }
-          if (w == work0 && kb == it.kb0) MAGIC_TR(3);
+          if (w == work0 && first_kb) MAGIC_TR(3);
+          first_kb = false;
           if (++stage == kNS) { stage = 0; phase ^= 1; }
         }
       }
@@ -675,32 +734,41 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       //                 K advance = 16 rows * 128 B.
       constexpr uint32_t a_lbo = A_MN ? kAtomBytes : 0, b_lbo = B_MN ? kAtomBytes : 0;
       constexpr uint32_t a_kadv = A_MN ? kUmmaK * 128 : kUmmaK * 2, b_kadv = B_MN ? kUmmaK * 128 : kUmmaK * 2;
+      // Descriptors: everything but the start address is constant; the k advance adds to the 14-bit start-address
+      // field (address >> 4), which cannot carry out of it (shared memory ends below 256 KiB).
+      constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+      constexpr uint32_t a_lo_c = ((a_lbo >> 4) & 0x3FFFu) << 16, b_lo_c = ((b_lbo >> 4) & 0x3FFFu) << 16;
+      // (the mask drops the window bits a shared-memory address carries above its 18-bit offset in a cluster launch)
+      const uint32_t a_addr0 = (ptx::smem_u32(smem_a) >> 4) & 0x3FFFu, b_addr0 = (ptx::smem_u32(smem_b) >> 4) & 0x3FFFu;
+      const int n_items = work0 < total_work ? (total_work - work0 + work_stride - 1) / work_stride : 0;
       uint32_t stage = 0, phase = 0, iter = 0;
-      for (int w = work0; w < total_work; w += work_stride, ++iter) {
-        const WorkItem it = decode_work(args, w, crank);
+      for (; (int)iter < n_items; ++iter) {
         const uint32_t acc = iter % kAcc, acc_phase = (iter / kAcc) & 1;
         ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
         if (iter < 8) MAGIC_TR(16 + iter * 5 + 0);
         const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kb = it.kb0; kb < it.kb1; ++kb) {
+        bool first_kb = true, last_kb;
+        do {                                              // every work item has at least one k-block (planner, KbWalk)
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          if (w == work0 && kb == it.kb0) MAGIC_TR(4);
-          const uint32_t a_base = ptx::smem_u32(smem_a + stage * kStageBytesA);
-          const uint32_t b_base = ptx::smem_u32(smem_b + stage * Cfg::kBytesB);
+          last_kb = stage_last[stage] != 0u;
+          if (iter == 0 && first_kb) MAGIC_TR(4);
+          const uint32_t a_lo = (a_addr0 + stage * (kStageBytesA >> 4)) | a_lo_c;
+          const uint32_t b_lo = (b_addr0 + stage * (Cfg::kBytesB >> 4)) | b_lo_c;
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            const uint64_t da = ptx::make_smem_desc_sw128(a_base + k * a_kadv, a_lbo, 1024);
-            const uint64_t db = ptx::make_smem_desc_sw128(b_base + k * b_kadv, b_lbo, 1024);
-            ptx::umma_bf16(d_tmem, da, db, idesc, (kb > it.kb0 || k > 0) ? 1u : 0u);
+            const uint64_t da = (static_cast<uint64_t>(desc_hi) << 32) | (a_lo + k * (a_kadv >> 4));
+            const uint64_t db = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + k * (b_kadv >> 4));
+            ptx::umma_bf16(d_tmem, da, db, idesc, (!first_kb || k > 0) ? 1u : 0u);
           }
           if (CM > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
           else ptx::umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
           if (++stage == kNS) { stage = 0; phase ^= 1; }
-        }
+          first_kb = false;
+        } while (!last_kb);
         ptx::umma_commit(&tfull_bar[acc]);        // accumulator complete -> epilogue
-        if (w == work0) MAGIC_TR(5);
+        if (iter == 0) MAGIC_TR(5);
         if (iter < 8) MAGIC_TR(16 + iter * 5 + 1);
       }
       MAGIC_TR(6);
@@ -826,25 +894,20 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     // this kernel's 112 registers, and one warp per stage already keeps up with the MMAs: profiles/r01p)
     static_assert(kNS == kExpandWarps, "expander warp e serves pipeline stage e");
     const int ew = warp - (2 + epi_warps(EPI));
-    struct Cursor { int w, kb, kb1, kblocks, m0, g; bool valid; };
+    struct Cursor { KbWalk walk; int w, m0, g; bool valid; };
     auto open = [&](Cursor& c) {
       c.valid = false;
       while (c.w < total_work) {
         const WorkItem it = decode_work(args, c.w, 0);
-        if (it.kb0 < it.kb1) {
-          c.kb = it.kb0; c.kb1 = it.kb1; c.kblocks = it.kblocks; c.m0 = it.m0; c.g = it.g; c.valid = true;
-          return;
-        }
+        c.walk.begin(args, it);
+        if (!c.walk.done()) { c.m0 = it.m0; c.g = it.g; c.valid = true; return; }
         c.w += work_stride;
       }
     };
     auto advance = [&](Cursor& c, int n) {       // n k-blocks further along the CTA's sequence of (work item, k-block)
-      while (c.valid && n > 0) {
-        const int left = c.kb1 - c.kb;
-        if (n < left) { c.kb += n; return; }
-        n -= left;
-        c.w += work_stride;
-        open(c);
+      for (; c.valid && n > 0; --n) {
+        c.walk.step();
+        if (c.walk.done()) { c.w += work_stride; open(c); }
       }
     };
     auto fetch = [&](const Cursor& c, uint2 (&v)[4]) {
@@ -852,8 +915,8 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       for (int q = 0; q < 4; ++q) v[q] = make_uint2(0u, 0u);
       if (c.valid && c.g >= 0) {
         const BitsA& ba = args.abits[c.g];
-        int kk = c.kb;
-        while (kk >= c.kblocks) kk -= c.kblocks;          // k-block inside its precision segment: every segment reads the same A
+        int kk = c.walk.kb;
+        while (kk >= c.walk.kblocks) kk -= c.walk.kblocks;   // k-block inside its precision segment: every segment reads the same A
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int r = lane + 32 * q;
@@ -877,7 +940,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     while (cur.valid) {
       fetch(pre, nxt);
       ptx::mbar_wait(&empty_bar[ew], phase ^ 1);          // the MMAs that read this stage have retired
-      if (cur.g >= 0) {
+      if (cur.g >= 0 && !(args.epi[0].dbg & 8)) {     // dbg 8: timing experiment, the stage is left as it is
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           uint8_t* dst = stage_base + q * (32 * 128);

@@ -972,6 +972,58 @@ void unpack_bits_planes(const uint32_t* xb, int xb_ld, int rows, __nv_bfloat16* 
 }
 
 
+// ------------------------------------------------------------------ zero-stage maps of the packed input rows
+// (GemmArgs.kmask, gemm_sm100.cuh.)  Forward GEMM: M tile t = packed rows [128 t, 128 t + 128), k-block kk = pixels
+// [64 kk, 64 kk + 64) = words 2 kk, 2 kk + 1; lane <-> k-block, so a warp reads 256 contiguous bytes per row.
+__global__ void __launch_bounds__(256) kmask_fwd_kernel(const uint32_t* __restrict__ xb, int xb_ld, int rows, int kblocks,
+                                                        uint32_t* mask, int mwords, int tiles) {
+  const int gw = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (gw >= tiles * mwords) return;
+  const int t = gw / mwords, j = gw % mwords;
+  const int kk = 32 * j + lane;
+  uint32_t acc = 0u;
+  if (kk < kblocks) {
+    const int r1 = min(rows, t * 128 + 128);
+#pragma unroll 8
+    for (int r = t * 128; r < r1; ++r) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(xb + (long long)r * xb_ld + 2 * kk));
+      acc |= v.x | v.y;
+    }
+  }
+  const uint32_t word = __ballot_sync(0xffffffffu, acc != 0u);
+  if (lane == 0) mask[(long long)t * mwords + j] = word;
+}
+// Weight gradient (A = X^T): M tile tm = pixels [128 tm, 128 tm + 128) = words 4 tm .. 4 tm + 3, k-block kb = rows
+// [64 kb, 64 kb + 64) of the group's row range.  lane <-> M tile (512 contiguous bytes per row), one warp per
+// (32 tiles, k-block); every lane ORs its bit into its own tile's map word (the map is cleared first).
+__global__ void __launch_bounds__(256) kmask_wg_kernel(const uint32_t* __restrict__ xb, int xb_ld, int krows, int tiles_m,
+                                                       uint32_t* mask, int mwords, int kblocks) {
+  const int gw = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  const int chunks = (tiles_m + 31) >> 5;
+  if (gw >= chunks * kblocks) return;
+  const int kb = gw / chunks, tm = (gw % chunks) * 32 + lane;
+  if (tm >= tiles_m) return;
+  uint32_t acc = 0u;
+  const int r1 = min(krows, kb * 64 + 64);
+#pragma unroll 8
+  for (int r = kb * 64; r < r1; ++r) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(xb + (long long)r * xb_ld + 4 * tm));
+    acc |= v.x | v.y | v.z | v.w;
+  }
+  if (acc) atomicOr(&mask[(long long)tm * mwords + (kb >> 5)], 1u << (kb & 31));
+}
+void build_kmask_fwd(const uint32_t* xb, int xb_ld, int rows, int kblocks, uint32_t* mask, int mwords, cudaStream_t s) {
+  const int tiles = (rows + 127) / 128;
+  const long long threads = (long long)tiles * mwords * 32;
+  kmask_fwd_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(xb, xb_ld, rows, kblocks, mask, mwords, tiles);
+}
+void build_kmask_wgrad(const uint32_t* xb, int xb_ld, int krows, int tiles_m, uint32_t* mask, int mwords, cudaStream_t s) {
+  const int kblocks = (krows + 63) / 64;
+  zero_fill(mask, sizeof(uint32_t) * (size_t)tiles_m * mwords, s);
+  const long long threads = (long long)((tiles_m + 31) / 32) * kblocks * 32;
+  kmask_wg_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(xb, xb_ld, krows, tiles_m, mask, mwords, kblocks);
+}
+
 // An SM changes its shared-memory carveout only when it is idle.  The GEMM kernels need the maximum carveout and the
 // generator shares SMs with them from its own stream, so every kernel of the library asks for the same carveout:
 // no launch ever waits for co-resident CTAs of the other stream to drain.
@@ -996,6 +1048,8 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(generate_pairs_kernel);
   MAGIC_MAX_CARVEOUT(pack_planes_bits_kernel);
   MAGIC_MAX_CARVEOUT(unpack_bits_planes_kernel);
+  MAGIC_MAX_CARVEOUT(kmask_fwd_kernel);
+  MAGIC_MAX_CARVEOUT(kmask_wg_kernel);
   fill_expand_lut_kernel<<<1, 256>>>();
   cudaDeviceSynchronize();      // init time only: the generator reads the table from its own stream
   cudaGetLastError();

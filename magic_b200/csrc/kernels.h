@@ -107,6 +107,12 @@ void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int s
 void pack_planes_bits(const __nv_bfloat16* planes, long long ld, int rows, int D, uint32_t* xb, int xb_ld, cudaStream_t s);
 void unpack_bits_planes(const uint32_t* xb, int xb_ld, int rows, __nv_bfloat16* planes, long long ld, cudaStream_t s);
 
+// Zero-stage maps of packed rows for the first layer's GEMMs (GemmArgs.kmask): which 128 x 64 operand stages hold a
+// set pixel.  fwd: mask[ceil(rows / 128)][mwords] over k-blocks of 64 pixels; wgrad: mask[tiles_m][mwords] over
+// k-blocks of 64 of the `krows` rows starting at xb, M tiles of 128 pixels.  mask size a multiple of 16 bytes.
+void build_kmask_fwd(const uint32_t* xb, int xb_ld, int rows, int kblocks, uint32_t* mask, int mwords, cudaStream_t s);
+void build_kmask_wgrad(const uint32_t* xb, int xb_ld, int krows, int tiles_m, uint32_t* mask, int mwords, cudaStream_t s);
+
 void zero_fill(void* ptr, size_t bytes, cudaStream_t s);   // kernel-based memset(0): ptr 16-byte aligned, bytes % 4 == 0
 void kernels_init();                                        // one-time function attributes (shared-memory carveout)
 

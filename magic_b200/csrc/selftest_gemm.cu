@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <string>
 #include "gemm.h"
+#include "kernels.h"
 
 using namespace magic;
 
@@ -43,6 +44,18 @@ struct HostMat {
     CK(cudaMalloc(&d, sizeof(__nv_bfloat16) * r * l));
     CK(cudaMemcpy(d, h.data(), sizeof(__nv_bfloat16) * r * l, cudaMemcpyHostToDevice));
   }
+  // zero whole 128 x 64 blocks (r = the 128-aligned axis, c = the 64-aligned axis) so that zero-stage maps have work:
+  // two blocks of three, plus every block of the 128-row band `dead_band`
+  void punch(bool r_is_row, int dead_band) {
+    std::vector<__nv_bfloat16> h(rows * ld);
+    for (long long i = 0; i < rows; ++i)
+      for (long long j = 0; j < ld; ++j) {
+        const long long a = r_is_row ? i / 128 : j / 128, b = r_is_row ? j / 64 : i / 64;
+        if (j < cols && ((a + b) % 3 != 0 || a == dead_band)) v[i * ld + j] = 0.f;
+        h[i * ld + j] = __float2bfloat16(v[i * ld + j]);
+      }
+    CK(cudaMemcpy(d, h.data(), sizeof(__nv_bfloat16) * rows * ld, cudaMemcpyHostToDevice));
+  }
   Mat mat() const { return Mat(d, rows, cols, ld); }
   float at(long long r, long long c) const { return v[r * ld + c]; }
 };
@@ -72,6 +85,7 @@ static void host_ref(int kind, int M, int N, int K, int nseg, const HostMat* a, 
 static int g_cluster = 1;   // cluster_m applied to the problems built below
 static int g_bn = 0;        // block_n applied to the problems built below (0 = the planner's choice)
 static int g_bits = 0;      // bench(): A operand as packed bits (all zero)
+static float g_density = 1.f;   // bench() with g_bits: fraction of operand stages marked non-zero in a random zero-stage map
 
 static void test_store(int kind, int M, int N, int K, int nseg, int split, int sms) {
   HostMat a[3], b[3];
@@ -225,15 +239,37 @@ static long long bits_pitch(int kind, int M, int K) {
 
 // The bits variant must reproduce the bf16-operand kernel bit for bit (same MMAs on the same shared-memory image) and
 // both must match the host reference.  FWD with nseg segments and split-K, fp32 store.
-static void test_bits_fwd_store(int M, int N, int K, int nseg, int split, int sms) {
+static void test_bits_fwd_store(int M, int N, int K, int nseg, int split, int sms, bool sparse = false) {
   HostMat a, b[3];
   a.init(M, K, (K + 63) / 64 * 64, 1.f, true);
+  if (sparse) a.punch(true, 1);
   for (int s = 0; s < nseg; ++s) b[s].init(K, N, (N + 63) / 64 * 64, 1.f);
   const long long pitch = bits_pitch(GEMM_FWD, M, K);
   uint32_t* dbits = pack_bits(a, pitch);
   const long long ldo = (N + 3) / 4 * 4;
   std::vector<float> h[2];
   int used_split = 0;
+  // zero-stage map (sparse runs): built by the library's own kernel from the packed rows
+  const int kblocks = (K + 63) / 64, mwords = (kblocks + 31) / 32, tiles = (M + 127) / 128;
+  uint32_t* dmask = nullptr;
+  if (sparse) {
+    CK(cudaMalloc(&dmask, sizeof(uint32_t) * tiles * mwords));
+    build_kmask_fwd(dbits, (int)pitch, M, kblocks, dmask, mwords, 0);
+    std::vector<uint32_t> hm((size_t)tiles * mwords);
+    CK(cudaMemcpy(hm.data(), dmask, sizeof(uint32_t) * hm.size(), cudaMemcpyDeviceToHost));
+    long long set = 0, bad = 0;
+    for (int t = 0; t < tiles; ++t)
+      for (int kk = 0; kk < kblocks; ++kk) {
+        bool any = false;
+        for (int m = t * 128; m < std::min(M, t * 128 + 128) && !any; ++m)
+          for (int k = kk * 64; k < std::min(K, kk * 64 + 64) && !any; ++k) any = a.at(m, k) != 0.f;
+        const bool bit = (hm[(size_t)t * mwords + (kk >> 5)] >> (kk & 31)) & 1u;
+        set += bit; bad += bit != any;
+      }
+    char nm[96];
+    snprintf(nm, sizeof nm, "   fwd zero-stage map (%lld of %d set)", set, tiles * kblocks);
+    report(nm, (double)bad, 0.0);
+  }
   for (int v = 0; v < 2; ++v) {
     float* dout;
     CK(cudaMalloc(&dout, sizeof(float) * M * ldo));
@@ -242,6 +278,7 @@ static void test_bits_fwd_store(int M, int N, int K, int nseg, int split, int sm
     p.kind = GEMM_FWD; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split; p.block_n = 256;
     for (int s = 0; s < nseg; ++s) { p.a[0][s] = a.mat(); p.b[0][s] = b[s].mat(); }
     if (v == 1) { p.a_bits = true; p.abits[0].base = dbits; p.abits[0].pitch = pitch; p.abits[0].rows = M; }
+    if (v == 1 && sparse) { p.kmask[0] = dmask; p.kmask_words = mwords; }
     EpiArgs e = {};
     e.out = dout; e.ld_out = ldo; e.alpha = 0.5f;
     p.e[0] = e;
@@ -265,11 +302,12 @@ static void test_bits_fwd_store(int M, int N, int K, int nseg, int split, int sm
       diff = fmax(diff, fabs((double)h[1][(size_t)m * ldo + n] - (double)h[0][(size_t)m * ldo + n]));
     }
   char name[128];
-  snprintf(name, sizeof name, "bits fwd store M=%d N=%d K=%d nseg=%d split=%d", M, N, K, nseg, used_split);
+  snprintf(name, sizeof name, "bits%s fwd store M=%d N=%d K=%d nseg=%d split=%d", sparse ? "+skip" : "", M, N, K, nseg, used_split);
   report(name, me, 2e-3 * sqrt((double)K * nseg) * 0.1 + 1e-4);
   // split-K sums partial tiles with red.add in arrival order: exact equality only without a split
   report("   bits vs bf16 operand", diff, used_split > 1 ? 1e-3 : 0.0);
   cudaFree(a.d); cudaFree(dbits);
+  if (dmask) cudaFree(dmask);
   for (int s = 0; s < nseg; ++s) cudaFree(b[s].d);
 }
 
@@ -320,11 +358,12 @@ static void test_bits_fwd_act(int M, int Nv, int K, int sms) {
 
 // WGRAD, two groups reading overlapping row ranges of one packed matrix (the engine's [rot; lock; key] stack), with and
 // without appended problems that keep their bf16 A operand
-static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms) {
+static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms, bool sparse = false) {
   // X [3 Bp, M] binary; group 0 = rows [0, 2 Bp), group 1 = rows [Bp, 3 Bp); dY [4 Bp, N]: group 0 rows [0, 2 Bp), group 1 rows [2 Bp, 4 Bp)
   const int K = 2 * Bp;
   HostMat x, dy, xa[2], xb[2];
   x.init(3LL * Bp, M, (M + 63) / 64 * 64, 1.f, true);
+  if (sparse) x.punch(false, 1);
   dy.init(4LL * Bp, N, (N + 63) / 64 * 64, 1.f);
   const long long pitch = bits_pitch(GEMM_WGRAD, M, K);
   uint32_t* dbits = pack_bits(x, pitch);
@@ -336,6 +375,27 @@ static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms) {
       xb[i].init(xs[i][2], xs[i][1], (xs[i][1] + 63) / 64 * 64, 1.f);
     }
   std::vector<float> h[2][2], hx[2][2];
+  const int tiles_m = (M + 127) / 128, wg_kb = (K + 63) / 64, mwords = (wg_kb + 31) / 32;
+  uint32_t* dmask[2] = {nullptr, nullptr};
+  if (sparse)
+    for (int g = 0; g < 2; ++g) {
+      CK(cudaMalloc(&dmask[g], sizeof(uint32_t) * ((size_t)tiles_m * mwords + 4)));
+      build_kmask_wgrad(dbits + (long long)g * Bp * pitch, (int)pitch, K, tiles_m, dmask[g], mwords, 0);
+      std::vector<uint32_t> hm((size_t)tiles_m * mwords);
+      CK(cudaMemcpy(hm.data(), dmask[g], sizeof(uint32_t) * hm.size(), cudaMemcpyDeviceToHost));
+      long long set = 0, bad = 0;
+      for (int t = 0; t < tiles_m; ++t)
+        for (int kb = 0; kb < wg_kb; ++kb) {
+          bool any = false;
+          for (int k = kb * 64; k < std::min(K, kb * 64 + 64) && !any; ++k)
+            for (int m = t * 128; m < std::min(M, t * 128 + 128) && !any; ++m) any = x.at((long long)g * Bp + k, m) != 0.f;
+          const bool bit = (hm[(size_t)t * mwords + (kb >> 5)] >> (kb & 31)) & 1u;
+          set += bit; bad += bit != any;
+        }
+      char nm[96];
+      snprintf(nm, sizeof nm, "   wgrad zero-stage map, group %d (%lld of %d set)", g, set, tiles_m * wg_kb);
+      report(nm, (double)bad, 0.0);
+    }
   for (int v = 0; v < 2; ++v) {
     float* dout[2];
     float* xout[2] = {nullptr, nullptr};
@@ -348,6 +408,7 @@ static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms) {
       p.a[g][0] = Mat(x.d + (long long)g * Bp * x.ld, K, M, x.ld);
       p.b[g][0] = Mat(dy.d + (long long)g * 2 * Bp * dy.ld, K, N, dy.ld);
       if (v == 1) { p.a_bits = true; p.abits[g].base = dbits + (long long)g * Bp * pitch; p.abits[g].pitch = pitch; p.abits[g].rows = K; }
+      if (v == 1 && sparse) { p.kmask[g] = dmask[g]; p.kmask_words = mwords; }
       EpiArgs e = {};
       e.out = dout[g]; e.ld_out = ldo; e.alpha = 1.f;
       p.e[g] = e;
@@ -400,10 +461,11 @@ static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms) {
         }
     }
   char name[128];
-  snprintf(name, sizeof name, "bits wgrad 2 groups M=%d N=%d K=%d%s", M, N, K, extras ? " + 2 appended" : "");
+  snprintf(name, sizeof name, "bits%s wgrad 2 groups M=%d N=%d K=%d%s", sparse ? "+skip" : "", M, N, K, extras ? " + 2 appended" : "");
   report(name, me, 2e-3 * sqrt((double)K) * 0.1 * 2 + 1e-4);
   report("   bits vs bf16 operand", diff, 0.0);
   cudaFree(x.d); cudaFree(dy.d); cudaFree(dbits);
+  for (int g = 0; g < 2; ++g) if (dmask[g]) cudaFree(dmask[g]);
   if (extras) for (int i = 0; i < 2; ++i) { cudaFree(xa[i].d); cudaFree(xb[i].d); }
 }
 
@@ -540,6 +602,17 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
     CK(cudaMalloc(&abits, sizeof(uint32_t) * rows * pitch));
     CK(cudaMemset(abits, 0x5A, sizeof(uint32_t) * rows * pitch));
     p.a_bits = true; p.abits[0].base = abits; p.abits[0].pitch = pitch; p.abits[0].rows = (int)rows; p.block_n = 256;
+    if (g_density < 1.f) {     // a random zero-stage map with this fraction of set stages (the bits stay as they are: timing only)
+      const int tiles = (M + 127) / 128, kbl = (K + 63) / 64, mw = (kbl + 31) / 32;
+      std::vector<uint32_t> hm((size_t)tiles * mw, 0u);
+      for (int t = 0; t < tiles; ++t)
+        for (int kk = 0; kk < kbl; ++kk)
+          if (frand() + 0.5f < g_density) hm[(size_t)t * mw + (kk >> 5)] |= 1u << (kk & 31);
+      uint32_t* dm;
+      CK(cudaMalloc(&dm, sizeof(uint32_t) * hm.size()));
+      CK(cudaMemcpy(dm, hm.data(), sizeof(uint32_t) * hm.size(), cudaMemcpyHostToDevice));
+      p.kmask[0] = dm; p.kmask_words = mw;
+    }
   }
   GemmPlan pl;
   std::string err = gemm_plan(p, sms, &pl);
@@ -668,6 +741,13 @@ int main(int argc, char** argv) {
   test_bits_wgrad(700, 500, 96, false, sms);
   test_bits_wgrad(1601, 120, 100, false, sms);
   test_bits_wgrad(1601, 500, 256, true, sms);
+  // ... with zero-stage maps: skipped stages, interleaved split-K slices, items without any set stage
+  test_bits_fwd_store(600, 500, 1601, 1, 1, sms, true);
+  test_bits_fwd_store(600, 500, 1601, 2, 1, sms, true);
+  test_bits_fwd_store(1000, 500, 3000, 2, 3, sms, true);
+  test_bits_fwd_store(300, 256, 5000, 1, 7, sms, true);
+  test_bits_wgrad(700, 500, 96, false, sms, true);
+  test_bits_wgrad(1601, 500, 256, true, sms, true);
   printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
   if (do_bench) {
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");
@@ -686,6 +766,15 @@ int main(int argc, char** argv) {
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd, A as bits");
     bench(GEMM_FWD, 12288, 512, 40064, 0, sms, "enc L0 fwd, A as bits (auto split)");
     bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, "enc L0 wgrad, A as bits");
+    for (float dn : {0.9999f, 0.75f, 0.5f, 0.25f}) {
+      g_density = dn;
+      char lbl[64];
+      snprintf(lbl, sizeof lbl, "enc L0 fwd, bits, %.0f%% stages", dn * 100);
+      bench(GEMM_FWD, 12288, 512, 40064, 0, sms, lbl);
+      snprintf(lbl, sizeof lbl, "enc L0 wgrad, bits, %.0f%% stages", dn * 100);
+      bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, lbl);
+    }
+    g_density = 1.f;
     g_bits = 0;
     bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd");
     bench(GEMM_FWD, 12288, 512, 512, 1, sms, "hidden fwd, tanh epilogue", EPI_ACT);

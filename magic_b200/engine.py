@@ -288,6 +288,17 @@ class Engine:
         check(self.lib.magic_export_batch(self._h, C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr())))
         return x, y
 
+    def set_option(self, name: str, value: int) -> None:
+        """Run-time switches of the engine; "skip_zero_stages" (default 1): see include/magic_b200.h."""
+        check(self.lib.magic_set_option(self._h, name.encode(), int(value)))
+
+    def input_density(self) -> Tuple[float, float]:
+        """Fraction of 128 x 64 first-layer operand stages of the loaded batch that hold a set pixel:
+        (forward GEMM, weight-gradient GEMM).  Synchronises."""
+        out = (C.c_double * 2)()
+        check(self.lib.magic_input_density(self._h, out))
+        return float(out[0]), float(out[1])
+
     def swap_batch(self) -> None:
         """Make the previously loaded batch (still resident in HBM) the loaded one again."""
         check(self.lib.magic_swap_batch(self._h))

@@ -158,26 +158,32 @@ def test_uint8_feed_equals_float_feed():
 
 @pytest.mark.parametrize("precision", ["bf16", "fp32"])
 def test_packed_first_layer_operand_matches_bf16_planes(precision, monkeypatch):
-    """The first layer's A operand is read as 1 bit per pixel and expanded inside the GEMM (default); with
-    MAGIC_BITS_A=0 the same GEMMs read bf16 planes through TMA.  Same products, same accumulators: losses, the batch
-    the generator exports and every gradient must agree to fp32 summation order (tile widths / split-K differ)."""
+    """The first layer's A operand is read as 1 bit per pixel and expanded inside the GEMM, and operand stages
+    without a set pixel are skipped (default); "skip_zero_stages" = 0 processes every stage; with MAGIC_BITS_A=0 the
+    same GEMMs read bf16 planes through TMA.  Same products, exact zeros left out: losses, the batch the generator
+    exports and every gradient must agree to fp32 summation order (tile widths / split-K slices differ)."""
     from magic_b200.engine import Engine
     from tests.util import engine_config_from_oracle
     ocfg = oracle_config(latent=20, encoder_neurons=[120, 72], decoder_neurons=[88, 104], n_input=1600)
     runs = []
-    for flag in ("1", "0"):
+    for flag, skip in (("1", 1), ("1", 0), ("0", 1)):
         monkeypatch.setenv("MAGIC_BITS_A", flag)
-        eng = Engine(engine_config_from_oracle(ocfg, 96, precision, seed=5))
+        eng = Engine(engine_config_from_oracle(ocfg, 300, precision, seed=5))
+        eng.set_option("skip_zero_stages", skip)
         eng.generate_batch(3, 7)
+        dens = eng.input_density()
         losses, dist = eng.step(apply=False, want_distance=True)
         X, y = eng.export_batch()
         grads = {(w, n): eng.get_grad(w, n) for w in (1, 2) for n in eng.param_names if eng.param_opts[n] & w}
-        runs.append((losses.cpu().numpy(), dist.cpu().numpy(), X.cpu().numpy(), y.cpu().numpy(), grads))
+        runs.append((losses.cpu().numpy(), dist.cpu().numpy(), X.cpu().numpy(), y.cpu().numpy(), grads, dens))
         eng.close()
-    a, b = runs
-    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])          # the same generated batch
+    a = runs[0]
     assert set(np.unique(a[2])) <= {0.0, 1.0} and a[2].sum() > 0
-    np.testing.assert_allclose(a[0], b[0], rtol=2e-5)
-    assert rel_l2(a[1], b[1]) < 2e-5
-    for k in a[4]:
-        assert rel_l2(a[4][k], b[4][k]) < 2e-5, k
+    assert 0.0 < a[5][0] < 1.0 and 0.0 < a[5][1] < 1.0, a[5]        # the generator leaves the canvas margins empty
+    assert runs[2][5] == (1.0, 1.0)                                  # no packed rows, no map
+    for b in runs[1:]:
+        assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])          # the same generated batch
+        np.testing.assert_allclose(a[0], b[0], rtol=2e-5)
+        assert rel_l2(a[1], b[1]) < 2e-5
+        for k in a[4]:
+            assert rel_l2(a[4][k], b[4][k]) < 2e-5, k

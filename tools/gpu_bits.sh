@@ -7,7 +7,7 @@ for es in 1; do
 done
 if [ "$1" != "quick" ]; then timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -8; fi
 MAGIC_EXPAND_SPLIT=1 timeout 600 python bench.py --steps 60 --warmup 5 --no-cpu-baseline > gpurun_out/bench_bits1.json 2> gpurun_out/bench_bits1.err; echo "bench rc=$?"
-MAGIC_BITS_A=0 timeout 600 python bench.py --steps 60 --warmup 5 --no-cpu-baseline > gpurun_out/bench_planes.json 2> gpurun_out/bench_planes.err; echo "bench(planes) rc=$?"
+MAGIC_SKIP_ZERO=0 timeout 600 python bench.py --steps 60 --warmup 5 --no-cpu-baseline > gpurun_out/bench_planes.json 2> gpurun_out/bench_planes.err; echo "bench(dense) rc=$?"
 python - <<'PY'
 import json
 for f in ("bits1", "planes"):
