@@ -11,7 +11,10 @@ configs[1]: experiment 8d (encoder 500x4, latent 200, cosine metric) at batch 40
 per-GPU batch stays fixed (weak scaling) and gradients are all-reduced over NCCL inside the step.
 
 Printed line (rank 0): value = pairs/s of the step with its inputs resident in HBM (two generated batches kept in
-the engine's input buffers and alternated; `with_generator` = the loop that also generates a new batch every step);
+the engine's input buffers and alternated; `with_generator` = the loop that also generates a new batch every step).
+The images are binary and mostly empty, the engine keeps them packed and its first-layer GEMMs skip operand stages
+without a set pixel (bit-identical results); `dense_inputs` = the same loop with that switched off (every stage
+multiplied), `input_density` = the fraction of stages that hold a set pixel;
 e2e = pairs/s of the training loop fed from pinned HOST memory, H2D of every step's inputs + step + D2H of the
 losses inside the timed region: headline = the dataset path (bit-packed lock/key pairs + labels through
 magic_feed_pairs_bits_host, one batch ahead; the rotated lock is made on the device as the reference's pipeline makes
@@ -218,8 +221,8 @@ def algorithmic_work(cfg, B, early_adam=False, fused_wgrad=False):
         # (with the small wgrads folded into the last launch only the decoder's output layer is final early)
         "adam.dual": ("hbm", 50.0 * n_enc + 30.0 * (n_dec - n_early if early_adam else n_dec)),
         "adam.decoder": ("hbm", 30.0 * n_early),
-        # generator writes three bf16 planes
-        "input.generate": ("hbm", 2.0 * 3 * B * D),
+        # generator writes three packed planes (1 bit per pixel)
+        "input.generate": ("hbm", 3.0 * B * D / 8),
     }
 
 
@@ -334,6 +337,28 @@ def run_b200(args):
     with_generator = {"value": B * world / (ms_gen * 1e-3), "unit": UNIT, "ms_per_step": ms_gen, "steps": Kg,
                       "note": "new generated batch every step inside the timed region (generator kernel + step)"}
 
+    # ---- leg 1d: the same resident-input loop with every operand stage processed (no zero-stage skipping)
+    eng.swap_batch()
+    density = eng.input_density()
+    Kd = max(3, min(K, 60))
+    eng.set_option("skip_zero_stages", 0)
+    for i in range(3):
+        eng.swap_batch()
+        eng.step()
+    e10, e11 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e10.record()
+    for i in range(Kd):
+        eng.swap_batch()
+        eng.step()
+    e11.record()
+    barrier()
+    ms_dense = max_over_ranks(e10.elapsed_time(e11)) / Kd
+    eng.set_option("skip_zero_stages", 1)
+    dense_inputs = {"value": B * world / (ms_dense * 1e-3), "unit": UNIT, "ms_per_step": ms_dense, "steps": Kd,
+                    "note": "skip_zero_stages = 0: every 128x64 operand stage of the first layer is expanded and multiplied "
+                            "(what an input without empty regions would cost)"}
+
     # ---- roofline of the dominant kernel family (by summed device time in the timed region)
     pk = peaks()
     fused_wgrad = world == 1 and args.precision == "bf16" and os.environ.get("MAGIC_FUSE_WGRAD", "1") != "0"
@@ -367,6 +392,15 @@ def run_b200(args):
                     "launches_timed": n, "measured_over": "%d steps with an event pair around every launch, run right "
                     "after the timed region on the same inputs" % Kp, "peak_source": pk["source"] + (" (sustained)" if kind == "tensor" else ""),
                     "algorithmic_per_launch": amount, "share_of_step": shares[tag]}
+            if tag in ("gemm.wgrad_enc0", "gemm.fwd_enc0") and os.environ.get("MAGIC_SKIP_ZERO", "1") != "0" \
+                    and os.environ.get("MAGIC_BITS_A", "1") != "0":
+                f = density[1] if tag == "gemm.wgrad_enc0" else density[0]
+                roof["executed_fraction"] = round(f, 4)
+                roof["achieved_executed"] = round(ach * f, 2)
+                roof["note"] = ("achieved counts the algorithmic (dense) FLOPs of SURVEY 8.4; %.1f %% of this GEMM's operand "
+                                "stages hold a set pixel and are multiplied, the rest are skipped as exact zeros, so the "
+                                "tensor pipe sustains achieved_executed (a fraction > 1 of the dense roofline is the "
+                                "sparsity of the images, not a faster pipe)" % (100 * f))
             break
     model_tflops = value / world * st.model_flops_per_pair * 1e-12
 
@@ -475,13 +509,17 @@ def run_b200(args):
                        "global_batch": B * world, "encoder": list(cfg.encoder_neurons), "latent": cfg.latent,
                        "metric_loss": cfg.metric + ("-reciprocal" if cfg.reciprocal else ""),
                        "parallelism": "dp%d" % world,
-                       "l2": "operands per step (bf16 planes %.0f MB, weights+Adam state %.0f MB) exceed the 126 MB L2; "
-                             "no flush needed" % (3 * B * cfg.D * 2 / 1e6, st.hbm_bytes / 1e6),
+                       "l2": "operands per step (weights, gradients and Adam state: %.0f MB streamed per step; packed input rows "
+                             "%.0f MB per batch) exceed the 126 MB L2; no flush needed"
+                             % ((50.0 * st.n_params2 + 30.0 * (st.n_params1 - st.n_params2)) / 1e6, 3 * B * cfg.D / 8 / 1e6),
                        "inputs": "two generated batches resident in HBM, alternated every step (magic_swap_batch); "
                                  "`with_generator` times the loop that generates a new batch every step"},
             "model_tflops_per_gpu": round(model_tflops, 1),
             "frac_of_bf16_sustained_peak": round(model_tflops / pk["tf_sustained"], 4),
             "with_generator": with_generator,
+            "dense_inputs": dense_inputs,
+            "input_density": {"forward": round(density[0], 4), "weight_gradient": round(density[1], 4),
+                              "what": "fraction of the first layer's 128x64 operand stages with a set pixel (generated batch)"},
             "ms_per_step_with_per_launch_events": ms_step_events,
             "roofline": roof, "kernel_time_shares": shares,
             "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,

@@ -773,6 +773,10 @@ void Engine::build_kmasks(InBuf& b, cudaStream_t s) {
   build_kmask_fwd(b.xb3, xb_ld_, 3 * B, km_fwd_kb_, b.kmask, km_fwd_words_, s);
   for (int g = 0; g < 2; ++g)
     build_kmask_wgrad(b.xb3 + (size_t)g * B * xb_ld_, xb_ld_, 2 * B, km_wg_tiles_, b.kmask + km_wg_off_[g], km_wg_words_, s);
+  // the plans that read this buffer get their work items re-dealt by the new maps (GemmArgs.order)
+  const int alt = &b == &in_[1] ? 1 : 0;
+  gemm_schedule(alt ? fwd_enc0_alt_ : fwd_enc_[0], s);
+  gemm_schedule(dp_fused_ ? pl_wg_enc0_sc_[alt] : fuse_wg_ ? pl_wg_enc0_fused_[alt] : (alt ? pl_wg_enc0_alt_ : pl_wg_enc_[0]), s);
   prof_end(s);
 }
 std::string Engine::set_option(const char* name, int value) {
@@ -801,9 +805,11 @@ std::string Engine::input_density(double* out2) {
 }
 // The first layer's plans carry their zero-stage maps; with the option off they run without (every stage processed).
 std::string Engine::launch_maybe_dense(GemmPlan& pl, int* launches, const char* tag) {
-  if (skip_zero_ || pl.args.kmask[0] == nullptr) return launch(pl, launches, tag);
+  if (skip_zero_ || pl.args.klist == nullptr) return launch(pl, launches, tag);
   GemmPlan dense = pl;
   for (auto& k : dense.args.kmask) k = nullptr;
+  dense.args.klist = nullptr;
+  dense.args.order = nullptr;
   return launch(dense, launches, tag);
 }
 

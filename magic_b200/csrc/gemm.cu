@@ -35,6 +35,81 @@ __global__ void gemm_finish_kernel(EpiArgs e, const float* __restrict__ ws, long
   epilogue_chunk<EPI, false>(e, TileOut{}, r, row, c * 32, M, N, dummy);
 }
 
+// ---------------------------------------------------------------------------- plans with a zero-stage map
+// Step 1: one k-block list per (group, M tile, split-K slice) from the map (GemmArgs.klist).  One warp per list:
+// 32 candidates at a time, ballot + prefix count compacts the set ones.
+__global__ void __launch_bounds__(256) gemm_klist_kernel(const __grid_constant__ GemmArgs args, uint16_t* klist, int* counts,
+                                                         int rows) {
+  const int r = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (r >= rows) return;
+  const int S = args.splitk, ks = r % S, mt = (r / S) % args.tiles_m, g = r / (S * args.tiles_m);
+  const uint32_t* mrow = args.kmask[g] + (long long)mt * args.kmask_words;
+  const int total_kb = args.nseg * args.kblocks;
+  const int ncand = S > 1 ? (total_kb - ks + S - 1) / S : total_kb;
+  uint16_t* out = klist + (long long)r * args.klist_pitch;
+  int n = 0;
+  for (int c0 = 0; c0 < ncand; c0 += 32) {
+    const int c = c0 + lane;
+    const int kb = S > 1 ? ks + c * S : c;
+    bool set = false;
+    if (c < ncand) {
+      int kk = kb;
+      while (kk >= args.kblocks) kk -= args.kblocks;
+      set = (__ldg(mrow + (kk >> 5)) >> (kk & 31)) & 1u;
+    }
+    const uint32_t b = __ballot_sync(0xffffffffu, set);
+    if (set) out[1 + n + __popc(b & ((1u << lane) - 1u))] = (uint16_t)kb;
+    n += __popc(b);
+  }
+  if (lane == 0) {
+    if (n == 0) { out[1] = (uint16_t)(S > 1 ? ks : 0); n = 1; }    // an all-zero stage: the accumulator must be written
+    out[0] = (uint16_t)n;
+    counts[r] = n;
+  }
+}
+// Step 2: work-item order (GemmArgs.order): cost = list length, counting sort by descending cost, then serpentine
+// dealing over the G persistent CTAs (round j hands out the next G items, every other round in reverse), so that each
+// CTA receives a similar total.  One CTA; a few thousand items at most.
+constexpr int kSchedMaxItems = 4096, kSchedMaxCost = 2048, kSchedThreads = 1024;
+__global__ void __launch_bounds__(kSchedThreads) gemm_schedule_kernel(const __grid_constant__ GemmArgs args, const int* counts,
+                                                                      int* order, int total, int G) {
+  __shared__ int hist[kSchedMaxCost + 1];
+  __shared__ unsigned short cost_of[kSchedMaxItems];
+  __shared__ int sorted[kSchedMaxItems];
+  for (int c = threadIdx.x; c <= kSchedMaxCost; c += kSchedThreads) hist[c] = 0;
+  __syncthreads();
+  for (int w = threadIdx.x; w < total; w += kSchedThreads) {
+    const WorkItem it = decode_work(args, w, 0);
+    int cost = it.g >= 0 ? counts[(it.g * args.tiles_m + it.mt) * args.splitk + it.ks] : it.kb1 - it.kb0;
+    cost = cost < 1 ? 1 : (cost > kSchedMaxCost ? kSchedMaxCost : cost);
+    cost_of[w] = (unsigned short)cost;
+    atomicAdd(&hist[cost], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {            // first position of every cost class, most expensive first
+    int pos = 0;
+    for (int c = kSchedMaxCost; c >= 1; --c) { const int n = hist[c]; hist[c] = pos; pos += n; }
+  }
+  __syncthreads();
+  for (int w = threadIdx.x; w < total; w += kSchedThreads) sorted[atomicAdd(&hist[cost_of[w]], 1)] = w;
+  __syncthreads();
+  for (int p = threadIdx.x; p < total; p += kSchedThreads) {
+    const int j = p / G, c = p - j * G;
+    const int nr = min(G, total - j * G);
+    order[j * G + ((j & 1) ? nr - 1 - c : c)] = sorted[p];
+  }
+}
+
+void gemm_schedule(const GemmPlan& pl, cudaStream_t s) {
+  if (!pl.klist) return;
+  uint16_t* klist = static_cast<uint16_t*>(pl.klist.get());
+  int* counts = reinterpret_cast<int*>(klist + (size_t)pl.klist_rows * pl.args.klist_pitch);
+  const long long threads = (long long)pl.klist_rows * 32;
+  gemm_klist_kernel<<<(int)((threads + 255) / 256), 256, 0, s>>>(pl.args, klist, counts, pl.klist_rows);
+  if (pl.order)
+    gemm_schedule_kernel<<<1, kSchedThreads, 0, s>>>(pl.args, counts, static_cast<int*>(pl.order.get()), (int)pl.items, pl.grid);
+}
+
 template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false>
 static cudaError_t set_smem() {
   return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN, A_BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -72,6 +147,8 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, true>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_SCATTER_F32, 256, true>();
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
+  cudaFuncSetAttribute(gemm_schedule_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  cudaFuncSetAttribute(gemm_klist_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_ACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaFuncSetAttribute(gemm_finish_kernel<EPI_DACT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   kernels_init();
@@ -378,6 +455,46 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
     items += item0;
   }
   pl.items = items;
+  pl.order.reset();
+  pl.klist.reset();
+  a.order = nullptr;
+  a.klist = nullptr;
+  if (a.kmask[0] != nullptr && cm == 1) {
+    // k-block lists, dense (every candidate) until gemm_schedule has seen a map
+    const int S = a.splitk, total_kb2 = a.nseg * a.kblocks;
+    const int rows = a.ngroups * a.tiles_m * S;
+    const int pitch = (int)((1 + (total_kb2 + S - 1) / S + 3) / 4 * 4);
+    if (total_kb2 > 65535) return "kmask: too many k-blocks for 16-bit lists";
+    std::vector<uint16_t> hl((size_t)rows * pitch, 0);
+    std::vector<int> hc((size_t)rows, 0);
+    for (int r = 0; r < rows; ++r) {
+      const int ks = r % S;
+      int n = 0;
+      for (int kb = S > 1 ? ks : 0; kb < total_kb2; kb += S > 1 ? S : 1) hl[(size_t)r * pitch + 1 + n++] = (uint16_t)kb;
+      hl[(size_t)r * pitch] = (uint16_t)n;
+      hc[(size_t)r] = n;
+    }
+    const size_t lbytes = sizeof(uint16_t) * hl.size();     // a multiple of 8: the counts behind it stay aligned
+    void* dptr = nullptr;
+    if (cudaMalloc(&dptr, lbytes + sizeof(int) * hc.size()) != cudaSuccess) return "cudaMalloc(k-block lists) failed";
+    pl.klist = std::shared_ptr<void>(dptr, [](void* q) { cudaFree(q); });
+    if (cudaMemcpy(dptr, hl.data(), lbytes, cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy(static_cast<char*>(dptr) + lbytes, hc.data(), sizeof(int) * hc.size(), cudaMemcpyHostToDevice) != cudaSuccess)
+      return "cudaMemcpy(k-block lists) failed";
+    pl.klist_rows = rows;
+    a.klist = static_cast<const uint16_t*>(dptr);
+    a.klist_pitch = pitch;
+  }
+  if (a.klist != nullptr && items <= kSchedMaxItems) {       // identity until gemm_schedule sees a map
+    std::vector<int> ident((size_t)items);
+    for (long long i = 0; i < items; ++i) ident[(size_t)i] = (int)i;
+    void* dptr = nullptr;
+    if (cudaMalloc(&dptr, sizeof(int) * (size_t)items) != cudaSuccess) return "cudaMalloc(work order) failed";
+    pl.order = std::shared_ptr<void>(dptr, [](void* q) { cudaFree(q); });
+    if (cudaMemcpy(dptr, ident.data(), sizeof(int) * (size_t)items, cudaMemcpyHostToDevice) != cudaSuccess)
+      return "cudaMemcpy(work order) failed";
+    a.order = static_cast<const int*>(dptr);
+  }
   const long long slots = num_sms / cm;              // refined at launch by the occupancy query when cm > 1
   pl.grid = (int)(items < slots ? items : slots) * cm;
   return "";

@@ -37,6 +37,9 @@ struct GemmPlan {
   int finish_epi_kind = 0;
   double flops = 0;
   std::shared_ptr<void> xbuf;   // device copy of the extras' descriptors (GemmExtraDev[nextra])
+  std::shared_ptr<void> order;  // plans with a zero-stage map: the work-item permutation args.order points at (int[items])
+  std::shared_ptr<void> klist;  // ... their k-block lists (args.klist, uint16[rows][klist_pitch]) followed by the list lengths (int[rows])
+  int klist_rows = 0;
 };
 
 // A problem appended to another problem's launch (GemmExtraDev in gemm_sm100.cuh): same kind / epilogue / segment
@@ -76,6 +79,9 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out);
 int gemm_launch(const GemmPlan& plan, cudaStream_t stream, std::string* err);
 // Point group g's epilogue at another output matrix of the same shape and pitch (re-encodes its output tile maps).
 std::string gemm_set_output(GemmPlan* plan, int g, void* out, void* out_lo);
+// Plans with a zero-stage map: rebuild the work-item order from the map's current contents (one small kernel on the
+// stream that just rebuilt the map).  No-op for other plans.
+void gemm_schedule(const GemmPlan& plan, cudaStream_t stream);
 std::string gemm_init();   // resolves cuTensorMapEncodeTiled, sets max dynamic smem on every variant
 int choose_splitk(int tiles, int total_kb, int num_sms, bool two_pass = false);
 

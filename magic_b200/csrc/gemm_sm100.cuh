@@ -146,17 +146,28 @@ struct GemmArgs {
   BitsA abits[kMaxGroups];           // A_BITS kernels: the main problem's A operand (extras keep bf16 A through TMA)
   // Zero-stage map of the main problem's A operand (A_BITS kernels; null = none): bit kk of row (m0 / 128) of group g's
   // map says "k-block kk of this M tile holds at least one set pixel".  A stage whose 128 x 64 pixels are all zero adds
-  // exact zeros to the accumulator, so it is neither fetched (B) nor expanded (A) nor multiplied.  With a map the
-  // split-K slices interleave (slice s takes k-blocks s, s + splitk, ...), so that every slice sees the same mix of the
-  // images' empty margins and busy centres.
+  // exact zeros to the accumulator, so it is neither fetched (B) nor expanded (A) nor multiplied.  The kernel does not
+  // read the map: gemm_schedule() turns it into one list of k-blocks per (group, M tile, split-K slice) -- klist row
+  // (g * tiles_m + mt) * splitk + ks: entry 0 = count (>= 1: an empty list is given the slice's first block, an
+  // all-zero stage, so that the accumulator is written), entries 1.. = k-block indices over nseg * kblocks, ascending.
+  // With lists the split-K slices interleave (slice s owns k-blocks s, s + splitk, ...), so that every slice sees the
+  // same mix of the images' empty margins and busy centres.
   const uint32_t* kmask[kMaxGroups];
   int kmask_words;                   // words per map row
+  const uint16_t* klist;             // null: every k-block of [kb0, kb1)
+  int klist_pitch;                   // entries per row (a multiple of 4: rows are read 8 bytes at a time)
+  // With a map the work items differ in length (an M tile in the images' empty margin is one forced k-block, one in
+  // the centre runs all of them), so the static round-robin `w = cta, cta + grid, ...` would leave most CTAs waiting
+  // for the unlucky ones.  order[w] (null = identity) is a permutation of the work items, rebuilt with every map
+  // (gemm_schedule): items sorted by their number of set stages and dealt to the CTAs in serpentine order.
+  const int* order;
 };
 
 struct WorkItem {
   int g;             // group of the main problem, or -1 - e for extra problem e
   int m0, n0, kb0, kb1;
   int kstep;         // k-blocks kb0, kb0 + kstep, ... < kb1 (1 unless the split-K slices interleave)
+  int mt, ks;        // main problem: M tile (cluster row) and split-K slice of the item
   int M, N, kblocks; // of the problem this item belongs to
 };
 
@@ -176,6 +187,7 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int cr
     it.kb0 = 0;
     it.kb1 = a.nseg * a.x_kb[e];
     it.kstep = 1;
+    it.mt = 0; it.ks = 0;
     it.M = a.x_m[e]; it.N = a.x_n[e]; it.kblocks = a.x_kb[e];
     return it;
   }
@@ -193,7 +205,9 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int cr
   int ks = t / a.ngroups;
   int total_kb = a.nseg * a.kblocks;
   int per = (total_kb + a.splitk - 1) / a.splitk;
-  if (a.kmask[0] != nullptr && a.splitk > 1) {       // interleaved slices (see GemmArgs.kmask)
+  it.ks = ks;
+  it.mt = mt;
+  if (a.klist != nullptr && a.splitk > 1) {          // interleaved slices (see GemmArgs.kmask)
     it.kb0 = ks; it.kb1 = total_kb; it.kstep = a.splitk;
   } else {
     it.kb0 = ks * per;
@@ -205,39 +219,45 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int cr
   return it;
 }
 
-// The k-blocks one work item processes, in order: every kstep-th block of [kb0, kb1) whose bit is set in the item's
-// zero-stage map row (all of them without a map).  Producer, expanders and MMA issuer each walk the same sequence, so
-// a skipped block consumes no pipeline stage.  An item without any set block still runs its first block (an all-zero
-// A stage): the accumulator must be written before the epilogue reads it.
+// The k-blocks one work item processes, in order: its klist row if the plan has lists, else every kstep-th block of
+// [kb0, kb1).  Producer and expanders each walk the same sequence, so a skipped block consumes no pipeline stage;
+// walking a list is one 8-byte load per four blocks and `skip(n)` is an index addition (the expanders look four
+// blocks ahead).
 struct KbWalk {
-  const uint32_t* mrow;
-  int kb, kb1, kstep, kblocks;
-  int cw;            // index of the map word held in cv (-1: none): one load per 32 candidate blocks, not one per test
-  uint32_t cv;
-  bool forced;
-  __device__ __forceinline__ bool set(int k) {
-    while (k >= kblocks) k -= kblocks;                  // the map is per k-block inside a precision segment
-    const int w = k >> 5;
-    if (w != cw) { cv = __ldg(mrow + w); cw = w; }
-    return (cv >> (k & 31)) & 1u;
+  const uint16_t* row;   // null: dense walk
+  int i, n;              // list position / length
+  int kb, kb1, kstep;
+  uint2 c4;              // the four list entries that contain position i
+  int c4_base;           // index of c4's first entry
+  __device__ __forceinline__ void load() {
+    if (i >= n) return;
+    const int e = i + 1, base = e & ~3;                   // entry 0 is the count
+    if (base != c4_base) { c4 = __ldg(reinterpret_cast<const uint2*>(row + base)); c4_base = base; }
+    const uint32_t w = (e & 2) ? c4.y : c4.x;
+    kb = (e & 1) ? (int)(w >> 16) : (int)(w & 0xFFFFu);
   }
   __device__ __forceinline__ void begin(const GemmArgs& a, const WorkItem& it) {
-    mrow = (it.g >= 0 && a.kmask[it.g] != nullptr) ? a.kmask[it.g] + (long long)(it.m0 / kBlockM) * a.kmask_words : nullptr;
-    kb = it.kb0; kb1 = it.kb1; kstep = it.kstep; kblocks = it.kblocks;
-    cw = -1; cv = 0u;
-    forced = false;
-    if (mrow) {
-      while (kb < kb1 && !set(kb)) kb += kstep;
-      if (kb >= kb1) { kb = it.kb0; forced = true; }
+    kb = it.kb0; kb1 = it.kb1; kstep = it.kstep;
+    row = nullptr;
+    if (it.g >= 0 && a.klist != nullptr) {
+      row = a.klist + ((long long)(it.g * a.tiles_m + it.mt) * a.splitk + it.ks) * a.klist_pitch;
+      c4 = __ldg(reinterpret_cast<const uint2*>(row));
+      c4_base = 0;
+      n = (int)(c4.x & 0xFFFFu);
+      i = 0;
+      load();
     }
   }
-  __device__ __forceinline__ bool done() const { return kb >= kb1; }
-  __device__ __forceinline__ void step() {
-    if (forced) { kb = kb1; return; }
-    kb += kstep;
-    if (mrow) while (kb < kb1 && !set(kb)) kb += kstep;
+  __device__ __forceinline__ bool done() const { return row ? i >= n : kb >= kb1; }
+  __device__ __forceinline__ void skip(int k) {          // k blocks further
+    if (row) { i += k; load(); }
+    else kb += k * kstep;
   }
+  __device__ __forceinline__ void step() { skip(1); }
+  __device__ __forceinline__ int left() const { return row ? n - i : (kb1 - kb + kstep - 1) / kstep; }   // blocks still to go (>= 0)
 };
+
+__device__ __forceinline__ int work_item_at(const GemmArgs& a, int w) { return a.order ? __ldg(a.order + w) : w; }
 
 // ---------------------------------------------------------------------------- epilogue math
 // ACT / PRECISE are compile-time: a run-time branch inside the per-element loops would stop ptxas from
@@ -685,7 +705,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (int w = work0; w < total_work; w += work_stride) {
-        const WorkItem it = decode_work(args, w, crank);
+        const WorkItem it = decode_work(args, work_item_at(args, w), crank);
         KbWalk walk;
         bool first_kb = true;
         walk.begin(args, it);
@@ -792,7 +812,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     // before the accumulator wait, their ~1.3 us of DRAM latency sat on the critical path of every tile (r01i trace).
     uint32_t xw[kMaxOwn], xw_next[kMaxOwn];
     auto load_xw = [&](int w_item, uint32_t (&dst)[kMaxOwn]) {
-      const WorkItem nit = decode_work(args, w_item, crank);
+      const WorkItem nit = decode_work(args, work_item_at(args, w_item), crank);
       const EpiArgs& ne = args.epi[nit.g];
       const int nrow = nit.m0 + q * 32 + lane;
       const int nn = (min(BN, args.N - nit.n0) + 31) >> 5;
@@ -806,7 +826,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       if (work0 < total_work) load_xw(work0, xw_next);
     }
     for (int w = work0; w < total_work; w += work_stride, ++iter) {
-      const WorkItem it = decode_work(args, w, crank);
+      const WorkItem it = decode_work(args, work_item_at(args, w), crank);
       const EpiArgs& e = it.g >= 0 ? args.epi[it.g] : args.xdev[-1 - it.g].epi;
       const uint32_t acc = iter % kAcc, acc_phase = (iter / kAcc) & 1;
       const int row = it.m0 + q * 32 + lane;
@@ -894,20 +914,23 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     // this kernel's 112 registers, and one warp per stage already keeps up with the MMAs: profiles/r01p)
     static_assert(kNS == kExpandWarps, "expander warp e serves pipeline stage e");
     const int ew = warp - (2 + epi_warps(EPI));
-    struct Cursor { KbWalk walk; int w, m0, g; bool valid; };
+    struct Cursor { KbWalk walk; int w, m0, g, kblocks; bool valid; };
     auto open = [&](Cursor& c) {
       c.valid = false;
       while (c.w < total_work) {
-        const WorkItem it = decode_work(args, c.w, 0);
+        const WorkItem it = decode_work(args, work_item_at(args, c.w), 0);
         c.walk.begin(args, it);
-        if (!c.walk.done()) { c.m0 = it.m0; c.g = it.g; c.valid = true; return; }
+        if (!c.walk.done()) { c.m0 = it.m0; c.g = it.g; c.kblocks = it.kblocks; c.valid = true; return; }
         c.w += work_stride;
       }
     };
     auto advance = [&](Cursor& c, int n) {       // n k-blocks further along the CTA's sequence of (work item, k-block)
-      for (; c.valid && n > 0; --n) {
-        c.walk.step();
-        if (c.walk.done()) { c.w += work_stride; open(c); }
+      while (c.valid && n > 0) {
+        const int left = c.walk.left();
+        if (n < left) { c.walk.skip(n); return; }
+        n -= left;
+        c.w += work_stride;
+        open(c);
       }
     };
     auto fetch = [&](const Cursor& c, uint2 (&v)[4]) {
@@ -916,7 +939,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       if (c.valid && c.g >= 0) {
         const BitsA& ba = args.abits[c.g];
         int kk = c.walk.kb;
-        while (kk >= c.walk.kblocks) kk -= c.walk.kblocks;   // k-block inside its precision segment: every segment reads the same A
+        while (kk >= c.kblocks) kk -= c.kblocks;          // k-block inside its precision segment: every segment reads the same A
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int r = lane + 32 * q;

@@ -285,6 +285,7 @@ static void test_bits_fwd_store(int M, int N, int K, int nseg, int split, int sm
     GemmPlan pl;
     std::string err = gemm_plan(p, sms, &pl);
     if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+    gemm_schedule(pl, 0);            // plans with a map: cost-balanced work order (no-op otherwise)
     if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
     CK(cudaDeviceSynchronize());
     used_split = pl.args.splitk;
@@ -427,6 +428,15 @@ static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms, bool spa
     GemmPlan pl;
     std::string err = gemm_plan(p, sms, &pl);
     if (!err.empty()) { printf("plan error: %s\n", err.c_str()); ++g_fail; return; }
+    gemm_schedule(pl, 0);
+    if (pl.order) {                  // the order must be a permutation of the work items
+      std::vector<int> ho((size_t)pl.items);
+      CK(cudaMemcpy(ho.data(), pl.order.get(), sizeof(int) * ho.size(), cudaMemcpyDeviceToHost));
+      std::vector<int> seen((size_t)pl.items, 0);
+      int bad = 0;
+      for (int o : ho) { if (o < 0 || o >= (int)pl.items || seen[o]++) ++bad; }
+      report("   work order is a permutation", (double)bad, 0.0);
+    }
     if (gemm_launch(pl, 0, &err) < 0) { printf("launch error: %s\n", err.c_str()); ++g_fail; return; }
     CK(cudaDeviceSynchronize());
     for (int g = 0; g < 2; ++g) {
@@ -617,6 +627,7 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   GemmPlan pl;
   std::string err = gemm_plan(p, sms, &pl);
   if (!err.empty()) { printf("plan error: %s\n", err.c_str()); return; }
+  gemm_schedule(pl, 0);
   if (getenv("MAGIC_TRACE")) {   // per-CTA phase stamps of one warm launch
     long long* tr;
     CK(cudaMalloc(&tr, sizeof(long long) * 64 * pl.grid));

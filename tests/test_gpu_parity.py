@@ -181,9 +181,12 @@ def test_packed_first_layer_operand_matches_bf16_planes(precision, monkeypatch):
     assert set(np.unique(a[2])) <= {0.0, 1.0} and a[2].sum() > 0
     assert 0.0 < a[5][0] < 1.0 and 0.0 < a[5][1] < 1.0, a[5]        # the generator leaves the canvas margins empty
     assert runs[2][5] == (1.0, 1.0)                                  # no packed rows, no map
+    # fp32 sums taken in another order differ in the last bits; in the bf16 mode such a difference can flip the
+    # rounding of a stored activation (2^-9 relative), so the modes agree to a tenth of the mode's tolerance
+    tol = TOL[precision] / 10
     for b in runs[1:]:
         assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])          # the same generated batch
-        np.testing.assert_allclose(a[0], b[0], rtol=2e-5)
-        assert rel_l2(a[1], b[1]) < 2e-5
+        np.testing.assert_allclose(a[0], b[0], rtol=tol)
+        assert rel_l2(a[1], b[1]) < tol
         for k in a[4]:
-            assert rel_l2(a[4][k], b[4][k]) < 2e-5, k
+            assert rel_l2(a[4][k], b[4][k]) < tol, k
