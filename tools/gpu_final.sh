@@ -11,7 +11,7 @@ timeout 600 $CMD > gpurun_out/launch_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -c 800 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/launch_ncu.log 2>&1
 tail -2 gpurun_out/launch_ncu.log | cut -c1-200
 if [ "$1" = "ncu" ]; then
-  timeout 900 bash tools/gpu_ncu_one.sh wgrad_enc0_bits 'gemm_tcgen05_kernel<1, 1, 0, 256, 1>' 3
-  timeout 900 bash tools/gpu_ncu_one.sh fwd_enc0_bits 'gemm_tcgen05_kernel<0, 1, 0, 256, 1>' 3
+  timeout 900 bash tools/gpu_ncu_one.sh wgrad_enc0_bits 'gemm_tcgen05_kernel<.bool.1, .bool.1, .int.0, .int.256, .bool.1>' 3
+  timeout 900 bash tools/gpu_ncu_one.sh fwd_enc0_bits 'gemm_tcgen05_kernel<.bool.0, .bool.1, .int.0, .int.256, .bool.1>' 3
   ls -la gpurun_out/*.ncu-rep
 fi
