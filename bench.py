@@ -279,7 +279,11 @@ def run_b200(args):
     # magic_swap_batch, so every step reads a batch that the previous step evicted from L2.  No events inside.
     eng.generate_batch(0, 0)
     eng.generate_batch(0, 1)
-    for i in range(W):
+    # N > 1: the first few dozen steps of a process group run slow (lazily mapped CUDA-IPC peer memory is touched page by
+    # page, NCCL brings up its channels): 8 GPUs measured 2.29 ms per step over steps 6..105 and 1.90 ms over steps
+    # 41..240 (profiles/r01p_bench_n8*.json).  Those settling steps are run on top of the W warm-up steps, untimed.
+    settle = 40 if world > 1 else 0
+    for i in range(W + settle):
         eng.swap_batch()
         eng.step()
     sampler = ClockSampler(local)
@@ -512,6 +516,7 @@ def run_b200(args):
                        "l2": "operands per step (weights, gradients and Adam state: %.0f MB streamed per step; packed input rows "
                              "%.0f MB per batch) exceed the 126 MB L2; no flush needed"
                              % ((50.0 * st.n_params2 + 30.0 * (st.n_params1 - st.n_params2)) / 1e6, 3 * B * cfg.D / 8 / 1e6),
+                       "settling_steps": settle,
                        "inputs": "two generated batches resident in HBM, alternated every step (magic_swap_batch); "
                                  "`with_generator` times the loop that generates a new batch every step"},
             "model_tflops_per_gpu": round(model_tflops, 1),
