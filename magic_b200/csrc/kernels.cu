@@ -850,7 +850,6 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
 // (outside of which the rotated plane is empty) is measured from the bitmap while it is loaded: the farthest set
 // pixel from the centre, in doubled coordinates.  Output is the packed rows only (the GEMMs' A operand and the BCE
 // target).
-constexpr int kPairsBitsMaxWords = 2048;      // side <= 256
 // Same footprint as the generator (384 threads, at most 56 registers, one CTA per SM): three of its warps fit beside
 // the GEMM's warps in a sub-partition's 16 K registers, so it runs UNDER the step instead of making GEMM CTAs wait for
 // a persistent grid to drain (256 threads x 2 CTAs per SM did exactly that: 0.82 ms per batch, e2e 2.41 -> 2.58 ms).

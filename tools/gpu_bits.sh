@@ -1,12 +1,12 @@
 # usage: bash tools/gpu_bits.sh -- packed first-layer operand: native self-test, GPU tests, bench in the operand modes
 mkdir -p gpurun_out
 for es in 1; do
-  MAGIC_EXPAND_SPLIT=$es timeout 600 magic_b200/csrc/build/selftest_gemm bench > gpurun_out/selftest_bits$es.log 2>&1; rc=$?; echo "selftest split=$es rc=$rc"
+  timeout 600 magic_b200/csrc/build/selftest_gemm bench > gpurun_out/selftest_bits$es.log 2>&1; rc=$?; echo "selftest split=$es rc=$rc"
   grep -E "bits|FAIL|SELFTEST|enc L0" gpurun_out/selftest_bits$es.log | grep -v "OK$" | cut -c1-150
   if [ $rc -ne 0 ]; then exit 1; fi
 done
 if [ "$1" != "quick" ]; then timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -8; fi
-MAGIC_EXPAND_SPLIT=1 timeout 600 python bench.py --steps 60 --warmup 5 --no-cpu-baseline > gpurun_out/bench_bits1.json 2> gpurun_out/bench_bits1.err; echo "bench rc=$?"
+timeout 600 python bench.py --steps 60 --warmup 5 --no-cpu-baseline > gpurun_out/bench_bits1.json 2> gpurun_out/bench_bits1.err; echo "bench rc=$?"
 MAGIC_SKIP_ZERO=0 timeout 600 python bench.py --steps 60 --warmup 5 --no-cpu-baseline > gpurun_out/bench_planes.json 2> gpurun_out/bench_planes.err; echo "bench(dense) rc=$?"
 python - <<'PY'
 import json
