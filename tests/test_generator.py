@@ -98,3 +98,37 @@ def test_generated_batch_trains():
     g2 = eng.get_grad(1, "decoder_out_mean_weights")      # split-K red.add order differs run to run: fp32 round-off
     assert np.linalg.norm(g1 - g2) <= 1e-5 * np.linalg.norm(g2)
     eng.close()
+
+
+def test_zero_stage_maps_match_the_exported_batch():
+    """magic_input_density counts the 128 x 64 first-layer operand stages with a set pixel from the engine's
+    zero-stage maps (the data its GEMMs skip by); recount them from the exported batch.  Forward: tiles of 128 packed
+    rows [rot; lock; key] x 64 pixels (bias column D included); weight gradient: tiles of 128 pixels x 64 rows of
+    the row ranges [0, 2B) and [B, 3B)."""
+    from magic_b200.engine import Engine, EngineConfig
+    B = 200                                    # not a multiple of 64 or 128: ragged last tiles
+    eng = Engine(EngineConfig.experiment("8c", batch=B, precision="bf16"))
+    eng.generate_batch(5, 2)
+    dens = eng.input_density()
+    X, _ = eng.export_batch()
+    D = eng.D
+    Xi = X.view(B, D, 3)
+    planes = torch.cat([Xi[:, :, 1], Xi[:, :, 0], Xi[:, :, 2]], 0) > 0          # rows [rot; lock; key]
+    kb = (D + 1 + 63) // 64
+    rows_pad = (3 * B + 127) // 128 * 128
+    P = torch.zeros(rows_pad, kb * 64, dtype=torch.bool, device=X.device)
+    P[:3 * B, :D] = planes
+    P[:3 * B, D] = True
+    fwd = P.view(rows_pad // 128, 128, kb, 64).any(3).any(1)
+    want_fwd = float(fwd.sum()) / (fwd.shape[0] * kb)
+    tm = (D + 1 + 127) // 128
+    kbw = (2 * B + 63) // 64
+    tot = 0
+    for g in range(2):
+        Q = torch.zeros(kbw * 64, tm * 128, dtype=torch.bool, device=X.device)
+        Q[:2 * B, :kb * 64] = P[g * B:g * B + 2 * B]
+        tot += int(Q.view(kbw, 64, tm, 128).any(3).any(1).sum())
+    want_wg = tot / (2.0 * tm * kbw)
+    assert abs(dens[0] - want_fwd) < 1e-12 and abs(dens[1] - want_wg) < 1e-12, (dens, want_fwd, want_wg)
+    assert 0.2 < dens[0] < 0.9
+    eng.close()
