@@ -517,6 +517,9 @@ def run_b200(args):
                              "%.0f MB per batch) exceed the 126 MB L2; no flush needed"
                              % ((50.0 * st.n_params2 + 30.0 * (st.n_params1 - st.n_params2)) / 1e6, 3 * B * cfg.D / 8 / 1e6),
                        "settling_steps": settle,
+                       "zero_stage_skipping": "on: first-layer operand stages (128x64 pixels) without a set pixel add exact "
+                                              "zeros and are skipped, results bit-identical; `dense_inputs` is the same loop with "
+                                              "every stage multiplied, `input_density` the fraction of stages that are not empty",
                        "inputs": "two generated batches resident in HBM, alternated every step (magic_swap_batch); "
                                  "`with_generator` times the loop that generates a new batch every step"},
             "model_tflops_per_gpu": round(model_tflops, 1),
