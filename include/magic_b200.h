@@ -89,8 +89,9 @@ int magic_get_step(magic_handle* h, int64_t* t);
 int magic_set_step(magic_handle* h, int64_t t);
 
 /* Input of one step.  The reference feeds X[B,120000] fp32, channel-interleaved (ch0 lock, ch1 rotated lock,
- * ch2 key; 8c/vae.py:166-179, 8c/overlap_input.py:195).  Each loader converts into the handle's planar bf16
- * operand buffer (pixels are {0,1}: exact). */
+ * ch2 key; 8c/vae.py:166-179, 8c/overlap_input.py:195).  Each loader converts into the handle's input
+ * buffer: packed rows [rot; lock; key], 1 bit per pixel (pixels are {0,1}: exact), which the first layer's GEMMs read
+ * directly; the array loaders go through planar bf16 on the way. */
 int magic_load_interleaved(magic_handle* h, const float* d_x);                       /* [B, 3*D] */
 /* Same layout as uint8: any non-zero byte is a set pixel.  The reference's feed_dict converts whatever array it is
  * given to the placeholder dtype, so a uint8/bool X is a legal argument of the same partial_fit (8c/vae.py:395); it

@@ -233,7 +233,7 @@ class Engine:
         self._keep = ts
 
     def load_pairs_u8(self, lock: torch.Tensor, key: torch.Tensor, seed: int, step: int) -> None:
-        """Dataset pairs (uint8 [B, D]) -> operand planes; the rotated lock is produced on the device."""
+        """Dataset pairs (uint8 [B, D]) -> the engine's packed input rows; the rotated lock is produced on the device."""
         ts = [x.to(device=self.device, dtype=torch.uint8).contiguous() for x in (lock, key)]
         for x in ts:
             if tuple(x.shape) != (self.B, self.D):
@@ -248,7 +248,7 @@ class Engine:
         return (self.D + 31) // 32
 
     def load_pairs_bits(self, lock_bits: torch.Tensor, key_bits: torch.Tensor, seed: int, step: int) -> None:
-        """Bit-packed dataset pairs already on the device (int32/uint32 [B, words_per_row]) -> operand planes."""
+        """Bit-packed dataset pairs already on the device (int32/uint32 [B, words_per_row]) -> packed input rows."""
         ts = [x.to(device=self.device).contiguous() for x in (lock_bits, key_bits)]
         for x in ts:
             if x.dim() != 2 or x.shape[0] != self.B or x.shape[1] < self.words_per_row or x.element_size() != 4:
@@ -259,7 +259,7 @@ class Engine:
 
     def feed_pairs_bits(self, lock_bits, key_bits, labels, seed: int, step: int, activate: bool = True) -> None:
         """Bit-packed pairs in HOST memory (numpy or CPU torch, 32-bit words [B, words_per_row]; pinned keeps the
-        copy asynchronous) -> operand planes, on the engine's input stream.  activate=False leaves the batch staged
+        copy asynchronous) -> packed input rows, on the engine's input stream.  activate=False leaves the batch staged
         until swap_batch().  The arrays must not change until the step that consumes them has been waited for."""
         arrs = []
         for x in (lock_bits, key_bits):
