@@ -401,6 +401,7 @@ def run_b200(args):
                 f = density[1] if tag == "gemm.wgrad_enc0" else density[0]
                 roof["executed_fraction"] = round(f, 4)
                 roof["achieved_executed"] = round(ach * f, 2)
+                roof["frac_executed"] = round(ach * f / peak, 4)
                 roof["note"] = ("achieved counts the algorithmic (dense) FLOPs of SURVEY 8.4; %.1f %% of this GEMM's operand "
                                 "stages hold a set pixel and are multiplied, the rest are skipped as exact zeros, so the "
                                 "tensor pipe sustains achieved_executed (a fraction > 1 of the dense roofline is the "
