@@ -136,6 +136,10 @@ int magic_swap_batch(magic_handle* h);
  * its weight gradient -- multiplies them.  The engine keeps them packed (1 bit per pixel) and skips every 128 x 64
  * operand stage without a set pixel: such a stage adds exact zeros, so results are bit-identical to processing it.
  *   magic_set_option(h, "skip_zero_stages", 0)  processes every stage (dense-input timing; default 1)
+ *   magic_set_option(h, "skip_untouched_rows", 1)  EXPERIMENTAL, default 0, one GPU: the Adam pass leaves rows of the
+ *                                                first-layer matrix alone whose 128-pixel input tile no batch has set so
+ *                                                far (gradient and both moments are exactly 0 there, so the update is
+ *                                                p - lr * 0 / (0 + eps) = p); magic_set_slot makes every row count as set
  *   magic_input_density                          fraction of stages with a set pixel in the loaded batch:
  *                                                out2[0] forward GEMM, out2[1] weight-gradient GEMM (synchronises) */
 int magic_set_option(magic_handle* h, const char* name, int32_t value);

@@ -253,12 +253,16 @@ __device__ __forceinline__ float adam_one(float g, float& m, float& v, float lr_
   return lr_t * m / (sqrtf(v) + eps);
 }
 
-__global__ void __launch_bounds__(256) adam_dual_kernel(AdamArgs a) {
+template <bool SKIP>
+__device__ __forceinline__ void adam_dual_body(const AdamArgs& a, const uint32_t* touched, long long skip_end, int ld0) {
   ptx::grid_dep_wait();
   // grid-stride: the full-width launch covers the range in one pass; the side-stream launch (a.thin) uses two CTAs
   // per SM so that it leaves room for the GEMM CTAs it runs beside
   const long long stride = (long long)gridDim.x * blockDim.x * 4;
   for (long long i4 = a.begin + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i4 < a.n_total; i4 += stride) {
+    if constexpr (SKIP) {        // rows of W0 whose input pixels were never set: nothing to update (adam_dual_skip)
+      if (i4 < skip_end && __ldg(touched + (((unsigned)i4 / (unsigned)ld0) >> 7)) == 0u) continue;
+    }
     float4 p = *reinterpret_cast<const float4*>(a.p + i4);
     float pv[4] = {p.x, p.y, p.z, p.w};
     {
@@ -292,12 +296,37 @@ __global__ void __launch_bounds__(256) adam_dual_kernel(AdamArgs a) {
   }
 }
 
-void adam_dual(const AdamArgs& a, cudaStream_t s) {
+__global__ void __launch_bounds__(256) adam_dual_kernel(AdamArgs a) { adam_dual_body<false>(a, nullptr, 0, 1); }
+__global__ void __launch_bounds__(256) adam_dual_skip_kernel(AdamArgs a, const uint32_t* touched, long long skip_end, int ld0) {
+  adam_dual_body<true>(a, touched, skip_end, ld0);
+}
+
+static long long adam_blocks(const AdamArgs& a) {
   const long long n4 = (a.n_total - a.begin + 3) / 4;
-  if (n4 <= 0) return;
+  if (n4 <= 0) return 0;
   long long blocks = (n4 + 255) / 256;
   if (a.thin > 0 && blocks > a.thin) blocks = a.thin;
-  launch_chain(adam_dual_kernel, dim3((unsigned)blocks), dim3(256), 0, s, a);
+  return blocks;
+}
+void adam_dual(const AdamArgs& a, cudaStream_t s) {
+  const long long blocks = adam_blocks(a);
+  if (blocks > 0) launch_chain(adam_dual_kernel, dim3((unsigned)blocks), dim3(256), 0, s, a);
+}
+void adam_dual_skip(const AdamArgs& a, const uint32_t* touched, long long skip_end, int ld0, cudaStream_t s) {
+  if (touched == nullptr || ld0 <= 0 || a.begin >= skip_end || skip_end >= (1ll << 32)) { adam_dual(a, s); return; }
+  const long long blocks = adam_blocks(a);
+  if (blocks > 0) launch_chain(adam_dual_skip_kernel, dim3((unsigned)blocks), dim3(256), 0, s, a, touched, skip_end, ld0);
+}
+
+__global__ void touch_rows_kernel(const uint32_t* km0, const uint32_t* km1, int words, int tiles, uint32_t* touched) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= tiles) return;
+  uint32_t any = 0;
+  for (int w = 0; w < words; ++w) any |= km0[(long long)t * words + w] | km1[(long long)t * words + w];
+  if (any) touched[t] = 1u;          // monotone: never cleared by a batch
+}
+void touch_rows(const uint32_t* km0, const uint32_t* km1, int words, int tiles, uint32_t* touched, cudaStream_t s) {
+  touch_rows_kernel<<<(tiles + 255) / 256, 256, 0, s>>>(km0, km1, words, tiles, touched);
 }
 
 // ------------------------------------------------------------------ data parallel: sharded reduce + dual Adam
@@ -1034,6 +1063,8 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(latent_metric_kernel);
   MAGIC_MAX_CARVEOUT(latent_backward_kernel);
   MAGIC_MAX_CARVEOUT(adam_dual_kernel);
+  MAGIC_MAX_CARVEOUT(adam_dual_skip_kernel);
+  MAGIC_MAX_CARVEOUT(touch_rows_kernel);
   MAGIC_MAX_CARVEOUT(adam_dual_sharded_kernel);
   MAGIC_MAX_CARVEOUT(push_range_kernel);
   MAGIC_MAX_CARVEOUT(mask_unowned_kernel);

@@ -1,6 +1,8 @@
 """Parity of the CUDA engine (through the C ABI) against the float64 oracle on identical weights, inputs,
 labels and noise.  Tolerances are BASELINE.json's: 1e-4 (fp32 mode) and 2e-2 (bf16 mode), applied as relative
 L2 error per tensor (tests/util.py)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -190,3 +192,49 @@ def test_packed_first_layer_operand_matches_bf16_planes(precision, monkeypatch):
         assert rel_l2(a[1], b[1]) < tol
         for k in a[4]:
             assert rel_l2(a[4][k], b[4][k]) < tol, k
+
+
+@pytest.mark.skipif(os.environ.get("MAGIC_TEST_EXPERIMENTAL", "0") == "0",
+                    reason="option not yet validated on a GPU (off by default); run with MAGIC_TEST_EXPERIMENTAL=1")
+def test_untouched_first_layer_rows_can_be_left_alone():
+    """set_option("skip_untouched_rows", 1): rows of W0 whose 128 input pixels no batch has set so far have zero
+    gradients and zero Adam moments in both optimisers, so leaving them alone must give the same bits as updating them:
+    parameters, both optimisers' slots and the losses after several steps on fresh batches.  A restored optimiser state
+    (set_slot) makes every row count as touched."""
+    from magic_b200 import _lib
+    from magic_b200.engine import Engine
+    ocfg = oracle_config(latent=20, encoder_neurons=[120, 72], decoder_neurons=[88, 104], n_input=4096)
+    engs = [Engine(engine_config_from_oracle(ocfg, 96, "bf16", seed=5)) for _ in range(2)]
+    engs[1].set_params(engs[0].get_params())
+    engs[1].set_option("skip_untouched_rows", 1)
+    union = np.zeros(4096, bool)
+    for step in range(4):
+        out = []
+        for e in engs:
+            e.generate_batch(3, step)
+            out.append(e.step()[0].cpu().numpy())
+        assert np.array_equal(out[0], out[1]), step
+        X, _ = engs[1].export_batch()
+        union |= X.cpu().numpy().reshape(96, 4096, 3).any(axis=(0, 2))
+    tiles = union.reshape(32, 128).any(axis=1)
+    assert 0 < tiles.sum() < 32, tiles                   # the canvas margins stay empty: some rows really were skipped
+    for n in engs[0].param_names:
+        assert np.array_equal(engs[0].get_param(n), engs[1].get_param(n)), n
+        for which in (1, 2):
+            if engs[0].param_opts[n] & which:
+                for sl in (_lib.SLOT_M, _lib.SLOT_V):
+                    assert np.array_equal(engs[0].get_slot(which, sl, n), engs[1].get_slot(which, sl, n)), (n, which, sl)
+    w0 = engs[1].param_names[0]
+    m = engs[1].get_slot(1, _lib.SLOT_M, w0)
+    assert not m[:128][~union[:128]].any()               # never-set pixels: moments still exactly zero
+    # a restored state may hold non-zero moments anywhere: after set_slot nothing is skipped
+    m2 = m.copy(); m2[0, :] = 1e-3
+    for e in engs:
+        e.set_slot(1, _lib.SLOT_M, w0, m2)
+        e.generate_batch(3, 9)
+        e.step()
+    assert np.array_equal(engs[0].get_param(w0), engs[1].get_param(w0))
+    assert np.array_equal(engs[0].get_slot(1, _lib.SLOT_M, w0), engs[1].get_slot(1, _lib.SLOT_M, w0))
+    assert engs[1].get_slot(1, _lib.SLOT_M, w0)[0].any()
+    for e in engs:
+        e.close()
