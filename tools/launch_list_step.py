@@ -20,7 +20,7 @@ for r in rows:
         out.append(dict(zip(hdr, r)))
 ends = [i for i, d in enumerate(out) if "adam_dual" in d["Kernel Name"] and int(d["Grid Size"].strip("()").split(",")[0]) > 1000]
 lo, hi = ends[n - 1] + 1, ends[n] + 1
-step = [d for d in out[lo:hi] if not any(k in d["Kernel Name"] for k in ("generate_pairs", "kmask", "klist", "schedule", "pairs_bits"))]
+step = [d for d in out[lo:hi] if not any(k in d["Kernel Name"] for k in ("generate_pairs", "kmask", "klist", "schedule", "pairs_bits", "touch_rows"))]
 tot = sum(float(d["Metric Value"]) for d in step) / 1000
 print("step %d of %s: %d launches, %.1f us summed (serialised, cold caches: shares, not absolutes)" % (n, sys.argv[1], len(step), tot))
 for d in step:
