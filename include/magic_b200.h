@@ -139,7 +139,8 @@ int magic_swap_batch(magic_handle* h);
  *   magic_set_option(h, "skip_untouched_rows", 1)  EXPERIMENTAL, default 0, one GPU: the Adam pass leaves rows of the
  *                                                first-layer matrix alone whose 128-pixel input tile no batch has set so
  *                                                far (gradient and both moments are exactly 0 there, so the update is
- *                                                p - lr * 0 / (0 + eps) = p); magic_set_slot makes every row count as set
+ *                                                p - lr * 0 / (0 + eps) = p); switch it on before the first batch is
+ *                                                loaded (later, or after magic_set_slot, every row counts as set)
  *   magic_input_density                          fraction of stages with a set pixel in the loaded batch:
  *                                                out2[0] forward GEMM, out2[1] weight-gradient GEMM (synchronises) */
 int magic_set_option(magic_handle* h, const char* name, int32_t value);

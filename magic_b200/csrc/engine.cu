@@ -775,7 +775,8 @@ void Engine::build_kmasks(InBuf& b, cudaStream_t s) {
   build_kmask_fwd(b.xb3, xb_ld_, 3 * B, km_fwd_kb_, b.kmask, km_fwd_words_, s);
   for (int g = 0; g < 2; ++g)
     build_kmask_wgrad(b.xb3 + (size_t)g * B * xb_ld_, xb_ld_, 2 * B, km_wg_tiles_, b.kmask + km_wg_off_[g], km_wg_words_, s);
-  touch_rows(b.kmask + km_wg_off_[0], b.kmask + km_wg_off_[1], km_wg_words_, km_wg_tiles_, touched_, s);
+  if (skip_untouched_) touch_rows(b.kmask + km_wg_off_[0], b.kmask + km_wg_off_[1], km_wg_words_, km_wg_tiles_, touched_, s);
+  else untracked_batches_ = true;      // the flags missed this batch: switching the option on later starts from "all set"
   // the plans that read this buffer get their work items re-dealt by the new maps (GemmArgs.order)
   const int alt = &b == &in_[1] ? 1 : 0;
   gemm_schedule(alt ? fwd_enc0_alt_ : fwd_enc_[0], s);
@@ -785,7 +786,13 @@ void Engine::build_kmasks(InBuf& b, cudaStream_t s) {
 std::string Engine::set_option(const char* name, int value) {
   if (!name) return "set_option: null name";
   if (std::string(name) == "skip_zero_stages") { skip_zero_ = value != 0; return ""; }
-  if (std::string(name) == "skip_untouched_rows") { skip_untouched_ = value != 0; return ""; }
+  if (std::string(name) == "skip_untouched_rows") {
+    // the flags are only maintained while the option is on; batches loaded without it may have set any pixel
+    if (value != 0 && !skip_untouched_ && untracked_batches_)
+      MAGIC_CUDA(cudaMemsetAsync(touched_, 0xFF, sizeof(uint32_t) * (size_t)km_wg_tiles_, stream));
+    skip_untouched_ = value != 0;
+    return "";
+  }
   return std::string("set_option: unknown option ") + name;
 }
 std::string Engine::input_density(double* out2) {

@@ -136,6 +136,7 @@ class Engine {
   bool bits_a_ = true;              // first-layer GEMMs read the packed rows (BitsA); MAGIC_BITS_A=0: the bf16 planes
   bool skip_zero_ = true;           // ... and skip operand stages without a set pixel (MAGIC_SKIP_ZERO=0 / set_option: all stages)
   bool skip_untouched_ = false;     // set_option("skip_untouched_rows"): Adam leaves W0 rows alone whose pixels were never set
+  bool untracked_batches_ = false;  // a batch was loaded while the option was off (its pixels are not in touched_)
   uint32_t* touched_ = nullptr;     // [km_wg_tiles_] != 0 once a tile of 128 input pixels was set in any batch (AdamArgs.touched)
   int km_fwd_tiles_ = 0, km_fwd_words_ = 0, km_fwd_kb_ = 0;     // map geometry: forward (rows of 128 packed rows x k-blocks of 64 pixels)
   int km_wg_tiles_ = 0, km_wg_words_ = 0;                       // weight gradient (tiles of 128 pixels x k-blocks of 64 batch rows)
