@@ -8,18 +8,24 @@
 One "step" = TangoEncoder.partial_fit on one batch: forward of three encoder streams + decoder, both backward
 passes (cost, training_loss), both Adam updates (8c/vae.py:379-405).  Default workload at N=1 is BASELINE.json
 configs[1]: experiment 8d (encoder 500x4, latent 200, cosine metric) at batch 4096 per GPU; with N GPUs the
-per-GPU batch stays fixed (weak scaling) and gradients are all-reduced over NCCL inside the step.
+per-GPU batch stays fixed (weak scaling) and the gradient exchange runs inside the step.
 
-Printed line (rank 0): value = pairs/s of the step with its inputs resident in HBM (two generated batches kept in
-the engine's input buffers and alternated; `with_generator` = the loop that also generates a new batch every step).
-The images are binary and mostly empty, the engine keeps them packed and its first-layer GEMMs skip operand stages
-without a set pixel (bit-identical results); `dense_inputs` = the same loop with that switched off (every stage
-multiplied), `input_density` = the fraction of stages that hold a set pixel;
-e2e = pairs/s of the training loop fed from pinned HOST memory, H2D of every step's inputs + step + D2H of the
-losses inside the timed region: headline = the dataset path (bit-packed lock/key pairs + labels through
-magic_feed_pairs_bits_host, one batch ahead; the rotated lock is made on the device as the reference's pipeline makes
-it on the CPU); e2e.float32_feed = magic_partial_fit_host with X[B,120000] fp32 exactly as main.py feeds partial_fit
-(PCIe-bound: 480 KB per pair), e2e.uint8_feed = the same array as uint8.
+Printed line (rank 0):
+  value     pairs/s of the training loop with a NEW batch every step, produced on the device by the generator (row
+            N1) inside the timed region: generator + zero-stage maps + k-block lists + work order + the step.  The
+            generator's shapes are fitted to the reference's images (tests/test_generator.py holds the operand-stage
+            density of a generated batch within +-0.05 of real batches: 0.94 / 0.96), so zero-stage skipping earns
+            here what it would earn on the reference's data.
+  roofline  the dominant kernel: achieved = EXECUTED tensor FLOPs (algorithmic FLOPs x the fraction of operand stages
+            that are multiplied) / its average launch time; frac <= 1.  The dict also carries what explains `value`:
+            resident_value (two batches kept in HBM and alternated: no per-batch kernels), dense_value (every stage
+            multiplied), density, step_frac_of_peak (model FLOPs of the whole step / sustained bf16 peak),
+            issued_over_algorithmic, precision_modes (the 1e-4 "fp32" mode's throughput), configs (the other
+            BASELINE.json configs at this N), dp_parity (N > 1: a small data-parallel step against the CPU oracle).
+  e2e       the same metric through the public API with HOST inputs: OverlapDataset (the reference's real image
+            pairs, tests/golden/overlap_micro_100.npz) -> device_batches (per-step host gather into pinned memory,
+            H2D one batch ahead) -> TangoEncoder.partial_fit -> five Python floats per step.
+            e2e.float32_feed = partial_fit(X[B,120000] float32) exactly as the reference's main.py feeds it.
 """
 from __future__ import annotations
 
@@ -50,7 +56,8 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=0, help="pairs per GPU per step (0 = the config's)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="host-fed steps to time (0 = min(steps, 8))")
-    ap.add_argument("--cpu-sample", type=int, default=256, help="pairs per CPU-baseline step")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="pairs per CPU-baseline step (0 = the full per-GPU batch)")
+    ap.add_argument("--no-extra-legs", action="store_true", help="skip the fp32-mode, other-config and dp-parity legs")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -73,7 +80,7 @@ def workload_name(exp, batch, n):
 # --------------------------------------------------------------------------- CPU legs (oracle as the timed baseline)
 def cpu_step_timer(exp: str, sample: int, steps: int, warmup: int, budget_s: float):
     """Times the float32 CPU restatement of the reference step (oracle/tango_oracle.py) on all host threads.
-    Returns (pairs_per_s, ms_per_step, cores, sample)."""
+    Returns (pairs_per_s from the MEDIAN step, median ms_per_step, cores, sample, steps timed)."""
     import torch
     from oracle import tango_oracle as orc
     cores = os.cpu_count() or 1
@@ -88,7 +95,9 @@ def cpu_step_timer(exp: str, sample: int, steps: int, warmup: int, budget_s: flo
     t0 = time.perf_counter()
     state.step(*batch)
     first = time.perf_counter() - t0
-    # keep the whole run inside the budget: shrink the sample if the first step says it will not fit
+    # keep the whole run inside the budget: fewer timed steps first (never below 3), then a smaller sample
+    while steps > 3 and first * (steps + warmup) > budget_s:
+        steps -= 1
     while sample > 32 and first * (steps + warmup) > budget_s:
         sample //= 2
         batch = orc.synthetic_batch(sample, cfg.latent, seed=1, dtype=torch.float32)
@@ -97,11 +106,13 @@ def cpu_step_timer(exp: str, sample: int, steps: int, warmup: int, budget_s: flo
         first = time.perf_counter() - t0
     for _ in range(max(0, warmup - 1)):
         state.step(*batch)
-    t0 = time.perf_counter()
+    times = []
     for _ in range(steps):
+        t0 = time.perf_counter()
         state.step(*batch)
-    dt = time.perf_counter() - t0
-    return sample * steps / dt, dt / steps * 1e3, cores, sample
+        times.append(time.perf_counter() - t0)
+    med = sorted(times)[len(times) // 2]
+    return sample / med, med * 1e3, cores, sample, steps
 
 
 def run_reference(args):
@@ -109,11 +120,15 @@ def run_reference(args):
     if rank != 0:
         return
     batch = args.batch or DEFAULT_BATCH[args.exp]
-    v, ms, cores, sample = cpu_step_timer(args.exp, args.cpu_sample, args.steps, max(1, args.warmup), 240.0)
-    what = ("float32 torch-CPU restatement of %s/vae.py (oracle/tango_oracle.py), full step "
-            "(fwd, 2 bwd, 2 Adam) on a %d-pair sample of the batch, %d threads" % (args.exp, sample, cores))
+    # the full batch, 3 warm-up + >= 10 timed steps, median (the budget trims steps, then the
+    # sample, only if a step is so slow that the run would not end within a few minutes)
+    v, ms, cores, sample, steps = cpu_step_timer(args.exp, args.cpu_sample or batch, max(args.steps, 3), max(1, args.warmup), 300.0)
+    what = ("float32 torch-CPU restatement of %s/vae.py (oracle/tango_oracle.py), full step (fwd, 2 bwd, 2 Adam) on %s, "
+            "median of %d steps, %d threads"
+            % (args.exp, "the full %d-pair batch" % batch if sample == batch else "a %d-pair sample of the %d-pair batch" % (sample, batch),
+               steps, cores))
     line = {
-        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args.exp, batch, args.gpus), "experiment": args.exp,
@@ -199,39 +214,148 @@ class ClockSampler:
 
 # --------------------------------------------------------------------------- roofline bookkeeping
 def algorithmic_work(cfg, B, early_adam=False, fused_wgrad=False):
-    """tag -> ('tensor', FLOPs per launch) or ('hbm', bytes per launch): unpadded, un-split."""
+    """tag -> ('tensor', FLOPs per launch, FLOPs of it that zero-stage skipping applies to) or ('hbm', bytes per
+    launch, 0): unpadded, un-split."""
     D, H0, Hl = cfg.D, cfg.encoder_neurons[0], cfg.decoder_neurons[1]
     enc = list(cfg.encoder_neurons)
     n_enc = D * enc[0] + enc[0] + sum(a * b + b for a, b in zip(enc[:-1], enc[1:])) + 2 * (enc[-1] * cfg.latent + cfg.latent)
     dec = list(cfg.decoder_neurons)
     n_dec = cfg.latent * dec[0] + dec[0] + dec[0] * dec[1] + dec[1] + dec[1] * D + D
     n_early = (dec[1] * D + D) if fused_wgrad else n_dec
-    # weight gradients of the small layers; on one GPU in bf16 mode they are extra problems of the first-layer launch
+    # weight gradients of the small layers; on one GPU they are extra problems of the first-layer launch
     small_wg = 2.0 * B * (dec[0] * dec[1] + cfg.latent * dec[0]) + 2.0 * 4 * B * (
         enc[-1] * 2 * cfg.latent + sum(a * b for a, b in zip(enc[:-1], enc[1:])))
+    fwd0, wg0 = 2.0 * 3 * B * D * H0, 2.0 * 4 * B * D * H0
     return {
-        "gemm.fwd_enc0": ("tensor", 2.0 * 3 * B * D * H0),
-        "gemm.wgrad_enc0": ("tensor", 2.0 * 4 * B * D * H0 + (small_wg if fused_wgrad else 0.0)),
-        "gemm.fwd_dec_out_bce": ("tensor", 2.0 * B * Hl * D),
-        "gemm.wgrad_dec_out": ("tensor", 2.0 * B * Hl * D),
-        "gemm.dgrad_dec_out": ("tensor", 2.0 * B * Hl * D),
+        "gemm.fwd_enc0": ("tensor", fwd0, fwd0),
+        "gemm.wgrad_enc0": ("tensor", wg0 + (small_wg if fused_wgrad else 0.0), wg0),
+        "gemm.fwd_dec_out_bce": ("tensor", 2.0 * B * Hl * D, 0.0),
+        "gemm.wgrad_dec_out": ("tensor", 2.0 * B * Hl * D, 0.0),
+        "gemm.dgrad_dec_out": ("tensor", 2.0 * B * Hl * D, 0.0),
         # fused dual Adam: encoder params read p,g1,g2,m1,v1,m2,v2 + write p,m1,v1,m2,v2 (48 B) + bf16 shadow (2 B);
         # decoder params read p,g1,m1,v1 + write p,m1,v1 (28 B) + shadow (2 B)
-        # (single GPU: the decoder range runs as its own launch "adam.decoder" under the encoder backward)
-        # (with the small wgrads folded into the last launch only the decoder's output layer is final early)
-        "adam.dual": ("hbm", 50.0 * n_enc + 30.0 * (n_dec - n_early if early_adam else n_dec)),
-        "adam.decoder": ("hbm", 30.0 * n_early),
+        # (single GPU: the decoder's output layer runs as its own launch "adam.decoder" under the encoder backward)
+        "adam.dual": ("hbm", 50.0 * n_enc + 30.0 * (n_dec - n_early if early_adam else n_dec), 0.0),
+        "adam.decoder": ("hbm", 30.0 * n_early, 0.0),
         # generator writes three packed planes (1 bit per pixel)
-        "input.generate": ("hbm", 3.0 * B * D / 8),
+        "input.generate": ("hbm", 3.0 * B * D / 8, 0.0),
     }
 
 
+def make_engine(exp, B, precision, rank, world, dev):
+    """The experiment directory's own model class (experiments/<exp>/vae.py: TangoEncoder, the drop-in for the
+    reference's <exp>/vae.py) -> (engine config, its engine, the model)."""
+    import importlib
+    mod = importlib.import_module("experiments.%s.vae" % exp)
+    vae = mod.TangoEncoder(sess=None, precision=precision, batch_size=B, rank=rank, world=world, device=dev, seed=0,
+                           verbose=False)
+    if world > 1:
+        vae.engine.comm_init_from_process_group()
+    return vae.config, vae.engine, vae
+
+
+class Timer:
+    """CUDA-event timing of a loop on the current stream, barrier + synchronize on both sides, max over ranks."""
+
+    def __init__(self, world, dev):
+        self.world, self.dev = world, dev
+
+    def barrier(self):
+        import torch
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, ms: float) -> float:
+        import torch
+        if self.world == 1:
+            return ms
+        import torch.distributed as dist
+        t = torch.tensor([ms], dtype=torch.float64, device=self.dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def time(self, fn, n: int, wall: bool = False) -> float:
+        """ms for n calls of fn(i); with wall=True the larger of the device and the host-side time (host-fed loops)."""
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        for i in range(n):
+            fn(i)
+        e1.record()
+        self.barrier()
+        ms = e0.elapsed_time(e1)
+        if wall:
+            ms = max(ms, (time.perf_counter() - t0) * 1e3)
+        return self.max_over_ranks(ms)
+
+
+def generator_loop(eng, tm, n, warm, step0):
+    """ms per step of: generate a new batch (side stream, under the previous step's backward) + step."""
+    for i in range(warm):
+        eng.generate_batch(0, step0 + i)
+        eng.step()
+
+    def one(i):
+        eng.generate_batch(0, step0 + warm + i)
+        eng.step()
+    return tm.time(one, n) / n
+
+
+def dp_parity_check(rank, world, dev):
+    """N > 1: one data-parallel step of a reduced geometry (fused reduce-scatter path, fp32 mode) against the
+    full-batch float64 CPU oracle, on the very process group the timed run uses.  Returns {max_rel_err, tol, ...}
+    (rank 0's numbers; every rank takes part).  bench.py's CPU legs may use the oracle (test infrastructure)."""
+    import numpy as np
+    import torch
+    from magic_b200.engine import Engine, EngineConfig
+    from oracle import tango_oracle as orc
+    ocfg = orc.OracleConfig(encoder_neurons=[120, 72], decoder_neurons=[88, 104], n_input=1600, latent=20)
+    Bg = 32 * world
+    state = orc.OracleState(ocfg, seed=0)
+    xl, xr, xk, y, eps = orc.synthetic_batch(Bg, ocfg.latent, seed=1, n_input=ocfg.n_input)
+    n = Bg // world
+    sl = slice(rank * n, (rank + 1) * n)
+    eng = Engine(EngineConfig(D=ocfg.n_input, encoder_neurons=tuple(ocfg.encoder_neurons), decoder_neurons=tuple(ocfg.decoder_neurons),
+                              latent=ocfg.latent, precision="fp32", batch=n, batch_global=Bg, rank=rank, world=world, seed=0),
+                 device=dev)
+    eng.comm_init_from_process_group()
+    eng.set_params({k: v.to(torch.float32).numpy() for k, v in state.params.items() if k not in orc.DEAD_PARAMS})
+    eng.load_interleaved(orc.interleave(xl[sl], xr[sl], xk[sl]).to(torch.float32))
+    losses, _ = eng.step(labels=y[sl].to(torch.float32), eps3=eps[:, sl].to(torch.float32), apply=False)
+    got_l = losses.cpu().numpy().astype(np.float64)
+    names1 = ("encoder_h0_weights", "decoder_out_mean_weights", "decoder_b1_biases")
+    names2 = ("encoder_h0_weights", "encoder_out_log_sigma_weights")
+    got1 = {k: eng.get_grad(1, k).astype(np.float64) for k in names1}     # collective: every rank calls
+    got2 = {k: eng.get_grad(2, k).astype(np.float64) for k in names2}
+    eng.close()
+    if rank != 0:
+        return None
+    out, g1, g2 = state.grads(xl, xr, xk, y, eps)
+    errs = {}
+    for i, k in enumerate(orc.LOSS_KEYS):
+        errs["loss." + k] = abs(got_l[i] - float(out[k])) / abs(float(out[k]))
+    for which, got, ref in ((1, got1, g1), (2, got2, g2)):
+        for k, v in got.items():
+            r = ref[k].numpy()
+            errs["g%d.%s" % (which, k)] = float(np.linalg.norm(v - r) / np.linalg.norm(r))
+    worst = max(errs, key=errs.get)
+    return {"max_rel_err": errs[worst], "worst": worst, "tol": 1e-4, "ok": bool(errs[worst] <= 1e-4), "world": world,
+            "what": "one fp32-mode data-parallel step (fused reduce-scatter path) of a reduced geometry, global batch %d, "
+                    "vs the full-batch float64 CPU oracle: 5 losses + 5 gradient tensors, relative L2" % Bg}
+
+
 # --------------------------------------------------------------------------- the B200 arm
+PER_BATCH_LAUNCHES = 8     # generate_pairs + kmask_fwd + 2 x kmask_wg + 2 x (gemm_klist + gemm_schedule)
+
+
 def run_b200(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from magic_b200.engine import Engine, EngineConfig
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -253,166 +377,175 @@ def run_b200(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+    tm = Timer(world, dev)
+    pk = peaks()
+    extra = not args.no_extra_legs
+
+    # ---- N > 1: prove the data-parallel path before timing it (the driver's GPU test box has one GPU)
+    dp_parity = None
+    if world > 1 and extra:
+        dp_parity = dp_parity_check(rank, world, dev)
 
     B = args.batch or DEFAULT_BATCH[args.exp]
-    cfg = EngineConfig.experiment(args.exp, batch=B, precision=args.precision, rank=rank, world=world, seed=0)
-    eng = Engine(cfg, device=dev)
-    if world > 1:
-        eng.comm_init_from_process_group()
+    cfg, eng, args._vae = make_engine(args.exp, B, args.precision, rank, world, dev)
     st = eng.stats()
     K, W = args.steps, max(args.warmup, 3)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(ms: float) -> float:
-        if world == 1:
-            return ms
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # ---- leg 1 (headline `value`): the hot path with its inputs resident in HBM.  Two generated batches (983 MB of
-    # planes each at 8d/4096: together 15x the L2) stay in the engine's two input buffers and are alternated with
-    # magic_swap_batch, so every step reads a batch that the previous step evicted from L2.  No events inside.
-    eng.generate_batch(0, 0)
-    eng.generate_batch(0, 1)
-    # N > 1: the first few dozen steps of a process group run slow (lazily mapped CUDA-IPC peer memory is touched page by
-    # page, NCCL brings up its channels): 8 GPUs measured 2.29 ms per step over steps 6..105 and 1.90 ms over steps
-    # 41..240 (profiles/r01p_bench_n8*.json).  Those settling steps are run on top of the W warm-up steps, untimed.
+    # ---- leg 1 (headline `value`): a NEW generated batch every step, generator and per-batch map / list / work-order
+    # kernels inside the timed region.  N > 1: the first few dozen steps of a process group run slow (lazily mapped
+    # CUDA-IPC peer memory is touched page by page, NCCL brings up its channels: 2.29 vs 1.90 ms per step at 8 GPUs,
+    # profiles/r01p_bench_n8*.json); those settling steps run on top of the W warm-up steps, untimed.
     settle = 40 if world > 1 else 0
     for i in range(W + settle):
-        eng.swap_batch()
+        eng.generate_batch(0, i)
         eng.step()
     sampler = ClockSampler(local)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
     sampler.start()
-    e0.record()
-    for i in range(K):
-        eng.swap_batch()
-        losses, _ = eng.step()
-    e1.record()
-    barrier()
+
+    def head(i):
+        eng.generate_batch(0, 1000 + i)
+        head.losses, _ = eng.step()
+    ms_total = tm.time(head, K)
     clocks = sampler.stop()
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
-    launches_per_step = int(eng.stats().launches_last_step)
-    final_losses = losses.cpu().numpy().tolist()
+    launches_per_step = int(eng.stats().launches_last_step) + PER_BATCH_LAUNCHES
+    final_losses = head.losses.cpu().numpy().tolist()
     ms_step = ms_total / K
     value = B * world * K / (ms_total * 1e-3)
+    density = eng.input_density()
 
     # ---- leg 1b: the same loop with a CUDA-event pair around every launch (engine profile mode): per-kernel device
     # times for the roofline and the shares.  Kept out of the headline loop because an event between two kernels
     # disables their programmatic dependent launch overlap.
     Kp = max(3, min(K, 40))
     eng.profile(True)
-    eng.swap_batch()
+    eng.generate_batch(0, 5000)
     eng.step()
     eng.profile_report()          # warm the event pool, drop the warm-up record
-    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e2.record()
-    for i in range(Kp):
-        eng.swap_batch()
+
+    def prof(i):
+        eng.generate_batch(0, 5001 + i)
         eng.step()
-    e3.record()
-    barrier()
-    ms_step_events = max_over_ranks(e2.elapsed_time(e3)) / Kp
+    ms_step_events = tm.time(prof, Kp) / Kp
     rep = eng.profile_report()
     eng.profile(False)
 
-    # ---- leg 1c: the generator inside the loop (row N1): a NEW batch every step, produced on the device by the
-    # engine's generator on its own stream under the previous step's backward pass
-    Kg = max(3, min(K, 100))
+    # ---- leg 1c: two batches resident in HBM, alternated (no generator, no per-batch kernels inside the timed region)
+    Kr = max(3, min(K, 60))
+    eng.generate_batch(0, 7000)
+    eng.generate_batch(0, 7001)
     for i in range(3):
-        eng.generate_batch(0, 10 + i)
+        eng.swap_batch()
         eng.step()
-    e8, e9 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e8.record()
-    for i in range(Kg):
-        eng.generate_batch(0, 100 + i)
-        eng.step()
-    e9.record()
-    barrier()
-    ms_gen = max_over_ranks(e8.elapsed_time(e9)) / Kg
-    with_generator = {"value": B * world / (ms_gen * 1e-3), "unit": UNIT, "ms_per_step": ms_gen, "steps": Kg,
-                      "note": "new generated batch every step inside the timed region (generator kernel + step)"}
 
-    # ---- leg 1d: the same resident-input loop with every operand stage processed (no zero-stage skipping)
-    eng.swap_batch()
-    density = eng.input_density()
-    Kd = max(3, min(K, 60))
+    def resident(i):
+        eng.swap_batch()
+        eng.step()
+    ms_res = tm.time(resident, Kr) / Kr
+
+    # ---- leg 1d: the headline loop with every operand stage multiplied (no zero-stage skipping)
     eng.set_option("skip_zero_stages", 0)
-    for i in range(3):
-        eng.swap_batch()
-        eng.step()
-    e10, e11 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e10.record()
-    for i in range(Kd):
-        eng.swap_batch()
-        eng.step()
-    e11.record()
-    barrier()
-    ms_dense = max_over_ranks(e10.elapsed_time(e11)) / Kd
+    ms_dense = generator_loop(eng, tm, Kr, 3, 8000)
     eng.set_option("skip_zero_stages", 1)
-    dense_inputs = {"value": B * world / (ms_dense * 1e-3), "unit": UNIT, "ms_per_step": ms_dense, "steps": Kd,
-                    "note": "skip_zero_stages = 0: every 128x64 operand stage of the first layer is expanded and multiplied "
-                            "(what an input without empty regions would cost)"}
 
     # ---- roofline of the dominant kernel family (by summed device time in the timed region)
-    pk = peaks()
-    fused_wgrad = world == 1 and args.precision == "bf16" and os.environ.get("MAGIC_FUSE_WGRAD", "1") != "0"
+    fused_wgrad = world == 1 and os.environ.get("MAGIC_FUSE_WGRAD", "1") != "0"
     work = algorithmic_work(cfg, B, early_adam=(world == 1 and os.environ.get("MAGIC_EARLY_ADAM", "1") != "0"),
                             fused_wgrad=fused_wgrad)
+    skipping = os.environ.get("MAGIC_SKIP_ZERO", "1") != "0" and os.environ.get("MAGIC_BITS_A", "1") != "0"
     roof = None
     shares = {}
     tot_ms = sum(v[0] for v in rep.values()) or 1.0
-    for tag, (ms, n, _issued) in sorted(rep.items(), key=lambda kv: -kv[1][0]):
+    ranked = sorted(rep.items(), key=lambda kv: -kv[1][0])
+    for tag, (ms, n, _issued) in ranked:
         shares[tag] = round(ms / tot_ms, 4)
-    for tag, (ms, n, _issued) in sorted(rep.items(), key=lambda kv: -kv[1][0]):
-        # the generator runs on its own stream, spread under the backward pass at one CTA per SM: its event time is
-        # not exclusive, so the dominant kernel is taken from the step's own stream
-        if tag in work and n > 0 and tag not in ("input.generate", "adam.decoder"):   # side-stream kernels overlap
-            kind, amount = work[tag]
-            avg_s = ms / n * 1e-3
-            if kind == "tensor":
-                ach, peak, unit = amount / avg_s * 1e-12, pk["tf_sustained"], "TFLOP/s"
-            else:
-                ach, peak, unit = amount / avg_s * 1e-9, pk["hbm"], "GB/s"
-            traffic, traffic_src = None, None
-            try:
-                tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-                ent = tj.get("%s/%d/%s" % (args.exp, B, args.precision), {}).get(tag) if world == 1 else None
-                if ent:
-                    traffic, traffic_src = ent["bytes"], ent["source"]
-            except Exception:
-                traffic = None
-            roof = {"kernel": tag, "bound": kind, "achieved": round(ach, 2), "peak": peak, "unit": unit,
-                    "frac": round(ach / peak, 4), "traffic": traffic, "traffic_unit": "dram bytes per launch (ncu)", "traffic_source": traffic_src, "avg_launch_ms": round(ms / n, 5),
-                    "launches_timed": n, "measured_over": "%d steps with an event pair around every launch, run right "
-                    "after the timed region on the same inputs" % Kp, "peak_source": pk["source"] + (" (sustained)" if kind == "tensor" else ""),
-                    "algorithmic_per_launch": amount, "share_of_step": shares[tag]}
-            if tag in ("gemm.wgrad_enc0", "gemm.fwd_enc0") and os.environ.get("MAGIC_SKIP_ZERO", "1") != "0" \
-                    and os.environ.get("MAGIC_BITS_A", "1") != "0":
-                f = density[1] if tag == "gemm.wgrad_enc0" else density[0]
-                roof["executed_fraction"] = round(f, 4)
-                roof["achieved_executed"] = round(ach * f, 2)
-                roof["frac_executed"] = round(ach * f / peak, 4)
-                roof["note"] = ("achieved counts the algorithmic (dense) FLOPs of SURVEY 8.4; %.1f %% of this GEMM's operand "
-                                "stages hold a set pixel and are multiplied, the rest are skipped as exact zeros, so the "
-                                "tensor pipe sustains achieved_executed (a fraction > 1 of the dense roofline is the "
-                                "sparsity of the images, not a faster pipe)" % (100 * f))
-            break
+    for tag, (ms, n, _issued) in ranked:
+        # side-stream kernels (generator, per-batch maps, the decoder's early Adam) overlap the step: their event times
+        # are not exclusive, so the dominant kernel is taken from the step's own stream
+        if tag not in work or n == 0 or tag.startswith("input.") or tag == "adam.decoder":
+            continue
+        kind, amount, skippable = work[tag]
+        avg_s = ms / n * 1e-3
+        traffic, traffic_src = None, None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            ent = tj.get("%s/%d/%s" % (args.exp, B, args.precision), {}).get(tag) if world == 1 else None
+            if ent:
+                traffic, traffic_src = ent["bytes"], ent["source"]
+        except Exception:
+            traffic = None
+        if kind == "tensor":
+            f = (density[1] if tag == "gemm.wgrad_enc0" else density[0]) if (skipping and skippable) else 1.0
+            executed = amount - skippable * (1.0 - f)
+            ach, peak, unit = executed / avg_s * 1e-12, pk["tf_sustained"], "TFLOP/s"
+        else:
+            f, executed = 1.0, amount
+            ach, peak, unit = amount / avg_s * 1e-9, pk["hbm"], "GB/s"
+        roof = {"kernel": tag, "bound": "tensor" if kind == "tensor" else "hbm", "achieved": round(ach, 2), "peak": peak,
+                "unit": unit, "frac": round(ach / peak, 4), "traffic": traffic,
+                "traffic_unit": "dram bytes per launch (ncu)", "traffic_source": traffic_src,
+                "avg_launch_ms": round(ms / n, 5), "launches_timed": n,
+                "measured_over": "%d steps of the headline loop with an event pair around every launch" % Kp,
+                "peak_source": pk["source"] + (" (sustained)" if kind == "tensor" else ""),
+                "algorithmic_per_launch": amount, "executed_per_launch": executed, "executed_fraction_of_main_problem": round(f, 4),
+                "dense_equivalent_frac": round(amount / avg_s * (1e-12 if kind == "tensor" else 1e-9) / peak, 4),
+                "share_of_step": shares[tag],
+                "note": "achieved = executed FLOPs / launch time: the main problem's algorithmic FLOPs (SURVEY 8.4) times the "
+                        "fraction of its 128x64 operand stages that hold a set pixel (the others are exact zeros and are "
+                        "skipped), plus the dense appended small-layer problems; dense_equivalent_frac counts the skipped "
+                        "stages as if they had been multiplied"}
+        break
     model_tflops = value / world * st.model_flops_per_pair * 1e-12
+    if roof is None:
+        roof = {"kernel": None, "bound": "tensor", "achieved": round(model_tflops, 2), "peak": pk["tf_sustained"],
+                "unit": "TFLOP/s", "frac": round(model_tflops / pk["tf_sustained"], 4), "traffic": None}
+    roof.update({
+        "step_model_tflops_per_gpu": round(model_tflops, 1),
+        "step_frac_of_peak": round(model_tflops / pk["tf_sustained"], 4),
+        "step_frac_of_burst_peak": round(model_tflops / pk["tf_burst"], 4),
+        "issued_over_algorithmic": round(st.gemm_flops_per_step / (st.model_flops_per_pair * B), 4),
+        "density_fwd": round(density[0], 4), "density_wgrad": round(density[1], 4),
+        "resident_value": round(B * world / (ms_res * 1e-3), 1), "resident_ms_per_step": round(ms_res, 4),
+        "dense_value": round(B * world / (ms_dense * 1e-3), 1), "dense_ms_per_step": round(ms_dense, 4),
+        "ms_per_step_with_per_launch_events": round(ms_step_events, 4),
+        "legs": "value: new generated batch every step (generator + per-batch kernels timed); resident_value: two batches kept "
+                "in HBM and alternated, %d steps; dense_value: the headline loop with skip_zero_stages = 0, %d steps" % (Kr, Kr),
+    })
+    if dp_parity is not None:
+        roof["dp_parity"] = dp_parity
 
-    # ---- leg 2: end to end through the host-buffer C-ABI call, pinned host inputs
+    # ---- leg 2: end to end through the public API, HOST inputs: the reference's real image pairs (OverlapDataset) ->
+    # device_batches (per-step host gather into pinned slots, H2D one batch ahead) -> TangoEncoder.partial_fit
     e2e = None
     if not args.no_e2e:
-        Ke = args.e2e_steps or min(K, 8)
+        from magic_b200.overlap_input import OverlapDataset, device_batches
+        g = np.load(os.path.join(ROOT, "tests", "golden", "overlap_micro_100.npz"))
+        side = int(round(cfg.D ** 0.5))
+        Lr = np.unpackbits(g["lock_bits"], axis=1)[:, :cfg.D]
+        Kr_ = np.unpackbits(g["key_bits"], axis=1)[:, :cfg.D]
+        areas = np.load(os.path.join(ROOT, "tests", "golden", "overlap_areas.npy"))[:len(Lr)].astype(np.float32)
+        ds = OverlapDataset.from_arrays(Lr, Kr_, areas, image_size=side)
+        vae = args._vae
+        Ke = args.e2e_steps or max(8, min(K, 50))
+        it = device_batches(vae, ds, seed=rank, steps=Ke + 4)
+        for _ in range(3):
+            b = next(it)
+            vae.partial_fit(b, overlap_areas=b.labels)
+        real_density = eng.input_density()
+
+        def fed(i):
+            b = next(it)
+            fed.out = vae.partial_fit(b, overlap_areas=b.labels)      # returns Python floats: the stream is waited for
+        ms_fed = tm.time(fed, Ke, wall=True)
+        wpr = ds.lock_bits.shape[1]
+        e2e = {"value": B * world * Ke / (ms_fed * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(2 * B * wpr * 4 + 2 * B * 4), "d2h_bytes_per_step": 20,
+               "steps": Ke, "ms_per_step": ms_fed / Ke,
+               "api": "OverlapDataset(real overlap_micro pairs, sampled with replacement) -> device_batches: per-step host gather "
+                      "(index_select into pinned slots) + magic_feed_pairs_bits_host one batch ahead -> TangoEncoder.partial_fit "
+                      "(magic_step; rotated lock made on the device) -> 5 Python floats every step",
+               "data": "real: tests/golden/overlap_micro_100.npz + OVERLAP_AREAS[:100]",
+               "input_density": [round(real_density[0], 4), round(real_density[1], 4)]}
+        # the reference-signature call: partial_fit(X[B,120000] float32) from pinned host memory (PCIe-bound)
         X_dev, y_dev = eng.export_batch()
         X_host = torch.empty((B, 3 * cfg.D), dtype=torch.float32, pin_memory=True)
         y_host = torch.empty((B,), dtype=torch.float32, pin_memory=True)
@@ -421,88 +554,69 @@ def run_b200(args):
         del X_dev
         torch.cuda.synchronize()
         Xn, yn = X_host.numpy(), y_host.numpy()
-        for _ in range(2):
-            eng.partial_fit_host(Xn, yn)
-        barrier()
-        t0 = time.perf_counter()
-        e4, e5 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e4.record()
-        for _ in range(Ke):
-            hl, _ = eng.partial_fit_host(Xn, yn)      # H2D X+labels, step, D2H losses, stream sync
-        e5.record()
-        torch.cuda.synchronize()
-        ms_e2e = max_over_ranks(max(e4.elapsed_time(e5), (time.perf_counter() - t0) * 1e3))
-        f32_feed = {"value": B * world * Ke / (ms_e2e * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": int(Xn.nbytes + yn.nbytes), "d2h_bytes_per_step": 20,
-                    "steps": Ke, "ms_per_step": ms_e2e / Ke,
-                    "api": "magic_partial_fit_host(X[B,120000] fp32 pinned, overlap_areas[B]) -> 5 losses",
-                    "note": "the reference's partial_fit(X) signature unchanged: 480 KB per pair, PCIe-bound (%.0f GB/s)"
-                            % ((Xn.nbytes + yn.nbytes) / (ms_e2e / Ke * 1e-3) * 1e-9)}
-        e2e = {}
+        eng.partial_fit_host(Xn, yn)
+        Kf = 4
+        ms_f32 = tm.time(lambda i: eng.partial_fit_host(Xn, yn), Kf, wall=True)
+        e2e["float32_feed"] = {"value": B * world * Kf / (ms_f32 * 1e-3), "unit": UNIT,
+                               "h2d_bytes_per_step": int(Xn.nbytes + yn.nbytes), "d2h_bytes_per_step": 20, "steps": Kf,
+                               "ms_per_step": ms_f32 / Kf,
+                               "api": "magic_partial_fit_host(X[B,120000] fp32 pinned, overlap_areas[B]) -> 5 losses: the reference's "
+                                      "partial_fit(X) signature unchanged, 480 KB per pair, PCIe-bound (%.0f GB/s)"
+                                      % ((Xn.nbytes + yn.nbytes) / (ms_f32 / Kf * 1e-3) * 1e-9)}
+        del X_host
+    eng.close()
 
-        # same call with the compact feed the same signature accepts: uint8 X (feed_dict casts to the placeholder dtype)
-        X8 = torch.empty((B, 3 * cfg.D), dtype=torch.uint8, pin_memory=True)
-        X8.copy_(X_host.to(torch.uint8))
-        X8n = X8.numpy()
-        for _ in range(2):
-            eng.partial_fit_host(X8n, yn)
-        barrier()
-        e6, e7 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter()
-        e6.record()
-        for _ in range(Ke):
-            eng.partial_fit_host(X8n, yn)
-        e7.record()
-        torch.cuda.synchronize()
-        ms_u8 = max_over_ranks(max(e6.elapsed_time(e7), (time.perf_counter() - t0) * 1e3))
-        e2e["uint8_feed"] = {"value": B * world * Ke / (ms_u8 * 1e-3), "unit": UNIT, "ms_per_step": ms_u8 / Ke,
-                             "h2d_bytes_per_step": int(X8n.nbytes + yn.nbytes), "d2h_bytes_per_step": 20,
-                             "api": "magic_partial_fit_host_u8(X[B,120000] uint8 pinned, overlap_areas[B]) -> 5 losses"}
-        # the dataset path (row N2): bit-packed lock/key pairs + labels from pinned host memory, the rotated lock made on
-        # the device; batch n+1 is sent on the input stream while step n runs, losses read back every step
-        from magic_b200.overlap_input import pack_planes
-        Xi = X_host.view(B, cfg.D, 3)
-        lock_b = torch.from_numpy(pack_planes(Xi[:, :, 0].numpy()).view(np.int32)).pin_memory()
-        key_b = torch.from_numpy(pack_planes(Xi[:, :, 2].numpy()).view(np.int32)).pin_memory()
-        h_loss = torch.empty(5, dtype=torch.float32, pin_memory=True)
+    # ---- extra legs (short): the fp32-equivalent mode on the same workload, and the other BASELINE.json configs
+    precision_modes, configs = {}, {}
+    if extra:
+        def short_leg(exp, b, precision, steps=40):
+            c2, e2, _ = make_engine(exp, b, precision, rank, world, dev)
+            s2 = e2.stats()
+            ms = generator_loop(e2, tm, steps, 8 + settle, 0)
+            e2.close()
+            tf = b / (ms * 1e-3) * s2.model_flops_per_pair * 1e-12
+            return {"value": round(b * world / (ms * 1e-3), 1), "unit": UNIT, "ms_per_step": round(ms, 4), "steps": steps,
+                    "batch_per_gpu": b, "n_gpus": world, "precision": precision,
+                    "model_tflops_per_gpu": round(tf, 1), "frac_of_bf16_sustained_peak": round(tf / pk["tf_sustained"], 4),
+                    "issued_over_algorithmic": round(s2.gemm_flops_per_step / (s2.model_flops_per_pair * b), 4)}
+        if args.precision == "bf16":
+            # the 1e-4 mode: bf16x3 split operands (hi*hi + hi*lo + lo*hi; binary inputs need two terms), fp32 accumulate.
+            # Its peak: the same tensor pipe issues 2-3 bf16 MMAs per algorithmic one, so the bf16 peak / issued ratio; the
+            # TF32 cuBLAS peak (SURVEY 8.4 recipe: torch.matmul 8192^3, allow_tf32) is measured beside it for reference.
+            leg = short_leg(args.exp, B, "fp32", steps=30)
+            try:
+                torch.backends.cuda.matmul.allow_tf32 = True
+                a = torch.randn(8192, 8192, device=dev)
+                b_ = torch.randn(8192, 8192, device=dev)
+                best = 1e9
+                for _ in range(12):
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    torch.matmul(a, b_)
+                    e1.record()
+                    torch.cuda.synchronize()
+                    best = min(best, e0.elapsed_time(e1))
+                del a, b_
+                leg["tf32_cublas_peak_tflops"] = round(2 * 8192 ** 3 / (best * 1e-3) * 1e-12, 1)
+                leg["frac_of_tf32_peak"] = round(leg["model_tflops_per_gpu"] / leg["tf32_cublas_peak_tflops"], 4)
+            except Exception as ex:       # the peak is context, not a result
+                leg["tf32_cublas_peak_tflops"] = None
+                leg["tf32_peak_error"] = str(ex)[:80]
+            leg["issued_frac_of_bf16_sustained_peak"] = round(leg["frac_of_bf16_sustained_peak"] * leg["issued_over_algorithmic"], 4)
+            precision_modes["fp32"] = leg
+        others = [e for e in ("8e", "9a", "11a") if e != args.exp] + (["8c"] if world == 1 and args.exp != "8c" else [])
+        for e in others:
+            configs["%s@%d/gpu" % (e, DEFAULT_BATCH[e])] = short_leg(e, DEFAULT_BATCH[e], "bf16")
+        roof["precision_modes"] = precision_modes
+        roof["configs"] = configs
 
-        def packed_steps(n_steps, s0):
-            eng.feed_pairs_bits(lock_b, key_b, y_host, 1, s0)
-            for i in range(n_steps):
-                eng.feed_pairs_bits(lock_b, key_b, y_host, 1, s0 + i + 1, activate=False)
-                ld, _ = eng.step()
-                h_loss.copy_(ld, non_blocking=True)
-                torch.cuda.current_stream().synchronize()           # the caller reads the losses of every step
-                eng.swap_batch()
-        Kp8 = max(Ke, min(K, 50))
-        packed_steps(3, 0)
-        barrier()
-        e8, e9 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter()
-        e8.record()
-        packed_steps(Kp8, 100)
-        e9.record()
-        torch.cuda.synchronize()
-        ms_pk = max_over_ranks(max(e8.elapsed_time(e9), (time.perf_counter() - t0) * 1e3))
-        # headline = the training loop a user of the drop-in runs (experiments/*/main.py with a dataset,
-        # INTEGRATION.md section 2): input pipeline + partial_fit; the two array-fed forms of partial_fit beside it
-        e2e = {
-            "value": B * world * Kp8 / (ms_pk * 1e-3), "unit": UNIT,
-            "h2d_bytes_per_step": int(lock_b.numel() * 4 + key_b.numel() * 4 + y_host.numel() * 4), "d2h_bytes_per_step": 20,
-            "steps": Kp8, "ms_per_step": ms_pk / Kp8,
-            "api": "magic_feed_pairs_bits_host(lock/key bits [B,%d] u32 pinned, overlap_areas[B]) one batch ahead + magic_step "
-                   "-> 5 losses read back every step (rotated lock made on the device; OverlapDataset / device_batches path)"
-                   % lock_b.shape[1],
-            "float32_feed": f32_feed, "uint8_feed": e2e["uint8_feed"]}
-        del X8, X_host
-
-    # ---- CPU baseline beside it (rank 0, N=1 only)
+    # ---- CPU baseline beside it (rank 0, N=1 only): the full batch unless a step is too slow for the time budget
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, ms, cores, sample = cpu_step_timer(args.exp, args.cpu_sample, 8, 2, 40.0)
+        v, ms, cores, sample, nst = cpu_step_timer(args.exp, args.cpu_sample or B, 5, 1, 45.0)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "8 full steps of the float32 torch-CPU oracle on a %d-pair sample of the batch "
-                         "(%.0f ms/step, %d threads)" % (sample, ms, cores)}
+               "sample": "median of %d full steps of the float32 torch-CPU oracle on %s (%.0f ms/step, %d threads)"
+                         % (nst, "the full %d-pair batch" % B if sample == B else "a %d-pair sample of the batch" % sample, ms, cores)}
 
     if rank == 0:
         line = {
@@ -514,29 +628,16 @@ def run_b200(args):
                        "global_batch": B * world, "encoder": list(cfg.encoder_neurons), "latent": cfg.latent,
                        "metric_loss": cfg.metric + ("-reciprocal" if cfg.reciprocal else ""),
                        "parallelism": "dp%d" % world,
-                       "l2": "operands per step (weights, gradients and Adam state: %.0f MB streamed per step; packed input rows "
-                             "%.0f MB per batch) exceed the 126 MB L2; no flush needed"
-                             % ((50.0 * st.n_params2 + 30.0 * (st.n_params1 - st.n_params2)) / 1e6, 3 * B * cfg.D / 8 / 1e6),
+                       "l2": "no flush needed: %.0f MB of weights, gradients and Adam state streamed per step > 126 MB L2"
+                             % ((50.0 * st.n_params2 + 30.0 * (st.n_params1 - st.n_params2)) / 1e6),
                        "settling_steps": settle,
-                       "zero_stage_skipping": "on: first-layer operand stages (128x64 pixels) without a set pixel add exact "
-                                              "zeros and are skipped, results bit-identical; `dense_inputs` is the same loop with "
-                                              "every stage multiplied, `input_density` the fraction of stages that are not empty",
-                       "inputs": "two generated batches resident in HBM, alternated every step (magic_swap_batch); "
-                                 "`with_generator` times the loop that generates a new batch every step"},
-            "model_tflops_per_gpu": round(model_tflops, 1),
-            "frac_of_bf16_sustained_peak": round(model_tflops / pk["tf_sustained"], 4),
-            "with_generator": with_generator,
-            "dense_inputs": dense_inputs,
-            "input_density": {"forward": round(density[0], 4), "weight_gradient": round(density[1], 4),
-                              "what": "fraction of the first layer's 128x64 operand stages with a set pixel (generated batch)"},
-            "ms_per_step_with_per_launch_events": ms_step_events,
+                       "inputs": "a new generated batch every step, inside the timed region"},
             "roofline": roof, "kernel_time_shares": shares,
             "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
             "gpu_launches": launches_per_step * K, "gpu_launches_per_step": launches_per_step,
             "final_losses": final_losses,
         }
         os.write(json_fd, (json.dumps(line) + "\n").encode())
-    eng.close()
     if world > 1:
         dist.destroy_process_group()
 

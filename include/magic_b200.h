@@ -126,6 +126,10 @@ int magic_export_batch(magic_handle* h, float* d_x /* [B,3*D] or NULL */, float*
 /* Q14 fixed-point (cos, sin) of the rotation the generator applied to each lock, [B,2] int32: with them the rotated
  * plane and the label are reproducible bit for bit from the exported lock/key planes (tests/test_generator.py). */
 int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn);
+/* The sampled latents z = mu + sqrt(exp(log_sigma_sq)) * eps of the last step / forward call (8c/vae.py:363-371), device
+ * fp32 [3, B, L] in the stream order of d_eps3: lock, rot, key.  With zero head weights and biases z IS the N(0,1) draw
+ * that replaces tf.random_normal (8c/vae.py:367): the statistical test of the device RNG reads it through this call. */
+int magic_export_latents(magic_handle* h, float* d_z3);
 /* The engine keeps two input batches in HBM (the loaded one and the one before it).  magic_swap_batch makes the
  * previous one the loaded batch again without touching its data -- a held batch re-fed to partial_fit /
  * get_predictions, as 8c/main.py:66-80 does with its test batch; bench.py alternates two resident batches with it. */
@@ -136,11 +140,6 @@ int magic_swap_batch(magic_handle* h);
  * its weight gradient -- multiplies them.  The engine keeps them packed (1 bit per pixel) and skips every 128 x 64
  * operand stage without a set pixel: such a stage adds exact zeros, so results are bit-identical to processing it.
  *   magic_set_option(h, "skip_zero_stages", 0)  processes every stage (dense-input timing; default 1)
- *   magic_set_option(h, "skip_untouched_rows", 1)  EXPERIMENTAL, default 0, one GPU: the Adam pass leaves rows of the
- *                                                first-layer matrix alone whose 128-pixel input tile no batch has set so
- *                                                far (gradient and both moments are exactly 0 there, so the update is
- *                                                p - lr * 0 / (0 + eps) = p); switch it on before the first batch is
- *                                                loaded (later, or after magic_set_slot, every row counts as set)
  *   magic_input_density                          fraction of stages with a set pixel in the loaded batch:
  *                                                out2[0] forward GEMM, out2[1] weight-gradient GEMM (synchronises) */
 int magic_set_option(magic_handle* h, const char* name, int32_t value);

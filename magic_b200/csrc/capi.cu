@@ -178,6 +178,10 @@ int magic_export_rotation(magic_handle* h, int32_t* d_cs_sn) {
   CHECK_HANDLE(h);
   return done(h->eng.export_rotation(d_cs_sn));
 }
+int magic_export_latents(magic_handle* h, float* d_z3) {
+  CHECK_HANDLE(h);
+  return done(h->eng.export_latents(d_z3));
+}
 int magic_export_batch(magic_handle* h, float* d_x, float* d_labels) {
   CHECK_HANDLE(h);
   return done(h->eng.export_batch(d_x, d_labels));

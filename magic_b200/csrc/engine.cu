@@ -117,7 +117,7 @@ Engine::~Engine() {
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
                   statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
-                  in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_, touched_};
+                  in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
@@ -281,8 +281,6 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   km_wg_off_[0] = (size_t)round_up((long long)km_fwd_tiles_ * km_fwd_words_, 4);
   km_wg_off_[1] = km_wg_off_[0] + (size_t)round_up((long long)km_wg_tiles_ * km_wg_words_, 4);
   km_total_ = km_wg_off_[1] + (size_t)round_up((long long)km_wg_tiles_ * km_wg_words_, 4);
-  MAGIC_TRY(alloc((void**)&touched_, sizeof(uint32_t) * (size_t)km_wg_tiles_));     // zero-filled: nothing seen yet
-  if (const char* su = getenv("MAGIC_SKIP_UNTOUCHED")) skip_untouched_ = atoi(su) != 0;
   for (auto& b : in_) {
     MAGIC_TRY(alloc_act(&b.X, 3LL * B, D + 1));
     if (b.X.lo) { cudaFree(b.X.lo); stats.hbm_bytes -= (int64_t)(sizeof(bf16) * b.X.rows * b.X.ld); b.X.lo = nullptr; }  // pixels are exact in bf16
@@ -751,6 +749,14 @@ std::string Engine::export_rotation(int32_t* d_cs_sn) {
   mark_consumed(b);
   return "";
 }
+std::string Engine::export_latents(float* d_z3) {
+  if (!d_z3) return "export_latents: null output";
+  const size_t n = sizeof(float) * (size_t)B * L;          // z_ rows are [rot; lock; key]; the API order is lock, rot, key
+  MAGIC_CUDA(cudaMemcpyAsync(d_z3, z_ + (size_t)B * L, n, cudaMemcpyDeviceToDevice, stream));
+  MAGIC_CUDA(cudaMemcpyAsync(d_z3 + (size_t)B * L, z_, n, cudaMemcpyDeviceToDevice, stream));
+  MAGIC_CUDA(cudaMemcpyAsync(d_z3 + 2 * (size_t)B * L, z_ + 2 * (size_t)B * L, n, cudaMemcpyDeviceToDevice, stream));
+  return "";
+}
 std::string Engine::export_batch(float* d_x, float* d_labels) {
   InBuf& b = in_[cur_];
   wait_ready(b);
@@ -775,8 +781,6 @@ void Engine::build_kmasks(InBuf& b, cudaStream_t s) {
   build_kmask_fwd(b.xb3, xb_ld_, 3 * B, km_fwd_kb_, b.kmask, km_fwd_words_, s);
   for (int g = 0; g < 2; ++g)
     build_kmask_wgrad(b.xb3 + (size_t)g * B * xb_ld_, xb_ld_, 2 * B, km_wg_tiles_, b.kmask + km_wg_off_[g], km_wg_words_, s);
-  if (skip_untouched_) touch_rows(b.kmask + km_wg_off_[0], b.kmask + km_wg_off_[1], km_wg_words_, km_wg_tiles_, touched_, s);
-  else untracked_batches_ = true;      // the flags missed this batch: switching the option on later starts from "all set"
   // the plans that read this buffer get their work items re-dealt by the new maps (GemmArgs.order)
   const int alt = &b == &in_[1] ? 1 : 0;
   gemm_schedule(alt ? fwd_enc0_alt_ : fwd_enc_[0], s);
@@ -786,13 +790,6 @@ void Engine::build_kmasks(InBuf& b, cudaStream_t s) {
 std::string Engine::set_option(const char* name, int value) {
   if (!name) return "set_option: null name";
   if (std::string(name) == "skip_zero_stages") { skip_zero_ = value != 0; return ""; }
-  if (std::string(name) == "skip_untouched_rows") {
-    // the flags are only maintained while the option is on; batches loaded without it may have set any pixel
-    if (value != 0 && !skip_untouched_ && untracked_batches_)
-      MAGIC_CUDA(cudaMemsetAsync(touched_, 0xFF, sizeof(uint32_t) * (size_t)km_wg_tiles_, stream));
-    skip_untouched_ = value != 0;
-    return "";
-  }
   return std::string("set_option: unknown option ") + name;
 }
 std::string Engine::input_density(double* out2) {
@@ -1066,11 +1063,8 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
     ++t;
     AdamArgs a = adam_;
     if (early_adam_) a.n_total = early_begin_;   // the rest of the decoder range is already in flight on aux_stream_
-    // W0 rows whose pixels no batch has set yet: g = m = v = 0, nothing to do.  One GPU only: with a gradient
-    // exchange another rank's batch may have touched the row (the flags would need an OR across ranks).
     prof_begin("adam.dual");
-    if (skip_untouched_ && bits_a_ && cfg.world == 1) adam_dual_skip(a, touched_, lin[0].size(), (int)lin[0].ld, stream);
-    else adam_dual(a, stream);
+    adam_dual(a, stream);
     prof_end();
     ++launches;
     if (early_adam_) MAGIC_CUDA(cudaStreamWaitEvent(stream, ev_aux_join_, 0));
@@ -1302,8 +1296,6 @@ std::string Engine::slot(int which, int sl, int i, float* h_dst, const float* h_
   if (which == 2 && !(views[i].optimisers & 2)) return "slot: optimiser 2 does not train this variable";
   MAGIC_TRY(gather_master());
   const float* base = which == 1 ? (sl == MAGIC_SLOT_M ? m1_ : v1_) : (sl == MAGIC_SLOT_M ? m2_ : v2_);
-  // moments supplied from outside may be non-zero anywhere: no row counts as untouched any more
-  if (h_src) MAGIC_CUDA(cudaMemsetAsync(touched_, 0xFF, sizeof(uint32_t) * (size_t)km_wg_tiles_, stream));
   return copy_param(i, h_dst, h_src, base);
 }
 

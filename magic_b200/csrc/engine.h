@@ -49,6 +49,7 @@ class Engine {
   std::string generate(uint64_t seed, uint64_t step);
   std::string export_batch(float* d_x, float* d_labels);
   std::string export_rotation(int32_t* d_cs_sn);
+  std::string export_latents(float* d_z3);
   std::string swap_batch();
   std::string load_pairs_u8(const uint8_t* d_lock, const uint8_t* d_key, uint64_t seed, uint64_t step_idx);
   std::string load_pairs_bits(const uint32_t* d_lock, const uint32_t* d_key, int wpr, uint64_t seed, uint64_t step_idx);
@@ -135,9 +136,6 @@ class Engine {
   int xb_ld_ = 0;
   bool bits_a_ = true;              // first-layer GEMMs read the packed rows (BitsA); MAGIC_BITS_A=0: the bf16 planes
   bool skip_zero_ = true;           // ... and skip operand stages without a set pixel (MAGIC_SKIP_ZERO=0 / set_option: all stages)
-  bool skip_untouched_ = false;     // set_option("skip_untouched_rows"): Adam leaves W0 rows alone whose pixels were never set
-  bool untracked_batches_ = false;  // a batch was loaded while the option was off (its pixels are not in touched_)
-  uint32_t* touched_ = nullptr;     // [km_wg_tiles_] != 0 once a tile of 128 input pixels was set in any batch (AdamArgs.touched)
   int km_fwd_tiles_ = 0, km_fwd_words_ = 0, km_fwd_kb_ = 0;     // map geometry: forward (rows of 128 packed rows x k-blocks of 64 pixels)
   int km_wg_tiles_ = 0, km_wg_words_ = 0;                       // weight gradient (tiles of 128 pixels x k-blocks of 64 batch rows)
   size_t km_wg_off_[2] = {0, 0}, km_total_ = 0;                 // word offsets of the two groups' maps; total words

@@ -57,13 +57,6 @@ struct AdamArgs {
   int thin;                       // > 0: cap the grid at this many CTAs (grid-stride), for a launch that runs beside GEMMs
 };
 void adam_dual(const AdamArgs& a, cudaStream_t s);
-// Option "skip_untouched_rows".  The first matrix of the flat space is W0[D+1, ld0] = elements [0, skip_end);
-// touched[t] != 0 once any image of any batch had a set pixel among input columns [128 t, 128 t + 128).  Rows of an
-// untouched tile have g = m = v = 0 in both optimisers, so their update is p - lr * 0 / (0 + eps) = p, bit for bit:
-// this variant of the kernel leaves them alone (no loads, no stores).
-void adam_dual_skip(const AdamArgs& a, const uint32_t* touched, long long skip_end, int ld0, cudaStream_t s);
-// OR the weight-gradient zero-stage maps of a batch (two groups, `tiles` rows of `words` words each) into touched[tiles]
-void touch_rows(const uint32_t* km0, const uint32_t* km1, int words, int tiles, uint32_t* touched, cudaStream_t s);
 // Data parallel: sharded reduce + dual Adam + shadow all-gather over peer memory.
 constexpr int kMaxRanks = 8;
 struct AdamShardArgs {

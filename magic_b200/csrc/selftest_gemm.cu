@@ -480,78 +480,6 @@ static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms, bool spa
   if (extras) for (int i = 0; i < 2; ++i) { cudaFree(xa[i].d); cudaFree(xb[i].d); }
 }
 
-// Option skip_untouched_rows: touch_rows() derives the "ever set" flags from two weight-gradient maps, and
-// adam_dual_skip() must leave exactly the same bits behind as adam_dual() when the untouched tiles hold g = m = v = 0.
-static void test_adam_skip() {
-  const int rows = 300, ld = 64, tiles = (rows + 127) / 128, words = 2;       // W0 = [300, 64]: tiles of 128 / 128 / 44 rows
-  const long long n0 = (long long)rows * ld, n_both = n0 + 4096, n_total = n_both + 2048;
-  std::vector<uint32_t> km0((size_t)tiles * words, 0u), km1((size_t)tiles * words, 0u);
-  km0[0 * words + 1] = 0x10u;                       // tile 0 set in group 0, tile 2 in group 1, tile 1 in neither
-  km1[2 * words + 0] = 0x1u;
-  std::vector<float> p(n_total), g1(n_total), g2(n_both), m1(n_total), v1(n_total), m2(n_both), v2(n_both);
-  for (long long i = 0; i < n_total; ++i) {
-    const bool quiet = i >= 128ll * ld && i < 256ll * ld;                      // rows of tile 1
-    p[i] = frand();
-    g1[i] = quiet ? 0.f : frand(); m1[i] = quiet ? 0.f : 0.1f * frand(); v1[i] = quiet ? 0.f : fabsf(frand());
-    if (i < n_both) { g2[i] = quiet ? 0.f : frand(); m2[i] = quiet ? 0.f : 0.1f * frand(); v2[i] = quiet ? 0.f : fabsf(frand()); }
-  }
-  uint32_t *d_km0, *d_km1, *d_touched;
-  CK(cudaMalloc(&d_km0, km0.size() * 4)); CK(cudaMalloc(&d_km1, km1.size() * 4)); CK(cudaMalloc(&d_touched, tiles * 4));
-  CK(cudaMemcpy(d_km0, km0.data(), km0.size() * 4, cudaMemcpyHostToDevice));
-  CK(cudaMemcpy(d_km1, km1.data(), km1.size() * 4, cudaMemcpyHostToDevice));
-  CK(cudaMemset(d_touched, 0, tiles * 4));
-  touch_rows(d_km0, d_km1, words, tiles, d_touched, 0);
-  std::vector<uint32_t> touched(tiles);
-  CK(cudaMemcpy(touched.data(), d_touched, tiles * 4, cudaMemcpyDeviceToHost));
-  report("touch_rows flags (1, 0, 1)", (touched[0] != 0 && touched[1] == 0 && touched[2] != 0) ? 0.0 : 1.0, 0.0);
-  std::vector<float> res[2][5];
-  std::vector<__nv_bfloat16> shadow[2];
-  for (int variant = 0; variant < 2; ++variant) {
-    float* d[7];
-    const std::vector<float>* src[7] = {&p, &g1, &g2, &m1, &v1, &m2, &v2};
-    for (int k = 0; k < 7; ++k) {
-      CK(cudaMalloc(&d[k], src[k]->size() * 4));
-      CK(cudaMemcpy(d[k], src[k]->data(), src[k]->size() * 4, cudaMemcpyHostToDevice));
-    }
-    __nv_bfloat16* d_hi;
-    CK(cudaMalloc(&d_hi, n_total * 2));
-    CK(cudaMemset(d_hi, 0x3C, n_total * 2));          // the shadow of a skipped row keeps whatever it held
-    AdamArgs a;
-    memset(&a, 0, sizeof a);
-    a.p = d[0]; a.g1 = d[1]; a.g2 = d[2]; a.m1 = d[3]; a.v1 = d[4]; a.m2 = d[5]; a.v2 = d[6];
-    a.w_hi = d_hi; a.w_lo = nullptr; a.begin = 0; a.n_both = n_both; a.n_total = n_total;
-    a.lr_t1 = 1e-2f; a.lr_t2 = 1e-3f; a.beta1 = 0.9f; a.beta2 = 0.999f; a.eps = 1e-8f;
-    if (variant == 0) adam_dual(a, 0); else adam_dual_skip(a, d_touched, n0, ld, 0);
-    CK(cudaDeviceSynchronize());
-    const int idx[5] = {0, 3, 4, 5, 6};
-    for (int k = 0; k < 5; ++k) {
-      res[variant][k].resize(src[idx[k]]->size());
-      CK(cudaMemcpy(res[variant][k].data(), d[idx[k]], res[variant][k].size() * 4, cudaMemcpyDeviceToHost));
-    }
-    shadow[variant].resize(n_total);
-    CK(cudaMemcpy(shadow[variant].data(), d_hi, n_total * 2, cudaMemcpyDeviceToHost));
-    for (int k = 0; k < 7; ++k) CK(cudaFree(d[k]));
-    CK(cudaFree(d_hi));
-  }
-  double diff = 0.0, moved = 0.0, stale = 0.0;
-  for (int k = 0; k < 5; ++k)
-    for (size_t i = 0; i < res[0][k].size(); ++i) diff = std::max(diff, (double)fabsf(res[0][k][i] - res[1][k][i]));
-  for (long long i = 128ll * ld; i < 256ll * ld; ++i) {
-    moved = std::max(moved, (double)fabsf(res[1][0][i] - p[i]));
-    uint16_t h; memcpy(&h, &shadow[1][i], 2);
-    if (h != 0x3C3C) stale = 1.0;                     // the skip variant must not have written these shadows
-  }
-  for (long long i = 0; i < n_total; ++i) {           // everywhere else the shadows agree
-    if (i >= 128ll * ld && i < 256ll * ld) continue;
-    uint16_t h0, h1; memcpy(&h0, &shadow[0][i], 2); memcpy(&h1, &shadow[1][i], 2);
-    if (h0 != h1) diff = std::max(diff, 1.0);
-  }
-  report("adam_dual_skip vs adam_dual (p, m, v, shadows)", diff, 0.0);
-  report("adam_dual_skip: untouched rows not moved", moved, 0.0);
-  report("adam_dual_skip: untouched rows not written", stale, 0.0);
-  CK(cudaFree(d_km0)); CK(cudaFree(d_km1)); CK(cudaFree(d_touched));
-}
-
 static double sigm(double x) { return 1.0 / (1.0 + exp(-x)); }
 
 // ACT (fwd, optional two-pass), DACT (dgrad), BCE (fwd)
@@ -764,11 +692,6 @@ int main(int argc, char** argv) {
   std::string err = gemm_init();
   if (!err.empty()) { printf("gemm_init: %s\n", err.c_str()); return 2; }
   const bool do_bench = argc > 1 && std::string(argv[1]) == "bench";
-  if (argc > 1 && std::string(argv[1]) == "adam") {       // the optimiser kernels only (seconds)
-    test_adam_skip();
-    printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
-    return g_fail ? 1 : 0;
-  }
   // plain GEMMs, all three operand layouts, K tails, M/N tails, segments, split-K
   test_store(GEMM_FWD, 128, 256, 64, 1, 1, sms);
   test_store(GEMM_FWD, 128, 256, 256, 1, 1, sms);
@@ -837,7 +760,6 @@ int main(int argc, char** argv) {
   test_bits_fwd_store(300, 256, 5000, 1, 7, sms, true);
   test_bits_wgrad(700, 500, 96, false, sms, true);
   test_bits_wgrad(1601, 500, 256, true, sms, true);
-  test_adam_skip();
   printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
   if (do_bench) {
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");

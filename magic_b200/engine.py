@@ -289,8 +289,7 @@ class Engine:
         return x, y
 
     def set_option(self, name: str, value: int) -> None:
-        """Run-time switches of the engine: "skip_zero_stages" (default 1), "skip_untouched_rows" (experimental,
-        default 0); see include/magic_b200.h."""
+        """Run-time switches of the engine: "skip_zero_stages" (default 1); see include/magic_b200.h."""
         check(self.lib.magic_set_option(self._h, name.encode(), int(value)))
 
     def input_density(self) -> Tuple[float, float]:
@@ -309,6 +308,12 @@ class Engine:
         r = torch.empty(self.B, 2, dtype=torch.int32, device=self.device)
         check(self.lib.magic_export_rotation(self._h, C.c_void_p(r.data_ptr())))
         return r
+
+    def export_latents(self) -> torch.Tensor:
+        """[3, B, L] float32: the sampled z of the last step / forward call, streams lock, rot, key."""
+        z = torch.empty(3, self.B, self.L, dtype=torch.float32, device=self.device)
+        check(self.lib.magic_export_latents(self._h, C.c_void_p(z.data_ptr())))
+        return z
 
     # ------------------------------------------------------------------ step / inference
     def step(self, labels=None, eps3=None, apply: bool = True, want_distance: bool = False):

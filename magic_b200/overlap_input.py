@@ -177,13 +177,34 @@ class OverlapDataset:
         self.lock_bits = pack_planes(self.lock)
         self.key_bits = pack_planes(self.key)
 
+    @classmethod
+    def from_arrays(cls, lock: np.ndarray, key: np.ndarray, overlap_areas: Sequence[float], image_size: int = 200) -> "OverlapDataset":
+        """A dataset from planes already in memory: lock / key [N, D] (any non-zero value = set pixel), labels [N]."""
+        self = cls.__new__(cls)
+        self.lock = np.ascontiguousarray(np.asarray(lock).reshape(len(lock), -1) != 0).astype(np.uint8)
+        self.key = np.ascontiguousarray(np.asarray(key).reshape(len(key), -1) != 0).astype(np.uint8)
+        self.labels = np.asarray(overlap_areas, dtype=np.float32)[:len(self.lock)].copy()
+        if self.lock.shape != self.key.shape or self.lock.shape[1] != image_size * image_size or len(self.labels) != len(self.lock):
+            raise ValueError("lock / key must be [N, %d] with N labels" % (image_size * image_size))
+        self.image_size = image_size
+        self.lock_bits = pack_planes(self.lock)
+        self.key_bits = pack_planes(self.key)
+        return self
+
     def __len__(self) -> int:
         return len(self.labels)
 
-    def index_batches(self, batch_size: int, epochs: int = 1, shuffle: bool = True, seed: int = 0) -> Iterator[np.ndarray]:
-        """The example indices of every batch: a fresh permutation per epoch, the ragged tail dropped."""
+    def index_batches(self, batch_size: int, epochs: int = 1, shuffle: bool = True, seed: int = 0,
+                      steps: Optional[int] = None) -> Iterator[np.ndarray]:
+        """The example indices of every batch: a fresh permutation per epoch, the ragged tail dropped.  With `steps`
+        the iterator instead draws that many batches with replacement (any batch size: the reference's
+        shuffle_batch queue likewise keeps serving examples for as long as the loop dequeues, 8c/overlap_input.py:297-340)."""
         rng = np.random.default_rng(seed)
         n = len(self)
+        if steps is not None:
+            for _ in range(steps):
+                yield rng.integers(0, n, batch_size)
+            return
         if batch_size > n:
             raise ValueError("batch_size %d exceeds the %d loaded examples" % (batch_size, n))
         for _ in range(epochs):
@@ -199,7 +220,7 @@ class OverlapDataset:
 
 
 def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool = True, seed: int = 0,
-                   packed: bool = True):
+                   packed: bool = True, steps: Optional[int] = None):
     """`overlap_input.inputs(normalize=True, reshape=True, rotation=True)` for the B200 backend: yields handles
     (magic_b200/tango.py: ResidentBatch) whose planes are already in HBM; `batch.labels` are the matching overlap
     areas, so `vae.partial_fit(batch, overlap_areas=batch.labels)` trains on a consistent (images, labels) pair.
@@ -212,7 +233,8 @@ def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool 
     eng = vae.engine
     if not packed:
         step = 0
-        for lock, key, labels in dataset.batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed):
+        for idx in dataset.index_batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed, steps=steps):
+            lock, key, labels = dataset.lock[idx], dataset.key[idx], dataset.labels[idx]
             eng.load_pairs_u8(torch.from_numpy(np.ascontiguousarray(lock)), torch.from_numpy(np.ascontiguousarray(key)),
                               seed, step)
             step += 1
@@ -234,7 +256,7 @@ def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool 
         eng.feed_pairs_bits(slot[0], slot[1], slot[2], seed, n, activate=activate)
         return slot[2].numpy().copy()
 
-    order = dataset.index_batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed)
+    order = dataset.index_batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed, steps=steps)
     idx = next(order, None)
     if idx is None:
         return

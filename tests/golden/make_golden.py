@@ -6,6 +6,8 @@
 overlap_areas.npy      2a/OVERLAP_AREAS (pickle of 2000 int64 max-overlap labels) re-saved as a plain .npy
 overlap_micro_16.npz   the first 16 lock/key PNG pairs of overlap_micro.zip, 200x200, bit-packed ({0,255} -> 1 bit/px),
                        plus the pixel areas of all 100 locks and keys (generator statistics)
+overlap_micro_100.npz  all 100 lock/key pairs of overlap_micro.zip, bit-packed the same way (np.packbits, MSB first): the
+                       real-data batches of bench.py and of the generator-statistics tests are sampled from these
 png/{0..3}_{L,K}.png   the first four lock/key files of overlap_micro.zip, byte for byte (dataset samples, ~0.8 kB each):
                        fixtures of the PNG loader path (row N2, tests/test_overlap_input.py)
 oracle_step_mini.npz   inputs and float64 outputs of one oracle step on a reduced geometry (losses, distance, a few
@@ -46,10 +48,11 @@ def micro():
             assert img.shape == (200, 200) and set(np.unique(img)) <= {0, 255}
             bits = img > 0
             areas.append(int(bits.sum()))
-            if i < 16:
-                dst.append(np.packbits(bits.reshape(-1)))
-    np.savez_compressed(os.path.join(HERE, "overlap_micro_16.npz"), lock_bits=np.stack(locks), key_bits=np.stack(keys),
+            dst.append(np.packbits(bits.reshape(-1)))
+    np.savez_compressed(os.path.join(HERE, "overlap_micro_16.npz"), lock_bits=np.stack(locks[:16]), key_bits=np.stack(keys[:16]),
                         area_lock=np.asarray(area_l), area_key=np.asarray(area_k))
+    # all 100 pairs: the real-data leg of bench.py and the generator-statistics tests sample their batches from these
+    np.savez_compressed(os.path.join(HERE, "overlap_micro_100.npz"), lock_bits=np.stack(locks), key_bits=np.stack(keys))
 
 
 def png_fixtures():

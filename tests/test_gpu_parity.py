@@ -24,15 +24,37 @@ CASES = [
 ]
 
 
-# Operand precision of the two modes relative to true fp32 (2^-24): the fp32 mode carries hi+lo bf16 pairs
-# (2^-17), the bf16 mode 2^-9.  An ill-conditioned quantity (9a: reciprocal of a near-zero cosine sum) amplifies
-# ANY rounding, also the reference's own fp32 arithmetic; its amplification is measured by running the oracle in
-# float32 ("noise floor").  Allowed error = max(north_star tolerance, AMP * floor).
+# Tolerances: BASELINE.json's north_star, 1e-4 (fp32 mode) / 2e-2 (bf16 mode) relative error, asserted as they stand
+# for every loss, the distances and every gradient tensor of both optimisers.  One exception, and only for the
+# configurations that take 1/distance (9a/vae.py:301, 11a/vae.py:306-311): training_loss, distance and the gradients of
+# training_loss (optimiser 2) sit behind a pole that amplifies ANY rounding, the reference's own fp32 arithmetic
+# included.  For those tensors alone the bound is max(tol, min(10 tol, AMP x floor)), floor = the error of the oracle
+# itself run in float32 (operand precision of the modes relative to fp32: hi+lo bf16 pairs 2^-17, bf16 2^-9).
 AMP = {"fp32": 2.0 * 2 ** 7, "bf16": 2.0 * 2 ** 15}
 
 
-def _compare_step(ocfg, batch, precision):
+def _allowed(ocfg, key, tol, amp, floor):
+    behind_pole = ocfg.reciprocal and (key in ("training_loss", "distance") or (isinstance(key, tuple) and key[0] == 2))
+    return max(tol, min(10.0 * tol, amp * floor)) if behind_pole else tol
+
+
+def _log_table(title, report):
+    """Per-tensor achieved error / bound / float32-oracle floor; appended to $MAGIC_PARITY_TABLE (profiles/r02_parity_table.txt)."""
+    path = os.environ.get("MAGIC_PARITY_TABLE")
+    lines = ["== %s" % title] + ["%-46s err %.3e  bound %.3e  f32-oracle floor %.3e%s" % (
+        k if isinstance(k, str) else "g%d %s" % k, v[0], v[1], v[2], "" if v[0] <= v[1] else "   <-- FAIL") for k, v in report.items()]
+    if path:
+        with open(path, "a") as f:
+            f.write("\n".join(lines) + "\n")
+    return "\n".join(lines)
+
+
+def _compare_step(ocfg, batch, precision, title=None, scale_params=None):
     state, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, batch, precision)
+    if scale_params:
+        for k, f in scale_params.items():
+            state.params[k] = state.params[k] * f
+        eng.set_params({k: v.to(torch.float32).numpy() for k, v in state.params.items() if k not in orc.DEAD_PARAMS})
     tol, amp = TOL[precision], AMP[precision]
     out, g1, g2 = state.grads(xl, xr, xk, y, eps)
     s32 = orc.OracleState(ocfg, params=state.params, dtype=torch.float32)
@@ -46,15 +68,16 @@ def _compare_step(ocfg, batch, precision):
         ref = float(out[k])
         floor = abs(float(out32[k]) - ref) / max(abs(ref), 1e-30)
         err = abs(losses[i] - ref) / max(abs(ref), 1e-30)
-        report[k] = (err, max(tol, amp * floor))
-    report["distance"] = (rel_l2(dist.cpu().numpy(), out["distance"].numpy()),
-                          max(tol, amp * rel_l2(out32["distance"].numpy(), out["distance"].numpy())))
+        report[k] = (err, _allowed(ocfg, k, tol, amp, floor), floor)
+    floor = rel_l2(out32["distance"].numpy(), out["distance"].numpy())
+    report["distance"] = (rel_l2(dist.cpu().numpy(), out["distance"].numpy()), _allowed(ocfg, "distance", tol, amp, floor), floor)
     for which, g, g32 in ((1, g1, g1_32), (2, g2, g2_32)):
         for name, ref in g.items():
             floor = rel_l2(g32[name].numpy(), ref.numpy())
-            report[(which, name)] = (rel_l2(eng.get_grad(which, name), ref.numpy()), max(tol, amp * floor))
+            report[(which, name)] = (rel_l2(eng.get_grad(which, name), ref.numpy()), _allowed(ocfg, (which, name), tol, amp, floor), floor)
+    table = _log_table("%s  B=%d  %s" % (title or "L=%d %s" % (ocfg.latent, ocfg.metric), batch, precision), report)
     bad = {k: v for k, v in report.items() if not v[0] <= v[1]}
-    assert not bad, "mismatch (rel error, allowed): %s" % bad
+    assert not bad, "mismatch:\n" + table
     eng.close()
     return report
 
@@ -62,50 +85,95 @@ def _compare_step(ocfg, batch, precision):
 @pytest.mark.parametrize("name,kw,batch", CASES, ids=[c[0] for c in CASES])
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 def test_losses_and_gradients(name, kw, batch, precision):
-    _compare_step(oracle_config(**kw), batch, precision)
+    _compare_step(oracle_config(**kw), batch, precision, title=name)
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 def test_full_size_8c(precision):
     """Experiment 8c as written (D=40000, 500x4, L=20), small batch so the float64 oracle finishes in seconds."""
-    _compare_step(orc.OracleConfig.experiment("8c"), 12, precision)
+    _compare_step(orc.OracleConfig.experiment("8c"), 12, precision, title="8c full geometry")
 
 
 @pytest.mark.parametrize("precision", ["bf16", "fp32"])
 def test_benchmark_config_8d_at_full_batch(precision):
     """bench.py's own workload: experiment 8d (L=200) at 4096 pairs -- the tile counts, split-K choices and
     persistent-loop trip counts of the measured run, checked against the float64 oracle (about 10 s of CPU each)."""
-    _compare_step(orc.OracleConfig.experiment("8d"), 4096, precision)
-
-
-def test_full_size_11a_fp32():
-    _compare_step(orc.OracleConfig.experiment("11a"), 8, "fp32")
+    _compare_step(orc.OracleConfig.experiment("8d"), 4096, precision, title="8d benchmark configuration")
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
-def test_ten_steps_track_the_oracle(precision):
-    """Params after 10 steps of both Adam optimisers (TF1 formula, W <- W - d1 - d2)."""
+@pytest.mark.parametrize("exp,batch", [("8e", 24), ("9a", 48), ("11a", 24)])
+def test_full_size_other_baseline_configs(exp, batch, precision):
+    """BASELINE.json configs 3-5 at their real geometry (D = 40000): 8e L = 2000 (4000-wide head GEMM, K = 2000 decoder
+    input), 9a L = 2 (heads that are almost all padding, reciprocal cosine), 11a (2 x 500 ELU encoder, L = 80,
+    reciprocal squared difference, deformation weight 100) -- small batches so the float64 oracle finishes in seconds."""
+    _compare_step(orc.OracleConfig.experiment(exp), batch, precision, title="%s full geometry" % exp)
+
+
+def test_saturated_logits_bf16():
+    """A trained decoder is confident: |logit| ~ 10-15 on most pixels.  The fast BCE epilogue forms sigmoid(s) as
+    0.5 + (u - 0.5) from approximate ex2 / rcp; check its gradient where that subtraction cancels (all other parity
+    cases use Xavier-initialised weights, |logit| < 1)."""
     ocfg = oracle_config(latent=20, **MINI)
-    state, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, 64, precision)
+    _compare_step(ocfg, 64, "bf16", title="saturated logits (decoder_out x40)", scale_params={"decoder_out_mean_weights": 40.0})
+
+
+def _ten_steps(ocfg, batch, precision, title, steps=10, names=None):
+    """Both Adam optimisers (TF1 formula, W <- W - d1 - d2) for `steps` steps on one batch; returns the per-tensor
+    relative L2 error of the accumulated UPDATE after the first and after the last step.  The first Adam steps move
+    every weight by ~lr regardless of |g|, so the update vector (not the parameter, which barely moves) is the
+    sensitive quantity; what bounds the agreement is the sign of gradients that are zero to working precision."""
+    state, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, batch, precision)
     X = orc.interleave(xl, xr, xk).to(torch.float32)
     p0 = {k: v.clone() for k, v in state.params.items()}
-    for it in range(10):
+    names = names or eng.param_names
+    errs = {}
+    for it in range(steps):
         out, _, _ = state.step(xl, xr, xk, y, eps)
         eng.load_interleaved(X)
         losses, _ = eng.step(labels=y.to(torch.float32), eps3=eps.to(torch.float32))
         l = losses.cpu().numpy()
         assert abs(l[0] - float(out["cost"])) <= max(TOL[precision], 1e-3) * abs(float(out["cost"])), (it, l[0])
-    assert eng.step_count == 10
-    # compare the accumulated UPDATE (the first Adam steps move every weight by ~lr regardless of |g|, so the
-    # update vector is the sensitive quantity); sign flips of ~zero gradients bound the achievable agreement
-    for name in eng.param_names:
-        upd_ref = (state.params[name] - p0[name]).numpy()
-        upd = eng.get_param(name).astype(np.float64) - p0[name].numpy()
-        if np.linalg.norm(upd_ref) == 0:
-            assert np.linalg.norm(upd) == 0
-            continue
-        assert rel_l2(upd, upd_ref) <= (0.02 if precision == "fp32" else 0.25), name
+        if it in (0, steps - 1):
+            for name in names:
+                upd_ref = (state.params[name] - p0[name]).numpy()
+                upd = eng.get_param(name).astype(np.float64) - p0[name].numpy()
+                if np.linalg.norm(upd_ref) == 0:
+                    assert np.linalg.norm(upd) == 0, name
+                    continue
+                cos = float((upd * upd_ref).sum() / (np.linalg.norm(upd) * np.linalg.norm(upd_ref)))
+                errs[(it + 1, name)] = (rel_l2(upd, upd_ref), cos)
+    assert eng.step_count == steps
     eng.close()
+    path = os.environ.get("MAGIC_PARITY_TABLE")
+    if path:
+        with open(path, "a") as f:
+            f.write("== update after n steps: %s  B=%d  %s\n" % (title, batch, precision))
+            for (n, name), (e, c) in errs.items():
+                f.write("step %2d  %-40s rel-L2 of the update %.3e  cosine %.6f\n" % (n, name, e, c))
+    return errs
+
+
+# bound on the relative L2 error of the accumulated update: fp32 mode 2 % (sign flips of ~zero gradients in the first,
+# sign-like Adam steps); bf16 mode: the same effect at 2^-9 operand precision
+UPDATE_TOL = {"fp32": 0.02, "bf16": 0.15}
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_ten_steps_track_the_oracle(precision):
+    errs = _ten_steps(oracle_config(latent=20, **MINI), 64, precision, "mini-cos")
+    for (n, name), (e, c) in errs.items():
+        assert e <= UPDATE_TOL[precision] and c >= 1.0 - UPDATE_TOL[precision] ** 2, (n, name, e, c)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_full_size_8c_parameters_after_one_and_ten_steps(precision):
+    """Experiment 8c at its real geometry: parameters after 1 and after 10 optimiser steps (SURVEY 8.3 parity procedure)."""
+    names = ["encoder_h0_weights", "encoder_h3_weights", "encoder_out_mean_weights", "encoder_b0_biases", "decoder_h1_weights",
+             "decoder_out_mean_weights", "decoder_out_mean_biases"]
+    errs = _ten_steps(orc.OracleConfig.experiment("8c"), 12, precision, "8c full geometry", names=names)
+    for (n, name), (e, c) in errs.items():
+        assert e <= UPDATE_TOL[precision] and c >= 1.0 - UPDATE_TOL[precision] ** 2, (n, name, e, c)
 
 
 def test_inference_surface():
@@ -181,7 +249,7 @@ def test_packed_first_layer_operand_matches_bf16_planes(precision, monkeypatch):
         eng.close()
     a = runs[0]
     assert set(np.unique(a[2])) <= {0.0, 1.0} and a[2].sum() > 0
-    assert 0.0 < a[5][0] < 1.0 and 0.0 < a[5][1] < 1.0, a[5]        # the generator leaves the canvas margins empty
+    assert 0.0 < a[5][0] <= 1.0 and 0.0 < a[5][1] <= 1.0, a[5]
     assert runs[2][5] == (1.0, 1.0)                                  # no packed rows, no map
     # fp32 sums taken in another order differ in the last bits; in the bf16 mode such a difference can flip the
     # rounding of a stored activation (2^-9 relative), so the modes agree to a tenth of the mode's tolerance
@@ -192,49 +260,3 @@ def test_packed_first_layer_operand_matches_bf16_planes(precision, monkeypatch):
         assert rel_l2(a[1], b[1]) < tol
         for k in a[4]:
             assert rel_l2(a[4][k], b[4][k]) < tol, k
-
-
-@pytest.mark.skipif(os.environ.get("MAGIC_TEST_EXPERIMENTAL", "0") == "0",
-                    reason="option not yet validated on a GPU (off by default); run with MAGIC_TEST_EXPERIMENTAL=1")
-def test_untouched_first_layer_rows_can_be_left_alone():
-    """set_option("skip_untouched_rows", 1): rows of W0 whose 128 input pixels no batch has set so far have zero
-    gradients and zero Adam moments in both optimisers, so leaving them alone must give the same bits as updating them:
-    parameters, both optimisers' slots and the losses after several steps on fresh batches.  A restored optimiser state
-    (set_slot) makes every row count as touched."""
-    from magic_b200 import _lib
-    from magic_b200.engine import Engine
-    ocfg = oracle_config(latent=20, encoder_neurons=[120, 72], decoder_neurons=[88, 104], n_input=4096)
-    engs = [Engine(engine_config_from_oracle(ocfg, 96, "bf16", seed=5)) for _ in range(2)]
-    engs[1].set_params(engs[0].get_params())
-    engs[1].set_option("skip_untouched_rows", 1)
-    union = np.zeros(4096, bool)
-    for step in range(4):
-        out = []
-        for e in engs:
-            e.generate_batch(3, step)
-            out.append(e.step()[0].cpu().numpy())
-        assert np.array_equal(out[0], out[1]), step
-        X, _ = engs[1].export_batch()
-        union |= X.cpu().numpy().reshape(96, 4096, 3).any(axis=(0, 2))
-    tiles = union.reshape(32, 128).any(axis=1)
-    assert 0 < tiles.sum() < 32, tiles                   # the canvas margins stay empty: some rows really were skipped
-    for n in engs[0].param_names:
-        assert np.array_equal(engs[0].get_param(n), engs[1].get_param(n)), n
-        for which in (1, 2):
-            if engs[0].param_opts[n] & which:
-                for sl in (_lib.SLOT_M, _lib.SLOT_V):
-                    assert np.array_equal(engs[0].get_slot(which, sl, n), engs[1].get_slot(which, sl, n)), (n, which, sl)
-    w0 = engs[1].param_names[0]
-    m = engs[1].get_slot(1, _lib.SLOT_M, w0)
-    assert not m[:128][~union[:128]].any()               # never-set pixels: moments still exactly zero
-    # a restored state may hold non-zero moments anywhere: after set_slot nothing is skipped
-    m2 = m.copy(); m2[0, :] = 1e-3
-    for e in engs:
-        e.set_slot(1, _lib.SLOT_M, w0, m2)
-        e.generate_batch(3, 9)
-        e.step()
-    assert np.array_equal(engs[0].get_param(w0), engs[1].get_param(w0))
-    assert np.array_equal(engs[0].get_slot(1, _lib.SLOT_M, w0), engs[1].get_slot(1, _lib.SLOT_M, w0))
-    assert engs[1].get_slot(1, _lib.SLOT_M, w0)[0].any()
-    for e in engs:
-        e.close()
