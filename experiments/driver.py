@@ -1,18 +1,17 @@
-"""The training loop every experiment directory shares (the caller of the hot path).
+"""The loop bodies every experiment directory's `main.train()` shares (the caller of the hot path).
 
-Mirrors `train()` of the reference drivers (8c/main.py:33-94; 11a/main.py:42-133): epochs x (n_samples / batch)
-steps of `vae.partial_fit`, the NaN guard that raises TrainingException (8c/main.py:29-30,51-52), the per-step
-loss line in the reference's format (8c/main.py:58-63, visible at 8c/nohup.out:27), a prediction MSE every 24
-steps (8c/main.py:66-80; 11a inverts its reciprocal distances first, 11a/main.py:100), KeyboardInterrupt returning
-the model (8c/main.py:91-92).  Left out on purpose: the HTTP "poor man's tensorboard" GET (8c/utils.py:250-260;
-no network), the matplotlib plots (cold, not installed) and 9a's sleep(10) + PNG dumps per step (9a/main.py:50-64).
-
-Batches come from the on-device generator (`vae.next_device_batch()`), images and labels jointly -- the fix the
-reference made in 10a/main.py:64 for the mismatched double dequeue of 8c-9b."""
+Two styles, as in the reference:
+* `run_8c_style`  -- 8c/main.py:33-94 (8c, 8d, 8e, 9a): per-step loss line in the reference's format (8c/main.py:58-63,
+  visible at 8c/nohup.out:27), prediction MSE every 24 steps (:66-80), per-epoch `Epoch: 0001 cost= ...` line (:86-88);
+* `run_11a_style` -- 11a/main.py:42-133: joint `sess.run([images_batch, labels_batch])`, 6-tuple partial_fit, evaluation
+  at `epoch % 10 == 0 and i == 3` with the reciprocal distances inverted (:94-100), per-epoch averages line (:124-126).
+Both keep the NaN guard that raises TrainingException (8c/main.py:29-30,51-52) and return the model on
+KeyboardInterrupt (8c/main.py:91-92).  Left out on purpose: the HTTP "poor man's tensorboard" GET (8c/utils.py:250-260;
+no network), the matplotlib plots and example dumps (cold, not installed), 9a's sleep(10) per step (9a/main.py:50-64).
+"""
 from __future__ import annotations
 
 import sys
-import time
 
 import numpy as np
 
@@ -21,7 +20,7 @@ class TrainingException(Exception):                     # 8c/main.py:29-30, 11a/
     pass
 
 
-def _line(epoch, epochs, i, total, cost, training_loss, rec_loss, lat_loss, def_loss) -> str:
+def loss_line(epoch, epochs, i, total, cost, training_loss, rec_loss, lat_loss, def_loss) -> str:
     fill = " "
     return (("Epoch: (" + str(epoch) + "/" + str(epochs) + ");").ljust(16, fill)
             + (" i: (" + str(i) + "/" + str(total) + ").").ljust(16, fill) + " "
@@ -32,44 +31,66 @@ def _line(epoch, epochs, i, total, cost, training_loss, rec_loss, lat_loss, def_
             + ("deformation loss: " + str(def_loss) + ".").ljust(27, fill) + "]")
 
 
-def train(model_cls, FLAGS, sess=None, batch_size=None, training_epochs=50, display_step=5, steps_per_epoch=None,
-          log=sys.stdout, seed=0, dataset=None, **model_kw):
-    """`dataset`: a magic_b200.overlap_input.OverlapDataset (the PNG pairs + OVERLAP_AREAS of FLAGS.DATA_DIR, row N2);
-    None trains on pairs produced by the on-device generator (row N1)."""
-    batch_size = int(batch_size or FLAGS.BATCH_SIZE)
-    vae = model_cls(sess=sess, batch_size=batch_size, **model_kw)
-    n_samples = len(dataset) if dataset is not None else FLAGS.NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN
-    total_batch = int(steps_per_epoch or max(1, n_samples // batch_size))
-    data_iter = None
-    if dataset is not None:
-        from magic_b200.overlap_input import device_batches
-        data_iter = device_batches(vae, dataset, epochs=training_epochs * 2 + 2, shuffle=True, seed=seed)
-    t0, pairs = time.time(), 0
+def run_8c_style(vae, images_batch, labels_batch, n_samples, batch_size, training_epochs, display_step, log=None,
+                 max_steps=None):
+    log = log or sys.stdout
+    steps = 0
     try:
         for epoch in range(training_epochs):
+            avg_cost = 0.
+            total_batch = int(n_samples / batch_size)
             for i in range(total_batch):
-                batch = next(data_iter) if data_iter is not None else vae.next_device_batch(seed)
-                out = vae.partial_fit(batch, overlap_areas=batch.labels)
-                cost, training_loss, rec_loss, lat_loss, def_loss = out[:5]
-                pairs += batch_size
+                batch_xs = images_batch.eval()
+                overlap_areas = labels_batch.eval()
+                cost, training_loss, rec_loss, lat_loss, def_loss = vae.partial_fit(batch_xs, overlap_areas=overlap_areas)[:5]
                 if np.isnan(cost):
                     raise TrainingException("Got cost=nan")
-                if log is not None and (i % display_step == 0 or i == total_batch - 1):
-                    print(_line(epoch, training_epochs, i, total_batch, cost, training_loss, rec_loss, lat_loss, def_loss),
-                          file=log)
+                print(loss_line(epoch, training_epochs, i, total_batch, cost, training_loss, rec_loss, lat_loss, def_loss), file=log)
                 if i % 24 == 0:
-                    test = next(data_iter) if data_iter is not None else vae.next_device_batch(seed + 1)
-                    areas = test.labels if data_iter is not None else test.labels.eval()
-                    predictions = vae.get_predictions(test, overlap_areas=test.labels)
-                    if vae.reciprocal_distance:
-                        predictions = 1.0 / predictions             # 11a/main.py:100
-                    mse = float(np.mean((predictions - areas) ** 2))
-                    if log is not None:
-                        print("Mean squared error on a fresh batch: " + str(mse), file=log)
+                    test_images = images_batch.eval()
+                    test_areas = labels_batch.eval()
+                    predictions = vae.get_predictions(test_images, overlap_areas=test_areas)
+                    mse = ((predictions - np.asarray(test_areas)) ** 2).mean(axis=None)
+                    print("mse: " + str(mse), file=log)
+                avg_cost += cost / n_samples * batch_size
+                steps += 1
+                if max_steps is not None and steps >= max_steps:
+                    return vae
+            if epoch % display_step == 0:
+                print("Epoch:", '%04d' % (epoch + 1), "cost=", "{:.9f}".format(avg_cost), file=log)
     except KeyboardInterrupt:
         pass
-    if log is not None:
-        dt = time.time() - t0
-        print("trained %d pairs in %.2f s (%.0f pairs/s including logging and evaluation)" % (pairs, dt, pairs / max(dt, 1e-9)),
-              file=log)
+    return vae
+
+
+def run_11a_style(vae, sess, images_batch, labels_batch, n_samples, batch_size, training_epochs, log=None, max_steps=None):
+    log = log or sys.stdout
+    steps = 0
+    try:
+        for epoch in range(training_epochs):
+            avg_cost = 0.
+            avg_loss = 0.
+            total_batch = int(n_samples / batch_size)
+            for i in range(total_batch):
+                batch_xs, overlap_areas = sess.run([images_batch, labels_batch])
+                cost, training_loss, rec_loss, lat_loss, def_loss, distance = vae.partial_fit(batch_xs, overlap_areas=overlap_areas)
+                if np.isnan(cost):
+                    raise TrainingException("Got cost=nan")
+                if epoch % 10 == 0 and i == 3:
+                    test_images, test_areas = sess.run([images_batch, labels_batch])
+                    predictions = vae.get_predictions(test_images, overlap_areas=test_areas)
+                    predictions = 1. / predictions                  # the distance is the inverse (11a/main.py:100)
+                    print("Predictions: " + str(predictions), file=log)
+                    print("Actual areas: " + str(np.asarray(test_areas)), file=log)
+                    mse = (np.array(predictions - np.asarray(test_areas)) ** 2).mean(axis=None)
+                    print("mse: " + str(mse) + "     ", file=log)
+                avg_cost += cost / n_samples * batch_size
+                avg_loss += training_loss / n_samples * batch_size
+                steps += 1
+                if max_steps is not None and steps >= max_steps:
+                    return vae
+            print(("Epoch: " + str(epoch)).ljust(20) + " " + ("Average cost: " + str(int(avg_cost)) + "").ljust(35) + " "
+                  + ("Average loss: " + str(int(avg_loss)) + "").ljust(35), file=log)
+    except KeyboardInterrupt:
+        pass
     return vae

@@ -170,6 +170,11 @@ int magic_forward(magic_handle* h, int32_t what, const float* d_eps3, float* d_o
 /* generate (8c/vae.py:416-428): decoder-only forward from a fed z [B,L] -> [B,D] */
 int magic_decode(magic_handle* h, const float* d_z, float* d_out);
 
+/* cosine_distance(a, b) (8c/vae.py:438-452), the public free function of the reference's vae.py: both [B, L] arrays are
+ * l2-normalised over axis 0 (the BATCH axis, eps 1e-12 under the max) and the products summed over the latent axis.
+ * Host fp32 in, host fp32 [B] out; runs on the current device, synchronous.  No handle needed. */
+int magic_cosine_distance(const float* h_a, const float* h_b, int32_t B, int32_t L, float* h_out);
+
 /* Data parallelism (new; the reference is single-device).  `nccl_unique_id` is the 128-byte ncclUniqueId
  * created on rank 0 and distributed by the host framework.  Afterwards magic_step all-reduces the cosine
  * batch statistics, the two gradients and the loss scalars over NCCL inside the step. */

@@ -210,6 +210,27 @@ int magic_decode(magic_handle* h, const float* d_z, float* d_out) {
   return done(h->eng.decode(d_z, d_out));
 }
 
+int magic_cosine_distance(const float* h_a, const float* h_b, int32_t B, int32_t L, float* h_out) {
+  if (!h_a || !h_b || !h_out) return fail("magic_cosine_distance: null argument");
+  if (B < 1 || L < 1) return fail("magic_cosine_distance: B and L must be >= 1");
+  const size_t n = sizeof(float) * (size_t)B * L;
+  float *d_a = nullptr, *d_b = nullptr, *d_ws = nullptr, *d_out = nullptr;
+  cudaError_t e = cudaMalloc((void**)&d_a, n);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&d_b, n);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&d_ws, sizeof(float) * 2 * (size_t)L);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&d_out, sizeof(float) * (size_t)B);
+  if (e == cudaSuccess) e = cudaMemcpy(d_a, h_a, n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_b, h_b, n, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    magic::cosine_distance_rows(d_a, d_b, B, L, d_ws, d_out, nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(h_out, d_out, sizeof(float) * (size_t)B, cudaMemcpyDeviceToHost);
+  cudaFree(d_a); cudaFree(d_b); cudaFree(d_ws); cudaFree(d_out);
+  if (e != cudaSuccess) return fail(std::string("magic_cosine_distance: ") + cudaGetErrorString(e));
+  return 0;
+}
+
 int magic_comm_unique_id(void* h_id128) {
   if (!h_id128) return fail("null output");
   return done(magic::nccl_unique_id(h_id128));

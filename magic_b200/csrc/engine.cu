@@ -117,7 +117,7 @@ Engine::~Engine() {
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
                   statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
-                  in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_};
+                  in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_, not_binary_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
@@ -292,6 +292,7 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
     MAGIC_CUDA(cudaEventCreateWithFlags(&b.ready, cudaEventDisableTiming));
     MAGIC_CUDA(cudaEventCreateWithFlags(&b.consumed, cudaEventDisableTiming));
   }
+  MAGIC_TRY(alloc((void**)&not_binary_, 16));
   MAGIC_CUDA(cudaStreamCreateWithFlags(&gen_stream_, cudaStreamNonBlocking));
   MAGIC_CUDA(cudaStreamCreateWithFlags(&aux_stream_, cudaStreamNonBlocking));
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_aux_fork_, cudaEventDisableTiming));
@@ -579,16 +580,32 @@ void Engine::mark_consumed(InBuf& b) {
   cudaEventRecord(b.consumed, stream);
   b.consumed_pending = true;
 }
+// The engine keeps images as 1 bit per pixel (first-layer operand, BCE target).  The reference's pipeline only ever
+// produces {0,1} (PNG {0,255} / 255, nearest-neighbour rotation: 8c/overlap_input.py:117, 8c/utils.py:337-338), but its
+// placeholder would accept any float: an array feed with another value must fail loudly, not be thresholded.
+std::string Engine::check_binary(const char* who) {
+  int flag = 0;
+  MAGIC_CUDA(cudaMemcpyAsync(&flag, not_binary_, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  MAGIC_CUDA(cudaStreamSynchronize(stream));
+  if (flag) {
+    MAGIC_CUDA(cudaMemsetAsync(not_binary_, 0, sizeof(int), stream));
+    in_[cur_ ^ 1].filled = false;
+    return std::string(who) + ": X holds values other than 0 and 1 (uint8: 0, 1, 255); the B200 backend trains on binary "
+           "images, as the reference's input pipeline produces them (8c/overlap_input.py:117)";
+  }
+  return "";
+}
 std::string Engine::load_interleaved(const float* d_x) {
   if (!d_x) return "load_interleaved: null input";
   InBuf& b = in_[cur_ ^ 1];
   wait_ready(b);
   prof_begin("input.deinterleave");
-  deinterleave_f32(d_x, B, D, b.X.hi, b.X.ld, stream);
+  deinterleave_f32(d_x, B, D, b.X.hi, b.X.ld, not_binary_, stream);
   pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
   build_kmasks(b, stream);
   b.planes_valid = true;
   prof_end();
+  MAGIC_TRY(check_binary("load_interleaved"));
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
@@ -602,11 +619,12 @@ std::string Engine::load_interleaved_u8(const uint8_t* d_x) {
   InBuf& b = in_[cur_ ^ 1];
   wait_ready(b);
   prof_begin("input.deinterleave");
-  deinterleave_u8(d_x, B, D, b.X.hi, b.X.ld, stream);
+  deinterleave_u8(d_x, B, D, b.X.hi, b.X.ld, not_binary_, stream);
   pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
   build_kmasks(b, stream);
   b.planes_valid = true;
   prof_end();
+  MAGIC_TRY(check_binary("load_interleaved_u8"));
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;
@@ -619,10 +637,11 @@ std::string Engine::load_planar_u8(const uint8_t* l, const uint8_t* r, const uin
   if (!l || !r || !k) return "load_planar_u8: null input";
   InBuf& b = in_[cur_ ^ 1];
   wait_ready(b);
-  planar_u8(l, r, k, B, D, b.X.hi, b.X.ld, stream);
+  planar_u8(l, r, k, B, D, b.X.hi, b.X.ld, not_binary_, stream);
   pack_planes_bits(b.X.hi, b.X.ld, 3 * B, D, b.xb3, xb_ld_, stream);
   build_kmasks(b, stream);
   b.planes_valid = true;
+  MAGIC_TRY(check_binary("load_planar_u8"));
   MAGIC_CUDA(cudaGetLastError());
   mark_consumed(b);
   b.has_labels = false;

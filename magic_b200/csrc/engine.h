@@ -144,6 +144,8 @@ class Engine {
   cudaStream_t gen_stream_ = nullptr;
   cudaEvent_t ev_gate_ = nullptr;   // recorded after the forward pass: earliest start of the next batch's generator
   bool gate_pending_ = false, gen_gate_ = true;
+  int* not_binary_ = nullptr;       // device flag raised by the array feeds when a pixel is neither 0 nor 1
+  std::string check_binary(const char* who);
   void wait_ready(InBuf& b);
   void mark_consumed(InBuf& b);
   std::vector<Act> H_;              // encoder hidden outputs [3B, enc_i + 1]

@@ -181,6 +181,39 @@ __global__ void __launch_bounds__(kLatWarps * 32) latent_metric_kernel(LatentArg
   }
 }
 
+// ------------------------------------------------------------------ cosine_distance(a, b) as a free function
+// (8c/vae.py:438-452: tf.nn.l2_normalize(x, 0) normalises over axis 0 = the BATCH axis, then the products are summed
+// over the latent axis.)  Two small kernels: column sums of squares of a and b, then one warp per row.
+__global__ void __launch_bounds__(256) cosine_colsq_kernel(const float* __restrict__ a, const float* __restrict__ b, int B, int L,
+                                                           float* colsq /* [2L], zeroed */) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= L) return;
+  float sa = 0.f, sb = 0.f;
+  for (int i = blockIdx.y; i < B; i += gridDim.y) {
+    const float x = a[(long long)i * L + j], y = b[(long long)i * L + j];
+    sa += x * x;
+    sb += y * y;
+  }
+  atomicAdd(&colsq[j], sa);
+  atomicAdd(&colsq[L + j], sb);
+}
+__global__ void __launch_bounds__(256) cosine_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int B, int L,
+                                                          const float* __restrict__ colsq, float* __restrict__ out) {
+  const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (i >= B) return;
+  float d = 0.f;
+  for (int j = lane; j < L; j += 32)
+    d += (a[(long long)i * L + j] * rsqrtf(fmaxf(colsq[j], 1e-12f))) * (b[(long long)i * L + j] * rsqrtf(fmaxf(colsq[L + j], 1e-12f)));
+  d = warp_sum(d);
+  if (lane == 0) out[i] = d;
+}
+void cosine_distance_rows(const float* a, const float* b, int B, int L, float* colsq_ws, float* out, cudaStream_t s) {
+  cudaMemsetAsync(colsq_ws, 0, sizeof(float) * 2 * (size_t)L, s);
+  const int slabs = B < 64 ? 1 : 64;
+  cosine_colsq_kernel<<<dim3((L + 255) / 256, slabs), 256, 0, s>>>(a, b, B, L, colsq_ws);
+  cosine_rows_kernel<<<(B + 7) / 8, 256, 0, s>>>(a, b, B, L, colsq_ws, out);
+}
+
 // ------------------------------------------------------------------ latent backward
 // dheads rows: [rot|cost ; lock|cost ; lock|metric ; key|metric], cols [d mu | d log sigma^2].
 // d z / d mu = 1 ;  d z / d lv = 0.5 * sqrt(exp(lv)) * eps = 0.5 * (z - mu).
@@ -420,7 +453,7 @@ void shadow_refresh(const float* p, __nv_bfloat16* hi, __nv_bfloat16* lo, long l
 // ------------------------------------------------------------------ input layout (8c/vae.py:166-179)
 // Each thread converts 8 pixels of one pair: 24 interleaved floats -> 8 bf16 into each of the three planes.
 __global__ void __launch_bounds__(256) deinterleave_kernel(const float* __restrict__ x, int B, int D,
-                                                           __nv_bfloat16* planes, long long ld) {
+                                                           __nv_bfloat16* planes, long long ld, int* not_binary) {
   const int per_row = (int)(ld / 8);
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * per_row) return;
@@ -435,6 +468,10 @@ __global__ void __launch_bounds__(256) deinterleave_kernel(const float* __restri
       const float4 v = src[q];
       f[4 * q] = v.x; f[4 * q + 1] = v.y; f[4 * q + 2] = v.z; f[4 * q + 3] = v.w;
     }
+    bool bad = false;
+#pragma unroll
+    for (int q = 0; q < 24; ++q) bad |= !(f[q] == 0.f || f[q] == 1.f);
+    if (bad) *not_binary = 1;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       lock[q] = ptx::pack_bf16(f[6 * q], f[6 * q + 3]);
@@ -449,6 +486,8 @@ __global__ void __launch_bounds__(256) deinterleave_kernel(const float* __restri
         const int p = p0 + 2 * q + h;
         for (int c = 0; c < 3; ++c)
           v[h][c] = p < D ? x[((long long)i * D + p) * 3 + c] : (p == D ? 1.f : 0.f);   // bias column, then zero pad
+        for (int c = 0; c < 3; ++c)
+          if (!(v[h][c] == 0.f || v[h][c] == 1.f)) *not_binary = 1;
       }
       lock[q] = ptx::pack_bf16(v[0][0], v[1][0]);
       rot[q] = ptx::pack_bf16(v[0][1], v[1][1]);
@@ -459,15 +498,15 @@ __global__ void __launch_bounds__(256) deinterleave_kernel(const float* __restri
   *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + p0) = make_uint4(lock[0], lock[1], lock[2], lock[3]);
   *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + p0) = make_uint4(key[0], key[1], key[2], key[3]);
 }
-void deinterleave_f32(const float* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s) {
+void deinterleave_f32(const float* x, int B, int D, __nv_bfloat16* planes, long long ld, int* not_binary, cudaStream_t s) {
   const long long n = (long long)B * (ld / 8);
-  deinterleave_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(x, B, D, planes, ld);
+  deinterleave_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(x, B, D, planes, ld, not_binary);
 }
 
-// X [B, 3*D] uint8 channel-interleaved ({0,1} or {0,255}: any non-zero byte is a set pixel) -> bf16 planes
+// X [B, 3*D] uint8 channel-interleaved ({0,1} or {0,255}; any other byte raises *not_binary) -> bf16 planes
 // (the compact host feed: 1/4 of the fp32 bytes over PCIe).  Each thread converts 8 pixels (24 bytes).
 __global__ void __launch_bounds__(256) deinterleave_u8_kernel(const uint8_t* __restrict__ x, int B, int D,
-                                                              __nv_bfloat16* planes, long long ld) {
+                                                              __nv_bfloat16* planes, long long ld, int* not_binary) {
   const int per_row = (int)(ld / 8);
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * per_row) return;
@@ -482,6 +521,10 @@ __global__ void __launch_bounds__(256) deinterleave_u8_kernel(const uint8_t* __r
       const uint2 v = src[q];
       *reinterpret_cast<uint2*>(b + 8 * q) = v;
     }
+    bool bad = false;
+#pragma unroll
+    for (int q = 0; q < 24; ++q) bad |= b[q] > 1 && b[q] != 255;
+    if (bad) *not_binary = 1;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const uint32_t one = (e & 1) ? 0x3F800000u : 0x00003F80u;
@@ -496,27 +539,28 @@ __global__ void __launch_bounds__(256) deinterleave_u8_kernel(const uint8_t* __r
   *reinterpret_cast<uint4*>(planes + (long long)(B + i) * ld + p0) = make_uint4(lock[0], lock[1], lock[2], lock[3]);
   *reinterpret_cast<uint4*>(planes + (long long)(2 * B + i) * ld + p0) = make_uint4(key[0], key[1], key[2], key[3]);
 }
-void deinterleave_u8(const uint8_t* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s) {
+void deinterleave_u8(const uint8_t* x, int B, int D, __nv_bfloat16* planes, long long ld, int* not_binary, cudaStream_t s) {
   const long long n = (long long)B * (ld / 8);
-  deinterleave_u8_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(x, B, D, planes, ld);
+  deinterleave_u8_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(x, B, D, planes, ld, not_binary);
 }
 
 __global__ void __launch_bounds__(256) planar_u8_kernel(const uint8_t* __restrict__ lock, const uint8_t* __restrict__ rot,
                                                         const uint8_t* __restrict__ key, int B, int D,
-                                                        __nv_bfloat16* planes, long long ld) {
+                                                        __nv_bfloat16* planes, long long ld, int* not_binary) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)3 * B * ld) return;
   const int c = (int)(idx % ld);
   const long long r = idx / ld;
   const int plane = (int)(r / B), i = (int)(r % B);
   const uint8_t* src = plane == 0 ? rot : (plane == 1 ? lock : key);
-  const float v = c < D ? (float)src[(long long)i * D + c] : (c == D ? 1.f : 0.f);
-  planes[idx] = __float2bfloat16(v);
+  const uint8_t b = c < D ? src[(long long)i * D + c] : (uint8_t)(c == D ? 1 : 0);
+  if (b > 1 && b != 255) *not_binary = 1;
+  planes[idx] = __float2bfloat16(b ? 1.f : 0.f);
 }
 void planar_u8(const uint8_t* lock, const uint8_t* rot, const uint8_t* key, int B, int D, __nv_bfloat16* planes,
-               long long ld, cudaStream_t s) {
+               long long ld, int* not_binary, cudaStream_t s) {
   const long long n = (long long)3 * B * ld;
-  planar_u8_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(lock, rot, key, B, D, planes, ld);
+  planar_u8_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(lock, rot, key, B, D, planes, ld, not_binary);
 }
 
 __global__ void __launch_bounds__(256) planes_to_interleaved_kernel(const __nv_bfloat16* __restrict__ planes, long long ld,

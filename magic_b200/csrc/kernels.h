@@ -43,6 +43,8 @@ struct LatentArgs {
 void latent_forward(const LatentArgs& a, cudaStream_t s);     // z, zdec, kl, def, colsq (cosine) ; sqdiff: also metric
 void latent_metric(const LatentArgs& a, cudaStream_t s);      // distance, training loss, g, colS (needs final colsq)
 void latent_backward(const LatentArgs& a, cudaStream_t s);    // dheads for the four backward streams
+// cosine_distance(a, b) of 8c/vae.py:438-452 on two device arrays [B, L]; colsq_ws: 2L floats of scratch; out[B]
+void cosine_distance_rows(const float* a, const float* b, int B, int L, float* colsq_ws, float* out, cudaStream_t s);
 
 struct AdamArgs {
   float* p;                       // fp32 master parameters, flat
@@ -85,10 +87,11 @@ void shadow_refresh(const float* p, __nv_bfloat16* hi, __nv_bfloat16* lo, long l
 
 // X [B, 3*D] fp32 channel-interleaved (8c/vae.py:166, ch0 lock, ch1 rot, ch2 key) -> planes bf16 [3B, ld]
 // rows [rot; lock; key], 1.0 at col D, zeros after.
-void deinterleave_f32(const float* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s);
-void deinterleave_u8(const uint8_t* x, int B, int D, __nv_bfloat16* planes, long long ld, cudaStream_t s);
+// *not_binary (device) is set to 1 when a value is neither 0 nor 1 (uint8 feeds: nor 255): the first layer reads the images as bits
+void deinterleave_f32(const float* x, int B, int D, __nv_bfloat16* planes, long long ld, int* not_binary, cudaStream_t s);
+void deinterleave_u8(const uint8_t* x, int B, int D, __nv_bfloat16* planes, long long ld, int* not_binary, cudaStream_t s);
 void planar_u8(const uint8_t* lock, const uint8_t* rot, const uint8_t* key, int B, int D, __nv_bfloat16* planes,
-               long long ld, cudaStream_t s);
+               long long ld, int* not_binary, cudaStream_t s);
 void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B, int D, float* x, cudaStream_t s);
 
 // On-device synthetic shape pairs (replaces 8c/overlap_input.py): random filled shapes on a

@@ -273,3 +273,104 @@ def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool 
             raise RuntimeError("another load replaced the engine's input buffers while iterating the dataset")
         eng.swap_batch()
         labels, n = staged, n + 1
+
+
+# ------------------------------------------------------------------ `overlap_input.inputs()` for the B200 backend
+# (8c/overlap_input.py:76-124, called at module level by 8c/main.py:25 and consumed as `images_batch.eval()` /
+# `labels_batch.eval()` at 8c/main.py:44-45 or jointly as `sess.run([images_batch, labels_batch])` at 11a/main.py:65.)
+_PIPELINES: list = []
+
+
+class InputPipeline:
+    """What the reference's queue runners + shuffle_batch are for one experiment: an endless source of batches.  With a
+    dataset under FLAGS.DATA_DIR (the '%d_L.png' / '%d_K.png' pairs + OVERLAP_AREAS) batches come from
+    `device_batches` (row N2), otherwise from the on-device generator (row N1).  Bound to the model when the
+    TangoEncoder is constructed -- main.py calls inputs() before the model exists, exactly like the reference."""
+
+    def __init__(self, flags, seed: int = 0):
+        self.flags, self.seed = flags, seed
+        self.model = None
+        self.batch = None
+        self._iter = None
+        self._dataset = None
+        d = getattr(flags, "DATA_DIR", None)
+        if d and (os.path.isdir(str(d)) or str(d).endswith(".zip")) and os.path.exists(str(d)):
+            areas = os.path.join(str(d), "OVERLAP_AREAS") if os.path.isdir(str(d)) else getattr(flags, "OVERLAP_AREAS", None)
+            if areas and os.path.exists(areas):
+                self._dataset = (str(d), areas)
+
+    @property
+    def source(self) -> str:
+        return "dataset " + self._dataset[0] if self._dataset else "on-device generator"
+
+    def bind(self, model) -> None:
+        self.model, self.batch, self._iter = model, None, None
+
+    def advance(self):
+        """Dequeue the next batch (images and labels together)."""
+        m = self.model
+        if m is None:
+            raise RuntimeError("overlap_input.inputs(): no TangoEncoder has been constructed yet (the handles evaluate on its engine)")
+        if self._dataset is None:
+            self.batch = m.next_device_batch(self.seed)
+            return self.batch
+        if self._iter is None:
+            ds = OverlapDataset(self._dataset[0], self._dataset[1], image_size=self.flags.IMAGE_SIZE) \
+                if not isinstance(self._dataset, OverlapDataset) else self._dataset
+            big = m.engine.B > len(ds)
+            self._iter = device_batches(m, ds, epochs=1 << 40, seed=self.seed, steps=(1 << 60) if big else None)
+        self.batch = next(self._iter)
+        return self.batch
+
+
+class _Handle:
+    def __init__(self, pipeline: InputPipeline):
+        self.pipeline = pipeline
+
+
+class ImagesHandle(_Handle):
+    """`images_batch`: .eval() dequeues a NEW batch and returns a handle onto it that `partial_fit`, `get_predictions`
+    and `reconstruct` accept without the images leaving HBM; np.asarray(handle) materialises [B, 120000] float32."""
+
+    def eval(self, session=None):
+        return self.pipeline.advance()
+
+    def _current(self):
+        return self.pipeline.batch
+
+
+class LabelsHandle(_Handle):
+    """`labels_batch`: .eval() returns the overlap areas of the batch the last images_batch.eval() dequeued (the
+    reference's two .eval() calls dequeue twice and so pair images with the labels of another batch, 8c/main.py:44-45;
+    10a/main.py:64 fixed that with a joint fetch -- here both forms yield a consistent pair)."""
+
+    def eval(self, session=None):
+        if self.pipeline.batch is None:
+            self.pipeline.advance()
+        return self._current()
+
+    def _current(self):
+        return self.pipeline.batch.labels
+
+
+def inputs(normalize: bool = False, reshape: bool = False, rotation: bool = False, flags=None, seed: int = 0):
+    """Returns (images, labels) handles.  The B200 backend implements the configuration every experiment from 7c on
+    uses: normalize=True (pixels {0,1}), reshape=True ([B, 120000] rows), rotation=True (three planes)."""
+    if flags is None:
+        raise ValueError("inputs() needs the experiment's FLAGS")
+    if not getattr(flags, "DATA_DIR", None):
+        raise ValueError("Please supply a data_dir")                      # 8c/overlap_input.py:98-99
+    if not (normalize and reshape and rotation):
+        raise NotImplementedError("the B200 backend feeds the three-stream model: inputs(normalize=True, reshape=True, rotation=True)")
+    p = InputPipeline(flags, seed)
+    _PIPELINES.append(p)
+    del _PIPELINES[:-8]                                                   # pipelines of long-gone experiments
+    return ImagesHandle(p), LabelsHandle(p)
+
+
+def bind_model(model) -> None:
+    """Called by TangoEncoder.__init__: pipelines created before the model existed now evaluate on it."""
+    for p in _PIPELINES:
+        stale = p.model is None or not getattr(getattr(p.model.engine, "_h", None), "value", None)     # never bound / closed
+        if stale or p.flags is model.flags:
+            p.bind(model)

@@ -45,6 +45,10 @@ class DeviceBatch:
         self._ensure_loaded()
         return self.model.engine.export_batch()[0].cpu().numpy()
 
+    def __array__(self, dtype=None, copy=None):
+        a = self.eval()
+        return a if dtype is None else a.astype(dtype)
+
 
 class ResidentBatch(DeviceBatch):
     """A dataset batch that a loader call has already placed in the engine's input buffer
@@ -67,6 +71,10 @@ class DeviceLabels:
     def eval(self) -> np.ndarray:
         self.batch._ensure_loaded()
         return self.batch.model.engine.export_batch()[1].cpu().numpy()
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.eval()
+        return a if dtype is None else a.astype(dtype)
 
 
 class TangoEncoder(object):
@@ -112,6 +120,8 @@ class TangoEncoder(object):
         self.engine = Engine(self.config, device=device)
         self._loaded_key = None
         self._gen_step = 0
+        from . import overlap_input as _oi
+        _oi.bind_model(self)                                   # inputs() handles made before the model now evaluate on it
         if verbose:                                            # the reference's build log, 8c/nohup.out:19-26
             for name, shape in self.engine.param_shapes.items():
                 if len(shape) == 2:
@@ -210,6 +220,40 @@ class TangoEncoder(object):
 
 
 def cosine_distance(a, b):
-    """Batch-axis-normalised cosine sum of 8c/vae.py:438-452, evaluated by the engine's latent kernels inside the
-    step; exposed here only so `from vae import cosine_distance` keeps resolving.  Raises: there is no host path."""
-    raise NotImplementedError("cosine_distance is evaluated on the GPU inside TangoEncoder (no host path)")
+    """`cosine_distance(a, b)` of 8c/vae.py:438-452: both [B, L] arrays l2-normalised over axis 0 (the batch axis, as
+    tf.nn.l2_normalize(x, 0) does) and the products summed over the latent axis -> [B].  Evaluated on the GPU by
+    magic_cosine_distance (inside a step the latent kernels compute the same quantity); there is no host path."""
+    import ctypes as C
+    a = np.ascontiguousarray(a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else a, dtype=np.float32)
+    b = np.ascontiguousarray(b.detach().cpu().numpy() if isinstance(b, torch.Tensor) else b, dtype=np.float32)
+    if a.ndim != 2 or a.shape != b.shape:
+        raise ValueError("cosine_distance expects two arrays of the same shape [B, L]")
+    out = np.empty(a.shape[0], dtype=np.float32)
+    lib = _lib.load()
+    _lib.check(lib.magic_cosine_distance(a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p), a.shape[0], a.shape[1],
+                                         out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+class Session(object):
+    """Stand-in for the `tf.Session` an experiment's main.py opens (8c/main.py:96, 11a/main.py:136) when
+    FLAGS.BACKEND == 'b200': a context manager whose `run(fetches)` evaluates input handles JOINTLY -- images and
+    labels of ONE batch, as `sess.run([images_batch, labels_batch])` does in 11a/main.py:65."""
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+    def run(self, fetches, feed_dict=None):
+        single = not isinstance(fetches, (list, tuple))
+        items = [fetches] if single else list(fetches)
+        pipes = {id(f.pipeline): f.pipeline for f in items if hasattr(f, "pipeline")}
+        for p in pipes.values():
+            p.advance()                                   # one dequeue per run() call, shared by every fetch of it
+        out = [f._current() if hasattr(f, "pipeline") else f for f in items]
+        return out[0] if single else out
+
+    def close(self):
+        pass

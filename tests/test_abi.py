@@ -5,6 +5,7 @@ import ctypes as C
 import os
 import re
 import subprocess
+import sys
 
 import pytest
 
@@ -96,3 +97,49 @@ def test_experiment_directories_expose_the_reference_surface():
         assert F.BATCH_SIZE == {"8c": 100, "8d": 100, "8e": 100, "9a": 24, "11a": 24}[exp]      # <exp>/constants.py:52
         want = m.DISTANCE_METRICS.SQUARED_DIFFERENCE if exp == "11a" else m.DISTANCE_METRICS.COSINE_DISTANCE
         assert F.DISTANCE_METRIC == want                                                           # <exp>/constants.py:60
+
+
+REFERENCE_FLAGS = (   # every attribute of 8c/constants.py:12-89 (11a adds RUN_INTERMEDIATE_TESTS, 11a/constants.py:88)
+    "DATA_DIR DATA_URL INTERNET ALLOW_DOWNLOADS IMAGE_SIZE NUM_EXAMPLES_TO_LOAD_INTO_QUEUE NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN "
+    "NUM_EXAMPLES_PER_EPOCH_FOR_EVAL MAX_EPOCHS TRAINING_STEP MAX_TRAIN_ITERATIONS ROTATE NUM_LAYERS BATCH_SIZE DISTANCE_METRIC "
+    "USE_FP16 TOWER_NAME NUM_THREADS NOTIFICATION_EMAIL EMAIL_INFO RESTORE RESTORE_FROM CHECKPOINT_DIR LEARNING_RATE CHECK_DATASET "
+    "TRAIN_DIR SUMMARIES_DIR USE_TENSORBOARD KEEP_PROBABILITY RUN_NAME PRINT_INFO SEND_LOSS_TO_POOR_MANS_TENSORBOARD_EVERY_N_STEPS "
+    "SAVE_NETSTATE_AND_EMAIL_STATUS_EVERY_N_STEPS").split()
+
+
+def test_experiment_main_modules_have_the_reference_layout():
+    """main.py of every experiment directory: module-level `images_batch, labels_batch = overlap_input.inputs(...)`,
+    `n_samples`, `TrainingException`, and `train(sess, batch_size=FLAGS.BATCH_SIZE, training_epochs=60, display_step=5)`
+    (8c/main.py:25-33; 11a/main.py:37-42 has no display_step); FLAGS carries every reference attribute."""
+    import importlib
+    import inspect
+    sys.path.insert(0, ROOT)
+    for exp in ("8c", "8d", "8e", "9a", "11a"):
+        main = importlib.import_module("experiments.%s.main" % exp)
+        F = main.FLAGS
+        for name in REFERENCE_FLAGS + (["RUN_INTERMEDIATE_TESTS"] if exp == "11a" else []):
+            assert hasattr(F, name), (exp, name)
+        assert F.NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN == (9600 if exp in ("8c", "8d", "8e") else 960)
+        assert main.n_samples == F.NUM_EXAMPLES_PER_EPOCH_FOR_TRAIN
+        assert issubclass(main.TrainingException, Exception)
+        assert hasattr(main.images_batch, "eval") and hasattr(main.labels_batch, "eval")
+        assert main.images_batch.pipeline is main.labels_batch.pipeline
+        params = list(inspect.signature(main.train).parameters.values())
+        want = ["sess", "batch_size", "training_epochs"] + (["display_step"] if exp != "11a" else [])
+        assert [p.name for p in params[:len(want)]] == want, exp
+        assert params[1].default == F.BATCH_SIZE and params[2].default == 60
+        if exp != "11a":
+            assert params[3].default == 5
+        oi = importlib.import_module("experiments.%s.overlap_input" % exp)
+        assert list(inspect.signature(oi.inputs).parameters) == ["normalize", "reshape", "rotation"]   # 8c/overlap_input.py:76
+        with pytest.raises(RuntimeError):
+            main.images_batch.eval()               # no TangoEncoder yet: the handles evaluate on its engine
+
+
+def test_inputs_requires_a_data_dir():
+    from magic_b200 import overlap_input
+
+    class F:
+        DATA_DIR = ""
+    with pytest.raises(ValueError, match="Please supply a data_dir"):          # 8c/overlap_input.py:98-99
+        overlap_input.inputs(normalize=True, reshape=True, rotation=True, flags=F)

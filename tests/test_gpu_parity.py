@@ -260,3 +260,27 @@ def test_packed_first_layer_operand_matches_bf16_planes(precision, monkeypatch):
         assert rel_l2(a[1], b[1]) < tol
         for k in a[4]:
             assert rel_l2(a[4][k], b[4][k]) < tol, k
+
+
+def test_non_binary_input_is_rejected():
+    """The engine keeps images as bits.  The reference's placeholder would take any float X, but its pipeline only ever
+    feeds {0,1} (8c/overlap_input.py:117); an array feed with a grey pixel must raise, not be thresholded silently."""
+    from magic_b200._lib import MagicError
+    ocfg = oracle_config(latent=20, **MINI)
+    _, eng, (xl, xr, xk, y, eps) = make_pair(ocfg, 64, "bf16", seed=0)
+    X = orc.interleave(xl, xr, xk).to(torch.float32).numpy()
+    eng.load_interleaved(X)                                     # binary: accepted
+    Xg = X.copy()
+    Xg[3, 1234] = 0.5
+    with pytest.raises(MagicError, match="other than 0 and 1"):
+        eng.load_interleaved(Xg)
+    with pytest.raises(MagicError, match="other than 0 and 1"):
+        eng.partial_fit_host(Xg, y.numpy().astype(np.float32))
+    X8 = (X * 255).astype(np.uint8)
+    eng.load_interleaved(X8)                                    # {0,255}: accepted
+    X8[5, 77] = 128
+    with pytest.raises(MagicError, match="other than 0 and 1"):
+        eng.load_interleaved(X8)
+    losses, _ = eng.partial_fit_host(X, y.numpy().astype(np.float32))      # the engine is still usable afterwards
+    assert np.all(np.isfinite(losses))
+    eng.close()

@@ -74,6 +74,11 @@ def test_partial_fit_matches_the_oracle_at_the_experiment_geometry(exp, capsys):
     vae.close()
 
 
+def importlib_vae(exp):
+    import importlib
+    return importlib.import_module("experiments.%s.vae" % exp)
+
+
 def test_error_behaviour():
     FLAGS, TangoEncoder = load_experiment("8c")
     vae = TangoEncoder(sess=None, batch_size=4, verbose=False)
@@ -95,23 +100,93 @@ def test_error_behaviour():
     vae.close()
 
 
-def test_driver_trains_on_generated_batches():
-    """experiments/driver.train at a reduced step count: losses finite, reconstruction loss falls from D ln 2
-    (KAT-2 / KAT-3: 8c/nohup.out:27 -> :5039)."""
-    from experiments.driver import train
-    FLAGS, TangoEncoder = load_experiment("8c")
-    log = io.StringIO()
-    vae = train(TangoEncoder, FLAGS, batch_size=128, training_epochs=1, steps_per_epoch=60, log=log, verbose=False)
-    lines = [l for l in log.getvalue().splitlines() if l.startswith("Epoch:")]
-    assert lines and "TRAINING LOSS:" in lines[0] and "[Reconstruction loss:" in lines[0]
+def test_main_train_runs_like_the_reference_driver(capsys):
+    """experiments/8c/main.py: `train(sess, batch_size, training_epochs, display_step)` (8c/main.py:33) for one epoch at
+    batch 128 (75 steps): the per-step loss line in the reference's format, the `mse:` line every 24 steps, the per-epoch
+    cost line; reconstruction loss falls from D ln 2 (KAT-2 / KAT-3: 8c/nohup.out:27 -> :5039)."""
+    import importlib
+    main = importlib.import_module("experiments.8c.main")
+    with main.Session() as sess:
+        vae = main.train(sess, batch_size=128, training_epochs=1, display_step=1, verbose=False)
+    out = capsys.readouterr().out
+    lines = [l for l in out.splitlines() if l.startswith("Epoch: (")]
+    assert len(lines) == 75 and "TRAINING LOSS:" in lines[0] and "[Reconstruction loss:" in lines[0]
     first = float(lines[0].split("Reconstruction loss: ")[1].split(";")[0])
     last = float(lines[-1].split("Reconstruction loss: ")[1].split(";")[0])
     assert abs(first - 40000 * np.log(2)) < 0.03 * 40000 * np.log(2)
-    assert last < 0.6 * first, (first, last)
-    assert "Mean squared error" in log.getvalue()
-    sd = vae.state_dict()
-    assert sd["step"] == 60
+    assert last < 0.7 * first, (first, last)
+    assert out.count("mse: ") == 4                                       # i = 0, 24, 48, 72
+    assert "Epoch: 0001 cost= " in out                                   # 8c/main.py:86-88
+    assert vae.state_dict()["step"] == 75
     vae.close()
+
+
+def test_reference_call_sequence_runs_unchanged(capsys):
+    """The calls 8c/main.py:33-94 makes, in its order and with its expressions, against experiments/8c with
+    BACKEND = 'b200': module-level `overlap_input.inputs(normalize=True, reshape=True, rotation=FLAGS.ROTATE)`,
+    `images_batch.eval()` / `labels_batch.eval()`, `vae.partial_fit(batch_xs, overlap_areas=...)` -> 5 floats,
+    `np.isnan(cost)`, `vae.get_predictions(...)`, `((predictions - areas) ** 2).mean(axis=None)`; then 11a's joint
+    `sess.run([images_batch, labels_batch])` and 6-tuple (11a/main.py:65-68,94-105)."""
+    import importlib
+    from magic_b200.tango import Session
+    overlap_input = importlib.import_module("experiments.8c.overlap_input")
+    FLAGS, TangoEncoder = load_experiment("8c")
+    images_batch, labels_batch = overlap_input.inputs(normalize=True, reshape=True, rotation=FLAGS.ROTATE)
+    sess = Session()
+    vae = TangoEncoder(sess=sess, verbose=False)
+    assert vae.batch_size == FLAGS.BATCH_SIZE == 100
+    costs = []
+    for i in range(3):
+        batch_xs = images_batch.eval()
+        overlap_areas = labels_batch.eval()
+        cost, training_loss, rec_loss, lat_loss, def_loss = vae.partial_fit(batch_xs, overlap_areas=overlap_areas)
+        assert not np.isnan(cost) and isinstance(cost, float)
+        costs.append(cost)
+        if i % 24 == 0:
+            accuracy_testing_images = images_batch.eval()
+            accuracy_testing_overlap_areas = labels_batch.eval()
+            predictions = vae.get_predictions(accuracy_testing_images, overlap_areas=accuracy_testing_overlap_areas)
+            mse = ((predictions - accuracy_testing_overlap_areas) ** 2).mean(axis=None)
+            assert predictions.shape == (100,) and np.isfinite(mse)
+    assert costs[-1] < costs[0]
+    # a caller that insists on arrays gets them, in the reference's layout, and they train the same way
+    X = np.asarray(batch_xs)
+    y = np.asarray(overlap_areas)
+    assert X.shape == (100, 200 * 200 * 3) and X.dtype == np.float32 and set(np.unique(X)) <= {0.0, 1.0}
+    assert y.shape == (100,) and np.all(y <= X.reshape(100, 40000, 3)[:, :, 0].sum(1))
+    assert len(vae.partial_fit(X, overlap_areas=y)) == 5
+    vae.close()
+    # 11a: joint fetch, 6-tuple, inverted predictions
+    overlap_input = importlib.import_module("experiments.11a.overlap_input")
+    FLAGS, TangoEncoder = load_experiment("11a")
+    images_batch, labels_batch = overlap_input.inputs(normalize=True, reshape=True, rotation=FLAGS.ROTATE)
+    with Session() as sess:
+        vae = TangoEncoder(sess=sess, verbose=False)
+        batch_xs, overlap_areas = sess.run([images_batch, labels_batch])
+        cost, training_loss, rec_loss, lat_loss, def_loss, distance = vae.partial_fit(batch_xs, overlap_areas=overlap_areas)
+        assert distance.shape == (24,) and np.isfinite(cost)
+        imgs2, areas2 = sess.run([images_batch, labels_batch])
+        assert imgs2 is not batch_xs                                     # every run() dequeues a new batch
+        predictions = 1. / vae.get_predictions(imgs2, overlap_areas=areas2)
+        assert np.isfinite((np.array(predictions - areas2) ** 2).mean(axis=None))
+        vae.close()
+    with pytest.raises(NotImplementedError):
+        overlap_input.inputs(normalize=False, reshape=True, rotation=True)
+
+
+def test_cosine_distance_is_a_real_call():
+    """`from vae import cosine_distance` (8c/vae.py:438-452): batch-axis l2-normalisation, sum over the latent axis."""
+    cd = importlib_vae("8c").cosine_distance
+    rng = np.random.default_rng(0)
+    for B, L in ((100, 20), (7, 200), (513, 3)):
+        a, b = rng.normal(size=(B, L)).astype(np.float32), rng.normal(size=(B, L)).astype(np.float32)
+        na = a / np.sqrt(np.maximum((a.astype(np.float64) ** 2).sum(0), 1e-12))
+        nb = b / np.sqrt(np.maximum((b.astype(np.float64) ** 2).sum(0), 1e-12))
+        np.testing.assert_allclose(cd(a, b), (na * nb).sum(1), rtol=2e-5, atol=1e-6)
+    z = np.zeros((4, 3), dtype=np.float32)
+    assert np.array_equal(cd(z, z), np.zeros(4, dtype=np.float32))       # the 1e-12 clamp, not a NaN
+    with pytest.raises(ValueError):
+        cd(np.zeros((4, 3)), np.zeros((4, 2)))
 
 
 def test_checkpoint_roundtrip():
