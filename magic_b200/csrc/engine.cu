@@ -116,7 +116,7 @@ Engine::~Engine() {
   cudaStreamSynchronize(stream);
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
-                  statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
+                  statbuf_, g_row_, dist_, losses_dev_, bias_part_, bias_count_, stage_x_, stage_labels_, stage_eps_,
                   in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_, not_binary_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -326,6 +326,8 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   MAGIC_TRY(alloc((void**)&g_row_, sizeof(float) * B));
   MAGIC_TRY(alloc((void**)&dist_, sizeof(float) * B));
   MAGIC_TRY(alloc((void**)&losses_dev_, sizeof(float) * 8));
+  MAGIC_TRY(alloc((void**)&bias_part_, sizeof(float) * 4 * (size_t)L * ((B + kLatBwdSlab - 1) / kLatBwdSlab)));
+  MAGIC_TRY(alloc((void**)&bias_count_, sizeof(unsigned) * ((L + 255) / 256)));
   for (auto& e : ev_bwd_) MAGIC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_comm_, cudaEventDisableTiming));
   MAGIC_TRY(build_plans());
@@ -527,7 +529,8 @@ std::string Engine::build_plans() {
     p.ws = ws_; p.ws_ld = out.ld;
     return finish(p, pl, "dgrad enc");
   };
-  MAGIC_TRY(wgrad2(&pl_wg_head_, H_[E - 1], c.enc[E - 1] + 1, false, dheads_, iHead));
+  // (without the ones column: the heads' bias gradients are summed in fp32 by latent_backward, see LatentArgs.g1_bias)
+  MAGIC_TRY(wgrad2(&pl_wg_head_, H_[E - 1], c.enc[E - 1], false, dheads_, iHead));
   MAGIC_TRY(dgrad2(&pl_dg_head_, dheads_, iHead, H_[E - 1], dH_[E - 1]));
   pl_wg_enc_.assign(E, GemmPlan());
   pl_dg_enc_.assign(E, GemmPlan());
@@ -858,18 +861,20 @@ void Engine::prof_begin(const char* tag, double flops, cudaStream_t on) {
     else cudaEventCreate(e);
   }
   cudaEventRecord(r.a, on);
+  prof_open_.push_back((int)prof_pending_.size());     // begin / end pairs nest (a loader times itself and its map kernels)
   prof_pending_.push_back(r);
 }
 void Engine::prof_end(cudaStream_t on) {
-  if (!profile_ || prof_pending_.empty()) return;
-  cudaEventRecord(prof_pending_.back().b, on ? on : stream);
+  if (!profile_ || prof_open_.empty()) return;
+  cudaEventRecord(prof_pending_[prof_open_.back()].b, on ? on : stream);
+  prof_open_.pop_back();
 }
 std::string Engine::profile_report() {
   cudaStreamSynchronize(gen_stream_);
   cudaStreamSynchronize(stream);
   for (auto& r : prof_pending_) {
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, r.a, r.b);
+    if (cudaEventElapsedTime(&ms, r.a, r.b) != cudaSuccess) { cudaGetLastError(); ms = 0.f; }   // a pair left open by an error path
     ProfAcc* acc = nullptr;
     for (auto& a : prof_acc_) if (a.tag == r.tag) { acc = &a; break; }
     if (!acc) { prof_acc_.push_back(ProfAcc()); acc = &prof_acc_.back(); acc->tag = r.tag; }
@@ -877,6 +882,7 @@ std::string Engine::profile_report() {
     prof_pool_.push_back(r.a); prof_pool_.push_back(r.b);
   }
   prof_pending_.clear();
+  prof_open_.clear();
   std::string out;
   char buf[256];
   for (auto& a : prof_acc_) {
@@ -914,6 +920,9 @@ LatentArgs Engine::latent_args(const float* d_eps3, const float* d_labels) {
   a.g = g_row_; a.distance = dist_;
   a.dz_dec = dz_dec_; a.ld_dz = ld_dz_;
   a.dheads = dheads_.hi; a.dheads_lo = dheads_.lo; a.ld_dheads = dheads_.ld;
+  a.bias_part = bias_part_; a.bias_count = bias_count_;
+  const long long bias_row = lin[iHead].off + (long long)lin[iHead].Kv * lin[iHead].ld;      // row Kv of the heads' matrix
+  a.g1_bias = g1_ + bias_row; a.g2_bias = g2_ + bias_row;
   return a;
 }
 

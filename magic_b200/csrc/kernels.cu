@@ -220,47 +220,79 @@ void cosine_distance_rows(const float* a, const float* b, int B, int L, float* c
 __global__ void __launch_bounds__(256) latent_backward_kernel(LatentArgs a) {
   ptx::grid_dep_wait();
   const int L = a.L, B = a.B;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)B * L) return;
-  const int i = (int)(idx / L), j = (int)(idx % L);
-  const float* h_rot = a.heads + (long long)i * a.ld_heads;
-  const float* h_lock = a.heads + (long long)(B + i) * a.ld_heads;
-  const float* h_key = a.heads + (long long)(2 * B + i) * a.ld_heads;
-  const float zr = a.z[(long long)i * L + j], zl = a.z[(long long)(B + i) * L + j], zk = a.z[(long long)(2 * B + i) * L + j];
-  const float mu = h_lock[j], lv = h_lock[L + j];
-  // --- optimiser 1: cost
-  const float ddef = 2.f * a.def_weight * (zl - zr) * a.inv_bg;
-  const float dz_l1 = a.dz_dec[(long long)i * a.ld_dz + j] * a.inv_bg + ddef;
-  const float dmu_l1 = dz_l1 + mu * a.inv_bg;
-  const float dlv_l1 = dz_l1 * 0.5f * (zl - mu) + 0.5f * (expf(lv) - 1.f) * a.inv_bg;
-  const float dz_r1 = -ddef;
-  const float dlv_r1 = dz_r1 * 0.5f * (zr - h_rot[j]);
-  // --- optimiser 2: metric
-  float da, db;
-  const float gi = a.g[i];
-  if (a.metric == METRIC_COSINE) {
-    const float sa = a.colsq[j], sb = a.colsq[L + j];
-    const float ra = rsqrtf(fmaxf(sa, 1e-12f)), rb = rsqrtf(fmaxf(sb, 1e-12f));
-    const float ah = zl * ra, bh = zk * rb;
-    const float S = a.colS[j];
-    // through x * rsqrt(max(sum x^2, eps)): the normalisation term vanishes when the clamp is active
-    da = (gi * bh - (sa > 1e-12f ? ah * S : 0.f)) * ra;
-    db = (gi * ah - (sb > 1e-12f ? bh * S : 0.f)) * rb;
-  } else {
-    da = gi * 2.f * (zl - zk);
-    db = -da;
+  const int j = blockIdx.x * 256 + threadIdx.x;                 // thread <-> latent column, CTA <-> slab of rows
+  const int i0 = blockIdx.y * kLatBwdSlab, i1 = min(B, i0 + kLatBwdSlab);
+  float bsum[4] = {0.f, 0.f, 0.f, 0.f};                         // g1: d mu, d lv ; g2: d mu, d lv
+  if (j < L) {
+    float sa = 0.f, sb = 0.f, ra = 0.f, rb = 0.f, S = 0.f;
+    if (a.metric == METRIC_COSINE) {
+      sa = a.colsq[j]; sb = a.colsq[L + j];
+      ra = rsqrtf(fmaxf(sa, 1e-12f)); rb = rsqrtf(fmaxf(sb, 1e-12f));
+      S = a.colS[j];
+    }
+    const long long ld = a.ld_dheads;
+    for (int i = i0; i < i1; ++i) {
+      const float* h_rot = a.heads + (long long)i * a.ld_heads;
+      const float* h_lock = a.heads + (long long)(B + i) * a.ld_heads;
+      const float* h_key = a.heads + (long long)(2 * B + i) * a.ld_heads;
+      const float zr = a.z[(long long)i * L + j], zl = a.z[(long long)(B + i) * L + j], zk = a.z[(long long)(2 * B + i) * L + j];
+      const float mu = h_lock[j], lv = h_lock[L + j];
+      // --- optimiser 1: cost
+      const float ddef = 2.f * a.def_weight * (zl - zr) * a.inv_bg;
+      const float dz_l0 = a.dz_dec[(long long)i * a.ld_dz + j] * a.inv_bg;       // through the decoder
+      const float dz_l1 = dz_l0 + ddef;
+      const float dmu_l1 = dz_l1 + mu * a.inv_bg;
+      const float dlv_l1 = dz_l1 * 0.5f * (zl - mu) + 0.5f * (expf(lv) - 1.f) * a.inv_bg;
+      const float dz_r1 = -ddef;
+      const float dlv_r1 = dz_r1 * 0.5f * (zr - h_rot[j]);
+      // --- optimiser 2: metric
+      float da, db;
+      const float gi = a.g[i];
+      if (a.metric == METRIC_COSINE) {
+        const float ah = zl * ra, bh = zk * rb;
+        // through x * rsqrt(max(sum x^2, eps)): the normalisation term vanishes when the clamp is active
+        da = (gi * bh - (sa > 1e-12f ? ah * S : 0.f)) * ra;
+        db = (gi * ah - (sb > 1e-12f ? bh * S : 0.f)) * rb;
+      } else {
+        da = gi * 2.f * (zl - zk);
+        db = -da;
+      }
+      const float dlv_l2 = da * 0.5f * (zl - mu);
+      const float dlv_k2 = db * 0.5f * (zk - h_key[j]);
+      store_split(a.dheads, a.dheads_lo, (long long)i * ld + j, dz_r1);
+      store_split(a.dheads, a.dheads_lo, (long long)i * ld + L + j, dlv_r1);
+      store_split(a.dheads, a.dheads_lo, (long long)(B + i) * ld + j, dmu_l1);
+      store_split(a.dheads, a.dheads_lo, (long long)(B + i) * ld + L + j, dlv_l1);
+      store_split(a.dheads, a.dheads_lo, (long long)(2 * B + i) * ld + j, da);
+      store_split(a.dheads, a.dheads_lo, (long long)(2 * B + i) * ld + L + j, dlv_l2);
+      store_split(a.dheads, a.dheads_lo, (long long)(3 * B + i) * ld + j, db);
+      store_split(a.dheads, a.dheads_lo, (long long)(3 * B + i) * ld + L + j, dlv_k2);
+      bsum[0] += dz_l0 + mu * a.inv_bg;             // = dz_r1 + dmu_l1 with the deformation terms cancelled exactly
+      bsum[1] += dlv_r1 + dlv_l1;
+      bsum[2] += da + db;
+      bsum[3] += dlv_l2 + dlv_k2;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) a.bias_part[((long long)blockIdx.y * 4 + q) * L + j] = bsum[q];
   }
-  const float dlv_l2 = da * 0.5f * (zl - mu);
-  const float dlv_k2 = db * 0.5f * (zk - h_key[j]);
-  const long long ld = a.ld_dheads;
-  store_split(a.dheads, a.dheads_lo, (long long)i * ld + j, dz_r1);
-  store_split(a.dheads, a.dheads_lo, (long long)i * ld + L + j, dlv_r1);
-  store_split(a.dheads, a.dheads_lo, (long long)(B + i) * ld + j, dmu_l1);
-  store_split(a.dheads, a.dheads_lo, (long long)(B + i) * ld + L + j, dlv_l1);
-  store_split(a.dheads, a.dheads_lo, (long long)(2 * B + i) * ld + j, da);
-  store_split(a.dheads, a.dheads_lo, (long long)(2 * B + i) * ld + L + j, dlv_l2);
-  store_split(a.dheads, a.dheads_lo, (long long)(3 * B + i) * ld + j, db);
-  store_split(a.dheads, a.dheads_lo, (long long)(3 * B + i) * ld + L + j, dlv_k2);
+  // the last CTA of this column block to arrive adds the slabs up (plain stores: nothing to clear between steps)
+  __shared__ bool last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(&a.bias_count[blockIdx.x], 1u) == gridDim.y - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  if (j < L) {
+    float t[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int y = 0; y < (int)gridDim.y; ++y) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) t[q] += __ldcg(a.bias_part + ((long long)y * 4 + q) * L + j);
+    }
+    a.g1_bias[j] = t[0]; a.g1_bias[L + j] = t[1];
+    a.g2_bias[j] = t[2]; a.g2_bias[L + j] = t[3];
+  }
+  if (threadIdx.x == 0) a.bias_count[blockIdx.x] = 0u;
 }
 
 static int lat_blocks(int B) { return (B + kLatWarps * kLatRowsPerWarp - 1) / (kLatWarps * kLatRowsPerWarp); }
@@ -272,8 +304,7 @@ void latent_metric(const LatentArgs& a, cudaStream_t s) {
   launch_chain(latent_metric_kernel, dim3(lat_blocks(a.B)), dim3(kLatWarps * 32), sizeof(float) * 3 * a.L, s, a);
 }
 void latent_backward(const LatentArgs& a, cudaStream_t s) {
-  const long long n = (long long)a.B * a.L;
-  launch_chain(latent_backward_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, a);
+  launch_chain(latent_backward_kernel, dim3((a.L + 255) / 256, (a.B + kLatBwdSlab - 1) / kLatBwdSlab), dim3(256), 0, s, a);
 }
 
 // ------------------------------------------------------------------ fused dual Adam (8c/vae.py:314-321)
@@ -622,18 +653,19 @@ __device__ void make_prims(Prim* out, uint64_t key, float side) {
   const uint64_t rf = splitmix64(key + 63);
   const float fx = c + (u01((uint32_t)rf) - 0.5f) * 0.45f * side;           // frame centre: 55..145 of 200
   const float fy = c + (u01((uint32_t)(rf >> 32)) - 0.5f) * 0.45f * side;
+  const float thick = 0.45f + 0.95f * u01((uint32_t)splitmix64(key + 62));   // per-shape thickness: spreads the area like the data's (1376 / 3378 / 5387 px at 10 / 50 / 90 %)
   for (int k = 0; k < kPrims; ++k) {
     const uint64_t r0 = splitmix64(key + 3 * k), r1 = splitmix64(key + 3 * k + 1), r2 = splitmix64(key + 3 * k + 2);
     Prim& q = out[k];
     q.cx = fx + (u01((uint32_t)r0) - 0.5f) * 0.30f * side;                   // +-30 around the frame centre
     q.cy = fy + (u01((uint32_t)(r0 >> 32)) - 0.5f) * 0.30f * side;
     q.box = k >= 2 ? 1 : 0;
-    if (!q.box) {                                                             // body: ellipse, half-axes 5..36
-      q.a = (0.025f + 0.155f * u01((uint32_t)r1)) * side;
-      q.b = (0.025f + 0.155f * u01((uint32_t)(r1 >> 32))) * side;
-    } else {                                                                  // limb: half-length 22..52, half-width 3..9
+    if (!q.box) {                                                             // body: ellipse, half-axes (5..36) x thickness
+      q.a = (0.025f + 0.155f * u01((uint32_t)r1)) * side * thick;
+      q.b = (0.025f + 0.155f * u01((uint32_t)(r1 >> 32))) * side * thick;
+    } else {                                                                  // limb: half-length 22..52, half-width (3..9) x thickness
       q.a = (0.11f + 0.15f * u01((uint32_t)r1)) * side;
-      q.b = (0.015f + 0.03f * u01((uint32_t)(r1 >> 32))) * side;
+      q.b = (0.015f + 0.03f * u01((uint32_t)(r1 >> 32))) * side * thick;
     }
     sincospif(2.f * u01((uint32_t)r2), &q.sn, &q.cs);
   }

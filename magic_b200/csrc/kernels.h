@@ -38,7 +38,14 @@ struct LatentArgs {
   __nv_bfloat16* dheads; // [4B, ld_dheads]: d mu at cols [0,L), d log sigma^2 at [L,2L)
   __nv_bfloat16* dheads_lo;
   long long ld_dheads;
+  // bias gradients of the two heads, summed here in fp32 (they are column sums of dheads in which the deformation terms
+  // of the rot and lock streams cancel exactly; summing the bf16-rounded rows instead loses the remainder):
+  float* bias_part;      // [slabs, 4, L] per-CTA partial sums (scratch)
+  unsigned* bias_count;  // [ceil(L / 256)] arrival counters, zero between launches
+  float* g1_bias;        // [2L] bias row of the heads' gradient, optimiser 1: d mu | d log sigma^2
+  float* g2_bias;        // [2L] optimiser 2
 };
+constexpr int kLatBwdSlab = 32;   // rows per CTA of latent_backward (bias_part holds ceil(B / kLatBwdSlab) slabs)
 
 void latent_forward(const LatentArgs& a, cudaStream_t s);     // z, zdec, kl, def, colsq (cosine) ; sqdiff: also metric
 void latent_metric(const LatentArgs& a, cudaStream_t s);      // distance, training loss, g, colS (needs final colsq)

@@ -28,14 +28,16 @@ CASES = [
 # for every loss, the distances and every gradient tensor of both optimisers.  One exception, and only for the
 # configurations that take 1/distance (9a/vae.py:301, 11a/vae.py:306-311): training_loss, distance and the gradients of
 # training_loss (optimiser 2) sit behind a pole that amplifies ANY rounding, the reference's own fp32 arithmetic
-# included.  For those tensors alone the bound is max(tol, min(10 tol, AMP x floor)), floor = the error of the oracle
-# itself run in float32 (operand precision of the modes relative to fp32: hi+lo bf16 pairs 2^-17, bf16 2^-9).
+# included (with L = 2 a cosine sum is the sum of two terms of either sign).  For those tensors alone the bound is
+# max(tol, AMP x floor), floor = the error of the oracle itself run in float32 and AMP = the operand precision of the
+# mode relative to fp32 (hi+lo bf16 pairs 2^-17, bf16 2^-9; x2).  profiles/r02_parity_table.txt lists every tensor's
+# achieved error, bound and floor; the cost-side gradients and the other four losses of 9a / 11a meet the plain tolerance.
 AMP = {"fp32": 2.0 * 2 ** 7, "bf16": 2.0 * 2 ** 15}
 
 
 def _allowed(ocfg, key, tol, amp, floor):
     behind_pole = ocfg.reciprocal and (key in ("training_loss", "distance") or (isinstance(key, tuple) and key[0] == 2))
-    return max(tol, min(10.0 * tol, amp * floor)) if behind_pole else tol
+    return max(tol, amp * floor) if behind_pole else tol
 
 
 def _log_table(title, report):
@@ -154,9 +156,10 @@ def _ten_steps(ocfg, batch, precision, title, steps=10, names=None):
     return errs
 
 
-# bound on the relative L2 error of the accumulated update: fp32 mode 2 % (sign flips of ~zero gradients in the first,
-# sign-like Adam steps); bf16 mode: the same effect at 2^-9 operand precision
-UPDATE_TOL = {"fp32": 0.02, "bf16": 0.15}
+# bound on the relative L2 error of the accumulated update (measured, profiles/r02_parity_table.txt: fp32 mode <= 0.5 %,
+# bf16 mode 6-9.5 % after the first step and 1-4 % after ten): the first Adam steps are sign-like, so what is compared is
+# the sign of gradients that are zero to working precision
+UPDATE_TOL = {"fp32": 0.01, "bf16": 0.12}
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
