@@ -12,14 +12,13 @@ per-GPU batch stays fixed (weak scaling) and the gradient exchange runs inside t
 
 Printed line (rank 0):
   value     pairs/s of the training loop with a NEW batch every step, produced on the device by the generator (row
-            N1) inside the timed region: generator + zero-stage maps + k-block lists + work order + the step.  The
-            generator's shapes are fitted to the reference's images (tests/test_generator.py holds the operand-stage
-            density of a generated batch within +-0.05 of real batches: 0.94 / 0.96), so zero-stage skipping earns
-            here what it would earn on the reference's data.
+            N1) inside the timed region.  The generator's shapes are fitted to the reference's images
+            (tests/test_generator.py holds the operand-stage density of a generated batch within +-0.05 of real
+            batches: 0.94 / 0.96); every operand stage is multiplied (zero-stage skipping is off by default).
   roofline  the dominant kernel: achieved = EXECUTED tensor FLOPs (algorithmic FLOPs x the fraction of operand stages
             that are multiplied) / its average launch time; frac <= 1.  The dict also carries what explains `value`:
-            resident_value (two batches kept in HBM and alternated: no per-batch kernels), dense_value (every stage
-            multiplied), density, step_frac_of_peak (model FLOPs of the whole step / sustained bf16 peak),
+            resident_value (two batches kept in HBM and alternated: no generator), zero_skip_value (the optional
+            skipping of empty operand stages switched on), density, step_frac_of_peak (model FLOPs of the whole step / sustained bf16 peak),
             issued_over_algorithmic, precision_modes (the 1e-4 "fp32" mode's throughput), configs (the other
             BASELINE.json configs at this N), dp_parity (N > 1: a small data-parallel step against the CPU oracle).
   e2e       the same metric through the public API with HOST inputs: OverlapDataset (the reference's real image
@@ -349,7 +348,7 @@ def dp_parity_check(rank, world, dev):
 
 
 # --------------------------------------------------------------------------- the B200 arm
-PER_BATCH_LAUNCHES = 8     # generate_pairs + kmask_fwd + 2 x kmask_wg + 2 x (gemm_klist + gemm_schedule)
+PER_BATCH_LAUNCHES = 1     # generate_pairs (zero-stage maps are off by default)
 
 
 def run_b200(args):
@@ -442,16 +441,17 @@ def run_b200(args):
         eng.step()
     ms_res = tm.time(resident, Kr) / Kr
 
-    # ---- leg 1d: the headline loop with every operand stage multiplied (no zero-stage skipping)
-    eng.set_option("skip_zero_stages", 0)
-    ms_dense = generator_loop(eng, tm, Kr, 3, 8000)
+    # ---- leg 1d: the headline loop with zero-stage skipping switched on (per-batch maps, lists and work order + skipped
+    # stages; off by default because the reference's images fill 94-97 % of the stages)
     eng.set_option("skip_zero_stages", 1)
+    ms_skip = generator_loop(eng, tm, Kr, 3, 8000)
+    eng.set_option("skip_zero_stages", 0)
 
     # ---- roofline of the dominant kernel family (by summed device time in the timed region)
     fused_wgrad = world == 1 and os.environ.get("MAGIC_FUSE_WGRAD", "1") != "0"
     work = algorithmic_work(cfg, B, early_adam=(world == 1 and os.environ.get("MAGIC_EARLY_ADAM", "1") != "0"),
                             fused_wgrad=fused_wgrad)
-    skipping = os.environ.get("MAGIC_SKIP_ZERO", "1") != "0" and os.environ.get("MAGIC_BITS_A", "1") != "0"
+    skipping = os.environ.get("MAGIC_SKIP_ZERO", "0") != "0" and os.environ.get("MAGIC_BITS_A", "1") != "0"
     roof = None
     shares = {}
     tot_ms = sum(v[0] for v in rep.values()) or 1.0
@@ -489,10 +489,9 @@ def run_b200(args):
                 "algorithmic_per_launch": amount, "executed_per_launch": executed, "executed_fraction_of_main_problem": round(f, 4),
                 "dense_equivalent_frac": round(amount / avg_s * (1e-12 if kind == "tensor" else 1e-9) / peak, 4),
                 "share_of_step": shares[tag],
-                "note": "achieved = executed FLOPs / launch time: the main problem's algorithmic FLOPs (SURVEY 8.4) times the "
-                        "fraction of its 128x64 operand stages that hold a set pixel (the others are exact zeros and are "
-                        "skipped), plus the dense appended small-layer problems; dense_equivalent_frac counts the skipped "
-                        "stages as if they had been multiplied"}
+                "note": "achieved = executed FLOPs / launch time.  Zero-stage skipping is off by default (every stage is "
+                        "multiplied: executed = algorithmic FLOPs of SURVEY 8.4); with MAGIC_SKIP_ZERO=1 executed counts only the "
+                        "fraction of the main problem's 128x64 operand stages that hold a set pixel"}
         break
     model_tflops = value / world * st.model_flops_per_pair * 1e-12
     if roof is None:
@@ -505,10 +504,11 @@ def run_b200(args):
         "issued_over_algorithmic": round(st.gemm_flops_per_step / (st.model_flops_per_pair * B), 4),
         "density_fwd": round(density[0], 4), "density_wgrad": round(density[1], 4),
         "resident_value": round(B * world / (ms_res * 1e-3), 1), "resident_ms_per_step": round(ms_res, 4),
-        "dense_value": round(B * world / (ms_dense * 1e-3), 1), "dense_ms_per_step": round(ms_dense, 4),
+        "zero_skip_value": round(B * world / (ms_skip * 1e-3), 1), "zero_skip_ms_per_step": round(ms_skip, 4),
         "ms_per_step_with_per_launch_events": round(ms_step_events, 4),
-        "legs": "value: new generated batch every step (generator + per-batch kernels timed); resident_value: two batches kept "
-                "in HBM and alternated, %d steps; dense_value: the headline loop with skip_zero_stages = 0, %d steps" % (Kr, Kr),
+        "legs": "value: new generated batch every step (generator timed), every operand stage multiplied; resident_value: two "
+                "batches kept in HBM and alternated, %d steps; zero_skip_value: the headline loop with skip_zero_stages = 1 "
+                "(per-batch maps + skipped empty stages), %d steps" % (Kr, Kr),
     })
     if dp_parity is not None:
         roof["dp_parity"] = dp_parity

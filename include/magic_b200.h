@@ -135,11 +135,13 @@ int magic_export_latents(magic_handle* h, float* d_z3);
  * get_predictions, as 8c/main.py:66-80 does with its test batch; bench.py alternates two resident batches with it. */
 int magic_swap_batch(magic_handle* h);
 
-/* The images are binary and mostly empty (8.5 % of the pixels set, shapes near the canvas centre: README.md:19-27,
- * overlap_micro.zip), and the first encoder layer -- 8c/vae.py:347, 3 of the 4 largest matrix products of the step with
- * its weight gradient -- multiplies them.  The engine keeps them packed (1 bit per pixel) and skips every 128 x 64
- * operand stage without a set pixel: such a stage adds exact zeros, so results are bit-identical to processing it.
- *   magic_set_option(h, "skip_zero_stages", 0)  processes every stage (dense-input timing; default 1)
+/* The images are binary (8.5 % of the pixels set: README.md:19-27, overlap_micro.zip), and the first encoder layer --
+ * 8c/vae.py:347, 3 of the 4 largest matrix products of the step with its weight gradient -- multiplies them.  The engine
+ * keeps them packed (1 bit per pixel) and expands them inside the GEMM.  It can also skip every 128 x 64 operand stage
+ * without a set pixel (such a stage adds exact zeros: results are bit-identical to processing it).  On the reference's
+ * images the shapes sit anywhere on the canvas and 94-97 % of the stages hold a set pixel, so the per-batch maps cost more
+ * than they save and the option is OFF by default; a data set whose shapes leave most of the canvas empty switches it on.
+ *   magic_set_option(h, "skip_zero_stages", 1)  skip empty stages from the next loaded batch on (default 0)
  *   magic_input_density                          fraction of stages with a set pixel in the loaded batch:
  *                                                out2[0] forward GEMM, out2[1] weight-gradient GEMM (synchronises) */
 int magic_set_option(magic_handle* h, const char* name, int32_t value);

@@ -126,6 +126,7 @@ class Engine {
     uint32_t* xb3 = nullptr;        // [3B, xb_ld] the same rows packed 1 bit per pixel, bias column set: the first layer's A operand
     uint32_t* xbits = nullptr;      // = xb3 + B * xb_ld: the packed lock plane, the BCE epilogue's target
     bool planes_valid = false;      // X holds this batch too (false when a loader only wrote the packed rows)
+    bool kmask_valid = false;       // kmask / k-block lists / work order describe this batch (built while skip_zero_stages is on)
     uint32_t* kmask = nullptr;      // zero-stage maps of xb3: [fwd | wgrad group 0 | wgrad group 1] (GemmArgs.kmask)
     float* labels = nullptr;        // [B] generated overlap labels
     int* rot = nullptr;             // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
@@ -136,11 +137,11 @@ class Engine {
   int cur_ = 0;
   int xb_ld_ = 0;
   bool bits_a_ = true;              // first-layer GEMMs read the packed rows (BitsA); MAGIC_BITS_A=0: the bf16 planes
-  bool skip_zero_ = true;           // ... and skip operand stages without a set pixel (MAGIC_SKIP_ZERO=0 / set_option: all stages)
+  bool skip_zero_ = false;          // ... and skip operand stages without a set pixel (MAGIC_SKIP_ZERO=1 / set_option); off: all stages
   int km_fwd_tiles_ = 0, km_fwd_words_ = 0, km_fwd_kb_ = 0;     // map geometry: forward (rows of 128 packed rows x k-blocks of 64 pixels)
   int km_wg_tiles_ = 0, km_wg_words_ = 0;                       // weight gradient (tiles of 128 pixels x k-blocks of 64 batch rows)
   size_t km_wg_off_[2] = {0, 0}, km_total_ = 0;                 // word offsets of the two groups' maps; total words
-  void build_kmasks(InBuf& b, cudaStream_t s);
+  void build_kmasks(InBuf& b, cudaStream_t s, bool force = false);
   std::string launch_maybe_dense(GemmPlan& pl, int* launches, const char* tag);
   cudaStream_t gen_stream_ = nullptr;
   cudaEvent_t ev_gate_ = nullptr;   // recorded after the forward pass: earliest start of the next batch's generator

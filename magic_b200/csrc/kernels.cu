@@ -625,14 +625,15 @@ void planes_to_interleaved_f32(const __nv_bfloat16* planes, long long ld, int B,
 //      bit for bit:  sx = (CS*(2x-W+1) - SN*(2y-W+1) + (W<<14)) >> 15,  sy = (SN*(2x-W+1) + CS*(2y-W+1) + (W<<14)) >> 15;
 //   3. label = the "maximum possible overlap area between the two shapes" (README.md:19-27; the reference's dataset
 //      generator is not in the repository), searched over rotations x translations of the key:
-//        popcount(lock AND T(key)),  T: lock pixel (x, y) reads key pixel
+//        overlap(r, t) = popcount(lock AND T(key)),  T: lock pixel (x, y) reads key pixel
 //          (cKx, cKy) +- ((cs X - sn Y + 8192) >> 14, (sn X + cs Y + 8192) >> 14),  X = x - cLx - tx, Y = y - cLy - ty
 //      with cL / cK the rounded pixel centroids of lock and key ((2 sum + area) / (2 area)), (cs, sn) the Q14 constants
 //      of r * 45 degrees for r = 0..3 and the minus sign (a point reflection through cK) giving r + 4.
-//      Stage 1: the 8 rotations at (tx, ty) = (0, 0), i.e. centroids aligned; stage 2: the first best rotation again at
-//      (+-s, 0) and (0, +-s), s = (3 W + 50) / 100 pixels.  On the reference's 100 real pairs this search reaches 93.5 %
-//      of the stored OVERLAP_AREAS label on average (median 96 %); rotations about the canvas centre alone, the
-//      previous definition, reached 66 %.
+//      The SEARCH runs on every 4th pixel in x and y (1/16 of the lock): first the 8 rotations with the centroids
+//      aligned (t = 0), then the first best rotation at (+-s, 0) and (0, +-s), s = (3 W + 50) / 100 pixels; the label is
+//      the EXACT overlap (all pixels) of the first best of those five candidates.  On the reference's 100 real pairs
+//      this reaches 91 % of the stored OVERLAP_AREAS label on average (median 95 %; tests/test_shape_stats.py);
+//      rotations about the canvas centre alone, the previous definition, reached 66 %.
 //   4. the three bitmaps go out as they are: packed rows [rot; lock; key] of xb3 with the bias column D set -- the
 //      first layer's GEMMs read them as their A operand (BitsA, gemm_sm100.cuh) and the BCE epilogue reads the lock
 //      rows as its target.  With `planes` != nullptr (MAGIC_BITS_A=0) they are also expanded to bf16 operand planes
@@ -757,8 +758,8 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
   uint32_t* const bm[3] = {bm_base, bm_base + bm_pitch, bm_base + 2 * bm_pitch};   // 0 lock, 1 key, 2 rot
   __shared__ Prim prims[2][kPrims];
   __shared__ int rot_q14[2];
-  __shared__ int rot_radius;                   // every lock pixel lies within this distance of the centre
-  __shared__ int counts[kLabelRots + 4];      // label search: 8 rotations, then 4 shifts of the best one
+  __shared__ int counts[kLabelRots + 5];      // label search: 8 rotations, 4 shifts of the best one, exact overlap of the winner
+  __shared__ int rot_box[4];                   // x0, x1, y0, y1: every pixel of the rotated lock lies inside
   __shared__ int cent[6];                      // lock: area, sum x, sum y ; key: the same
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // persistent: the grid is at most one CTA per SM, so the generator shares every SM with the step's GEMM CTA
@@ -772,17 +773,23 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
     rot_q14[0] = __float2int_rn(cs * 16384.f);
     rot_q14[1] = __float2int_rn(sn * 16384.f);
     if (rot_cs_sn) { rot_cs_sn[2 * i] = rot_q14[0]; rot_cs_sn[2 * i + 1] = rot_q14[1]; }
+    // bounding box of the rotated lock: destination = R(-theta) source about the canvas centre, so a primitive centred
+    // at c + p lands around c + (cs px + sn py, -sn px + cs py); nearest-neighbour resampling moves a pixel by < 1.5
     const float c = 0.5f * (side - 1.f);
-    float rad = 0.f;
+    float bx0 = 1e9f, bx1 = -1e9f, by0 = 1e9f, by1 = -1e9f;
     for (int k = 0; k < kPrims; ++k) {
       const Prim& q = prims[0][k];
-      const float ext = q.box ? sqrtf(q.a * q.a + q.b * q.b) : fmaxf(q.a, q.b);
-      rad = fmaxf(rad, sqrtf((q.cx - c) * (q.cx - c) + (q.cy - c) * (q.cy - c)) + ext);
+      const float ext = (q.box ? sqrtf(q.a * q.a + q.b * q.b) : fmaxf(q.a, q.b)) + 2.f;
+      const float px = q.cx - c, py = q.cy - c;
+      const float dx = c + (cs * px + sn * py), dy = c + (-sn * px + cs * py);
+      bx0 = fminf(bx0, dx - ext); bx1 = fmaxf(bx1, dx + ext);
+      by0 = fminf(by0, dy - ext); by1 = fmaxf(by1, dy + ext);
     }
-    rot_radius = (int)ceilf(rad) + 2;
+    rot_box[0] = max(0, (int)floorf(bx0)); rot_box[1] = min(side - 1, (int)ceilf(bx1));
+    rot_box[2] = max(0, (int)floorf(by0)); rot_box[3] = min(side - 1, (int)ceilf(by1));
   }
   if (threadIdx.x == 32) make_prims(prims[1], rng_key(seed, step, 12, (uint64_t)i * 64), (float)side);
-  if (threadIdx.x < kLabelRots + 4) counts[threadIdx.x] = 0;
+  if (threadIdx.x < kLabelRots + 5) counts[threadIdx.x] = 0;
   if (threadIdx.x >= 64 && threadIdx.x < 70) cent[threadIdx.x - 64] = 0;
   __syncthreads();
 
@@ -800,17 +807,17 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
   }
   __syncthreads();
 
-  // ---- 2. rotated lock: one warp per 32-pixel word, ballot assembles the word.  Only rows inside the disc that
-  //         contains the lock can receive pixels.
+  // ---- 2. rotated lock: one warp per 32-pixel word, ballot assembles the word.  Only words that reach into the
+  //         bounding box of the rotated lock can receive pixels.
   {
     const int cs = rot_q14[0], sn = rot_q14[1];
-    const int ylo = max(0, (side - 1) / 2 - rot_radius), yhi = min(side - 1, side / 2 + rot_radius);
-    const int xlo = ylo, xhi = yhi;
+    const int xlo = rot_box[0], xhi = rot_box[1], ylo = rot_box[2], yhi = rot_box[3];
     const int w_begin = (ylo * side) >> 5, w_end = min(nwords, ((yhi * side + side - 1) >> 5) + 1);
     for (int w = w_begin + warp; w < w_end; w += kGenThreads / 32) {
       const int p0 = w * 32;
       const int y0 = (int)__umulhi((uint32_t)p0, inv_side), x0 = p0 - y0 * side;
-      if (x0 + 31 < side && (x0 > xhi || x0 + 31 < xlo)) continue;     // whole word on one row, outside the disc's box
+      // a word lies on one row, or on the end of one and the start of the next
+      if (x0 + 31 < side ? (x0 > xhi || x0 + 31 < xlo) : (x0 > xhi && x0 + 31 - side < xlo)) continue;
       int x = x0 + lane, y = y0;
       if (x >= side) { x -= side; ++y; }
       const uint32_t bit = (p0 + lane < D) ? bit_at(bm[0], rotated_index(x, y, side, cs, sn)) : 0u;
@@ -850,20 +857,18 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
   const int cLx = (2 * cent[1] + areaL) / (2 * areaL), cLy = (2 * cent[2] + areaL) / (2 * areaL);
   const int cKx = (2 * cent[4] + areaK) / (2 * areaK), cKy = (2 * cent[5] + areaK) / (2 * areaK);
   const int zbit = nwords << 5;                            // a bit of the zero padding behind every bitmap
-  // 3b: the 8 rotations with the centroids aligned.  Only words where the lock has pixels; each lane counts its own
-  //     pixel (masked by its lock bit); out-of-canvas sources read the zero padding, so the loop is branch-free.
+  // 3b: search, on every 4th pixel of the lock in x and y: the 8 rotations with the centroids aligned.  Lane <-> one
+  //     sample; its count is masked by its lock bit; out-of-canvas sources read the zero padding (branch-free).
+  const int nsx = (side + 3) >> 2, nsamp = nsx * nsx;
   {
     int cnt[kLabelRots];
 #pragma unroll
     for (int r = 0; r < kLabelRots; ++r) cnt[r] = 0;
-    for (int w = warp; w < nwords; w += kGenThreads / 32) {
-      const uint32_t lw = bm[0][w];
-      if (lw == 0u) continue;
-      const uint32_t lb = (lw >> lane) & 1u;
-      const int p0 = w * 32;
-      const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
-      int x = p0 - y0 * side + lane, y = y0;
-      if (x >= side) { x -= side; ++y; }
+    for (int q0 = warp * 32; q0 < nsamp; q0 += kGenThreads) {
+      const int q = q0 + lane, qy = q / nsx, x = 4 * (q - qy * nsx), y = 4 * qy;
+      const int p = y * side + x;
+      const uint32_t lb = q < nsamp ? (bm[0][p >> 5] >> (p & 31)) & 1u : 0u;
+      if (__ballot_sync(0xffffffffu, lb != 0u) == 0u) continue;
       const int X = x - cLx, Y = y - cLy;
 #pragma unroll
       for (int r = 0; r < kLabelRots / 2; ++r) {
@@ -882,30 +887,27 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
     }
   }
   __syncthreads();
-  // 3c: the first best rotation again, shifted by +-s along x and y
-  {
-    int rb = 0;
+  // 3c: the first best rotation again, shifted by +-s along x and y (same samples)
+  int rb = 0;
 #pragma unroll
-    for (int r = 1; r < kLabelRots; ++r) rb = counts[r] > counts[rb] ? r : rb;
-    const int rr = rb & 3;
-    const int cs = rr == 0 ? rot_cs(0) : rr == 1 ? rot_cs(1) : rr == 2 ? rot_cs(2) : rot_cs(3);
-    const int sn = rr == 0 ? rot_sn(0) : rr == 1 ? rot_sn(1) : rr == 2 ? rot_sn(2) : rot_sn(3);
-    const int sgn = rb >= 4 ? -1 : 1;
-    const int sh = (3 * side + 50) / 100;
+  for (int r = 1; r < kLabelRots; ++r) rb = counts[r] > counts[rb] ? r : rb;
+  const int rr = rb & 3;
+  const int bcs = rr == 0 ? rot_cs(0) : rr == 1 ? rot_cs(1) : rr == 2 ? rot_cs(2) : rot_cs(3);
+  const int bsn = rr == 0 ? rot_sn(0) : rr == 1 ? rot_sn(1) : rr == 2 ? rot_sn(2) : rot_sn(3);
+  const int sgn = rb >= 4 ? -1 : 1;
+  const int sh = (3 * side + 50) / 100;
+  {
     int cnt[4] = {0, 0, 0, 0};
-    for (int w = warp; w < nwords; w += kGenThreads / 32) {
-      const uint32_t lw = bm[0][w];
-      if (lw == 0u) continue;
-      const uint32_t lb = (lw >> lane) & 1u;
-      const int p0 = w * 32;
-      const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
-      int x = p0 - y0 * side + lane, y = y0;
-      if (x >= side) { x -= side; ++y; }
+    for (int q0 = warp * 32; q0 < nsamp; q0 += kGenThreads) {
+      const int q = q0 + lane, qy = q / nsx, x = 4 * (q - qy * nsx), y = 4 * qy;
+      const int p = y * side + x;
+      const uint32_t lb = q < nsamp ? (bm[0][p >> 5] >> (p & 31)) & 1u : 0u;
+      if (__ballot_sync(0xffffffffu, lb != 0u) == 0u) continue;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         const int tx = c == 0 ? sh : c == 1 ? -sh : 0, ty = c == 2 ? sh : c == 3 ? -sh : 0;
         const int X = x - cLx - tx, Y = y - cLy - ty;
-        const int ax = cKx + sgn * ((cs * X - sn * Y + 8192) >> 14), ay = cKy + sgn * ((sn * X + cs * Y + 8192) >> 14);
+        const int ax = cKx + sgn * ((bcs * X - bsn * Y + 8192) >> 14), ay = cKy + sgn * ((bsn * X + bcs * Y + 8192) >> 14);
         const int sp = ((unsigned)ax < (unsigned)side && (unsigned)ay < (unsigned)side) ? ay * side + ax : zbit;
         cnt[c] += (int)((bm[1][sp >> 5] >> (sp & 31)) & lb);
       }
@@ -917,11 +919,32 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int best = 0;
-    for (int r = 0; r < kLabelRots + 4; ++r) best = max(best, counts[r]);
-    labels[i] = (float)best;
+  // 3d: the exact overlap (every lock pixel) of the first best of the five candidates (t = 0 first)
+  {
+    int tb = -1, best = counts[rb];
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (counts[kLabelRots + c] > best) { best = counts[kLabelRots + c]; tb = c; }
+    const int tx = tb == 0 ? sh : tb == 1 ? -sh : 0, ty = tb == 2 ? sh : tb == 3 ? -sh : 0;
+    int cnt = 0;
+    for (int w = warp; w < nwords; w += kGenThreads / 32) {
+      const uint32_t lw = bm[0][w];
+      if (lw == 0u) continue;
+      const uint32_t lb = (lw >> lane) & 1u;
+      const int p0 = w * 32;
+      const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
+      int x = p0 - y0 * side + lane, y = y0;
+      if (x >= side) { x -= side; ++y; }
+      const int X = x - cLx - tx, Y = y - cLy - ty;
+      const int ax = cKx + sgn * ((bcs * X - bsn * Y + 8192) >> 14), ay = cKy + sgn * ((bsn * X + bcs * Y + 8192) >> 14);
+      const int sp = ((unsigned)ax < (unsigned)side && (unsigned)ay < (unsigned)side) ? ay * side + ax : zbit;
+      cnt += (int)((bm[1][sp >> 5] >> (sp & 31)) & lb);
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (lane == 0 && cnt) atomicAdd(&counts[kLabelRots + 4], cnt);
   }
+  __syncthreads();
+  if (threadIdx.x == 0) labels[i] = (float)counts[kLabelRots + 4];
 
   // ---- 4. packed rows [rot; lock; key] with the bias bit (D % 32 == 0: the bitmaps end on a word boundary)
   for (int w = threadIdx.x; w < xb_ld; w += kGenThreads) {

@@ -289,7 +289,8 @@ class Engine:
         return x, y
 
     def set_option(self, name: str, value: int) -> None:
-        """Run-time switches of the engine: "skip_zero_stages" (default 1); see include/magic_b200.h."""
+        """Run-time switches of the engine: "skip_zero_stages" (default 0; takes effect with the next loaded batch); see
+        include/magic_b200.h."""
         check(self.lib.magic_set_option(self._h, name.encode(), int(value)))
 
     def input_density(self) -> Tuple[float, float]:

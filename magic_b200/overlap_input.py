@@ -245,34 +245,53 @@ def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool 
     src = [torch.from_numpy(dataset.lock_bits.view(np.int32)), torch.from_numpy(dataset.key_bits.view(np.int32)),
            torch.from_numpy(dataset.labels)]
     pin = torch.cuda.is_available()
+    # three pinned slots: batch n is being trained on, batch n+1 is crossing PCIe / staged on the device, batch n+2 is
+    # being gathered from the dataset by a worker thread (index_select releases the GIL) while the caller waits for
+    # the losses of step n -- the host gather never sits between two steps
     ring = [(torch.empty((eng.B, wpr), dtype=torch.int32, pin_memory=pin), torch.empty((eng.B, wpr), dtype=torch.int32, pin_memory=pin),
-             torch.empty((eng.B,), dtype=torch.float32, pin_memory=pin)) for _ in range(2)]
+             torch.empty((eng.B,), dtype=torch.float32, pin_memory=pin)) for _ in range(3)]
+    from concurrent.futures import ThreadPoolExecutor
+    pool = ThreadPoolExecutor(max_workers=1)
 
-    def send(n, idx, activate):
-        slot = ring[n % 2]                                    # its previous batch (n - 2) has been consumed by a step
+    def gather(n, idx):
+        slot = ring[n % 3]                                    # its previous batch (n - 3) was consumed two steps ago
         it = torch.from_numpy(np.ascontiguousarray(idx, dtype=np.int64))
         for dst, s_ in zip(slot, src):
             torch.index_select(s_, 0, it, out=dst)
+        return n
+
+    def feed(n, activate):
+        slot = ring[n % 3]
         eng.feed_pairs_bits(slot[0], slot[1], slot[2], seed, n, activate=activate)
         return slot[2].numpy().copy()
 
     order = dataset.index_batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed, steps=steps)
-    idx = next(order, None)
-    if idx is None:
-        return
-    labels = send(0, idx, True)
-    n = 0
-    while True:
+    try:
         idx = next(order, None)
-        staged = send(n + 1, idx, False) if idx is not None else None
-        batch = ResidentBatch(vae, labels)
-        yield batch
-        if staged is None:
+        if idx is None:
             return
-        if vae._loaded_key is not batch._token:
-            raise RuntimeError("another load replaced the engine's input buffers while iterating the dataset")
-        eng.swap_batch()
-        labels, n = staged, n + 1
+        gather(0, idx)
+        labels = feed(0, True)
+        idx = next(order, None)
+        pending = pool.submit(gather, 1, idx) if idx is not None else None
+        n = 0
+        while True:
+            staged = None
+            if pending is not None:
+                pending.result()
+                staged = feed(n + 1, False)
+                idx = next(order, None)
+                pending = pool.submit(gather, n + 2, idx) if idx is not None else None
+            batch = ResidentBatch(vae, labels)
+            yield batch
+            if staged is None:
+                return
+            if vae._loaded_key is not batch._token:
+                raise RuntimeError("another load replaced the engine's input buffers while iterating the dataset")
+            eng.swap_batch()
+            labels, n = staged, n + 1
+    finally:
+        pool.shutdown(wait=True)
 
 
 # ------------------------------------------------------------------ `overlap_input.inputs()` for the B200 backend

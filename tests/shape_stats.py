@@ -59,9 +59,10 @@ def centroid(img: np.ndarray):
     return int((2 * int(xs.sum()) + a) // (2 * a)), int((2 * int(ys.sum()) + a) // (2 * a))
 
 
-def aligned_overlap(lock: np.ndarray, key: np.ndarray, r: int, tx: int = 0, ty: int = 0) -> int:
+def aligned_overlap(lock: np.ndarray, key: np.ndarray, r: int, tx: int = 0, ty: int = 0, stride: int = 1) -> int:
     """popcount(lock AND T(key)) for rotation r (0..7) and shift (tx, ty): lock pixel (x, y) reads key pixel
-    cK +- ((cs X - sn Y + 8192) >> 14, (sn X + cs Y + 8192) >> 14), X = x - cLx - tx, Y = y - cLy - ty."""
+    cK +- ((cs X - sn Y + 8192) >> 14, (sn X + cs Y + 8192) >> 14), X = x - cLx - tx, Y = y - cLy - ty.
+    stride > 1: only lock pixels with x % stride == 0 and y % stride == 0 are counted (the search grid)."""
     side = lock.shape[0]
     (clx, cly), (ckx, cky) = centroid(lock), centroid(key)
     cs, sn, sgn = ROT_CS[r & 3], ROT_SN[r & 3], (-1 if r >= 4 else 1)
@@ -69,19 +70,22 @@ def aligned_overlap(lock: np.ndarray, key: np.ndarray, r: int, tx: int = 0, ty: 
     X, Y = x - clx - tx, y - cly - ty
     sx = ckx + sgn * ((cs * X - sn * Y + 8192) >> 14)
     sy = cky + sgn * ((sn * X + cs * Y + 8192) >> 14)
-    ok = (sx >= 0) & (sx < side) & (sy >= 0) & (sy < side) & (lock > 0)
+    ok = (sx >= 0) & (sx < side) & (sy >= 0) & (sy < side) & (lock > 0) & (x % stride == 0) & (y % stride == 0)
     return int((key[sy[ok], sx[ok]] > 0).sum())
 
 
 def max_overlap_label(lock: np.ndarray, key: np.ndarray) -> int:
-    """The generator's label: 8 rotations with the centroids aligned, then the first best rotation shifted by +-s along
-    x and y, s = (3 side + 50) // 100 (README.md:19-27 "maximum possible overlap area")."""
+    """The generator's label (kernels.cu, phase 3; README.md:19-27 "maximum possible overlap area").  Search on every
+    4th pixel: 8 rotations with the centroids aligned, then the first best rotation shifted by +-s along x and y,
+    s = (3 side + 50) // 100; the label is the exact overlap of the first best of those five candidates."""
     side = lock.shape[0]
-    stage1 = [aligned_overlap(lock, key, r) for r in range(8)]
+    stage1 = [aligned_overlap(lock, key, r, stride=4) for r in range(8)]
     rb = int(np.argmax(stage1))                              # first maximum, like the kernel's strict '>' scan
     s = (3 * side + 50) // 100
-    stage2 = [aligned_overlap(lock, key, rb, tx, ty) for tx, ty in ((s, 0), (-s, 0), (0, s), (0, -s))]
-    return max(stage1 + stage2)
+    shifts = [(0, 0), (s, 0), (-s, 0), (0, s), (0, -s)]
+    stage2 = [stage1[rb]] + [aligned_overlap(lock, key, rb, tx, ty, stride=4) for tx, ty in shifts[1:]]
+    tx, ty = shifts[int(np.argmax(stage2))]
+    return aligned_overlap(lock, key, rb, tx, ty)
 
 
 def stage_density(planes: np.ndarray, B: int):
