@@ -116,7 +116,7 @@ Engine::~Engine() {
   cudaStreamSynchronize(stream);
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
-                  statbuf_, g_row_, dist_, losses_dev_, bias_part_, bias_count_, stage_x_, stage_labels_, stage_eps_,
+                  statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
                   in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_, not_binary_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -270,7 +270,7 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   // two input buffers: the generator fills one on its own stream while the step consumes the other
   // packed rows: wide enough for the 64-column k-blocks of the forward GEMM and the 128-row tiles of the weight
   // gradient (both reach past column D, the bias column, into zero padding)
-  xb_ld_ = (int)round_up(4 * ((D + 1 + 127) / 128), 8);
+  xb_ld_ = (int)round_up(4 * ((D + 1 + 127) / 128 + 1), 8);   // (+ 1 tile: a CTA pair's empty partner tile reads zeros there)
   if (const char* ba = getenv("MAGIC_BITS_A")) bits_a_ = atoi(ba) != 0;
   if (const char* sz = getenv("MAGIC_SKIP_ZERO")) skip_zero_ = atoi(sz) != 0;
   km_fwd_tiles_ = (3 * B + 127) / 128;
@@ -326,8 +326,6 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   MAGIC_TRY(alloc((void**)&g_row_, sizeof(float) * B));
   MAGIC_TRY(alloc((void**)&dist_, sizeof(float) * B));
   MAGIC_TRY(alloc((void**)&losses_dev_, sizeof(float) * 8));
-  MAGIC_TRY(alloc((void**)&bias_part_, sizeof(float) * 4 * (size_t)L * ((B + kLatBwdSlab - 1) / kLatBwdSlab)));
-  MAGIC_TRY(alloc((void**)&bias_count_, sizeof(unsigned) * ((L + 255) / 256)));
   for (auto& e : ev_bwd_) MAGIC_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_comm_, cudaEventDisableTiming));
   MAGIC_TRY(build_plans());
@@ -396,6 +394,7 @@ std::string Engine::build_plans() {
                    i == 0);
       p.e[0] = act_epi(H_[i], lin[i].Nv);
       p.ws = ws_; p.ws_ld = H_[i].ld;
+      p.cta_pair = i == 0;       // the 40000-deep first layer: CTA pairs (tcgen05 cta_group::2) where the variant exists
       if (i == 0 && bits_a_) {   // the images stay packed in HBM: 1 KiB instead of 16 KiB per 128 x 64 stage
         p.a_bits = true;
         p.abits[0].base = in_[alt].xb3; p.abits[0].pitch = xb_ld_; p.abits[0].rows = 3 * B;
@@ -442,6 +441,7 @@ std::string Engine::build_plans() {
     }
     e.aux_split = 1 << 30;
     p.e[0] = e;
+    p.cta_pair = true;
     // MAGIC_CLUSTER_OUT=2|4: CTAs along M form a cluster and receive the weight tile by one multicast load.  Measured
     // on B200 (profiles/r01g): no gain at cluster sizes <= 4 (L2 already merges the concurrent unicast requests) and
     // only 33 clusters of 4 are co-resident (132 of 148 SMs), so the default stays 1.
@@ -464,6 +464,7 @@ std::string Engine::build_plans() {
     add_segments(p, 0, amat(x, false, 0, B, xcols), amat(x, true, 0, B, xcols), amat(dy, false, 0, B, p.N),
                  amat(dy, true, 0, B, p.N), false);
     p.e[0] = f32_epi(g1_ + lin[layer].off, lin[layer].ld, inv_bg);
+    p.cta_pair = layer == iOut;
     MAGIC_TRY(finish(p, pl, "wgrad dec"));
     if (layer != iOut) small_wg.push_back(p);
     if (pl->args.splitk > 1) zero_.push_back({g1_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
@@ -475,6 +476,7 @@ std::string Engine::build_plans() {
     add_segments(p, 0, amat(dy, false, 0, B, p.K), amat(dy, true, 0, B, p.K), wmat(layer, false), wmat(layer, true), false);
     p.e[0] = dact_epi(out, y, lin[layer].Kv, 1 << 30, 0);
     p.ws = ws_; p.ws_ld = out.ld;
+    p.cta_pair = layer == iOut;
     return finish(p, pl, "dgrad dec");
   };
   MAGIC_TRY(wgrad1(&pl_wg_out_, D2_, c.dec[1] + 1, dA_, iOut));
@@ -511,6 +513,7 @@ std::string Engine::build_plans() {
                  amat(dy, false, 2LL * B, 2LL * B, p.N), amat(dy, true, 2LL * B, 2LL * B, p.N), x_exact);
     p.e[0] = f32_epi(g1_ + lin[layer].off, lin[layer].ld, 1.f);
     p.e[1] = f32_epi(g2_ + lin[layer].off, lin[layer].ld, 1.f);
+    p.cta_pair = layer == 0;
     MAGIC_TRY(finish(p, pl, "wgrad enc"));
     if (layer != 0) small_wg.push_back(p);
     else enc0_wg[pl == &pl_wg_enc0_alt_ ? 1 : 0] = p;
@@ -925,7 +928,6 @@ LatentArgs Engine::latent_args(const float* d_eps3, const float* d_labels) {
   a.g = g_row_; a.distance = dist_;
   a.dz_dec = dz_dec_; a.ld_dz = ld_dz_;
   a.dheads = dheads_.hi; a.dheads_lo = dheads_.lo; a.ld_dheads = dheads_.ld;
-  a.bias_part = bias_part_; a.bias_count = bias_count_;
   const long long bias_row = lin[iHead].off + (long long)lin[iHead].Kv * lin[iHead].ld;      // row Kv of the heads' matrix
   a.g1_bias = g1_ + bias_row; a.g2_bias = g2_ + bias_row;
   return a;
@@ -941,7 +943,10 @@ std::string Engine::allreduce(float* buf, size_t n, cudaStream_t s) {
 
 std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) {
   refresh_shadow();
-  zero_fill(statbuf_, sizeof(float) * (8 + 3 * L), stream);
+  {   // the step's statistics and the heads' bias-gradient rows (latent_backward adds into them)
+    const long long bias_row = lin[iHead].off + (long long)lin[iHead].Kv * lin[iHead].ld;
+    zero_fill3(statbuf_, 8 + 3 * L, g1_ + bias_row, train ? 2 * L : 0, g2_ + bias_row, train ? 2 * L : 0, stream);
+  }
   InBuf& ib = in_[cur_];
   wait_ready(ib);
   for (int i = 0; i <= E; ++i)

@@ -162,7 +162,6 @@ class Engine {
   float* ws_ = nullptr; long long ws_ld_ = 0;            // split-K workspace
   float* statbuf_ = nullptr;        // [8 sums | 2L colsq | L colS]
   float *g_row_ = nullptr, *dist_ = nullptr, *losses_dev_ = nullptr;
-  float* bias_part_ = nullptr; unsigned* bias_count_ = nullptr;      // latent_backward's fp32 head-bias sums (LatentArgs)
   void* stage_x_ = nullptr; size_t stage_x_bytes_ = 0;                            // partial_fit_host staging
   float *stage_labels_ = nullptr, *stage_eps_ = nullptr;
   uint32_t* bits_stage_ = nullptr; size_t bits_stage_bytes_ = 0;                     // feed_pairs_bits_host staging

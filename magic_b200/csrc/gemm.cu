@@ -110,10 +110,17 @@ void gemm_schedule(const GemmPlan& pl, cudaStream_t s) {
     gemm_schedule_kernel<<<1, kSchedThreads, 0, s>>>(pl.args, counts, static_cast<int*>(pl.order.get()), (int)pl.items, pl.grid);
 }
 
-template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false>
+template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false, bool CG2 = false>
 static cudaError_t set_smem() {
-  return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN, A_BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  return cudaFuncSetAttribute(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN, A_BITS, CG2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                               (int)gemm_smem_bytes(EPI));
+}
+// (kind, epilogue, packed A) combinations that exist as CTA-pair kernels: the 40000-wide GEMMs of the step
+static bool has_pair_variant(int kind, int epi, bool a_bits) {
+  if (kind == GEMM_FWD) return a_bits ? (epi == EPI_STORE_F32 || epi == EPI_ACT) : (epi == EPI_BCE);
+  if (kind == GEMM_WGRAD) return epi == EPI_STORE_F32;
+  if (kind == GEMM_DGRAD) return !a_bits && epi == EPI_STORE_F32;
+  return false;
 }
 
 std::string gemm_init() {
@@ -146,6 +153,13 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<false, true, EPI_ACT, 256, true>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, true>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_SCATTER_F32, 256, true>();
+  // CTA pairs (tcgen05 cta_group::2)
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_BCE, 256, false, true>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, false, true>();
+  if (e == cudaSuccess) e = set_smem<false, false, EPI_STORE_F32, 256, false, true>();
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_STORE_F32, 256, true, true>();
+  if (e == cudaSuccess) e = set_smem<false, true, EPI_ACT, 256, true, true>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, true, true>();
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
   cudaFuncSetAttribute(gemm_schedule_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaFuncSetAttribute(gemm_klist_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -316,6 +330,27 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   }
   int cm_b = (b_mn && (p.cluster_m == 2 || p.cluster_m == 4)) ? p.cluster_m : 1;
   while (cm_b > 1 && ((p.M + kBlockM - 1) / kBlockM) % cm_b != 0) cm_b >>= 1;   // every CTA of a cluster gets a real M tile
+  // CTA pairs: 256 x 256 tiles, each CTA loads half of the B tile's columns (an odd last M tile is paired with an empty one,
+  // whose loads are clipped to zeros and whose rows the epilogue masks).  MAGIC_CG2=0 keeps the single-CTA kernels.
+  static const bool cg2_enabled = !(getenv("MAGIC_CG2") && atoi(getenv("MAGIC_CG2")) == 0);
+  const bool linear = p.epi == EPI_STORE_F32;   // SCATTER_F32 stores plain values to peer memory: never split
+  const bool can_split = linear || (p.ws != nullptr && p.ngroups == 1 && (p.epi == EPI_ACT || p.epi == EPI_DACT));
+  const int total_kb = (p.K + kBlockK - 1) / kBlockK * p.nseg;
+  auto split_for = [&](int cmx) {               // split-K slices when `cmx` CTAs share a work item
+    const int tiles_x = (((p.M + kBlockM - 1) / kBlockM + cmx - 1) / cmx) * ((p.N + bn - 1) / bn) * p.ngroups;
+    int sp = 1;
+    if (can_split) sp = p.force_splitk > 0 ? p.force_splitk : choose_splitk(tiles_x, total_kb, num_sms / cmx, !linear);
+    int per = (total_kb + sp - 1) / sp;
+    while (sp > 1 && (long long)(sp - 1) * per >= total_kb) { --sp; per = (total_kb + sp - 1) / sp; }
+    return sp;
+  };
+  // the kernel that runs is the epilogue's own variant, or -- split along K with a finishing pass -- the fp32-store one
+  const bool pair_direct = has_pair_variant(p.kind, p.epi, p.a_bits);
+  const bool pair_two_pass = !linear && can_split && has_pair_variant(p.kind, EPI_STORE_F32, p.a_bits) && split_for(2) > 1;
+  const bool pair = p.cta_pair && cg2_enabled && cm_b == 1 && bn == 256 && num_sms >= 2 &&
+                    (pair_two_pass || (pair_direct && (linear || !can_split || split_for(2) == 1)));
+  pl.cta_pair = pair;
+  const int bdiv = pair ? 2 : cm_b;                 // B columns fetched per CTA = bn / bdiv
   for (int g = 0; g < p.ngroups; ++g)
     for (int s = 0; s < p.nseg; ++s) {
       const Mat& A = p.a[g][s];
@@ -332,10 +367,10 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       if (!err.empty()) return "A: " + err;
       if (!b_mn) {   // Mat[N,K]
         if (B.cols != p.K) return "B cols != K";
-        err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, bn);
+        err = make_tmap(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, pair ? bn / 2 : bn);
       } else {       // Mat[K,N]
         if (B.rows != p.K) return "B rows != K";
-        err = make_tmap_mn(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, (bn / 64) / cm_b);
+        err = make_tmap_mn(&pl.args.tb[g][s], B.ptr, B.cols, B.rows, B.ld, kBlockK, (bn / 64) / bdiv);
       }
       if (!err.empty()) return "B: " + err;
     }
@@ -357,20 +392,12 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.tiles_m = (p.M + kBlockM - 1) / kBlockM;
   a.tiles_n = (p.N + bn - 1) / bn;
   a.bn = bn;
-  const int cm = cm_b;
+  const int cm = pair ? 2 : cm_b;
   a.cluster_m = cm;
-  a.tiles_m /= cm;                                   // cluster rows from here on
+  a.tiles_m = (a.tiles_m + cm - 1) / cm;             // cluster rows from here on
   a.m_fastest = p.N > p.M ? 1 : 0;   // keep the larger operand's tiles adjacent in time so it is read from HBM once
   const int tiles = a.tiles_m * a.tiles_n * a.ngroups;
-  const int total_kb = a.nseg * a.kblocks;
-  const bool linear = p.epi == EPI_STORE_F32;   // SCATTER_F32 stores plain values to peer memory: never split
-  const bool can_split = linear || (p.ws != nullptr && p.ngroups == 1 && (p.epi == EPI_ACT || p.epi == EPI_DACT));
-  int split = 1;
-  if (can_split) split = p.force_splitk > 0 ? p.force_splitk : choose_splitk(tiles, total_kb, num_sms, !linear);
-  {
-    int per = (total_kb + split - 1) / split;
-    while (split > 1 && (long long)(split - 1) * per >= total_kb) { --split; per = (total_kb + split - 1) / split; }
-  }
+  const int split = split_for(cm);
   a.splitk = split;
   pl.two_pass = false;
   for (int g = 0; g < p.ngroups; ++g) a.epi[g] = p.e[g];
@@ -404,7 +431,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.xdev = nullptr;
   pl.xbuf.reset();
   if (!p.extra.empty()) {
-    if (p.epi != EPI_STORE_F32 || pl.epi != EPI_STORE_F32 || cm != 1) return "extra problems need EPI_STORE_F32 and no cluster";
+    if (p.epi != EPI_STORE_F32 || pl.epi != EPI_STORE_F32 || (cm != 1 && !pair)) return "extra problems need EPI_STORE_F32 and no multicast cluster";
     if ((int)p.extra.size() > kMaxExtra) return "too many extra problems";
     std::vector<GemmExtraDev> host(p.extra.size());
     memset(host.data(), 0, sizeof(GemmExtraDev) * host.size());
@@ -426,10 +453,10 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
         if (!err.empty()) return "extra A: " + err;
         if (!b_mn) {
           if (Bm.cols != x.K) return "extra B cols != K";
-          err = make_tmap(&d.tb[sgm], Bm.ptr, Bm.cols, Bm.rows, Bm.ld, kBlockK, bn);
+          err = make_tmap(&d.tb[sgm], Bm.ptr, Bm.cols, Bm.rows, Bm.ld, kBlockK, pair ? bn / 2 : bn);
         } else {
           if (Bm.rows != x.K) return "extra B rows != K";
-          err = make_tmap_mn(&d.tb[sgm], Bm.ptr, Bm.cols, Bm.rows, Bm.ld, kBlockK, bn / 64);
+          err = make_tmap_mn(&d.tb[sgm], Bm.ptr, Bm.cols, Bm.rows, Bm.ld, kBlockK, (bn / 64) / (pair ? 2 : 1));
         }
         if (!err.empty()) return "extra B: " + err;
       }
@@ -438,7 +465,7 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       if ((reinterpret_cast<uintptr_t>(x.e.out) & 15) != 0 || (x.e.ld_out * 4) % 16 != 0) return "extra output not 16-byte aligned";
       std::string err = make_tmap_out(&d.tout[0], x.e.out, true, x.N, x.M, x.e.ld_out);
       if (!err.empty()) return "extra out: " + err;
-      const int tm = (x.M + kBlockM - 1) / kBlockM, tn = (x.N + bn - 1) / bn;
+      const int tm = ((x.M + kBlockM - 1) / kBlockM + cm - 1) / cm, tn = (x.N + bn - 1) / bn;     // cluster rows
       a.x_item0[i] = item0;
       a.x_m[i] = x.M; a.x_n[i] = x.N; a.x_kb[i] = (x.K + kBlockK - 1) / kBlockK; a.x_tn[i] = tn;
       item0 += tm * tn;
@@ -500,42 +527,44 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   return "";
 }
 
-template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false>
+template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false, bool CG2 = false>
 static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
   const int cm = pl.args.cluster_m;
-  if (cm <= 1 || A_BITS) {
-    launch_chain(gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN, A_BITS>, dim3(pl.grid), dim3(gemm_threads(EPI, A_BITS)),
-                 gemm_smem_bytes(EPI), s, pl.args);
+  auto kernel = gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN, A_BITS, CG2>;
+  if (cm <= 1) {
+    launch_chain(kernel, dim3(pl.grid), dim3(gemm_threads(EPI, A_BITS)), gemm_smem_bytes(EPI), s, pl.args);
     return;
   }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof cfg);
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = cm;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
-  cfg.blockDim = dim3(gemm_threads(EPI));
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;       // CTA pairs chain like every other step kernel
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.blockDim = dim3(gemm_threads(EPI, A_BITS));
   cfg.dynamicSmemBytes = gemm_smem_bytes(EPI);
   cfg.stream = s;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = (CG2 && pdl_enabled()) ? 2 : 1;
   // A cluster lives inside one GPC, so fewer than num_sms / cm clusters may be co-resident; the persistent loop
-  // strides by the number of clusters, which must therefore all be resident at once.
+  // strides by the number of clusters.
   static int max_clusters[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (max_clusters[cm] == 0) {
     cfg.gridDim = dim3(pl.grid);
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, &cfg) != cudaSuccess || n <= 0) {
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess || n <= 0) {
       (void)cudaGetLastError();
       n = pl.grid / cm;
     }
     max_clusters[cm] = n;
-    if (getenv("MAGIC_VERBOSE")) fprintf(stderr, "[magic] cluster_m=%d: %d co-resident clusters\n", cm, n);
+    if (getenv("MAGIC_VERBOSE")) fprintf(stderr, "[magic] cluster_m=%d%s: %d co-resident clusters\n", cm, CG2 ? " (CTA pairs)" : "", n);
   }
   long long ncl = pl.items < max_clusters[cm] ? pl.items : max_clusters[cm];
   cfg.gridDim = dim3((unsigned)(ncl * cm));
-  cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<A_MN, B_MN, EPI, BN>, pl.args);
+  cudaLaunchKernelEx(&cfg, kernel, pl.args);
 }
 
 int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
@@ -543,8 +572,14 @@ int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
   if (pl.two_pass) {
     zero_fill(pl.ws, sizeof(float) * pl.ws_ld * pl.args.M, s);
   }
-  const int key = pl.kind * 8 + pl.epi + (pl.args.bn == 128 ? 64 : 0) + (pl.a_bits ? 128 : 0);
+  const int key = pl.kind * 8 + pl.epi + (pl.args.bn == 128 ? 64 : 0) + (pl.a_bits ? 128 : 0) + (pl.cta_pair ? 256 : 0);
   switch (key) {
+    case 256 + GEMM_FWD * 8 + EPI_BCE: launch_variant<false, true, EPI_BCE, 256, false, true>(pl, s); break;
+    case 256 + GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32, 256, false, true>(pl, s); break;
+    case 256 + GEMM_DGRAD * 8 + EPI_STORE_F32: launch_variant<false, false, EPI_STORE_F32, 256, false, true>(pl, s); break;
+    case 256 + 128 + GEMM_FWD * 8 + EPI_STORE_F32: launch_variant<false, true, EPI_STORE_F32, 256, true, true>(pl, s); break;
+    case 256 + 128 + GEMM_FWD * 8 + EPI_ACT: launch_variant<false, true, EPI_ACT, 256, true, true>(pl, s); break;
+    case 256 + 128 + GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32, 256, true, true>(pl, s); break;
     case 128 + GEMM_FWD * 8 + EPI_STORE_F32: launch_variant<false, true, EPI_STORE_F32, 256, true>(pl, s); break;
     case 128 + GEMM_FWD * 8 + EPI_ACT: launch_variant<false, true, EPI_ACT, 256, true>(pl, s); break;
     case 128 + GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32, 256, true>(pl, s); break;

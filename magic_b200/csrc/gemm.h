@@ -28,6 +28,7 @@ struct GemmPlan {
   GemmArgs args;
   int kind = 0, epi = 0, grid = 0;
   bool a_bits = false;   // the A_BITS kernel variant: the main problem's A operand is read as packed bits (args.abits)
+  bool cta_pair = false; // the CG2 kernel variant (clusters of two CTAs, args.cluster_m == 2)
   long long items = 0;   // work items (per cluster when args.cluster_m > 1)
   // split-K with a non-linear epilogue: GEMM accumulates fp32 into ws (red.add), then finish applies epi
   bool two_pass = false;
@@ -61,6 +62,7 @@ struct GemmProblem {
   std::vector<GemmExtra> extra;   // appended problems (EPI_STORE_F32 only)
   int block_n = 0;           // tile width: 0 = heuristic, 128 or 256 forces it (self-test)
   int cluster_m = 1;         // CTAs per cluster along M sharing the B tile by TMA multicast (FWD / WGRAD kinds; 1, 2 or 4)
+  bool cta_pair = false;     // ask for the CTA-pair kernel (tcgen05 cta_group::2, 256 x 256 tiles): used when the variant exists
   float* ws = nullptr;       // fp32 workspace [M, ws_ld] for two-pass split-K (ACT / DACT); may be null
   long long ws_ld = 0;
   // A as packed bits instead of a[g][*] (FWD: bits of A[M,K]; WGRAD: bits of A[K,M]; see BitsA in gemm_sm100.cuh).

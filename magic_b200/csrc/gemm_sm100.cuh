@@ -182,7 +182,7 @@ __device__ __forceinline__ WorkItem decode_work(const GemmArgs& a, int w, int cr
     while (e + 1 < a.nextra && x >= a.x_item0[e + 1]) ++e;
     const int l = x - a.x_item0[e];
     it.g = -1 - e;
-    it.m0 = (l / a.x_tn[e]) * kBlockM;
+    it.m0 = ((l / a.x_tn[e]) * a.cluster_m + crank) * kBlockM;      // (x_item0 counts cluster rows, like tiles_m)
     it.n0 = (l % a.x_tn[e]) * a.bn;
     it.kb0 = 0;
     it.kb1 = a.nseg * a.x_kb[e];
@@ -627,7 +627,11 @@ __device__ __forceinline__ void expand16(uint32_t v16, uint32_t (&w)[8]) {
 }
 
 // ---------------------------------------------------------------------------- the kernel
-template <bool A_MN, bool B_MN, int EPI, int BN, bool A_BITS = false>
+// CG2: the CTA-pair variant (tcgen05 cta_group::2, ptx.cuh): launched as clusters of two, args.cluster_m == 2; a work
+// item is a 256 x BN tile, CTA `crank` of the pair owns its rows [128 crank, 128 crank + 128) -- A tile, accumulator,
+// epilogue -- and loads columns [BN/2 crank, BN/2 crank + BN/2) of the B tile; the leader (crank 0) issues the MMAs.
+// Six pipeline stages of 16 + 16 KiB instead of four of 16 + 32.
+template <bool A_MN, bool B_MN, int EPI, int BN, bool A_BITS = false, bool CG2 = false>
 // 112 registers: three of this kernel's warps (3 x 32 x 112) and three warps of the batch generator (3 x 32 x 56) fit
 // the 16K registers of one SM sub-partition, so the generator's CTA stays co-resident with every GEMM variant; it is
 // the 576-thread BCE variant has five warps on a sub-partition, hence 96.
@@ -644,9 +648,10 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       args.trace[(size_t)blockIdx.x * 64 + 11] = (long long)gt;
     }
   }
-  using Cfg = TileCfg<BN>;
+  static_assert(!CG2 || BN == 256, "CTA pairs run 256 x 256 tiles");
+  using Cfg = TileCfg<CG2 ? BN / 2 : BN>;  // per-CTA share of a stage: a pair member holds half of the B tile's columns
   constexpr int kNS = Cfg::kStagesN;       // pipeline stages
-  constexpr int kAcc = Cfg::kAcc;          // accumulator stages
+  constexpr int kAcc = 512 / BN;           // accumulator stages
   extern __shared__ uint8_t smem_raw[];
   // 128-byte swizzle atoms need 1024-byte aligned stage bases
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -679,17 +684,19 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         ptx::tma_prefetch_desc(&args.tb[g][s]);
       }
     for (int i = 0; i < kNS; ++i) {
-      ptx::mbar_init(&full_bar[i], A_BITS ? 2 : 1);   // the producer's expect_tx arrival + the stage's expander warp
-      ptx::mbar_init(&empty_bar[i], CM);   // one arrival per CTA of the cluster (multicast commit)
+      // arrivals on a stage's "full" barrier: the producer's expect_tx (+ the stage's expander warp); in a CTA pair the
+      // leader's barrier also takes the other CTA's producer (and expander) -- only the leader's is ever waited on
+      ptx::mbar_init(&full_bar[i], (A_BITS ? 2 : 1) * (CG2 ? 2 : 1));
+      ptx::mbar_init(&empty_bar[i], CG2 ? 1 : CM);   // one arrival per committing CTA (multicast commit); a pair: the leader's
     }
     for (int i = 0; i < kAcc; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
-      ptx::mbar_init(&tempty_bar[i], epi_warps(EPI) * 32);
+      ptx::mbar_init(&tempty_bar[i], CG2 ? 2 * epi_warps(EPI) : epi_warps(EPI) * 32);   // pair: one arrival per epilogue warp of both CTAs
     }
     ptx::fence_barrier_init();
   } else if (warp == 1) {
-    ptx::tmem_alloc(tmem_ptr, kTmemCols);
-    ptx::tmem_relinquish();
+    if constexpr (CG2) { ptx::tmem_alloc_pair(tmem_ptr, kTmemCols); ptx::tmem_relinquish_pair(); }
+    else { ptx::tmem_alloc(tmem_ptr, kTmemCols); ptx::tmem_relinquish(); }
   }
   ptx::tc_fence_before();
   if (CM > 1) ptx::cluster_sync();       // barriers of every CTA are initialised before anybody multicasts into them
@@ -700,8 +707,11 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
   ptx::grid_dep_wait();     // everything above overlapped the previous kernel's tail; its outputs are visible from here
   if (threadIdx.x == 0) MAGIC_TR(2);
 
+  // pair: the leader's barriers as seen from either CTA (its own address space for the leader itself)
+  [[maybe_unused]] const bool leader = !CG2 || crank == 0;
+  auto leader_addr = [&](const void* local) { return CG2 ? ptx::mapa_u32(ptx::smem_u32(local), 0u) : ptx::smem_u32(local); };
   if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer (one thread)
+    // ------------------------------------------------------------ TMA producer (one thread; in a pair: one per CTA)
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (int w = work0; w < total_work; w += work_stride) {
@@ -715,13 +725,30 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
           const int seg = kb / it.kblocks;
           const int k0 = (kb - seg * it.kblocks) * kBlockK;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          stage_last[stage] = walk.done() ? 1u : 0u;
           const bool a_by_tma = !A_BITS || it.g < 0;   // A_BITS: the main problem's A stage is written by the expander warps
-          ptx::mbar_expect_tx(&full_bar[stage], a_by_tma ? Cfg::kBytes : Cfg::kBytesB);
           uint8_t* sa = smem_a + stage * kStageBytesA;
           uint8_t* sb = smem_b + stage * Cfg::kBytesB;
           const CUtensorMap* ta = it.g >= 0 ? &args.ta[it.g][seg] : &args.xdev[-1 - it.g].ta[seg];
           const CUtensorMap* tb = it.g >= 0 ? &args.tb[it.g][seg] : &args.xdev[-1 - it.g].tb[seg];
+          if constexpr (CG2) {
+            // both CTAs' bytes are counted on the leader's barrier: it expects the pair's total, the other CTA only arrives
+            const uint32_t fb = leader_addr(&full_bar[stage]);
+            if (leader) {
+              stage_last[stage] = walk.done() ? 1u : 0u;
+              ptx::mbar_expect_tx(&full_bar[stage], 2u * (a_by_tma ? Cfg::kBytes : Cfg::kBytesB));
+            } else {
+              ptx::mbar_arrive_cluster(fb);
+            }
+            if (a_by_tma) {
+              if constexpr (!A_MN) ptx::tma_load_2d_pair(ta, fb, sa, k0, it.m0);                 // box {64 k, 128 m}
+              else ptx::tma_load_3d_pair(ta, fb, sa, 0, k0, it.m0 >> 6);                         // box {64 m, 64 k, 2 slabs}
+            }
+            const int nh = it.n0 + crank * (BN / 2);                                             // this CTA's half of the B tile
+            if constexpr (!B_MN) ptx::tma_load_2d_pair(tb, fb, sb, k0, nh);                      // box {64 k, BN/2 n}
+            else ptx::tma_load_3d_pair(tb, fb, sb, 0, k0, nh >> 6);                              // box {64 n, 64 k, BN/128 slabs}
+          } else {
+          stage_last[stage] = walk.done() ? 1u : 0u;
+          ptx::mbar_expect_tx(&full_bar[stage], a_by_tma ? Cfg::kBytes : Cfg::kBytesB);
           if (a_by_tma) {
             if constexpr (!A_MN) {
               ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);              // box {64 k, 128 m}
@@ -739,16 +766,19 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
             ptx::tma_load_3d_multicast(tb, &full_bar[stage], sb + crank * per * kAtomBytes, 0, k0,
                                        (it.n0 >> 6) + crank * per, cmask);
           }
+          }
           if (w == work0 && first_kb) MAGIC_TR(3);
           first_kb = false;
           if (++stage == kNS) { stage = 0; phase ^= 1; }
         }
       }
+      // the other CTA of a pair issues no MMAs: its trigger for the next kernel of the stream comes when its loads are out
+      if (CG2 && !leader) ptx::grid_dep_launch();
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(kBlockM, BN, A_MN, B_MN);
+    // ------------------------------------------------------------ MMA issuer (one thread; in a pair: the leader's)
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(CG2 ? 2 * kBlockM : kBlockM, BN, A_MN, B_MN);
       // K-major SW128: 8-row groups 1024 B apart, K advance = 32 B inside the swizzle row.
       // MN-major SW128: 64-element MN atoms kBlockK*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO),
       //                 K advance = 16 rows * 128 B.
@@ -780,14 +810,17 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             const uint64_t da = (static_cast<uint64_t>(desc_hi) << 32) | (a_lo + k * (a_kadv >> 4));
             const uint64_t db = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + k * (b_kadv >> 4));
-            ptx::umma_bf16(d_tmem, da, db, idesc, (!first_kb || k > 0) ? 1u : 0u);
+            if constexpr (CG2) ptx::umma_bf16_pair(d_tmem, da, db, idesc, (!first_kb || k > 0) ? 1u : 0u);
+            else ptx::umma_bf16(d_tmem, da, db, idesc, (!first_kb || k > 0) ? 1u : 0u);
           }
-          if (CM > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
+          if constexpr (CG2) ptx::umma_commit_pair(&empty_bar[stage], (uint16_t)3);   // frees the stage in both CTAs
+          else if (CM > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
           else ptx::umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
           if (++stage == kNS) { stage = 0; phase ^= 1; }
           first_kb = false;
         } while (!last_kb);
-        ptx::umma_commit(&tfull_bar[acc]);        // accumulator complete -> epilogue
+        if constexpr (CG2) ptx::umma_commit_pair(&tfull_bar[acc], (uint16_t)3);   // both CTAs' epilogues
+        else ptx::umma_commit(&tfull_bar[acc]);   // accumulator complete -> epilogue
         if (iter == 0) MAGIC_TR(5);
         if (iter < 8) MAGIC_TR(16 + iter * 5 + 1);
       }
@@ -842,6 +875,17 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       if (warp == 2 && lane == 0 && w == work0) MAGIC_TR(7);
       if (warp == 2 && lane == 0 && iter < 8) MAGIC_TR(16 + iter * 5 + 2);
       bool arrived = false;
+      // hand the accumulator stage back to the MMA issuer: per thread on this CTA's barrier, or -- in a pair -- one
+      // arrival per warp on the leader's, which waits for the epilogue warps of both CTAs
+      auto release_acc = [&](uint32_t a_) {
+        ptx::tc_fence_before();
+        if constexpr (CG2) {
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive_cluster(leader_addr(&tempty_bar[a_]));
+        } else {
+          ptx::mbar_arrive(&tempty_bar[a_]);
+        }
+      };
       // Two chunks are read per TMEM wait: a tcgen05.ld queues behind the MMAs already issued for the next tile, so
       // every separate load-wait round trip costs ~1-2 us during which the accumulator stays locked (r01i: the BCE
       // kernel ran 0.043 ms slower than its main loop with an epilogue that only read TMEM).  With 16 epilogue
@@ -876,18 +920,14 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         if (two) ptx::tmem_ld_32x32(tbase + c1 * 32, rb);
         ptx::tmem_ld_wait();
         if (grp + (k + kBatch) * kGroups >= nchunks || k + kBatch >= kMaxOwn) {   // this warp's last TMEM read of the accumulator
-          ptx::tc_fence_before();
-          ptx::mbar_arrive(&tempty_bar[acc]);
+          release_acc(acc);
           arrived = true;
           if (warp == 2 && lane == 0 && iter < 8) MAGIC_TR(16 + iter * 5 + 3);
         }
         process(ra, k);
         if (two) process(rb, k + 1);
       }
-      if (!arrived) {
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(&tempty_bar[acc]);
-      }
+      if (!arrived) release_acc(acc);
       if (warp == 2 && lane == 0 && iter < 8) MAGIC_TR(16 + iter * 5 + 4);
     }
     if (warp == 2 && lane == 0) MAGIC_TR(8);
@@ -912,13 +952,13 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     // a warp's next k-block are fetched while it expands the current one -- four k-block times ahead of their use.
     // (448 threads: two more warps per stage -- 576 threads -- do not fit the 16 K registers of an SM sub-partition at
     // this kernel's 112 registers, and one warp per stage already keeps up with the MMAs: profiles/r01p)
-    static_assert(kNS == kExpandWarps, "expander warp e serves pipeline stage e");
+    static_assert(kNS >= kExpandWarps, "expander warp e serves the k-blocks e, e + 4, ... of the CTA's sequence");
     const int ew = warp - (2 + epi_warps(EPI));
     struct Cursor { KbWalk walk; int w, m0, g, kblocks; bool valid; };
     auto open = [&](Cursor& c) {
       c.valid = false;
       while (c.w < total_work) {
-        const WorkItem it = decode_work(args, work_item_at(args, c.w), 0);
+        const WorkItem it = decode_work(args, work_item_at(args, c.w), crank);
         c.walk.begin(args, it);
         if (!c.walk.done()) { c.m0 = it.m0; c.g = it.g; c.kblocks = it.kblocks; c.valid = true; return; }
         c.w += work_stride;
@@ -957,12 +997,13 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     advance(pre, 4);
     uint2 now[4], nxt[4];
     fetch(cur, now);
-    uint8_t* const stage_base = smem_a + ew * kStageBytesA + lane * 128;
     const int x = lane & 7;
-    uint32_t phase = 0;
+    uint32_t pos = (uint32_t)ew;                          // position in the CTA's k-block sequence: stage pos % kNS
     while (cur.valid) {
       fetch(pre, nxt);
-      ptx::mbar_wait(&empty_bar[ew], phase ^ 1);          // the MMAs that read this stage have retired
+      const uint32_t st = pos % kNS, phase = (pos / kNS) & 1u;
+      uint8_t* const stage_base = smem_a + st * kStageBytesA + lane * 128;
+      ptx::mbar_wait(&empty_bar[st], phase ^ 1);          // the MMAs that read this stage have retired
       if (cur.g >= 0 && !(args.epi[0].dbg & 8)) {     // dbg 8: timing experiment, the stage is left as it is
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -979,8 +1020,11 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         ptx::fence_proxy_async_smem();                    // generic-proxy writes -> visible to the MMA's async-proxy reads
       }
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&full_bar[ew]);
-      phase ^= 1;
+      if (lane == 0) {
+        if constexpr (CG2) ptx::mbar_arrive_cluster(leader_addr(&full_bar[st]));
+        else ptx::mbar_arrive(&full_bar[st]);
+      }
+      pos += kExpandWarps;
 #pragma unroll
       for (int q = 0; q < 4; ++q) now[q] = nxt[q];
       cur = pre;
@@ -993,7 +1037,8 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
   else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, kTmemCols);
+    if constexpr (CG2) ptx::tmem_dealloc_pair(tmem_base, kTmemCols);
+    else ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
   if constexpr (EPI == EPI_BCE) {
     if (threadIdx.x == 64 && work0 < total_work) {

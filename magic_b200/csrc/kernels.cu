@@ -44,6 +44,18 @@ __global__ void __launch_bounds__(256) zero_kernel(uint4* p, long long n16, uint
   if (i < n16) p[i] = make_uint4(0u, 0u, 0u, 0u);
   if (i < ntail) tail[i] = 0u;
 }
+// three ranges in one launch (the step's statistics and the two bias rows latent_backward adds into)
+__global__ void __launch_bounds__(256) zero3_kernel(float* p0, int n0, float* p1, int n1, float* p2, int n2) {
+  ptx::grid_dep_wait();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n0) p0[i] = 0.f;
+  if (i < n1) p1[i] = 0.f;
+  if (i < n2) p2[i] = 0.f;
+}
+void zero_fill3(float* p0, int n0, float* p1, int n1, float* p2, int n2, cudaStream_t s) {
+  const int n = n0 > n1 ? (n0 > n2 ? n0 : n2) : (n1 > n2 ? n1 : n2);
+  if (n > 0) launch_chain(zero3_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, s, p0, n0, p1, n1, p2, n2);
+}
 void zero_fill(void* ptr, size_t bytes, cudaStream_t s) {   // ptr 16-byte aligned, bytes a multiple of 4
   const long long n16 = (long long)(bytes / 16);
   const int ntail = (int)((bytes % 16) / 4);
@@ -217,10 +229,12 @@ void cosine_distance_rows(const float* a, const float* b, int B, int L, float* c
 // ------------------------------------------------------------------ latent backward
 // dheads rows: [rot|cost ; lock|cost ; lock|metric ; key|metric], cols [d mu | d log sigma^2].
 // d z / d mu = 1 ;  d z / d lv = 0.5 * sqrt(exp(lv)) * eps = 0.5 * (z - mu).
+// CTA = 64 latent columns x 4 row groups; a slab of kLatBwdSlab rows per CTA, so each thread walks kLatBwdSlab / 4 rows.
 __global__ void __launch_bounds__(256) latent_backward_kernel(LatentArgs a) {
   ptx::grid_dep_wait();
   const int L = a.L, B = a.B;
-  const int j = blockIdx.x * 256 + threadIdx.x;                 // thread <-> latent column, CTA <-> slab of rows
+  const int tc = threadIdx.x & 63, rg = threadIdx.x >> 6;
+  const int j = blockIdx.x * 64 + tc;
   const int i0 = blockIdx.y * kLatBwdSlab, i1 = min(B, i0 + kLatBwdSlab);
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};                         // g1: d mu, d lv ; g2: d mu, d lv
   if (j < L) {
@@ -231,7 +245,7 @@ __global__ void __launch_bounds__(256) latent_backward_kernel(LatentArgs a) {
       S = a.colS[j];
     }
     const long long ld = a.ld_dheads;
-    for (int i = i0; i < i1; ++i) {
+    for (int i = i0 + rg; i < i1; i += 4) {
       const float* h_rot = a.heads + (long long)i * a.ld_heads;
       const float* h_lock = a.heads + (long long)(B + i) * a.ld_heads;
       const float* h_key = a.heads + (long long)(2 * B + i) * a.ld_heads;
@@ -272,27 +286,21 @@ __global__ void __launch_bounds__(256) latent_backward_kernel(LatentArgs a) {
       bsum[2] += da + db;
       bsum[3] += dlv_l2 + dlv_k2;
     }
-#pragma unroll
-    for (int q = 0; q < 4; ++q) a.bias_part[((long long)blockIdx.y * 4 + q) * L + j] = bsum[q];
   }
-  // the last CTA of this column block to arrive adds the slabs up (plain stores: nothing to clear between steps)
-  __shared__ bool last;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(&a.bias_count[blockIdx.x], 1u) == gridDim.y - 1;
-  __syncthreads();
-  if (!last) return;
-  __threadfence();
-  if (j < L) {
-    float t[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int y = 0; y < (int)gridDim.y; ++y) {
+  // the heads' bias gradients: the four row groups meet in shared memory, one atomic per (column, sum) and CTA into
+  // the bias rows of g1 / g2 (cleared with the step's statistics, Engine::run_forward)
+  __shared__ float red[4][4][64];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) t[q] += __ldcg(a.bias_part + ((long long)y * 4 + q) * L + j);
+  for (int q = 0; q < 4; ++q) red[rg][q][tc] = bsum[q];
+  __syncthreads();
+  if (rg == 0 && j < L) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float t = red[0][q][tc] + red[1][q][tc] + red[2][q][tc] + red[3][q][tc];
+      float* dst = (q < 2 ? a.g1_bias : a.g2_bias) + ((q & 1) ? L + j : j);
+      if (t != 0.f) atomicAdd(dst, t);
     }
-    a.g1_bias[j] = t[0]; a.g1_bias[L + j] = t[1];
-    a.g2_bias[j] = t[2]; a.g2_bias[L + j] = t[3];
   }
-  if (threadIdx.x == 0) a.bias_count[blockIdx.x] = 0u;
 }
 
 static int lat_blocks(int B) { return (B + kLatWarps * kLatRowsPerWarp - 1) / (kLatWarps * kLatRowsPerWarp); }
@@ -304,7 +312,7 @@ void latent_metric(const LatentArgs& a, cudaStream_t s) {
   launch_chain(latent_metric_kernel, dim3(lat_blocks(a.B)), dim3(kLatWarps * 32), sizeof(float) * 3 * a.L, s, a);
 }
 void latent_backward(const LatentArgs& a, cudaStream_t s) {
-  launch_chain(latent_backward_kernel, dim3((a.L + 255) / 256, (a.B + kLatBwdSlab - 1) / kLatBwdSlab), dim3(256), 0, s, a);
+  launch_chain(latent_backward_kernel, dim3((a.L + 63) / 64, (a.B + kLatBwdSlab - 1) / kLatBwdSlab), dim3(256), 0, s, a);
 }
 
 // ------------------------------------------------------------------ fused dual Adam (8c/vae.py:314-321)
@@ -1037,9 +1045,9 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
 // p >> 5 (numpy packbits(bitorder='little')): 10 KB per pair instead of 80 KB as uint8 or 480 KB as the float32
 // array the reference feeds.  Persistent CTAs, one pair at a time: the lock's bitmap goes to shared memory, lock and
 // key words pass straight through to their packed rows of xb3 (tail bits masked, bias column set), and each warp
-// assembles 32 rotated pixels into one word with a ballot -- the generator's phase 2; the disc that bounds the lock
-// (outside of which the rotated plane is empty) is measured from the bitmap while it is loaded: the farthest set
-// pixel from the centre, in doubled coordinates.  Output is the packed rows only (the GEMMs' A operand and the BCE
+// assembles 32 rotated pixels into one word with a ballot -- the generator's phase 2; only words that reach into the
+// bounding box of the rotated lock are visited (the lock's own box is measured from the bitmap while it is loaded and
+// its corners are rotated).  Output is the packed rows only (the GEMMs' A operand and the BCE
 // target).
 // Same footprint as the generator (384 threads, at most 56 registers, one CTA per SM): three of its warps fit beside
 // the GEMM's warps in a sub-partition's 16 K registers, so it runs UNDER the step instead of making GEMM CTAs wait for
@@ -1052,7 +1060,8 @@ __global__ void __maxnreg__(56) pairs_bits_kernel(const uint32_t* __restrict__ l
                                                                        int* rot_cs_sn) {
   extern __shared__ uint32_t bm[];              // the lock's bitmap: nwords words (5 KB at 200 x 200)
   __shared__ int q14[2];
-  __shared__ int r2max;                         // max over the lock's pixels of (2x - W + 1)^2 + (2y - W + 1)^2
+  __shared__ int box[4];                        // the lock's bounding box: min x, max x, min y, max y
+  __shared__ int rbox[4];                       // ... of the rotated lock: x0, x1, y0, y1
   const int D = side * side;
   const int nwords = (D + 31) >> 5;
   const uint32_t tail = (D & 31) ? ((1u << (D & 31)) - 1u) : 0xffffffffu;     // bits past D in the last word are ignored
@@ -1071,14 +1080,13 @@ __global__ void __maxnreg__(56) pairs_bits_kernel(const uint32_t* __restrict__ l
       q14[0] = __float2int_rn(cs * 16384.f);
       q14[1] = __float2int_rn(sn * 16384.f);
       if (rot_cs_sn) { rot_cs_sn[2 * i] = q14[0]; rot_cs_sn[2 * i + 1] = q14[1]; }
-      r2max = 0;
+      box[0] = side; box[1] = -1; box[2] = side; box[3] = -1;
     }
     __syncthreads();
-    int r2 = 0;
+    int bx0 = side, bx1 = -1, by0 = side, by1 = -1;
     auto far = [&](int p) {
       const int y = (int)__umulhi((uint32_t)p, inv_side), x = p - y * side;
-      const int X2 = 2 * x - side + 1, Y2 = 2 * y - side + 1;
-      r2 = max(r2, X2 * X2 + Y2 * Y2);
+      bx0 = min(bx0, x); bx1 = max(bx1, x); by0 = min(by0, y); by1 = max(by1, y);
     };
     for (int w = threadIdx.x; w < xb_ld; w += kPairsBitsThreads) {
       const uint32_t m = w == nwords - 1 ? tail : 0xffffffffu;
@@ -1088,11 +1096,11 @@ __global__ void __maxnreg__(56) pairs_bits_kernel(const uint32_t* __restrict__ l
       if (w < nwords) bm[w] = vl;
       olock[w] = vl | bias;
       okey[w] = vk | bias;
-      orot[w] = bias;                           // the words inside the lock's disc are overwritten below
+      orot[w] = bias;                           // the words inside the rotated lock's box are overwritten below
       if (vl) {
         const int p0 = w * 32;
         const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
-        if (p0 - y0 * side + 31 < side) {       // one canvas row: the farthest set pixel is the first or the last one
+        if (p0 - y0 * side + 31 < side) {       // one canvas row: its extreme set pixels are the first and the last one
           far(p0 + __ffs(vl) - 1);
           far(p0 + 31 - __clz(vl));
         } else {                                // the word wraps onto the next row(s): look at every set pixel
@@ -1100,18 +1108,32 @@ __global__ void __maxnreg__(56) pairs_bits_kernel(const uint32_t* __restrict__ l
         }
       }
     }
-    if (r2) atomicMax(&r2max, r2);
+    if (bx1 >= 0) { atomicMin(&box[0], bx0); atomicMax(&box[1], bx1); atomicMin(&box[2], by0); atomicMax(&box[3], by1); }
     __syncthreads();
     const int cs = q14[0], sn = q14[1];
-    // rotation keeps the distance from the centre; nearest-neighbour rounding moves a sample by less than one pixel
-    const int rd = (int)ceilf(sqrtf((float)r2max)) + 4;               // doubled coordinates: + 2 pixels
-    const int lo = max(0, (side - 1 - rd) >> 1), hi = min(side - 1, (side + rd) >> 1);
-    const int w_begin = (lo * side) >> 5, w_end = min(nwords, ((hi * side + side - 1) >> 5) + 1);
+    if (threadIdx.x == 0) {
+      // destination = R(-theta) source about the canvas centre: rotate the four corners of the lock's box;
+      // nearest-neighbour rounding moves a sample by less than 1.5 pixels
+      const float c = 0.5f * (side - 1.f), fc = cs * (1.f / 16384.f), fs = sn * (1.f / 16384.f);
+      float x0 = 1e9f, x1 = -1e9f, y0 = 1e9f, y1 = -1e9f;
+      for (int k = 0; k < 4; ++k) {
+        const float px = (float)box[k & 1] - c, py = (float)box[2 + (k >> 1)] - c;
+        const float dx = c + (fc * px + fs * py), dy = c + (-fs * px + fc * py);
+        x0 = fminf(x0, dx); x1 = fmaxf(x1, dx); y0 = fminf(y0, dy); y1 = fmaxf(y1, dy);
+      }
+      const bool empty = box[1] < 0;
+      rbox[0] = empty ? side : max(0, (int)floorf(x0 - 2.f)); rbox[1] = empty ? -1 : min(side - 1, (int)ceilf(x1 + 2.f));
+      rbox[2] = empty ? side : max(0, (int)floorf(y0 - 2.f)); rbox[3] = empty ? -1 : min(side - 1, (int)ceilf(y1 + 2.f));
+    }
+    __syncthreads();
+    const int xlo = rbox[0], xhi = rbox[1], lo = rbox[2], hi = rbox[3];
+    const int w_begin = (max(lo, 0) * side) >> 5, w_end = hi < 0 ? 0 : min(nwords, ((hi * side + side - 1) >> 5) + 1);
     for (int w = w_begin + warp; w < w_end; w += kPairsBitsThreads / 32) {
       const int p0 = w * 32;
       const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
       const int x0 = p0 - y0 * side;
-      if (x0 + 31 < side && (x0 > hi || x0 + 31 < lo)) continue;      // whole word on one row, outside the disc's box
+      // a word lies on one row, or on the end of one and the start of the next
+      if (x0 + 31 < side ? (x0 > xhi || x0 + 31 < xlo) : (x0 > xhi && x0 + 31 - side < xlo)) continue;
       int x = x0 + lane, y = y0;
       while (x >= side) { x -= side; ++y; }
       const uint32_t bit = (p0 + lane < D) ? bit_at(bm, rotated_index(x, y, side, cs, sn)) : 0u;
@@ -1221,6 +1243,7 @@ void build_kmask_wgrad(const uint32_t* xb, int xb_ld, int krows, int tiles_m, ui
   cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)
 void kernels_init() {
   MAGIC_MAX_CARVEOUT(zero_kernel);
+  MAGIC_MAX_CARVEOUT(zero3_kernel);
   MAGIC_MAX_CARVEOUT(latent_forward_kernel);
   MAGIC_MAX_CARVEOUT(latent_metric_kernel);
   MAGIC_MAX_CARVEOUT(latent_backward_kernel);

@@ -40,16 +40,15 @@ struct LatentArgs {
   long long ld_dheads;
   // bias gradients of the two heads, summed here in fp32 (they are column sums of dheads in which the deformation terms
   // of the rot and lock streams cancel exactly; summing the bf16-rounded rows instead loses the remainder):
-  float* bias_part;      // [slabs, 4, L] per-CTA partial sums (scratch)
-  unsigned* bias_count;  // [ceil(L / 256)] arrival counters, zero between launches
-  float* g1_bias;        // [2L] bias row of the heads' gradient, optimiser 1: d mu | d log sigma^2
+  float* g1_bias;        // [2L] bias row of the heads' gradient, optimiser 1: d mu | d log sigma^2 (zero before the launch)
   float* g2_bias;        // [2L] optimiser 2
 };
-constexpr int kLatBwdSlab = 32;   // rows per CTA of latent_backward (bias_part holds ceil(B / kLatBwdSlab) slabs)
+constexpr int kLatBwdSlab = 32;   // rows per CTA of latent_backward
 
 void latent_forward(const LatentArgs& a, cudaStream_t s);     // z, zdec, kl, def, colsq (cosine) ; sqdiff: also metric
 void latent_metric(const LatentArgs& a, cudaStream_t s);      // distance, training loss, g, colS (needs final colsq)
-void latent_backward(const LatentArgs& a, cudaStream_t s);    // dheads for the four backward streams
+void latent_backward(const LatentArgs& a, cudaStream_t s);    // dheads for the four backward streams, head bias gradients
+void zero_fill3(float* p0, int n0, float* p1, int n1, float* p2, int n2, cudaStream_t s);   // three float ranges, one launch
 // cosine_distance(a, b) of 8c/vae.py:438-452 on two device arrays [B, L]; colsq_ws: 2L floats of scratch; out[B]
 void cosine_distance_rows(const float* a, const float* b, int B, int L, float* colsq_ws, float* out, cudaStream_t s);
 

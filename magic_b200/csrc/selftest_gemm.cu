@@ -84,6 +84,7 @@ static void host_ref(int kind, int M, int N, int K, int nseg, const HostMat* a, 
 }
 
 static int g_cluster = 1;   // cluster_m applied to the problems built below
+static bool g_pair = false; // cta_pair applied to the problems built below (CTA-pair kernels where the variant exists)
 static int g_bn = 0;        // block_n applied to the problems built below (0 = the planner's choice)
 static int g_bits = 0;      // bench(): A operand as packed bits (all zero)
 static float g_density = 1.f;   // bench() with g_bits: fraction of operand stages marked non-zero in a random zero-stage map
@@ -100,7 +101,7 @@ static void test_store(int kind, int M, int N, int K, int nseg, int split, int s
   CK(cudaMemset(dout, 0, sizeof(float) * M * ldo));
   GemmProblem p;
   p.kind = kind; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
-  p.cluster_m = g_cluster;
+  p.cluster_m = g_cluster; p.cta_pair = g_pair;
   p.block_n = g_bn;
   for (int s = 0; s < nseg; ++s) { p.a[0][s] = a[s].mat(); p.b[0][s] = b[s].mat(); }
   EpiArgs e = {};
@@ -130,7 +131,7 @@ static void test_wgrad_groups(int M, int N, int K, int sms) {
   float* dout[2];
   long long ldo = (N + 3) / 4 * 4;
   GemmProblem p;
-  p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K;
+  p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K; p.cta_pair = g_pair;
   for (int g = 0; g < 2; ++g) {
     a[g].init(K, M, (M + 63) / 64 * 64, 1.f, true);
     b[g].init(K, N, (N + 63) / 64 * 64, 1.f);
@@ -169,7 +170,7 @@ static void test_wgrad_extras(int sms) {
   float* xout[4];
   const long long ldo = 512;
   GemmProblem p;
-  p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K; p.block_n = g_bn;
+  p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K; p.block_n = g_bn; p.cta_pair = g_pair;
   for (int g = 0; g < 2; ++g) {
     a[g].init(K, M, (M + 63) / 64 * 64, 1.f, true);
     b[g].init(K, N, (N + 63) / 64 * 64, 1.f);
@@ -234,7 +235,8 @@ static uint32_t* pack_bits(const HostMat& m, long long pitch) {
   return d;
 }
 static long long bits_pitch(int kind, int M, int K) {
-  const long long need = kind == GEMM_WGRAD ? 4LL * ((M + 127) / 128) : 2LL * ((K + 63) / 64);
+  // (+ 1 tile: a CTA pair may run an empty partner tile behind an odd last M tile)
+  const long long need = kind == GEMM_WGRAD ? 4LL * ((M + 127) / 128 + 1) : 2LL * ((K + 63) / 64);
   return (need + 7) / 8 * 8;
 }
 
@@ -276,7 +278,7 @@ static void test_bits_fwd_store(int M, int N, int K, int nseg, int split, int sm
     CK(cudaMalloc(&dout, sizeof(float) * M * ldo));
     CK(cudaMemset(dout, 0, sizeof(float) * M * ldo));
     GemmProblem p;
-    p.kind = GEMM_FWD; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split; p.block_n = 256;
+    p.kind = GEMM_FWD; p.epi = EPI_STORE_F32; p.nseg = nseg; p.M = M; p.N = N; p.K = K; p.force_splitk = split; p.block_n = 256; p.cta_pair = g_pair;
     for (int s = 0; s < nseg; ++s) { p.a[0][s] = a.mat(); p.b[0][s] = b[s].mat(); }
     if (v == 1) { p.a_bits = true; p.abits[0].base = dbits; p.abits[0].pitch = pitch; p.abits[0].rows = M; }
     if (v == 1 && sparse) { p.kmask[0] = dmask; p.kmask_words = mwords; }
@@ -327,7 +329,7 @@ static void test_bits_fwd_act(int M, int Nv, int K, int sms) {
     CK(cudaMalloc(&dout, 2 * M * ldo));
     CK(cudaMemset(dout, 0xFF, 2 * M * ldo));
     GemmProblem p;
-    p.kind = GEMM_FWD; p.epi = EPI_ACT; p.M = M; p.K = K; p.N = (int)ldo; p.force_splitk = 1; p.block_n = 256;
+    p.kind = GEMM_FWD; p.epi = EPI_ACT; p.M = M; p.K = K; p.N = (int)ldo; p.force_splitk = 1; p.block_n = 256; p.cta_pair = g_pair;
     p.a[0][0] = a.mat(); p.b[0][0] = b.mat();
     if (v == 1) { p.a_bits = true; p.abits[0].base = dbits; p.abits[0].pitch = pitch; p.abits[0].rows = M; }
     EpiArgs e = {};
@@ -402,7 +404,7 @@ static void test_bits_wgrad(int M, int N, int Bp, bool extras, int sms, bool spa
     float* dout[2];
     float* xout[2] = {nullptr, nullptr};
     GemmProblem p;
-    p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K; p.block_n = 256;
+    p.kind = GEMM_WGRAD; p.epi = EPI_STORE_F32; p.ngroups = 2; p.nseg = 1; p.M = M; p.N = N; p.K = K; p.block_n = 256; p.cta_pair = g_pair;
     p.force_splitk = 1;
     for (int g = 0; g < 2; ++g) {
       CK(cudaMalloc(&dout[g], sizeof(float) * M * ldo));
@@ -513,7 +515,7 @@ static void test_fused(int epi, int M, int Nv, int K, int split, int precise, in
   CK(cudaMalloc(&ws, sizeof(float) * M * ldo));
   GemmProblem p;
   p.kind = kind; p.epi = epi; p.M = M; p.K = K; p.force_splitk = split;
-  p.cluster_m = g_cluster;
+  p.cluster_m = g_cluster; p.cta_pair = g_pair;
   p.block_n = g_bn;
   p.N = epi == EPI_BCE ? Nv : (int)ldo;
   p.a[0][0] = a.mat(); p.b[0][0] = b.mat();
@@ -583,7 +585,7 @@ static void bench(int kind, int M, int N, int K, int split, int sms, const char*
   CK(cudaMemset(out, 0, sizeof(float) * M * ldo));
   GemmProblem p;
   p.kind = kind; p.epi = epi; p.M = M; p.N = N; p.K = K; p.force_splitk = split;
-  p.cluster_m = g_cluster;
+  p.cluster_m = g_cluster; p.cta_pair = g_pair;
   p.block_n = g_bn;
   p.a[0][0] = kind == GEMM_WGRAD ? Mat(a, K, M, (M + 63) / 64 * 64) : Mat(a, M, K, (K + 63) / 64 * 64);
   p.b[0][0] = kind == GEMM_DGRAD ? Mat(b, N, K, (K + 63) / 64 * 64) : Mat(b, K, N, (N + 63) / 64 * 64);
@@ -692,6 +694,25 @@ int main(int argc, char** argv) {
   std::string err = gemm_init();
   if (!err.empty()) { printf("gemm_init: %s\n", err.c_str()); return 2; }
   const bool do_bench = argc > 1 && std::string(argv[1]) == "bench";
+  const bool pair_only = argc > 1 && std::string(argv[1]) == "pair";    // the CTA-pair checks and their timings only
+  auto pair_bench = [&]() {
+    for (int pr = 0; pr < 2; ++pr) {
+      g_pair = pr != 0;
+      const char* tag = pr ? " [CTA pairs]" : "";
+      char lbl[96];
+      snprintf(lbl, sizeof lbl, "dec out fwd, BCE%s", tag); bench(GEMM_FWD, 4096, 40000, 512, 1, sms, lbl, EPI_BCE);
+      snprintf(lbl, sizeof lbl, "dec out dgrad (auto)%s", tag); bench(GEMM_DGRAD, 4096, 512, 40000, 0, sms, lbl);
+      snprintf(lbl, sizeof lbl, "dec out wgrad%s", tag); bench(GEMM_WGRAD, 512, 40000, 4096, 1, sms, lbl);
+      snprintf(lbl, sizeof lbl, "enc L0 wgrad, bf16 A%s", tag); bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, lbl);
+      snprintf(lbl, sizeof lbl, "square 8192 dgrad%s", tag); bench(GEMM_DGRAD, 8192, 8192, 8192, 1, sms, lbl);
+      g_bits = 1;
+      snprintf(lbl, sizeof lbl, "enc L0 fwd, bits (auto)%s", tag); bench(GEMM_FWD, 12288, 512, 40064, 0, sms, lbl);
+      snprintf(lbl, sizeof lbl, "enc L0 wgrad, bits%s", tag); bench(GEMM_WGRAD, 40064, 512, 8192, 1, sms, lbl);
+      g_bits = 0;
+    }
+    g_pair = false;
+  };
+  if (!pair_only) {
   // plain GEMMs, all three operand layouts, K tails, M/N tails, segments, split-K
   test_store(GEMM_FWD, 128, 256, 64, 1, 1, sms);
   test_store(GEMM_FWD, 128, 256, 256, 1, 1, sms);
@@ -726,6 +747,37 @@ int main(int argc, char** argv) {
     test_fused(EPI_ACT, 2048, 500, 501, 1, 1, sms);
   }
   g_cluster = 1;
+  }
+  // CTA pairs (tcgen05 cta_group::2): every instantiated variant, odd and even numbers of M tiles, split-K, segments, groups,
+  // appended problems, packed A
+  g_pair = true; g_bn = 256;
+  printf("-- CTA pairs\n");
+  test_store(GEMM_DGRAD, 128, 256, 64, 1, 1, sms);
+  test_store(GEMM_DGRAD, 300, 501, 840, 1, 1, sms);
+  test_store(GEMM_DGRAD, 1300, 501, 8400, 3, 4, sms);
+  test_store(GEMM_DGRAD, 4096, 500, 4000, 1, 0, sms);
+  test_store(GEMM_WGRAD, 128, 256, 64, 1, 1, sms);
+  test_store(GEMM_WGRAD, 501, 500, 700, 1, 1, sms);
+  test_store(GEMM_WGRAD, 1500, 1000, 2048, 2, 1, sms);
+  test_store(GEMM_WGRAD, 501, 140, 2048, 2, 0, sms);
+  test_wgrad_groups(1100, 500, 512, sms);
+  test_wgrad_extras(sms);
+  test_fused(EPI_BCE, 300, 1000, 501, 1, 1, sms);
+  test_fused(EPI_BCE, 300, 1000, 501, 1, 0, sms);
+  test_fused(EPI_BCE, 2048, 3000, 501, 1, 0, sms);
+  test_bits_fwd_store(128, 256, 64, 1, 1, sms);
+  test_bits_fwd_store(300, 500, 1601, 2, 1, sms);
+  test_bits_fwd_store(1000, 500, 3000, 2, 3, sms);
+  test_bits_fwd_act(300, 500, 1601, sms);
+  test_bits_wgrad(700, 500, 96, false, sms);
+  test_bits_wgrad(1601, 120, 100, false, sms);
+  test_bits_wgrad(1601, 500, 256, true, sms);
+  g_pair = false; g_bn = 0;
+  if (pair_only) {
+    printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
+    pair_bench();
+    return g_fail ? 1 : 0;
+  }
   // 128-wide tiles (6 pipeline stages, 4 accumulator stages), every kind / epilogue instantiated at that width
   g_bn = 128;
   test_store(GEMM_FWD, 128, 128, 64, 1, 1, sms);
@@ -762,6 +814,7 @@ int main(int argc, char** argv) {
   test_bits_wgrad(1601, 500, 256, true, sms, true);
   printf("%s (%d failures)\n", g_fail ? "SELFTEST FAILED" : "SELFTEST PASSED", g_fail);
   if (do_bench) {
+    pair_bench();
     bench(GEMM_FWD, 12288, 512, 40064, 1, sms, "enc L0 fwd");
     bench(GEMM_FWD, 12288, 512, 40064, 0, sms, "enc L0 fwd (auto split)");
     bench(GEMM_FWD, 4096, 40000, 512, 1, sms, "dec out fwd");
