@@ -331,8 +331,12 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   int cm_b = (b_mn && (p.cluster_m == 2 || p.cluster_m == 4)) ? p.cluster_m : 1;
   while (cm_b > 1 && ((p.M + kBlockM - 1) / kBlockM) % cm_b != 0) cm_b >>= 1;   // every CTA of a cluster gets a real M tile
   // CTA pairs: 256 x 256 tiles, each CTA loads half of the B tile's columns (an odd last M tile is paired with an empty one,
-  // whose loads are clipped to zeros and whose rows the epilogue masks).  MAGIC_CG2=0 keeps the single-CTA kernels.
-  static const bool cg2_enabled = !(getenv("MAGIC_CG2") && atoi(getenv("MAGIC_CG2")) == 0);
+  // whose loads are clipped to zeros and whose rows the epilogue masks).  OPT-IN (MAGIC_CG2=1): the variants are
+  // correct (selftest_gemm pair: every check passes on a B200) but measured about 2x SLOWER than the single-CTA kernels on
+  // every shape of the step (dec-out BCE 0.334 vs 0.236 ms, first-layer wgrad 0.58 vs 0.27 ms, square 8192 651 vs 1448
+  // TFLOP/s; step 3.45 vs 2.31 ms) -- with the MMAs removed the time stays, with the loads removed it drops to the
+  // single-CTA time, i.e. the cta_group::2 loads signalling the leader's barrier are what is slow.  DESIGN.md section 4.
+  static const bool cg2_enabled = getenv("MAGIC_CG2") && atoi(getenv("MAGIC_CG2")) != 0;
   const bool linear = p.epi == EPI_STORE_F32;   // SCATTER_F32 stores plain values to peer memory: never split
   const bool can_split = linear || (p.ws != nullptr && p.ngroups == 1 && (p.epi == EPI_ACT || p.epi == EPI_DACT));
   const int total_kb = (p.K + kBlockK - 1) / kBlockK * p.nseg;

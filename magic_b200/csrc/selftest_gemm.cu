@@ -691,6 +691,7 @@ int main(int argc, char** argv) {
   CK(cudaGetDeviceProperties(&prop, dev));
   printf("device: %s, %d SMs, cc %d.%d\n", prop.name, prop.multiProcessorCount, prop.major, prop.minor);
   const int sms = prop.multiProcessorCount;
+  setenv("MAGIC_CG2", "1", 0);       // the CTA-pair variants are opt-in in the library; the self-test always checks them
   std::string err = gemm_init();
   if (!err.empty()) { printf("gemm_init: %s\n", err.c_str()); return 2; }
   const bool do_bench = argc > 1 && std::string(argv[1]) == "bench";
