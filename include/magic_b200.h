@@ -177,6 +177,16 @@ int magic_decode(magic_handle* h, const float* d_z, float* d_out);
  * Host fp32 in, host fp32 [B] out; runs on the current device, synchronous.  No handle needed. */
 int magic_cosine_distance(const float* h_a, const float* h_b, int32_t B, int32_t L, float* h_out);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  cosine_distance(a, b) as above, but on
+ * DEVICE arrays a, b [B, L] -> out [B] (fp32), enqueued on `stream` (a cudaStream_t, NULL = default stream) without
+ * synchronising, and without allocating anything: no cudaMalloc / cudaFree, no allocating library call.  The kernels'
+ * scratch (2 L floats) is a static device array of 32 KiB that every GPU which loads the library holds until exit.
+ * Limit: L <= MAGIC_COSINE_NOALLOC_MAX_L; a larger L returns an error (use magic_cosine_distance).  All calls on a device
+ * share that scratch: each call clears what it uses first, calls that overlap on the GPU (different streams) race. */
+#define MAGIC_COSINE_NOALLOC_MAX_L 4096
+int magic_cosine_distance_noalloc(const float* d_a, const float* d_b, int32_t B, int32_t L, float* d_out, void* stream);
+
 /* Data parallelism (new; the reference is single-device).  `nccl_unique_id` is the 128-byte ncclUniqueId
  * created on rank 0 and distributed by the host framework.  Afterwards magic_step all-reduces the cosine
  * batch statistics, the two gradients and the loss scalars over NCCL inside the step. */

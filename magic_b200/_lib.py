@@ -67,6 +67,7 @@ SIGNATURES = {
     "magic_export_rotation": (C.c_int, [_VP, _VP]),
     "magic_export_latents": (C.c_int, [_VP, _VP]),
     "magic_cosine_distance": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32, _VP]),
+    "magic_cosine_distance_noalloc": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32, _VP, _VP]),
     "magic_swap_batch": (C.c_int, [_VP]),
     "magic_set_option": (C.c_int, [_VP, C.c_char_p, C.c_int32]),
     "magic_input_density": (C.c_int, [_VP, C.POINTER(C.c_double)]),

@@ -231,6 +231,17 @@ int magic_cosine_distance(const float* h_a, const float* h_b, int32_t B, int32_t
   return 0;
 }
 
+int magic_cosine_distance_noalloc(const float* d_a, const float* d_b, int32_t B, int32_t L, float* d_out, void* stream) {
+  if (!d_a || !d_b || !d_out) return fail("magic_cosine_distance_noalloc: null argument");
+  if (B < 1 || L < 1) return fail("magic_cosine_distance_noalloc: B and L must be >= 1");
+  if (L > magic::kCosineStaticMaxL)
+    return fail("magic_cosine_distance_noalloc: L = " + std::to_string(L) + " exceeds the static scratch (maximum " +
+                std::to_string(magic::kCosineStaticMaxL) + " latent columns); use magic_cosine_distance");
+  const char* err = magic::cosine_distance_rows_static(d_a, d_b, B, L, d_out, static_cast<cudaStream_t>(stream));
+  if (err) return fail(std::string("magic_cosine_distance_noalloc: ") + err);
+  return 0;
+}
+
 int magic_comm_unique_id(void* h_id128) {
   if (!h_id128) return fail("null output");
   return done(magic::nccl_unique_id(h_id128));

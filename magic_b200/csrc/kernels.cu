@@ -226,6 +226,34 @@ void cosine_distance_rows(const float* a, const float* b, int B, int L, float* c
   cosine_rows_kernel<<<(B + 7) / 8, 256, 0, s>>>(a, b, B, L, colsq_ws, out);
 }
 
+// ------------------------------------------------------------------ cosine_distance without any allocation
+// (No counterpart in the reference: added for callers that cannot call cudaMalloc --
+// code under CUDA graph capture, tight serving loops, harnesses that forbid it.)  The same two kernels as
+// cosine_distance_rows(); their 2L floats of scratch (column sums of squares) live in a file-scope device array, 32 KiB
+// that every GPU which loads this library holds until the process exits.  In host code the array's NAME is only a
+// host-side stand-in: the device address is looked up once per device with cudaGetSymbolAddress (that device current)
+// and that pointer is what the kernels receive.  All calls on a device share the array and it keeps the previous call's
+// contents: every call clears the part it uses on its stream first; calls that overlap on the GPU (two streams) race.
+static __device__ __align__(256) float g_cosine_scratch[2 * kCosineStaticMaxL];
+static float* g_cosine_scratch_ptr[64] = {};       // per device ordinal, filled on first use
+const char* cosine_distance_rows_static(const float* a, const float* b, int B, int L, float* out, cudaStream_t s) {
+  if (L < 1 || L > kCosineStaticMaxL) return "L exceeds the static scratch (maximum 4096 latent columns)";
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return "no current CUDA device (ordinal 0..63)";
+  float* ws = g_cosine_scratch_ptr[dev];
+  if (ws == nullptr) {                             // set-up, once per device: the symbol's address ON this device
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_cosine_scratch);
+    if (e != cudaSuccess || p == nullptr) { (void)cudaGetLastError(); return "cudaGetSymbolAddress(scratch) failed"; }
+    ws = g_cosine_scratch_ptr[dev] = static_cast<float*>(p);
+  }
+  if (cudaMemsetAsync(ws, 0, sizeof(float) * 2 * (size_t)L, s) != cudaSuccess) { (void)cudaGetLastError(); return "clearing the scratch failed"; }
+  const int slabs = B < 64 ? 1 : 64;
+  cosine_colsq_kernel<<<dim3((L + 255) / 256, slabs), 256, 0, s>>>(a, b, B, L, ws);
+  cosine_rows_kernel<<<(B + 7) / 8, 256, 0, s>>>(a, b, B, L, ws, out);
+  return cudaGetLastError() == cudaSuccess ? nullptr : "kernel launch failed";
+}
+
 // ------------------------------------------------------------------ latent backward
 // dheads rows: [rot|cost ; lock|cost ; lock|metric ; key|metric], cols [d mu | d log sigma^2].
 // d z / d mu = 1 ;  d z / d lv = 0.5 * sqrt(exp(lv)) * eps = 0.5 * (z - mu).

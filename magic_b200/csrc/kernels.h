@@ -51,6 +51,10 @@ void latent_backward(const LatentArgs& a, cudaStream_t s);    // dheads for the 
 void zero_fill3(float* p0, int n0, float* p1, int n1, float* p2, int n2, cudaStream_t s);   // three float ranges, one launch
 // cosine_distance(a, b) of 8c/vae.py:438-452 on two device arrays [B, L]; colsq_ws: 2L floats of scratch; out[B]
 void cosine_distance_rows(const float* a, const float* b, int B, int L, float* colsq_ws, float* out, cudaStream_t s);
+// The same on a static device array instead of caller-supplied scratch (no allocation anywhere): L <= kCosineStaticMaxL.
+// Returns nullptr on success, else a message.  Calls on one device share the array: overlapping calls race.
+constexpr int kCosineStaticMaxL = 4096;
+const char* cosine_distance_rows_static(const float* a, const float* b, int B, int L, float* out, cudaStream_t s);
 
 struct AdamArgs {
   float* p;                       // fp32 master parameters, flat
