@@ -572,6 +572,38 @@ std::string Engine::build_plans() {
       fuse_wg_ = true;
     }
   }
+  // ---------------- hidden-layer chains (MAGIC_CHAIN=0: every layer its own launch)
+  chain_fwd_.valid = chain_dg_.valid = false;
+  chain_dg_has_head_ = false;
+  {
+    // MAGIC_CHAIN: 0 = every layer its own launch, 1 = forward chain only (default), 2 = forward and dgrad chains.  The
+    // dgrad chain sits where the next batch's generator / dataset feed runs on its own stream: its 230 KB of shared memory
+    // cannot share an SM with one of their CTAs, and the step with a new batch every iteration loses 5 % with it
+    // (measured: 1.838 M pairs/s at level 2, 1.943 M at level 1, 1.940 M at level 0).
+    const char* ch = getenv("MAGIC_CHAIN");
+    const int chain_level = ch ? atoi(ch) : 1;
+    if (!split && chain_level > 0) {
+      std::vector<const GemmPlan*> ls;
+      std::vector<Mat> ws;
+      std::vector<ChainOut> outs;
+      for (int i = 1; i < E; ++i) { ls.push_back(&fwd_enc_[i]); ws.push_back(wmat(i, false)); outs.push_back({H_[i].hi, H_[i].rows, H_[i].ld}); }
+      std::string why = chain_plan(ls, ws, outs, num_sms, &chain_fwd_);
+      if (getenv("MAGIC_VERBOSE")) fprintf(stderr, "[magic] forward chain: %s\n", chain_fwd_.valid ? "on" : why.c_str());
+      ls.clear(); ws.clear(); outs.clear();
+      chain_dg_has_head_ = pl_dg_head_.args.kblocks <= kChainKb && E <= kChainMaxLayers;
+      if (chain_dg_has_head_) { ls.push_back(&pl_dg_head_); ws.push_back(wmat(iHead, false)); outs.push_back({dH_[E - 1].hi, dH_[E - 1].rows, dH_[E - 1].ld}); }
+      for (int i = E - 1; i >= 1; --i) { ls.push_back(&pl_dg_enc_[i]); ws.push_back(wmat(i, false)); outs.push_back({dH_[i - 1].hi, dH_[i - 1].rows, dH_[i - 1].ld}); }
+      why = chain_level >= 2 ? chain_plan(ls, ws, outs, num_sms, &chain_dg_) : std::string("off (MAGIC_CHAIN < 2)");
+      if (chain_level >= 2 && !chain_dg_.valid && chain_dg_has_head_) {         // the heads' dgrad does not fit the chain: try the hidden layers alone
+        chain_dg_has_head_ = false;
+        ls.erase(ls.begin()); ws.erase(ws.begin()); outs.erase(outs.begin());
+        why = chain_plan(ls, ws, outs, num_sms, &chain_dg_);
+      }
+      if (!chain_dg_.valid) chain_dg_has_head_ = false;
+      if (getenv("MAGIC_VERBOSE")) fprintf(stderr, "[magic] dgrad chain: %s%s\n", chain_dg_.valid ? "on" : why.c_str(),
+                                           chain_dg_.valid && chain_dg_has_head_ ? " (with the heads' dgrad)" : "");
+    }
+  }
   stats.gemm_flops_per_step = flops;
   return "";
 }
@@ -911,6 +943,16 @@ std::string Engine::launch(GemmPlan& pl, int* launches, const char* tag) {
   return "";
 }
 
+std::string Engine::launch_chain_plan(ChainPlan& cp, int* launches, const char* tag) {
+  std::string err;
+  prof_begin(tag, cp.flops);
+  const int n = chain_launch(cp, stream, &err);
+  prof_end();
+  if (n < 0) return err;
+  *launches += n;
+  return "";
+}
+
 LatentArgs Engine::latent_args(const float* d_eps3, const float* d_labels) {
   LatentArgs a;
   memset(&a, 0, sizeof a);
@@ -949,9 +991,14 @@ std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) 
   }
   InBuf& ib = in_[cur_];
   wait_ready(ib);
-  for (int i = 0; i <= E; ++i)
+  for (int i = 0; i <= E; ++i) {
+    if (chain_fwd_.valid && i >= 1 && i < E) {            // hidden layers 1 .. E-1: one launch
+      if (i == 1) MAGIC_TRY(launch_chain_plan(chain_fwd_, launches, "gemm.fwd_enc_hidden"));
+      continue;
+    }
     MAGIC_TRY(launch_maybe_dense(i == 0 && cur_ == 1 ? fwd_enc0_alt_ : fwd_enc_[i], launches,
                                  i == 0 ? "gemm.fwd_enc0" : (i == E ? "gemm.fwd_heads" : "gemm.fwd_enc_hidden")));
+  }
   const float* labels = have_labels_ext_ ? labels_ext_ : ib.labels;
   LatentArgs la = latent_args(d_eps3, labels);
   prof_begin("latent.forward"); latent_forward(la, stream); prof_end();
@@ -1010,10 +1057,16 @@ std::string Engine::run_backward(int* launches) {
   prof_begin("latent.backward"); latent_backward(la, stream); prof_end();
   *launches += 1;
   if (!fw) MAGIC_TRY(launch(pl_wg_head_, launches, "gemm.wgrad_small"));
-  MAGIC_TRY(launch(pl_dg_head_, launches, "gemm.dgrad_small"));
-  for (int i = E - 1; i >= 1; --i) {
-    if (!fw) MAGIC_TRY(launch(pl_wg_enc_[i], launches, "gemm.wgrad_small"));
-    MAGIC_TRY(launch(pl_dg_enc_[i], launches, "gemm.dgrad_small"));
+  if (!(chain_dg_.valid && chain_dg_has_head_)) MAGIC_TRY(launch(pl_dg_head_, launches, "gemm.dgrad_small"));
+  if (chain_dg_.valid) {                                    // dgrads through (the heads and) hidden layers E-1 .. 1: one launch
+    MAGIC_TRY(launch_chain_plan(chain_dg_, launches, "gemm.dgrad_small"));
+    if (!fw)
+      for (int i = E - 1; i >= 1; --i) MAGIC_TRY(launch(pl_wg_enc_[i], launches, "gemm.wgrad_small"));
+  } else {
+    for (int i = E - 1; i >= 1; --i) {
+      if (!fw) MAGIC_TRY(launch(pl_wg_enc_[i], launches, "gemm.wgrad_small"));
+      MAGIC_TRY(launch(pl_dg_enc_[i], launches, "gemm.dgrad_small"));
+    }
   }
   if (dp) {   // bucket 1: hidden encoder layers + heads, both optimisers
     MAGIC_CUDA(cudaEventRecord(ev_bwd_[1], stream));

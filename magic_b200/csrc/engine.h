@@ -177,6 +177,11 @@ class Engine {
   GemmPlan pl_wg_out_, pl_dg_out_, pl_wg_h2_, pl_dg_h2_, pl_wg_h1_, pl_dg_h1_;
   GemmPlan pl_wg_head_, pl_dg_head_;
   std::vector<GemmPlan> pl_wg_enc_, pl_dg_enc_;   // index i: wgrad of layer i; dgrad through layer i (i >= 1)
+  // hidden-layer chains (chain_sm100.cuh; bf16 mode, 512-wide hidden layers): one launch instead of fwd_enc_[1 .. E-1] /
+  // instead of the dgrads through the heads (when they are at most 512 deep) and hidden layers E-1 .. 1
+  ChainPlan chain_fwd_, chain_dg_;
+  bool chain_dg_has_head_ = false;
+  std::string launch_chain_plan(ChainPlan& cp, int* launches, const char* tag);
   struct ZeroRange { float* ptr; size_t bytes; };
   std::vector<ZeroRange> zero_;     // gradient windows written with red.add (split-K) -> cleared every step
 

@@ -160,6 +160,8 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<false, true, EPI_STORE_F32, 256, true, true>();
   if (e == cudaSuccess) e = set_smem<false, true, EPI_ACT, 256, true, true>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, true, true>();
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(chain_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChainSmemBytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(chain_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChainSmemBytes);
   if (e != cudaSuccess) return std::string("cudaFuncSetAttribute(smem) failed: ") + cudaGetErrorString(e);
   cudaFuncSetAttribute(gemm_schedule_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   cudaFuncSetAttribute(gemm_klist_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -569,6 +571,62 @@ static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
   long long ncl = pl.items < max_clusters[cm] ? pl.items : max_clusters[cm];
   cfg.gridDim = dim3((unsigned)(ncl * cm));
   cudaLaunchKernelEx(&cfg, kernel, pl.args);
+}
+
+std::string chain_plan(const std::vector<const GemmPlan*>& layers, const std::vector<Mat>& weights,
+                       const std::vector<ChainOut>& outs, int num_sms, ChainPlan* plan) {
+  ChainPlan& cp = *plan;
+  cp.valid = false;
+  memset(&cp.args, 0, sizeof cp.args);
+  const int nl = (int)layers.size();
+  if (nl < 2 || nl > kChainMaxLayers || outs.size() != layers.size() || weights.size() != layers.size()) return "chain: 2..4 layers";
+  const int kind = layers[0]->kind;
+  if (kind != GEMM_FWD && kind != GEMM_DGRAD) return "chain: forward or dgrad layers";
+  cp.dgrad = kind == GEMM_DGRAD;
+  cp.flops = 0;
+  for (int l = 0; l < nl; ++l) {
+    const GemmPlan& pl = *layers[l];
+    const GemmArgs& a = pl.args;
+    // a layer the planner split along K runs a linear store + a finishing pass: its real epilogue is the finishing one
+    const int epi_kind = pl.two_pass ? pl.finish_epi_kind : pl.epi;
+    const EpiArgs& e = pl.two_pass ? pl.finish_epi[0] : a.epi[0];
+    if (pl.kind != kind || epi_kind != (cp.dgrad ? EPI_DACT : EPI_ACT)) return "chain: mixed kinds / epilogues";
+    if (pl.a_bits || pl.cta_pair || a.ngroups != 1 || a.nseg != 1 || a.cluster_m != 1 || a.nextra != 0)
+      return "chain: a layer is grouped, segmented (fp32 mode) or clustered";
+    if (a.N != kChainN || a.kblocks > kChainKb) return "chain: layers must be 512 wide and at most 512 deep";
+    if (a.M != layers[0]->args.M) return "chain: layers differ in M";
+    if (l > 0 && a.kblocks != kChainKb) return "chain: inner layers must read the whole 512-wide slab";
+    if (e.out_lo != nullptr || e.precise) return "chain: bf16 mode only";
+    if (outs[l].ld != kChainN || outs[l].rows < a.M || static_cast<void*>(outs[l].ptr) != e.out) return "chain: output does not match the layer's plan";
+    // weights as the layer's B operand, in 256-column boxes whatever tile width the layer's own plan chose
+    const Mat& W = weights[l];
+    std::string err = cp.dgrad ? make_tmap(&cp.args.tb[l], W.ptr, W.cols, W.rows, W.ld, kBlockK, 256)
+                               : make_tmap_mn(&cp.args.tb[l], W.ptr, W.cols, W.rows, W.ld, kBlockK, 256 / 64);
+    if (!err.empty()) return "chain weights: " + err;
+    cp.args.epi[l] = e;
+    cp.args.kb[l] = a.kblocks;
+    err = make_tmap(&cp.args.tout[l], outs[l].ptr, kChainN, a.M, outs[l].ld, kBlockK, kBlockM);
+    if (!err.empty()) return "chain out: " + err;
+    cp.flops += pl.flops;
+  }
+  cp.args.ta0 = layers[0]->args.ta[0][0];                  // box {64 k, 128 m} at every tile width
+  cp.args.nlayers = nl;
+  cp.args.M = layers[0]->args.M;
+  cp.args.n_slabs = (cp.args.M + kBlockM - 1) / kBlockM;
+  // a handful of slabs would leave most SMs idle for the whole chain: the per-layer launches spread wider then
+  if (cp.args.n_slabs < 16) return "chain: fewer than 16 slabs of 128 rows";
+  cp.grid = cp.args.n_slabs < num_sms ? cp.args.n_slabs : num_sms;
+  cp.valid = true;
+  return "";
+}
+
+int chain_launch(const ChainPlan& cp, cudaStream_t s, std::string* err) {
+  if (!cp.valid) { if (err) *err = "chain_launch: plan not valid"; return -1; }
+  if (cp.dgrad) launch_chain(chain_tcgen05_kernel<true>, dim3(cp.grid), dim3(kChainThreads), kChainSmemBytes, s, cp.args);
+  else launch_chain(chain_tcgen05_kernel<false>, dim3(cp.grid), dim3(kChainThreads), kChainSmemBytes, s, cp.args);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { if (err) *err = std::string("chain launch failed: ") + cudaGetErrorString(e); return -1; }
+  return 1;
 }
 
 int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {

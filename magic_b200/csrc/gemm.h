@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 #include "gemm_sm100.cuh"
+#include "chain_sm100.cuh"
 
 namespace magic {
 
@@ -74,6 +75,22 @@ struct GemmProblem {
   const uint32_t* kmask[kMaxGroups] = {};
   int kmask_words = 0;
 };
+
+// A chain of hidden layers run by ONE launch (chain_sm100.cuh).  Built from the per-layer plans it replaces: their weight
+// tensor maps and epilogue arguments are reused, so the chain computes exactly what launching them one by one would.
+struct ChainPlan {
+  ChainArgs args;
+  bool valid = false, dgrad = false;
+  int grid = 0;
+  double flops = 0;
+};
+struct ChainOut { __nv_bfloat16* ptr; long long rows, ld; };      // output activation of a layer: [rows, ld] bf16
+// `layers` in execution order; `outs[l]` = where layer l writes.  Returns "" and sets plan->valid when the chain kernel
+// applies (every layer: forward + EPI_ACT or dgrad + EPI_DACT, bf16, one group / segment, 512 wide, at most 8 k-blocks;
+// 2..4 layers; at least 16 slabs of 128 rows); returns the reason otherwise (plan->valid = false: launch the layers one by one).
+std::string chain_plan(const std::vector<const GemmPlan*>& layers, const std::vector<Mat>& weights /* each layer's B operand */,
+                       const std::vector<ChainOut>& outs, int num_sms, ChainPlan* plan);
+int chain_launch(const ChainPlan& plan, cudaStream_t stream, std::string* err);
 
 // Returns empty string on success, else an error message.
 std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out);

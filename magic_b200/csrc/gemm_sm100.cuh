@@ -663,11 +663,6 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
   uint64_t* tfull_bar = bars + 2 * kNS;
   uint64_t* tempty_bar = bars + 2 * kNS + kAcc;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kNS + 2 * kAcc);   // (2*6 + 2*4) * 8 + 4 <= 192 bytes
-  // per pipeline stage: 1 = "last k-block of its work item", written by the producer before it arms the stage's
-  // barrier and read by the MMA issuer after that barrier completes -- the issuer needs nothing else to know about the
-  // work list (no item decoding, no zero-stage map walk on the thread whose issue rate paces the tensor pipe)
-  volatile uint32_t* stage_last = reinterpret_cast<volatile uint32_t*>(bars + 24);   // byte 192 .. 216 of the 256
-
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_work = args.tiles_m * args.tiles_n * args.ngroups * args.splitk +
@@ -712,64 +707,81 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
   auto leader_addr = [&](const void* local) { return CG2 ? ptx::mapa_u32(ptx::smem_u32(local), 0u) : ptx::smem_u32(local); };
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (one thread; in a pair: one per CTA)
+    // This thread's per-k-block instruction chain paces the whole pipeline (one warp, dependent scalar code: ~6 cycles per
+    // instruction; ncu r02l: with ~150 instructions per k-block -- a division by kblocks, the list walker, flags -- the
+    // tensor pipe was 58 % busy), so everything that does not change from one k-block to the next is hoisted to the work
+    // item: tensor maps, byte counts, the segment / k offset (stepped, not divided).
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
+      bool first_item = true;
       for (int w = work0; w < total_work; w += work_stride) {
         const WorkItem it = decode_work(args, work_item_at(args, w), crank);
-        KbWalk walk;
-        bool first_kb = true;
-        walk.begin(args, it);
-        while (!walk.done()) {
-          const int kb = walk.kb;
-          walk.step();                                  // one ahead: is this the item's last block?
-          const int seg = kb / it.kblocks;
-          const int k0 = (kb - seg * it.kblocks) * kBlockK;
+        const bool main_p = it.g >= 0;
+        const CUtensorMap* ta0 = main_p ? &args.ta[it.g][0] : &args.xdev[-1 - it.g].ta[0];     // [segment]
+        const CUtensorMap* tb0 = main_p ? &args.tb[it.g][0] : &args.xdev[-1 - it.g].tb[0];
+        const bool a_by_tma = !A_BITS || !main_p;   // A_BITS: the main problem's A stage is written by the expander warps
+        const uint32_t tx = a_by_tma ? Cfg::kBytes : Cfg::kBytesB;
+        const bool no_loads = CG2 && (args.epi[0].dbg & 16) != 0;     // timing experiment (pairs): barriers only
+        // one k-block: wait for the stage, arm its barrier, issue the loads
+        auto issue = [&](const CUtensorMap* ta, const CUtensorMap* tb, int k0) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          const bool a_by_tma = !A_BITS || it.g < 0;   // A_BITS: the main problem's A stage is written by the expander warps
           uint8_t* sa = smem_a + stage * kStageBytesA;
           uint8_t* sb = smem_b + stage * Cfg::kBytesB;
-          const CUtensorMap* ta = it.g >= 0 ? &args.ta[it.g][seg] : &args.xdev[-1 - it.g].ta[seg];
-          const CUtensorMap* tb = it.g >= 0 ? &args.tb[it.g][seg] : &args.xdev[-1 - it.g].tb[seg];
           if constexpr (CG2) {
             // both CTAs' bytes are counted on the leader's barrier: it expects the pair's total, the other CTA only arrives
             const uint32_t fb = leader_addr(&full_bar[stage]);
-            if (leader) {
-              stage_last[stage] = walk.done() ? 1u : 0u;
-              ptx::mbar_expect_tx(&full_bar[stage], 2u * (a_by_tma ? Cfg::kBytes : Cfg::kBytesB));
-            } else {
-              ptx::mbar_arrive_cluster(fb);
+            if (leader) ptx::mbar_expect_tx(&full_bar[stage], no_loads ? 0u : 2u * tx);
+            else ptx::mbar_arrive_cluster(fb);
+            if (!no_loads) {
+              if (a_by_tma) {
+                if constexpr (!A_MN) ptx::tma_load_2d_pair(ta, fb, sa, k0, it.m0);                 // box {64 k, 128 m}
+                else ptx::tma_load_3d_pair(ta, fb, sa, 0, k0, it.m0 >> 6);                         // box {64 m, 64 k, 2 slabs}
+              }
+              const int nh = it.n0 + crank * (BN / 2);                                             // this CTA's half of the B tile
+              if constexpr (!B_MN) ptx::tma_load_2d_pair(tb, fb, sb, k0, nh);                      // box {64 k, BN/2 n}
+              else ptx::tma_load_3d_pair(tb, fb, sb, 0, k0, nh >> 6);                              // box {64 n, 64 k, BN/128 slabs}
             }
+          } else {
+            ptx::mbar_expect_tx(&full_bar[stage], tx);
             if (a_by_tma) {
-              if constexpr (!A_MN) ptx::tma_load_2d_pair(ta, fb, sa, k0, it.m0);                 // box {64 k, 128 m}
-              else ptx::tma_load_3d_pair(ta, fb, sa, 0, k0, it.m0 >> 6);                         // box {64 m, 64 k, 2 slabs}
+              if constexpr (!A_MN) ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);          // box {64 k, 128 m}
+              else ptx::tma_load_3d(ta, &full_bar[stage], sa, 0, k0, it.m0 >> 6);                  // box {64 m, 64 k, 2 slabs}
             }
-            const int nh = it.n0 + crank * (BN / 2);                                             // this CTA's half of the B tile
-            if constexpr (!B_MN) ptx::tma_load_2d_pair(tb, fb, sb, k0, nh);                      // box {64 k, BN/2 n}
-            else ptx::tma_load_3d_pair(tb, fb, sb, 0, k0, nh >> 6);                              // box {64 n, 64 k, BN/128 slabs}
-          } else {
-          stage_last[stage] = walk.done() ? 1u : 0u;
-          ptx::mbar_expect_tx(&full_bar[stage], a_by_tma ? Cfg::kBytes : Cfg::kBytesB);
-          if (a_by_tma) {
-            if constexpr (!A_MN) {
-              ptx::tma_load_2d(ta, &full_bar[stage], sa, k0, it.m0);              // box {64 k, 128 m}
+            if constexpr (!B_MN) {
+              ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);                               // box {64 k, BN n}
+            } else if (CM == 1) {
+              ptx::tma_load_3d(tb, &full_bar[stage], sb, 0, k0, it.n0 >> 6);                       // box {64 n, 64 k, BN/64 slabs}
             } else {
-              ptx::tma_load_3d(ta, &full_bar[stage], sa, 0, k0, it.m0 >> 6);      // box {64 m, 64 k, 2 slabs}
+              // the cluster shares this B tile: each CTA fetches 4/CM slabs and multicasts them to all
+              const int per = (BN / 64) / CM;
+              ptx::tma_load_3d_multicast(tb, &full_bar[stage], sb + crank * per * kAtomBytes, 0, k0,
+                                         (it.n0 >> 6) + crank * per, cmask);
             }
           }
-          if constexpr (!B_MN) {
-            ptx::tma_load_2d(tb, &full_bar[stage], sb, k0, it.n0);              // box {64 k, BN n}
-          } else if (CM == 1) {
-            ptx::tma_load_3d(tb, &full_bar[stage], sb, 0, k0, it.n0 >> 6);      // box {64 n, 64 k, BN/64 slabs}
-          } else {
-            // the cluster shares this B tile: each CTA fetches 4/CM slabs and multicasts them to all
-            const int per = (BN / 64) / CM;
-            ptx::tma_load_3d_multicast(tb, &full_bar[stage], sb + crank * per * kAtomBytes, 0, k0,
-                                       (it.n0 >> 6) + crank * per, cmask);
-          }
-          }
-          if (w == work0 && first_kb) MAGIC_TR(3);
-          first_kb = false;
           if (++stage == kNS) { stage = 0; phase ^= 1; }
+        };
+        if (first_item) MAGIC_TR(3);
+        first_item = false;
+        if (!(main_p && args.klist != nullptr)) {
+          // every k-block of [kb0, kb1): (segment, k offset) stepped along
+          int seg = it.kb0 / it.kblocks;
+          int k0 = (it.kb0 - seg * it.kblocks) * kBlockK;
+          const int kend = it.kblocks * kBlockK;
+          for (int kb = it.kb0; kb < it.kb1; ++kb) {
+            issue(ta0 + seg, tb0 + seg, k0);
+            k0 += kBlockK;
+            if (k0 >= kend) { k0 = 0; ++seg; }
+          }
+        } else {
+          // the item's k-block list (zero-stage skipping)
+          KbWalk walk;
+          walk.begin(args, it);
+          while (!walk.done()) {
+            const int kb = walk.kb;
+            walk.step();
+            const int seg = kb / it.kblocks;
+            issue(ta0 + seg, tb0 + seg, (kb - seg * it.kblocks) * kBlockK);
+          }
         }
       }
       // the other CTA of a pair issues no MMAs: its trigger for the next kernel of the stream comes when its loads are out
@@ -792,33 +804,39 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       const uint32_t a_addr0 = (ptx::smem_u32(smem_a) >> 4) & 0x3FFFu, b_addr0 = (ptx::smem_u32(smem_b) >> 4) & 0x3FFFu;
       const int n_items = work0 < total_work ? (total_work - work0 + work_stride - 1) / work_stride : 0;
       uint32_t stage = 0, phase = 0, iter = 0;
+      // Like the producer, this thread's per-k-block instruction chain paces the pipeline: the loop body is the barrier
+      // wait, two descriptor words, the four MMAs and the commit.  How many k-blocks a work item has is known up front
+      // (its k range, or the length of its list) -- no per-stage flag from the producer.
       for (; (int)iter < n_items; ++iter) {
+        const WorkItem it = decode_work(args, work_item_at(args, work0 + (int)iter * work_stride), crank);
+        int n_kb;                                             // >= 1 (planner, gemm_klist_kernel)
+        if (it.g >= 0 && args.klist != nullptr)
+          n_kb = (int)__ldg(args.klist + ((long long)(it.g * args.tiles_m + it.mt) * args.splitk + it.ks) * args.klist_pitch);
+        else
+          n_kb = (it.kb1 - it.kb0 + it.kstep - 1) / it.kstep;
         const uint32_t acc = iter % kAcc, acc_phase = (iter / kAcc) & 1;
         ptx::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
         if (iter < 8) MAGIC_TR(16 + iter * 5 + 0);
         const uint32_t d_tmem = tmem_base + acc * BN;
-        bool first_kb = true, last_kb;
-        do {                                              // every work item has at least one k-block (planner, KbWalk)
+        for (int i = 0; i < n_kb; ++i) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          last_kb = stage_last[stage] != 0u;
-          if (iter == 0 && first_kb) MAGIC_TR(4);
           const uint32_t a_lo = (a_addr0 + stage * (kStageBytesA >> 4)) | a_lo_c;
           const uint32_t b_lo = (b_addr0 + stage * (Cfg::kBytesB >> 4)) | b_lo_c;
+          const bool no_mma = CG2 && (args.epi[0].dbg & 32) != 0;   // timing experiment (pairs): barriers and loads only
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             const uint64_t da = (static_cast<uint64_t>(desc_hi) << 32) | (a_lo + k * (a_kadv >> 4));
             const uint64_t db = (static_cast<uint64_t>(desc_hi) << 32) | (b_lo + k * (b_kadv >> 4));
-            if constexpr (CG2) ptx::umma_bf16_pair(d_tmem, da, db, idesc, (!first_kb || k > 0) ? 1u : 0u);
-            else ptx::umma_bf16(d_tmem, da, db, idesc, (!first_kb || k > 0) ? 1u : 0u);
+            if constexpr (CG2) { if (!no_mma) ptx::umma_bf16_pair(d_tmem, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u); }
+            else ptx::umma_bf16(d_tmem, da, db, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
           if constexpr (CG2) ptx::umma_commit_pair(&empty_bar[stage], (uint16_t)3);   // frees the stage in both CTAs
           else if (CM > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
           else ptx::umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
           if (++stage == kNS) { stage = 0; phase ^= 1; }
-          first_kb = false;
-        } while (!last_kb);
+        }
         if constexpr (CG2) ptx::umma_commit_pair(&tfull_bar[acc], (uint16_t)3);   // both CTAs' epilogues
         else ptx::umma_commit(&tfull_bar[acc]);   // accumulator complete -> epilogue
         if (iter == 0) MAGIC_TR(5);

@@ -318,3 +318,55 @@ def test_zero_stage_skipping_on_sparse_images_at_full_geometry():
     assert rel_l2(out[0][1], out[1][1]) < tol
     for k in out[0][3]:
         assert rel_l2(out[0][3][k], out[1][3][k]) < tol, k
+
+
+CHAIN_CASES = [
+    # name, engine config, batch, exact
+    ("8d-4096", dict(exp="8d"), 4096, True),              # the benchmark shape: per-layer plans = 256-wide tiles, no split-K
+    ("8e-2048", dict(exp="8e"), 2048, False),             # heads too deep for the chain (K = 4000): hidden layers only
+    ("11a-4096", dict(exp="11a"), 4096, False),           # E = 2, ELU: no forward chain (one hidden layer), dgrad chain of two
+    ("small-D-8192", dict(D=1600, encoder_neurons=(500, 500, 500, 500), decoder_neurons=(500, 500), latent=20), 8192, False),
+]                                                          # 192 / 256 slabs: more than one slab per CTA
+
+
+@pytest.mark.parametrize("name,kw,batch,exact", CHAIN_CASES, ids=[c[0] for c in CHAIN_CASES])
+def test_hidden_layer_chains(name, kw, batch, exact, monkeypatch):
+    """chain_sm100.cuh runs the hidden layers (forward) and their dgrads in one launch each, the activation slab resident
+    in shared memory.  Same MMAs in the same order and the same epilogue arithmetic as the per-layer launches: with
+    MAGIC_CHAIN=0 (every layer its own launch) losses, distances and every gradient must come out the same -- to the
+    last bits of the atomically summed scalars where the per-layer plans are not split along K, to a tenth of the mode's
+    tolerance otherwise.  Level 2 = forward and dgrad chains (the engine's default, level 1, is the forward chain only and
+    is what every other test in this file runs)."""
+    from magic_b200.engine import Engine, EngineConfig
+    runs = []
+    for chain in ("2", "0"):
+        monkeypatch.setenv("MAGIC_CHAIN", chain)
+        kw2 = dict(kw)
+        cfg = EngineConfig.experiment(kw2.pop("exp"), batch=batch, precision="bf16", seed=3) if "exp" in kw2 \
+            else EngineConfig(batch=batch, precision="bf16", seed=3, **kw2)
+        eng = Engine(cfg)
+        eng.generate_batch(5, 1)
+        eps = torch.randn(3, batch, cfg.latent, generator=torch.Generator().manual_seed(1))
+        losses, dist = eng.step(eps3=eps, apply=False, want_distance=True)
+        names = [n for n in eng.param_names if n.startswith("encoder_") and not n.endswith("h0_weights")]
+        grads = {(w, n): eng.get_grad(w, n) for w in (1, 2) for n in names}
+        grads[(1, "encoder_h0_weights")] = eng.get_grad(1, "encoder_h0_weights")
+        runs.append((losses.cpu().numpy().copy(), dist.cpu().numpy().copy(), grads, int(eng.stats().launches_last_step)))
+        eng.close()
+    on, off = runs
+    assert on[3] < off[3], (on[3], off[3])                 # fewer launches with the chains
+    if exact:
+        # same products in the same order inside every GEMM; what differs run to run anyway is the order of the atomic
+        # adds behind the loss scalars, the head-bias sums and the batch-axis statistics (last bits)
+        np.testing.assert_allclose(on[0], off[0], rtol=2e-6)
+        assert rel_l2(on[1], off[1]) < 2e-6
+        for k in on[2]:
+            # bf16 gradients downstream of those sums: a last-bit change upstream flips a few bf16 roundings (measured
+            # 4.5e-5 on optimiser 2's encoder_h1_weights; one flipped bf16 rounding is 4e-3 of that element)
+            assert rel_l2(on[2][k], off[2][k]) < 2e-4, k
+    else:
+        tol = TOL["bf16"] / 10
+        np.testing.assert_allclose(on[0], off[0], rtol=tol)
+        assert rel_l2(on[1], off[1]) < 10 * tol                                  # (distances of reciprocal configs sit behind a pole)
+        for k in on[2]:
+            assert rel_l2(on[2][k], off[2][k]) < (10 * tol if k[0] == 2 else tol), k
