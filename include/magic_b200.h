@@ -142,6 +142,13 @@ int magic_swap_batch(magic_handle* h);
  * images the shapes sit anywhere on the canvas and 94-97 % of the stages hold a set pixel, so the per-batch maps cost more
  * than they save and the option is OFF by default; a data set whose shapes leave most of the canvas empty switches it on.
  *   magic_set_option(h, "skip_zero_stages", 1)  skip empty stages from the next loaded batch on (default 0)
+ *   magic_set_option(h, "fuse_first_layer_adam", 1)  single GPU: run the first layer's two Adam updates (8c/vae.py:314-321,
+ *                                                40 % of all parameters) in the epilogue of its weight-gradient GEMM instead
+ *                                                of the Adam launch: same arithmetic, same result, that gradient is never
+ *                                                written to HBM (magic_get_grad of encoder_h0_* after an APPLIED step then
+ *                                                returns older contents; steps with apply = 0 always store it).  Default 0:
+ *                                                measured no faster on B200; fails on handles that
+ *                                                cannot do it (data parallel, planar first-layer operand)
  *   magic_input_density                          fraction of stages with a set pixel in the loaded batch:
  *                                                out2[0] forward GEMM, out2[1] weight-gradient GEMM (synchronises) */
 int magic_set_option(magic_handle* h, const char* name, int32_t value);

@@ -299,7 +299,7 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_aux_join_, cudaEventDisableTiming));
   if (const char* ea = getenv("MAGIC_EARLY_ADAM")) early_adam_ok_ = atoi(ea) != 0;
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_gate_, cudaEventDisableTiming));
-  if (const char* g = getenv("MAGIC_GEN_GATE")) gen_gate_ = atoi(g) != 0;   // tuning knob, default on
+  if (const char* g = getenv("MAGIC_GEN_GATE")) gen_gate_ = atoi(g);        // tuning knob, default 1
   H_.resize(E);
   dH_.resize(E);
   for (int i = 0; i < E; ++i) {
@@ -570,6 +570,47 @@ std::string Engine::build_plans() {
         flops -= pl_wg_enc0_fused_[v].flops;
       }
       fuse_wg_ = true;
+    }
+  }
+  // ---------------- the first layer's dual Adam inside that launch's epilogue
+  fuse_adam_ok_ = fuse_adam_plans_ok_ = false;
+  {
+    const char* fa = getenv("MAGIC_FUSE_ADAM");
+    if (c.world == 1 && bits_a_ && !(fa && atoi(fa) < 0)) {          // (MAGIC_FUSE_ADAM=-1: do not even build the plans)
+      AdamFuse af;
+      memset(&af, 0, sizeof af);
+      const long long o = lin[0].off;
+      af.p = p_ + o; af.m[0] = m1_ + o; af.v[0] = v1_ + o; af.m[1] = m2_ + o; af.v[1] = v2_ + o;
+      af.w_hi = w_hi_ + o; af.w_lo = w_lo_ ? w_lo_ + o : nullptr;
+      af.ld = lin[0].ld; af.beta1 = c.beta1; af.beta2 = c.beta2; af.eps = c.eps;
+      if (const char* d = getenv("MAGIC_ADAM_DBG")) af.dbg = atoi(d);   // timing experiments only: results are wrong
+      std::string why;
+      for (int v = 0; v < 2 && why.empty(); ++v) {
+        GemmProblem p = enc0_wg[v];
+        if (fuse_wg_)
+          for (auto& sp : small_wg)
+            for (int g = 0; g < sp.ngroups; ++g) {
+              GemmExtra x;
+              for (int sg = 0; sg < sp.nseg; ++sg) { x.a[sg] = sp.a[g][sg]; x.b[sg] = sp.b[g][sg]; }
+              x.e = sp.e[g]; x.M = sp.M; x.N = sp.N; x.K = sp.K;
+              p.extra.push_back(x);
+            }
+        for (auto& k : p.kmask) k = nullptr;             // dense: no k-block lists (the zero-stage option keeps the plain launch)
+        p.kmask_words = 0;
+        why = finish(p, &pl_wg_enc0_adam_[v], "wgrad enc0 + Adam");
+        flops -= pl_wg_enc0_adam_[v].flops;
+        if (why.empty()) why = gemm_fuse_adam(&pl_wg_enc0_adam_[v], af);
+      }
+      fuse_adam_plans_ok_ = why.empty();
+      // OFF unless asked for (MAGIC_FUSE_ADAM=1 or magic_set_option): correct, but no faster.  The main loop of this
+      // launch lives on L2 hits for its B operand and is latency-bound (4 stages in flight); with 1.2 GB of optimiser
+      // state streaming through the same L2 / HBM queues its tensor pipe drops from 77 % to 53 % busy, and the launch
+      // grows by what the separate Adam pass costs (0.47 -> 0.66 ms alone, 0.52 -> 0.82 ms in the step;
+      // profiles/r02q_*).  DESIGN.md section 4, "measured and rejected".
+      fuse_adam_ok_ = fuse_adam_plans_ok_ && fa && atoi(fa) != 0;
+      if (getenv("MAGIC_VERBOSE"))
+        fprintf(stderr, "[magic] first-layer Adam in the wgrad epilogue: %s\n",
+                fuse_adam_ok_ ? ("rows < " + std::to_string(pl_wg_enc0_adam_[0].adam_rows_end)).c_str() : why.c_str());
     }
   }
   // ---------------- hidden-layer chains (MAGIC_CHAIN=0: every layer its own launch)
@@ -851,6 +892,11 @@ void Engine::build_kmasks(InBuf& b, cudaStream_t s, bool force) {
 std::string Engine::set_option(const char* name, int value) {
   if (!name) return "set_option: null name";
   if (std::string(name) == "skip_zero_stages") { skip_zero_ = value != 0; return ""; }
+  if (std::string(name) == "fuse_first_layer_adam") {
+    if (value != 0 && !fuse_adam_plans_ok_) return "set_option: fuse_first_layer_adam is not available for this handle (data parallel, or bf16 planes as the first layer's operand)";
+    fuse_adam_ok_ = value != 0;
+    return "";
+  }
   return std::string("set_option: unknown option ") + name;
 }
 std::string Engine::input_density(double* out2) {
@@ -1013,8 +1059,7 @@ std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) 
     MAGIC_TRY(launch(cur_ == 1 ? pl_out_bce_alt_ : pl_out_bce_, launches, "gemm.fwd_dec_out_bce"));
     // gate for the next batch's generator: let it share the GPU with the backward GEMMs (tensor-bound, HBM half
     // idle) rather than with the HBM-bound Adam pass of the previous step
-    MAGIC_CUDA(cudaEventRecord(ev_gate_, stream));
-    gate_pending_ = true;
+    if (gen_gate_ == 1) { MAGIC_CUDA(cudaEventRecord(ev_gate_, stream)); gate_pending_ = true; }
   } else {
     mark_consumed(ib);
   }
@@ -1091,8 +1136,15 @@ std::string Engine::run_backward(int* launches) {
     prof_end();
     *launches += 2;
   }
-  MAGIC_TRY(launch_maybe_dense(dp_fused_ ? pl_wg_enc0_sc_[cur_] : fw ? pl_wg_enc0_fused_[cur_] : (cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0]),
-                               launches, "gemm.wgrad_enc0"));
+  if (gen_gate_ == 2) { MAGIC_CUDA(cudaEventRecord(ev_gate_, stream)); gate_pending_ = true; }
+  if (fuse_adam_) {
+    GemmPlan& pl = pl_wg_enc0_adam_[cur_];
+    pl.args.adam.lr_t[0] = adam_.lr_t1; pl.args.adam.lr_t[1] = adam_.lr_t2;
+    MAGIC_TRY(launch(pl, launches, "gemm.wgrad_enc0"));
+  } else {
+    MAGIC_TRY(launch_maybe_dense(dp_fused_ ? pl_wg_enc0_sc_[cur_] : fw ? pl_wg_enc0_fused_[cur_] : (cur_ == 1 ? pl_wg_enc0_alt_ : pl_wg_enc_[0]),
+                                 launches, "gemm.wgrad_enc0"));
+  }
   mark_consumed(in_[cur_]);                 // last read of the input buffer in the step
   if (dp) {   // bucket 2: the two 40000-wide first-layer gradients
     MAGIC_CUDA(cudaEventRecord(ev_bwd_[2], stream));
@@ -1123,6 +1175,8 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   // with the small wgrads folded into the last launch only the decoder's output layer (98% of the decoder) is final early
   early_begin_ = fuse_wg_ ? lin[iOut].off : n_both;
   if (early_begin_ % 4) early_adam_ = false;
+  // the first layer's update rides in its wgrad launch (the zero-stage option keeps the plain launch and its lists)
+  fuse_adam_ = apply && cfg.world == 1 && fuse_adam_ok_ && !(skip_zero_ && in_[cur_].kmask_valid);
   std::string err = run_forward(d_eps3, true, &launches);
   if (err.empty()) err = run_backward(&launches);
   have_labels_ext_ = false;
@@ -1154,6 +1208,7 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
     ++t;
     AdamArgs a = adam_;
     if (early_adam_) a.n_total = early_begin_;   // the rest of the decoder range is already in flight on aux_stream_
+    if (fuse_adam_) a.begin = lin[0].off + pl_wg_enc0_adam_[cur_].adam_rows_end * lin[0].ld;   // rows below: done in the wgrad epilogue
     prof_begin("adam.dual");
     adam_dual(a, stream);
     prof_end();

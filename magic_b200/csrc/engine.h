@@ -145,7 +145,8 @@ class Engine {
   std::string launch_maybe_dense(GemmPlan& pl, int* launches, const char* tag);
   cudaStream_t gen_stream_ = nullptr;
   cudaEvent_t ev_gate_ = nullptr;   // recorded after the forward pass: earliest start of the next batch's generator
-  bool gate_pending_ = false, gen_gate_ = true;
+  bool gate_pending_ = false;
+  int gen_gate_ = 1;                // 0 = no gate, 1 = after the forward pass, 2 = after the last dgrad (tuning knob MAGIC_GEN_GATE)
   int* not_binary_ = nullptr;       // device flag raised by the array feeds when a pixel is neither 0 nor 1
   std::string check_binary(const char* who);
   void wait_ready(InBuf& b);
@@ -173,6 +174,10 @@ class Engine {
   GemmPlan pl_d1_, pl_d2_, pl_out_bce_, pl_out_sig_;
   GemmPlan pl_wg_enc0_fused_[2];            // first-layer wgrad + every small layer's wgrad as extra problems (world == 1)
   bool fuse_wg_ = false;
+  // ... and its EPI_ADAM variant: the first layer's dual Adam runs in the wgrad launch's epilogue (gemm_fuse_adam); used
+  // by applied single-GPU steps without zero-stage lists (MAGIC_FUSE_ADAM=0 turns it off)
+  GemmPlan pl_wg_enc0_adam_[2];
+  bool fuse_adam_plans_ok_ = false, fuse_adam_ok_ = false, fuse_adam_ = false;
   GemmPlan fwd_enc0_alt_, pl_out_bce_alt_, pl_wg_enc0_alt_;   // the plans that read the input batch, on in_[1]
   GemmPlan pl_wg_out_, pl_dg_out_, pl_wg_h2_, pl_dg_h2_, pl_wg_h1_, pl_dg_h1_;
   GemmPlan pl_wg_head_, pl_dg_head_;

@@ -153,6 +153,7 @@ std::string gemm_init() {
   if (e == cudaSuccess) e = set_smem<false, true, EPI_ACT, 256, true>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, true>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_SCATTER_F32, 256, true>();
+  if (e == cudaSuccess) e = set_smem<true, true, EPI_ADAM, 256, true>();        // ... or consumed by the fused dual Adam
   // CTA pairs (tcgen05 cta_group::2)
   if (e == cudaSuccess) e = set_smem<false, true, EPI_BCE, 256, false, true>();
   if (e == cudaSuccess) e = set_smem<true, true, EPI_STORE_F32, 256, false, true>();
@@ -533,6 +534,51 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   return "";
 }
 
+std::string gemm_fuse_adam(GemmPlan* plan, const AdamFuse& af) {
+  GemmPlan& pl = *plan;
+  const GemmArgs& a = pl.args;
+  if (pl.kind != GEMM_WGRAD || pl.epi != EPI_STORE_F32 || !pl.a_bits || pl.cta_pair || pl.two_pass)
+    return "fused Adam: needs the packed-operand wgrad kernel with the plain fp32 epilogue";
+  if (a.ngroups != 2 || a.splitk != 1 || a.cluster_m != 1 || a.bn != 256 || a.klist != nullptr)
+    return "fused Adam: needs two groups, whole-K work items, 256-wide tiles and no zero-stage lists";
+  if (a.epi[0].atomic || a.epi[1].atomic) return "fused Adam: the gradient is accumulated (split-K)";
+  if (a.N % 4 != 0 || af.ld % 4 != 0) return "fused Adam: the layer's width must be a multiple of 4";
+  const long long pairs = (long long)a.tiles_m * a.tiles_n, grid = pl.grid;
+  const long long main_items = 2 * pairs;
+  if (pl.items < main_items || grid <= 0) return "fused Adam: inconsistent plan";
+  // Pair rows: the CTAs walk w = cta, cta + grid, ...; rows 2i and 2i + 1 of that walk hold group 0 and group 1 of pair
+  // i * grid + cta.  Only whole rows of pairs are laid out this way: the remaining pairs (fewer than `grid`) would
+  // occupy two more rows with most CTAs idle, so their items follow one by one -- in the wave they share with the
+  // appended problems -- and store their gradient; the caller's Adam launch covers their rows.
+  const long long paired = pairs / grid * grid;
+  const long long mt_fused = paired / a.tiles_n;                        // whole M tiles inside the paired region
+  if (mt_fused <= 0) return "fused Adam: fewer tiles than CTAs";
+  auto item = [&](long long pr, int g) -> int {                         // inverse of decode_work (main problem, splitk 1)
+    const long long mt = pr / a.tiles_n, nt = pr % a.tiles_n;
+    return (int)(a.m_fastest ? ((long long)g * a.tiles_n + nt) * a.tiles_m + mt : ((long long)g * a.tiles_m + mt) * a.tiles_n + nt);
+  };
+  std::vector<int> order((size_t)pl.items);
+  for (long long w = 0; w < 2 * paired; ++w) {
+    const long long row = w / grid, c = w % grid;
+    order[(size_t)w] = item((row >> 1) * grid + c, (int)(row & 1));
+  }
+  long long w = 2 * paired;
+  for (long long pr = paired; pr < pairs; ++pr)
+    for (int g = 0; g < 2; ++g) order[(size_t)w++] = item(pr, g);
+  for (; w < pl.items; ++w) order[(size_t)w] = (int)w;                  // appended problems
+  void* dptr = nullptr;
+  if (cudaMalloc(&dptr, sizeof(int) * order.size()) != cudaSuccess) return "cudaMalloc(fused Adam work order) failed";
+  pl.order = std::shared_ptr<void>(dptr, [](void* q) { cudaFree(q); });
+  if (cudaMemcpy(dptr, order.data(), sizeof(int) * order.size(), cudaMemcpyHostToDevice) != cudaSuccess)
+    return "cudaMemcpy(fused Adam work order) failed";
+  pl.args.order = static_cast<const int*>(dptr);
+  pl.args.adam = af;
+  pl.args.adam.rows_end = (int)(mt_fused * kBlockM);
+  pl.adam_rows_end = mt_fused * kBlockM;
+  pl.adam_fuse = true;
+  return "";
+}
+
 template <bool A_MN, bool B_MN, int EPI, int BN = 256, bool A_BITS = false, bool CG2 = false>
 static void launch_variant(const GemmPlan& pl, cudaStream_t s) {
   const int cm = pl.args.cluster_m;
@@ -634,8 +680,10 @@ int gemm_launch(const GemmPlan& pl, cudaStream_t s, std::string* err) {
   if (pl.two_pass) {
     zero_fill(pl.ws, sizeof(float) * pl.ws_ld * pl.args.M, s);
   }
-  const int key = pl.kind * 8 + pl.epi + (pl.args.bn == 128 ? 64 : 0) + (pl.a_bits ? 128 : 0) + (pl.cta_pair ? 256 : 0);
+  const int key = pl.kind * 8 + (pl.adam_fuse ? (int)EPI_ADAM : pl.epi) + (pl.args.bn == 128 ? 64 : 0) + (pl.a_bits ? 128 : 0) +
+                  (pl.cta_pair ? 256 : 0);
   switch (key) {
+    case 128 + GEMM_WGRAD * 8 + EPI_ADAM: launch_variant<true, true, EPI_ADAM, 256, true>(pl, s); break;
     case 256 + GEMM_FWD * 8 + EPI_BCE: launch_variant<false, true, EPI_BCE, 256, false, true>(pl, s); break;
     case 256 + GEMM_WGRAD * 8 + EPI_STORE_F32: launch_variant<true, true, EPI_STORE_F32, 256, false, true>(pl, s); break;
     case 256 + GEMM_DGRAD * 8 + EPI_STORE_F32: launch_variant<false, false, EPI_STORE_F32, 256, false, true>(pl, s); break;

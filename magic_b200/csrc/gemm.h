@@ -42,6 +42,8 @@ struct GemmPlan {
   std::shared_ptr<void> order;  // plans with a zero-stage map: the work-item permutation args.order points at (int[items])
   std::shared_ptr<void> klist;  // ... their k-block lists (args.klist, uint16[rows][klist_pitch]) followed by the list lengths (int[rows])
   int klist_rows = 0;
+  bool adam_fuse = false;       // the EPI_ADAM kernel variant (gemm_fuse_adam): args.adam is live, args.order pairs the groups
+  long long adam_rows_end = 0;  // rows [0, adam_rows_end) of the output are updated in the epilogue, the rest is stored
 };
 
 // A problem appended to another problem's launch (GemmExtraDev in gemm_sm100.cuh): same kind / epilogue / segment
@@ -98,6 +100,11 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out);
 int gemm_launch(const GemmPlan& plan, cudaStream_t stream, std::string* err);
 // Point group g's epilogue at another output matrix of the same shape and pitch (re-encodes its output tile maps).
 std::string gemm_set_output(GemmPlan* plan, int g, void* out, void* out_lo);
+// Turn a planned first-layer weight-gradient launch (wgrad kind, packed-bit A operand, two groups, EPI_STORE_F32, not
+// split along K, no zero-stage lists) into its EPI_ADAM variant (AdamFuse in gemm_sm100.cuh): builds the work order that
+// hands both groups of a tile to one CTA and sets plan->adam_rows_end.  af.rows_end / lr_t are filled in here / per launch.
+// Returns the reason when the plan does not qualify (the plan is left as it was).
+std::string gemm_fuse_adam(GemmPlan* plan, const AdamFuse& af);
 // Plans with a zero-stage map: rebuild the work-item order from the map's current contents (one small kernel on the
 // stream that just rebuilt the map).  No-op for other plans.
 void gemm_schedule(const GemmPlan& plan, cudaStream_t stream);

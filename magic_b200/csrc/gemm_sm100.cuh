@@ -69,7 +69,8 @@ __host__ __device__ constexpr uint32_t gemm_smem_bytes(int epi) {
   return kGemmSmemBytes + (epi == 5 /*EPI_SCATTER_F32*/ ? 8 * kScatterStageBytes : 1024 + tile_stage_bytes(epi));
 }
 
-enum EpiKind : int { EPI_STORE_F32 = 0, EPI_ACT = 1, EPI_DACT = 2, EPI_BCE = 3, EPI_SIGMOID = 4, EPI_SCATTER_F32 = 5 };
+enum EpiKind : int { EPI_STORE_F32 = 0, EPI_ACT = 1, EPI_DACT = 2, EPI_BCE = 3, EPI_SIGMOID = 4, EPI_SCATTER_F32 = 5,
+                     EPI_ADAM = 6 };   // EPI_ADAM: kernel variant only (planned as EPI_STORE_F32, see AdamFuse)
 constexpr int kMaxPeers = 8;
 enum ActKind : int { ACT_NONE = 0, ACT_TANH = 1, ACT_ELU = 2 };
 
@@ -114,6 +115,26 @@ struct alignas(128) GemmExtraDev {
   CUtensorMap tb[kMaxSegs];
   CUtensorMap tout[2];
   EpiArgs epi;
+};
+
+// EPI_ADAM (single GPU, first layer's wgrad): the weight gradient never leaves the SM.  The main problem has two groups
+// (optimiser 1 = cost, optimiser 2 = metric: 8c/vae.py:314-321) and the work order (GemmArgs.order, built by
+// gemm_fuse_adam) hands both groups of an output tile to the SAME CTA, group 0 first, so the same thread sees the same
+// elements twice:   group 0:  m1, v1 <- ApplyAdam(g1) ; p <- p - d1        group 1:  m2, v2 <- ApplyAdam(g2) ; p <- p - d2 ;
+// bf16 shadow <- p.  Same arithmetic, in the same order, as adam_dual_kernel (kernels.cu) on a stored gradient.  Tiles with
+// m0 >= rows_end (the last, partly filled wave, whose pairs would cost a wave of their own) and the appended problems
+// store their gradient as EPI_STORE_F32 does and are updated by the Adam launch that follows.
+// Opt-in (magic_set_option "fuse_first_layer_adam"): on B200 the optimiser-state traffic slows the latency-bound main
+// loop by as much as the separate Adam pass costs, so nothing is gained (profiles/r02q_*).
+struct AdamFuse {
+  float* p;                  // fp32 master weights of the layer, row pitch ld
+  float* m[2]; float* v[2];  // the two optimisers' moments
+  __nv_bfloat16* w_hi; __nv_bfloat16* w_lo;   // bf16 shadow (lo may be null)
+  long long ld;
+  int rows_end;              // output rows below this are updated in the epilogue (a multiple of 128)
+  float lr_t[2];             // lr * sqrt(1-beta2^t) / (1-beta1^t), set per launch
+  float beta1, beta2, eps;
+  int dbg;                   // timing experiments (MAGIC_ADAM_DBG; results are wrong): 1 = no global accesses, 2 = no arithmetic, 4 = nothing
 };
 
 // The A operand as packed bits (A_BITS kernels): element (r, c) of a row-major {0,1} matrix is bit c & 31 of word
@@ -161,6 +182,7 @@ struct GemmArgs {
   // for the unlucky ones.  order[w] (null = identity) is a permutation of the work items, rebuilt with every map
   // (gemm_schedule): items sorted by their number of set stages and dealt to the CTAs in serpentine order.
   const int* order;
+  AdamFuse adam;        // EPI_ADAM kernels only
 };
 
 struct WorkItem {
@@ -592,6 +614,96 @@ __device__ __forceinline__ void scatter_chunk(const EpiArgs& e, const uint32_t (
   }
 }
 
+// EPI_ADAM: one 32 x 32 chunk of the accumulator (lane = row in `r`), 16 columns at a time.  The half chunk is turned
+// round in the warp's staging slot (written lane = row in the tile stores' 64B swizzle, read back as 8 rows x 4 pieces of
+// 16 bytes) so that every global access of the update is whole 32-byte sectors: four lanes cover the 64 contiguous bytes
+// a row owns in each of m, v, p (and the 32 bytes of the bf16 shadow).  Straight from the accumulator layout every lane
+// would walk its own 128-byte line 16 bytes at a time -- 32 lines per instruction, partial-sector stores: the launch
+// took 1.08 ms in the step that way, 0.82 ms this way, 0.52 ms without the update (why: AdamFuse above).
+__device__ __forceinline__ float adam_fused_one(float g, float& m, float& v, float lr_t, float b1, float b2, float eps) {
+  m = b1 * m + (1.f - b1) * g;                      // (adam_one in kernels.cu, term by term)
+  v = b2 * v + (1.f - b2) * g * g;
+  return lr_t * m / (sqrtf(v) + eps);
+}
+// The update of one staged half chunk (32 rows x 16 columns in `slot`).  Not inlined, arguments by value: inlined into
+// the eight places of the unrolled epilogue loop the IEEE division and square root grow the kernel from 4.7 k to 13.3 k
+// instructions (6.2 k this way) for no gain -- the epilogue is nowhere near its issue limit.
+static __device__ __noinline__ void adam_rows(float* p, float* mg, float* vg, __nv_bfloat16* w_hi, __nv_bfloat16* w_lo,
+                                       long long ld, float lr, float b1, float b2, float eps, float alpha, int last_group,
+                                       const uint8_t* slot, int lane, int row0, int col0, int M, int N, int dbg) {
+  const int c4 = lane & 3, rsub = lane >> 2;
+  const int col = col0 + 4 * c4;
+  if (col >= N) return;                             // N % 4 == 0 (gemm_fuse_adam)
+#pragma unroll 1
+  for (int it = 0; it < 4; it += 2) {
+    float4 gv[2], m4[2], v4[2], p4[2];
+    long long idx[2];
+    bool ok[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int lr_ = (it + h) * 8 + rsub;          // row inside the chunk
+      const int row = row0 + lr_;
+      ok[h] = row < M;
+      idx[h] = (long long)row * ld + col;
+      gv[h] = *reinterpret_cast<const float4*>(slot + lr_ * 64 + ((c4 ^ ((lr_ >> 1) & 3)) << 4));
+      m4[h] = v4[h] = p4[h] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ok[h] && !(dbg & 1)) {
+        // streaming (evict-first) accesses: 0.9 GB of optimiser state passes through the L2 during this launch and
+        // should not push out what the main loop lives on (the B operand, 16 MB re-read by every M tile)
+        m4[h] = __ldcs(reinterpret_cast<const float4*>(mg + idx[h]));
+        v4[h] = __ldcs(reinterpret_cast<const float4*>(vg + idx[h]));
+        p4[h] = __ldcs(reinterpret_cast<const float4*>(p + idx[h]));
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (!ok[h]) continue;
+      if (!(dbg & 2)) {
+        p4[h].x -= adam_fused_one(gv[h].x * alpha, m4[h].x, v4[h].x, lr, b1, b2, eps);
+        p4[h].y -= adam_fused_one(gv[h].y * alpha, m4[h].y, v4[h].y, lr, b1, b2, eps);
+        p4[h].z -= adam_fused_one(gv[h].z * alpha, m4[h].z, v4[h].z, lr, b1, b2, eps);
+        p4[h].w -= adam_fused_one(gv[h].w * alpha, m4[h].w, v4[h].w, lr, b1, b2, eps);
+      }
+      if (dbg & 1) { if (p4[h].x == 123.f) p[idx[h]] = 0.f; continue; }
+      __stcs(reinterpret_cast<float4*>(mg + idx[h]), m4[h]);
+      __stcs(reinterpret_cast<float4*>(vg + idx[h]), v4[h]);
+      __stcs(reinterpret_cast<float4*>(p + idx[h]), p4[h]);
+      if (last_group) {
+        const uint32_t h0 = ptx::pack_bf16(p4[h].x, p4[h].y), h1 = ptx::pack_bf16(p4[h].z, p4[h].w);
+        __stcs(reinterpret_cast<uint2*>(w_hi + idx[h]), make_uint2(h0, h1));
+        if (w_lo) {
+          const uint32_t l0 = ptx::pack_bf16(p4[h].x - ptx::bf16_lo(h0), p4[h].y - ptx::bf16_hi(h0));
+          const uint32_t l1 = ptx::pack_bf16(p4[h].z - ptx::bf16_lo(h1), p4[h].w - ptx::bf16_hi(h1));
+          __stcs(reinterpret_cast<uint2*>(w_lo + idx[h]), make_uint2(l0, l1));
+        }
+      }
+    }
+  }
+}
+template <int OFF>
+__device__ __forceinline__ void adam_half(const AdamFuse& af, int g, float alpha, const uint32_t (&r)[32], uint8_t* slot,
+                                          int lane, int row0, int col0, int M, int N) {
+  if (af.dbg & 4) return;
+  if (lane == 0) ptx::bulk_wait_read();             // a tile store of an earlier (stored) item may still read the slot
+  __syncwarp();
+  {
+    uint8_t* rowp = slot + lane * 64;
+    const int x = (lane >> 1) & 3;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      ptx::st_shared_v4(rowp + ((j ^ x) << 4), r[OFF + 4 * j], r[OFF + 4 * j + 1], r[OFF + 4 * j + 2], r[OFF + 4 * j + 3]);
+  }
+  __syncwarp();
+  adam_rows(af.p, af.m[g], af.v[g], af.w_hi, af.w_lo, af.ld, af.lr_t[g], af.beta1, af.beta2, af.eps, alpha, g == 1, slot,
+            lane, row0, col0, M, N, af.dbg);
+  __syncwarp();                                      // the slot is rewritten by the next half chunk
+}
+__device__ __forceinline__ void adam_chunk(const AdamFuse& af, int g, float alpha, const uint32_t (&r)[32], uint8_t* slot,
+                                           int lane, int row0, int col0, int M, int N) {
+  adam_half<0>(af, g, alpha, r, slot, lane, row0, col0, M, N);
+  adam_half<16>(af, g, alpha, r, slot, lane, row0, col0 + 16, M, N);
+}
+
 // Run-time (act, precise) -> compile-time variant, decided once per 32-column chunk (warp-uniform).
 template <int EPI, bool TILE>
 __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, const TileOut& t, const uint32_t (&r)[32], int row,
@@ -915,6 +1027,9 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
         if constexpr (EPI == EPI_SCATTER_F32) {
           scatter_chunk(e, r, row, it.n0 + c * 32, it.M, it.N,
                         smem + kStages * kStageBytes + 256 + (warp - 2) * kScatterStageBytes, lane);
+        } else if (EPI == EPI_ADAM && it.g >= 0 && it.m0 < args.adam.rows_end) {
+          adam_chunk(args.adam, it.g, e.alpha, r, smem + kTileStageOffset + (warp - 2) * 2048, lane, it.m0 + q * 32,
+                     it.n0 + c * 32, it.M, it.N);
         } else {
           TileOut t;
           t.hi = it.g >= 0 ? &args.tout[it.g][0] : &args.xdev[-1 - it.g].tout[0];
@@ -923,7 +1038,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
           t.lane = lane;
           t.row0 = it.m0 + q * 32;
           t.reduce = e.atomic;
-          epilogue_chunk<EPI, true>(e, t, r, row, it.n0 + c * 32, it.M, it.N, loss_acc, xwk);
+          epilogue_chunk<EPI == EPI_ADAM ? EPI_STORE_F32 : EPI, true>(e, t, r, row, it.n0 + c * 32, it.M, it.N, loss_acc, xwk);
         }
       };
       constexpr int kBatch = epi_warps(EPI) == 16 ? 2 : 1;   // 8-warp epilogues own 4 chunks: one at a time (registers)

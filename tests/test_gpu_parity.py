@@ -370,3 +370,47 @@ def test_hidden_layer_chains(name, kw, batch, exact, monkeypatch):
         assert rel_l2(on[1], off[1]) < 10 * tol                                  # (distances of reciprocal configs sit behind a pole)
         for k in on[2]:
             assert rel_l2(on[2][k], off[2][k]) < (10 * tol if k[0] == 2 else tol), k
+
+
+ADAM_FUSE_CASES = [
+    # name, experiment, batch, precision
+    ("8d-4096-bf16", "8d", 4096, "bf16"),       # the benchmark shape: 592 of 626 tile pairs updated in the epilogue
+    ("8c-300-bf16", "8c", 300, "bf16"),         # ragged batch (K = 600 rows per group)
+    ("8d-1024-fp32", "8d", 1024, "fp32"),       # split-bf16 mode: three precision segments, hi + lo shadow weights
+]
+
+
+@pytest.mark.parametrize("name,exp,batch,precision", ADAM_FUSE_CASES, ids=[c[0] for c in ADAM_FUSE_CASES])
+def test_first_layer_adam_in_the_wgrad_epilogue(name, exp, batch, precision):
+    """Single GPU: the first layer's dual Adam (8c/vae.py:314-321) runs in the epilogue of its weight-gradient GEMM
+    (EPI_ADAM, gemm_sm100.cuh).  Same arithmetic on the same accumulators as storing the gradient and updating in
+    adam_dual_kernel: after four steps on fresh batches (both input buffers, growing bias correction) every parameter and
+    both optimisers' moments must agree with the option off as closely as two runs with the option off agree."""
+    from magic_b200.engine import Engine, EngineConfig
+    runs = []
+    for fuse in (1, 0, 0):
+        eng = Engine(EngineConfig.experiment(exp, batch=batch, precision=precision, seed=9))
+        eng.set_option("fuse_first_layer_adam", fuse)          # raises if the handle could not build the fused plans
+        eps_gen = torch.Generator().manual_seed(4)
+        losses = []
+        for step in range(4):
+            eng.generate_batch(7, step)
+            eps = torch.randn(3, batch, eng.L, generator=eps_gen)
+            losses.append(eng.step(eps3=eps)[0].cpu().numpy().copy())
+        params = {n: eng.get_param(n) for n in eng.param_names}
+        slots = {(w, s): eng.get_slot(w, s, "encoder_h0_weights") for w in (1, 2) for s in (0, 1)}
+        slots[("b", 1, 0)] = eng.get_slot(1, 0, "encoder_b0_biases")
+        runs.append((np.stack(losses), params, slots))
+        eng.close()
+    on, off, off2 = runs
+    # Two runs of ONE setting already differ: the batch-axis statistics are summed with atomics, their last bits move
+    # the gradients' last bits, and Adam's first steps turn a near-zero gradient's sign into +-lr (measured on 8d / 4096:
+    # 1.9e-4 of the first layer's norm after four steps).  The fused path must stay inside that run-to-run band.
+    rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-30)))
+    assert rel(on[0], off[0]) <= max(5.0 * rel(off2[0], off[0]), 1e-4), (rel(on[0], off[0]), rel(off2[0], off[0]))
+    for n in on[1]:
+        floor = rel_l2(off2[1][n], off[1][n])
+        assert rel_l2(on[1][n], off[1][n]) <= max(5.0 * floor, 2e-5), (n, floor)
+    for k in on[2]:
+        floor = rel_l2(off2[2][k], off[2][k])
+        assert rel_l2(on[2][k], off[2][k]) <= max(5.0 * floor, 2e-5), (k, floor)
