@@ -534,7 +534,7 @@ def run_b200(args):
 
         def fed(i):
             b = next(it)
-            fed.out = vae.partial_fit(b, overlap_areas=b.labels)      # returns Python floats: the stream is waited for
+            fed.out = vae.partial_fit(b, overlap_areas=b.labels)      # returns this step's losses as Python floats
         ms_fed = tm.time(fed, Ke, wall=True)
         wpr = ds.lock_bits.shape[1]
         e2e = {"value": B * world * Ke / (ms_fed * 1e-3), "unit": UNIT,
@@ -542,7 +542,9 @@ def run_b200(args):
                "steps": Ke, "ms_per_step": ms_fed / Ke,
                "api": "OverlapDataset(real overlap_micro pairs, sampled with replacement) -> device_batches: per-step host gather "
                       "(index_select into pinned slots) + magic_feed_pairs_bits_host one batch ahead -> TangoEncoder.partial_fit "
-                      "(magic_step; rotated lock made on the device) -> 5 Python floats every step",
+                      "(magic_step; rotated lock made on the device) -> 5 Python floats every step (magic_read_losses: the call returns once "
+                      "the forward pass has produced them, the backward pass and the update overlap the host's next call; the "
+                      "timed region ends with a device synchronize)",
                "data": "real: tests/golden/overlap_micro_100.npz + OVERLAP_AREAS[:100]",
                "input_density": [round(real_density[0], 4), round(real_density[1], 4)]}
         # the reference-signature call: partial_fit(X[B,120000] float32) from pinned host memory (PCIe-bound)

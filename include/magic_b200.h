@@ -164,6 +164,13 @@ int magic_step(magic_handle* h, const float* d_labels, const float* d_eps3, floa
 /* Same, without the Adam update (gradients stay readable through magic_get_grad): parity tests. */
 int magic_step_grads_only(magic_handle* h, const float* d_labels, const float* d_eps3, float* d_losses5,
                           float* d_distance);
+/* The five losses of the last magic_step / magic_step_grads_only that was given a d_losses5, copied to host memory.
+ * partial_fit returns its cost to Python on every call (8c/vae.py:395-405, printed by 8c/main.py:60-63); the losses are
+ * final once the forward pass is, so on one rank this call waits for THAT point of the step only -- the backward pass and
+ * the update keep running while the caller prepares its next step (data parallel: the losses are published after the
+ * step's closing all-reduce, and the call waits for that).  Reading d_losses5 on the step's own stream still works and
+ * waits for the whole step. */
+int magic_read_losses(magic_handle* h, float h_losses5[5]);
 /* Host-buffer form of partial_fit: H2D copies of X/labels/eps, the step, D2H of the results, then a stream
  * synchronise.  h_eps3 and h_distance may be NULL. */
 int magic_partial_fit_host(magic_handle* h, const float* h_x, const float* h_labels, const float* h_eps3,

@@ -72,6 +72,7 @@ SIGNATURES = {
     "magic_set_option": (C.c_int, [_VP, C.c_char_p, C.c_int32]),
     "magic_input_density": (C.c_int, [_VP, C.POINTER(C.c_double)]),
     "magic_step": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    "magic_read_losses": (C.c_int, [_VP, C.POINTER(C.c_float)]),
     "magic_step_grads_only": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "magic_partial_fit_host": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     "magic_forward": (C.c_int, [_VP, _I32, _VP, _VP]),

@@ -191,6 +191,10 @@ int magic_step(magic_handle* h, const float* d_labels, const float* d_eps3, floa
   CHECK_HANDLE(h);
   return done(h->eng.step(d_labels, d_eps3, d_losses5, d_distance, true));
 }
+int magic_read_losses(magic_handle* h, float h_losses5[5]) {
+  CHECK_HANDLE(h);
+  return done(h->eng.read_losses(h_losses5));
+}
 int magic_step_grads_only(magic_handle* h, const float* d_labels, const float* d_eps3, float* d_losses5,
                           float* d_distance) {
   CHECK_HANDLE(h);

@@ -133,6 +133,9 @@ Engine::~Engine() {
   if (gen_stream_) cudaStreamDestroy(gen_stream_);
   if (aux_stream_) { cudaStreamSynchronize(aux_stream_); cudaStreamDestroy(aux_stream_); }
   if (ev_aux_fork_) cudaEventDestroy(ev_aux_fork_);
+  if (read_stream_) { cudaStreamSynchronize(read_stream_); cudaStreamDestroy(read_stream_); }
+  if (ev_losses_) cudaEventDestroy(ev_losses_);
+  if (h_losses_) cudaFreeHost(h_losses_);
   if (ev_aux_join_) cudaEventDestroy(ev_aux_join_);
   if (ev_gate_) cudaEventDestroy(ev_gate_);
   for (auto& b : in_) { if (b.ready) cudaEventDestroy(b.ready); if (b.consumed) cudaEventDestroy(b.consumed); }
@@ -296,6 +299,9 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   MAGIC_CUDA(cudaStreamCreateWithFlags(&gen_stream_, cudaStreamNonBlocking));
   MAGIC_CUDA(cudaStreamCreateWithFlags(&aux_stream_, cudaStreamNonBlocking));
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_aux_fork_, cudaEventDisableTiming));
+  MAGIC_CUDA(cudaStreamCreateWithFlags(&read_stream_, cudaStreamNonBlocking));
+  MAGIC_CUDA(cudaEventCreateWithFlags(&ev_losses_, cudaEventDisableTiming));
+  MAGIC_CUDA(cudaMallocHost((void**)&h_losses_, sizeof(float) * 8));
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_aux_join_, cudaEventDisableTiming));
   if (const char* ea = getenv("MAGIC_EARLY_ADAM")) early_adam_ok_ = atoi(ea) != 0;
   MAGIC_CUDA(cudaEventCreateWithFlags(&ev_gate_, cudaEventDisableTiming));
@@ -899,6 +905,15 @@ std::string Engine::set_option(const char* name, int value) {
   }
   return std::string("set_option: unknown option ") + name;
 }
+std::string Engine::read_losses(float* h_losses5) {
+  if (!h_losses5) return "read_losses: null output";
+  if (!losses_src_) return "read_losses: no step with a loss buffer has been enqueued on this handle";
+  MAGIC_CUDA(cudaStreamWaitEvent(read_stream_, ev_losses_, 0));
+  MAGIC_CUDA(cudaMemcpyAsync(h_losses_, losses_src_, sizeof(float) * 5, cudaMemcpyDeviceToHost, read_stream_));
+  MAGIC_CUDA(cudaStreamSynchronize(read_stream_));
+  memcpy(h_losses5, h_losses_, sizeof(float) * 5);
+  return "";
+}
 std::string Engine::input_density(double* out2) {
   if (!out2) return "input_density: null output";
   out2[0] = out2[1] = 1.0;
@@ -1178,11 +1193,22 @@ std::string Engine::step(const float* d_labels, const float* d_eps3, float* d_lo
   // the first layer's update rides in its wgrad launch (the zero-stage option keeps the plain launch and its lists)
   fuse_adam_ = apply && cfg.world == 1 && fuse_adam_ok_ && !(skip_zero_ && in_[cur_].kmask_valid);
   std::string err = run_forward(d_eps3, true, &launches);
+  // One rank: the loss scalars are complete once the forward pass is (BCE epilogue, latent_forward, latent_metric), so
+  // they are published here and read_losses() need not wait for the backward pass.  Data parallel: after the all-reduce
+  // at the end of the step (which the fused path also uses as its barrier).
+  const bool early_losses = cfg.world == 1 && d_losses5 != nullptr;
+  auto publish_losses = [&]() {
+    launch_chain(finalize_losses_kernel, dim3(1), dim3(32), 0, stream, (const float*)statbuf_, d_losses5);
+    ++launches;
+    cudaEventRecord(ev_losses_, stream);
+    losses_src_ = d_losses5;
+  };
+  if (err.empty() && early_losses) publish_losses();
   if (err.empty()) err = run_backward(&launches);
   have_labels_ext_ = false;
   if (!err.empty()) return err;
   MAGIC_TRY(allreduce(statbuf_, 4, stream));   // loss scalars: local sums / Bg add up to the global means
-  if (d_losses5) { launch_chain(finalize_losses_kernel, dim3(1), dim3(32), 0, stream, (const float*)statbuf_, d_losses5); ++launches; }
+  if (d_losses5 && !early_losses) publish_losses();
   if (d_distance) MAGIC_CUDA(cudaMemcpyAsync(d_distance, dist_, sizeof(float) * B, cudaMemcpyDeviceToDevice, stream));
   if (dp_fused_) {
     // The loss all-reduce above is also the barrier that says: every rank's partial gradients have landed in the

@@ -62,6 +62,7 @@ class Engine {
   std::string forward(int what, const float* d_eps3, float* d_out);
   std::string decode(const float* d_z, float* d_out);
   std::string set_option(const char* name, int value);
+  std::string read_losses(float* h_losses5);
   std::string input_density(double* out2);    // fraction of operand stages with a set pixel: [forward, weight gradient]
   std::string comm_init(const void* uid);
   // Fused data parallelism over peer memory: every rank exports CUDA IPC handles of its gradient
@@ -200,6 +201,13 @@ class Engine {
   cudaEvent_t ev_aux_fork_ = nullptr, ev_aux_join_ = nullptr;
   AdamArgs adam_;
   bool early_adam_ = false, early_adam_ok_ = true;
+  // the step's five losses are final after the forward pass: read_losses() waits for ev_losses_ on its own stream, so a
+  // caller that wants its cost every step does not drain the backward pass and the update with it
+  cudaEvent_t ev_losses_ = nullptr;
+  cudaStream_t read_stream_ = nullptr;
+  float* h_losses_ = nullptr;               // pinned, 5 floats
+  const float* losses_src_ = nullptr;       // device buffer the last step wrote its losses to
+
   long long early_begin_ = 0;               // first parameter of the early (side-stream) Adam range
   cudaEvent_t ev_bwd_[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_comm_ = nullptr;

@@ -328,6 +328,13 @@ class Engine:
         self._keep2 = (lab, eps)
         return self._losses[:5], (self._dist if want_distance else None)
 
+    def read_losses(self) -> np.ndarray:
+        """The last step's five losses as a host array (magic_read_losses): waits for the point of the step where they are
+        final -- the end of the forward pass on one rank -- not for the backward pass and the update behind it."""
+        out = np.empty(5, dtype=np.float32)
+        check(self.lib.magic_read_losses(self._h, out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
     def partial_fit_host(self, X: np.ndarray, labels: np.ndarray, eps3: Optional[np.ndarray] = None,
                          want_distance: bool = False):
         """Host-buffer partial_fit through magic_partial_fit_host (copies + step + sync)."""

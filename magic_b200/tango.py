@@ -168,8 +168,9 @@ class TangoEncoder(object):
         labels = self._labels(overlap_areas)
         self._load(X)
         losses, dist = self.engine.step(labels=labels, eps3=eps, want_distance=self.returns_distance)
-        l = losses.cpu().numpy()
-        out = tuple(float(v) for v in l)
+        # the cost is final after the forward pass: wait for that, not for the rest of the step (8c/main.py reads it every
+        # step; the host then prepares the next call while the backward pass and both Adams are still running)
+        out = tuple(float(v) for v in self.engine.read_losses())
         if self.returns_distance:
             return out + (dist.cpu().numpy(),)
         return out

@@ -132,8 +132,9 @@ def test_experiment_main_modules_have_the_reference_layout():
             assert params[3].default == 5
         oi = importlib.import_module("experiments.%s.overlap_input" % exp)
         assert list(inspect.signature(oi.inputs).parameters) == ["normalize", "reshape", "rotation"]   # 8c/overlap_input.py:76
-        with pytest.raises(RuntimeError):
-            main.images_batch.eval()               # no TangoEncoder yet: the handles evaluate on its engine
+        if main.images_batch.pipeline.model is None:   # (an earlier test of the same process may have built a TangoEncoder)
+            with pytest.raises(RuntimeError):
+                main.images_batch.eval()           # no TangoEncoder yet: the handles evaluate on its engine
 
 
 def test_inputs_requires_a_data_dir():

@@ -207,3 +207,31 @@ def test_checkpoint_roundtrip():
         pa, pb = a.get_params()[n], b.get_params()[n]
         assert np.linalg.norm(pa - pb) <= 1e-6 * np.linalg.norm(pa)
     a.close(); b.close()
+
+
+def test_read_losses_returns_the_step_s_losses_without_draining_the_step():
+    """magic_read_losses (partial_fit's way to its return values, 8c/vae.py:395-405): the five losses of the step just
+    enqueued, equal to what the step wrote to its device buffer -- and available while the backward pass is still in
+    flight (checked through a CUDA event recorded behind the step)."""
+    from magic_b200 import _lib
+    from magic_b200.engine import Engine, EngineConfig
+    eng = Engine(EngineConfig.experiment("8d", batch=2048, precision="bf16", seed=1))
+    with pytest.raises(_lib.MagicError, match="no step"):
+        eng.read_losses()
+    early = 0
+    for step in range(6):
+        eng.generate_batch(3, step)
+        losses_dev, _ = eng.step()
+        done = torch.cuda.Event()
+        done.record()
+        got = eng.read_losses()
+        early += 0 if done.query() else 1                 # the step's tail had not finished when the losses were back
+        want = losses_dev.cpu().numpy()
+        np.testing.assert_array_equal(got, want)
+        assert np.all(np.isfinite(got)) and got[0] > 0
+    assert early >= 3, early                              # (a loaded box may finish a step before the host looks)
+    # steps that do not apply the update publish their losses the same way
+    eng.generate_batch(3, 99)
+    losses_dev, _ = eng.step(apply=False)
+    np.testing.assert_array_equal(eng.read_losses(), losses_dev.cpu().numpy())
+    eng.close()
