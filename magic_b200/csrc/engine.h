@@ -133,7 +133,13 @@ class Engine {
     int* rot = nullptr;             // [B, 2] Q14 (cos, sin) of the generator's lock rotation (tests)
     cudaEvent_t ready = nullptr, consumed = nullptr;
     bool ready_pending = false, consumed_pending = false, has_labels = false, filled = false, has_rot = false;
+    // feed_pairs_bits_host(activate = 0): the packed planes have been copied to bits_stage_ (on gen_stream_), the kernel
+    // that rotates and lays them out is still to be launched -- by the next step, behind its forward pass (flush_expand)
+    bool expand_pending = false;
+    uint64_t exp_seed = 0, exp_step = 0;
+    int exp_wpr = 0;
   };
+  void flush_expand(InBuf& b, bool behind_gate);
   InBuf in_[2];                     // the generator fills in_[cur_ ^ 1] on gen_stream_ while the step reads in_[cur_]
   int cur_ = 0;
   int xb_ld_ = 0;
