@@ -462,7 +462,8 @@ std::string Engine::build_plans() {
 
   // ---------------- backward of `cost` through the decoder
   zero_.clear();
-  std::vector<GemmProblem> small_wg;   // the weight-gradient problems of every layer but the two 40000-wide ones
+  std::vector<GemmProblem>& small_wg = small_wg_;
+  small_wg_.clear(); small_wg_layer_.clear();
   GemmProblem enc0_wg[2];
   auto wgrad1 = [&](GemmPlan* pl, const Act& x, int xcols, const Act& dy, int layer) -> std::string {
     GemmProblem p;
@@ -472,7 +473,7 @@ std::string Engine::build_plans() {
     p.e[0] = f32_epi(g1_ + lin[layer].off, lin[layer].ld, inv_bg);
     p.cta_pair = layer == iOut;
     MAGIC_TRY(finish(p, pl, "wgrad dec"));
-    if (layer != iOut) small_wg.push_back(p);
+    if (layer != iOut) { small_wg.push_back(p); small_wg_layer_.push_back(layer); }
     if (pl->args.splitk > 1) zero_.push_back({g1_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
     return "";
   };
@@ -521,7 +522,7 @@ std::string Engine::build_plans() {
     p.e[1] = f32_epi(g2_ + lin[layer].off, lin[layer].ld, 1.f);
     p.cta_pair = layer == 0;
     MAGIC_TRY(finish(p, pl, "wgrad enc"));
-    if (layer != 0) small_wg.push_back(p);
+    if (layer != 0) { small_wg.push_back(p); small_wg_layer_.push_back(layer); }
     else enc0_wg[pl == &pl_wg_enc0_alt_ ? 1 : 0] = p;
     if (pl->args.splitk > 1) {
       zero_.push_back({g1_ + lin[layer].off, sizeof(float) * (size_t)lin[layer].size()});
@@ -1104,7 +1105,7 @@ std::string Engine::run_forward(const float* d_eps3, bool train, int* launches) 
 }
 
 std::string Engine::run_backward(int* launches) {
-  const bool fw = fuse_wg_;                        // small-layer wgrads folded into the first-layer launch
+  const bool fw = fuse_wg_ || (dp_fused_ && dp_small_fused_);   // small-layer wgrads folded into the first-layer launch
   if (!fw) {
     prof_begin("memset.grad_windows");
     for (auto& z : zero_) zero_fill(z.ptr, z.bytes, stream);
@@ -1163,10 +1164,12 @@ std::string Engine::run_backward(int* launches) {
     memset(&pa, 0, sizeof pa);
     pa.slice_len = slice_len_; pa.rank = cfg.rank; pa.world = cfg.world; pa.gran_shift = kDpGranShift;
     prof_begin("dp.push_small");
-    pa.src = g1_; pa.begin = lin[0].size(); pa.end = lin[iOut].off;
+    // (with the small layers in the scatter launch only the heads' bias rows -- summed by latent_backward -- are local)
+    const long long bias_row = lin[iHead].off + (long long)lin[iHead].Kv * lin[iHead].ld;
+    pa.src = g1_; pa.begin = dp_small_fused_ ? bias_row : lin[0].size(); pa.end = dp_small_fused_ ? bias_row + lin[iHead].ld : lin[iOut].off;
     for (int r = 0; r < cfg.world; ++r) pa.peer[r] = peer_stage_[r];
     push_range(pa, stream);
-    pa.src = g2_; pa.begin = lin[0].size(); pa.end = n_both;
+    pa.src = g2_; pa.begin = dp_small_fused_ ? bias_row : lin[0].size(); pa.end = dp_small_fused_ ? bias_row + lin[iHead].ld : n_both;
     for (int r = 0; r < cfg.world; ++r) pa.peer[r] = peer_stage_[r] + alloc_len_;
     push_range(pa, stream);
     prof_end();
@@ -1425,9 +1428,34 @@ std::string Engine::build_dp_plans() {
       p.abits[1].base = in_[alt].xb3 + (size_t)B * xb_ld_; p.abits[1].pitch = xb_ld_; p.abits[1].rows = 2 * B;
       p.kmask[0] = in_[alt].kmask + km_wg_off_[0]; p.kmask[1] = in_[alt].kmask + km_wg_off_[1]; p.kmask_words = km_wg_words_;
     }
+    // The small layers' weight gradients ride in this launch as appended whole-K problems, each scattering its tiles to
+    // the owners like the main problem (one rank does the same with plain stores: pl_wg_enc0_fused_).  Without this they
+    // are six split-K launches accumulating locally, a window clear before and two push_range launches after them:
+    // 0.17 ms of a 2.29 ms step at 8 GPUs (profiles/r02x_dp_probe_n8.txt).  MAGIC_DP_FUSE_SMALL=0 keeps that path.
+    GemmProblem pf = p;
+    size_t nx = 0;
+    bool want = !(getenv("MAGIC_DP_FUSE_SMALL") && atoi(getenv("MAGIC_DP_FUSE_SMALL")) == 0);
+    for (auto& sp : small_wg_) { nx += sp.ngroups; want = want && sp.nseg == p.nseg; }
+    if (want && nx <= (size_t)kMaxExtra) {
+      for (size_t i = 0; i < small_wg_.size(); ++i) {
+        const GemmProblem& sp = small_wg_[i];
+        for (int g = 0; g < sp.ngroups; ++g) {
+          GemmExtra x;
+          for (int sg = 0; sg < sp.nseg; ++sg) { x.a[sg] = sp.a[g][sg]; x.b[sg] = sp.b[g][sg]; }
+          x.e = scatter_epi(sp.ngroups == 2 ? g + 1 : 1, small_wg_layer_[i], sp.e[g].alpha);
+          x.M = sp.M; x.N = sp.N; x.K = sp.K;
+          pf.extra.push_back(x);
+        }
+      }
+      GemmPlan tmp;
+      if (gemm_plan(pf, num_sms, &tmp).empty()) { pl_wg_enc0_sc_[alt] = tmp; dp_small_fused_ = true; continue; }
+    }
+    if (alt == 1 && dp_small_fused_) return "dp wgrad enc0: the second input buffer's plan does not take the appended problems";
+    dp_small_fused_ = false;
     std::string err = gemm_plan(p, num_sms, &pl_wg_enc0_sc_[alt]);
     if (!err.empty()) return "dp wgrad enc0: " + err;
   }
+  if (getenv("MAGIC_VERBOSE")) fprintf(stderr, "[magic] data parallel: small layers' wgrads %s\n", dp_small_fused_ ? "in the scatter launch" : "on their own");
   return "";
 }
 

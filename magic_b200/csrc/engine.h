@@ -181,6 +181,9 @@ class Engine {
   GemmPlan pl_d1_, pl_d2_, pl_out_bce_, pl_out_sig_;
   GemmPlan pl_wg_enc0_fused_[2];            // first-layer wgrad + every small layer's wgrad as extra problems (world == 1)
   bool fuse_wg_ = false;
+  std::vector<GemmProblem> small_wg_;       // the weight-gradient problems of every layer but the two 40000-wide ones ...
+  std::vector<int> small_wg_layer_;         // ... and the layer each belongs to (build_dp_plans appends them to the scatter launch)
+  bool dp_small_fused_ = false;             // data parallel: they ride in the first layer's scatter launch (no split-K, no push)
   // ... and its EPI_ADAM variant: the first layer's dual Adam runs in the wgrad launch's epilogue (gemm_fuse_adam); used
   // by applied single-GPU steps without zero-stage lists (MAGIC_FUSE_ADAM=0 turns it off)
   GemmPlan pl_wg_enc0_adam_[2];

@@ -438,7 +438,9 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
   a.xdev = nullptr;
   pl.xbuf.reset();
   if (!p.extra.empty()) {
-    if (p.epi != EPI_STORE_F32 || pl.epi != EPI_STORE_F32 || (cm != 1 && !pair)) return "extra problems need EPI_STORE_F32 and no multicast cluster";
+    const bool x_scatter = p.epi == EPI_SCATTER_F32 && pl.epi == EPI_SCATTER_F32;      // every extra scatters like the main problem
+    if (!((p.epi == EPI_STORE_F32 && pl.epi == EPI_STORE_F32) || x_scatter) || (cm != 1 && !pair))
+      return "extra problems need EPI_STORE_F32 or EPI_SCATTER_F32 and no multicast cluster";
     if ((int)p.extra.size() > kMaxExtra) return "too many extra problems";
     std::vector<GemmExtraDev> host(p.extra.size());
     memset(host.data(), 0, sizeof(GemmExtraDev) * host.size());
@@ -469,9 +471,11 @@ std::string gemm_plan(const GemmProblem& p, int num_sms, GemmPlan* out) {
       }
       d.epi = x.e;
       d.epi.atomic = 0;
-      if ((reinterpret_cast<uintptr_t>(x.e.out) & 15) != 0 || (x.e.ld_out * 4) % 16 != 0) return "extra output not 16-byte aligned";
-      std::string err = make_tmap_out(&d.tout[0], x.e.out, true, x.N, x.M, x.e.ld_out);
-      if (!err.empty()) return "extra out: " + err;
+      if (!x_scatter) {
+        if ((reinterpret_cast<uintptr_t>(x.e.out) & 15) != 0 || (x.e.ld_out * 4) % 16 != 0) return "extra output not 16-byte aligned";
+        std::string err = make_tmap_out(&d.tout[0], x.e.out, true, x.N, x.M, x.e.ld_out);
+        if (!err.empty()) return "extra out: " + err;
+      }
       const int tm = ((x.M + kBlockM - 1) / kBlockM + cm - 1) / cm, tn = (x.N + bn - 1) / bn;     // cluster rows
       a.x_item0[i] = item0;
       a.x_m[i] = x.M; a.x_n[i] = x.N; a.x_kb[i] = (x.K + kBlockK - 1) / kBlockK; a.x_tn[i] = tn;
