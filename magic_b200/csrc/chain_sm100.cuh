@@ -100,7 +100,7 @@ __global__ void __maxnreg__(96) chain_tcgen05_kernel(const __grid_constant__ Cha
 
   if (warp == 0) {
     // ------------------------------------------------------------ weight producer: every slab streams every layer again (L2-resident)
-    if (lane == 0) {
+    if (ptx::elect_one()) {                                    // (elect.sync: direct UTMALDG / UTCHMMA, see gemm_sm100.cuh)
       uint32_t stage = 0, phase = 0;
       for (int w = blockIdx.x; w < args.n_slabs; w += gridDim.x)
         for (int l = 0; l < nl; ++l)
@@ -116,7 +116,7 @@ __global__ void __maxnreg__(96) chain_tcgen05_kernel(const __grid_constant__ Cha
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ slab loads, MMAs, output stores (one thread)
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       constexpr uint32_t idesc = ptx::make_idesc_bf16(kBlockM, 256, false, !DGRAD);
       constexpr uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
       constexpr uint32_t b_lbo = DGRAD ? 0u : kAtomBytes;

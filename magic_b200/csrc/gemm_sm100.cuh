@@ -822,8 +822,10 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     // This thread's per-k-block instruction chain paces the whole pipeline (one warp, dependent scalar code: ~6 cycles per
     // instruction; ncu r02l: with ~150 instructions per k-block -- a division by kblocks, the list walker, flags -- the
     // tensor pipe was 58 % busy), so everything that does not change from one k-block to the next is hoisted to the work
-    // item: tensor maps, byte counts, the segment / k offset (stepped, not divided).
-    if (lane == 0) {
+    // item: tensor maps, byte counts, the segment / k offset (stepped, not divided).  The thread is chosen with elect.sync
+    // (ptx::elect_one): inside, ptxas issues UTMALDG / UTCHMMA / UTCBAR directly; under `lane == 0` it wrapped every one of
+    // them in an ELECT ... BRA.U.ANY loop over the active threads (85 -> 45 instructions per k-block in the MMA issuer).
+    if (ptx::elect_one()) {
       uint32_t stage = 0, phase = 0;
       bool first_item = true;
       for (int w = work0; w < total_work; w += work_stride) {
@@ -901,7 +903,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread; in a pair: the leader's)
-    if (lane == 0 && leader) {
+    if (leader && ptx::elect_one()) {
       constexpr uint32_t idesc = ptx::make_idesc_bf16(CG2 ? 2 * kBlockM : kBlockM, BN, A_MN, B_MN);
       // K-major SW128: 8-row groups 1024 B apart, K advance = 32 B inside the swizzle row.
       // MN-major SW128: 64-element MN atoms kBlockK*128 B apart (LBO), 8-k-row groups 1024 B apart (SBO),
