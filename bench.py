@@ -22,8 +22,9 @@ Printed line (rank 0):
             issued_over_algorithmic, precision_modes (the 1e-4 "fp32" mode's throughput), configs (the other
             BASELINE.json configs at this N), dp_parity (N > 1: a small data-parallel step against the CPU oracle).
   e2e       the same metric through the public API with HOST inputs: OverlapDataset (the reference's real image
-            pairs, tests/golden/overlap_micro_100.npz) -> device_batches (per-step host gather into pinned memory,
-            H2D one batch ahead) -> TangoEncoder.partial_fit -> five Python floats per step.
+            pairs, tests/golden/overlap_micro_100.npz) -> device_batches (the packed data set sits in pinned host memory; the
+            rows of each batch cross PCIe one batch ahead, read by the GPU) -> TangoEncoder.partial_fit -> five Python
+            floats per step.
             e2e.float32_feed = partial_fit(X[B,120000] float32) exactly as the reference's main.py feeds it.
 """
 from __future__ import annotations
@@ -514,7 +515,7 @@ def run_b200(args):
         roof["dp_parity"] = dp_parity
 
     # ---- leg 2: end to end through the public API, HOST inputs: the reference's real image pairs (OverlapDataset) ->
-    # device_batches (per-step host gather into pinned slots, H2D one batch ahead) -> TangoEncoder.partial_fit
+    # device_batches (the batch's rows read from the pinned packed data set over PCIe, one batch ahead) -> TangoEncoder.partial_fit
     e2e = None
     if not args.no_e2e:
         from magic_b200.overlap_input import OverlapDataset, device_batches
@@ -538,10 +539,12 @@ def run_b200(args):
         ms_fed = tm.time(fed, Ke, wall=True)
         wpr = ds.lock_bits.shape[1]
         e2e = {"value": B * world * Ke / (ms_fed * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": int(2 * B * wpr * 4 + 2 * B * 4), "d2h_bytes_per_step": 20,
+               "h2d_bytes_per_step": int(2 * B * ((wpr + 3) // 4 * 4) * 4 + 2 * B * 4), "d2h_bytes_per_step": 20,
                "steps": Ke, "ms_per_step": ms_fed / Ke,
-               "api": "OverlapDataset(real overlap_micro pairs, sampled with replacement) -> device_batches: per-step host gather "
-                      "(index_select into pinned slots) + magic_feed_pairs_bits_host one batch ahead -> TangoEncoder.partial_fit "
+               "api": "OverlapDataset(real overlap_micro pairs, sampled with replacement) -> device_batches one batch ahead: rows gathered "
+                      "into a pinned slot by host threads + magic_feed_pairs_bits_host (copy engine) when this rank has >= 6 host "
+                      "threads, else magic_feed_pairs_bits_gather (the GPU reads the rows from the pinned data set over PCIe) "
+                      "-> TangoEncoder.partial_fit "
                       "(magic_step; rotated lock made on the device) -> 5 Python floats every step (magic_read_losses: the call returns once "
                       "the forward pass has produced them, the backward pass and the update overlap the host's next call; the "
                       "timed region ends with a device synchronize)",

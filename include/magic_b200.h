@@ -118,6 +118,16 @@ int magic_load_pairs_bits(magic_handle* h, const uint32_t* d_lock_bits, const ui
  * asynchronous.  With labels given, magic_step(d_labels = NULL) uses them. */
 int magic_feed_pairs_bits_host(magic_handle* h, const uint32_t* h_lock_bits, const uint32_t* h_key_bits, const float* h_labels,
                                int32_t words_per_row, uint64_t seed, uint64_t step, int32_t activate);
+/* The same with the shuffle-batch gather (tf.train.shuffle_batch, 8c/overlap_input.py:297-340) done by the device: the
+ * caller keeps the WHOLE packed data set in pinned host memory -- h_lock_all / h_key_all: [n_rows, words_per_row], row i =
+ * pair i, words_per_row a multiple of 4 -- and names the rows of this batch, h_idx[B] (entries outside [0, n_rows) give
+ * empty images).  A thin kernel on the input stream reads those rows over PCIe straight into the staging area; per step
+ * the host touches 16 KB of indices and labels instead of gathering 10 KB per pair into a pinned slot.  Everything else
+ * (asynchrony, activate, labels, lifetime of the index / label buffers) as magic_feed_pairs_bits_host; the data set
+ * arrays must stay pinned and unchanged while batches are being fed from them. */
+int magic_feed_pairs_bits_gather(magic_handle* h, const uint32_t* h_lock_all, const uint32_t* h_key_all, int32_t words_per_row,
+                                 int64_t n_rows, const int32_t* h_idx, const float* h_labels, uint64_t seed, uint64_t step,
+                                 int32_t activate);
 /* Replaces overlap_input.inputs() (8c/overlap_input.py:76-124): synthesises B shape pairs + rotated lock +
  * max-overlap labels on the device for (seed, step, rank).  Labels go to an internal buffer used when
  * magic_step is given d_labels = NULL. */

@@ -61,6 +61,7 @@ SIGNATURES = {
     "magic_load_planar_u8": (C.c_int, [_VP, _VP, _VP, _VP]),
     "magic_load_pairs_u8": (C.c_int, [_VP, _VP, _VP, C.c_uint64, C.c_uint64]),
     "magic_load_pairs_bits": (C.c_int, [_VP, _VP, _VP, C.c_int32, C.c_uint64, C.c_uint64]),
+    "magic_feed_pairs_bits_gather": (C.c_int, [_VP, _VP, _VP, C.c_int32, C.c_int64, _VP, _VP, C.c_uint64, C.c_uint64, C.c_int32]),
     "magic_feed_pairs_bits_host": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int32, C.c_uint64, C.c_uint64, C.c_int32]),
     "magic_generate_batch": (C.c_int, [_VP, _U64, _U64]),
     "magic_export_batch": (C.c_int, [_VP, _VP, _VP]),

@@ -153,6 +153,12 @@ int magic_load_pairs_bits(magic_handle* h, const uint32_t* d_lock_bits, const ui
   CHECK_HANDLE(h);
   return done(h->eng.load_pairs_bits(d_lock_bits, d_key_bits, words_per_row, seed, step));
 }
+int magic_feed_pairs_bits_gather(magic_handle* h, const uint32_t* h_lock_all, const uint32_t* h_key_all, int32_t words_per_row,
+                                 int64_t n_rows, const int32_t* h_idx, const float* h_labels, uint64_t seed, uint64_t step,
+                                 int32_t activate) {
+  CHECK_HANDLE(h);
+  return done(h->eng.feed_pairs_bits_gather(h_lock_all, h_key_all, words_per_row, n_rows, h_idx, h_labels, seed, step, activate != 0));
+}
 int magic_feed_pairs_bits_host(magic_handle* h, const uint32_t* h_lock_bits, const uint32_t* h_key_bits, const float* h_labels,
                                int32_t words_per_row, uint64_t seed, uint64_t step, int32_t activate) {
   CHECK_HANDLE(h);

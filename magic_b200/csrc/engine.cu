@@ -832,6 +832,56 @@ std::string Engine::feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t*
   if (activate) cur_ ^= 1;
   return "";
 }
+// The same with the GATHER on the device: the caller keeps the whole packed dataset in pinned host memory and passes the
+// rows of this batch as indices; a thin kernel on the input stream pulls the rows over PCIe into the staging area (41 MB per
+// 4096 pairs, the same bytes the copy engine moved before) and the host does no per-step work beyond 16 KB of indices and
+// labels.  With the gather on the host, eight ranks on one 32-core box were bound by their index_select threads (5.2 ms
+// per end-to-end step against 2.3 ms of GPU time, profiles/r02z_bench_n8.json).
+std::string Engine::feed_pairs_bits_gather(const uint32_t* h_lock_all, const uint32_t* h_key_all, int wpr, long long n_rows,
+                                           const int32_t* h_idx, const float* h_labels, uint64_t seed, uint64_t step_idx,
+                                           bool activate) {
+  if (!h_lock_all || !h_key_all || !h_idx) return "feed_pairs_bits_gather: null input";
+  const int side = (int)llround(sqrt((double)D));
+  if (side * side != D || side > 256) return "feed_pairs_bits_gather: D must be a square canvas with side <= 256";
+  if (wpr < (D + 31) / 32 || wpr % 4 != 0) return "feed_pairs_bits_gather: words_per_row must cover D pixels and be a multiple of 4";
+  if (n_rows <= 0) return "feed_pairs_bits_gather: empty dataset";
+  void *d_lock_all = nullptr, *d_key_all = nullptr;
+  if (cudaHostGetDevicePointer(&d_lock_all, const_cast<uint32_t*>(h_lock_all), 0) != cudaSuccess ||
+      cudaHostGetDevicePointer(&d_key_all, const_cast<uint32_t*>(h_key_all), 0) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return "feed_pairs_bits_gather: the dataset arrays must be pinned host memory (cudaHostAlloc / cudaHostRegister / torch pin_memory)";
+  }
+  const size_t plane = sizeof(uint32_t) * (size_t)B * wpr;
+  if (bits_stage_bytes_ < 2 * plane) {
+    MAGIC_CUDA(cudaStreamSynchronize(gen_stream_));
+    if (bits_stage_) cudaFree(bits_stage_);
+    bits_stage_ = nullptr; bits_stage_bytes_ = 0;
+    MAGIC_CUDA(cudaMalloc((void**)&bits_stage_, 2 * plane));
+    bits_stage_bytes_ = 2 * plane;
+  }
+  if (!gather_idx_) MAGIC_TRY(alloc((void**)&gather_idx_, sizeof(int32_t) * B));
+  InBuf& b = in_[cur_ ^ 1];
+  flush_expand(in_[cur_], false);
+  b.expand_pending = false;
+  if (b.ready_pending) { MAGIC_CUDA(cudaStreamWaitEvent(gen_stream_, b.ready, 0)); b.ready_pending = false; }
+  if (b.consumed_pending) { MAGIC_CUDA(cudaStreamWaitEvent(gen_stream_, b.consumed, 0)); b.consumed_pending = false; }
+  MAGIC_CUDA(cudaMemcpyAsync(gather_idx_, h_idx, sizeof(int32_t) * B, cudaMemcpyHostToDevice, gen_stream_));
+  if (h_labels) MAGIC_CUDA(cudaMemcpyAsync(b.labels, h_labels, sizeof(float) * B, cudaMemcpyHostToDevice, gen_stream_));
+  prof_begin("input.gather_rows", 0, gen_stream_);
+  gather_rows_host(static_cast<const uint32_t*>(d_lock_all), static_cast<const uint32_t*>(d_key_all), gather_idx_, B, wpr, n_rows,
+                   bits_stage_, bits_stage_ + (size_t)B * wpr, gen_stream_);
+  prof_end(gen_stream_);
+  b.expand_pending = true;
+  b.exp_seed = seed; b.exp_step = step_idx; b.exp_wpr = wpr;
+  b.planes_valid = !bits_a_;
+  if (activate) flush_expand(b, false);
+  MAGIC_CUDA(cudaGetLastError());
+  b.has_labels = h_labels != nullptr;
+  b.has_rot = true;
+  b.filled = true;
+  if (activate) cur_ ^= 1;
+  return "";
+}
 std::string Engine::generate(uint64_t seed, uint64_t step_idx) {
   const int side = (int)llround(sqrt((double)D));
   if (side * side != D || side % 8 != 0 || side > 256)

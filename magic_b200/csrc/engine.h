@@ -55,6 +55,8 @@ class Engine {
   std::string load_pairs_bits(const uint32_t* d_lock, const uint32_t* d_key, int wpr, uint64_t seed, uint64_t step_idx);
   std::string feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t* h_key, const float* h_labels, int wpr, uint64_t seed,
                                    uint64_t step_idx, bool activate);
+  std::string feed_pairs_bits_gather(const uint32_t* h_lock_all, const uint32_t* h_key_all, int wpr, long long n_rows,
+                                     const int32_t* h_idx, const float* h_labels, uint64_t seed, uint64_t step_idx, bool activate);
   std::string step(const float* d_labels, const float* d_eps3, float* d_losses5, float* d_distance, bool apply);
   std::string load_interleaved_u8(const uint8_t* d_x);
   std::string partial_fit_host(const void* h_x, bool x_is_u8, const float* h_labels, const float* h_eps3,
@@ -172,6 +174,7 @@ class Engine {
   float *g_row_ = nullptr, *dist_ = nullptr, *losses_dev_ = nullptr;
   void* stage_x_ = nullptr; size_t stage_x_bytes_ = 0;                            // partial_fit_host staging
   float *stage_labels_ = nullptr, *stage_eps_ = nullptr;
+  int32_t* gather_idx_ = nullptr;           // [B] dataset row of every pair of the batch being fed (feed_pairs_bits_gather)
   uint32_t* bits_stage_ = nullptr; size_t bits_stage_bytes_ = 0;                     // feed_pairs_bits_host staging
   const float* labels_ext_ = nullptr;
   bool have_labels_ext_ = false;

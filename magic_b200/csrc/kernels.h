@@ -117,6 +117,11 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
 // generator, and `planes` when it is not null
 void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
                 __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, int max_ctas, cudaStream_t s);
+// Gather of dataset rows that live in PINNED HOST memory (mapped into the device's address space): row idx[b] of
+// lock_all / key_all ([n_rows, wpr] words, wpr % 4 == 0) -> row b of out_lock / out_key in HBM.  The GPU reads the rows over
+// PCIe itself; a thin grid (one 128-thread CTA on some of the SMs, <= 32 registers) that fits beside every GEMM CTA.
+void gather_rows_host(const uint32_t* lock_all, const uint32_t* key_all, const int32_t* idx, int B, int wpr, long long n_rows,
+                      uint32_t* out_lock, uint32_t* out_key, cudaStream_t s);
 void pack_planes_bits(const __nv_bfloat16* planes, long long ld, int rows, int D, uint32_t* xb, int xb_ld, cudaStream_t s);
 void unpack_bits_planes(const uint32_t* xb, int xb_ld, int rows, __nv_bfloat16* planes, long long ld, cudaStream_t s);
 

@@ -279,6 +279,29 @@ class Engine:
             C.c_uint64(seed), C.c_uint64(step), C.c_int32(1 if activate else 0)))
         self._keep_feed = (getattr(self, "_keep_feed", ()) + ((arrs, lab),))[-2:]     # the two batches in flight
 
+    def feed_pairs_bits_gather(self, lock_all: torch.Tensor, key_all: torch.Tensor, idx: torch.Tensor, labels, seed: int,
+                               step: int, activate: bool = True) -> None:
+        """Rows `idx` ([B] int32, host) of a packed data set that lives in PINNED host memory ([n, words] int32 tensors,
+        words % 4 == 0) -> packed input rows; the gather runs on the GPU, reading the rows over PCIe
+        (magic_feed_pairs_bits_gather).  idx / labels must not change until the step that consumes them has been waited for."""
+        for x in (lock_all, key_all):
+            if not isinstance(x, torch.Tensor) or x.is_cuda or not x.is_pinned() or x.dim() != 2 or x.element_size() != 4 \
+                    or not x.is_contiguous() or x.shape != lock_all.shape or x.shape[1] < self.words_per_row or x.shape[1] % 4:
+                raise ValueError("the data set must be two pinned, contiguous host tensors [n, >= %d words, a multiple of 4] "
+                                 "of 32-bit words" % self.words_per_row)
+        if idx.is_cuda or idx.dtype != torch.int32 or tuple(idx.shape) != (self.B,) or not idx.is_contiguous():
+            raise ValueError("idx must be a contiguous host int32 [B]")
+        lab = None
+        if labels is not None:
+            lab = labels if isinstance(labels, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(labels, dtype=np.float32))
+            if lab.is_cuda or lab.dtype != torch.float32 or tuple(lab.shape) != (self.B,) or not lab.is_contiguous():
+                raise ValueError("labels must be a contiguous host float32 [B]")
+        check(self.lib.magic_feed_pairs_bits_gather(
+            self._h, C.c_void_p(lock_all.data_ptr()), C.c_void_p(key_all.data_ptr()), C.c_int32(lock_all.shape[1]),
+            C.c_int64(lock_all.shape[0]), C.c_void_p(idx.data_ptr()), C.c_void_p(lab.data_ptr()) if lab is not None else None,
+            C.c_uint64(seed), C.c_uint64(step), C.c_int32(1 if activate else 0)))
+        self._keep_feed = (getattr(self, "_keep_feed", ()) + (((lock_all, key_all, idx), lab),))[-2:]
+
     def generate_batch(self, seed: int, step: int) -> None:
         check(self.lib.magic_generate_batch(self._h, C.c_uint64(seed), C.c_uint64(step)))
 

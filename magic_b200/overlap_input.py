@@ -220,14 +220,19 @@ class OverlapDataset:
 
 
 def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool = True, seed: int = 0,
-                   packed: bool = True, steps: Optional[int] = None):
+                   packed: bool = True, steps: Optional[int] = None, gather: str = "auto"):
     """`overlap_input.inputs(normalize=True, reshape=True, rotation=True)` for the B200 backend: yields handles
     (magic_b200/tango.py: ResidentBatch) whose planes are already in HBM; `batch.labels` are the matching overlap
     areas, so `vae.partial_fit(batch, overlap_areas=batch.labels)` trains on a consistent (images, labels) pair.
 
     packed=True (default): batches travel bit-packed and one step ahead -- while the caller trains on batch n,
     batch n+1 is already crossing PCIe / being unpacked on the engine's input stream (`magic_feed_pairs_bits_host`
-    with activate=0, then `magic_swap_batch`).  packed=False sends uint8 planes with `magic_load_pairs_u8`."""
+    with activate=0, then `magic_swap_batch`).  packed=False sends uint8 planes with `magic_load_pairs_u8`.
+
+    gather: where the rows of a batch are picked out of the data set.  "device" pins the packed data set once and lets the
+    GPU read the rows of each batch over PCIe (`magic_feed_pairs_bits_gather`): per step the host handles 16 KB of indices
+    and labels.  "host" gathers them into a pinned slot on worker threads and copies the slot (copy engine: faster per byte,
+    but the host must keep up).  "auto" = "host" when this rank has at least six host threads to itself, else "device"."""
     import torch
     from .tango import ResidentBatch
     eng = vae.engine
@@ -245,6 +250,32 @@ def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool 
     src = [torch.from_numpy(dataset.lock_bits.view(np.int32)), torch.from_numpy(dataset.key_bits.view(np.int32)),
            torch.from_numpy(dataset.labels)]
     pin = torch.cuda.is_available()
+    if gather not in ("auto", "device", "host"):
+        raise ValueError("gather must be 'auto', 'device' or 'host'")
+    local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1))
+    host_threads = (os.cpu_count() or 8) // local_world - 1              # what this rank can spend on its gather
+    if gather == "auto":
+        # measured on B200 boxes: GPU-side reads of pinned memory reach ~18 GB/s (a 4096-pair batch in 2.3 ms), the copy engine
+        # 50 GB/s -- the host gather wins whenever the host keeps up (7 threads: yes; 3 threads, 8 ranks on 32 cores: 5.2 ms)
+        gather = "host" if host_threads >= 6 else "device"
+    if gather != "host" and pin:
+        pinned = getattr(dataset, "_pinned_bits", None)
+        if pinned is None:
+            try:
+                wpr4 = (wpr + 3) // 4 * 4                     # rows padded to 16 bytes: the gather moves 16-byte pieces
+                pinned = tuple(torch.zeros((len(dataset.labels), wpr4), dtype=torch.int32).pin_memory() for _ in range(2))
+                pinned[0][:, :wpr] = src[0]                   # once per data set (10 KB per pair)
+                pinned[1][:, :wpr] = src[1]
+                dataset._pinned_bits = pinned
+            except RuntimeError:
+                if gather == "device":
+                    raise
+                pinned = None
+        if pinned is not None:
+            yield from _device_gather_batches(vae, dataset, pinned, epochs, shuffle, seed, steps)
+            return
+    elif gather == "device":
+        raise ValueError("gather='device' needs CUDA")
     # three pinned slots: batch n is being trained on, batch n+1 is crossing PCIe / staged on the device, batch n+2 is
     # being gathered from the dataset by a worker thread (index_select releases the GIL) while the caller waits for
     # the losses of step n -- the host gather never sits between two steps
@@ -254,8 +285,7 @@ def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool 
     pool = ThreadPoolExecutor(max_workers=1)
     # The gather itself is split over a few threads of its own: launchers such as torchrun set OMP_NUM_THREADS=1, which
     # makes a single index_select of 41 MB take longer than a training step (measured at 2 GPUs: 4.0 vs 2.7 ms per step).
-    local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1))
-    n_gather = max(1, min(8, (os.cpu_count() or 8) // local_world - 1))
+    n_gather = max(1, min(8, host_threads))
     gpool = ThreadPoolExecutor(max_workers=n_gather) if n_gather > 1 else None
 
     def gather(n, idx):
@@ -307,6 +337,41 @@ def device_batches(vae, dataset: OverlapDataset, epochs: int = 1, shuffle: bool 
         pool.shutdown(wait=True)
         if gpool is not None:
             gpool.shutdown(wait=True)
+
+
+def _device_gather_batches(vae, dataset: OverlapDataset, pinned, epochs, shuffle, seed, steps):
+    """device_batches with the gather on the GPU: one batch ahead, three small pinned slots of (indices, labels)."""
+    import torch
+    from .tango import ResidentBatch
+    eng = vae.engine
+    ring = [(torch.empty((eng.B,), dtype=torch.int32, pin_memory=True), torch.empty((eng.B,), dtype=torch.float32, pin_memory=True))
+            for _ in range(3)]
+    labels_all = dataset.labels
+
+    def feed(n, idx, activate):
+        slot = ring[n % 3]                                    # its previous batch (n - 3) was consumed two steps ago
+        slot[0].numpy()[:] = idx
+        slot[1].numpy()[:] = labels_all[idx]
+        eng.feed_pairs_bits_gather(pinned[0], pinned[1], slot[0], slot[1], seed, n, activate=activate)
+        return slot[1].numpy().copy()
+
+    order = dataset.index_batches(eng.B, epochs=epochs, shuffle=shuffle, seed=seed, steps=steps)
+    idx = next(order, None)
+    if idx is None:
+        return
+    labels = feed(0, idx, True)
+    n = 0
+    while True:
+        idx = next(order, None)
+        staged = feed(n + 1, idx, False) if idx is not None else None
+        batch = ResidentBatch(vae, labels)
+        yield batch
+        if staged is None:
+            return
+        if vae._loaded_key is not batch._token:
+            raise RuntimeError("another load replaced the engine's input buffers while iterating the dataset")
+        eng.swap_batch()
+        labels, n = staged, n + 1
 
 
 # ------------------------------------------------------------------ `overlap_input.inputs()` for the B200 backend

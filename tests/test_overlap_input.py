@@ -221,19 +221,29 @@ def test_packed_feed_equals_the_uint8_loader_and_pipelines_one_batch_ahead():
     assert np.array_equal(Xo.reshape(2, 40000, 3)[:, :, 0].astype(np.uint8), ds.lock[other])
     assert np.isfinite(out_a).all()
     # 3. the iterator: 2 epochs x 2 batches, each batch pairs images with their own labels, one batch staged ahead
-    seen = []
-    for batch in oi.device_batches(vae, ds, epochs=2, shuffle=True, seed=4):
-        X, _, y = loaded()
-        assert np.array_equal(y, batch.labels)
-        lock = X.reshape(2, 40000, 3)[:, :, 0].astype(np.uint8)
-        for r in range(2):
-            i = int(np.flatnonzero((ds.lock == lock[r]).all(1))[0])
-            assert ds.labels[i] == batch.labels[r]
-            assert np.array_equal(X.reshape(2, 40000, 3)[r, :, 2].astype(np.uint8), ds.key[i])
-            seen.append(i)
-        out = vae.partial_fit(batch, overlap_areas=batch.labels)
-        assert np.isfinite(out[0])
-    assert sorted(seen[:4]) == [0, 1, 2, 3] == sorted(seen[4:])
+    #    -- with the rows of a batch gathered by the GPU from the pinned data set (the default) and by the host
+    per_mode = {}
+    for mode in ("device", "host"):
+        seen, rots = [], []
+        for batch in oi.device_batches(vae, ds, epochs=2, shuffle=True, seed=4, gather=mode):
+            X, R, y = loaded()
+            assert np.array_equal(y, batch.labels)
+            lock = X.reshape(2, 40000, 3)[:, :, 0].astype(np.uint8)
+            for r in range(2):
+                i = int(np.flatnonzero((ds.lock == lock[r]).all(1))[0])
+                assert ds.labels[i] == batch.labels[r]
+                assert np.array_equal(X.reshape(2, 40000, 3)[r, :, 2].astype(np.uint8), ds.key[i])
+                seen.append(i)
+            rots.append(R.copy())
+            out = vae.partial_fit(batch, overlap_areas=batch.labels)
+            assert np.isfinite(out[0])
+        assert sorted(seen[:4]) == [0, 1, 2, 3] == sorted(seen[4:])
+        per_mode[mode] = (seen, np.stack(rots))
+    assert per_mode["device"][0] == per_mode["host"][0]                            # same order, same rotations
+    assert np.array_equal(per_mode["device"][1], per_mode["host"][1])
+    with pytest.raises(Exception, match="pinned"):                                 # the device gather reads pinned memory only
+        eng.feed_pairs_bits_gather(torch.zeros((4, 1252), dtype=torch.int32), torch.zeros((4, 1252), dtype=torch.int32),
+                                   torch.zeros(2, dtype=torch.int32), None, 0, 0)
     # a foreign load between two batches is reported, not silently trained on
     it = oi.device_batches(vae, ds, epochs=2, shuffle=False)
     next(it)
