@@ -439,7 +439,10 @@ struct TileOut {
 template <int OFF>
 __device__ __forceinline__ void tile_emit_64(const TileOut& t, const CUtensorMap* map, const uint32_t* v, int col0,
                                              bool reduce) {
-  if (t.lane == 0) ptx::bulk_wait_read();   // earlier tile stores of this warp have finished reading the slot
+  // (the issuing lane is chosen by elect.sync -- the same lane every time for a full warp -- so that ptxas emits the
+  //  UTMASTG / UTMAREDG directly, see ptx::elect_one; bulk groups belong to that thread)
+  const bool issuer = ptx::elect_one();
+  if (issuer) ptx::bulk_wait_read();        // earlier tile stores of this warp have finished reading the slot
   __syncwarp();
   uint8_t* rowp = t.slot + t.lane * 64;
   const int x = (t.lane >> 1) & 3;
@@ -448,7 +451,7 @@ __device__ __forceinline__ void tile_emit_64(const TileOut& t, const CUtensorMap
     ptx::st_shared_v4(rowp + ((j ^ x) << 4), v[OFF + 4 * j], v[OFF + 4 * j + 1], v[OFF + 4 * j + 2], v[OFF + 4 * j + 3]);
   ptx::fence_proxy_async_smem();
   __syncwarp();
-  if (t.lane == 0) {
+  if (issuer) {
     if (reduce) ptx::tma_reduce_add_2d(map, t.slot, col0, t.row0);
     else ptx::tma_store_2d(map, t.slot, col0, t.row0);
     ptx::bulk_commit();
@@ -684,7 +687,7 @@ template <int OFF>
 __device__ __forceinline__ void adam_half(const AdamFuse& af, int g, float alpha, const uint32_t (&r)[32], uint8_t* slot,
                                           int lane, int row0, int col0, int M, int N) {
   if (af.dbg & 4) return;
-  if (lane == 0) ptx::bulk_wait_read();             // a tile store of an earlier (stored) item may still read the slot
+  if (ptx::elect_one()) ptx::bulk_wait_read();      // a tile store of an earlier (stored) item may still read the slot (same lane: tile_emit_64)
   __syncwarp();
   {
     uint8_t* rowp = slot + lane * 64;
