@@ -255,7 +255,8 @@ std::string Engine::init(const magic_config& c, cudaStream_t s) {
   MAGIC_TRY(alloc((void**)&w_hi_, sizeof(bf16) * alloc_len_));
   if (split) MAGIC_TRY(alloc((void**)&w_lo_, sizeof(bf16) * alloc_len_));
   if (c.world > 1) {
-    MAGIC_TRY(alloc((void**)&stage_, sizeof(float) * 2 * alloc_len_));
+    xchg_off_ = (size_t)2 * alloc_len_;
+    MAGIC_TRY(alloc((void**)&stage_, sizeof(float) * (2 * alloc_len_ + xchg_area_floats(c.world))));
     MAGIC_TRY(alloc((void**)&barrier_buf_, sizeof(float) * 8));
   }
   for (size_t vi = 0; vi < views.size(); ++vi) {
@@ -1110,6 +1111,14 @@ LatentArgs Engine::latent_args(const float* d_eps3, const float* d_labels) {
 std::string Engine::allreduce(float* buf, size_t n, cudaStream_t s) {
   if (cfg.world == 1) return "";
   if (!comm_) return "world > 1 but magic_comm_init was not called";
+  if (xchg_ok_ && n <= (size_t)kXchgMaxFloats) {       // the step's small exchanges: over peer memory (kernels.h)
+    XchgArgs a;
+    memset(&a, 0, sizeof a);
+    for (int r = 0; r < cfg.world; ++r) a.peer[r] = peer_stage_[r] + xchg_off_;
+    a.buf = buf; a.n = (int)n; a.world = cfg.world; a.rank = cfg.rank; a.epoch = ++xchg_epoch_;
+    peer_allreduce_small(a, s);
+    return "";
+  }
   const int r = g_nccl.allreduce(buf, buf, n, /*ncclFloat32*/ 7, /*ncclSum*/ 0, comm_, s);
   if (r != 0) return std::string("ncclAllReduce: ") + (g_nccl.errstr ? g_nccl.errstr(r) : "error");
   return "";
@@ -1435,6 +1444,8 @@ std::string Engine::comm_import_peers(const void* h_blobs) {
   }
   MAGIC_TRY(build_dp_plans());
   dp_fused_ = true;
+  // every rank reaches this point with the same sequence of calls behind it, so the epochs agree from here on
+  { const char* x = getenv("MAGIC_DP_XCHG"); xchg_ok_ = !(x && atoi(x) == 0); }
   return "";
 }
 
@@ -1478,13 +1489,15 @@ std::string Engine::build_dp_plans() {
       p.abits[1].base = in_[alt].xb3 + (size_t)B * xb_ld_; p.abits[1].pitch = xb_ld_; p.abits[1].rows = 2 * B;
       p.kmask[0] = in_[alt].kmask + km_wg_off_[0]; p.kmask[1] = in_[alt].kmask + km_wg_off_[1]; p.kmask_words = km_wg_words_;
     }
-    // The small layers' weight gradients ride in this launch as appended whole-K problems, each scattering its tiles to
-    // the owners like the main problem (one rank does the same with plain stores: pl_wg_enc0_fused_).  Without this they
-    // are six split-K launches accumulating locally, a window clear before and two push_range launches after them:
-    // 0.17 ms of a 2.29 ms step at 8 GPUs (profiles/r02x_dp_probe_n8.txt).  MAGIC_DP_FUSE_SMALL=0 keeps that path.
+    // MAGIC_DP_FUSE_SMALL=1: the small layers' weight gradients ride in this launch as appended whole-K problems, each
+    // scattering its tiles to the owners like the main problem (one rank does the same with plain stores:
+    // pl_wg_enc0_fused_), instead of six split-K launches accumulating locally, a window clear before and two push_range
+    // launches after them (0.15 ms of the step).  Correct (tests/test_dp_gpu.py passes with it) but OFF: with the scatter
+    // epilogue the appended items cost the launch 0.20 ms (0.524 -> 0.728 ms at 2 GPUs, step 2.19 -> 2.25 ms,
+    // profiles/r03k_dp_probe_n2.txt) where the plain-store launch absorbs them in its last wave; not yet understood.
     GemmProblem pf = p;
     size_t nx = 0;
-    bool want = !(getenv("MAGIC_DP_FUSE_SMALL") && atoi(getenv("MAGIC_DP_FUSE_SMALL")) == 0);
+    bool want = getenv("MAGIC_DP_FUSE_SMALL") && atoi(getenv("MAGIC_DP_FUSE_SMALL")) != 0;
     for (auto& sp : small_wg_) { nx += sp.ngroups; want = want && sp.nseg == p.nseg; }
     if (want && nx <= (size_t)kMaxExtra) {
       for (size_t i = 0; i < small_wg_.size(); ++i) {

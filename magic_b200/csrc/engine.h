@@ -234,6 +234,9 @@ class Engine {
   long long alloc_len_ = 0;         // world * slice_len (>= n_total): size of the parameter-shaped buffers
   float* stage_ = nullptr;          // [2][world][slice_len]: partial g1 / g2 of the owned slice from every rank
   float* peer_stage_[kMaxRanks] = {};
+  size_t xchg_off_ = 0;             // floats: the exchange area of peer_allreduce_small sits behind the two staging halves
+  unsigned xchg_epoch_ = 0;
+  bool xchg_ok_ = false;            // fused path set up and MAGIC_DP_XCHG != 0: small all-reduces go over peer memory, not NCCL
   bf16* peer_whi_[kMaxRanks] = {};
   bf16* peer_wlo_[kMaxRanks] = {};
   float* barrier_buf_ = nullptr;

@@ -399,6 +399,45 @@ static long long adam_blocks(const AdamArgs& a) {
   if (a.thin > 0 && blocks > a.thin) blocks = a.thin;
   return blocks;
 }
+// ------------------------------------------------------------------ small all-reduce over peer memory
+__global__ void __launch_bounds__(256) peer_allreduce_small_kernel(XchgArgs a) {
+  ptx::grid_dep_wait();
+  const int par = (int)(a.epoch & 1u);
+  const size_t slot = ((size_t)par * a.world + a.rank) * kXchgMaxFloats;
+  for (int i = threadIdx.x; i < a.n; i += blockDim.x) {
+    const float v = a.buf[i];
+    for (int r = 0; r < a.world; ++r) a.peer[r][slot + i] = v;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if ((int)threadIdx.x < a.world) {
+    unsigned* flag = reinterpret_cast<unsigned*>(a.peer[threadIdx.x] + (size_t)2 * a.world * kXchgMaxFloats) + par * 8 + a.rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(a.epoch) : "memory");
+    // ... and wait for rank threadIdx.x's flag in the own area
+    const unsigned* mine = reinterpret_cast<const unsigned*>(a.peer[a.rank] + (size_t)2 * a.world * kXchgMaxFloats) + par * 8 + threadIdx.x;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+      unsigned v;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+      if (v == a.epoch) break;
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > kXchgTimeoutNs) __trap();              // a peer is gone: fail the context rather than hang the box
+    }
+  }
+  __syncthreads();
+  const float* own = a.peer[a.rank] + (size_t)par * a.world * kXchgMaxFloats;
+  for (int i = threadIdx.x; i < a.n; i += blockDim.x) {
+    float sum = 0.f;
+    for (int r = 0; r < a.world; ++r) sum += __ldcv(own + (size_t)r * kXchgMaxFloats + i);
+    a.buf[i] = sum;
+  }
+}
+void peer_allreduce_small(const XchgArgs& a, cudaStream_t s) {
+  launch_chain(peer_allreduce_small_kernel, dim3(1), dim3(256), 0, s, a);
+}
+
 // ------------------------------------------------------------------ dataset rows from pinned host memory
 // 32 registers, 4 warps: one warp per SM sub-partition next to the fullest GEMM CTA of the step (BCE: 576 threads x 96
 // registers leave 1024 registers on two of the four sub-partitions).  With 39 registers the gather's CTAs and the GEMMs'
@@ -1318,6 +1357,7 @@ void kernels_init() {
   MAGIC_MAX_CARVEOUT(latent_forward_kernel);
   MAGIC_MAX_CARVEOUT(latent_metric_kernel);
   MAGIC_MAX_CARVEOUT(latent_backward_kernel);
+  MAGIC_MAX_CARVEOUT(peer_allreduce_small_kernel);
   MAGIC_MAX_CARVEOUT(gather_rows_host_kernel);   // (it lives beside GEMM CTAs for most of a step: same carveout or the SM serialises them)
   MAGIC_MAX_CARVEOUT(adam_dual_kernel);
   MAGIC_MAX_CARVEOUT(adam_dual_sharded_kernel);

@@ -117,6 +117,23 @@ void pairs_u8(const uint8_t* lock, const uint8_t* key, int B, int side, uint64_t
 // generator, and `planes` when it is not null
 void pairs_bits(const uint32_t* lock, const uint32_t* key, int wpr, int B, int side, uint64_t seed, uint64_t step,
                 __nv_bfloat16* planes, long long ld, uint32_t* xb3, int xb_ld, int* rot_cs_sn, int max_ctas, cudaStream_t s);
+// Small all-reduce (sum) over peer memory, for the handful of floats the data-parallel step exchanges (batch-axis
+// statistics of the cosine metric, the loss scalars, its two barriers): every rank stores its n values into slot `rank`
+// of every peer's exchange area, raises a flag there, waits for all flags in its own area and sums the slots in rank
+// order (same result on every rank, bit for bit).  One CTA; ~5 us against ~25 us for an NCCL call of this size, and the
+// step has four of them on its critical path.  Two areas alternate (epoch parity) so that a rank one call ahead does not
+// overwrite what a slower rank is still reading.  A peer that never arrives traps after kXchgTimeoutNs instead of hanging.
+constexpr int kXchgMaxFloats = 8192;
+constexpr unsigned long long kXchgTimeoutNs = 10000000000ull;
+// layout of one rank's exchange area (floats): [2 parities][world][kXchgMaxFloats] data, then [2][kMaxRanks] flags (u32)
+inline size_t xchg_area_floats(int world) { return (size_t)2 * world * kXchgMaxFloats + 2 * 8; }
+struct XchgArgs {
+  float* peer[8];                 // every rank's exchange area (own one included), as mapped here
+  float* buf;                     // local values in, sums out
+  int n, world, rank;
+  unsigned epoch;                 // 1, 2, 3, ... : the same sequence on every rank
+};
+void peer_allreduce_small(const XchgArgs& a, cudaStream_t s);
 // Gather of dataset rows that live in PINNED HOST memory (mapped into the device's address space): row idx[b] of
 // lock_all / key_all ([n_rows, wpr] words, wpr % 4 == 0) -> row b of out_lock / out_key in HBM.  The GPU reads the rows over
 // PCIe itself; a thin grid (one 128-thread CTA on some of the SMs, <= 32 registers) that fits beside every GEMM CTA.
