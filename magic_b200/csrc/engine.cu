@@ -1459,6 +1459,7 @@ std::string Engine::build_dp_plans() {
     e.flat_base = lin[layer].off; e.slice_len = slice_len_; e.src_rank = cfg.rank;
     e.world = cfg.world; e.gran_shift = kDpGranShift;
     for (int r = 0; r < cfg.world; ++r) e.peer[r] = peer_stage_[r] + (which == 2 ? alloc_len_ : 0);
+    if (const char* d = getenv("MAGIC_EPI_DBG")) e.dbg = atoi(d);   // timing experiments only: results are wrong
     return e;
   };
   {
