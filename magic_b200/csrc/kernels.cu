@@ -844,6 +844,34 @@ __device__ __forceinline__ uint32_t bit_at(const uint32_t* bm, int sp) {
   return sp < 0 ? 0u : (bm[sp >> 5] >> (sp & 31)) & 1u;
 }
 
+// The 32 pixels p0 .. p0 + 31 of the rotated image as one word, by ONE thread: the two Q15 source coordinates of
+// rotated_index() are linear in x, so along a row they advance by (2 cs, 2 sn) per pixel -- two adds, two shifts, the
+// bounds test and one shared-memory read per pixel, bit for bit the same map.  (One warp per word with a ballot spent
+// ~100 warp instructions on 32 pixels, most of them warp-uniform bookkeeping: 44 % of the generator's instructions,
+// profiles/r03q_generate_ncu_full_summary.csv.)  (x0, y0) = position of pixel p0; a word may wrap onto following rows.
+__device__ __forceinline__ uint32_t rotated_word(const uint32_t* bm, int side, int D, int cs, int sn, int p0, int x0, int y0) {
+  const int k0 = side << 14;
+  int x = x0;
+  int Y2 = 2 * y0 - side + 1;
+  int X2 = 2 * x0 - side + 1;
+  int ax = cs * X2 - sn * Y2 + k0, ay = sn * X2 + cs * Y2 + k0;
+  const int n = min(32, D - p0);
+  uint32_t word = 0u;
+  for (int j = 0; j < n; ++j) {
+    const int sx = ax >> 15, sy = ay >> 15;
+    if ((unsigned)sx < (unsigned)side && (unsigned)sy < (unsigned)side) {
+      const int sp = sy * side + sx;
+      word |= ((bm[sp >> 5] >> (sp & 31)) & 1u) << j;
+    }
+    ax += 2 * cs; ay += 2 * sn;
+    if (++x == side) {                                  // next row starts at x = 0
+      x = 0; Y2 += 2; X2 = 1 - side;
+      ax = cs * X2 - sn * Y2 + k0; ay = sn * X2 + cs * Y2 + k0;
+    }
+  }
+  return word;
+}
+
 // nibble -> four bf16 values (two packed words): bit k of the nibble -> 1.0 (0x3F80) in element k
 __device__ __forceinline__ uint2 expand_nibble(uint32_t n) {
   uint2 r;
@@ -925,22 +953,18 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
   }
   __syncthreads();
 
-  // ---- 2. rotated lock: one warp per 32-pixel word, ballot assembles the word.  Only words that reach into the
-  //         bounding box of the rotated lock can receive pixels.
+  // ---- 2. rotated lock: one thread per 32-pixel word (rotated_word).  Only words that reach into the bounding box of
+  //         the rotated lock can receive pixels.
   {
     const int cs = rot_q14[0], sn = rot_q14[1];
     const int xlo = rot_box[0], xhi = rot_box[1], ylo = rot_box[2], yhi = rot_box[3];
     const int w_begin = (ylo * side) >> 5, w_end = min(nwords, ((yhi * side + side - 1) >> 5) + 1);
-    for (int w = w_begin + warp; w < w_end; w += kGenThreads / 32) {
+    for (int w = w_begin + (int)threadIdx.x; w < w_end; w += kGenThreads) {
       const int p0 = w * 32;
       const int y0 = (int)__umulhi((uint32_t)p0, inv_side), x0 = p0 - y0 * side;
-      // a word lies on one row, or on the end of one and the start of the next
-      if (x0 + 31 < side ? (x0 > xhi || x0 + 31 < xlo) : (x0 > xhi && x0 + 31 - side < xlo)) continue;
-      int x = x0 + lane, y = y0;
-      if (x >= side) { x -= side; ++y; }
-      const uint32_t bit = (p0 + lane < D) ? bit_at(bm[0], rotated_index(x, y, side, cs, sn)) : 0u;
-      const uint32_t word = __ballot_sync(0xffffffffu, bit != 0u);
-      if (lane == 0) bm[2][w] = word;
+      // a word lies on one row, or on the end of one and the start of the next (side >= 32; smaller canvases: every word)
+      if (side >= 32 && (x0 + 31 < side ? (x0 > xhi || x0 + 31 < xlo) : (x0 > xhi && x0 + 31 - side < xlo))) continue;
+      bm[2][w] = rotated_word(bm[0], side, D, cs, sn, p0, x0, y0);
     }
   }
   // ---- 3. label (see the header comment).  3a: area and coordinate sums of lock and key, one thread per word:
@@ -1238,17 +1262,13 @@ __global__ void __maxnreg__(56) pairs_bits_kernel(const uint32_t* __restrict__ l
     __syncthreads();
     const int xlo = rbox[0], xhi = rbox[1], lo = rbox[2], hi = rbox[3];
     const int w_begin = (max(lo, 0) * side) >> 5, w_end = hi < 0 ? 0 : min(nwords, ((hi * side + side - 1) >> 5) + 1);
-    for (int w = w_begin + warp; w < w_end; w += kPairsBitsThreads / 32) {
+    for (int w = w_begin + (int)threadIdx.x; w < w_end; w += kPairsBitsThreads) {     // one thread per word (rotated_word)
       const int p0 = w * 32;
       const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
       const int x0 = p0 - y0 * side;
-      // a word lies on one row, or on the end of one and the start of the next
-      if (x0 + 31 < side ? (x0 > xhi || x0 + 31 < xlo) : (x0 > xhi && x0 + 31 - side < xlo)) continue;
-      int x = x0 + lane, y = y0;
-      while (x >= side) { x -= side; ++y; }
-      const uint32_t bit = (p0 + lane < D) ? bit_at(bm, rotated_index(x, y, side, cs, sn)) : 0u;
-      const uint32_t word = __ballot_sync(0xffffffffu, bit != 0u);
-      if (lane == 0) orot[w] = word | (w == bias_w ? bias_b : 0u);
+      // a word lies on one row, or on the end of one and the start of the next (side >= 32; smaller canvases: every word)
+      if (side >= 32 && (x0 + 31 < side ? (x0 > xhi || x0 + 31 < xlo) : (x0 > xhi && x0 + 31 - side < xlo))) continue;
+      orot[w] = rotated_word(bm, side, D, cs, sn, p0, x0, y0) | (w == bias_w ? bias_b : 0u);
     }
     __syncthreads();                            // the bitmap is reused by the next pair
   }
