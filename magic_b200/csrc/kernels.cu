@@ -1068,19 +1068,27 @@ __global__ void __launch_bounds__(kGenThreads) generate_pairs_kernel(uint64_t se
     for (int c = 0; c < 4; ++c)
       if (counts[kLabelRots + c] > best) { best = counts[kLabelRots + c]; tb = c; }
     const int tx = tb == 0 ? sh : tb == 1 ? -sh : 0, ty = tb == 2 ? sh : tb == 3 ? -sh : 0;
+    // one thread per lock word (the map is linear in x: u, v advance by (bcs, bsn) per pixel; same integers as 3b / 3c)
     int cnt = 0;
-    for (int w = warp; w < nwords; w += kGenThreads / 32) {
+    for (int w = threadIdx.x; w < nwords; w += kGenThreads) {
       const uint32_t lw = bm[0][w];
       if (lw == 0u) continue;
-      const uint32_t lb = (lw >> lane) & 1u;
       const int p0 = w * 32;
       const int y0 = (int)__umulhi((uint32_t)p0, inv_side);
-      int x = p0 - y0 * side + lane, y = y0;
-      if (x >= side) { x -= side; ++y; }
-      const int X = x - cLx - tx, Y = y - cLy - ty;
-      const int ax = cKx + sgn * ((bcs * X - bsn * Y + 8192) >> 14), ay = cKy + sgn * ((bsn * X + bcs * Y + 8192) >> 14);
-      const int sp = ((unsigned)ax < (unsigned)side && (unsigned)ay < (unsigned)side) ? ay * side + ax : zbit;
-      cnt += (int)((bm[1][sp >> 5] >> (sp & 31)) & lb);
+      int x = p0 - y0 * side, Y = y0 - cLy - ty;
+      int X = x - cLx - tx;
+      int u = bcs * X - bsn * Y + 8192, v = bsn * X + bcs * Y + 8192;
+      const int last = 31 - __clz(lw);                     // nothing to count behind the last set pixel
+      for (int j = 0; j <= last; ++j) {
+        const int ax = cKx + sgn * (u >> 14), ay = cKy + sgn * (v >> 14);
+        const int sp = ((unsigned)ax < (unsigned)side && (unsigned)ay < (unsigned)side) ? ay * side + ax : zbit;
+        cnt += (int)((bm[1][sp >> 5] >> (sp & 31)) & (lw >> j) & 1u);
+        u += bcs; v += bsn;
+        if (++x == side) {                                 // the word continues on the next row
+          x = 0; ++Y; X = -cLx - tx;
+          u = bcs * X - bsn * Y + 8192; v = bsn * X + bcs * Y + 8192;
+        }
+      }
     }
     cnt = __reduce_add_sync(0xffffffffu, cnt);
     if (lane == 0 && cnt) atomicAdd(&counts[kLabelRots + 4], cnt);
