@@ -32,11 +32,18 @@ constexpr int kMaxSegs = 3;
 // epilogues, 16 for the sigmoid-BCE epilogue whose ~20 instructions per element need four warps per scheduler to
 // hide MUFU and TMEM latencies.
 __host__ __device__ constexpr int epi_warps(int epi) { return epi == 3 /*EPI_BCE*/ ? 16 : 8; }
+// A_BITS kernels (packed first-layer operand) run FOUR epilogue warps, one per TMEM lane quarter: with their four
+// expander warps that is 10 warps = 320 threads, the footprint of every other GEMM CTA, and a CTA of the batch generator /
+// dataset feed (384 threads x 56 registers) fits on the same SM: 3 + 3 warps per sub-partition.  With eight (448 threads,
+// 4 warps on two of the sub-partitions) it did not, and whatever part of the generator had not finished under the first
+// half of the backward pass delayed the first-layer wgrad.  Their items are long (K = 8192 .. 13355 per tile), so an
+// epilogue twice as slow still hides under the next item's main loop.
+__host__ __device__ constexpr int epi_warps(int epi, bool a_bits) { return a_bits ? 4 : epi_warps(epi); }
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 // A_BITS variants (the first encoder layer: its A operand is a binary image, kept in HBM as 1 bit per pixel): four more
 // warps expand the packed bits of a pipeline stage into the bf16 swizzle layout the MMA reads -- see BitsA.
 constexpr int kExpandWarps = 4;     // one per pipeline stage of the 256-wide tile configuration
-__host__ __device__ constexpr int gemm_threads(int epi, bool a_bits) { return gemm_threads(epi) + (a_bits ? 32 * kExpandWarps : 0); }
+__host__ __device__ constexpr int gemm_threads(int epi, bool a_bits) { return 64 + 32 * epi_warps(epi, a_bits) + (a_bits ? 32 * kExpandWarps : 0); }
 constexpr uint32_t kStageBytesA = kBlockM * kBlockK * 2;   // 16 KiB
 constexpr uint32_t kStageBytesB = kBlockN * kBlockK * 2;   // 32 KiB
 constexpr uint32_t kStageBytes = kStageBytesA + kStageBytesB;
@@ -750,7 +757,7 @@ template <bool A_MN, bool B_MN, int EPI, int BN, bool A_BITS = false, bool CG2 =
 // 112 registers: three of this kernel's warps (3 x 32 x 112) and three warps of the batch generator (3 x 32 x 56) fit
 // the 16K registers of one SM sub-partition, so the generator's CTA stays co-resident with every GEMM variant; it is
 // the 576-thread BCE variant has five warps on a sub-partition, hence 96.
-__global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
+__global__ void __maxnreg__(epi_warps(EPI, A_BITS) == 16 ? 96 : 112) gemm_tcgen05_kernel(const __grid_constant__ GemmArgs args) {
 #define MAGIC_TR(slot)                                                                  \
   do {                                                                                  \
     if (args.trace) args.trace[(size_t)blockIdx.x * 64 + (slot)] = clock64();           \
@@ -801,7 +808,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     }
     for (int i = 0; i < kAcc; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
-      ptx::mbar_init(&tempty_bar[i], CG2 ? 2 * epi_warps(EPI) : epi_warps(EPI) * 32);   // pair: one arrival per epilogue warp of both CTAs
+      ptx::mbar_init(&tempty_bar[i], CG2 ? 2 * epi_warps(EPI, A_BITS) : epi_warps(EPI, A_BITS) * 32);   // pair: one arrival per epilogue warp of both CTAs
     }
     ptx::fence_barrier_init();
   } else if (warp == 1) {
@@ -966,12 +973,12 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
       // following kernels' CTAs on the SMs for the whole duration and starves the generator's side stream.
       ptx::grid_dep_launch();
     }
-  } else if (warp < 2 + epi_warps(EPI)) {
+  } else if (warp < 2 + epi_warps(EPI, A_BITS)) {
     // ------------------------------------------------------------ epilogue warps
     // TMEM lane quarter = warp % 4 (hardware rule); the two warps of a quarter split the 32-column chunks
     // even/odd, so every scheduler has two epilogue warps to overlap latencies with.
     const int q = warp & 3;
-    constexpr int kGroups = epi_warps(EPI) / 4;          // warps per lane quarter; chunk c belongs to group c % kGroups
+    constexpr int kGroups = epi_warps(EPI, A_BITS) / 4;  // warps per lane quarter; chunk c belongs to group c % kGroups
     constexpr int kMaxOwn = (BN / 32 + kGroups - 1) / kGroups;
     const int grp = (warp - 2) >> 2;
     uint32_t iter = 0;
@@ -1046,7 +1053,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
           epilogue_chunk<EPI == EPI_ADAM ? EPI_STORE_F32 : EPI, true>(e, t, r, row, it.n0 + c * 32, it.M, it.N, loss_acc, xwk);
         }
       };
-      constexpr int kBatch = epi_warps(EPI) == 16 ? 2 : 1;   // 8-warp epilogues own 4 chunks: one at a time (registers)
+      constexpr int kBatch = epi_warps(EPI, A_BITS) == 16 ? 2 : 1;   // 8-warp epilogues own 4 chunks: one at a time (registers)
 #pragma unroll
       for (int k = 0; k < kMaxOwn; k += kBatch) {
         const int c0 = grp + k * kGroups, c1 = grp + (k + 1) * kGroups;
@@ -1088,10 +1095,10 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     // l + 64, l + 96), so four stages are being expanded at once, each with its own wait -> store -> fence -> arrive
     // round trip (one group walking the stages in turn was bound by that latency: 920 cycles per k-block).  The bits of
     // a warp's next k-block are fetched while it expands the current one -- four k-block times ahead of their use.
-    // (448 threads: two more warps per stage -- 576 threads -- do not fit the 16 K registers of an SM sub-partition at
+    // (a second expander warp per stage -- measured with eight epilogue warps: 576 threads -- did not fit the 16 K registers of an SM sub-partition at
     // this kernel's 112 registers, and one warp per stage already keeps up with the MMAs: profiles/r01p)
     static_assert(kNS >= kExpandWarps, "expander warp e serves the k-blocks e, e + 4, ... of the CTA's sequence");
-    const int ew = warp - (2 + epi_warps(EPI));
+    const int ew = warp - (2 + epi_warps(EPI, A_BITS));
     struct Cursor { KbWalk walk; int w, m0, g, kblocks; bool valid; };
     auto open = [&](Cursor& c) {
       c.valid = false;
@@ -1182,7 +1189,7 @@ __global__ void __maxnreg__(epi_warps(EPI) == 16 ? 96 : 112) gemm_tcgen05_kernel
     if (threadIdx.x == 64 && work0 < total_work) {
       float sum = 0.f;
 #pragma unroll
-      for (int w = 0; w < epi_warps(EPI); ++w) sum += *reinterpret_cast<const float*>(smem + kTileStageOffset + w * 2048);
+      for (int w = 0; w < epi_warps(EPI, A_BITS); ++w) sum += *reinterpret_cast<const float*>(smem + kTileStageOffset + w * 2048);
       atomicAdd(args.epi[0].scalar, sum * args.epi[0].alpha);
     }
   }
