@@ -1490,15 +1490,15 @@ std::string Engine::build_dp_plans() {
       p.abits[1].base = in_[alt].xb3 + (size_t)B * xb_ld_; p.abits[1].pitch = xb_ld_; p.abits[1].rows = 2 * B;
       p.kmask[0] = in_[alt].kmask + km_wg_off_[0]; p.kmask[1] = in_[alt].kmask + km_wg_off_[1]; p.kmask_words = km_wg_words_;
     }
-    // MAGIC_DP_FUSE_SMALL=1: the small layers' weight gradients ride in this launch as appended whole-K problems, each
-    // scattering its tiles to the owners like the main problem (one rank does the same with plain stores:
-    // pl_wg_enc0_fused_), instead of six split-K launches accumulating locally, a window clear before and two push_range
-    // launches after them (0.15 ms of the step).  Correct (tests/test_dp_gpu.py passes with it) but OFF: with the scatter
-    // epilogue the appended items cost the launch 0.20 ms (0.524 -> 0.728 ms at 2 GPUs, step 2.19 -> 2.25 ms,
-    // profiles/r03k_dp_probe_n2.txt) where the plain-store launch absorbs them in its last wave; not yet understood.
+    // The small layers' weight gradients ride in this launch as appended whole-K problems, each scattering its tiles to
+    // the owners like the main problem (one rank does the same with plain stores: pl_wg_enc0_fused_), instead of six
+    // split-K launches accumulating locally, a window clear before and two push_range launches after them (0.15 ms of the
+    // step): 2 GPUs 2.131 -> 2.049 ms per step (profiles/r03u_dp_probe_n2.txt).  MAGIC_DP_FUSE_SMALL=0 keeps them apart.
+    // (While the packed-operand kernels could not share an SM with the generator this LOST 0.06 ms: the shorter backward
+    // pass left more of the generator to block this launch -- profiles/r03k_dp_probe_n2.txt.)
     GemmProblem pf = p;
     size_t nx = 0;
-    bool want = getenv("MAGIC_DP_FUSE_SMALL") && atoi(getenv("MAGIC_DP_FUSE_SMALL")) != 0;
+    bool want = !(getenv("MAGIC_DP_FUSE_SMALL") && atoi(getenv("MAGIC_DP_FUSE_SMALL")) == 0);
     for (auto& sp : small_wg_) { nx += sp.ngroups; want = want && sp.nseg == p.nseg; }
     if (want && nx <= (size_t)kMaxExtra) {
       for (size_t i = 0; i < small_wg_.size(); ++i) {

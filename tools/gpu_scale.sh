@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 if [ "$N" = "2" ]; then
 timeout 600 python -m pytest tests/test_dp_gpu.py -m gpu -q > gpurun_out/dp_tests.log 2>&1; echo "dp tests (fused) rc=$?"; tail -3 gpurun_out/dp_tests.log
 MAGIC_DP_MODE=allreduce timeout 600 python -m pytest tests/test_dp_gpu.py -m gpu -q > gpurun_out/dp_tests_allreduce.log 2>&1; echo "dp tests (NCCL all-reduce baseline) rc=$?"; tail -3 gpurun_out/dp_tests_allreduce.log
-MAGIC_DP_FUSE_SMALL=1 MAGIC_DP_XCHG=0 timeout 600 python -m pytest tests/test_dp_gpu.py -m gpu -q > gpurun_out/dp_tests_variants.log 2>&1; echo "dp tests (small layers in the scatter launch, NCCL exchanges) rc=$?"; tail -3 gpurun_out/dp_tests_variants.log
+MAGIC_DP_FUSE_SMALL=0 MAGIC_DP_XCHG=0 timeout 600 python -m pytest tests/test_dp_gpu.py -m gpu -q > gpurun_out/dp_tests_variants.log 2>&1; echo "dp tests (small layers on their own, NCCL exchanges) rc=$?"; tail -3 gpurun_out/dp_tests_variants.log
 fi
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 100 --warmup 10 --no-cpu-baseline ${SCALE_ARGS} > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench n$N rc=$?"
 python - <<PY
