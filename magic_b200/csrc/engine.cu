@@ -117,7 +117,7 @@ Engine::~Engine() {
   void* ptrs[] = {p_, g1_, g2_, m1_, v1_, m2_, v2_, w_hi_, w_lo_, in_[0].X.hi, in_[1].X.hi, heads_, z_, zdec_.hi, zdec_.lo, D1_.hi, D1_.lo,
                   D2_.hi, D2_.lo, dA_.hi, dA_.lo, dD2_.hi, dD2_.lo, dD1_.hi, dD1_.lo, dz_dec_, dheads_.hi, dheads_.lo, ws_,
                   statbuf_, g_row_, dist_, losses_dev_, stage_x_, stage_labels_, stage_eps_,
-                  in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_, not_binary_};
+                  in_[0].xb3, in_[1].xb3, in_[0].kmask, in_[1].kmask, in_[0].labels, in_[1].labels, in_[0].rot, in_[1].rot, stage_, barrier_buf_, bits_stage_, not_binary_, gather_idx_};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (auto& a : H_) { if (a.hi) cudaFree(a.hi); if (a.lo) cudaFree(a.lo); }
@@ -804,6 +804,7 @@ std::string Engine::feed_pairs_bits_host(const uint32_t* h_lock, const uint32_t*
   if (wpr < (D + 31) / 32) return "feed_pairs_bits_host: words_per_row is smaller than ceil(D / 32)";
   const size_t plane = sizeof(uint32_t) * (size_t)B * wpr;
   if (bits_stage_bytes_ < 2 * plane) {
+    flush_expand(in_[0], false); flush_expand(in_[1], false);     // a staged batch still waiting in the old staging area
     MAGIC_CUDA(cudaStreamSynchronize(gen_stream_));
     if (bits_stage_) cudaFree(bits_stage_);
     bits_stage_ = nullptr; bits_stage_bytes_ = 0;
@@ -854,6 +855,7 @@ std::string Engine::feed_pairs_bits_gather(const uint32_t* h_lock_all, const uin
   }
   const size_t plane = sizeof(uint32_t) * (size_t)B * wpr;
   if (bits_stage_bytes_ < 2 * plane) {
+    flush_expand(in_[0], false); flush_expand(in_[1], false);     // a staged batch still waiting in the old staging area
     MAGIC_CUDA(cudaStreamSynchronize(gen_stream_));
     if (bits_stage_) cudaFree(bits_stage_);
     bits_stage_ = nullptr; bits_stage_bytes_ = 0;
