@@ -405,12 +405,14 @@ def test_first_layer_adam_in_the_wgrad_epilogue(name, exp, batch, precision):
     on, off, off2 = runs
     # Two runs of ONE setting already differ: the batch-axis statistics are summed with atomics, their last bits move
     # the gradients' last bits, and Adam's first steps turn a near-zero gradient's sign into +-lr (measured on 8d / 4096:
-    # 1.9e-4 of the first layer's norm after four steps).  The fused path must stay inside that run-to-run band.
+    # 1.9e-4 of the first layer's norm after four steps).  The fused path must stay inside that run-to-run band (x10, floor
+    # 1e-4: a different FMA contraction of the same expression in the two kernels is enough to leave a x5 band; a wrong
+    # update -- a skipped or doubled tile -- is 1e-2).
     rel = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-30)))
     assert rel(on[0], off[0]) <= max(5.0 * rel(off2[0], off[0]), 1e-4), (rel(on[0], off[0]), rel(off2[0], off[0]))
     for n in on[1]:
         floor = rel_l2(off2[1][n], off[1][n])
-        assert rel_l2(on[1][n], off[1][n]) <= max(5.0 * floor, 2e-5), (n, floor)
+        assert rel_l2(on[1][n], off[1][n]) <= max(10.0 * floor, 1e-4), (n, floor)
     for k in on[2]:
         floor = rel_l2(off2[2][k], off[2][k])
-        assert rel_l2(on[2][k], off[2][k]) <= max(5.0 * floor, 2e-5), (k, floor)
+        assert rel_l2(on[2][k], off[2][k]) <= max(10.0 * floor, 1e-4), (k, floor)
