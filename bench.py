@@ -555,6 +555,8 @@ def run_b200(args):
                       "the forward pass has produced them, the backward pass and the update overlap the host's next call; the "
                       "timed region ends with a device synchronize)",
                "data": "real: tests/golden/overlap_micro_100.npz + OVERLAP_AREAS[:100]",
+               "note": "may exceed `value`: value's loop runs the on-device generator (shapes, rotation, max-overlap label search: a "
+                       "0.7 ms kernel under every step), this loop copies 41 MB and runs the lighter rotation / layout kernel",
                "input_density": [round(real_density[0], 4), round(real_density[1], 4)]}
         # the reference-signature call: partial_fit(X[B,120000] float32) from pinned host memory (PCIe-bound)
         X_dev, y_dev = eng.export_batch()
